@@ -1,0 +1,310 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY. C entry points (JSON in, JSON out) so the
+// Python tests and bench.py's cpu_baseline leg can drive the CPU restatement.
+// Nothing under kubernetes_b200/ may include or link this.
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "json.hpp"
+#include "model.hpp"
+#include "scheduler.hpp"
+
+using namespace oracle;
+namespace json = ksb::json;
+
+static void put_kv(std::string& out, const char* k, const std::string& v, bool comma = true) {
+  json::escape_to(out, k);
+  out += ":";
+  json::escape_to(out, v);
+  if (comma) out += ",";
+}
+
+static void result_to_json(std::string& out, const ScheduleResult& r) {
+  out += "{";
+  put_kv(out, "host", r.host);
+  out += "\"status\":" + std::to_string((int)r.status) + ",";
+  out += "\"filtered\":" + std::to_string(r.num_filtered) + ",";
+  out += "\"score\":" + std::to_string(r.score) + ",";
+  put_kv(out, "message", r.message);
+  out += "\"devices\":{";
+  bool first = true;
+  for (auto& kv : r.binding) {
+    if (!first) out += ",";
+    first = false;
+    json::escape_to(out, kv.first);
+    out += ":[";
+    for (size_t i = 0; i < kv.second.size(); ++i) {
+      if (i) out += ",";
+      json::escape_to(out, kv.second[i]);
+    }
+    out += "]";
+  }
+  out += "}}";
+}
+
+static void apply_options(Oracle& o, const json::Value& v) {
+  o.workers = (int)v.get_int("workers", 1);
+  o.hardPodAffinityWeight = (int)v.get_int("hardPodAffinityWeight", 1);
+  o.lastNodeIndex = (uint64_t)v.get_int("lastNodeIndex", 0);
+  if (const json::Value* w = v.find("weights"); w && !w->is_null()) {
+    o.weights.least_requested = w->get_int("LeastRequestedPriority", 1);
+    o.weights.balanced = w->get_int("BalancedResourceAllocation", 1);
+    o.weights.selector_spread = w->get_int("SelectorSpreadPriority", 1);
+    o.weights.node_affinity = w->get_int("NodeAffinityPriority", 1);
+    o.weights.taint_toleration = w->get_int("TaintTolerationPriority", 1);
+    o.weights.inter_pod_affinity = w->get_int("InterPodAffinityPriority", 1);
+    o.weights.prefer_avoid = w->get_int("NodePreferAvoidPodsPriority", 10000);
+  }
+}
+
+static std::string run_stream(const json::Value& req) {
+  json::Value cv;
+  const json::Value* c = req.find("cluster");
+  if (!c) {
+    cv = json::parse_file(req.get_str("cluster_path"));
+    c = &cv;
+  }
+  ksb::Cluster cl = ksb::cluster_from_json(*c);
+  Oracle o;
+  apply_options(o, req);
+  o.load(cl);
+  int64_t limit = req.get_int("limit", -1);
+  size_t n = cl.pods.size();
+  if (limit >= 0 && (size_t)limit < n) n = (size_t)limit;
+  std::string out = "{\"results\":[";
+  auto t0 = std::chrono::steady_clock::now();
+  std::vector<ScheduleResult> results;
+  results.reserve(n);
+  for (size_t i = 0; i < n; ++i) results.push_back(o.schedule_one(cl.pods[i]));
+  auto t1 = std::chrono::steady_clock::now();
+  for (size_t i = 0; i < n; ++i) {
+    if (i) out += ",";
+    result_to_json(out, results[i]);
+  }
+  double secs = std::chrono::duration<double>(t1 - t0).count();
+  out += "],\"seconds\":" + std::to_string(secs) + ",\"pods\":" + std::to_string(n) +
+         ",\"lastNodeIndex\":" + std::to_string(o.lastNodeIndex) + "}";
+  return out;
+}
+
+// priorityFunction(map, reduce, meta) adapter of priorities/test_util.go:45-61: Map on every
+// listed node, then Reduce over all of them (no predicate filtering).
+static std::string run_priority(const json::Value& req) {
+  ksb::Cluster cl = ksb::cluster_from_json(*req.find("cluster"));
+  ksb::Pod pod = ksb::pod_from_json(*req.find("pod"));
+  Oracle o;
+  apply_options(o, req);
+  o.load(cl);
+  o.cachedNodeInfoMap = o.cache.nodes;
+  std::vector<NodePtr> nodes;
+  for (auto& n : cl.nodes) nodes.push_back(o.cachedNodeInfoMap.at(n.name).node);
+  std::string name = req.get_str("name");
+  HostPriorityList list;
+  Oracle::PriorityMeta pm = o.make_priority_meta(pod);
+  std::string err;
+  if (name == "InterPodAffinityPriority") {
+    if (!o.inter_pod_affinity_priority(pod, nodes, &list, &err)) return "{\"error\":\"" + err + "\"}";
+  } else {
+    for (auto& n : nodes) {
+      const NodeInfo& ni = o.cachedNodeInfoMap.at(n->name);
+      int64_t s = 0;
+      if (name == "LeastRequestedPriority") s = Oracle::least_requested_map(pm, ni);
+      else if (name == "BalancedResourceAllocation") s = Oracle::balanced_map(pm, ni);
+      else if (name == "SelectorSpreadPriority") s = Oracle::selector_spread_map(pod, pm, ni);
+      else if (name == "NodeAffinityPriority") {
+        if (!Oracle::node_affinity_map(pod, ni, &s, &err)) return "{\"error\":\"" + err + "\"}";
+      } else if (name == "TaintTolerationPriority") s = Oracle::taint_toleration_map(pm, ni);
+      else if (name == "NodePreferAvoidPodsPriority") s = Oracle::prefer_avoid_map(pod, ni);
+      else return "{\"error\":\"unknown priority\"}";
+      list.push_back({n->name, s});
+    }
+    if (name == "SelectorSpreadPriority") o.selector_spread_reduce(list);
+    else if (name == "NodeAffinityPriority") Oracle::normalize_reduce(list, false);
+    else if (name == "TaintTolerationPriority") Oracle::normalize_reduce(list, true);
+  }
+  std::string out = "{\"scores\":[";
+  for (size_t i = 0; i < list.size(); ++i) {
+    if (i) out += ",";
+    out += "{";
+    put_kv(out, "host", list[i].host);
+    out += "\"score\":" + std::to_string(list[i].score) + "}";
+  }
+  out += "]}";
+  return out;
+}
+
+// One predicate (or the whole DefaultProvider set, name "all") on one node.
+static std::string run_predicate(const json::Value& req) {
+  ksb::Cluster cl = ksb::cluster_from_json(*req.find("cluster"));
+  ksb::Pod pod = ksb::pod_from_json(*req.find("pod"));
+  Oracle o;
+  apply_options(o, req);
+  o.load(cl);
+  o.cachedNodeInfoMap = o.cache.nodes;
+  std::string node_name = req.get_str("node");
+  const NodeInfo& ni = o.cachedNodeInfoMap.at(node_name);
+  std::string name = req.get_str("name");
+  PredicateMeta meta = o.make_predicate_meta(pod);
+  std::vector<std::string> fails;
+  std::string err;
+  bool hard_error = false;
+  if (name == "PodFitsResources") {
+    Oracle::pod_fits_resources(meta, ni, &fails);
+  } else if (name == "PodFitsHost") {
+    if (!pod.node_name.empty() && pod.node_name != ni.node->name) fails.push_back("HostName");
+  } else if (name == "PodFitsHostPorts") {
+    if (!meta.podPorts.empty() && ports_conflict(ni.usedPorts, meta.podPorts)) fails.push_back("PodFitsHostPorts");
+  } else if (name == "PodMatchNodeSelector") {
+    if (!Oracle::pod_matches_node_labels(pod, *ni.node)) fails.push_back("MatchNodeSelector");
+  } else if (name == "PodToleratesNodeTaints") {
+    for (auto& t : ni.taints) {
+      if (t.effect != "NoSchedule" && t.effect != "NoExecute") continue;
+      if (!tolerations_tolerate_taint(pod.tolerations, t)) {
+        fails.push_back("PodToleratesNodeTaints");
+        break;
+      }
+    }
+  } else if (name == "CheckNodeMemoryPressure") {
+    if (meta.bestEffort && ni.memoryPressure == "True") fails.push_back("NodeUnderMemoryPressure");
+  } else if (name == "CheckNodeDiskPressure") {
+    if (ni.diskPressure == "True") fails.push_back("NodeUnderDiskPressure");
+  } else if (name == "CheckNodeCondition") {
+    Oracle::check_node_condition(ni, &fails);
+  } else if (name == "MatchInterPodAffinity" || name == "all") {
+    std::vector<PodPtr> allPods = o.all_pods();
+    std::vector<Oracle::TermProbe> aff, anti;
+    if (pod.affinity.present) {
+      for (auto& t : required_terms(pod.affinity.pod)) aff.push_back(Oracle::probe(pod, t));
+      for (auto& t : required_terms(pod.affinity.anti)) anti.push_back(Oracle::probe(pod, t));
+    }
+    if (name == "all") {
+      if (!o.pod_fits_on_node(pod, meta, ni, allPods, aff, anti, &fails, &err)) hard_error = true;
+    } else {
+      if (!o.inter_pod_affinity_matches(pod, meta, ni, allPods, aff, anti, &fails, &err)) hard_error = true;
+    }
+  } else if (name == "HasExtendedResources") {
+    std::map<std::string, std::vector<std::string>> binding;
+    std::string why;
+    bool ok = Oracle::has_extended_resources(pod, ni, &binding, &why);
+    if (!ok) fails.push_back(why);
+    std::string out = std::string("{\"fits\":") + (ok ? "true" : "false") + ",\"reasons\":[";
+    if (!ok) json::escape_to(out, why);
+    out += "],\"devices\":{";
+    bool first = true;
+    for (auto& kv : binding) {
+      if (!first) out += ",";
+      first = false;
+      json::escape_to(out, kv.first);
+      out += ":[";
+      for (size_t i = 0; i < kv.second.size(); ++i) {
+        if (i) out += ",";
+        json::escape_to(out, kv.second[i]);
+      }
+      out += "]";
+    }
+    out += "}}";
+    return out;
+  } else {
+    return "{\"error\":\"unknown predicate\"}";
+  }
+  std::string out = std::string("{\"fits\":") + ((fails.empty() && !hard_error) ? "true" : "false") + ",\"reasons\":[";
+  for (size_t i = 0; i < fails.size(); ++i) {
+    if (i) out += ",";
+    json::escape_to(out, fails[i]);
+  }
+  out += "],\"error\":";
+  json::escape_to(out, hard_error ? err : "");
+  out += "}";
+  return out;
+}
+
+// isDeviceAMatch (core/extended_resources.go:152-167) on one device.
+static std::string run_device_match(const json::Value& req) {
+  ksb::ExtendedDevice dev;
+  const json::Value* d = req.find("device");
+  dev.id = d->get_str("id");
+  dev.attributes = ksb::detail::strmap(d->find("attributes"));
+  std::vector<ksb::SelectorRequirement> reqs = ksb::detail::reqs(req.find("required"));
+  bool ok = false;
+  std::string err;
+  bool noerr = Oracle::is_device_a_match(dev, reqs, &ok, &err);
+  std::string out = std::string("{\"match\":") + ((noerr && ok) ? "true" : "false") + ",\"error\":";
+  json::escape_to(out, noerr ? "" : err);
+  out += "}";
+  return out;
+}
+
+// Dump one node's NodeInfo aggregates after loading the cluster (cache tests).
+static std::string run_node_info(const json::Value& req) {
+  ksb::Cluster cl = ksb::cluster_from_json(*req.find("cluster"));
+  Oracle o;
+  o.load(cl);
+  for (auto& p : req.get_arr("forget")) o.cache.ForgetPod(ksb::pod_from_json(p));
+  const NodeInfo& ni = o.cache.nodes.at(req.get_str("node"));
+  std::string out = "{";
+  out += "\"requested\":{\"cpu\":" + std::to_string(ni.requested.MilliCPU) + ",\"memory\":" +
+         std::to_string(ni.requested.Memory) + ",\"gpu\":" + std::to_string(ni.requested.NvidiaGPU) +
+         ",\"ephemeral\":" + std::to_string(ni.requested.EphemeralStorage) + ",\"scalars\":{";
+  bool first = true;
+  for (auto& kv : ni.requested.Scalar) {
+    if (!first) out += ",";
+    first = false;
+    json::escape_to(out, kv.first);
+    out += ":" + std::to_string(kv.second);
+  }
+  out += "}},\"nonzero\":{\"cpu\":" + std::to_string(ni.nonzero.MilliCPU) + ",\"memory\":" +
+         std::to_string(ni.nonzero.Memory) + "},\"pods\":" + std::to_string(ni.pods.size()) + ",\"usedPorts\":[";
+  first = true;
+  for (auto& p : ni.usedPorts) {
+    if (!first) out += ",";
+    first = false;
+    json::escape_to(out, p);
+  }
+  out += "],\"available\":{";
+  first = true;
+  for (auto& kv : ni.ext.available) {
+    if (!first) out += ",";
+    first = false;
+    json::escape_to(out, kv.first);
+    out += ":[";
+    bool f2 = true;
+    for (auto& d : kv.second) {
+      if (!f2) out += ",";
+      f2 = false;
+      json::escape_to(out, d.first);
+    }
+    out += "]";
+  }
+  out += "}}";
+  return out;
+}
+
+extern "C" {
+
+// Generic entry: {"op": "stream" | "priority" | "predicate" | "device_match" | "node_info", ...}.
+// Returns a malloc'd NUL-terminated JSON string; free with oracle_free.
+char* oracle_call(const char* json_in) {
+  std::string out;
+  try {
+    json::Value req = json::parse(json_in);
+    std::string op = req.get_str("op");
+    if (op == "stream") out = run_stream(req);
+    else if (op == "priority") out = run_priority(req);
+    else if (op == "predicate") out = run_predicate(req);
+    else if (op == "device_match") out = run_device_match(req);
+    else if (op == "node_info") out = run_node_info(req);
+    else out = "{\"error\":\"unknown op\"}";
+  } catch (const std::exception& e) {
+    out = "{\"error\":";
+    json::escape_to(out, e.what());
+    out += "}";
+  }
+  char* p = (char*)malloc(out.size() + 1);
+  memcpy(p, out.c_str(), out.size() + 1);
+  return p;
+}
+
+void oracle_free(char* p) { free(p); }
+
+}  // extern "C"
