@@ -1,0 +1,155 @@
+/*
+ * ksched_b200 — C-ABI of the B200 scheduling engine.
+ *
+ * This is the drop-in boundary for ONE path of rotorliu/kubernetes: the body of
+ * genericScheduler.Schedule (findNodesThatFit -> PrioritizeNodes -> selectHost) with the
+ * DefaultProvider predicates/priorities and the fork's device-attribute matching.
+ * A Go shim implementing algorithm.ScheduleAlgorithm binds these symbols through cgo
+ * (INTEGRATION.md shows the stub). Paths cited below are relative to
+ * /root/reference/plugin/pkg/scheduler.
+ *
+ * Conventions
+ *  - Objects cross the boundary as flat little-endian byte records (include/ksb_wire.hpp
+ *    documents the layout): one buffer per Node / Pod / selector owner. cgo may not pass Go
+ *    memory that itself holds Go pointers, so byte buffers are the idiomatic form; the
+ *    engine copies what it needs before returning and never retains caller memory.
+ *  - Every call returns 0 on success, <0 on error (text via ksb_last_error).
+ *  - ksb_schedule* are called from one thread at a time (the reference calls Schedule from a
+ *    single goroutine, scheduler.go:179). Mutators may be called from other threads; they
+ *    are serialised by an internal mutex and become visible at the next ksb_schedule* call,
+ *    which is the reference's snapshot point (core/generic_scheduler.go:122).
+ *  - There is no CPU fallback: if no CUDA device is usable ksb_create fails.
+ */
+#ifndef KSCHED_B200_H_
+#define KSCHED_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ksb_engine ksb_engine;
+
+/* Priority weights and capacities. Replaces the priorityConfigs / hardPodAffinityWeight
+ * arguments of core.NewGenericScheduler (core/generic_scheduler.go:1013-1035) as resolved by
+ * factory.CreateFromKeys (factory/factory.go:897-958) from defaults.go:217-257. */
+typedef struct ksb_config {
+  int32_t device;                   /* CUDA device ordinal */
+  int32_t w_least_requested;        /* LeastRequestedPriority        (default 1) */
+  int32_t w_balanced;               /* BalancedResourceAllocation    (default 1) */
+  int32_t w_selector_spread;        /* SelectorSpreadPriority        (default 1) */
+  int32_t w_node_affinity;          /* NodeAffinityPriority          (default 1) */
+  int32_t w_taint_toleration;       /* TaintTolerationPriority       (default 1) */
+  int32_t w_inter_pod_affinity;     /* InterPodAffinityPriority      (default 1) */
+  int32_t w_prefer_avoid;           /* NodePreferAvoidPodsPriority   (default 10000) */
+  int32_t hard_pod_affinity_weight; /* v1.DefaultHardPodAffinitySymmetricWeight = 1 */
+  int32_t label_words;              /* 64-bit words of the per-node label bitset (default 4) */
+  int32_t shard_rank;               /* node-table shard held by this engine (0 when unsharded) */
+  int32_t shard_count;              /* number of shards (1 when unsharded) */
+  int32_t group_size;               /* pods evaluated per speculative group (0 = default) */
+} ksb_config;
+
+/* Fill *cfg with the DefaultProvider values (algorithmprovider/defaults/defaults.go:217-257). */
+void ksb_config_default(ksb_config* cfg);
+
+/* core.NewGenericScheduler (core/generic_scheduler.go:1013-1035). */
+ksb_engine* ksb_create(const ksb_config* cfg, char* err, size_t err_len);
+void ksb_destroy(ksb_engine* e);
+const char* ksb_last_error(const ksb_engine* e);
+
+/* ---- state: the decorator of schedulercache.Cache (schedulercache/interface.go:61-121) ---- */
+
+/* Cache.AddNode / UpdateNode (schedulercache/cache.go:347-371) -> NodeInfo.SetNode
+ * (schedulercache/node_info.go:469-491). buf = Node record. */
+int32_t ksb_node_upsert(ksb_engine* e, const uint8_t* buf, size_t len);
+/* Cache.RemoveNode (schedulercache/cache.go:373-387). */
+int32_t ksb_node_remove(ksb_engine* e, const char* name, size_t name_len);
+/* Cache.AssumePod / AddPod (schedulercache/cache.go:118-137, :223-260) -> NodeInfo.AddPod
+ * (node_info.go:329-356). buf = Pod record with NodeName (and Assigned device ids) set. */
+int32_t ksb_pod_add(ksb_engine* e, const uint8_t* buf, size_t len);
+/* Cache.ForgetPod / RemovePod (schedulercache/cache.go:170-197, :283-312) -> NodeInfo.RemovePod
+ * (node_info.go:359-419). The pod is identified by namespace/name. */
+int32_t ksb_pod_remove(ksb_engine* e, const char* ns, size_t ns_len, const char* name, size_t name_len);
+
+/* The listers SelectorSpread reads (algorithm/priorities/metadata.go:69-96; algorithm/types.go
+ * ServiceLister/ControllerLister/ReplicaSetLister/StatefulSetLister). kind: 0 service, 1 RC,
+ * 2 ReplicaSet, 3 StatefulSet. buf = SelectorOwner record. */
+int32_t ksb_selector_owner_upsert(ksb_engine* e, int32_t kind, const uint8_t* buf, size_t len);
+int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, size_t ns_len, const char* name,
+                                  size_t name_len);
+
+/* ---- the hot path ---- */
+
+enum {
+  KSB_SCHEDULED = 0,        /* host chosen */
+  KSB_NO_NODES = 1,         /* ErrNoNodesAvailable (core/generic_scheduler.go:58,117) */
+  KSB_FIT_ERROR = 2,        /* *core.FitError (core/generic_scheduler.go:133-139) */
+  KSB_SCHEDULE_ERROR = 3    /* any other error the reference returns from Schedule */
+};
+
+#define KSB_MAX_EXT_ENTRIES 4
+#define KSB_MAX_DEVICES 32
+
+/* Return value of ScheduleAlgorithm.Schedule (algorithm/scheduler_interface.go:48-61):
+ * (selectedMachine, v1.ExtendedResourceBinding, error). */
+typedef struct ksb_result {
+  int32_t status;          /* KSB_* */
+  int32_t node_index;      /* row of the chosen node in bytewise name order, -1 if none */
+  int32_t num_filtered;    /* len(filteredNodes) */
+  int32_t num_nodes;       /* len(nodes) */
+  int64_t score;           /* total score of the chosen host; 0 on the one-fit shortcut */
+  /* binding: for pod.Spec.ExtendedResources[i], a bitmask over the node's devices of that
+   * resource in ascending device-id order (resolve to ids with ksb_device_id). */
+  uint32_t device_mask[KSB_MAX_EXT_ENTRIES];
+} ksb_result;
+
+/* genericScheduler.Schedule (core/generic_scheduler.go:109-161). Does NOT assume the pod:
+ * the caller follows with ksb_pod_add exactly as scheduler.go:478 calls cache.AssumePod. */
+int32_t ksb_schedule(ksb_engine* e, const uint8_t* pod, size_t len, ksb_result* out);
+
+/* n sequential iterations of scheduleOne's algorithm + assume steps (scheduler.go:430-497,
+ * bind always succeeding, device ids echoed as storage.go:180-187 would): semantically
+ * identical to n times {ksb_schedule; ksb_pod_add with NodeName and Assigned filled in}.
+ * pods = n Pod records back to back, offsets[i]..offsets[i+1] delimiting record i. */
+int32_t ksb_schedule_batch(ksb_engine* e, const uint8_t* pods, const uint64_t* offsets, int32_t n, ksb_result* out);
+
+/* Name of node row `index` (valid until the next node mutation). */
+int32_t ksb_node_name(const ksb_engine* e, int32_t index, const char** name, size_t* len);
+/* Id of device `bit` of extended resource `resource` on node row `index`. */
+int32_t ksb_device_id(const ksb_engine* e, int32_t index, const char* resource, size_t resource_len, int32_t bit,
+                      const char** id, size_t* len);
+/* FitError.Error() text (core/generic_scheduler.go:70-88) for the most recent KSB_FIT_ERROR of
+ * ksb_schedule, or for pod `i` of the most recent ksb_schedule_batch. */
+int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_len);
+
+/* genericScheduler.lastNodeIndex (core/generic_scheduler.go:100): selectHost's round-robin counter. */
+uint64_t ksb_get_last_node_index(const ksb_engine* e);
+void ksb_set_last_node_index(ksb_engine* e, uint64_t v);
+
+/* Counters for measurement (utiltrace steps of core/generic_scheduler.go:110-154 have no
+ * numeric counterpart; these are the engine's own). */
+typedef struct ksb_stats {
+  uint64_t pods_scheduled;     /* pods that went through the device path */
+  uint64_t kernel_launches;    /* CUDA kernels launched by the engine */
+  uint64_t groups;             /* speculative groups executed */
+  uint64_t group_restarts;     /* pods re-evaluated because a speculation was invalidated */
+  uint64_t h2d_bytes;          /* host->device bytes copied */
+  uint64_t d2h_bytes;          /* device->host bytes copied */
+  double last_batch_kernel_ms; /* CUDA-event time of the kernels of the last ksb_schedule_batch */
+  double last_batch_encode_ms; /* host time spent encoding the last batch */
+  int32_t num_nodes;
+  int32_t node_row_bytes;      /* bytes of node-table columns one (pod,node) evaluation may read */
+} ksb_stats;
+int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out);
+
+/* Re-run the device part of the most recent ksb_schedule_batch `iters` times against a
+ * restored copy of the node table it started from, with inputs already resident in HBM, and
+ * return the average CUDA-event milliseconds per run (measurement only; state is restored). */
+int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_result* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KSCHED_B200_H_ */

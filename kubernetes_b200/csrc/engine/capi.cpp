@@ -1,0 +1,169 @@
+// extern "C" surface of include/ksched_b200.h over ksb::Engine.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../../include/ksb_wire.hpp"
+#include "../../../include/ksched_b200.h"
+#include "engine.hpp"
+
+struct ksb_engine {
+  ksb::Engine* impl;
+  std::string err;
+};
+
+namespace {
+template <class F>
+int32_t guarded(ksb_engine* e, F&& f) {
+  if (!e || !e->impl) return -1;
+  try {
+    f();
+    return 0;
+  } catch (const std::exception& ex) {
+    e->err = ex.what();
+    return -1;
+  }
+}
+}  // namespace
+
+extern "C" {
+
+void ksb_config_default(ksb_config* c) {
+  memset(c, 0, sizeof *c);
+  c->device = 0;
+  c->w_least_requested = 1;
+  c->w_balanced = 1;
+  c->w_selector_spread = 1;
+  c->w_node_affinity = 1;
+  c->w_taint_toleration = 1;
+  c->w_inter_pod_affinity = 1;
+  c->w_prefer_avoid = 10000;
+  c->hard_pod_affinity_weight = 1;
+  c->label_words = 4;
+  c->shard_rank = 0;
+  c->shard_count = 1;
+  c->group_size = 0;
+}
+
+ksb_engine* ksb_create(const ksb_config* cfg, char* err, size_t err_len) {
+  try {
+    ksb_engine* e = new ksb_engine();
+    e->impl = new ksb::Engine(*cfg);
+    return e;
+  } catch (const std::exception& ex) {
+    if (err && err_len) {
+      strncpy(err, ex.what(), err_len - 1);
+      err[err_len - 1] = 0;
+    }
+    return nullptr;
+  }
+}
+
+void ksb_destroy(ksb_engine* e) {
+  if (!e) return;
+  delete e->impl;
+  delete e;
+}
+
+const char* ksb_last_error(const ksb_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+int32_t ksb_node_upsert(ksb_engine* e, const uint8_t* buf, size_t len) {
+  return guarded(e, [&] {
+    ksb::wire::Reader r(buf, len);
+    e->impl->node_upsert(ksb::wire::get_node(r));
+  });
+}
+
+int32_t ksb_node_remove(ksb_engine* e, const char* name, size_t name_len) {
+  return guarded(e, [&] { e->impl->node_remove(std::string(name, name_len)); });
+}
+
+int32_t ksb_pod_add(ksb_engine* e, const uint8_t* buf, size_t len) {
+  return guarded(e, [&] {
+    ksb::wire::Reader r(buf, len);
+    e->impl->pod_add(ksb::wire::get_pod(r));
+  });
+}
+
+int32_t ksb_pod_remove(ksb_engine* e, const char* ns, size_t ns_len, const char* name, size_t name_len) {
+  return guarded(e, [&] { e->impl->pod_remove(std::string(ns, ns_len), std::string(name, name_len)); });
+}
+
+int32_t ksb_selector_owner_upsert(ksb_engine* e, int32_t kind, const uint8_t* buf, size_t len) {
+  return guarded(e, [&] {
+    ksb::wire::Reader r(buf, len);
+    e->impl->owner_upsert(kind, ksb::wire::get_owner(r));
+  });
+}
+
+int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, size_t ns_len, const char* name,
+                                  size_t name_len) {
+  return guarded(e, [&] { e->impl->owner_remove(kind, std::string(ns, ns_len), std::string(name, name_len)); });
+}
+
+int32_t ksb_schedule(ksb_engine* e, const uint8_t* pod, size_t len, ksb_result* out) {
+  return guarded(e, [&] {
+    ksb::wire::Reader r(pod, len);
+    std::vector<ksb::Pod> batch;
+    batch.push_back(ksb::wire::get_pod(r));
+    e->impl->schedule_batch(batch, out, false);
+  });
+}
+
+int32_t ksb_schedule_batch(ksb_engine* e, const uint8_t* pods, const uint64_t* offsets, int32_t n, ksb_result* out) {
+  return guarded(e, [&] {
+    std::vector<ksb::Pod> batch;
+    batch.reserve(n);
+    for (int32_t i = 0; i < n; ++i) {
+      ksb::wire::Reader r(pods + offsets[i], (size_t)(offsets[i + 1] - offsets[i]));
+      batch.push_back(ksb::wire::get_pod(r));
+    }
+    e->impl->schedule_batch(batch, out, true);
+  });
+}
+
+int32_t ksb_node_name(const ksb_engine* e, int32_t index, const char** name, size_t* len) {
+  if (!e || !e->impl) return -1;
+  const std::string* s = e->impl->node_name_at(index);
+  if (!s) return -1;
+  *name = s->data();
+  *len = s->size();
+  return 0;
+}
+
+int32_t ksb_device_id(const ksb_engine* e, int32_t index, const char* resource, size_t resource_len, int32_t bit,
+                      const char** id, size_t* len) {
+  if (!e || !e->impl) return -1;
+  const std::string* s = e->impl->device_id_at(index, std::string(resource, resource_len), bit);
+  if (!s) return -1;
+  *id = s->data();
+  *len = s->size();
+  return 0;
+}
+
+int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_len) {
+  return guarded(e, [&] {
+    std::string m = e->impl->fit_error_message(i);
+    if (buf && buf_len) {
+      strncpy(buf, m.c_str(), buf_len - 1);
+      buf[buf_len - 1] = 0;
+    }
+  });
+}
+
+uint64_t ksb_get_last_node_index(const ksb_engine* e) { return e && e->impl ? e->impl->last_node_index : 0; }
+void ksb_set_last_node_index(ksb_engine* e, uint64_t v) {
+  if (e && e->impl) e->impl->last_node_index = v;
+}
+
+int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out) {
+  if (!e || !e->impl) return -1;
+  *out = e->impl->stats;
+  return 0;
+}
+
+int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_result* out) {
+  return guarded(e, [&] { e->impl->replay_last_batch(iters, avg_ms, out); });
+}
+
+}  // extern "C"

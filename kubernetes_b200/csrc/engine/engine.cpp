@@ -1,0 +1,734 @@
+// Host side of the engine (see engine.hpp). Reference paths are under
+// /root/reference/plugin/pkg/scheduler unless noted.
+#include "engine.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <stdexcept>
+
+namespace ksb {
+
+#define CUDA_OK(call)                                                                          \
+  do {                                                                                         \
+    cudaError_t e_ = (call);                                                                   \
+    if (e_ != cudaSuccess)                                                                     \
+      throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " + \
+                               __FILE__ + ":" + std::to_string(__LINE__));                     \
+  } while (0)
+
+void DevBuf::ensure(size_t bytes) {
+  if (bytes <= cap) return;
+  if (d) cudaFree(d);
+  size_t want = std::max(bytes, cap * 2);
+  want = (want + 255) & ~(size_t)255;
+  cudaError_t e = cudaMalloc(&d, want);
+  if (e != cudaSuccess) {
+    d = nullptr;
+    cap = 0;
+    throw std::runtime_error(std::string("cudaMalloc failed: ") + cudaGetErrorString(e));
+  }
+  cap = want;
+}
+void DevBuf::release() {
+  if (d) cudaFree(d);
+  d = nullptr;
+  cap = 0;
+}
+
+static std::string join3(const std::string& a, const std::string& b, const std::string& c) {
+  std::string s = a;
+  s.push_back('\0');
+  s += b;
+  s.push_back('\0');
+  s += c;
+  return s;
+}
+
+static bool is_scalar_resource(const std::string& n) {  // pkg/apis/core/v1/helper/helpers.go:32-84
+  bool default_ns = n.find('/') == std::string::npos || n.find("kubernetes.io/") != std::string::npos;
+  return !default_ns || n.rfind("hugepages-", 0) == 0;
+}
+
+// toleration.go:37-56
+static bool tolerates(const Toleration& t, const Taint& taint) {
+  if (!t.effect.empty() && t.effect != taint.effect) return false;
+  if (!t.key.empty() && t.key != taint.key) return false;
+  if (t.op.empty() || t.op == "Equal") return t.value == taint.value;
+  return t.op == "Exists";
+}
+
+Engine::Engine(const ksb_config& c) : cfg(c) {
+  W = cfg.label_words > 0 ? cfg.label_words : 4;
+  if (W > 16) throw std::runtime_error("label_words must be <= 16");
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    throw std::runtime_error("no usable CUDA device: the engine has no CPU fallback");
+  CUDA_OK(cudaSetDevice(cfg.device));
+  CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  topo_values.reserve(KSB_MAX_TOPO);
+}
+
+Engine::~Engine() {
+  cudaSetDevice(cfg.device);
+  for (DevBuf* b : {&b_i64, &b_u32, &b_u64, &b_dev_class, &b_topo, &b_spread, &b_tables, &b_headers, &b_pool,
+                    &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool})
+    b->release();
+  if (stream) cudaStreamDestroy(stream);
+}
+
+// ------------------------------------------------------------------ dictionaries
+
+bool Engine::node_has_label_bit(const Node& nd, const LabelBitDef& d) const {
+  auto it = nd.labels.find(d.key);
+  if (it == nd.labels.end()) return false;
+  switch (d.kind) {
+    case 'P':
+      return it->second == d.value;
+    case 'K':
+      return true;
+    default: {  // 'G' / 'L' (selector.go:214-233)
+      int64_t v;
+      if (!sel::to_int64(it->second, &v)) return false;
+      return d.kind == 'G' ? v > d.num : v < d.num;
+    }
+  }
+}
+
+int Engine::label_bit(char kind, const std::string& key, const std::string& value, int64_t num) {
+  std::string k(1, kind);
+  k += join3(key, value, kind == 'G' || kind == 'L' ? std::to_string(num) : std::string());
+  auto it = label_bits.find(k);
+  if (it != label_bits.end()) return it->second;
+  int bit = (int)label_defs.size();
+  if (bit >= W * 64)
+    throw std::runtime_error("label universe exceeds label_words*64 bits; create the engine with a larger label_words");
+  LabelBitDef d;
+  d.kind = kind;
+  d.key = key;
+  d.value = value;
+  d.num = num;
+  label_defs.push_back(d);
+  label_bits[k] = bit;
+  if (!layout_dirty) {  // fill the new bit column from the retained node labels
+    for (int r = 0; r < n; ++r)
+      if (node_has_label_bit(rows[r]->node, d)) u64(bit >> 6, r) |= 1ull << (bit & 63);
+    dirty_label_words.insert(bit >> 6);
+  }
+  return bit;
+}
+
+int Engine::topo_key(const std::string& key) {
+  auto it = topo_idx.find(key);
+  if (it != topo_idx.end()) return it->second;
+  int k = (int)topo_keys.size();
+  if (k >= KSB_MAX_TOPO) throw std::runtime_error("more than KSB_MAX_TOPO distinct topology keys");
+  topo_keys.push_back(key);
+  topo_values.emplace_back();
+  topo_idx[key] = k;
+  if (!layout_dirty) {
+    for (int r = 0; r < n; ++r) h_topo[(size_t)k * n_pad + r] = (uint32_t)topo_domain(k, rows[r]->node);
+    dirty_topo_cols.insert(k);
+  }
+  return k;
+}
+
+int Engine::topo_domain(int k, const Node& nd) {  // priorities/util/topologies.go:51-71
+  if (!nd.has_labels) return 0;
+  auto it = nd.labels.find(topo_keys[k]);
+  if (it == nd.labels.end()) return 0;
+  auto& dict = topo_values[k];
+  auto d = dict.find(it->second);
+  if (d != dict.end()) return d->second;
+  int id = (int)dict.size() + 1;
+  dict[it->second] = id;
+  // tables over this key grow by one domain
+  for (auto& t : tables)
+    if (t.topo == k) t.vals.resize(id + 1, 0);
+  arena_dirty = true;
+  return id;
+}
+
+int Engine::scalar_slot(const std::string& name) {
+  auto it = scalar_idx.find(name);
+  if (it != scalar_idx.end()) return it->second;
+  int s = (int)scalar_names.size();
+  if (s >= KSB_MAX_SCALARS) throw std::runtime_error("more than KSB_MAX_SCALARS distinct scalar resource names");
+  scalar_names.push_back(name);
+  scalar_idx[name] = s;
+  return s;
+}
+
+int Engine::port_bit(const std::string& proto_port) {
+  auto it = port_slot.find(proto_port);
+  if (it != port_slot.end()) return it->second;
+  int b = (int)port_slot.size();
+  if (b >= KSB_PORT_WORDS * 64) throw std::runtime_error("more than 256 distinct protocol/hostPort pairs");
+  port_slot[proto_port] = b;
+  return b;
+}
+int Engine::port_exact_bit(const std::string& triple) {
+  auto it = port_exact_slot.find(triple);
+  if (it != port_exact_slot.end()) return it->second;
+  int b = (int)port_exact_slot.size();
+  if (b >= KSB_PORT_WORDS * 64) throw std::runtime_error("more than 256 distinct protocol/hostIP/hostPort triples");
+  port_exact_slot[triple] = b;
+  return b;
+}
+
+// ------------------------------------------------------------------ signatures and classes
+
+SigInfo* Engine::sig_of(const Pod& p) {
+  std::string k = p.ns;
+  for (auto& kv : p.labels) {
+    k.push_back('\0');
+    k += kv.first;
+    k.push_back('\1');
+    k += kv.second;
+  }
+  auto it = sigs.find(k);
+  if (it != sigs.end()) return it->second.get();
+  auto s = std::make_unique<SigInfo>();
+  s->ns = p.ns;
+  s->labels = p.labels;
+  SigInfo* raw = s.get();
+  sigs.emplace(std::move(k), std::move(s));
+  return raw;
+}
+
+bool Engine::sig_matches_sel(SigInfo* s, int c) {
+  if ((int)s->sel_match.size() <= c) s->sel_match.resize(selclasses.size(), -1);
+  if (s->sel_match[c] < 0) {
+    const SelClass& sc = selclasses[c];
+    s->sel_match[c] = sc.nss.count(s->ns) && sel::matches(sc.selector, s->labels);  // topologies.go:41-50
+  }
+  return s->sel_match[c] != 0;
+}
+
+bool Engine::sig_matches_spread(SigInfo* s, int c) {
+  if ((int)s->spread_match.size() <= c) s->spread_match.resize(spread_classes.size(), -1);
+  if (s->spread_match[c] < 0) {
+    const SpreadClass& sc = spread_classes[c];
+    bool m = false;
+    if (sc.ns == s->ns)
+      for (auto& selx : sc.selectors)
+        if (sel::matches(selx, s->labels)) {
+          m = true;
+          break;
+        }
+    s->spread_match[c] = m;
+  }
+  return s->spread_match[c] != 0;
+}
+
+int Engine::selclass_of(const Pod& owner, const PodAffinityTerm& t, bool* ok) {
+  sel::Selector sx;
+  *ok = sel::from_label_selector(t.selector, &sx);
+  if (!*ok) return -1;
+  std::set<std::string> nss;  // topologies.go:28-37
+  if (t.namespaces.empty()) nss.insert(owner.ns);
+  else nss.insert(t.namespaces.begin(), t.namespaces.end());
+  std::string key;
+  for (auto& x : nss) {
+    key += x;
+    key.push_back('\x04');
+  }
+  key.push_back('\x05');
+  key += sel::canonical(sx);
+  auto it = selclass_idx.find(key);
+  if (it != selclass_idx.end()) return it->second;
+  int id = (int)selclasses.size();
+  SelClass c;
+  c.nss = std::move(nss);
+  c.selector = std::move(sx);
+  selclasses.push_back(std::move(c));
+  selclass_idx[key] = id;
+  return id;
+}
+
+int Engine::table_of(int kind, int selclass, int topo) {
+  std::string key = std::to_string(kind) + "|" + std::to_string(selclass) + "|" + std::to_string(topo);
+  auto it = table_idx.find(key);
+  if (it != table_idx.end()) return it->second;
+  int id = (int)tables.size();
+  Table t;
+  t.kind = kind;
+  t.selclass = selclass;
+  t.topo = topo;
+  t.vals.assign(topo_values[topo].size() + 1, 0);
+  if (kind == TK_MATCH && !layout_dirty) {
+    // count the existing pods that match this class, per topology domain of their node
+    for (auto& kv : pods) {
+      const Pod& ep = kv.second.pod;
+      auto nit = nodes.find(ep.node_name);
+      if (nit == nodes.end() || nit->second.row < 0) continue;
+      if (!sig_matches_sel(sig_of(ep), selclass)) continue;
+      uint32_t d = h_topo[(size_t)topo * n_pad + nit->second.row];
+      if (d) t.vals[d] += 1;
+      t.vals[0] += 1;
+    }
+  }
+  tables.push_back(std::move(t));
+  table_idx[key] = id;
+  if (kind == TK_MATCH) selclasses[selclass].match_tables.push_back(id);
+  else if (kind == TK_HELD_ANTI) held_anti_tables.push_back(id);
+  else held_w_tables.push_back(id);
+  arena_dirty = true;
+  return id;
+}
+
+void Engine::layout_arena() {
+  uint32_t off = 0;
+  for (auto& t : tables) {
+    t.off = off;
+    off += (uint32_t)t.vals.size();
+  }
+  arena_words = off;
+}
+
+// priorities/metadata.go:69-96 over the in-memory listers (testing/fake_lister.go:80-178)
+int Engine::spread_class_of(const Pod& p, SigInfo* s) {
+  if (s->spread_class != -2) return s->spread_class;
+  std::vector<sel::Selector> sels;
+  for (int kind = 0; kind < 2; ++kind)
+    for (auto& o : owners[kind])
+      if (o.ns == p.ns && sel::set_matches(o.map_selector, p.labels)) sels.push_back(sel::from_set(o.map_selector));
+  for (int kind = 2; kind < 4; ++kind) {
+    std::vector<sel::Selector> tmp;
+    bool ok = true;
+    for (auto& o : owners[kind]) {
+      if (o.ns != p.ns) continue;
+      sel::Selector sx;
+      if (!sel::from_label_selector(o.selector, &sx)) {
+        ok = false;
+        break;
+      }
+      if (sel::matches(sx, p.labels)) tmp.push_back(std::move(sx));
+    }
+    if (ok)
+      for (auto& x : tmp) sels.push_back(std::move(x));
+  }
+  if (sels.empty()) {
+    s->spread_class = -1;
+    return -1;
+  }
+  std::vector<std::string> canon;
+  for (auto& x : sels) canon.push_back(sel::canonical(x));
+  std::sort(canon.begin(), canon.end());
+  canon.erase(std::unique(canon.begin(), canon.end()), canon.end());
+  std::string key = p.ns;
+  for (auto& c : canon) {
+    key.push_back('\x06');
+    key += c;
+  }
+  auto it = spread_idx.find(key);
+  if (it != spread_idx.end()) {
+    s->spread_class = it->second;
+    return it->second;
+  }
+  int id = (int)spread_classes.size();
+  SpreadClass sc;
+  sc.ns = p.ns;
+  sc.selectors = std::move(sels);
+  spread_classes.push_back(std::move(sc));
+  spread_idx[key] = id;
+  h_spread.emplace_back((size_t)n_pad, 0u);
+  if (!layout_dirty) {  // selector_spreading.go:85-108 over every pod already on a node
+    auto& col = h_spread.back();
+    for (auto& kv : pods) {
+      const Pod& ep = kv.second.pod;
+      if (ep.deleting) continue;
+      auto nit = nodes.find(ep.node_name);
+      if (nit == nodes.end() || nit->second.row < 0) continue;
+      if (sig_matches_spread(sig_of(ep), id)) col[nit->second.row] += 1;
+    }
+    dirty_spread_cols.insert(id);
+  }
+  s->spread_class = id;
+  return id;
+}
+
+// ------------------------------------------------------------------ node / pod state
+
+static void reslist_to_aggregates(const ResourceList& rl, int64_t* cpu, int64_t* mem, int64_t* agpu, int64_t* eph,
+                                  int64_t* pods, std::map<std::string, int64_t>* scalars) {  // node_info.go:90-111
+  for (auto& kv : rl) {
+    if (kv.first == kResCPU) *cpu += kv.second;
+    else if (kv.first == kResMemory) *mem += kv.second;
+    else if (kv.first == kResAlphaGPU) *agpu += kv.second;
+    else if (kv.first == kResPods) { if (pods) *pods += kv.second; }
+    else if (kv.first == kResEphemeral) *eph += kv.second;
+    else if (is_scalar_resource(kv.first)) (*scalars)[kv.first] += kv.second;
+  }
+}
+
+void Engine::node_upsert(const Node& nd) {
+  std::lock_guard<std::mutex> g(mu);
+  HostNode& hn = nodes[nd.name];
+  bool was_listed = hn.has_node;
+  hn.node = nd;
+  hn.has_node = true;
+  // NodeInfo.SetNode (node_info.go:469-491): pressure conditions are sticky
+  for (auto& c : nd.conditions) {
+    if (c.type == "MemoryPressure") hn.mem_pressure = c.status;
+    else if (c.type == "DiskPressure") hn.disk_pressure = c.status;
+  }
+  // fork: extendedResourceManager.SetNode (schedulercache/extended_resources.go:154-207)
+  for (auto& kv : hn.ext) {
+    DeviceState& ds = kv.second;
+    auto nres = nd.extended.find(kv.first);
+    if (nres == nd.extended.end()) {
+      ds.available.clear();
+      ds.domain_present = true;
+      continue;
+    }
+    for (auto& a : ds.allocatable) {
+      bool present = false;
+      for (auto& d : nres->second)
+        if (d.id == a.first) present = true;
+      if (!present) ds.available.erase(a.first);
+    }
+  }
+  for (auto& kv : nd.extended) {
+    auto it = hn.ext.find(kv.first);
+    if (it == hn.ext.end()) {
+      DeviceState ds;
+      for (auto& d : kv.second) {
+        ds.allocatable[d.id] = d;
+        ds.available.insert(d.id);
+      }
+      ds.domain_present = true;
+      hn.ext[kv.first] = std::move(ds);
+      continue;
+    }
+    for (auto& d : kv.second) {
+      if (it->second.used.count(d.id)) continue;
+      it->second.available.insert(d.id);
+      it->second.allocatable[d.id] = d;
+    }
+  }
+  if (!was_listed || layout_dirty) {
+    layout_dirty = true;
+  } else {
+    // topology domains may be new; tables are resized inside topo_domain
+    fill_row(hn.row);
+    dirty_rows.insert(hn.row);
+  }
+}
+
+void Engine::node_remove(const std::string& name) {
+  std::lock_guard<std::mutex> g(mu);
+  auto it = nodes.find(name);
+  if (it == nodes.end()) return;
+  it->second.has_node = false;  // cache.go:373-387: the NodeInfo survives while it still holds pods
+  if (it->second.pod_keys.empty()) nodes.erase(it);
+  layout_dirty = true;
+}
+
+void Engine::owner_upsert(int kind, const SelectorOwner& o) {
+  std::lock_guard<std::mutex> g(mu);
+  if (kind < 0 || kind > 3) throw std::runtime_error("selector owner kind out of range");
+  bool found = false;
+  for (auto& x : owners[kind])
+    if (x.ns == o.ns && x.name == o.name) {
+      x = o;
+      found = true;
+    }
+  if (!found) owners[kind].push_back(o);
+  for (auto& kv : sigs) kv.second->spread_class = -2;
+}
+
+void Engine::owner_remove(int kind, const std::string& ns, const std::string& name) {
+  std::lock_guard<std::mutex> g(mu);
+  if (kind < 0 || kind > 3) return;
+  auto& v = owners[kind];
+  v.erase(std::remove_if(v.begin(), v.end(), [&](const SelectorOwner& x) { return x.ns == ns && x.name == name; }),
+          v.end());
+  for (auto& kv : sigs) kv.second->spread_class = -2;
+}
+
+static std::string port_string(const ContainerPort& p) {  // node_info.go:444-456
+  std::string proto = p.protocol.empty() ? "TCP" : p.protocol;
+  std::string ip = p.host_ip.empty() ? "0.0.0.0" : p.host_ip;
+  return proto + "/" + ip + "/" + std::to_string(p.host_port);
+}
+
+// NodeInfo.AddPod (node_info.go:329-356) on the host-side record
+void Engine::host_add_pod(const Pod& p, HostNode& hn) {
+  int64_t dummy_pods = 0;
+  for (auto& c : p.containers) {
+    reslist_to_aggregates(c.requests, &hn.req_cpu, &hn.req_mem, &hn.req_agpu, &hn.req_eph, &dummy_pods, &hn.req_scalar);
+    auto cpu = c.requests.find(kResCPU);
+    auto mem = c.requests.find(kResMemory);
+    hn.nz_cpu += cpu == c.requests.end() ? 100 : cpu->second;                    // non_zero.go:29-50
+    hn.nz_mem += mem == c.requests.end() ? 200LL * 1024 * 1024 : mem->second;
+    for (auto& port : c.ports)
+      if (port.host_port != 0) hn.used_ports.insert(port_string(port));
+  }
+  hn.pod_keys.insert(p.key());
+  for (auto& e : p.extended) {  // extended_resources.go:86-110
+    if (e.limits.size() != 1) continue;
+    auto ds = hn.ext.find(e.limits.begin()->first);
+    if (ds == hn.ext.end()) continue;
+    for (auto& id : e.assigned) {
+      if (!ds->second.available.count(id)) continue;
+      ds->second.available.erase(id);
+      ds->second.used.insert(id);
+    }
+  }
+}
+
+// NodeInfo.RemovePod (node_info.go:359-419), including the missing EphemeralStorage subtraction
+void Engine::host_remove_pod(const Pod& p, HostNode& hn) {
+  int64_t dummy_pods = 0, eph_ignored = 0;
+  int64_t cpu = 0, mem = 0, agpu = 0;
+  std::map<std::string, int64_t> sc;
+  for (auto& c : p.containers) {
+    reslist_to_aggregates(c.requests, &cpu, &mem, &agpu, &eph_ignored, &dummy_pods, &sc);
+    auto ccpu = c.requests.find(kResCPU);
+    auto cmem = c.requests.find(kResMemory);
+    hn.nz_cpu -= ccpu == c.requests.end() ? 100 : ccpu->second;
+    hn.nz_mem -= cmem == c.requests.end() ? 200LL * 1024 * 1024 : cmem->second;
+    for (auto& port : c.ports)
+      if (port.host_port != 0) hn.used_ports.erase(port_string(port));
+  }
+  hn.req_cpu -= cpu;
+  hn.req_mem -= mem;
+  hn.req_agpu -= agpu;
+  for (auto& kv : sc) hn.req_scalar[kv.first] -= kv.second;
+  hn.pod_keys.erase(p.key());
+  for (auto& e : p.extended) {  // extended_resources.go:114-152
+    if (e.limits.size() != 1) continue;
+    auto ds = hn.ext.find(e.limits.begin()->first);
+    if (ds == hn.ext.end()) continue;
+    for (auto& id : e.assigned) {
+      if (!ds->second.used.count(id)) continue;
+      ds->second.used.erase(id);
+      if (ds->second.allocatable.count(id)) ds->second.available.insert(id);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ layout
+
+void Engine::fill_ports(int row) {
+  HostNode& hn = *rows[row];
+  for (int w = 0; w < KSB_PORT_WORDS; ++w) {
+    u64(U64_PORT_ANY() + w, row) = 0;
+    u64(U64_PORT_WILD() + w, row) = 0;
+    u64(U64_PORT_EXACT() + w, row) = 0;
+  }
+  for (auto& s : hn.used_ports) {  // predicates/utils.go:161-202 turned into three bit tests
+    size_t a = s.find('/');
+    size_t b = s.find('/', a + 1);
+    std::string proto = s.substr(0, a), ip = s.substr(a + 1, b - a - 1), port = s.substr(b + 1);
+    int pb = port_bit(proto + "/" + port);
+    int eb = port_exact_bit(s);
+    u64(U64_PORT_ANY() + (pb >> 6), row) |= 1ull << (pb & 63);
+    if (ip == "0.0.0.0") u64(U64_PORT_WILD() + (pb >> 6), row) |= 1ull << (pb & 63);
+    u64(U64_PORT_EXACT() + (eb >> 6), row) |= 1ull << (eb & 63);
+  }
+}
+
+void Engine::fill_devices(int row) {
+  HostNode& hn = *rows[row];
+  for (int rs = 0; rs < KSB_MAX_RES; ++rs) {
+    u32(U32_DEV_AVAIL + rs, row) = 0;
+    for (int d = 0; d < KSB_MAX_DEV; ++d) h_dev_class[((size_t)rs * n_pad + row) * KSB_MAX_DEV + d] = 0;
+  }
+  uint32_t& flags = u32(U32_FLAGS, row);
+  for (auto& kv : hn.ext) {
+    auto it = res_idx.find(kv.first);
+    int rs;
+    if (it == res_idx.end()) {
+      rs = (int)res_names.size();
+      if (rs >= KSB_MAX_RES) throw std::runtime_error("more than KSB_MAX_RES distinct extended resource names");
+      res_names.push_back(kv.first);
+      res_idx[kv.first] = rs;
+    } else {
+      rs = it->second;
+    }
+    if (kv.second.domain_present) flags |= 256u << rs;
+    if (kv.second.allocatable.size() > KSB_MAX_DEV)
+      throw std::runtime_error("node " + hn.node.name + " has more than KSB_MAX_DEV devices of " + kv.first);
+    int bit = 0;
+    for (auto& dev : kv.second.allocatable) {  // ascending id = bit order
+      std::string ck;
+      for (auto& a : dev.second.attributes) {
+        ck += a.first;
+        ck.push_back('\1');
+        ck += a.second;
+        ck.push_back('\2');
+      }
+      auto ci = class_idx.find(ck);
+      int cls;
+      if (ci == class_idx.end()) {
+        cls = (int)class_attrs.size();
+        if (cls >= KSB_CLASS_WORDS * 64) throw std::runtime_error("more than 256 distinct device attribute classes");
+        class_attrs.push_back(dev.second.attributes);
+        class_idx[ck] = cls;
+      } else {
+        cls = ci->second;
+      }
+      h_dev_class[((size_t)rs * n_pad + row) * KSB_MAX_DEV + bit] = (uint16_t)cls;
+      if (kv.second.available.count(dev.first)) u32(U32_DEV_AVAIL + rs, row) |= 1u << bit;
+      ++bit;
+    }
+  }
+}
+
+// Everything about one row that derives from its Node object and its aggregates (not the
+// per-class counters, which follow the pods).
+void Engine::fill_row(int row) {
+  HostNode& hn = *rows[row];
+  const Node& nd = hn.node;
+  int64_t cpu = 0, mem = 0, agpu = 0, eph = 0, npods = 0;
+  std::map<std::string, int64_t> sc;
+  reslist_to_aggregates(nd.allocatable, &cpu, &mem, &agpu, &eph, &npods, &sc);
+  i64(I64_ALLOC_CPU, row) = cpu;
+  i64(I64_ALLOC_MEM, row) = mem;
+  i64(I64_ALLOC_AGPU, row) = agpu;
+  i64(I64_ALLOC_EPH, row) = eph;
+  i64(I64_REQ_CPU, row) = hn.req_cpu;
+  i64(I64_REQ_MEM, row) = hn.req_mem;
+  i64(I64_REQ_AGPU, row) = hn.req_agpu;
+  i64(I64_REQ_EPH, row) = hn.req_eph;
+  i64(I64_NZ_CPU, row) = hn.nz_cpu;
+  i64(I64_NZ_MEM, row) = hn.nz_mem;
+  for (int s = 0; s < KSB_MAX_SCALARS; ++s) {
+    i64(I64_ALLOC_SCALAR + s, row) = 0;
+    i64(I64_REQ_SCALAR + s, row) = 0;
+  }
+  for (auto& kv : sc) i64(I64_ALLOC_SCALAR + scalar_slot(kv.first), row) = kv.second;
+  for (auto& kv : hn.req_scalar) i64(I64_REQ_SCALAR + scalar_slot(kv.first), row) = kv.second;
+  u32(U32_ALLOC_PODS, row) = (uint32_t)(int32_t)npods;
+  u32(U32_NUM_PODS, row) = (uint32_t)hn.pod_keys.size();
+  uint32_t flags = 0;  // predicates.go:1382-1441
+  for (auto& c : nd.conditions) {
+    if (c.type == "Ready" && c.status != "True") flags |= NF_NOT_READY;
+    else if (c.type == "OutOfDisk" && c.status != "False") flags |= NF_OUT_OF_DISK;
+    else if (c.type == "NetworkUnavailable" && c.status != "False") flags |= NF_NET_UNAVAILABLE;
+  }
+  if (nd.unschedulable) flags |= NF_UNSCHEDULABLE;
+  if (hn.mem_pressure == "True") flags |= NF_MEM_PRESSURE;
+  if (hn.disk_pressure == "True") flags |= NF_DISK_PRESSURE;
+  u32(U32_FLAGS, row) = flags;
+  // zone key (pkg/util/node/node.go:116-133)
+  uint32_t zone = 0;
+  if (nd.has_labels) {
+    auto r = nd.labels.find(kLabelRegion);
+    auto z = nd.labels.find(kLabelZone);
+    std::string region = r == nd.labels.end() ? "" : r->second;
+    std::string zn = z == nd.labels.end() ? "" : z->second;
+    if (!region.empty() || !zn.empty()) {
+      std::string key = region + std::string(":\x00:", 3) + zn;
+      auto zi = zone_idx.find(key);
+      if (zi == zone_idx.end()) {
+        zone = (uint32_t)zone_idx.size() + 1;
+        zone_idx[key] = (int)zone;
+      } else {
+        zone = (uint32_t)zi->second;
+      }
+    }
+  }
+  u32(U32_ZONE, row) = zone;
+  for (int w = 0; w < W; ++w) u64(w, row) = 0;
+  for (size_t b = 0; b < label_defs.size(); ++b)
+    if (node_has_label_bit(nd, label_defs[b])) u64((int)(b >> 6), row) |= 1ull << (b & 63);
+  uint64_t hard = 0, soft = 0;
+  for (auto& t : nd.taints) {
+    std::string k = join3(t.key, t.value, t.effect);
+    if (t.effect == "NoSchedule" || t.effect == "NoExecute") {
+      auto it = hard_taint_idx.find(k);
+      int b;
+      if (it == hard_taint_idx.end()) {
+        b = (int)hard_taints.size();
+        if (b >= 64) throw std::runtime_error("more than 64 distinct NoSchedule/NoExecute taints");
+        hard_taints.push_back(t);
+        hard_taint_idx[k] = b;
+      } else {
+        b = it->second;
+      }
+      hard |= 1ull << b;
+    } else if (t.effect == "PreferNoSchedule") {
+      auto it = soft_taint_idx.find(k);
+      int b;
+      if (it == soft_taint_idx.end()) {
+        b = (int)soft_taints.size();
+        if (b >= 64) throw std::runtime_error("more than 64 distinct PreferNoSchedule taints");
+        soft_taints.push_back(t);
+        soft_taint_idx[k] = b;
+      } else {
+        b = it->second;
+      }
+      soft |= 1ull << b;
+    }
+  }
+  u64(U64_HARD(), row) = hard;
+  u64(U64_SOFT(), row) = soft;
+  uint64_t avoid = 0;
+  if (!nd.avoid_annotation_invalid)
+    for (auto& a : nd.avoid) {
+      std::string k = a.kind;
+      k.push_back('\0');
+      k += a.uid;
+      auto it = avoid_idx.find(k);
+      int b;
+      if (it == avoid_idx.end()) {
+        b = (int)avoid_idx.size();
+        if (b >= 64) throw std::runtime_error("more than 64 distinct preferAvoidPods controller references");
+        avoid_idx[k] = b;
+      } else {
+        b = it->second;
+      }
+      avoid |= 1ull << b;
+    }
+  u64(U64_AVOID(), row) = avoid;
+  fill_ports(row);
+  fill_devices(row);
+  for (int k = 0; k < (int)topo_keys.size(); ++k) h_topo[(size_t)k * n_pad + row] = (uint32_t)topo_domain(k, nd);
+}
+
+// Rebuild every column from the host records (node set changed).
+void Engine::rebuild_layout() {
+  rows.clear();
+  for (auto& kv : nodes) {
+    kv.second.row = -1;
+    if (kv.second.has_node) {
+      kv.second.row = (int)rows.size();
+      rows.push_back(&kv.second);
+    }
+  }
+  n = (int)rows.size();
+  n_pad = std::max(256, (n + 255) & ~255);
+  h_i64.assign((size_t)I64_COLS * n_pad, 0);
+  h_u32.assign((size_t)U32_COLS * n_pad, 0);
+  h_u64.assign((size_t)u64_cols() * n_pad, 0);
+  h_dev_class.assign((size_t)KSB_MAX_RES * n_pad * KSB_MAX_DEV, 0);
+  h_topo.assign((size_t)KSB_MAX_TOPO * n_pad, 0);
+  for (auto& c : h_spread) c.assign((size_t)n_pad, 0u);
+  layout_dirty = false;
+  for (int r = 0; r < n; ++r) fill_row(r);
+  // per-class counters follow the pods: recount them all
+  for (auto& t : tables) std::fill(t.vals.begin(), t.vals.end(), 0);
+  for (auto& kv : pods) register_pod_classes(kv.second.pod);
+  for (auto& t : tables) t.vals.resize(topo_values[t.topo].size() + 1, 0);
+  for (auto& kv : pods) {
+    const Pod& p = kv.second.pod;
+    auto nit = nodes.find(p.node_name);
+    if (nit == nodes.end() || nit->second.row < 0) continue;
+    std::vector<CommitEntry> commits;
+    std::vector<int> inc;
+    commit_lists(p, sig_of(p), &commits, &inc);
+    apply_class_part_host(nit->second.row, commits, inc, +1);
+  }
+  dirty_rows.clear();
+  dirty_label_words.clear();
+  dirty_topo_cols.clear();
+  dirty_spread_cols.clear();
+  arena_dirty = true;
+  full_upload = true;
+}
+
+}  // namespace ksb

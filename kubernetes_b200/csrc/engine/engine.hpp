@@ -1,0 +1,247 @@
+// Host side of the engine: dictionaries that turn strings into bit positions / ids, the host
+// mirror of the structure-of-arrays node table, the per-pod requirement-block encoder, and the
+// driver of the batch kernel. No scheduling decision is made here: fit, scores and host
+// selection are computed only by the CUDA kernels in kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <memory>
+#include <mutex>
+#include <set>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/ksched_b200.h"
+#include "device_types.h"
+#include "kernels.h"
+#include "model.hpp"
+#include "selectors.hpp"
+
+namespace ksb {
+
+struct DevBuf {  // growable device buffer
+  void* d = nullptr;
+  size_t cap = 0;
+  void ensure(size_t bytes);
+  void release();
+};
+
+struct DeviceState {  // fork: ExtendedResourceCacheManagerImpl (schedulercache/extended_resources.go:39-207)
+  std::map<std::string, ExtendedDevice> allocatable;  // ascending id = bit order
+  std::set<std::string> available, used;
+  bool domain_present = false;  // `available[rName]` exists
+};
+
+struct HostNode {
+  Node node;
+  bool has_node = false;
+  int row = -1;
+  std::set<std::string> pod_keys;
+  std::set<std::string> used_ports;  // "proto/ip/port" (node_info.go:435-466)
+  std::map<std::string, DeviceState> ext;
+  int64_t req_cpu = 0, req_mem = 0, req_agpu = 0, req_eph = 0, nz_cpu = 0, nz_mem = 0;
+  std::map<std::string, int64_t> req_scalar;
+  std::string mem_pressure, disk_pressure;  // sticky ConditionStatus (node_info.go:478-488)
+};
+
+struct HostPod {
+  Pod pod;  // node_name and extended[i].assigned filled in
+};
+
+struct SelClass {  // (namespaces, label selector) of a pod-affinity term
+  std::set<std::string> nss;
+  sel::Selector selector;
+  std::vector<int> match_tables;  // MATCH tables over this class
+};
+
+enum TableKind { TK_MATCH = 0, TK_HELD_ANTI = 1, TK_HELD_W = 2 };
+
+struct Table {
+  int kind, selclass, topo;
+  std::vector<int32_t> vals;  // [domains(topo) + 1]; slot 0 of MATCH tables = matching pods anywhere
+  uint32_t off = 0;
+};
+
+struct SpreadClass {
+  std::string ns;
+  std::vector<sel::Selector> selectors;
+};
+
+struct SigInfo {  // memo per distinct (namespace, labels) signature
+  std::string ns;
+  StrMap labels;
+  std::vector<int8_t> spread_match;  // per spread class
+  std::vector<int8_t> sel_match;     // per SelClass
+  int spread_class = -2;             // -2 unknown, -1 none
+};
+
+struct CommitEntry {  // one per-domain counter the assume step bumps
+  int table;
+  int32_t delta;
+};
+
+struct EncodedPod {
+  KsbPodHeader h;
+  std::vector<uint64_t> pool;
+  std::vector<CommitEntry> commits;  // host-side form of the pool's commit list
+  std::vector<int> spread_inc;
+  std::vector<std::string> ext_reasons;  // failure text for RB_EXT0.. / RB_EXT_LIMITS
+};
+
+class Engine {
+ public:
+  explicit Engine(const ksb_config& cfg);
+  ~Engine();
+
+  // mutators (schedulercache.Cache decorator)
+  void node_upsert(const Node& n);
+  void node_remove(const std::string& name);
+  void pod_add(const Pod& p);
+  void pod_remove(const std::string& ns, const std::string& name);
+  void owner_upsert(int kind, const SelectorOwner& o);
+  void owner_remove(int kind, const std::string& ns, const std::string& name);
+
+  // hot path
+  void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
+  void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
+  std::string fit_error_message(int i);
+
+  std::string last_error;
+  ksb_config cfg;
+  std::mutex mu;
+  ksb_stats stats{};
+  uint64_t last_node_index = 0;
+
+  const std::string* node_name_at(int row) const;
+  const std::string* device_id_at(int row, const std::string& resource, int bit) const;
+
+ private:
+  // ---- dictionaries
+  int W;  // label words
+  std::unordered_map<std::string, int> label_bits;  // "P\0k\0v" | "K\0k" | "G\0k\0n" | "L\0k\0n" -> bit
+  struct LabelBitDef {
+    char kind;
+    std::string key, value;
+    int64_t num = 0;
+  };
+  std::vector<LabelBitDef> label_defs;
+  std::vector<Taint> hard_taints, soft_taints;
+  std::unordered_map<std::string, int> hard_taint_idx, soft_taint_idx;
+  std::unordered_map<std::string, int> avoid_idx;
+  std::unordered_map<std::string, int> port_slot, port_exact_slot;
+  std::unordered_map<std::string, int> scalar_idx;
+  std::vector<std::string> scalar_names;
+  std::unordered_map<std::string, int> res_idx;
+  std::vector<std::string> res_names;
+  std::unordered_map<std::string, int> class_idx;
+  std::vector<StrMap> class_attrs;
+  std::unordered_map<std::string, int> zone_idx;
+  std::unordered_map<std::string, int> topo_idx;
+  std::vector<std::string> topo_keys;
+  std::vector<std::unordered_map<std::string, int>> topo_values;  // value -> domain id (1-based)
+
+  int label_bit(char kind, const std::string& key, const std::string& value, int64_t num);
+  bool node_has_label_bit(const Node& n, const LabelBitDef& d) const;
+  int topo_key(const std::string& key);
+  int topo_domain(int k, const Node& n);
+  int scalar_slot(const std::string& name);
+  int port_bit(const std::string& proto_port);
+  int port_exact_bit(const std::string& triple);
+
+  // ---- cluster state
+  std::map<std::string, HostNode> nodes;  // by name: iteration order = row order
+  std::vector<HostNode*> rows;
+  std::unordered_map<std::string, HostPod> pods;
+  std::vector<SelectorOwner> owners[4];
+  bool layout_dirty = true;
+
+  // ---- class registries
+  std::vector<SelClass> selclasses;
+  std::unordered_map<std::string, int> selclass_idx;
+  std::vector<Table> tables;
+  std::unordered_map<std::string, int> table_idx;
+  std::vector<int> held_anti_tables, held_w_tables;
+  bool arena_dirty = true;
+  uint32_t arena_words = 0;
+  std::vector<SpreadClass> spread_classes;
+  std::unordered_map<std::string, int> spread_idx;
+  std::unordered_map<std::string, std::unique_ptr<SigInfo>> sigs;
+  SigInfo* sig_of(const Pod& p);
+  bool sig_matches_sel(SigInfo* s, int selclass);
+  bool sig_matches_spread(SigInfo* s, int cls);
+  int selclass_of(const Pod& owner, const PodAffinityTerm& t, bool* ok);
+  int table_of(int kind, int selclass, int topo);
+  int spread_class_of(const Pod& p, SigInfo* s);
+  void layout_arena();
+
+  // ---- host mirror of the node table (same family layout as the device buffers)
+  int n = 0, n_pad = 0;
+  enum { I64_ALLOC_CPU = 0, I64_ALLOC_MEM, I64_ALLOC_AGPU, I64_ALLOC_EPH, I64_REQ_CPU, I64_REQ_MEM, I64_REQ_AGPU,
+         I64_REQ_EPH, I64_NZ_CPU, I64_NZ_MEM, I64_ALLOC_SCALAR, I64_REQ_SCALAR = I64_ALLOC_SCALAR + KSB_MAX_SCALARS,
+         I64_COLS = I64_REQ_SCALAR + KSB_MAX_SCALARS };
+  enum { U32_ALLOC_PODS = 0, U32_NUM_PODS, U32_FLAGS, U32_ZONE, U32_DEV_AVAIL, U32_COLS = U32_DEV_AVAIL + KSB_MAX_RES };
+  int u64_cols() const { return W + 3 + 3 * KSB_PORT_WORDS; }
+  int U64_HARD() const { return W; }
+  int U64_SOFT() const { return W + 1; }
+  int U64_AVOID() const { return W + 2; }
+  int U64_PORT_ANY() const { return W + 3; }
+  int U64_PORT_WILD() const { return W + 3 + KSB_PORT_WORDS; }
+  int U64_PORT_EXACT() const { return W + 3 + 2 * KSB_PORT_WORDS; }
+  std::vector<int64_t> h_i64;
+  std::vector<uint32_t> h_u32;
+  std::vector<uint64_t> h_u64;
+  std::vector<uint16_t> h_dev_class;  // [KSB_MAX_RES][n_pad][KSB_MAX_DEV]
+  std::vector<uint32_t> h_topo;       // [KSB_MAX_TOPO][n_pad]
+  std::vector<std::vector<uint32_t>> h_spread;
+  int64_t& i64(int col, int row) { return h_i64[(size_t)col * n_pad + row]; }
+  uint32_t& u32(int col, int row) { return h_u32[(size_t)col * n_pad + row]; }
+  uint64_t& u64(int col, int row) { return h_u64[(size_t)col * n_pad + row]; }
+  bool full_upload = true;
+  std::set<int> dirty_rows;
+  std::set<int> dirty_label_words, dirty_topo_cols, dirty_spread_cols;
+  void rebuild_layout();
+  void fill_row(int row);
+  void fill_ports(int row);
+  void fill_devices(int row);
+
+  // ---- device
+  cudaStream_t stream = nullptr;
+  KsbNodeTable dT{};
+  DevBuf b_i64, b_u32, b_u64, b_dev_class, b_topo, b_spread, b_tables, b_headers, b_pool, b_results, b_scratch,
+      b_snapshot, b_one_header, b_one_pool;
+  size_t spread_cap_cols = 0;
+  int grid = 0, threads = 0, max_grid = 0;
+  size_t smem_bytes = 0;
+  void upload_all();
+  void upload_dirty();
+  void sync_device();
+  void setup_table_pointers();
+  KsbBatchArgs make_args(int n_pods, bool commit);
+  void launch(const KsbBatchArgs& a);
+
+  // ---- encoder
+  void register_pod_classes(const Pod& p);
+  void encode_pod(const Pod& p, EncodedPod* out);
+  void compile_expr(const SelectorRequirement& r, bool* ok, std::vector<uint64_t>* mask, uint32_t* kind);
+  void commit_lists(const Pod& p, SigInfo* s, std::vector<CommitEntry>* commits, std::vector<int>* spread_inc);
+  // host mirror of commit_pod
+  void apply_node_part_host(int row, const EncodedPod& e, const uint32_t* dev_masks);
+  void apply_class_part_host(int row, const std::vector<CommitEntry>& commits, const std::vector<int>& spread_inc,
+                             int sign);
+  void host_add_pod(const Pod& p, HostNode& hn);
+  void host_remove_pod(const Pod& p, HostNode& hn);
+
+  // ---- last batch (for ksb_replay_last_batch and fit-error messages)
+  std::vector<EncodedPod> last_encoded;
+  std::vector<KsbResult> last_results;
+  std::vector<int32_t> last_fiterr_hist;
+  int last_n_nodes = 0;
+  uint64_t last_index_before = 0;
+  bool have_snapshot = false;
+  void snapshot_dynamic();
+  void restore_dynamic();
+};
+
+}  // namespace ksb

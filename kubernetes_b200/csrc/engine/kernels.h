@@ -1,0 +1,40 @@
+// Host/device interface of kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "device_types.h"
+
+struct KsbBatchArgs {
+  KsbNodeTable table;
+  const KsbPodHeader* headers;  // [n_pods]
+  const uint64_t* pool;
+  int32_t n_pods;
+  int32_t zone_stride;
+  int32_t commit;               // 1: apply the assume step after each pod (ksb_schedule_batch)
+  int32_t pad0;
+  KsbResult* results;           // [n_pods]
+  // scratch (global memory beyond inputs and outputs)
+  KsbNorms* norms;              // [2] ping-pong per pod
+  int32_t* zone_sum;            // [2][zone_stride]
+  int4* raw;                    // [n_pad] phase-1 Map results
+  int32_t* score;               // [n_pad] phase-2 totals
+  uint32_t* reasons;            // [n_pad] failure-reason masks
+  int32_t* blk_max;             // [grid]
+  int32_t* blk_cnt;             // [grid]
+  uint32_t* barrier;            // grid barrier counter, zero at launch
+  int32_t* error_flag;
+  int32_t* fiterr_count;
+  int32_t* fiterr_hist;         // [KSB_MAX_FITERR][KSB_REASON_BITS]
+  uint64_t* last_node_index;    // genericScheduler.lastNodeIndex
+};
+
+extern "C" {
+int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream);
+int ksb_batch_kernel_limits(int device, size_t smem_bytes, int* max_grid, int* threads);
+int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* header, const uint64_t* pool, int row,
+                     const uint32_t* masks, cudaStream_t stream);
+size_t ksb_batch_smem_bytes(int n_zones);
+int ksb_max_pool_words();
+}

@@ -1,0 +1,278 @@
+// Test / bench harness over the host mirror: the scheduleOne loop of the reference
+// (scheduler.go:430-497) with in-memory listers and every bind succeeding, driven from JSON
+// cluster files (the same files the CPU oracle consumes). Exposed to Python through a few
+// extern "C" entry points; everything below them goes through include/ksched_b200.h only.
+#include "gpu_scheduler.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+
+#include "json.hpp"
+
+using namespace ksb;
+
+namespace {
+
+struct Session {
+  Cluster cluster;
+  // pre-serialised host buffers (what the Go shim would hand to cgo)
+  std::vector<std::string> node_bufs, existing_bufs;
+  std::vector<std::pair<int, std::string>> owner_bufs;
+  std::string pod_stream;
+  std::vector<uint64_t> pod_offsets;
+};
+
+std::string esc(const std::string& s) {
+  std::string o;
+  json::escape_to(o, s);
+  return o;
+}
+
+uint64_t fnv1a(uint64_t h, const void* p, size_t n) {
+  const unsigned char* c = (const unsigned char*)p;
+  for (size_t i = 0; i < n; ++i) {
+    h ^= c[i];
+    h *= 1099511628211ull;
+  }
+  return h;
+}
+
+void load_cluster(EngineHandle& h, const Session& s) {
+  for (auto& b : s.node_bufs) h.check(ksb_node_upsert(h.get(), (const uint8_t*)b.data(), b.size()), "node_upsert");
+  for (auto& kb : s.owner_bufs)
+    h.check(ksb_selector_owner_upsert(h.get(), kb.first, (const uint8_t*)kb.second.data(), kb.second.size()),
+            "selector_owner_upsert");
+  for (auto& b : s.existing_bufs) h.check(ksb_pod_add(h.get(), (const uint8_t*)b.data(), b.size()), "pod_add");
+}
+
+std::string run(Session& s, const json::Value& opt) {
+  ksb_config cfg;
+  ksb_config_default(&cfg);
+  cfg.device = (int32_t)opt.get_int("device", 0);
+  cfg.label_words = (int32_t)opt.get_int("label_words", 4);
+  cfg.hard_pod_affinity_weight = (int32_t)opt.get_int("hardPodAffinityWeight", 1);
+  cfg.group_size = (int32_t)opt.get_int("group_size", 0);
+  if (const json::Value* w = opt.find("weights"); w && !w->is_null()) {
+    cfg.w_least_requested = (int32_t)w->get_int("LeastRequestedPriority", 1);
+    cfg.w_balanced = (int32_t)w->get_int("BalancedResourceAllocation", 1);
+    cfg.w_selector_spread = (int32_t)w->get_int("SelectorSpreadPriority", 1);
+    cfg.w_node_affinity = (int32_t)w->get_int("NodeAffinityPriority", 1);
+    cfg.w_taint_toleration = (int32_t)w->get_int("TaintTolerationPriority", 1);
+    cfg.w_inter_pod_affinity = (int32_t)w->get_int("InterPodAffinityPriority", 1);
+    cfg.w_prefer_avoid = (int32_t)w->get_int("NodePreferAvoidPodsPriority", 10000);
+  }
+  const int64_t batch = opt.get_int("batch", -1);  // -1: whole stream in one call; 0: Schedule + AssumePod per pod
+  int64_t limit = opt.get_int("limit", -1);
+  const bool want_results = opt.get_bool("results", true);
+  const int replay_iters = (int)opt.get_int("replay_iters", 0);
+  size_t np = s.cluster.pods.size();
+  if (limit >= 0 && (size_t)limit < np) np = (size_t)limit;
+
+  EngineHandle h(cfg);
+  ksb_set_last_node_index(h.get(), (uint64_t)opt.get_int("lastNodeIndex", 0));
+  auto tl0 = std::chrono::steady_clock::now();
+  load_cluster(h, s);
+  auto tl1 = std::chrono::steady_clock::now();
+
+  std::vector<ksb_result> results(np);
+  std::vector<std::string> hosts(np), messages(np);
+  std::vector<ExtendedResourceBinding> bindings(np);
+  GpuScheduler sched(h);
+  CacheDecorator cache(h);
+  double kernel_ms = 0, encode_ms = 0, replay_ms = 0;
+  std::vector<double> lat_us;
+  auto t0 = std::chrono::steady_clock::now();
+  if (batch == 0) {
+    // the reference's own call sequence: Schedule, then AssumePod with NodeName and Assigned set
+    lat_us.reserve(np);
+    for (size_t i = 0; i < np; ++i) {
+      const Pod& pod = s.cluster.pods[i];
+      auto a0 = std::chrono::steady_clock::now();
+      ksb_result r;
+      h.check(ksb_schedule(h.get(), (const uint8_t*)s.pod_stream.data() + s.pod_offsets[i],
+                           (size_t)(s.pod_offsets[i + 1] - s.pod_offsets[i]), &r),
+              "Schedule");
+      auto a1 = std::chrono::steady_clock::now();
+      lat_us.push_back(std::chrono::duration<double, std::micro>(a1 - a0).count());
+      results[i] = r;
+      try {
+        ScheduleOutcome o = sched.outcome(pod, r, 0);
+        hosts[i] = o.host;
+        bindings[i] = o.binding;
+        Pod assumed = pod;  // scheduler.go:478
+        assumed.node_name = o.host;
+        for (auto& e : assumed.extended) {
+          auto it = o.binding.find(e.name);
+          if (it != o.binding.end()) e.assigned = it->second;
+        }
+        cache.AssumePod(assumed);
+      } catch (const FitError& fe) {
+        messages[i] = fe.what();
+      } catch (const std::exception& ex) {
+        messages[i] = ex.what();
+      }
+    }
+  } else {
+    size_t step = batch < 0 ? np : (size_t)batch;
+    for (size_t b0 = 0; b0 < np; b0 += step) {
+      size_t b1 = std::min(np, b0 + step);
+      h.check(ksb_schedule_batch(h.get(), (const uint8_t*)s.pod_stream.data(), s.pod_offsets.data() + b0, (int32_t)(b1 - b0),
+                                 results.data() + b0),
+              "ScheduleBatch");
+      ksb_stats st;
+      ksb_get_stats(h.get(), &st);
+      kernel_ms += st.last_batch_kernel_ms;
+      encode_ms += st.last_batch_encode_ms;
+      if (want_results || b1 == np) {
+        for (size_t i = b0; i < b1; ++i) {
+          if (!want_results && results[i].status != KSB_SCHEDULED) continue;
+          if (!want_results) continue;
+          try {
+            ScheduleOutcome o = sched.outcome(s.cluster.pods[i], results[i], (int)(i - b0));
+            hosts[i] = o.host;
+            bindings[i] = o.binding;
+          } catch (const std::exception& ex) {
+            messages[i] = ex.what();
+          }
+        }
+      }
+    }
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (replay_iters > 0 && batch < 0) {
+    std::vector<ksb_result> again(np);
+    h.check(ksb_replay_last_batch(h.get(), replay_iters, &replay_ms, again.data()), "replay");
+    for (size_t i = 0; i < np; ++i)
+      if (again[i].status != results[i].status || again[i].node_index != results[i].node_index)
+        throw std::runtime_error("replay diverged from the first run at pod " + std::to_string(i));
+  }
+  ksb_stats st;
+  ksb_get_stats(h.get(), &st);
+
+  uint64_t hash = 1469598103934665603ull;
+  size_t scheduled = 0, fit_errors = 0, errors = 0;
+  for (size_t i = 0; i < np; ++i) {
+    int32_t v[2] = {results[i].status, results[i].node_index};
+    hash = fnv1a(hash, v, sizeof v);
+    hash = fnv1a(hash, results[i].device_mask, sizeof results[i].device_mask);
+    if (results[i].status == KSB_SCHEDULED) scheduled++;
+    else if (results[i].status == KSB_FIT_ERROR) fit_errors++;
+    else errors++;
+  }
+  std::string out = "{";
+  out += "\"pods\":" + std::to_string(np);
+  out += ",\"nodes\":" + std::to_string(s.cluster.nodes.size());
+  out += ",\"scheduled\":" + std::to_string(scheduled);
+  out += ",\"fit_errors\":" + std::to_string(fit_errors);
+  out += ",\"errors\":" + std::to_string(errors);
+  out += ",\"placement_hash\":\"" + std::to_string(hash) + "\"";
+  out += ",\"load_ms\":" + std::to_string(std::chrono::duration<double, std::milli>(tl1 - tl0).count());
+  out += ",\"e2e_ms\":" + std::to_string(std::chrono::duration<double, std::milli>(t1 - t0).count());
+  out += ",\"kernel_ms\":" + std::to_string(kernel_ms);
+  out += ",\"encode_ms\":" + std::to_string(encode_ms);
+  out += ",\"replay_ms\":" + std::to_string(replay_ms);
+  out += ",\"kernel_launches\":" + std::to_string(st.kernel_launches);
+  out += ",\"h2d_bytes\":" + std::to_string(st.h2d_bytes);
+  out += ",\"d2h_bytes\":" + std::to_string(st.d2h_bytes);
+  out += ",\"lastNodeIndex\":" + std::to_string(ksb_get_last_node_index(h.get()));
+  if (!lat_us.empty()) {
+    std::vector<double> sorted = lat_us;
+    std::sort(sorted.begin(), sorted.end());
+    out += ",\"p50_us\":" + std::to_string(sorted[sorted.size() / 2]);
+    out += ",\"p99_us\":" + std::to_string(sorted[std::min(sorted.size() - 1, (size_t)(sorted.size() * 0.99))]);
+  }
+  if (want_results) {
+    out += ",\"results\":[";
+    for (size_t i = 0; i < np; ++i) {
+      if (i) out += ",";
+      out += "{\"host\":" + esc(hosts[i]) + ",\"status\":" + std::to_string(results[i].status) +
+             ",\"filtered\":" + std::to_string(results[i].num_filtered) + ",\"score\":" + std::to_string(results[i].score) +
+             ",\"message\":" + esc(messages[i]) + ",\"devices\":{";
+      bool first = true;
+      for (auto& kv : bindings[i]) {
+        if (!first) out += ",";
+        first = false;
+        out += esc(kv.first) + ":[";
+        for (size_t k = 0; k < kv.second.size(); ++k) {
+          if (k) out += ",";
+          out += esc(kv.second[k]);
+        }
+        out += "]";
+      }
+      out += "}}";
+    }
+    out += "]";
+  }
+  out += "}";
+  return out;
+}
+
+char* dup(const std::string& s) {
+  char* p = (char*)malloc(s.size() + 1);
+  memcpy(p, s.c_str(), s.size() + 1);
+  return p;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Parse a cluster (inline JSON text or a file path) and pre-serialise it into wire records.
+void* ksbh_session_create(const char* cluster_json_or_path, int is_path, char** err) {
+  try {
+    auto s = std::make_unique<Session>();
+    json::Value v = is_path ? json::parse_file(cluster_json_or_path) : json::parse(cluster_json_or_path);
+    s->cluster = cluster_from_json(v);
+    for (auto& n : s->cluster.nodes) {
+      wire::Writer w;
+      wire::put(w, n);
+      s->node_bufs.push_back(std::move(w.buf));
+    }
+    const std::vector<SelectorOwner>* lists[4] = {&s->cluster.services, &s->cluster.rcs, &s->cluster.rss, &s->cluster.sss};
+    for (int k = 0; k < 4; ++k) {
+      int idx = 0;
+      for (auto o : *lists[k]) {
+        if (o.name.empty()) o.name = "owner-" + std::to_string(k) + "-" + std::to_string(idx);
+        ++idx;
+        wire::Writer w;
+        wire::put(w, o);
+        s->owner_bufs.push_back({k, std::move(w.buf)});
+      }
+    }
+    for (auto& p : s->cluster.existing_pods) {
+      wire::Writer w;
+      wire::put(w, p);
+      s->existing_bufs.push_back(std::move(w.buf));
+    }
+    wire::Writer w;
+    s->pod_offsets.push_back(0);
+    for (auto& p : s->cluster.pods) {
+      wire::put(w, p);
+      s->pod_offsets.push_back(w.buf.size());
+    }
+    s->pod_stream = std::move(w.buf);
+    return s.release();
+  } catch (const std::exception& ex) {
+    if (err) *err = dup(ex.what());
+    return nullptr;
+  }
+}
+
+void ksbh_session_destroy(void* s) { delete (Session*)s; }
+
+// Run the pod stream on a fresh engine. Returns JSON (free with ksbh_free); on failure {"error": ...}.
+char* ksbh_session_run(void* session, const char* options_json) {
+  try {
+    json::Value opt = json::parse(options_json && *options_json ? options_json : "{}");
+    return dup(run(*(Session*)session, opt));
+  } catch (const std::exception& ex) {
+    return dup(std::string("{\"error\":") + esc(ex.what()) + "}");
+  }
+}
+
+void ksbh_free(char* p) { free(p); }
+
+}  // extern "C"
