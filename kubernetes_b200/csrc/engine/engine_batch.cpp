@@ -255,8 +255,11 @@ void Engine::replay_last_batch(int iters, double* avg_ms, ksb_result* out) {
   CUDA_OK(cudaEventCreate(&ev1));
   double total = 0;
   uint64_t saved_index = last_node_index;
+  const size_t flush_bytes = (size_t)256 << 20;  // larger than the 126 MB L2
+  b_flush.ensure(flush_bytes);
   for (int it = 0; it < iters; ++it) {
     restore_dynamic();
+    CUDA_OK(cudaMemsetAsync(b_flush.d, it & 0xff, flush_bytes, stream));  // flush L2 between timed runs
     last_node_index = last_index_before;
     CUDA_OK(cudaStreamSynchronize(stream));
     CUDA_OK(cudaEventRecord(ev0, stream));

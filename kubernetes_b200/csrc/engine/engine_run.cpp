@@ -111,6 +111,14 @@ void Engine::commit_lists(const Pod& p, SigInfo* s, std::vector<CommitEntry>* co
     for (auto& t : req) held(TK_HELD_ANTI, t, req.back().topology_key, 1);
     for (auto& wt : p.affinity.anti.preferred) held(TK_HELD_W, wt.term, wt.term.topology_key, -wt.weight);
   }
+  // one entry per table: the device applies the list lane-parallel, so a table may appear only once
+  std::sort(commits->begin(), commits->end(), [](const CommitEntry& a, const CommitEntry& b) { return a.table < b.table; });
+  size_t w = 0;
+  for (size_t i = 0; i < commits->size(); ++i) {
+    if (w > 0 && (*commits)[w - 1].table == (*commits)[i].table) (*commits)[w - 1].delta += (*commits)[i].delta;
+    else (*commits)[w++] = (*commits)[i];
+  }
+  commits->resize(w);
 }
 
 // ------------------------------------------------------------------ encoder
