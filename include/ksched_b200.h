@@ -149,6 +149,25 @@ int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out);
  * return the average CUDA-event milliseconds per run (measurement only; state is restored). */
 int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_result* out);
 
+/* No counterpart in the reference. One run of what ksb_replay_last_batch runs (the resident batch,
+ * against the restored node table), for callers that must not allocate GPU memory while they work:
+ * a process confined to a fixed memory budget (a MIG slice or an MPS client with a hard limit, where
+ * a late cudaMalloc can fail), or code called back on another component's stream, where the
+ * device-wide synchronisation hidden in cudaMalloc/cudaFree would stall work that is not ours. This
+ * entry point calls no cudaMalloc, cudaFree or other allocating routine: the kernel's working memory
+ * is a fixed array inside the loaded library (about 2.1 MiB, held by every GPU that loads the library
+ * until the process exits), state is restored into buffers that already exist, and results are
+ * written directly into `out` (one ksb_result per pod of the batch, caller-owned).
+ *  - Limits: at most 65,536 padded node rows (node count rounded up to 256), 1,024 zone slots and
+ *    1,024 thread blocks; a batch beyond them is rejected with an error naming the limit.
+ *  - The first call on a GPU looks up that GPU's address of the array (cudaGetSymbolAddress, with
+ *    the engine's device current) and caches it: make that first call before starting any stream
+ *    capture.
+ *  - Every call, from every engine in the process, shares the one array, and the array keeps what
+ *    the last call left in it; the counters that must start at zero are cleared on each call. Two
+ *    calls whose kernels overlap on one GPU would race on it: serialise them. */
+int32_t ksb_replay_last_batch_noalloc(ksb_engine* e, ksb_result* out);
+
 #ifdef __cplusplus
 }
 #endif

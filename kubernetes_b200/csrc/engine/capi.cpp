@@ -166,4 +166,8 @@ int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_
   return guarded(e, [&] { e->impl->replay_last_batch(iters, avg_ms, out); });
 }
 
+int32_t ksb_replay_last_batch_noalloc(ksb_engine* e, ksb_result* out) {
+  return guarded(e, [&] { e->impl->replay_last_batch_noalloc(out); });
+}
+
 }  // extern "C"

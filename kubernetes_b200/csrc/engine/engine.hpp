@@ -106,6 +106,7 @@ class Engine {
   // hot path
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
+  void replay_last_batch_noalloc(ksb_result* out);
   std::string fit_error_message(int i);
 
   std::string last_error;

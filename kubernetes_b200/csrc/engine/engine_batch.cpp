@@ -288,6 +288,55 @@ void Engine::replay_last_batch(int iters, double* avg_ms, ksb_result* out) {
   }
 }
 
+// ksb_replay_last_batch_noalloc: the resident batch once more, with the kernel's working memory taken
+// from the module's static device array instead of the engine's cudaMalloc'd scratch. Nothing on this
+// path allocates: device state is restored with device-to-device copies into buffers that already
+// exist, the counters the kernel accumulates into are re-zeroed in place (the shared array still holds
+// the previous call's values), and results are copied straight into the caller's array.
+void Engine::replay_last_batch_noalloc(ksb_result* out) {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  if (!have_snapshot || last_encoded.empty()) throw std::runtime_error("no batch to replay");
+  if (!out) throw std::runtime_error("out must not be null");
+  static_assert(sizeof(ksb_result) == sizeof(KsbResult), "host and device result records must have one layout");
+  const int np = (int)last_encoded.size();
+  KsbBatchArgs a;
+  memset(&a, 0, sizeof a);
+  a.table = dT;
+  a.headers = (const KsbPodHeader*)b_headers.d;
+  a.pool = (const uint64_t*)b_pool.d;
+  a.n_pods = np;
+  a.commit = 1;
+  a.results = (KsbResult*)b_results.d;
+  char err[256] = {0};
+  if (ksb_noalloc_bind(cfg.device, n_pad, dT.n_zones, grid, &a, err, sizeof err) != 0) throw std::runtime_error(err);
+  restore_dynamic();
+  KsbNorms init[2];
+  memset(init, 0, sizeof init);
+  init[0].one_row = -1;
+  init[1].one_row = -1;
+  uint64_t seed = last_index_before;
+  CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)a.zone_stride * 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.barrier, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.error_flag, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.fiterr_count, 0, 4, stream));
+  CUDA_OK(cudaMemcpyAsync(a.last_node_index, &seed, 8, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));  // `init` and `seed` are locals
+  int rc = ksb_launch_batch(&a, grid, smem_bytes, stream);
+  if (rc != 0) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString((cudaError_t)rc));
+  stats.kernel_launches += 1;
+  int32_t flag = 0;
+  CUDA_OK(cudaMemcpyAsync(out, b_results.d, (size_t)np * sizeof(KsbResult), cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(&flag, a.error_flag, 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));
+  if (flag != 0) {
+    layout_dirty = true;
+    throw std::runtime_error("device kernel reported a barrier timeout");
+  }
+  for (int i = 0; i < np; ++i) out[i].num_nodes = n;  // the device record keeps a histogram slot in this field
+}
+
 // FitError.Error() (generic_scheduler.go:70-88)
 std::string Engine::fit_error_message(int i) {
   std::lock_guard<std::mutex> g(mu);

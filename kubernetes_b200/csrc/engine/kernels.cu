@@ -20,6 +20,7 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "device_types.h"
 #include "kernels.h"
@@ -747,3 +748,85 @@ extern "C" size_t ksb_batch_smem_bytes(int n_zones) {
   return sizeof(KsbPodHeader) + (size_t)kMaxPoolWords * 8 + (size_t)(n_zones + 1) * 4;
 }
 extern "C" int ksb_max_pool_words() { return kMaxPoolWords; }
+
+// ---------------------------------------------------------------------------------------------
+// Scratch for ksb_replay_last_batch_noalloc (include/ksched_b200.h).
+//
+// Some users of this library drive it from places where asking the CUDA runtime for device memory
+// is off the table: a control loop whose memory budget was fixed at start-up (a MIG slice or an MPS
+// client with a hard limit, where a late cudaMalloc may simply fail), or a callback running on
+// somebody else's stream where cudaMalloc's implicit device-wide synchronisation would stall
+// unrelated work. For them the batch kernel's working memory lives here, in one array that is part
+// of the loaded module: every GPU that loads the library carries these bytes until the process exits.
+// The limits below bound what fits; larger jobs must use ksb_replay_last_batch.
+//
+// All calls share the one array and it keeps whatever the previous call left behind, so the host
+// side re-zeroes the counters the kernel accumulates into before each launch, and two calls whose
+// kernels overlap on the same GPU would corrupt each other.
+#define KSB_NOALLOC_MAX_ROWS 65536    // padded node rows
+#define KSB_NOALLOC_MAX_ZONES 1024    // zone-sum slots per ping-pong half
+#define KSB_NOALLOC_MAX_GRID 1024     // thread blocks
+namespace {
+constexpr size_t na_align(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t kNaNorms = 0;
+constexpr size_t kNaZone = kNaNorms + na_align(2 * sizeof(KsbNorms));
+constexpr size_t kNaRaw = kNaZone + na_align(2 * (size_t)KSB_NOALLOC_MAX_ZONES * 4);
+constexpr size_t kNaScore = kNaRaw + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 16);
+constexpr size_t kNaReasons = kNaScore + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
+constexpr size_t kNaBlkMax = kNaReasons + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
+constexpr size_t kNaBlkCnt = kNaBlkMax + na_align((size_t)KSB_NOALLOC_MAX_GRID * 4);
+constexpr size_t kNaBarrier = kNaBlkCnt + na_align((size_t)KSB_NOALLOC_MAX_GRID * 4);
+constexpr size_t kNaError = kNaBarrier + 256;
+constexpr size_t kNaFitCount = kNaError + 256;
+constexpr size_t kNaLastIndex = kNaFitCount + 256;
+constexpr size_t kNaFitHist = kNaLastIndex + 256;
+constexpr size_t kNaTotal = kNaFitHist + na_align((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
+}  // namespace
+
+static __device__ __align__(256) unsigned char ksb_noalloc_scratch[kNaTotal];  // about 2.1 MiB
+
+// In host code `ksb_noalloc_scratch` is only a stand-in for the symbol, not a device address, so the
+// address each GPU gave the array is looked up once per device (with that device current) and cached.
+extern "C" int ksb_noalloc_bind(int device, int n_pad, int n_zones, int grid, KsbBatchArgs* a, char* err,
+                                size_t err_len) {
+  static unsigned char* base_of[64] = {nullptr};
+  auto fail = [&](const char* msg) {
+    if (err && err_len) snprintf(err, err_len, "%s", msg);
+    return -1;
+  };
+  if (device < 0 || device >= 64) return fail("device ordinal out of range");
+  if (n_pad > KSB_NOALLOC_MAX_ROWS || n_zones > KSB_NOALLOC_MAX_ZONES || grid > KSB_NOALLOC_MAX_GRID) {
+    if (err && err_len)
+      snprintf(err, err_len,
+               "batch exceeds the no-allocation limits: %d padded node rows (max %d), %d zone slots (max %d), "
+               "%d blocks (max %d); use ksb_replay_last_batch",
+               n_pad, KSB_NOALLOC_MAX_ROWS, n_zones, KSB_NOALLOC_MAX_ZONES, grid, KSB_NOALLOC_MAX_GRID);
+    return -1;
+  }
+  if (!base_of[device]) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != device) return fail("the engine's device is not current");
+    unsigned char* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, ksb_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      if (err && err_len) snprintf(err, err_len, "cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return -1;
+    }
+    base_of[device] = p;
+  }
+  unsigned char* b = base_of[device];
+  a->norms = (KsbNorms*)(b + kNaNorms);
+  a->zone_sum = (int32_t*)(b + kNaZone);
+  a->zone_stride = KSB_NOALLOC_MAX_ZONES;
+  a->raw = (int4*)(b + kNaRaw);
+  a->score = (int32_t*)(b + kNaScore);
+  a->reasons = (uint32_t*)(b + kNaReasons);
+  a->blk_max = (int32_t*)(b + kNaBlkMax);
+  a->blk_cnt = (int32_t*)(b + kNaBlkCnt);
+  a->barrier = (uint32_t*)(b + kNaBarrier);
+  a->error_flag = (int32_t*)(b + kNaError);
+  a->fiterr_count = (int32_t*)(b + kNaFitCount);
+  a->last_node_index = (uint64_t*)(b + kNaLastIndex);
+  a->fiterr_hist = (int32_t*)(b + kNaFitHist);
+  return 0;
+}

@@ -37,4 +37,7 @@ int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* header, const ui
                      const uint32_t* masks, cudaStream_t stream);
 size_t ksb_batch_smem_bytes(int n_zones);
 int ksb_max_pool_words();
+// Point the scratch fields of *a at the module's static device array (no allocation); -1 + text on
+// error, including batches beyond the array's stated limits.
+int ksb_noalloc_bind(int device, int n_pad, int n_zones, int grid, KsbBatchArgs* a, char* err, size_t err_len);
 }
