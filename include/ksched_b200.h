@@ -141,6 +141,9 @@ typedef struct ksb_stats {
   double last_batch_encode_ms; /* host time spent encoding the last batch */
   int32_t num_nodes;
   int32_t node_row_bytes;      /* bytes of node-table columns one (pod,node) evaluation may read */
+  /* SM cycles block 0 spent, last batch: staging, phase 1, barrier 1, phase 2, barrier 2, phase 3, barrier 3;
+   * then inside phase 3: prefetch, changed rows, select, commit, wait, deferred FitError histograms */
+  uint64_t stage_cycles[13];
 } ksb_stats;
 int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out);
 
@@ -155,7 +158,7 @@ int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_
  * a late cudaMalloc can fail), or code called back on another component's stream, where the
  * device-wide synchronisation hidden in cudaMalloc/cudaFree would stall work that is not ours. This
  * entry point calls no cudaMalloc, cudaFree or other allocating routine: the kernel's working memory
- * is a fixed array inside the loaded library (about 2.1 MiB, held by every GPU that loads the library
+ * is a fixed array inside the loaded library (about 2.4 MiB, held by every GPU that loads the library
  * until the process exits), state is restored into buffers that already exist, and results are
  * written directly into `out` (one ksb_result per pod of the batch, caller-owned).
  *  - Limits: at most 65,536 padded node rows (node count rounded up to 256), 1,024 zone slots and

@@ -18,6 +18,9 @@
 #define KSB_MAX_DEV 32        // devices per (node, resource)
 #define KSB_MAX_FITERR 4096   // no-fit pods per batch that keep a reason histogram
 #define KSB_REASON_BITS 32
+#define KSB_MAX_GROUP 32      // pods evaluated against one snapshot of the table
+#define KSB_MAX_SEGMENTS 2048 // 256-row segments per shard (524,288 node rows)
+#define KSB_SEG_CACHE 4096    // (group size) x (segments) bound: segment statistics held in shared memory
 
 // node flags (predicates.go:1382-1441)
 #define NF_NOT_READY 1u

@@ -73,7 +73,7 @@ Engine::Engine(const ksb_config& c) : cfg(c) {
 Engine::~Engine() {
   cudaSetDevice(cfg.device);
   for (DevBuf* b : {&b_i64, &b_u32, &b_u64, &b_dev_class, &b_topo, &b_spread, &b_tables, &b_headers, &b_pool,
-                    &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush})
+                    &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush, &b_dep})
     b->release();
   if (stream) cudaStreamDestroy(stream);
 }

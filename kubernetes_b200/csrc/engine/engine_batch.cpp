@@ -19,11 +19,10 @@ namespace ksb {
 
 namespace {
 struct ScratchLayout {
-  size_t norms, zone_sum, raw, score, reasons, blk_max, blk_cnt, barrier, error_flag, fiterr_count, last_index,
-      fiterr_hist, total;
-  int zone_stride;
+  size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, barrier, error_flag, fiterr_count, last_index,
+      group_done, counters, ghist, fiterr_hist, total;
 };
-ScratchLayout scratch_layout(int n_pad, int n_zones, int grid) {
+ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   ScratchLayout L;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -31,18 +30,20 @@ ScratchLayout scratch_layout(int n_pad, int n_zones, int grid) {
     off += (bytes + 255) & ~(size_t)255;
     return o;
   };
-  L.zone_stride = (n_zones + 63) & ~63;
-  L.norms = take(2 * sizeof(KsbNorms));
-  L.zone_sum = take(2 * (size_t)L.zone_stride * 4);
-  L.raw = take((size_t)n_pad * 16);
-  L.score = take((size_t)n_pad * 4);
-  L.reasons = take((size_t)n_pad * 4);
-  L.blk_max = take((size_t)grid * 4);
-  L.blk_cnt = take((size_t)grid * 4);
+  L.norms = take(2 * (size_t)KSB_MAX_GROUP * sizeof(KsbNorms));
+  L.zone_sum = take(2 * (size_t)KSB_MAX_GROUP * zone_stride * 4);
+  L.raw = take((size_t)G * n_pad * 16);
+  L.score = take((size_t)G * n_pad * 4);
+  L.reasons = take((size_t)G * n_pad * 4);
+  L.seg_max = take((size_t)G * nseg * 4);
+  L.seg_cnt = take((size_t)G * nseg * 4);
   L.barrier = take(4);
   L.error_flag = take(4);
   L.fiterr_count = take(4);
   L.last_index = take(8);
+  L.group_done = take(8);
+  L.counters = take(128);
+  L.ghist = take(2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
   L.total = off;
   return L;
@@ -50,56 +51,72 @@ ScratchLayout scratch_layout(int n_pad, int n_zones, int grid) {
 }  // namespace
 
 KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
-  const int n_zones = dT.n_zones;
-  smem_bytes = ksb_batch_smem_bytes(n_zones);
+  zone_stride = (dT.n_zones + 63) & ~63;
+  // group size: as configured, bounded by what the zone-sum arrays may take of shared memory
+  group = cfg.group_size > 0 ? std::min(cfg.group_size, KSB_MAX_GROUP) : KSB_MAX_GROUP;
+  group = std::max(1, std::min(group, 16384 / zone_stride));
+  nseg = (n + 255) / 256;
+  if (nseg > KSB_MAX_SEGMENTS) throw std::runtime_error("more than 524,288 node rows in one shard");
+  group = std::max(1, std::min(group, KSB_SEG_CACHE / nseg));
+  if (zone_stride * 4 * KSB_MAX_GROUP > 160 * 1024) throw std::runtime_error("more than 1,280 distinct zones");
+  smem_bytes = ksb_batch_smem_bytes(zone_stride);
   int mg = 0, th = 0;
   int rc = ksb_batch_kernel_limits(cfg.device, smem_bytes, &mg, &th);
   if (rc != 0) throw std::runtime_error(std::string("kernel attribute query failed: ") + cudaGetErrorString((cudaError_t)rc));
   max_grid = mg;
   threads = th;
-  grid = std::max(1, std::min(max_grid, (n + threads - 1) / threads));
-  ScratchLayout L = scratch_layout(n_pad, n_zones, grid);
+  if (max_grid < 1) throw std::runtime_error("batch kernel does not fit on this device");
+  // enough blocks to cover every segment; when segments are few, extra blocks split the group's pods
+  grid = nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, nseg * group));
+  ScratchLayout L = scratch_layout(n_pad, zone_stride, nseg, group);
   b_scratch.ensure(L.total);
   char* base = (char*)b_scratch.d;
   KsbBatchArgs a;
+  memset(&a, 0, sizeof a);
   a.table = dT;
   a.headers = (const KsbPodHeader*)b_headers.d;
   a.pool = (const uint64_t*)b_pool.d;
+  a.dep = (const int32_t*)b_dep.d;
   a.n_pods = n_pods;
-  a.zone_stride = L.zone_stride;
+  a.zone_stride = zone_stride;
   a.commit = commit ? 1 : 0;
-  a.pad0 = 0;
+  a.group_size = group;
+  a.nseg = nseg;
   a.results = (KsbResult*)b_results.d;
   a.norms = (KsbNorms*)(base + L.norms);
   a.zone_sum = (int32_t*)(base + L.zone_sum);
   a.raw = (int4*)(base + L.raw);
   a.score = (int32_t*)(base + L.score);
   a.reasons = (uint32_t*)(base + L.reasons);
-  a.blk_max = (int32_t*)(base + L.blk_max);
-  a.blk_cnt = (int32_t*)(base + L.blk_cnt);
+  a.seg_max = (int32_t*)(base + L.seg_max);
+  a.seg_cnt = (int32_t*)(base + L.seg_cnt);
   a.barrier = (uint32_t*)(base + L.barrier);
   a.error_flag = (int32_t*)(base + L.error_flag);
   a.fiterr_count = (int32_t*)(base + L.fiterr_count);
   a.fiterr_hist = (int32_t*)(base + L.fiterr_hist);
   a.last_node_index = (uint64_t*)(base + L.last_index);
+  a.group_done = (int32_t*)(base + L.group_done);
+  a.counters = (uint64_t*)(base + L.counters);
+  a.ghist = (int32_t*)(base + L.ghist);
   return a;
 }
 
-// Zero what must start at zero, seed the round-robin counter, launch.
+// Zero what must start at zero, seed the round-robin counter, launch. Works on whatever scratch the
+// arguments point at (the engine's own buffer or the static no-allocation array).
 void Engine::launch(const KsbBatchArgs& a) {
-  ScratchLayout L = scratch_layout(n_pad, dT.n_zones, grid);
-  char* base = (char*)b_scratch.d;
-  KsbNorms init[2];
+  static KsbNorms init[2 * KSB_MAX_GROUP];
   memset(init, 0, sizeof init);
-  init[0].one_row = -1;
-  init[1].one_row = -1;
-  CUDA_OK(cudaMemcpyAsync(base + L.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemsetAsync(base + L.zone_sum, 0, 2 * (size_t)L.zone_stride * 4, stream));
-  CUDA_OK(cudaMemsetAsync(base + L.barrier, 0, 4, stream));
-  CUDA_OK(cudaMemsetAsync(base + L.error_flag, 0, 4, stream));
-  CUDA_OK(cudaMemsetAsync(base + L.fiterr_count, 0, 4, stream));
-  CUDA_OK(cudaMemcpyAsync(base + L.last_index, &last_node_index, 8, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaStreamSynchronize(stream));  // `init` is a local
+  for (auto& x : init) x.one_row = -1;
+  CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)KSB_MAX_GROUP * a.zone_stride * 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.barrier, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.error_flag, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.fiterr_count, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.group_done, 0, 8, stream));
+  CUDA_OK(cudaMemsetAsync(a.counters, 0, 128, stream));
+  CUDA_OK(cudaMemsetAsync(a.ghist, 0, 2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4, stream));
+  CUDA_OK(cudaMemcpyAsync(a.last_node_index, &last_node_index, 8, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));  // last_node_index may change right after this call
   int rc = ksb_launch_batch(&a, grid, smem_bytes, stream);
   if (rc != 0) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString((cudaError_t)rc));
   stats.kernel_launches += 1;
@@ -168,6 +185,30 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     pool.insert(pool.end(), last_encoded[i].pool.begin(), last_encoded[i].pool.end());
   }
   if (pool.empty()) pool.push_back(0);
+  // dep[j]: the latest earlier pod whose assume step bumps a counter pod j reads (its SelectorSpread column
+  // or any inter-pod-affinity table). A group never holds both, so those inputs are constant inside a group.
+  std::vector<int32_t> dep(np, -1);
+  {
+    std::vector<int32_t> last_spread(h_spread.size(), -1), last_table(tables.size(), -1);
+    std::unordered_map<uint32_t, int> table_by_off;
+    for (size_t t = 0; t < tables.size(); ++t) table_by_off[tables[t].off] = (int)t;
+    for (int i = 0; i < np; ++i) {
+      const EncodedPod& e = last_encoded[i];
+      int32_t d = -1;
+      if (e.h.spread_col >= 0) d = std::max(d, last_spread[e.h.spread_col]);
+      const uint64_t* pw = e.pool.data() + (size_t)e.h.n_exprs * W + ((e.h.flags & PF_HAS_PORTS) ? 6 * KSB_PORT_WORDS : 0) +
+                           (size_t)e.h.n_ext * KSB_CLASS_WORDS;
+      for (int c = 0; c < e.h.n_checks; ++c) {
+        if (((pw[c] >> 40) & 0xff) == CM_FAIL_ALWAYS) continue;
+        d = std::max(d, last_table[table_by_off.at((uint32_t)pw[c])]);
+      }
+      pw += e.h.n_checks;
+      for (int c = 0; c < e.h.n_score; ++c) d = std::max(d, last_table[table_by_off.at((uint32_t)pw[2 * c])]);
+      dep[i] = d;
+      for (int c : e.spread_inc) last_spread[c] = i;
+      for (auto& c : e.commits) last_table[c.table] = i;
+    }
+  }
   auto t1 = std::chrono::steady_clock::now();
   stats.last_batch_encode_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
 
@@ -175,9 +216,11 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   b_headers.ensure(headers.size() * sizeof(KsbPodHeader));
   b_pool.ensure(pool.size() * 8);
   b_results.ensure((size_t)np * sizeof(KsbResult));
+  b_dep.ensure((size_t)np * 4);
+  CUDA_OK(cudaMemcpyAsync(b_dep.d, dep.data(), (size_t)np * 4, cudaMemcpyHostToDevice, stream));
   CUDA_OK(cudaMemcpyAsync(b_headers.d, headers.data(), headers.size() * sizeof(KsbPodHeader), cudaMemcpyHostToDevice, stream));
   CUDA_OK(cudaMemcpyAsync(b_pool.d, pool.data(), pool.size() * 8, cudaMemcpyHostToDevice, stream));
-  stats.h2d_bytes += headers.size() * sizeof(KsbPodHeader) + pool.size() * 8;
+  stats.h2d_bytes += headers.size() * sizeof(KsbPodHeader) + pool.size() * 8 + (size_t)np * 4;
   KsbBatchArgs a = make_args(np, assume);
   if (assume) snapshot_dynamic();
   last_index_before = last_node_index;
@@ -194,6 +237,8 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   CUDA_OK(cudaMemcpyAsync(&flags[0], a.error_flag, 4, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaMemcpyAsync(&flags[1], a.fiterr_count, 4, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaMemcpyAsync(&last_node_index, a.last_node_index, 8, cudaMemcpyDeviceToHost, stream));
+  uint64_t counters[15] = {0};
+  CUDA_OK(cudaMemcpyAsync(counters, a.counters, sizeof counters, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaStreamSynchronize(stream));
   float ms = 0;
   CUDA_OK(cudaEventElapsedTime(&ms, ev0, ev1));
@@ -212,7 +257,9 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     stats.d2h_bytes += last_fiterr_hist.size() * 4;
   }
   stats.pods_scheduled += np;
-  stats.groups += np;
+  stats.groups += counters[0];
+  stats.group_restarts += counters[1];
+  for (int i = 0; i < 13; ++i) stats.stage_cycles[i] = counters[2 + i];
 
   for (int i = 0; i < np; ++i) {
     const KsbResult& r = last_results[i];
@@ -309,23 +356,15 @@ void Engine::replay_last_batch_noalloc(ksb_result* out) {
   a.commit = 1;
   a.results = (KsbResult*)b_results.d;
   char err[256] = {0};
-  if (ksb_noalloc_bind(cfg.device, n_pad, dT.n_zones, grid, &a, err, sizeof err) != 0) throw std::runtime_error(err);
+  a.dep = (const int32_t*)b_dep.d;
+  a.zone_stride = zone_stride;
+  a.nseg = nseg;
+  if (ksb_noalloc_bind(cfg.device, n_pad, zone_stride, grid, &a, err, sizeof err) != 0) throw std::runtime_error(err);
   restore_dynamic();
-  KsbNorms init[2];
-  memset(init, 0, sizeof init);
-  init[0].one_row = -1;
-  init[1].one_row = -1;
-  uint64_t seed = last_index_before;
-  CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)a.zone_stride * 4, stream));
-  CUDA_OK(cudaMemsetAsync(a.barrier, 0, 4, stream));
-  CUDA_OK(cudaMemsetAsync(a.error_flag, 0, 4, stream));
-  CUDA_OK(cudaMemsetAsync(a.fiterr_count, 0, 4, stream));
-  CUDA_OK(cudaMemcpyAsync(a.last_node_index, &seed, 8, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaStreamSynchronize(stream));  // `init` and `seed` are locals
-  int rc = ksb_launch_batch(&a, grid, smem_bytes, stream);
-  if (rc != 0) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString((cudaError_t)rc));
-  stats.kernel_launches += 1;
+  const uint64_t saved_index = last_node_index;
+  last_node_index = last_index_before;  // launch() seeds the device counter from this member
+  launch(a);                            // async copies/memsets + one kernel launch: nothing allocates
+  last_node_index = saved_index;
   int32_t flag = 0;
   CUDA_OK(cudaMemcpyAsync(out, b_results.d, (size_t)np * sizeof(KsbResult), cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaMemcpyAsync(&flag, a.error_flag, 4, cudaMemcpyDeviceToHost, stream));

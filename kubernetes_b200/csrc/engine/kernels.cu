@@ -1,23 +1,42 @@
 // sm_100a kernels of the scheduling engine.
 //
-// One persistent cooperative kernel walks a batch of pods in FIFO order and, per pod, does
-// what genericScheduler.Schedule does (reference, paths under plugin/pkg/scheduler):
-//   phase 1  findNodesThatFit   core/generic_scheduler.go:283-362  -> eval_node (all predicates,
-//            the fork's device matching core/extended_resources.go:83-150, and the Map half of
-//            every priority) + grid-wide reductions of the Reduce inputs
-//   phase 2  PrioritizeNodes    core/generic_scheduler.go:509-640  -> final integer score per node
-//            + per-block (max, tie count)
+// One persistent cooperative kernel walks a batch of pods in FIFO order. Pods are taken in GROUPS of
+// up to 32: every pod of a group is evaluated against the node table as it stands when the group
+// starts (phases 1 and 2, all blocks), then block 0 commits the group's pods one by one, in order,
+// re-evaluating only the rows changed by the pods committed before (phase 3). What the reference
+// does per pod (paths under /root/reference/plugin/pkg/scheduler):
+//   phase 1  findNodesThatFit   core/generic_scheduler.go:283-362  -> eval_node: every predicate, the
+//            fork's device matching (core/extended_resources.go:83-150) and the Map half of every
+//            priority, + grid-wide reductions of the Reduce inputs
+//   phase 2  PrioritizeNodes    core/generic_scheduler.go:509-640  -> final integer score per node,
+//            per 256-row segment (max, tie count)
 //   phase 3  selectHost         core/generic_scheduler.go:177-192  -> round-robin pick among the
-//            max-score ties in descending name (= row) order, then the assume step
-//            (scheduler.go:478 -> schedulercache/node_info.go:329-356) applied to the one node
-//            column that changed, so the next pod sees it exactly as the reference would.
+//            max-score ties in descending name (= row) order, then the assume step (scheduler.go:478 ->
+//            schedulercache/node_info.go:329-356) on the chosen row.
 //
-// The path is integer/bit work over a structure-of-arrays node table: one thread per node,
-// every column read is a coalesced 4/8-byte load, the pod's requirement block is staged in
-// shared memory, reductions are warp shuffles (redux) + one atomic per block. No tensor cores:
-// nothing here is a dense contraction. float64 priorities use __d*_rn so no FMA is ever formed
-// (Go on amd64 never fuses; the file is also compiled with -fmad=false).
-#include <cooperative_groups.h>
+// Why grouping is exact. A pod's evaluation can differ from its group-start evaluation only through
+//  (a) counters other pods bump (SelectorSpread columns, inter-pod-affinity tables): the host marks, per
+//      pod, the latest earlier pod that writes anything it reads (`dep`), and a group never contains
+//      both, so inside a group these inputs are constant;
+//  (b) the rows of nodes chosen earlier in the group: phase 3 re-evaluates exactly those rows against
+//      the current table. Binding only ever adds load, so a row can only turn from fit to unfit; if
+//      that happens for a row that was fit at group start, the Reduce inputs (maxima, zone sums, fit
+//      count) may have moved, the speculation is dropped and the group ends before that pod, which is
+//      then re-evaluated from scratch as the first pod of the next group. Otherwise every unchanged
+//      row keeps its group-start score, the changed rows get fresh ones, and the per-segment tie counts
+//      are patched before the rank-select.
+// With group size 1 this degenerates to evaluating every pod against the live table.
+//
+// Phase 3 is a single warp: the changed rows' mutable columns live in a shared-memory row cache (filled
+// when a row is first chosen, updated by every later commit), so re-evaluating a pod on them costs no
+// memory round trip; the group's segment statistics are prefetched into shared memory; FitError
+// histograms are deferred to the end of the group and built by all warps.
+//
+// The work is integer/bit work over a structure-of-arrays node table: one thread per node, coalesced
+// 4/8-byte column loads (re-reads across the pods of a group hit L1), requirement blocks staged in
+// shared memory, reductions by warp shuffle (redux) + one atomic per block. No tensor cores: nothing
+// here is a dense contraction. float64 priorities use __d*_rn so no FMA is ever formed (Go on amd64
+// never fuses; the file is also compiled with -fmad=false).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -28,7 +47,19 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxPoolWords = 1024;  // pool words one pod may use (checked on the host)
+constexpr int kWarps = kThreads / 32;
+constexpr int kSeg = 256;             // rows per segment (= per block iteration)
+constexpr int kMaxG = KSB_MAX_GROUP;  // pods per group
+constexpr int kMaxPoolWords = 1024;   // pool words one pod may use (checked on the host)
+constexpr int kGroupPoolWords = 4096; // pool words staged per group
+constexpr int kMaxSeg = KSB_MAX_SEGMENTS;
+constexpr int kSegCache = KSB_SEG_CACHE;  // (pods in group) x (segments) entries of segment stats kept in shared memory
+
+template <bool CG, typename V>
+__device__ __forceinline__ V ldx(const V* p) {
+  if (CG) return __ldcg(p);  // L2-coherent: rows block 0 itself just rewrote
+  return *p;
+}
 
 struct PodView {
   const KsbPodHeader* h;
@@ -85,22 +116,18 @@ __device__ __forceinline__ int64_t unused_score(int64_t requested, int64_t capac
 
 // The fork's per-node device selection (core/extended_resources.go:83-150), devices visited in
 // ascending id order (= bit order). Returns the failing reason bit or 0; fills picks[] on success.
+// `avail_in` holds the node's available-device masks per resource slot.
 __device__ __forceinline__ uint32_t select_devices(const KsbNodeTable& T, int r, const PodView& pv, uint32_t nflags,
-                                                   uint32_t* picks) {
+                                                   const uint32_t* avail_in, uint32_t* picks) {
   const KsbPodHeader* h = pv.h;
   uint32_t avail[KSB_MAX_RES];
-  bool loaded[KSB_MAX_RES];
 #pragma unroll
-  for (int s = 0; s < KSB_MAX_RES; ++s) loaded[s] = false;
+  for (int s = 0; s < KSB_MAX_RES; ++s) avail[s] = avail_in[s];
   for (int i = 0; i < h->n_ext; ++i) {
     if ((h->flags & PF_EXT_LIMITS_ERROR) && i == h->ext_err_entry) return 1u << RB_EXT_LIMITS;
     int rs = h->ext[i].rslot;
     int num = h->ext[i].num;
     if (rs == 255 || !(nflags & (256u << rs))) return 1u << (RB_EXT0 + i);  // available[rName] missing
-    if (!loaded[rs]) {
-      avail[rs] = T.dev_avail[(size_t)rs * T.n_pad + r];
-      loaded[rs] = true;
-    }
     uint32_t a = avail[rs];
     uint32_t sel = 0;
     int got = 0;
@@ -109,7 +136,7 @@ __device__ __forceinline__ uint32_t select_devices(const KsbNodeTable& T, int r,
       const uint4* cls4 = reinterpret_cast<const uint4*>(T.dev_class + ((size_t)rs * T.n_pad + r) * KSB_MAX_DEV);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        uint4 v = cls4[q];
+        uint4 v = cls4[q];  // device classes are static: never rewritten by the kernel
         uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -146,6 +173,8 @@ __device__ __forceinline__ bool eval_expr(const uint64_t* lab, const uint64_t* m
 
 // Everything the reference computes for one (pod, node): podFitsOnNode's predicates
 // (core/generic_scheduler.go:402-501) and the Map functions of PrioritizeNodes (:557-574).
+// CG = true reads the columns the kernel mutates straight from L2 (phase 3, rows just rewritten).
+template <bool CG>
 __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const PodView& pv, EvalOut& o,
                                           uint32_t* picks) {
   const KsbPodHeader* h = pv.h;
@@ -154,22 +183,23 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
   const uint32_t pf = h->flags;
 
   // --- PodFitsResources (predicates.go:630-687)
-  const int32_t num_pods = T.num_pods[r];
+  const int32_t num_pods = ldx<CG>(T.num_pods + r);
   const int32_t alloc_pods = T.alloc_pods[r];
   const int64_t acpu = T.alloc_cpu[r], amem = T.alloc_mem[r];
-  const int64_t ncpu = T.nz_cpu[r], nmem = T.nz_mem[r];
+  const int64_t ncpu = ldx<CG>(T.nz_cpu + r), nmem = ldx<CG>(T.nz_mem + r);
   const uint32_t nflags = T.flags[r];
   if (num_pods + 1 > alloc_pods) reasons |= 1u << RB_PODS;
   if (pf & PF_HAS_REQUEST) {
-    if (acpu < h->req_cpu + T.req_cpu[r]) reasons |= 1u << RB_CPU;
-    if (amem < h->req_mem + T.req_mem[r]) reasons |= 1u << RB_MEM;
-    if (T.alloc_agpu[r] < h->req_agpu + T.req_agpu[r]) reasons |= 1u << RB_AGPU;
-    if (T.alloc_eph[r] < h->req_eph + T.req_eph[r]) reasons |= 1u << RB_EPH;
+    if (acpu < h->req_cpu + ldx<CG>(T.req_cpu + r)) reasons |= 1u << RB_CPU;
+    if (amem < h->req_mem + ldx<CG>(T.req_mem + r)) reasons |= 1u << RB_MEM;
+    if (T.alloc_agpu[r] < h->req_agpu + ldx<CG>(T.req_agpu + r)) reasons |= 1u << RB_AGPU;
+    if (T.alloc_eph[r] < h->req_eph + ldx<CG>(T.req_eph + r)) reasons |= 1u << RB_EPH;
     uint32_t sm = h->scalar_mask;
 #pragma unroll
     for (int s = 0; s < KSB_MAX_SCALARS; ++s)
       if ((sm >> s) & 1u)
-        if (T.alloc_scalar[s * np + r] < h->scalar_req[s] + T.req_scalar[s * np + r]) reasons |= 1u << (RB_SCALAR0 + s);
+        if (T.alloc_scalar[s * np + r] < h->scalar_req[s] + ldx<CG>(T.req_scalar + s * np + r))
+          reasons |= 1u << (RB_SCALAR0 + s);
   }
   // --- PodFitsHost (predicates.go:764-776)
   if (h->pinned_row != -1 && h->pinned_row != T.row_base + r) reasons |= 1u << RB_HOSTNAME;
@@ -178,9 +208,9 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
     uint64_t hit = 0;
 #pragma unroll
     for (int w = 0; w < KSB_PORT_WORDS; ++w) {
-      hit |= T.port_any[w * np + r] & pv.ports[w];
-      hit |= T.port_wild[w * np + r] & pv.ports[KSB_PORT_WORDS + w];
-      hit |= T.port_exact[w * np + r] & pv.ports[2 * KSB_PORT_WORDS + w];
+      hit |= ldx<CG>(T.port_any + w * np + r) & pv.ports[w];
+      hit |= ldx<CG>(T.port_wild + w * np + r) & pv.ports[KSB_PORT_WORDS + w];
+      hit |= ldx<CG>(T.port_exact + w * np + r) & pv.ports[2 * KSB_PORT_WORDS + w];
     }
     if (hit) reasons |= 1u << RB_PORTS;
   }
@@ -226,7 +256,8 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
   if (nflags & NF_OUT_OF_DISK) reasons |= 1u << RB_OUT_OF_DISK;
   if (nflags & NF_NET_UNAVAILABLE) reasons |= 1u << RB_NET_UNAVAILABLE;
   if (nflags & NF_UNSCHEDULABLE) reasons |= 1u << RB_UNSCHEDULABLE;
-  // --- MatchInterPodAffinity (predicates.go:1047-1346) over per-(term class, topology domain) counts
+  // --- MatchInterPodAffinity (predicates.go:1047-1346) over per-(term class, topology domain) counts.
+  //     Inside a group no pod reads a table an earlier pod of the group writes, so plain loads do.
   for (int i = 0; i < h->n_checks; ++i) {
     uint64_t c = pv.checks[i];
     uint32_t off = (uint32_t)c;
@@ -234,13 +265,13 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
     uint32_t mode = (uint32_t)(c >> 40) & 0xffu;
     uint32_t self = (uint32_t)(c >> 48) & 1u;
     uint32_t d = mode == CM_FAIL_ALWAYS ? 0u : T.topo[tk * np + r];
-    bool in_domain = d != 0 && T.tables[off + d] > 0;
+    bool in_domain = d != 0 && ldx<CG>(T.tables + off + d) > 0;
     uint32_t bad = 0;
     if (mode == CM_FORBID_EXISTING) {
       if (in_domain) bad = 1u << RB_IPA_EXISTING_ANTI;
     } else if (mode == CM_REQUIRE) {
       if (!in_domain) {
-        bool exists = T.tables[off] > 0;  // slot 0: matching pods anywhere
+        bool exists = ldx<CG>(T.tables + off) > 0;  // slot 0: matching pods anywhere
         if (exists || !self) bad = 1u << RB_IPA_AFFINITY;
       }
     } else if (mode == CM_FORBID_OWN) {
@@ -256,7 +287,10 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
   // --- fork: device selection runs only on nodes that passed every predicate (generic_scheduler.go:357)
   if (reasons == 0 && h->n_ext) {
     uint32_t local[KSB_MAX_EXT];
-    uint32_t bad = select_devices(T, r, pv, nflags, picks ? picks : local);
+    uint32_t avail[KSB_MAX_RES];
+#pragma unroll
+    for (int s = 0; s < KSB_MAX_RES; ++s) avail[s] = ldx<CG>(T.dev_avail + (size_t)s * np + r);
+    uint32_t bad = select_devices(T, r, pv, nflags, avail, picks ? picks : local);
     reasons |= bad;
   }
 
@@ -276,12 +310,12 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
   o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
   o.na = na;
   o.tt = tt;
-  o.sc = h->spread_col >= 0 ? T.spread[(size_t)h->spread_col * np + r] : 0u;  // selector_spreading.go:64-113
+  o.sc = h->spread_col >= 0 ? ldx<CG>(T.spread + (size_t)h->spread_col * np + r) : 0u;  // selector_spreading.go:64-113
   int64_t ipa = 0;  // interpod_affinity.go:121-216
   for (int i = 0; i < h->n_score; ++i) {
     uint64_t c = pv.score[2 * i];
     uint32_t d = T.topo[((uint32_t)(c >> 32) & 0xffu) * np + r];
-    if (d) ipa += (int64_t)pv.score[2 * i + 1] * (int64_t)T.tables[(uint32_t)c + d];
+    if (d) ipa += (int64_t)pv.score[2 * i + 1] * (int64_t)ldx<CG>(T.tables + (uint32_t)c + d);
   }
   o.ipa = (int32_t)ipa;
   o.zone = T.zone[r];
@@ -289,9 +323,9 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
 }
 
 // PrioritizeNodes' Reduce functions and weighted sum (generic_scheduler.go:575-606).
-__device__ __forceinline__ int32_t final_score(const KsbNodeTable& T, const KsbPodHeader* h, const KsbNorms& nm,
-                                               const int32_t* zone_sum, int32_t max_zone, int32_t base, int32_t na,
-                                               int32_t tt, uint32_t sc, int32_t ipa, uint32_t zone) {
+__device__ __forceinline__ int32_t final_score(const KsbNodeTable& T, const KsbNorms& nm, const int32_t* zone_sum,
+                                               int32_t max_zone, int32_t base, int32_t na, int32_t tt, uint32_t sc,
+                                               int32_t ipa, uint32_t zone) {
   // selector_spreading.go:119-174
   double f = 10.0;
   if (nm.max_sc > 0) f = __dmul_rn(10.0, __ddiv_rn((double)(nm.max_sc - (int32_t)sc), (double)nm.max_sc));
@@ -343,25 +377,27 @@ __device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch) {
 }
 
 // The assume step on the chosen node: NodeInfo.AddPod (schedulercache/node_info.go:329-356) plus
-// the per-class counters that stand in for the node's pod list. One warp, lane-parallel where it can be.
+// the per-class counters that stand in for the node's pod list. One warp, lane-parallel where it can
+// be. Reads bypass L1: the same row may be committed twice within one group.
 __device__ __forceinline__ void commit_pod(const KsbNodeTable& T, int r, const PodView& pv, const uint32_t* picks) {
   const KsbPodHeader* h = pv.h;
   const size_t np = T.n_pad;
   const int lane = threadIdx.x & 31;
   if (lane == 0) {
-    T.req_cpu[r] += h->add_cpu;
-    T.req_mem[r] += h->add_mem;
-    T.req_agpu[r] += h->add_agpu;
-    T.req_eph[r] += h->add_eph;
-    T.nz_cpu[r] += h->nz_cpu;
-    T.nz_mem[r] += h->nz_mem;
-    T.num_pods[r] += 1;
+    T.req_cpu[r] = __ldcg(T.req_cpu + r) + h->add_cpu;
+    T.req_mem[r] = __ldcg(T.req_mem + r) + h->add_mem;
+    T.req_agpu[r] = __ldcg(T.req_agpu + r) + h->add_agpu;
+    T.req_eph[r] = __ldcg(T.req_eph + r) + h->add_eph;
+    T.nz_cpu[r] = __ldcg(T.nz_cpu + r) + h->nz_cpu;
+    T.nz_mem[r] = __ldcg(T.nz_mem + r) + h->nz_mem;
+    T.num_pods[r] = __ldcg(T.num_pods + r) + 1;
   }
-  if (lane < KSB_MAX_SCALARS && h->scalar_add[lane] != 0) T.req_scalar[lane * np + r] += h->scalar_add[lane];
+  if (lane < KSB_MAX_SCALARS && h->scalar_add[lane] != 0)
+    T.req_scalar[lane * np + r] = __ldcg(T.req_scalar + lane * np + r) + h->scalar_add[lane];
   if ((h->flags & PF_HAS_PORTS) && lane < KSB_PORT_WORDS) {
-    T.port_any[lane * np + r] |= pv.ports[3 * KSB_PORT_WORDS + lane];
-    T.port_wild[lane * np + r] |= pv.ports[4 * KSB_PORT_WORDS + lane];
-    T.port_exact[lane * np + r] |= pv.ports[5 * KSB_PORT_WORDS + lane];
+    T.port_any[lane * np + r] = __ldcg(T.port_any + lane * np + r) | pv.ports[3 * KSB_PORT_WORDS + lane];
+    T.port_wild[lane * np + r] = __ldcg(T.port_wild + lane * np + r) | pv.ports[4 * KSB_PORT_WORDS + lane];
+    T.port_exact[lane * np + r] = __ldcg(T.port_exact + lane * np + r) | pv.ports[5 * KSB_PORT_WORDS + lane];
   }
   if (lane == 1 && h->n_ext) {
     // bind echo (pkg/registry/core/pod/storage/storage.go:180-187): the assigned devices leave `available`
@@ -372,16 +408,19 @@ __device__ __forceinline__ void commit_pod(const KsbNodeTable& T, int r, const P
       if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
 #pragma unroll
     for (int s = 0; s < KSB_MAX_RES; ++s)
-      if (take[s]) T.dev_avail[s * np + r] &= ~take[s];
+      if (take[s]) T.dev_avail[s * np + r] = __ldcg(T.dev_avail + s * np + r) & ~take[s];
   }
-  for (int i = lane; i < h->n_spread_inc; i += 32) T.spread[(size_t)pv.spread_inc[i] * np + r] += 1u;
+  for (int i = lane; i < h->n_spread_inc; i += 32) {
+    uint32_t* p = T.spread + (size_t)pv.spread_inc[i] * np + r;
+    *p = __ldcg(p) + 1u;
+  }
   for (int i = lane; i < h->n_commit; i += 32) {
     uint64_t c = pv.commits[2 * i];
     int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
     uint32_t off = (uint32_t)c;
     uint32_t d = T.topo[((uint32_t)(c >> 32) & 0xffu) * np + r];
-    if (d) T.tables[off + d] += delta;
-    if ((c >> 40) & 1ull) T.tables[off] += delta;  // slot 0: total matching pods anywhere
+    if (d) T.tables[off + d] = __ldcg(T.tables + off + d) + delta;
+    if ((c >> 40) & 1ull) T.tables[off] = __ldcg(T.tables + off) + delta;  // slot 0: total matching pods anywhere
   }
 }
 
@@ -389,19 +428,283 @@ __device__ __forceinline__ int32_t warp_max(int32_t v) { return __reduce_max_syn
 __device__ __forceinline__ int32_t warp_min(int32_t v) { return __reduce_min_sync(0xffffffffu, v); }
 __device__ __forceinline__ int32_t warp_sum(int32_t v) { return __reduce_add_sync(0xffffffffu, v); }
 
+// Mutable (and a few static) columns of one node row, kept in shared memory by phase 3 for every row
+// chosen earlier in the current group.
+//   q[0..3] alloc cpu/mem/alpha-gpu/ephemeral   q[4..7] requested cpu/mem/alpha-gpu/ephemeral
+//   q[8..9] nonzero cpu/mem   q[10..13] scalar alloc   q[14..17] scalar requested
+//   q[18..21] port_any   q[22..25] port_wild   q[26..29] port_exact   q[30] preferAvoid set
+struct RowCache {
+  int64_t q[31];
+  int32_t apods, npods;
+  uint32_t flags, zone;
+  uint32_t avail[KSB_MAX_RES];
+  int32_t row, pad;
+};
+
+// reason bits that depend on columns a bind changes; every other bit of a row is constant inside a group
+constexpr uint32_t kDynMask = 0x1ffu | (1u << RB_PORTS) | (0xfu << RB_EXT0) | (1u << RB_EXT_LIMITS);
+
+// The part of eval_node that can change while a group is committed, computed from the row cache.
+// Must stay in step with eval_node (the group-size tests compare the two paths bit for bit).
+__device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCache& c, const PodView& pv,
+                                            uint32_t static_reasons, uint32_t* reasons_out, int32_t* base_out,
+                                            uint32_t* picks) {
+  const KsbPodHeader* h = pv.h;
+  const uint32_t pf = h->flags;
+  uint32_t reasons = static_reasons;
+  if (c.npods + 1 > c.apods) reasons |= 1u << RB_PODS;
+  if (pf & PF_HAS_REQUEST) {
+    if (c.q[0] < h->req_cpu + c.q[4]) reasons |= 1u << RB_CPU;
+    if (c.q[1] < h->req_mem + c.q[5]) reasons |= 1u << RB_MEM;
+    if (c.q[2] < h->req_agpu + c.q[6]) reasons |= 1u << RB_AGPU;
+    if (c.q[3] < h->req_eph + c.q[7]) reasons |= 1u << RB_EPH;
+    const uint32_t sm = h->scalar_mask;
+#pragma unroll
+    for (int s = 0; s < KSB_MAX_SCALARS; ++s)
+      if ((sm >> s) & 1u)
+        if (c.q[10 + s] < h->scalar_req[s] + c.q[14 + s]) reasons |= 1u << (RB_SCALAR0 + s);
+  }
+  if (pf & PF_HAS_PORTS) {
+    uint64_t hit = 0;
+#pragma unroll
+    for (int w = 0; w < KSB_PORT_WORDS; ++w) {
+      hit |= (uint64_t)c.q[18 + w] & pv.ports[w];
+      hit |= (uint64_t)c.q[22 + w] & pv.ports[KSB_PORT_WORDS + w];
+      hit |= (uint64_t)c.q[26 + w] & pv.ports[2 * KSB_PORT_WORDS + w];
+    }
+    if (hit) reasons |= 1u << RB_PORTS;
+  }
+  if (reasons == 0 && h->n_ext) {
+    uint32_t local[KSB_MAX_EXT];
+    reasons |= select_devices(T, c.row, pv, c.flags, c.avail, picks ? picks : local);
+  }
+  const int64_t acpu = c.q[0], amem = c.q[1];
+  const int64_t cpu = h->nz_cpu + c.q[8];
+  const int64_t mem = h->nz_mem + c.q[9];
+  const int32_t lr = (int32_t)((unused_score(cpu, acpu) + unused_score(mem, amem)) / 2);
+  const double cf = acpu == 0 ? 1.0 : __ddiv_rn((double)cpu, (double)acpu);
+  const double mf = amem == 0 ? 1.0 : __ddiv_rn((double)mem, (double)amem);
+  int32_t bra = 0;
+  if (!(cf >= 1.0 || mf >= 1.0)) {
+    double diff = fabs(__dsub_rn(cf, mf));
+    bra = (int32_t)(__dmul_rn(__dsub_rn(1.0, diff), 10.0));
+  }
+  const int32_t av = ((uint64_t)c.q[30] & h->avoid_mask) ? 0 : 10;
+  *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
+  *reasons_out = reasons;
+}
+
+// One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads).
+__device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCache* c, int lane) {
+  const size_t np = T.n_pad;
+  const int64_t* p = nullptr;
+  switch (lane) {
+    case 0: p = T.alloc_cpu + r; break;
+    case 1: p = T.alloc_mem + r; break;
+    case 2: p = T.alloc_agpu + r; break;
+    case 3: p = T.alloc_eph + r; break;
+    case 4: p = T.req_cpu + r; break;
+    case 5: p = T.req_mem + r; break;
+    case 6: p = T.req_agpu + r; break;
+    case 7: p = T.req_eph + r; break;
+    case 8: p = T.nz_cpu + r; break;
+    case 9: p = T.nz_mem + r; break;
+    default: break;
+  }
+  if (lane >= 10 && lane < 14) p = T.alloc_scalar + (size_t)(lane - 10) * np + r;
+  if (lane >= 14 && lane < 18) p = T.req_scalar + (size_t)(lane - 14) * np + r;
+  if (lane >= 18 && lane < 22) p = reinterpret_cast<const int64_t*>(T.port_any + (size_t)(lane - 18) * np + r);
+  if (lane >= 22 && lane < 26) p = reinterpret_cast<const int64_t*>(T.port_wild + (size_t)(lane - 22) * np + r);
+  if (lane >= 26 && lane < 30) p = reinterpret_cast<const int64_t*>(T.port_exact + (size_t)(lane - 26) * np + r);
+  if (lane == 30) p = reinterpret_cast<const int64_t*>(T.avoid + r);
+  if (lane < 31) {
+    c->q[lane] = __ldcg(p);
+  } else {
+    c->apods = T.alloc_pods[r];
+    c->npods = __ldcg(T.num_pods + r);
+    c->flags = T.flags[r];
+    c->zone = T.zone[r];
+#pragma unroll
+    for (int s = 0; s < KSB_MAX_RES; ++s) c->avail[s] = __ldcg(T.dev_avail + (size_t)s * np + r);
+    c->row = r;
+  }
+}
+
+// One warp: the assume step (NodeInfo.AddPod, schedulercache/node_info.go:329-356) applied to the cache
+// entry and written through to the table; the class counters are bumped in global memory only (no pod
+// of the same group reads them).
+__device__ __forceinline__ void commit_cached(const KsbNodeTable& T, RowCache* c, const PodView& pv,
+                                              const uint32_t* picks, int lane) {
+  const KsbPodHeader* h = pv.h;
+  const size_t np = T.n_pad;
+  const int r = c->row;
+  int64_t add = 0;
+  int64_t* dst = nullptr;
+  switch (lane) {
+    case 4: add = h->add_cpu; dst = T.req_cpu + r; break;
+    case 5: add = h->add_mem; dst = T.req_mem + r; break;
+    case 6: add = h->add_agpu; dst = T.req_agpu + r; break;
+    case 7: add = h->add_eph; dst = T.req_eph + r; break;
+    case 8: add = h->nz_cpu; dst = T.nz_cpu + r; break;
+    case 9: add = h->nz_mem; dst = T.nz_mem + r; break;
+    default: break;
+  }
+  if (lane >= 14 && lane < 18) {
+    add = h->scalar_add[lane - 14];
+    dst = T.req_scalar + (size_t)(lane - 14) * np + r;
+  }
+  if (dst && add != 0) {
+    c->q[lane] += add;
+    *dst = c->q[lane];
+  }
+  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30) {
+    const int j = lane - 18;  // pool ports[12..23] = add_any[4], add_wild[4], add_exact[4]
+    uint64_t v = (uint64_t)c->q[lane] | pv.ports[3 * KSB_PORT_WORDS + j];
+    c->q[lane] = (int64_t)v;
+    uint64_t* pd = (j < 4 ? T.port_any : (j < 8 ? T.port_wild : T.port_exact)) + (size_t)(j & 3) * np + r;
+    *pd = v;
+  }
+  if (lane == 31) {
+    c->npods += 1;
+    T.num_pods[r] = c->npods;
+    if (h->n_ext) {
+      // bind echo (pkg/registry/core/pod/storage/storage.go:180-187): the assigned devices leave `available`
+      uint32_t take[KSB_MAX_RES];
+#pragma unroll
+      for (int s = 0; s < KSB_MAX_RES; ++s) take[s] = 0;
+      for (int i = 0; i < h->n_ext; ++i)
+        if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
+#pragma unroll
+      for (int s = 0; s < KSB_MAX_RES; ++s)
+        if (take[s]) {
+          c->avail[s] &= ~take[s];
+          T.dev_avail[(size_t)s * np + r] = c->avail[s];
+        }
+    }
+  }
+}
+
+// The class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
+// of the same group reads them, so they live in global memory only. Split in two so the loads can be in
+// flight together with the row-cache fill.
+struct CounterLoads {
+  uint32_t spread_v;
+  int32_t tab_v, tot_v;
+  uint32_t tab_d;
+};
+__device__ __forceinline__ bool counters_fast(const KsbPodHeader* h) { return h->n_spread_inc <= 32 && h->n_commit <= 32; }
+__device__ __forceinline__ CounterLoads counters_load(const KsbNodeTable& T, int r, const PodView& pv, int lane) {
+  const KsbPodHeader* h = pv.h;
+  const size_t np = T.n_pad;
+  CounterLoads L;
+  L.spread_v = 0;
+  L.tab_v = 0;
+  L.tot_v = 0;
+  L.tab_d = 0;
+  if (lane < h->n_spread_inc) L.spread_v = __ldcg(T.spread + (size_t)pv.spread_inc[lane] * np + r);
+  if (lane < h->n_commit) {
+    const uint64_t cm = pv.commits[2 * lane];
+    const uint32_t off = (uint32_t)cm;
+    L.tab_d = T.topo[((uint32_t)(cm >> 32) & 0xffu) * np + r];
+    if (L.tab_d) L.tab_v = __ldcg(T.tables + off + L.tab_d);
+    if ((cm >> 40) & 1ull) L.tot_v = __ldcg(T.tables + off);
+  }
+  return L;
+}
+__device__ __forceinline__ void counters_store(const KsbNodeTable& T, int r, const PodView& pv, const CounterLoads& L,
+                                               int lane) {
+  const KsbPodHeader* h = pv.h;
+  const size_t np = T.n_pad;
+  if (lane < h->n_spread_inc) T.spread[(size_t)pv.spread_inc[lane] * np + r] = L.spread_v + 1u;
+  if (lane < h->n_commit) {
+    const uint64_t cm = pv.commits[2 * lane];
+    const int32_t delta = (int32_t)(int64_t)pv.commits[2 * lane + 1];
+    const uint32_t off = (uint32_t)cm;
+    if (L.tab_d) T.tables[off + L.tab_d] = L.tab_v + delta;
+    if ((cm >> 40) & 1ull) T.tables[off] = L.tot_v + delta;  // slot 0: matching pods anywhere
+  }
+}
+__device__ __forceinline__ void counters_slow(const KsbNodeTable& T, int r, const PodView& pv, int lane) {
+  const KsbPodHeader* h = pv.h;
+  const size_t np = T.n_pad;
+  for (int i = lane; i < h->n_spread_inc; i += 32) {
+    uint32_t* p = T.spread + (size_t)pv.spread_inc[i] * np + r;
+    *p = __ldcg(p) + 1u;
+  }
+  for (int i = lane; i < h->n_commit; i += 32) {
+    uint64_t cm = pv.commits[2 * i];
+    int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
+    uint32_t off = (uint32_t)cm;
+    uint32_t d = T.topo[((uint32_t)(cm >> 32) & 0xffu) * np + r];
+    if (d) T.tables[off + d] = __ldcg(T.tables + off + d) + delta;
+    if ((cm >> 40) & 1ull) T.tables[off] = __ldcg(T.tables + off) + delta;
+  }
+}
+
+// dynamic shared memory carve-up
+struct Smem {
+  KsbPodHeader* hdr;   // [kMaxG]
+  uint64_t* pool;      // [kGroupPoolWords]
+  int32_t* pool_off;   // [kMaxG] offset of pod g's pool inside `pool`
+  int32_t* zone;       // [kMaxG][zone_stride] phase 1: block-local sums; phase 2/3: global sums
+  int32_t* part;       // [kMaxG][kWarps][8] per-warp partials of the Reduce inputs
+  KsbNorms* norm;      // [kMaxG]
+  int32_t* max_zone;   // [kMaxG]
+  int32_t* wstat;      // [kMaxG][kWarps][2] per-warp (max, count) of one segment
+  int32_t* seg_max;    // [kSegCache] block 0: [pod][segment]
+  int32_t* seg_cnt;    // [kSegCache]
+  RowCache* rows;      // [kMaxG] block 0: rows changed in this group
+  int32_t* fe_hist;    // [KSB_REASON_BITS] block 0: FitError histogram correction for changed rows
+};
+
+__device__ __host__ __forceinline__ size_t smem_layout(size_t* offs, int zone_stride) {
+  size_t off = 0;
+  int i = 0;
+  auto take = [&](size_t bytes) {
+    offs[i++] = off;
+    off += (bytes + 15) & ~(size_t)15;
+  };
+  take(sizeof(KsbPodHeader) * kMaxG);
+  take((size_t)kGroupPoolWords * 8);
+  take(kMaxG * 4);
+  take((size_t)kMaxG * zone_stride * 4);
+  take((size_t)kMaxG * kWarps * 8 * 4);
+  take(sizeof(KsbNorms) * kMaxG);
+  take(kMaxG * 4);
+  take((size_t)kMaxG * kWarps * 2 * 4);
+  take((size_t)kSegCache * 4);
+  take((size_t)kSegCache * 4);
+  take(sizeof(RowCache) * kMaxG);
+  take((size_t)kMaxG * KSB_REASON_BITS * 4);
+  return off;
+}
+
+__device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
+  size_t o[12];
+  smem_layout(o, zone_stride);
+  Smem s;
+  s.hdr = (KsbPodHeader*)(base + o[0]);
+  s.pool = (uint64_t*)(base + o[1]);
+  s.pool_off = (int32_t*)(base + o[2]);
+  s.zone = (int32_t*)(base + o[3]);
+  s.part = (int32_t*)(base + o[4]);
+  s.norm = (KsbNorms*)(base + o[5]);
+  s.max_zone = (int32_t*)(base + o[6]);
+  s.wstat = (int32_t*)(base + o[7]);
+  s.seg_max = (int32_t*)(base + o[8]);
+  s.seg_cnt = (int32_t*)(base + o[9]);
+  s.rows = (RowCache*)(base + o[10]);
+  s.fe_hist = (int32_t*)(base + o[11]);
+  return s;
+}
+
 }  // namespace
 
-// Shared-memory layout (dynamic): pod header | pool words | zone sums.
 __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  KsbPodHeader* sh = reinterpret_cast<KsbPodHeader*>(smem_raw);
-  uint64_t* spool = reinterpret_cast<uint64_t*>(smem_raw + sizeof(KsbPodHeader));
-  int32_t* szone = reinterpret_cast<int32_t*>(spool + kMaxPoolWords);
-  __shared__ int32_t s_red[8];       // fit, max_na, max_tt, max_sc, ipa_max, ipa_min, have_zones, one_row
-  __shared__ int32_t s_bmax, s_bcnt;
-  __shared__ int32_t s_sel[4];       // target block, remaining index, chosen local row, scratch
-  __shared__ uint32_t s_picks[KSB_MAX_EXT];
-  __shared__ int32_t s_warp[kThreads / 32];
+  const Smem S = carve(smem_raw, A.zone_stride);
+  __shared__ int32_t s_gc;            // pods in the current group
+  __shared__ int32_t s_consumed;      // pods of the group that were committed
 
   const KsbNodeTable& T = A.table;
   const int tid = threadIdx.x;
@@ -409,297 +712,510 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const int warp = tid >> 5;
   const int nblk = gridDim.x;
   const int b = blockIdx.x;
-  // contiguous row range of this block, in ascending name order
-  const int rows_per_block = (T.n + nblk - 1) / nblk;
-  const int row0 = b * rows_per_block;
-  const int row1 = min(T.n, row0 + rows_per_block);
   const int nz = T.n_zones;
+  const int zs = A.zone_stride;
+  const int nseg = A.nseg;
+  const int G = A.group_size;
+  const size_t np = T.n_pad;
   uint32_t epoch = 0;
-  uint64_t last_index = *A.last_node_index;
+  uint64_t last_index = *A.last_node_index;  // used by warp 0 of block 0 only
+  int p0 = 0;
+  int gi = 0;
 
-  for (int p = 0; p < A.n_pods; ++p) {
-    // ---- stage the pod requirement block
+  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long tmark = clock64();
+#define KSB_TICK(i)                      \
+  do {                                   \
+    long long now_ = clock64();          \
+    tk[i] += now_ - tmark;               \
+    tmark = now_;                        \
+  } while (0)
+  while (p0 < A.n_pods) {
+    const int slot = gi & 1;
+    // ---- stage the group's requirement blocks; every block derives the same group extent
     {
-      const uint4* src = reinterpret_cast<const uint4*>(A.headers + p);
-      uint4* dst = reinterpret_cast<uint4*>(sh);
-      for (int i = tid; i < (int)(sizeof(KsbPodHeader) / 16); i += kThreads) dst[i] = src[i];
+      const int avail = min(G, A.n_pods - p0);
+      const uint4* src = reinterpret_cast<const uint4*>(A.headers + p0);
+      uint4* dst = reinterpret_cast<uint4*>(S.hdr);
+      const int n16 = avail * (int)(sizeof(KsbPodHeader) / 16);
+      for (int i = tid; i < n16; i += kThreads) dst[i] = src[i];
       __syncthreads();
-      const int pw = pool_words(sh, T.W);
-      const uint64_t* psrc = A.pool + sh->pool_off;
-      for (int i = tid; i < pw; i += kThreads) spool[i] = psrc[i];
-      for (int i = tid; i < nz; i += kThreads) szone[i] = 0;
-      if (tid < 8) s_red[tid] = (tid == 5) ? 0 : ((tid == 7) ? -1 : 0);
+      if (warp == 0) {
+        bool ok = false;
+        if (lane < avail) {
+          const KsbPodHeader* h = S.hdr + lane;
+          int rel_end = (int)(h->pool_off - S.hdr[0].pool_off) + pool_words(h, T.W);
+          ok = rel_end <= kGroupPoolWords && (lane == 0 || __ldg(A.dep + p0 + lane) < p0);
+          S.pool_off[lane] = (int32_t)(h->pool_off - S.hdr[0].pool_off);
+        }
+        uint32_t bal = __ballot_sync(0xffffffffu, ok);
+        int gc = __ffs(~bal) - 1;  // leading run of admissible pods
+        if (gc < 0) gc = 32;
+        if (lane == 0) s_gc = max(1, min(gc, avail));
+      }
+      __syncthreads();
+      const int gc = s_gc;
+      const KsbPodHeader* hl = S.hdr + (gc - 1);
+      const int words = S.pool_off[gc - 1] + pool_words(hl, T.W);
+      const uint64_t* psrc = A.pool + S.hdr[0].pool_off;
+      for (int i = tid; i < words; i += kThreads) S.pool[i] = psrc[i];
+      for (int i = tid; i < gc * zs; i += kThreads) S.zone[i] = 0;
+      for (int i = tid; i < gc * kWarps * 8; i += kThreads) {
+        int f = i & 7;
+        S.part[i] = (f == 7) ? -1 : 0;  // fit, max_na, max_tt, max_sc, ipa_max, ipa_min, have_zones, one_row
+      }
       __syncthreads();
     }
-    const PodView pv = make_view(sh, spool, T.W);
-    KsbNorms* norms = A.norms + (p & 1);
-    int32_t* zsum = A.zone_sum + (size_t)(p & 1) * A.zone_stride;
-    const bool whole_pod_error = (sh->flags & PF_SCHED_ERROR) != 0;
+    const int Gc = s_gc;
+    KSB_TICK(0);
+    KsbNorms* norms = A.norms + (size_t)slot * kMaxG;
+    int32_t* zsum = A.zone_sum + (size_t)slot * kMaxG * zs;
 
-    // ---- phase 1: predicates + Map on every node of this block
-    if (!whole_pod_error) {
-      int32_t fit = 0, mna = 0, mtt = 0, msc = 0, imax = 0, imin = 0, hz = 0, one = -1;
-      for (int r = row0 + tid; r < row1; r += kThreads) {
-        EvalOut o;
-        eval_node(T, r, pv, o, nullptr);
-        int4 raw;
-        if (o.reasons == 0) {
-          fit += 1;
-          mna = max(mna, o.na);
-          mtt = max(mtt, o.tt);
-          msc = max(msc, (int32_t)o.sc);
-          imax = max(imax, o.ipa);
-          imin = min(imin, o.ipa);
-          one = max(one, T.row_base + r);
-          if (o.zone) {
-            hz = 1;
-            if (o.sc) atomicAdd(&szone[o.zone], (int32_t)o.sc);
-          }
-          raw = make_int4(o.base, o.na, (o.tt << 24) | (int32_t)(o.sc & 0xffffffu), o.ipa);
-        } else {
-          raw = make_int4(INT32_MIN, 0, 0, 0);
-        }
-        A.raw[r] = raw;
-        A.reasons[r] = o.reasons;
-      }
-      fit = warp_sum(fit);
-      mna = warp_max(mna);
-      mtt = warp_max(mtt);
-      msc = warp_max(msc);
-      imax = warp_max(imax);
-      imin = warp_min(imin);
-      hz = warp_max(hz);
-      one = warp_max(one);
-      if (lane == 0) {
-        if (fit) atomicAdd(&s_red[0], fit);
-        if (mna) atomicMax(&s_red[1], mna);
-        if (mtt) atomicMax(&s_red[2], mtt);
-        if (msc) atomicMax(&s_red[3], msc);
-        if (imax) atomicMax(&s_red[4], imax);
-        if (imin) atomicMin(&s_red[5], imin);
-        if (hz) atomicMax(&s_red[6], hz);
-        if (one >= 0) atomicMax(&s_red[7], one);
-      }
-      __syncthreads();
-      if (tid == 0) {
-        if (s_red[0]) atomicAdd(&norms->fit_count, s_red[0]);
-        if (s_red[1]) atomicMax(&norms->max_na, s_red[1]);
-        if (s_red[2]) atomicMax(&norms->max_tt, s_red[2]);
-        if (s_red[3]) atomicMax(&norms->max_sc, s_red[3]);
-        if (s_red[4]) atomicMax(&norms->ipa_max, s_red[4]);
-        if (s_red[5]) atomicMin(&norms->ipa_min, s_red[5]);
-        if (s_red[6]) atomicMax(&norms->have_zones, 1);
-        if (s_red[7] >= 0) atomicMax(&norms->one_row, s_red[7]);
-      }
-      for (int z = tid; z < nz; z += kThreads)
-        if (szone[z]) atomicAdd(&zsum[z], szone[z]);
+    // work split for phases 1 and 2: a block owns segments (all pods) when there are at least as many
+    // segments as blocks; otherwise several blocks share a segment and split the group's pods
+    int seg_first = b, seg_step = nblk, pod_first = 0, pod_step = 1;
+    bool active = true;
+    if (nseg < nblk) {
+      const int parts = min(Gc, nblk / nseg);
+      seg_first = b % nseg;
+      seg_step = nseg;  // exactly one segment
+      pod_first = b / nseg;
+      pod_step = parts;
+      active = pod_first < parts;
     }
-    grid_barrier(A, epoch);
 
-    // ---- phase 2: Reduce + weighted sum, per-block (max, tie count)
-    KsbNorms nm;
-    {
-      const int32_t* np32 = reinterpret_cast<const int32_t*>(norms);
-      nm.fit_count = __ldcg(np32 + 0);
-      nm.max_na = __ldcg(np32 + 1);
-      nm.max_tt = __ldcg(np32 + 2);
-      nm.max_sc = __ldcg(np32 + 3);
-      nm.ipa_max = __ldcg(np32 + 4);
-      nm.ipa_min = __ldcg(np32 + 5);
-      nm.have_zones = __ldcg(np32 + 6);
-      nm.one_row = __ldcg(np32 + 7);
-    }
-    const bool prio_needed = !whole_pod_error && nm.fit_count >= 2 && !(sh->flags & PF_PRIO_ERROR);
-    if (prio_needed) {
-      int32_t mz = 0;
-      for (int z = tid; z < nz; z += kThreads) {
-        int32_t v = __ldcg(zsum + z);
-        szone[z] = v;
-        mz = max(mz, v);
-      }
-      mz = warp_max(mz);
-      if (lane == 0) s_warp[warp] = mz;
-      __syncthreads();
-      int32_t max_zone = 0;
-#pragma unroll
-      for (int w = 0; w < kThreads / 32; ++w) max_zone = max(max_zone, s_warp[w]);
-      int32_t bmax = INT32_MIN, bcnt = 0;
-      for (int r = row0 + tid; r < row1; r += kThreads) {
-        int4 raw = A.raw[r];
-        int32_t s = INT32_MIN;
-        if (raw.x != INT32_MIN) {
-          s = final_score(T, sh, nm, szone, max_zone, raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
-                          (uint32_t)raw.z & 0xffffffu, raw.w, T.zone[r]);
-          if (s > bmax) {
-            bmax = s;
-            bcnt = 1;
-          } else if (s == bmax) {
-            bcnt++;
-          }
-        }
-        A.score[r] = s;
-      }
-      int32_t wm = warp_max(bmax);
-      int32_t wc = warp_sum(bmax == wm && bmax != INT32_MIN ? bcnt : 0);
-      __syncthreads();
-      if (lane == 0) {
-        s_warp[warp] = wm;
-      }
-      __syncthreads();
-      int32_t blockmax = INT32_MIN;
-#pragma unroll
-      for (int w = 0; w < kThreads / 32; ++w) blockmax = max(blockmax, s_warp[w]);
-      if (tid == 0) s_bcnt = 0;
-      __syncthreads();
-      if (lane == 0 && wm == blockmax && wm != INT32_MIN) atomicAdd(&s_bcnt, wc);
-      __syncthreads();
-      if (tid == 0) {
-        A.blk_max[b] = blockmax;
-        A.blk_cnt[b] = s_bcnt;
-      }
-    }
-    grid_barrier(A, epoch);
-
-    // ---- phase 3: selectHost + assume, block 0 only (other blocks go straight to the barrier)
-    if (b == 0) {
-      KsbResult res;
-      res.status = 0;
-      res.row = -1;
-      res.num_filtered = nm.fit_count;
-      res.fiterr_slot = -1;
-      res.score = 0;
-#pragma unroll
-      for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = 0;
-      int chosen = -1;  // global row
-      if (whole_pod_error || (nm.fit_count >= 2 && (sh->flags & PF_PRIO_ERROR))) {
-        res.status = 3;
-      } else if (nm.fit_count == 0) {
-        res.status = 2;
-        // FitError: histogram of failure reasons over all nodes (generic_scheduler.go:70-88)
-        __shared__ int32_t s_hist[KSB_REASON_BITS];
-        __shared__ int32_t s_slot;
-        if (tid < KSB_REASON_BITS) s_hist[tid] = 0;
-        if (tid == 0) s_slot = atomicAdd(A.fiterr_count, 1);
-        __syncthreads();
-        if (s_slot < KSB_MAX_FITERR) {
-          for (int r = tid; r < T.n; r += kThreads) {
-            uint32_t m = __ldcg(A.reasons + r);
-            while (m) {
-              int bit = __ffs(m) - 1;
-              m &= m - 1;
-              atomicAdd(&s_hist[bit], 1);
-            }
-          }
-          __syncthreads();
-          if (tid < KSB_REASON_BITS) A.fiterr_hist[(size_t)s_slot * KSB_REASON_BITS + tid] = s_hist[tid];
-          res.fiterr_slot = s_slot;
-        }
-      } else if (nm.fit_count == 1) {
-        chosen = nm.one_row;  // generic_scheduler.go:144-146: no selectHost, counter untouched
-      } else {
-        // global max and tie count over blocks; ties are ordered by descending row
-        int32_t gmax = INT32_MIN;
-        for (int i = tid; i < nblk; i += kThreads) gmax = max(gmax, __ldcg(A.blk_max + i));
-        gmax = warp_max(gmax);
-        if (lane == 0) s_warp[warp] = gmax;
-        __syncthreads();
-        gmax = INT32_MIN;
-#pragma unroll
-        for (int w = 0; w < kThreads / 32; ++w) gmax = max(gmax, s_warp[w]);
-        __syncthreads();
-        if (tid == 0) {
-          int64_t k = 0;
-          for (int i = 0; i < nblk; ++i)
-            if (__ldcg(A.blk_max + i) == gmax) k += __ldcg(A.blk_cnt + i);
-          uint64_t ix = k > 0 ? last_index % (uint64_t)k : 0;
-          int tb = -1;
-          for (int i = nblk - 1; i >= 0; --i) {
-            if (__ldcg(A.blk_max + i) != gmax) continue;
-            uint64_t c = (uint64_t)__ldcg(A.blk_cnt + i);
-            if (ix < c) {
-              tb = i;
-              break;
-            }
-            ix -= c;
-          }
-          s_sel[0] = tb;
-          s_sel[1] = (int32_t)ix;
-          s_sel[2] = -1;
-        }
-        __syncthreads();
-        const int tb = s_sel[0];
-        int remaining = s_sel[1];
-        // rank-select inside the target block, scanning rows downward in chunks of kThreads
-        const int trow0 = tb * rows_per_block;
-        const int trow1 = min(T.n, trow0 + rows_per_block);
-        for (int top = trow1; top > trow0 && s_sel[2] < 0; top -= kThreads) {
-          int r = top - 1 - tid;  // thread 0 looks at the highest row
-          bool tie = r >= trow0 && __ldcg(A.score + r) == gmax;
-          uint32_t bal = __ballot_sync(0xffffffffu, tie);
-          if (lane == 0) s_warp[warp] = __popc(bal);
-          __syncthreads();
-          int before = 0;
-          for (int w = 0; w < warp; ++w) before += s_warp[w];
-          int total = 0;
-#pragma unroll
-          for (int w = 0; w < kThreads / 32; ++w) total += s_warp[w];
-          int my = before + __popc(bal & ((1u << lane) - 1u));
-          if (tie && my == remaining) s_sel[2] = r;
-          __syncthreads();
-          remaining -= total;
-          if (tid == 0) s_sel[1] = remaining;
-          __syncthreads();
-        }
-        if (s_sel[2] >= 0) {
-          chosen = T.row_base + s_sel[2];
-          res.score = gmax;
-        } else {
-          res.status = 3;  // only reachable after a barrier timeout
-        }
-        last_index += 1;
-      }
-      if (chosen >= 0) {
-        const int r = chosen - T.row_base;
-        if (warp == 0) {
-          if (lane == 0 && sh->n_ext) {
+    // ---- phase 1: predicates + Map
+    if (active) {
+      for (int seg = seg_first; seg < nseg; seg += seg_step) {
+        const int r = seg * kSeg + tid;
+        const bool live = r < T.n;
+        for (int g = pod_first; g < Gc; g += pod_step) {
+          const KsbPodHeader* h = S.hdr + g;
+          int32_t fit = 0, mna = 0, mtt = 0, msc = 0, imax = 0, imin = 0, hz = 0, one = -1;
+          if (live && !(h->flags & PF_SCHED_ERROR)) {
+            const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
             EvalOut o;
-            uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
-            eval_node(T, r, pv, o, picks);
-#pragma unroll
-            for (int i = 0; i < KSB_MAX_EXT; ++i) s_picks[i] = picks[i];
+            eval_node<false>(T, r, pv, o, nullptr);
+            int4 raw;
+            if (o.reasons == 0) {
+              fit = 1;
+              mna = o.na;
+              mtt = o.tt;
+              msc = (int32_t)o.sc;
+              imax = max(0, o.ipa);
+              imin = min(0, o.ipa);
+              one = T.row_base + r;
+              if (o.zone) {
+                hz = 1;
+                if (o.sc) atomicAdd(&S.zone[g * zs + o.zone], (int32_t)o.sc);
+              }
+              raw = make_int4(o.base, o.na, (o.tt << 24) | (int32_t)(o.sc & 0xffffffu), o.ipa);
+            } else {
+              raw = make_int4(INT32_MIN, 0, 0, 0);
+            }
+            A.raw[(size_t)g * np + r] = raw;
+            A.reasons[(size_t)g * np + r] = o.reasons;
           }
-          __syncwarp();
-          if (A.commit) commit_pod(T, r, pv, s_picks);
-        }
-        res.row = chosen;
-        if (sh->n_ext) {
-          __syncthreads();
-#pragma unroll
-          for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = s_picks[i];
+          fit = warp_sum(fit);
+          mna = warp_max(mna);
+          mtt = warp_max(mtt);
+          msc = warp_max(msc);
+          imax = warp_max(imax);
+          imin = warp_min(imin);
+          hz = warp_max(hz);
+          one = warp_max(one);
+          if (lane == 0) {  // this warp's own slot: no atomics needed
+            int32_t* pp = S.part + (g * kWarps + warp) * 8;
+            pp[0] += fit;
+            pp[1] = max(pp[1], mna);
+            pp[2] = max(pp[2], mtt);
+            pp[3] = max(pp[3], msc);
+            pp[4] = max(pp[4], imax);
+            pp[5] = min(pp[5], imin);
+            pp[6] = max(pp[6], hz);
+            pp[7] = max(pp[7], one);
+          }
         }
       }
-      if (tid == 0) {
-        A.results[p] = res;
-        // reset the other scratch slot for pod p+1
-        KsbNorms* nn = A.norms + ((p + 1) & 1);
-        nn->fit_count = 0;
-        nn->max_na = 0;
-        nn->max_tt = 0;
-        nn->max_sc = 0;
-        nn->ipa_max = 0;
-        nn->ipa_min = 0;
-        nn->have_zones = 0;
-        nn->one_row = -1;
-      }
-      int32_t* zn = A.zone_sum + (size_t)((p + 1) & 1) * A.zone_stride;
-      for (int z = tid; z < nz; z += kThreads) zn[z] = 0;
-    } else {
-      // every block tracks the round-robin counter so it never has to be re-read
-      if (!whole_pod_error && nm.fit_count >= 2 && !(sh->flags & PF_PRIO_ERROR)) last_index += 1;
     }
+    __syncthreads();
+    if (active) {
+      for (int i = tid; i < Gc * 8; i += kThreads) {
+        const int g = i >> 3, f = i & 7;
+        int32_t v = (f == 7) ? -1 : 0;
+        for (int w = 0; w < kWarps; ++w) {
+          int32_t x = S.part[(g * kWarps + w) * 8 + f];
+          if (f == 0) v += x;
+          else if (f == 5) v = min(v, x);
+          else v = max(v, x);
+        }
+        int32_t* dst = reinterpret_cast<int32_t*>(norms + g) + f;
+        if (f == 0) { if (v) atomicAdd(dst, v); }
+        else if (f == 5) { if (v) atomicMin(dst, v); }
+        else if (f == 7) { if (v >= 0) atomicMax(dst, v); }
+        else { if (v) atomicMax(dst, v); }
+      }
+      for (int i = tid; i < Gc * zs; i += kThreads) {
+        int z = i % zs;
+        if (z < nz && S.zone[i]) atomicAdd(&zsum[i], S.zone[i]);
+      }
+    }
+    KSB_TICK(1);
     grid_barrier(A, epoch);
+    KSB_TICK(2);
+
+    // ---- phase 2: Reduce + weighted sum; per-segment (max, tie count) of every pod
+    for (int i = tid; i < Gc * 8; i += kThreads)
+      reinterpret_cast<int32_t*>(S.norm)[i] = __ldcg(reinterpret_cast<const int32_t*>(norms) + i);
+    for (int i = tid; i < Gc * zs; i += kThreads) S.zone[i] = (i % zs) < nz ? __ldcg(zsum + i) : 0;
+    __syncthreads();
+    if (tid < Gc) {
+      int32_t mz = 0;
+      for (int z = 0; z < nz; ++z) mz = max(mz, S.zone[tid * zs + z]);
+      S.max_zone[tid] = mz;
+    }
+    __syncthreads();
+    if (active) {
+      for (int seg = seg_first; seg < nseg; seg += seg_step) {
+        const int r = seg * kSeg + tid;
+        const bool live = r < T.n;
+        const uint32_t zone = live ? T.zone[r] : 0u;
+        for (int g = pod_first; g < Gc; g += pod_step) {
+          const KsbPodHeader* h = S.hdr + g;
+          const KsbNorms nm = S.norm[g];
+          const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && nm.fit_count >= 2;
+          if (nm.fit_count == 0 && !(h->flags & PF_SCHED_ERROR)) {
+            // no node fits: histogram of failure reasons for FitError.Error() (generic_scheduler.go:70-88),
+            // one ballot per reason bit present in the warp; lane b owns bit b
+            const uint32_t m = live ? A.reasons[(size_t)g * np + r] : 0u;
+            uint32_t un = __reduce_or_sync(0xffffffffu, m);
+            int32_t acc = 0;
+            while (un) {
+              const int bit = __ffs(un) - 1;
+              un &= un - 1;
+              const int c = __popc(__ballot_sync(0xffffffffu, (m >> bit) & 1u));
+              if (lane == bit) acc = c;
+            }
+            if (acc) atomicAdd(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane, acc);
+          }
+          if (!prio) continue;  // uniform per (block, g)
+          int32_t s = INT32_MIN;
+          if (live) {
+            int4 raw = A.raw[(size_t)g * np + r];
+            if (raw.x != INT32_MIN)
+              s = final_score(T, nm, S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
+                              (uint32_t)raw.z & 0xffffffu, raw.w, zone);
+            A.score[(size_t)g * np + r] = s;
+          }
+          int32_t wm = warp_max(s);
+          int32_t wc = warp_sum((s == wm && s != INT32_MIN) ? 1 : 0);
+          if (lane == 0) {
+            S.wstat[(g * kWarps + warp) * 2] = wm;
+            S.wstat[(g * kWarps + warp) * 2 + 1] = wc;
+          }
+        }
+        __syncthreads();
+        if (tid < Gc && tid >= pod_first && (tid - pod_first) % pod_step == 0) {
+          const int g = tid;
+          const KsbPodHeader* h = S.hdr + g;
+          const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[g].fit_count >= 2;
+          if (prio) {
+            int32_t m = INT32_MIN, c = 0;
+            for (int w = 0; w < kWarps; ++w) {
+              int32_t wm = S.wstat[(g * kWarps + w) * 2], wc = S.wstat[(g * kWarps + w) * 2 + 1];
+              if (wm > m) {
+                m = wm;
+                c = wc;
+              } else if (wm == m) {
+                c += wc;
+              }
+            }
+            if (m == INT32_MIN) c = 0;
+            A.seg_max[(size_t)g * nseg + seg] = m;
+            A.seg_cnt[(size_t)g * nseg + seg] = c;
+          }
+        }
+        __syncthreads();
+      }
+    }
+    KSB_TICK(3);
+    grid_barrier(A, epoch);
+    KSB_TICK(4);
+
+    // ---- phase 3: block 0 commits the group's pods in order
+    if (b == 0) {
+      // prefetch the segment statistics of every pod that will be ranked by score
+      for (int g = 0; g < Gc; ++g) {
+        const KsbPodHeader* h = S.hdr + g;
+        const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[g].fit_count >= 2;
+        if (!prio) continue;
+        for (int i = tid; i < nseg; i += kThreads) {
+          S.seg_max[g * nseg + i] = __ldcg(A.seg_max + (size_t)g * nseg + i);
+          S.seg_cnt[g * nseg + i] = __ldcg(A.seg_cnt + (size_t)g * nseg + i);
+        }
+      }
+      __syncthreads();
+      long long t3[6] = {0, 0, 0, 0, 0, 0};
+      long long m3 = clock64();
+#define KSB_T3(i)                      \
+  do {                                 \
+    long long now_ = clock64();        \
+    t3[i] += now_ - m3;                \
+    m3 = now_;                         \
+  } while (0)
+      KSB_T3(0);  // prefetch + sync
+      if (warp == 0) {
+        int ncr = 0;       // rows in the cache (uniform across the warp)
+        int consumed = 0;
+        for (int g = 0; g < Gc; ++g) {
+          const KsbPodHeader* h = S.hdr + g;
+          const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+          const KsbNorms nm = S.norm[g];
+          const bool sched_err = (h->flags & PF_SCHED_ERROR) != 0;
+          const bool prio = !sched_err && !(h->flags & PF_PRIO_ERROR) && nm.fit_count >= 2;
+          KsbResult res;
+          res.status = 0;
+          res.row = -1;
+          res.num_filtered = nm.fit_count;
+          res.fiterr_slot = -1;
+          res.score = 0;
+#pragma unroll
+          for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = 0;
+          int chosen = -1;  // local row
+          if (sched_err) {
+            res.status = 3;
+          } else {
+            // (1) this pod on the rows changed earlier in the group, from the row cache
+            uint32_t old_reasons = 0, new_reasons = 0;
+            int32_t cnew = INT32_MIN, cold = INT32_MIN;
+            int crow = -1;
+            bool flip = false;
+            if (lane < ncr) {
+              const RowCache& c = S.rows[lane];
+              crow = c.row;
+              const int4 raw0 = __ldcg(A.raw + (size_t)g * np + crow);
+              old_reasons = __ldcg(A.reasons + (size_t)g * np + crow);
+              if (prio) cold = __ldcg(A.score + (size_t)g * np + crow);
+              int32_t base;
+              eval_cached(T, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr);
+              const bool was_fit = raw0.x != INT32_MIN;
+              flip = was_fit && new_reasons != 0;  // a fit row turned unfit: the Reduce inputs may have moved
+              if (prio && was_fit && new_reasons == 0)
+                cnew = final_score(T, nm, S.zone + g * zs, S.max_zone[g], base, raw0.y, (int32_t)((uint32_t)raw0.z >> 24),
+                                   (uint32_t)raw0.z & 0xffffffu, raw0.w, c.zone);
+              else
+                cold = INT32_MIN;
+              if (!was_fit) cold = INT32_MIN;
+            }
+            if (__any_sync(0xffffffffu, flip)) break;  // speculation dropped: this pod opens the next group
+            KSB_T3(1);  // changed rows
+
+            if (nm.fit_count >= 2 && (h->flags & PF_PRIO_ERROR)) {
+              res.status = 3;
+            } else if (nm.fit_count == 0) {
+              // FitError (generic_scheduler.go:133-139): histogram built after the loop by all warps; here only
+              // the correction for rows whose reasons changed since the group started
+              res.status = 2;
+              int slotv = 0;
+              if (lane == 0) slotv = atomicAdd(A.fiterr_count, 1);
+              slotv = __shfl_sync(0xffffffffu, slotv, 0);
+              if (slotv < KSB_MAX_FITERR) {
+                S.fe_hist[lane] = 0;
+                __syncwarp();
+                if (lane < ncr) {  // rows whose reasons changed since the group started
+                  uint32_t m = old_reasons;
+                  while (m) {
+                    int bit = __ffs(m) - 1;
+                    m &= m - 1;
+                    atomicAdd(&S.fe_hist[bit], -1);
+                  }
+                  m = new_reasons;
+                  while (m) {
+                    int bit = __ffs(m) - 1;
+                    m &= m - 1;
+                    atomicAdd(&S.fe_hist[bit], 1);
+                  }
+                }
+                __syncwarp();
+                A.fiterr_hist[(size_t)slotv * KSB_REASON_BITS + lane] =
+                    __ldcg(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
+                res.fiterr_slot = slotv;
+              }
+              __syncwarp();
+            } else if (nm.fit_count == 1) {
+              chosen = nm.one_row - T.row_base;  // generic_scheduler.go:144-146: no selectHost, counter untouched
+            } else {
+              // (2) selectHost over group-start segment statistics patched with the changed rows
+              int32_t* smax = S.seg_max + g * nseg;
+              int32_t* scnt = S.seg_cnt + g * nseg;
+              int32_t m = cnew;
+              for (int i = lane; i < nseg; i += 32) m = max(m, smax[i]);
+              const int32_t gmax = warp_max(m);
+              for (int i = lane; i < nseg; i += 32) scnt[i] = (smax[i] == gmax) ? scnt[i] : 0;
+              __syncwarp();
+              if (lane < ncr) {
+                const int sg = crow / kSeg;
+                if (cold == gmax) atomicAdd(&scnt[sg], -1);
+                if (cnew == gmax) atomicAdd(&scnt[sg], 1);
+              }
+              __syncwarp();
+              int32_t c = 0;
+              for (int i = lane; i < nseg; i += 32) c += scnt[i];
+              const int32_t k = warp_sum(c);
+              if (k <= 0) break;  // every holder of the group-start maximum changed and fell below it
+              int rem = (int)(last_index % (uint64_t)k);
+              int found = -1;
+              for (int hi = nseg; hi > 0 && found < 0; hi -= 32) {
+                const int sg = hi - 1 - lane;  // lane 0 = highest segment
+                const int cnt = sg >= 0 ? scnt[sg] : 0;
+                int incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                  int t = __shfl_up_sync(0xffffffffu, incl, d);
+                  if (lane >= d) incl += t;
+                }
+                const int total = __shfl_sync(0xffffffffu, incl, 31);
+                const bool here = rem >= incl - cnt && rem < incl;
+                const uint32_t bal = __ballot_sync(0xffffffffu, here);
+                if (bal) {
+                  const int src = __ffs(bal) - 1;
+                  found = __shfl_sync(0xffffffffu, sg, src);
+                  rem -= __shfl_sync(0xffffffffu, incl - cnt, src);
+                } else {
+                  rem -= total;
+                }
+              }
+              int pick = -1;
+              if (found >= 0) {
+                // rank-select inside the segment, rows from the highest down: 8 rows per lane
+                const int base_row = found * kSeg;
+                int32_t v[kSeg / 32];
+#pragma unroll
+                for (int j = 0; j < kSeg / 32; ++j) {
+                  const int r = base_row + j * 32 + lane;
+                  v[j] = r < T.n ? __ldcg(A.score + (size_t)g * np + r) : INT32_MIN;
+                }
+                for (int i = 0; i < ncr; ++i) {  // fresh scores override the stash on changed rows
+                  const int cr = __shfl_sync(0xffffffffu, crow, i);
+                  const int32_t cn = __shfl_sync(0xffffffffu, cnew, i);
+                  const int32_t co = __shfl_sync(0xffffffffu, cold, i);
+                  const int rel = cr - base_row;
+                  if (rel >= 0 && rel < kSeg && (rel & 31) == lane && !(cn == INT32_MIN && co == INT32_MIN)) {
+#pragma unroll
+                    for (int j = 0; j < kSeg / 32; ++j)
+                      if (j == (rel >> 5)) v[j] = cn;
+                  }
+                }
+#pragma unroll
+                for (int j = kSeg / 32 - 1; j >= 0; --j) {
+                  const uint32_t bal = __ballot_sync(0xffffffffu, v[j] == gmax);
+                  const int cnt = __popc(bal);
+                  if (pick < 0) {
+                    if (rem < cnt) {
+                      // the tie with exactly `rem` ties above it in this 32-row slice
+                      const bool me = ((bal >> lane) & 1u) && __popc(bal >> 1 >> lane) == rem;
+                      const int bit = __ffs(__ballot_sync(0xffffffffu, me)) - 1;
+                      pick = base_row + j * 32 + bit;
+                    } else {
+                      rem -= cnt;
+                    }
+                  }
+                }
+              }
+              if (pick >= 0) {
+                chosen = pick;
+                res.score = gmax;
+              } else {
+                res.status = 3;  // only reachable after a barrier timeout
+              }
+              last_index += 1;
+            }
+          }
+          KSB_T3(2);  // select
+          // (3) the assume step on the chosen row
+          if (chosen >= 0) {
+            uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
+            if (A.commit) {
+              int idx = -1;
+              {
+                const bool mine = lane < ncr && S.rows[lane].row == chosen;
+                const uint32_t bal = __ballot_sync(0xffffffffu, mine);
+                if (bal) idx = __ffs(bal) - 1;
+              }
+              const bool fast = counters_fast(h);
+              CounterLoads cl;
+              if (fast) cl = counters_load(T, chosen, pv, lane);  // in flight together with the cache fill
+              if (idx < 0) {
+                idx = ncr;
+                cache_fill(T, chosen, S.rows + idx, lane);
+                ncr += 1;
+                __syncwarp();
+              }
+              if (h->n_ext) {
+                if (lane == 0) {
+                  uint32_t rs_, base_;
+                  eval_cached(T, S.rows[idx], pv, 0u, &rs_, (int32_t*)&base_, picks);
+                }
+#pragma unroll
+                for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+              }
+              commit_cached(T, S.rows + idx, pv, picks, lane);
+              if (fast) counters_store(T, chosen, pv, cl, lane);
+              else counters_slow(T, chosen, pv, lane);
+              __syncwarp();
+            } else if (h->n_ext) {
+              if (lane == 0) {
+                EvalOut o;
+                eval_node<true>(T, chosen, pv, o, picks);
+              }
+#pragma unroll
+              for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+            }
+            res.row = T.row_base + chosen;
+#pragma unroll
+            for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
+          }
+          if (lane == 0) A.results[p0 + g] = res;
+          consumed = g + 1;
+          KSB_T3(3);  // commit + result
+        }
+        if (lane == 0) s_consumed = consumed;
+      }
+      __syncthreads();
+      KSB_T3(4);
+      // publish how far the group got; reset the other scratch half for the next group
+      if (tid == 0) {
+        A.group_done[slot] = s_consumed;
+        atomicAdd((unsigned long long*)A.counters, 1ull);
+        if (s_consumed < Gc) atomicAdd((unsigned long long*)A.counters + 1, 1ull);
+      }
+      KsbNorms* nn = A.norms + (size_t)(slot ^ 1) * kMaxG;
+      for (int i = tid; i < kMaxG * 8; i += kThreads) reinterpret_cast<int32_t*>(nn)[i] = ((i & 7) == 7) ? -1 : 0;
+      int32_t* zn = A.zone_sum + (size_t)(slot ^ 1) * kMaxG * zs;
+      for (int i = tid; i < kMaxG * zs; i += kThreads) zn[i] = 0;
+      int32_t* gh = A.ghist + (size_t)(slot ^ 1) * kMaxG * KSB_REASON_BITS;
+      for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
+      KSB_T3(5);  // deferred FitError histograms + resets
+      if (tid == 0)
+        for (int i = 0; i < 6; ++i) A.counters[9 + i] += (uint64_t)t3[i];
+#undef KSB_T3
+    }
+    KSB_TICK(5);
+    grid_barrier(A, epoch);
+    KSB_TICK(6);
+    const int adv = __ldcg(A.group_done + slot);
+    if (adv <= 0 || __ldcg(A.error_flag) != 0) {  // only after a barrier timeout: stop instead of spinning
+      if (tid == 0) atomicExch(A.error_flag, 1);
+      break;
+    }
+    p0 += adv;
+    gi += 1;
   }
-  if (b == 0 && tid == 0) *A.last_node_index = last_index;
+  if (b == 0 && tid == 0) {
+    *A.last_node_index = last_index;
+    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)tk[i];  // block 0's cycles per stage
+  }
+#undef KSB_TICK
 }
 
 // Applies the assume step for a pod placed outside a batch (ksb_pod_add after ksb_schedule).
@@ -715,6 +1231,11 @@ __global__ void ksb_apply_kernel(KsbNodeTable T, const KsbPodHeader* header, con
   __syncwarp();
   PodView pv = make_view(header, pool + header->pool_off, T.W);
   commit_pod(T, row, pv, picks);
+}
+
+extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
+  size_t o[12];
+  return smem_layout(o, zone_stride);
 }
 
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
@@ -744,9 +1265,6 @@ extern "C" int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* heade
   return (int)cudaGetLastError();
 }
 
-extern "C" size_t ksb_batch_smem_bytes(int n_zones) {
-  return sizeof(KsbPodHeader) + (size_t)kMaxPoolWords * 8 + (size_t)(n_zones + 1) * 4;
-}
 extern "C" int ksb_max_pool_words() { return kMaxPoolWords; }
 
 // ---------------------------------------------------------------------------------------------
@@ -758,36 +1276,42 @@ extern "C" int ksb_max_pool_words() { return kMaxPoolWords; }
 // somebody else's stream where cudaMalloc's implicit device-wide synchronisation would stall
 // unrelated work. For them the batch kernel's working memory lives here, in one array that is part
 // of the loaded module: every GPU that loads the library carries these bytes until the process exits.
-// The limits below bound what fits; larger jobs must use ksb_replay_last_batch.
+// The limits below bound what fits; larger jobs must use ksb_replay_last_batch. To keep the array
+// small this path runs the kernel with groups of one pod (same results, by construction).
 //
 // All calls share the one array and it keeps whatever the previous call left behind, so the host
 // side re-zeroes the counters the kernel accumulates into before each launch, and two calls whose
 // kernels overlap on the same GPU would corrupt each other.
 #define KSB_NOALLOC_MAX_ROWS 65536    // padded node rows
-#define KSB_NOALLOC_MAX_ZONES 1024    // zone-sum slots per ping-pong half
+#define KSB_NOALLOC_MAX_ZONES 1024    // zone-sum slots
 #define KSB_NOALLOC_MAX_GRID 1024     // thread blocks
 namespace {
 constexpr size_t na_align(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr size_t kNaSegs = KSB_NOALLOC_MAX_ROWS / kSeg;
 constexpr size_t kNaNorms = 0;
-constexpr size_t kNaZone = kNaNorms + na_align(2 * sizeof(KsbNorms));
-constexpr size_t kNaRaw = kNaZone + na_align(2 * (size_t)KSB_NOALLOC_MAX_ZONES * 4);
-constexpr size_t kNaScore = kNaRaw + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 16);
+constexpr size_t kNaZone = kNaNorms + na_align(2 * kMaxG * sizeof(KsbNorms));
+constexpr size_t kNaZoneBig = 2 * (size_t)kMaxG * KSB_NOALLOC_MAX_ZONES * 4;
+constexpr size_t kNaRawBase = kNaZone + na_align(kNaZoneBig);
+constexpr size_t kNaScore = kNaRawBase + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 16);
 constexpr size_t kNaReasons = kNaScore + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
-constexpr size_t kNaBlkMax = kNaReasons + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
-constexpr size_t kNaBlkCnt = kNaBlkMax + na_align((size_t)KSB_NOALLOC_MAX_GRID * 4);
-constexpr size_t kNaBarrier = kNaBlkCnt + na_align((size_t)KSB_NOALLOC_MAX_GRID * 4);
+constexpr size_t kNaSegMax = kNaReasons + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
+constexpr size_t kNaSegCnt = kNaSegMax + na_align(kNaSegs * 4);
+constexpr size_t kNaBarrier = kNaSegCnt + na_align(kNaSegs * 4);
 constexpr size_t kNaError = kNaBarrier + 256;
 constexpr size_t kNaFitCount = kNaError + 256;
 constexpr size_t kNaLastIndex = kNaFitCount + 256;
-constexpr size_t kNaFitHist = kNaLastIndex + 256;
+constexpr size_t kNaGroupDone = kNaLastIndex + 256;
+constexpr size_t kNaCounters = kNaGroupDone + 256;
+constexpr size_t kNaGhist = kNaCounters + 256;  // counters: 15 x 8 bytes
+constexpr size_t kNaFitHist = kNaGhist + na_align(2 * (size_t)kMaxG * KSB_REASON_BITS * 4);
 constexpr size_t kNaTotal = kNaFitHist + na_align((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
 }  // namespace
 
-static __device__ __align__(256) unsigned char ksb_noalloc_scratch[kNaTotal];  // about 2.1 MiB
+static __device__ __align__(256) unsigned char ksb_noalloc_scratch[kNaTotal];  // about 2.4 MiB
 
 // In host code `ksb_noalloc_scratch` is only a stand-in for the symbol, not a device address, so the
 // address each GPU gave the array is looked up once per device (with that device current) and cached.
-extern "C" int ksb_noalloc_bind(int device, int n_pad, int n_zones, int grid, KsbBatchArgs* a, char* err,
+extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid, KsbBatchArgs* a, char* err,
                                 size_t err_len) {
   static unsigned char* base_of[64] = {nullptr};
   auto fail = [&](const char* msg) {
@@ -795,12 +1319,12 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int n_zones, int grid, Ks
     return -1;
   };
   if (device < 0 || device >= 64) return fail("device ordinal out of range");
-  if (n_pad > KSB_NOALLOC_MAX_ROWS || n_zones > KSB_NOALLOC_MAX_ZONES || grid > KSB_NOALLOC_MAX_GRID) {
+  if (n_pad > KSB_NOALLOC_MAX_ROWS || zone_stride > KSB_NOALLOC_MAX_ZONES || grid > KSB_NOALLOC_MAX_GRID) {
     if (err && err_len)
       snprintf(err, err_len,
                "batch exceeds the no-allocation limits: %d padded node rows (max %d), %d zone slots (max %d), "
                "%d blocks (max %d); use ksb_replay_last_batch",
-               n_pad, KSB_NOALLOC_MAX_ROWS, n_zones, KSB_NOALLOC_MAX_ZONES, grid, KSB_NOALLOC_MAX_GRID);
+               n_pad, KSB_NOALLOC_MAX_ROWS, zone_stride, KSB_NOALLOC_MAX_ZONES, grid, KSB_NOALLOC_MAX_GRID);
     return -1;
   }
   if (!base_of[device]) {
@@ -815,18 +1339,21 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int n_zones, int grid, Ks
     base_of[device] = p;
   }
   unsigned char* b = base_of[device];
+  a->group_size = 1;  // one pod per group: the stashes need one row set, not 32
   a->norms = (KsbNorms*)(b + kNaNorms);
   a->zone_sum = (int32_t*)(b + kNaZone);
-  a->zone_stride = KSB_NOALLOC_MAX_ZONES;
-  a->raw = (int4*)(b + kNaRaw);
+  a->raw = (int4*)(b + kNaRawBase);
   a->score = (int32_t*)(b + kNaScore);
   a->reasons = (uint32_t*)(b + kNaReasons);
-  a->blk_max = (int32_t*)(b + kNaBlkMax);
-  a->blk_cnt = (int32_t*)(b + kNaBlkCnt);
+  a->seg_max = (int32_t*)(b + kNaSegMax);
+  a->seg_cnt = (int32_t*)(b + kNaSegCnt);
   a->barrier = (uint32_t*)(b + kNaBarrier);
   a->error_flag = (int32_t*)(b + kNaError);
   a->fiterr_count = (int32_t*)(b + kNaFitCount);
   a->last_node_index = (uint64_t*)(b + kNaLastIndex);
+  a->group_done = (int32_t*)(b + kNaGroupDone);
+  a->counters = (uint64_t*)(b + kNaCounters);
+  a->ghist = (int32_t*)(b + kNaGhist);
   a->fiterr_hist = (int32_t*)(b + kNaFitHist);
   return 0;
 }

@@ -10,24 +10,30 @@ struct KsbBatchArgs {
   KsbNodeTable table;
   const KsbPodHeader* headers;  // [n_pods]
   const uint64_t* pool;
+  const int32_t* dep;           // [n_pods] latest earlier pod writing a counter this pod reads, -1 if none
   int32_t n_pods;
-  int32_t zone_stride;
+  int32_t zone_stride;          // ints per pod in the zone-sum arrays (>= table.n_zones)
   int32_t commit;               // 1: apply the assume step after each pod (ksb_schedule_batch)
+  int32_t group_size;           // pods per group, 1..KSB_MAX_GROUP
+  int32_t nseg;                 // 256-row segments in this shard
   int32_t pad0;
   KsbResult* results;           // [n_pods]
   // scratch (global memory beyond inputs and outputs)
-  KsbNorms* norms;              // [2] ping-pong per pod
-  int32_t* zone_sum;            // [2][zone_stride]
-  int4* raw;                    // [n_pad] phase-1 Map results
-  int32_t* score;               // [n_pad] phase-2 totals
-  uint32_t* reasons;            // [n_pad] failure-reason masks
-  int32_t* blk_max;             // [grid]
-  int32_t* blk_cnt;             // [grid]
+  KsbNorms* norms;              // [2][KSB_MAX_GROUP] ping-pong per group
+  int32_t* zone_sum;            // [2][KSB_MAX_GROUP][zone_stride]
+  int4* raw;                    // [group_size][n_pad] phase-1 Map results
+  int32_t* score;               // [group_size][n_pad] phase-2 totals
+  uint32_t* reasons;            // [group_size][n_pad] failure-reason masks
+  int32_t* seg_max;             // [group_size][nseg]
+  int32_t* seg_cnt;             // [group_size][nseg]
   uint32_t* barrier;            // grid barrier counter, zero at launch
   int32_t* error_flag;
   int32_t* fiterr_count;
   int32_t* fiterr_hist;         // [KSB_MAX_FITERR][KSB_REASON_BITS]
   uint64_t* last_node_index;    // genericScheduler.lastNodeIndex
+  int32_t* group_done;          // [2] pods consumed by the group, ping-pong
+  uint64_t* counters;           // [16] groups run, groups cut short by a dropped speculation, stage cycles
+  int32_t* ghist;               // [2][KSB_MAX_GROUP][KSB_REASON_BITS] reason histograms of no-fit pods, ping-pong
 };
 
 extern "C" {
@@ -35,9 +41,9 @@ int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cuda
 int ksb_batch_kernel_limits(int device, size_t smem_bytes, int* max_grid, int* threads);
 int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* header, const uint64_t* pool, int row,
                      const uint32_t* masks, cudaStream_t stream);
-size_t ksb_batch_smem_bytes(int n_zones);
+size_t ksb_batch_smem_bytes(int zone_stride);
 int ksb_max_pool_words();
-// Point the scratch fields of *a at the module's static device array (no allocation); -1 + text on
-// error, including batches beyond the array's stated limits.
-int ksb_noalloc_bind(int device, int n_pad, int n_zones, int grid, KsbBatchArgs* a, char* err, size_t err_len);
+// Point the scratch fields of *a at the module's static device array (no allocation) and set the group
+// size that array supports; -1 + text on error, including batches beyond the array's stated limits.
+int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid, KsbBatchArgs* a, char* err, size_t err_len);
 }

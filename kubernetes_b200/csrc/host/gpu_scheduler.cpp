@@ -175,6 +175,11 @@ std::string run(Session& s, const json::Value& opt) {
   out += ",\"encode_ms\":" + std::to_string(encode_ms);
   out += ",\"replay_ms\":" + std::to_string(replay_ms);
   out += ",\"kernel_launches\":" + std::to_string(st.kernel_launches);
+  out += ",\"stage_cycles\":[";
+  for (int i = 0; i < 13; ++i) out += (i ? "," : "") + std::to_string(st.stage_cycles[i]);
+  out += "]";
+  out += ",\"groups\":" + std::to_string(st.groups);
+  out += ",\"group_restarts\":" + std::to_string(st.group_restarts);
   out += ",\"h2d_bytes\":" + std::to_string(st.h2d_bytes);
   out += ",\"d2h_bytes\":" + std::to_string(st.d2h_bytes);
   out += ",\"lastNodeIndex\":" + std::to_string(ksb_get_last_node_index(h.get()));

@@ -1,0 +1,20 @@
+"""Sweep the speculative group size on one synthetic config; prints kernel time, groups, restarts."""
+import json
+import sys
+
+sys.path.insert(0, ".")
+from kubernetes_b200 import lib, workloads
+
+cfg, nodes, pods = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
+sizes = [int(x) for x in sys.argv[4].split(",")] if len(sys.argv) > 4 else [1, 2, 4, 8, 16, 32]
+cluster = workloads.generate(cfg, nodes, pods)
+sess = lib.Session(cluster=cluster)
+sess.run(results=False)
+for g in sizes:
+    out = sess.run(results=False, group_size=g, replay_iters=2)
+    print(json.dumps({"cfg": cfg, "nodes": nodes, "pods": pods, "G": g, "kernel_ms": round(out["kernel_ms"], 2),
+                      "replay_ms": round(out["replay_ms"], 2), "us_per_pod": round(1000 * out["replay_ms"] / pods, 2),
+                      "groups": out["groups"], "restarts": out["group_restarts"], "encode_ms": round(out["encode_ms"], 1),
+                      "e2e_ms": round(out["e2e_ms"], 1), "hash": out["placement_hash"][-6:],
+                      "stage_us_per_pod": [round(c / 1965.0 / pods, 2) for c in out["stage_cycles"]]}))
+sess.close()

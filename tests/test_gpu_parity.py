@@ -58,6 +58,31 @@ def test_small_batches_match_one_batch():
     assert a["placement_hash"] == b["placement_hash"]
 
 
+@pytest.mark.parametrize("cfg,nodes,pods", [(1, 64, 800), (2, 60, 900), (3, 700, 3000), (5, 120, 900)])
+def test_group_sizes_agree(cfg, nodes, pods):
+    """Speculative groups of any size must give the placements of one-pod groups (live evaluation)."""
+    cluster = workloads.generate(cfg, nodes, pods)
+    sess = lib.Session(cluster=cluster)
+    base = sess.run(results=False, group_size=1)
+    seen = {}
+    for g in (2, 5, 16, 32):
+        out = sess.run(results=False, group_size=g)
+        seen[g] = (out["placement_hash"], out["lastNodeIndex"])
+        assert out["groups"] <= base["groups"]
+    sess.close()
+    assert all(v == (base["placement_hash"], base["lastNodeIndex"]) for v in seen.values()), (seen, base["placement_hash"])
+
+
+def test_full_node_and_tight_cluster_forces_restarts():
+    """A small, nearly full cluster: rows turn unfit inside groups, so speculation is dropped often."""
+    cluster = workloads.generate(1, 12, 700)
+    for n in cluster["nodes"]:
+        n["allocatable"]["pods"] = 40
+    got, want = compare(cluster, "tight cfg1")
+    assert any(r["status"] == 2 for r in want["results"])
+    assert got["group_restarts"] > 0
+
+
 def test_unpadded_names_and_heterogeneous_devices():
     c1 = workloads.generate(1, 120, 600, padded=False)  # "node-10" < "node-9" bytewise
     compare(c1, "cfg1 unpadded")
