@@ -152,6 +152,17 @@ int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out);
  * return the average CUDA-event milliseconds per run (measurement only; state is restored). */
 int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_result* out);
 
+/* ---- sharding the node table over the GPUs of one NVSwitch domain ----
+ * No counterpart in the reference (its only parallelism is workqueue.Parallelize(16, ...) over nodes,
+ * core/generic_scheduler.go:326,574). One engine per GPU is created with shard_rank / shard_count set; every
+ * engine is fed every node, pod and selector owner. After the cluster is loaded each engine calls
+ * ksb_shard_export (which fixes the capacities of the buffers peers will map), the callers exchange the
+ * blobs (torch.distributed in bench.py), and each engine calls ksb_shard_connect with all of them. From then
+ * on ksb_schedule_batch / ksb_replay_last_batch must be called on every rank with the same arguments; the
+ * kernels synchronise over NVLink and every rank receives the same results. */
+int32_t ksb_shard_export(ksb_engine* e, int32_t max_batch_pods, uint8_t* out, size_t cap, size_t* len);
+int32_t ksb_shard_connect(ksb_engine* e, const uint8_t* blobs, const uint64_t* offsets, int32_t n_ranks);
+
 /* No counterpart in the reference. One run of what ksb_replay_last_batch runs (the resident batch,
  * against the restored node table), for callers that must not allocate GPU memory while they work:
  * a process confined to a fixed memory budget (a MIG slice or an MPS client with a hard limit, where

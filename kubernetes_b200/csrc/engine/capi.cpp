@@ -1,5 +1,6 @@
 // extern "C" surface of include/ksched_b200.h over ksb::Engine.
 #include <cstring>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -164,6 +165,24 @@ int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out) {
 
 int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_result* out) {
   return guarded(e, [&] { e->impl->replay_last_batch(iters, avg_ms, out); });
+}
+
+int32_t ksb_shard_export(ksb_engine* e, int32_t max_batch_pods, uint8_t* out, size_t cap, size_t* len) {
+  return guarded(e, [&] {
+    std::string b = e->impl->shard_export(max_batch_pods);
+    if (b.size() > cap) throw std::runtime_error("ksb_shard_export: output buffer too small");
+    memcpy(out, b.data(), b.size());
+    *len = b.size();
+  });
+}
+
+int32_t ksb_shard_connect(ksb_engine* e, const uint8_t* blobs, const uint64_t* offsets, int32_t n_ranks) {
+  return guarded(e, [&] {
+    std::vector<std::string> v;
+    for (int32_t i = 0; i < n_ranks; ++i)
+      v.emplace_back((const char*)blobs + offsets[i], (size_t)(offsets[i + 1] - offsets[i]));
+    e->impl->shard_connect(v);
+  });
 }
 
 int32_t ksb_replay_last_batch_noalloc(ksb_engine* e, ksb_result* out) {

@@ -20,6 +20,7 @@
 #define KSB_REASON_BITS 32
 #define KSB_MAX_GROUP 32      // pods evaluated against one snapshot of the table
 #define KSB_MAX_SEGMENTS 2048 // 256-row segments per shard (524,288 node rows)
+#define KSB_MAX_RANKS 8        // shards of one node table (one NVSwitch domain)
 #define KSB_SEG_CACHE 4096    // (group size) x (segments) bound: segment statistics held in shared memory
 
 // node flags (predicates.go:1382-1441)

@@ -72,6 +72,7 @@ Engine::Engine(const ksb_config& c) : cfg(c) {
 
 Engine::~Engine() {
   cudaSetDevice(cfg.device);
+  for (void* m : ipc_mappings) cudaIpcCloseMemHandle(m);
   for (DevBuf* b : {&b_i64, &b_u32, &b_u64, &b_dev_class, &b_topo, &b_spread, &b_tables, &b_headers, &b_pool,
                     &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush, &b_dep})
     b->release();
@@ -112,11 +113,38 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
   label_defs.push_back(d);
   label_bits[k] = bit;
   if (!layout_dirty) {  // fill the new bit column from the retained node labels
-    for (int r = 0; r < n; ++r)
-      if (node_has_label_bit(rows[r]->node, d)) u64(bit >> 6, r) |= 1ull << (bit & 63);
+    if (!label_index_valid) build_label_index();
+    const std::vector<int>* cand = nullptr;
+    if (kind == 'P') {
+      std::string pk = key;
+      pk.push_back('\0');
+      pk += value;
+      auto it2 = rows_by_pair.find(pk);
+      if (it2 != rows_by_pair.end()) cand = &it2->second;
+    } else {
+      auto it2 = rows_by_key.find(key);
+      if (it2 != rows_by_key.end()) cand = &it2->second;
+    }
+    if (cand)
+      for (int r : *cand)
+        if (node_has_label_bit(rows[r]->node, d)) u64(bit >> 6, r) |= 1ull << (bit & 63);
     dirty_label_words.insert(bit >> 6);
   }
   return bit;
+}
+
+void Engine::build_label_index() {
+  rows_by_pair.clear();
+  rows_by_key.clear();
+  for (int r = 0; r < n; ++r)
+    for (auto& kv : rows[r]->node.labels) {
+      std::string pk = kv.first;
+      pk.push_back('\0');
+      pk += kv.second;
+      rows_by_pair[pk].push_back(r);
+      rows_by_key[kv.first].push_back(r);
+    }
+  label_index_valid = true;
 }
 
 int Engine::topo_key(const std::string& key) {
@@ -414,6 +442,7 @@ void Engine::node_upsert(const Node& nd) {
     // topology domains may be new; tables are resized inside topo_domain
     fill_row(hn.row);
     dirty_rows.insert(hn.row);
+    label_index_valid = false;
   }
 }
 
@@ -709,6 +738,7 @@ void Engine::rebuild_layout() {
   h_topo.assign((size_t)KSB_MAX_TOPO * n_pad, 0);
   for (auto& c : h_spread) c.assign((size_t)n_pad, 0u);
   layout_dirty = false;
+  label_index_valid = false;
   for (int r = 0; r < n; ++r) fill_row(r);
   // per-class counters follow the pods: recount them all
   for (auto& t : tables) std::fill(t.vals.begin(), t.vals.end(), 0);

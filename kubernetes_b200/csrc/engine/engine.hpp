@@ -107,6 +107,9 @@ class Engine {
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
   void replay_last_batch_noalloc(ksb_result* out);
+  // sharding over the GPUs of one NVSwitch domain
+  std::string shard_export(int max_batch_pods);
+  void shard_connect(const std::vector<std::string>& blobs);
   std::string fit_error_message(int i);
 
   std::string last_error;
@@ -128,6 +131,11 @@ class Engine {
     int64_t num = 0;
   };
   std::vector<LabelBitDef> label_defs;
+  // inverted index over the retained node labels (rows by "key\0value" and by key): a label bit interned
+  // later fills its column from the matching rows only instead of scanning every node
+  std::unordered_map<std::string, std::vector<int>> rows_by_pair, rows_by_key;
+  bool label_index_valid = false;
+  void build_label_index();
   std::vector<Taint> hard_taints, soft_taints;
   std::unordered_map<std::string, int> hard_taint_idx, soft_taint_idx;
   std::unordered_map<std::string, int> avoid_idx;
@@ -215,6 +223,25 @@ class Engine {
   size_t spread_cap_cols = 0;
   int grid = 0, threads = 0, max_grid = 0, group = 1, nseg = 0, zone_stride = 64;
   size_t smem_bytes = 0;
+  // shard geometry: device rows [lbase, lbase + ln), device column stride ln_pad
+  int lbase = 0, ln = 0, ln_pad = 0, rows_per_shard = 0;
+  size_t min_spread_cols = 0, min_table_bytes = 0;
+  bool shard_connected = false;
+  struct PeerMap {
+    void* p[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int ln = 0, ln_pad = 0, lbase = 0;
+  };
+  std::vector<PeerMap> peer_maps;    // rank 0: every other shard's buffers as mapped into this process
+  size_t shard_results_cap = 0;
+  int segs_per_shard = 1, nseg_total = 0;
+  void prepare_geometry();
+  void* peer0_scratch = nullptr;     // other ranks: rank 0's scratch buffer, mapped
+  std::vector<void*> ipc_mappings;
+  void plan_shard();
+  void fill_table_pointers(KsbNodeTable* T, void* i64b, void* u32b, void* u64b, void* devb, void* topob, void* spreadb,
+                           void* tablesb, size_t np) const;
+  void upload_family(DevBuf& dst, const void* src, size_t elem, int cols);
+  void upload_column(void* dev_base, const void* host_col, size_t elem, int dev_col);
   void upload_all();
   void upload_dirty();
   void sync_device();

@@ -20,7 +20,7 @@ namespace ksb {
 namespace {
 struct ScratchLayout {
   size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, barrier, error_flag, fiterr_count, last_index,
-      group_done, counters, ghist, fiterr_hist, total;
+      group_done, counters, ghist, release, xbar, xstate, peers, fiterr_hist, total;
 };
 ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   ScratchLayout L;
@@ -44,20 +44,28 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   L.group_done = take(8);
   L.counters = take(128);
   L.ghist = take(2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4);
+  L.release = take(4);
+  L.xbar = take(4);
+  L.xstate = take(4);
+  L.peers = take(sizeof(KsbPeer) * KSB_MAX_RANKS);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
   L.total = off;
   return L;
 }
 }  // namespace
 
-KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
+// Geometry of the next launch (group size, segments, grid, shared memory) and the scratch buffer for it.
+void Engine::prepare_geometry() {
+  const int R = std::max(1, cfg.shard_count);
   zone_stride = (dT.n_zones + 63) & ~63;
-  // group size: as configured, bounded by what the zone-sum arrays may take of shared memory
+  nseg = (ln + 255) / 256;
+  segs_per_shard = R == 1 ? std::max(1, nseg) : rows_per_shard / 256;
+  nseg_total = R == 1 ? nseg : (n + 255) / 256;
+  // group size: as configured, bounded by what the zone sums and the segment statistics may take of shared memory
   group = cfg.group_size > 0 ? std::min(cfg.group_size, KSB_MAX_GROUP) : KSB_MAX_GROUP;
   group = std::max(1, std::min(group, 16384 / zone_stride));
-  nseg = (n + 255) / 256;
-  if (nseg > KSB_MAX_SEGMENTS) throw std::runtime_error("more than 524,288 node rows in one shard");
-  group = std::max(1, std::min(group, KSB_SEG_CACHE / nseg));
+  if (nseg_total > KSB_MAX_SEGMENTS) throw std::runtime_error("more than 524,288 node rows");
+  group = std::max(1, std::min(group, KSB_SEG_CACHE / std::max(1, nseg_total)));
   if (zone_stride * 4 * KSB_MAX_GROUP > 160 * 1024) throw std::runtime_error("more than 1,280 distinct zones");
   smem_bytes = ksb_batch_smem_bytes(zone_stride);
   int mg = 0, th = 0;
@@ -67,9 +75,17 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   threads = th;
   if (max_grid < 1) throw std::runtime_error("batch kernel does not fit on this device");
   // enough blocks to cover every segment; when segments are few, extra blocks split the group's pods
-  grid = nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, nseg * group));
-  ScratchLayout L = scratch_layout(n_pad, zone_stride, nseg, group);
+  grid = nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, std::max(1, nseg) * group));
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group);
+  if (shard_connected && L.total > b_scratch.cap)
+    throw std::runtime_error("sharded engine: scratch outgrew the shared buffer (re-run ksb_shard_export/connect)");
   b_scratch.ensure(L.total);
+}
+
+KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
+  const int R = std::max(1, cfg.shard_count);
+  prepare_geometry();
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group);
   char* base = (char*)b_scratch.d;
   KsbBatchArgs a;
   memset(&a, 0, sizeof a);
@@ -98,6 +114,25 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.group_done = (int32_t*)(base + L.group_done);
   a.counters = (uint64_t*)(base + L.counters);
   a.ghist = (int32_t*)(base + L.ghist);
+  a.release = (uint32_t*)(base + L.release);
+  a.xbar = (uint32_t*)(base + L.xbar);
+  a.xstate = (uint32_t*)(base + L.xstate);
+  a.peers = (const KsbPeer*)(base + L.peers);
+  a.n_ranks = R;
+  a.rank = R == 1 ? 0 : cfg.shard_rank;
+  a.segs_per_shard = segs_per_shard;
+  a.nseg_total = nseg_total;
+  if (R > 1) {
+    if (!shard_connected) throw std::runtime_error("sharded engine: call ksb_shard_export / ksb_shard_connect first");
+    if (a.rank != 0) {  // the reduction targets and the cross-GPU barrier live in rank 0's memory
+      char* b0 = (char*)peer0_scratch;
+      a.norms = (KsbNorms*)(b0 + L.norms);
+      a.zone_sum = (int32_t*)(b0 + L.zone_sum);
+      a.ghist = (int32_t*)(b0 + L.ghist);
+      a.group_done = (int32_t*)(b0 + L.group_done);
+      a.xbar = (uint32_t*)(b0 + L.xbar);
+    }
+  }
   return a;
 }
 
@@ -107,15 +142,69 @@ void Engine::launch(const KsbBatchArgs& a) {
   static KsbNorms init[2 * KSB_MAX_GROUP];
   memset(init, 0, sizeof init);
   for (auto& x : init) x.one_row = -1;
-  CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)KSB_MAX_GROUP * a.zone_stride * 4, stream));
+  if (a.n_ranks == 1) {  // sharded: rank 0's kernel clears these itself, behind the opening barrier
+    CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)KSB_MAX_GROUP * a.zone_stride * 4, stream));
+    CUDA_OK(cudaMemsetAsync(a.ghist, 0, 2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4, stream));
+    CUDA_OK(cudaMemsetAsync(a.group_done, 0, 8, stream));
+  }
   CUDA_OK(cudaMemsetAsync(a.barrier, 0, 4, stream));
   CUDA_OK(cudaMemsetAsync(a.error_flag, 0, 4, stream));
   CUDA_OK(cudaMemsetAsync(a.fiterr_count, 0, 4, stream));
-  CUDA_OK(cudaMemsetAsync(a.group_done, 0, 8, stream));
   CUDA_OK(cudaMemsetAsync(a.counters, 0, 128, stream));
-  CUDA_OK(cudaMemsetAsync(a.ghist, 0, 2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4, stream));
   CUDA_OK(cudaMemcpyAsync(a.last_node_index, &last_node_index, 8, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemsetAsync(a.release, 0, 4, stream));
+  static KsbPeer self;  // what rank 0 sees of this (only) shard: its own buffers
+  if (a.n_ranks == 1) {
+    CUDA_OK(cudaMemsetAsync(a.xbar, 0, 4, stream));
+    CUDA_OK(cudaMemsetAsync(a.xstate, 0, 4, stream));
+    self.table = a.table;
+    self.raw = a.raw;
+    self.score = a.score;
+    self.reasons = a.reasons;
+    self.seg_max = a.seg_max;
+    self.seg_cnt = a.seg_cnt;
+    self.results = a.results;
+    self.last_node_index = a.last_node_index;
+    self.nseg = a.nseg;
+    self.seg_base = 0;
+    CUDA_OK(cudaMemcpyAsync((void*)a.peers, &self, sizeof self, cudaMemcpyHostToDevice, stream));
+  } else if (a.rank == 0) {
+    // the peer table: this rank from its own buffers, the others from their mapped buffers and geometry
+    std::vector<KsbPeer> pt(a.n_ranks);
+    pt[0].table = a.table;
+    pt[0].raw = a.raw;
+    pt[0].score = a.score;
+    pt[0].reasons = a.reasons;
+    pt[0].seg_max = a.seg_max;
+    pt[0].seg_cnt = a.seg_cnt;
+    pt[0].results = a.results;
+    pt[0].last_node_index = a.last_node_index;
+    pt[0].nseg = a.nseg;
+    pt[0].seg_base = 0;
+    for (int q = 1; q < a.n_ranks; ++q) {
+      const PeerMap& m = peer_maps[q];
+      KsbPeer& P = pt[q];
+      P.table = a.table;  // weights, W, zone count
+      P.table.n = m.ln;
+      P.table.n_pad = m.ln_pad;
+      P.table.row_base = m.lbase;
+      fill_table_pointers(&P.table, m.p[0], m.p[1], m.p[2], m.p[3], m.p[4], m.p[5], m.p[6], (size_t)m.ln_pad);
+      const int nseg_q = (m.ln + 255) / 256;
+      ScratchLayout Lq = scratch_layout(m.ln_pad, a.zone_stride, std::max(1, nseg_q), a.group_size);
+      char* sb = (char*)m.p[7];
+      P.raw = (int4*)(sb + Lq.raw);
+      P.score = (int32_t*)(sb + Lq.score);
+      P.reasons = (uint32_t*)(sb + Lq.reasons);
+      P.seg_max = (int32_t*)(sb + Lq.seg_max);
+      P.seg_cnt = (int32_t*)(sb + Lq.seg_cnt);
+      P.last_node_index = (uint64_t*)(sb + Lq.last_index);
+      P.results = (KsbResult*)m.p[8];
+      P.nseg = nseg_q;
+      P.seg_base = q * a.segs_per_shard;
+    }
+    CUDA_OK(cudaMemcpy((void*)a.peers, pt.data(), sizeof(KsbPeer) * pt.size(), cudaMemcpyHostToDevice));
+  }
   CUDA_OK(cudaStreamSynchronize(stream));  // last_node_index may change right after this call
   int rc = ksb_launch_batch(&a, grid, smem_bytes, stream);
   if (rc != 0) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString((cudaError_t)rc));
@@ -124,8 +213,8 @@ void Engine::launch(const KsbBatchArgs& a) {
 
 void Engine::snapshot_dynamic() {
   // everything the kernel mutates: int64 family, u32 family, u64 family (ports), spread, tables
-  size_t s0 = h_i64.size() * 8, s1 = h_u32.size() * 4, s2 = h_u64.size() * 8;
-  size_t s3 = h_spread.size() * (size_t)n_pad * 4, s4 = (size_t)std::max<uint32_t>(arena_words, 1) * 4;
+  size_t s0 = (size_t)I64_COLS * ln_pad * 8, s1 = (size_t)U32_COLS * ln_pad * 4, s2 = (size_t)u64_cols() * ln_pad * 8;
+  size_t s3 = h_spread.size() * (size_t)ln_pad * 4, s4 = (size_t)std::max<uint32_t>(arena_words, 1) * 4;
   b_snapshot.ensure(s0 + s1 + s2 + s3 + s4);
   char* d = (char*)b_snapshot.d;
   CUDA_OK(cudaMemcpyAsync(d, b_i64.d, s0, cudaMemcpyDeviceToDevice, stream));
@@ -137,8 +226,8 @@ void Engine::snapshot_dynamic() {
 }
 
 void Engine::restore_dynamic() {
-  size_t s0 = h_i64.size() * 8, s1 = h_u32.size() * 4, s2 = h_u64.size() * 8;
-  size_t s3 = h_spread.size() * (size_t)n_pad * 4, s4 = (size_t)std::max<uint32_t>(arena_words, 1) * 4;
+  size_t s0 = (size_t)I64_COLS * ln_pad * 8, s1 = (size_t)U32_COLS * ln_pad * 4, s2 = (size_t)u64_cols() * ln_pad * 8;
+  size_t s3 = h_spread.size() * (size_t)ln_pad * 4, s4 = (size_t)std::max<uint32_t>(arena_words, 1) * 4;
   char* d = (char*)b_snapshot.d;
   CUDA_OK(cudaMemcpyAsync(b_i64.d, d, s0, cudaMemcpyDeviceToDevice, stream));
   CUDA_OK(cudaMemcpyAsync(b_u32.d, d + s0, s1, cudaMemcpyDeviceToDevice, stream));
@@ -215,6 +304,8 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   sync_device();
   b_headers.ensure(headers.size() * sizeof(KsbPodHeader));
   b_pool.ensure(pool.size() * 8);
+  if (shard_connected && (size_t)np * sizeof(KsbResult) > b_results.cap)
+    throw std::runtime_error("sharded engine: batch larger than the max_batch_pods given to ksb_shard_export");
   b_results.ensure((size_t)np * sizeof(KsbResult));
   b_dep.ensure((size_t)np * 4);
   CUDA_OK(cudaMemcpyAsync(b_dep.d, dep.data(), (size_t)np * 4, cudaMemcpyHostToDevice, stream));
@@ -359,7 +450,12 @@ void Engine::replay_last_batch_noalloc(ksb_result* out) {
   a.dep = (const int32_t*)b_dep.d;
   a.zone_stride = zone_stride;
   a.nseg = nseg;
-  if (ksb_noalloc_bind(cfg.device, n_pad, zone_stride, grid, &a, err, sizeof err) != 0) throw std::runtime_error(err);
+  a.n_ranks = 1;
+  a.rank = 0;
+  a.segs_per_shard = nseg;
+  a.nseg_total = nseg;
+  if (cfg.shard_count > 1) throw std::runtime_error("ksb_replay_last_batch_noalloc does not support sharded engines");
+  if (ksb_noalloc_bind(cfg.device, ln_pad, zone_stride, grid, &a, err, sizeof err) != 0) throw std::runtime_error(err);
   restore_dynamic();
   const uint64_t saved_index = last_node_index;
   last_node_index = last_index_before;  // launch() seeds the device counter from this member
@@ -374,6 +470,89 @@ void Engine::replay_last_batch_noalloc(ksb_result* out) {
     throw std::runtime_error("device kernel reported a barrier timeout");
   }
   for (int i = 0; i < np; ++i) out[i].num_nodes = n;  // the device record keeps a histogram slot in this field
+}
+
+// ------------------------------------------------------------------ sharding
+//
+// One engine per GPU, each holding a contiguous range of node rows. Every engine receives every node, pod
+// and selector owner (host state is replicated and stays identical); only the device buffers are sharded.
+// Phases 1 and 2 run on every GPU over its own rows; the reduction targets live in rank 0's memory and are
+// updated with NVLink atomics; phase 3 runs on rank 0, which reaches the other shards' stashes and node
+// columns through CUDA-IPC mappings of their buffers.
+
+namespace {
+struct ShardBlob {
+  uint32_t magic;
+  int32_t rank, n_ranks, n, ln, ln_pad, lbase, rows_per_shard;
+  uint64_t results_cap;
+  cudaIpcMemHandle_t h[9];  // i64, u32, u64, dev_class, topo, spread, tables, scratch, results
+};
+constexpr uint32_t kShardMagic = 0x4b534231u;
+}  // namespace
+
+std::string Engine::shard_export(int max_batch_pods) {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  if (cfg.shard_count < 2) throw std::runtime_error("engine was not created with shard_count > 1");
+  if (cfg.shard_count > KSB_MAX_RANKS) throw std::runtime_error("more than KSB_MAX_RANKS shards");
+  if (shard_connected) throw std::runtime_error("shard already connected");
+  // fixed capacities: shared buffers may not be reallocated once peers have mapped them
+  min_spread_cols = 1024;
+  min_table_bytes = (size_t)4 << 20;
+  spread_cap_cols = 0;
+  arena_dirty = true;
+  sync_device();
+  prepare_geometry();
+  CUDA_OK(cudaMemsetAsync(b_scratch.d, 0, b_scratch.cap, stream));
+  b_results.ensure((size_t)std::max(1, max_batch_pods) * sizeof(KsbResult));
+  CUDA_OK(cudaStreamSynchronize(stream));
+  ShardBlob b;
+  memset(&b, 0, sizeof b);
+  b.magic = kShardMagic;
+  b.rank = cfg.shard_rank;
+  b.n_ranks = cfg.shard_count;
+  b.n = n;
+  b.ln = ln;
+  b.ln_pad = ln_pad;
+  b.lbase = lbase;
+  b.rows_per_shard = rows_per_shard;
+  b.results_cap = b_results.cap;
+  void* ptrs[9] = {b_i64.d, b_u32.d, b_u64.d, b_dev_class.d, b_topo.d, b_spread.d, b_tables.d, b_scratch.d, b_results.d};
+  for (int i = 0; i < 9; ++i) CUDA_OK(cudaIpcGetMemHandle(&b.h[i], ptrs[i]));
+  shard_results_cap = b_results.cap;
+  return std::string((const char*)&b, sizeof b);
+}
+
+void Engine::shard_connect(const std::vector<std::string>& blobs) {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  const int R = cfg.shard_count;
+  if ((int)blobs.size() != R) throw std::runtime_error("shard_connect: need one blob per rank");
+  std::vector<ShardBlob> bs(R);
+  for (int q = 0; q < R; ++q) {
+    if (blobs[q].size() != sizeof(ShardBlob)) throw std::runtime_error("shard_connect: bad blob size");
+    memcpy(&bs[q], blobs[q].data(), sizeof(ShardBlob));
+    if (bs[q].magic != kShardMagic || bs[q].rank != q || bs[q].n_ranks != R || bs[q].n != n ||
+        bs[q].rows_per_shard != rows_per_shard)
+      throw std::runtime_error("shard_connect: blob " + std::to_string(q) + " does not describe the same cluster");
+  }
+  peer_maps.assign(R, PeerMap());
+  if (cfg.shard_rank == 0) {
+    for (int q = 1; q < R; ++q) {
+      PeerMap& m = peer_maps[q];
+      m.ln = bs[q].ln;
+      m.ln_pad = bs[q].ln_pad;
+      m.lbase = bs[q].lbase;
+      for (int i = 0; i < 9; ++i) {
+        CUDA_OK(cudaIpcOpenMemHandle(&m.p[i], bs[q].h[i], cudaIpcMemLazyEnablePeerAccess));
+        ipc_mappings.push_back(m.p[i]);
+      }
+    }
+  } else {
+    CUDA_OK(cudaIpcOpenMemHandle(&peer0_scratch, bs[0].h[7], cudaIpcMemLazyEnablePeerAccess));
+    ipc_mappings.push_back(peer0_scratch);
+  }
+  shard_connected = true;
 }
 
 // FitError.Error() (generic_scheduler.go:70-88)
@@ -424,6 +603,13 @@ void Engine::pod_add(const Pod& p) {
     // rows are about to be rebuilt from the host records (or the node has no Node object yet)
     host_add_pod(p, hn);
     pods[p.key()] = HostPod{p};
+    return;
+  }
+  if (cfg.shard_count > 1) {
+    // sharded: keep the host records exact and re-upload this engine's slice before the next batch
+    host_add_pod(p, hn);
+    pods[p.key()] = HostPod{p};
+    layout_dirty = true;
     return;
   }
   CUDA_OK(cudaSetDevice(cfg.device));

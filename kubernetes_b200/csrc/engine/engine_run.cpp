@@ -488,12 +488,31 @@ void Engine::apply_class_part_host(int row, const std::vector<CommitEntry>& comm
 }
 
 // ------------------------------------------------------------------ device synchronisation
+//
+// The host mirror always holds every row. The device holds this engine's shard: rows
+// [lbase, lbase + ln) with column stride ln_pad (the whole table when shard_count == 1).
+
+void Engine::plan_shard() {
+  const int R = std::max(1, cfg.shard_count);
+  if (R == 1) {
+    lbase = 0;
+    ln = n;
+    ln_pad = n_pad;
+    rows_per_shard = n_pad;
+    return;
+  }
+  rows_per_shard = std::max(256, (((n + R - 1) / R) + 255) & ~255);  // whole segments per shard
+  lbase = std::min(n, cfg.shard_rank * rows_per_shard);
+  ln = std::max(0, std::min(n - lbase, rows_per_shard));
+  ln_pad = rows_per_shard;
+}
 
 void Engine::setup_table_pointers() {
   KsbNodeTable& T = dT;
-  T.n = n;
-  T.n_pad = n_pad;
-  T.row_base = 0;
+  const size_t np = ln_pad;
+  T.n = ln;
+  T.n_pad = ln_pad;
+  T.row_base = lbase;
   T.n_total = n;
   T.W = W;
   T.n_zones = (int)zone_idx.size() + 1;
@@ -504,52 +523,65 @@ void Engine::setup_table_pointers() {
   T.w_tt = cfg.w_taint_toleration;
   T.w_ipa = cfg.w_inter_pod_affinity;
   T.w_avoid = cfg.w_prefer_avoid;
-  int64_t* a = (int64_t*)b_i64.d;
-  auto c64 = [&](int col) { return a + (size_t)col * n_pad; };
-  T.alloc_cpu = c64(I64_ALLOC_CPU);
-  T.alloc_mem = c64(I64_ALLOC_MEM);
-  T.alloc_agpu = c64(I64_ALLOC_AGPU);
-  T.alloc_eph = c64(I64_ALLOC_EPH);
-  T.req_cpu = c64(I64_REQ_CPU);
-  T.req_mem = c64(I64_REQ_MEM);
-  T.req_agpu = c64(I64_REQ_AGPU);
-  T.req_eph = c64(I64_REQ_EPH);
-  T.nz_cpu = c64(I64_NZ_CPU);
-  T.nz_mem = c64(I64_NZ_MEM);
-  T.alloc_scalar = c64(I64_ALLOC_SCALAR);
-  T.req_scalar = c64(I64_REQ_SCALAR);
-  uint32_t* b = (uint32_t*)b_u32.d;
-  T.alloc_pods = (int32_t*)(b + (size_t)U32_ALLOC_PODS * n_pad);
-  T.num_pods = (int32_t*)(b + (size_t)U32_NUM_PODS * n_pad);
-  T.flags = b + (size_t)U32_FLAGS * n_pad;
-  T.zone = b + (size_t)U32_ZONE * n_pad;
-  T.dev_avail = b + (size_t)U32_DEV_AVAIL * n_pad;
-  uint64_t* c = (uint64_t*)b_u64.d;
-  T.labels = c;
-  T.taint_hard = c + (size_t)U64_HARD() * n_pad;
-  T.taint_soft = c + (size_t)U64_SOFT() * n_pad;
-  T.avoid = c + (size_t)U64_AVOID() * n_pad;
-  T.port_any = c + (size_t)U64_PORT_ANY() * n_pad;
-  T.port_wild = c + (size_t)U64_PORT_WILD() * n_pad;
-  T.port_exact = c + (size_t)U64_PORT_EXACT() * n_pad;
-  T.dev_class = (uint16_t*)b_dev_class.d;
-  T.topo = (uint32_t*)b_topo.d;
-  T.spread = (uint32_t*)b_spread.d;
-  T.tables = (int32_t*)b_tables.d;
+  fill_table_pointers(&T, b_i64.d, b_u32.d, b_u64.d, b_dev_class.d, b_topo.d, b_spread.d, b_tables.d, np);
+}
+
+// Column pointers of a shard from the base addresses of its buffers (also used for peers' mapped buffers).
+void Engine::fill_table_pointers(KsbNodeTable* T, void* i64b, void* u32b, void* u64b, void* devb, void* topob,
+                                 void* spreadb, void* tablesb, size_t np) const {
+  int64_t* a = (int64_t*)i64b;
+  auto c64 = [&](int col) { return a + (size_t)col * np; };
+  T->alloc_cpu = c64(I64_ALLOC_CPU);
+  T->alloc_mem = c64(I64_ALLOC_MEM);
+  T->alloc_agpu = c64(I64_ALLOC_AGPU);
+  T->alloc_eph = c64(I64_ALLOC_EPH);
+  T->req_cpu = c64(I64_REQ_CPU);
+  T->req_mem = c64(I64_REQ_MEM);
+  T->req_agpu = c64(I64_REQ_AGPU);
+  T->req_eph = c64(I64_REQ_EPH);
+  T->nz_cpu = c64(I64_NZ_CPU);
+  T->nz_mem = c64(I64_NZ_MEM);
+  T->alloc_scalar = c64(I64_ALLOC_SCALAR);
+  T->req_scalar = c64(I64_REQ_SCALAR);
+  uint32_t* b = (uint32_t*)u32b;
+  T->alloc_pods = (int32_t*)(b + (size_t)U32_ALLOC_PODS * np);
+  T->num_pods = (int32_t*)(b + (size_t)U32_NUM_PODS * np);
+  T->flags = b + (size_t)U32_FLAGS * np;
+  T->zone = b + (size_t)U32_ZONE * np;
+  T->dev_avail = b + (size_t)U32_DEV_AVAIL * np;
+  uint64_t* c = (uint64_t*)u64b;
+  T->labels = c;
+  T->taint_hard = c + (size_t)U64_HARD() * np;
+  T->taint_soft = c + (size_t)U64_SOFT() * np;
+  T->avoid = c + (size_t)U64_AVOID() * np;
+  T->port_any = c + (size_t)U64_PORT_ANY() * np;
+  T->port_wild = c + (size_t)U64_PORT_WILD() * np;
+  T->port_exact = c + (size_t)U64_PORT_EXACT() * np;
+  T->dev_class = (uint16_t*)devb;
+  T->topo = (uint32_t*)topob;
+  T->spread = (uint32_t*)spreadb;
+  T->tables = (int32_t*)tablesb;
+}
+
+// Copy `cols` columns of `elem`-byte entries: host column stride n_pad, device column stride ln_pad, rows
+// [lbase, lbase + ln). The padding rows of the device columns are zeroed first.
+void Engine::upload_family(DevBuf& dst, const void* src, size_t elem, int cols) {
+  const size_t bytes = (size_t)cols * ln_pad * elem;
+  dst.ensure(std::max<size_t>(bytes, 256));
+  CUDA_OK(cudaMemsetAsync(dst.d, 0, bytes, stream));
+  if (ln > 0)
+    CUDA_OK(cudaMemcpy2DAsync(dst.d, (size_t)ln_pad * elem, (const char*)src + (size_t)lbase * elem, (size_t)n_pad * elem,
+                              (size_t)ln * elem, cols, cudaMemcpyHostToDevice, stream));
+  stats.h2d_bytes += (size_t)cols * ln * elem;
 }
 
 void Engine::upload_all() {
-  b_i64.ensure(h_i64.size() * 8);
-  b_u32.ensure(h_u32.size() * 4);
-  b_u64.ensure(h_u64.size() * 8);
-  b_dev_class.ensure(h_dev_class.size() * 2);
-  b_topo.ensure(h_topo.size() * 4);
-  CUDA_OK(cudaMemcpyAsync(b_i64.d, h_i64.data(), h_i64.size() * 8, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_u32.d, h_u32.data(), h_u32.size() * 4, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_u64.d, h_u64.data(), h_u64.size() * 8, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_dev_class.d, h_dev_class.data(), h_dev_class.size() * 2, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_topo.d, h_topo.data(), h_topo.size() * 4, cudaMemcpyHostToDevice, stream));
-  stats.h2d_bytes += h_i64.size() * 8 + h_u32.size() * 4 + h_u64.size() * 8 + h_dev_class.size() * 2 + h_topo.size() * 4;
+  plan_shard();
+  upload_family(b_i64, h_i64.data(), 8, I64_COLS);
+  upload_family(b_u32, h_u32.data(), 4, U32_COLS);
+  upload_family(b_u64, h_u64.data(), 8, u64_cols());
+  upload_family(b_dev_class, h_dev_class.data(), (size_t)KSB_MAX_DEV * 2, KSB_MAX_RES);
+  upload_family(b_topo, h_topo.data(), 4, KSB_MAX_TOPO);
   spread_cap_cols = 0;  // force the spread block to be re-uploaded below
   full_upload = false;
   dirty_rows.clear();
@@ -557,40 +589,41 @@ void Engine::upload_all() {
   dirty_topo_cols.clear();
 }
 
+void Engine::upload_column(void* dev_base, const void* host_col, size_t elem, int dev_col) {
+  if (ln <= 0) return;
+  CUDA_OK(cudaMemcpyAsync((char*)dev_base + (size_t)dev_col * ln_pad * elem, (const char*)host_col + (size_t)lbase * elem,
+                          (size_t)ln * elem, cudaMemcpyHostToDevice, stream));
+  stats.h2d_bytes += (size_t)ln * elem;
+}
+
 void Engine::upload_dirty() {
   if (dirty_rows.size() > 64) {
     upload_all();
     return;
   }
-  for (int w : dirty_label_words) {
-    CUDA_OK(cudaMemcpyAsync((uint64_t*)b_u64.d + (size_t)w * n_pad, &h_u64[(size_t)w * n_pad], (size_t)n_pad * 8,
-                            cudaMemcpyHostToDevice, stream));
-    stats.h2d_bytes += (size_t)n_pad * 8;
-  }
+  for (int w : dirty_label_words) upload_column(b_u64.d, &h_u64[(size_t)w * n_pad], 8, w);
   dirty_label_words.clear();
-  for (int k : dirty_topo_cols) {
-    CUDA_OK(cudaMemcpyAsync((uint32_t*)b_topo.d + (size_t)k * n_pad, &h_topo[(size_t)k * n_pad], (size_t)n_pad * 4,
-                            cudaMemcpyHostToDevice, stream));
-    stats.h2d_bytes += (size_t)n_pad * 4;
-  }
+  for (int k : dirty_topo_cols) upload_column(b_topo.d, &h_topo[(size_t)k * n_pad], 4, k);
   dirty_topo_cols.clear();
-  for (int r : dirty_rows) {  // rare path (node update, pod removal): one element per column
+  for (int gr : dirty_rows) {  // rare path (node update, pod removal): one element per column
+    const int r = gr - lbase;
+    if (r < 0 || r >= ln) continue;  // another shard's row
+    const size_t np = ln_pad;
     for (int c = 0; c < I64_COLS; ++c)
-      CUDA_OK(cudaMemcpyAsync((int64_t*)b_i64.d + (size_t)c * n_pad + r, &i64(c, r), 8, cudaMemcpyHostToDevice, stream));
+      CUDA_OK(cudaMemcpyAsync((int64_t*)b_i64.d + (size_t)c * np + r, &i64(c, gr), 8, cudaMemcpyHostToDevice, stream));
     for (int c = 0; c < U32_COLS; ++c)
-      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_u32.d + (size_t)c * n_pad + r, &u32(c, r), 4, cudaMemcpyHostToDevice, stream));
+      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_u32.d + (size_t)c * np + r, &u32(c, gr), 4, cudaMemcpyHostToDevice, stream));
     for (int c = 0; c < u64_cols(); ++c)
-      CUDA_OK(cudaMemcpyAsync((uint64_t*)b_u64.d + (size_t)c * n_pad + r, &u64(c, r), 8, cudaMemcpyHostToDevice, stream));
-    for (int rs = 0; rs < KSB_MAX_RES; ++rs) {
-      size_t off = ((size_t)rs * n_pad + r) * KSB_MAX_DEV;
-      CUDA_OK(cudaMemcpyAsync((uint16_t*)b_dev_class.d + off, &h_dev_class[off], KSB_MAX_DEV * 2, cudaMemcpyHostToDevice,
+      CUDA_OK(cudaMemcpyAsync((uint64_t*)b_u64.d + (size_t)c * np + r, &u64(c, gr), 8, cudaMemcpyHostToDevice, stream));
+    for (int rs = 0; rs < KSB_MAX_RES; ++rs)
+      CUDA_OK(cudaMemcpyAsync((uint16_t*)b_dev_class.d + ((size_t)rs * np + r) * KSB_MAX_DEV,
+                              &h_dev_class[((size_t)rs * n_pad + gr) * KSB_MAX_DEV], KSB_MAX_DEV * 2, cudaMemcpyHostToDevice,
                               stream));
-    }
     for (int k = 0; k < KSB_MAX_TOPO; ++k)
-      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_topo.d + (size_t)k * n_pad + r, &h_topo[(size_t)k * n_pad + r], 4,
+      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_topo.d + (size_t)k * np + r, &h_topo[(size_t)k * n_pad + gr], 4,
                               cudaMemcpyHostToDevice, stream));
     for (size_t c = 0; c < h_spread.size() && c < spread_cap_cols; ++c)
-      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_spread.d + c * n_pad + r, &h_spread[c][r], 4, cudaMemcpyHostToDevice, stream));
+      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_spread.d + c * np + r, &h_spread[c][gr], 4, cudaMemcpyHostToDevice, stream));
     stats.h2d_bytes += 8 * I64_COLS + 4 * U32_COLS + 8 * u64_cols() + KSB_MAX_RES * KSB_MAX_DEV * 2;
   }
   dirty_rows.clear();
@@ -600,28 +633,27 @@ void Engine::sync_device() {
   if (layout_dirty) rebuild_layout();
   if (full_upload) upload_all();
   else upload_dirty();
-  // spread columns: capacity grows geometrically; new columns are uploaded individually
+  // spread columns: capacity grows geometrically (fixed when the shard's buffers are shared with peers);
+  // new columns are uploaded individually
   if (h_spread.size() > spread_cap_cols || b_spread.d == nullptr) {
-    size_t cap = std::max<size_t>(16, h_spread.size() * 2);
-    b_spread.ensure(cap * n_pad * 4);
-    for (size_t c = 0; c < h_spread.size(); ++c)
-      CUDA_OK(cudaMemcpyAsync((uint32_t*)b_spread.d + c * n_pad, h_spread[c].data(), (size_t)n_pad * 4,
-                              cudaMemcpyHostToDevice, stream));
-    stats.h2d_bytes += h_spread.size() * n_pad * 4;
+    size_t cap = std::max<size_t>(std::max<size_t>(16, min_spread_cols), h_spread.size() * 2);
+    if (shard_connected && cap * ln_pad * 4 > b_spread.cap)
+      throw std::runtime_error("sharded engine: more SelectorSpread classes than the shared buffers were sized for");
+    b_spread.ensure(cap * ln_pad * 4);
+    CUDA_OK(cudaMemsetAsync(b_spread.d, 0, cap * ln_pad * 4, stream));
+    for (size_t c = 0; c < h_spread.size(); ++c) upload_column(b_spread.d, h_spread[c].data(), 4, (int)c);
     spread_cap_cols = cap;
     dirty_spread_cols.clear();
   }
-  for (int c : dirty_spread_cols) {
-    CUDA_OK(cudaMemcpyAsync((uint32_t*)b_spread.d + (size_t)c * n_pad, h_spread[c].data(), (size_t)n_pad * 4,
-                            cudaMemcpyHostToDevice, stream));
-    stats.h2d_bytes += (size_t)n_pad * 4;
-  }
+  for (int c : dirty_spread_cols) upload_column(b_spread.d, h_spread[c].data(), 4, c);
   dirty_spread_cols.clear();
   if (arena_dirty) {
     layout_arena();
     std::vector<int32_t> arena(std::max<uint32_t>(arena_words, 1), 0);
     for (auto& t : tables) std::copy(t.vals.begin(), t.vals.end(), arena.begin() + t.off);
-    b_tables.ensure(arena.size() * 4);
+    if (shard_connected && arena.size() * 4 > b_tables.cap)
+      throw std::runtime_error("sharded engine: affinity tables outgrew the shared buffer");
+    b_tables.ensure(std::max<size_t>(arena.size() * 4, min_table_bytes));
     CUDA_OK(cudaMemcpyAsync(b_tables.d, arena.data(), arena.size() * 4, cudaMemcpyHostToDevice, stream));
     CUDA_OK(cudaStreamSynchronize(stream));  // `arena` is a local
     stats.h2d_bytes += arena.size() * 4;

@@ -352,25 +352,56 @@ __device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
   return v;
 }
 
-// Grid-wide barrier on a monotonically increasing counter (cooperative launch guarantees that
-// all blocks are co-resident). A bounded spin turns a lost block into an error, not a hang.
-__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch) {
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Spin until *p (read with `sys`) reaches `target`; a bounded wait turns a lost participant into an error.
+template <bool SYS>
+__device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, uint32_t target) {
+  uint32_t spins = 0;
+  long long t0 = 0;
+  while ((int32_t)((SYS ? ld_acquire_sys(p) : ld_acquire(p)) - target) < 0) {
+    if ((++spins & 1023u) == 0) {
+      long long now = clock64();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 6000000000ll || ld_acquire((const uint32_t*)A.error_flag) != 0) {  // ~3 s
+        atomicExch(A.error_flag, 1);
+        break;
+      }
+    }
+  }
+}
+
+// Barrier over every block of every GPU holding a shard. Locally: a monotonically increasing arrival
+// counter (cooperative launch guarantees co-residency). Across GPUs: block 0 of each rank, once its own
+// grid has arrived, bumps a counter in rank 0's memory over NVLink and waits for all ranks, then releases
+// its grid. With one rank it is a plain grid barrier.
+__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch) {
   __syncthreads();
   if (threadIdx.x == 0) {
     epoch += gridDim.x;
-    __threadfence();
-    atomicAdd(A.barrier, 1u);
-    uint32_t spins = 0;
-    long long t0 = 0;
-    while ((int32_t)(ld_acquire(A.barrier) - epoch) < 0) {
-      if ((++spins & 1023u) == 0) {
-        long long now = clock64();
-        if (t0 == 0) t0 = now;
-        if (now - t0 > 6000000000ll || ld_acquire((const uint32_t*)A.error_flag) != 0) {  // ~3 s
-          atomicExch(A.error_flag, 1);
-          break;
-        }
+    if (A.n_ranks == 1) {
+      __threadfence();
+      atomicAdd(A.barrier, 1u);
+      spin_until<false>(A, A.barrier, epoch);
+    } else {
+      __threadfence_system();
+      atomicAdd(A.barrier, 1u);
+      if (blockIdx.x == 0) {
+        spin_until<false>(A, A.barrier, epoch);
+        xepoch += (uint32_t)A.n_ranks;
+        __threadfence_system();
+        atomicAdd_system(A.xbar, 1u);
+        spin_until<true>(A, A.xbar, xepoch);
+        __threadfence_system();
+        atomicExch(A.release, epoch);
+      } else {
+        spin_until<false>(A, A.release, epoch);
       }
+      __threadfence_system();
     }
   }
   __syncthreads();
@@ -705,6 +736,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const Smem S = carve(smem_raw, A.zone_stride);
   __shared__ int32_t s_gc;            // pods in the current group
   __shared__ int32_t s_consumed;      // pods of the group that were committed
+  __shared__ KsbPeer s_peers[KSB_MAX_RANKS];  // rank 0, block 0: the shard table, read once
 
   const KsbNodeTable& T = A.table;
   const int tid = threadIdx.x;
@@ -717,11 +749,31 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const int nseg = A.nseg;
   const int G = A.group_size;
   const size_t np = T.n_pad;
-  uint32_t epoch = 0;
+  uint32_t epoch = 0, xepoch = 0;
+  const bool multi = A.n_ranks > 1;
   uint64_t last_index = *A.last_node_index;  // used by warp 0 of block 0 only
   int p0 = 0;
   int gi = 0;
 
+  if (blockIdx.x == 0 && A.rank == 0) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(A.peers);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(s_peers);
+    for (int i = threadIdx.x; i < A.n_ranks * (int)(sizeof(KsbPeer) / 4); i += kThreads) dst[i] = src[i];
+    __syncthreads();
+  }
+  if (multi) {
+    // sharded: the cross-GPU counter is never reset, its epoch is carried from launch to launch; rank 0 clears
+    // the shared reduction targets itself and an opening barrier publishes that before any rank adds to them
+    xepoch = *A.xstate;
+    if (A.rank == 0 && blockIdx.x == 0) {
+      for (int i = threadIdx.x; i < 2 * kMaxG * 8; i += kThreads)
+        reinterpret_cast<int32_t*>(A.norms)[i] = ((i & 7) == 7) ? -1 : 0;
+      for (int i = threadIdx.x; i < 2 * kMaxG * A.zone_stride; i += kThreads) A.zone_sum[i] = 0;
+      for (int i = threadIdx.x; i < 2 * kMaxG * KSB_REASON_BITS; i += kThreads) A.ghist[i] = 0;
+      if (threadIdx.x < 2) A.group_done[threadIdx.x] = 0;
+    }
+    grid_barrier(A, epoch, xepoch);
+  }
   long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long tmark = clock64();
 #define KSB_TICK(i)                      \
@@ -850,24 +902,34 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           else v = max(v, x);
         }
         int32_t* dst = reinterpret_cast<int32_t*>(norms + g) + f;
-        if (f == 0) { if (v) atomicAdd(dst, v); }
-        else if (f == 5) { if (v) atomicMin(dst, v); }
-        else if (f == 7) { if (v >= 0) atomicMax(dst, v); }
-        else { if (v) atomicMax(dst, v); }
+        if (multi) {  // the reduction targets live in rank 0's memory: NVLink atomics
+          if (f == 0) { if (v) atomicAdd_system(dst, v); }
+          else if (f == 5) { if (v) atomicMin_system(dst, v); }
+          else if (f == 7) { if (v >= 0) atomicMax_system(dst, v); }
+          else { if (v) atomicMax_system(dst, v); }
+        } else {
+          if (f == 0) { if (v) atomicAdd(dst, v); }
+          else if (f == 5) { if (v) atomicMin(dst, v); }
+          else if (f == 7) { if (v >= 0) atomicMax(dst, v); }
+          else { if (v) atomicMax(dst, v); }
+        }
       }
       for (int i = tid; i < Gc * zs; i += kThreads) {
         int z = i % zs;
-        if (z < nz && S.zone[i]) atomicAdd(&zsum[i], S.zone[i]);
+        if (z < nz && S.zone[i]) {
+          if (multi) atomicAdd_system(&zsum[i], S.zone[i]);
+          else atomicAdd(&zsum[i], S.zone[i]);
+        }
       }
     }
     KSB_TICK(1);
-    grid_barrier(A, epoch);
+    grid_barrier(A, epoch, xepoch);
     KSB_TICK(2);
 
     // ---- phase 2: Reduce + weighted sum; per-segment (max, tie count) of every pod
     for (int i = tid; i < Gc * 8; i += kThreads)
-      reinterpret_cast<int32_t*>(S.norm)[i] = __ldcg(reinterpret_cast<const int32_t*>(norms) + i);
-    for (int i = tid; i < Gc * zs; i += kThreads) S.zone[i] = (i % zs) < nz ? __ldcg(zsum + i) : 0;
+      reinterpret_cast<int32_t*>(S.norm)[i] = __ldcv(reinterpret_cast<const int32_t*>(norms) + i);
+    for (int i = tid; i < Gc * zs; i += kThreads) S.zone[i] = (i % zs) < nz ? __ldcv(zsum + i) : 0;
     __syncthreads();
     if (tid < Gc) {
       int32_t mz = 0;
@@ -896,7 +958,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               const int c = __popc(__ballot_sync(0xffffffffu, (m >> bit) & 1u));
               if (lane == bit) acc = c;
             }
-            if (acc) atomicAdd(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane, acc);
+            if (acc) {
+              int32_t* gp = A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane;
+              if (multi) atomicAdd_system(gp, acc);
+              else atomicAdd(gp, acc);
+            }
           }
           if (!prio) continue;  // uniform per (block, g)
           int32_t s = INT32_MIN;
@@ -939,19 +1005,26 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
     }
     KSB_TICK(3);
-    grid_barrier(A, epoch);
+    grid_barrier(A, epoch, xepoch);
     KSB_TICK(4);
 
-    // ---- phase 3: block 0 commits the group's pods in order
-    if (b == 0) {
+    // ---- phase 3: block 0 of rank 0 commits the group's pods in order. Rows of other shards are reached
+    //      through the peer table (NVLink P2P loads/stores); with one rank every peer access is local.
+    if (b == 0 && A.rank == 0) {
+      const int nsegT = A.nseg_total;
+      const int sps = A.segs_per_shard;
+      const int R = A.n_ranks;
       // prefetch the segment statistics of every pod that will be ranked by score
       for (int g = 0; g < Gc; ++g) {
         const KsbPodHeader* h = S.hdr + g;
         const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[g].fit_count >= 2;
         if (!prio) continue;
-        for (int i = tid; i < nseg; i += kThreads) {
-          S.seg_max[g * nseg + i] = __ldcg(A.seg_max + (size_t)g * nseg + i);
-          S.seg_cnt[g * nseg + i] = __ldcg(A.seg_cnt + (size_t)g * nseg + i);
+        for (int i = tid; i < nsegT; i += kThreads) {
+          const int q = i / sps;
+          const KsbPeer& P = s_peers[q];
+          const int ls = i - q * sps;
+          S.seg_max[g * nsegT + i] = __ldcv(P.seg_max + (size_t)g * P.nseg + ls);
+          S.seg_cnt[g * nsegT + i] = __ldcv(P.seg_cnt + (size_t)g * P.nseg + ls);
         }
       }
       __syncthreads();
@@ -963,7 +1036,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     t3[i] += now_ - m3;                \
     m3 = now_;                         \
   } while (0)
-      KSB_T3(0);  // prefetch + sync
+      KSB_T3(0);
       if (warp == 0) {
         int ncr = 0;       // rows in the cache (uniform across the warp)
         int consumed = 0;
@@ -981,23 +1054,27 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           res.score = 0;
 #pragma unroll
           for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = 0;
-          int chosen = -1;  // local row
+          int chosen = -1, chosen_rank = 0;  // local row on shard chosen_rank
           if (sched_err) {
             res.status = 3;
           } else {
             // (1) this pod on the rows changed earlier in the group, from the row cache
             uint32_t old_reasons = 0, new_reasons = 0;
             int32_t cnew = INT32_MIN, cold = INT32_MIN;
-            int crow = -1;
+            int crow = -1, crank = 0, cseg = -1;  // local row, shard, global segment
             bool flip = false;
             if (lane < ncr) {
               const RowCache& c = S.rows[lane];
               crow = c.row;
-              const int4 raw0 = __ldcg(A.raw + (size_t)g * np + crow);
-              old_reasons = __ldcg(A.reasons + (size_t)g * np + crow);
-              if (prio) cold = __ldcg(A.score + (size_t)g * np + crow);
+              crank = c.pad;
+              const KsbPeer& P = s_peers[crank];
+              cseg = P.seg_base + crow / kSeg;
+              const size_t pn = P.table.n_pad;
+              const int4 raw0 = __ldcv(P.raw + (size_t)g * pn + crow);
+              old_reasons = __ldcv(P.reasons + (size_t)g * pn + crow);
+              if (prio) cold = __ldcv(P.score + (size_t)g * pn + crow);
               int32_t base;
-              eval_cached(T, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr);
+              eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr);
               const bool was_fit = raw0.x != INT32_MIN;
               flip = was_fit && new_reasons != 0;  // a fit row turned unfit: the Reduce inputs may have moved
               if (prio && was_fit && new_reasons == 0)
@@ -1013,8 +1090,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (nm.fit_count >= 2 && (h->flags & PF_PRIO_ERROR)) {
               res.status = 3;
             } else if (nm.fit_count == 0) {
-              // FitError (generic_scheduler.go:133-139): histogram built after the loop by all warps; here only
-              // the correction for rows whose reasons changed since the group started
+              // FitError (generic_scheduler.go:133-139): the histogram over all rows was built in phase 2; here
+              // only the correction for rows whose reasons changed since the group started
               res.status = 2;
               int slotv = 0;
               if (lane == 0) slotv = atomicAdd(A.fiterr_count, 1);
@@ -1022,7 +1099,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               if (slotv < KSB_MAX_FITERR) {
                 S.fe_hist[lane] = 0;
                 __syncwarp();
-                if (lane < ncr) {  // rows whose reasons changed since the group started
+                if (lane < ncr) {
                   uint32_t m = old_reasons;
                   while (m) {
                     int bit = __ffs(m) - 1;
@@ -1038,34 +1115,35 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 }
                 __syncwarp();
                 A.fiterr_hist[(size_t)slotv * KSB_REASON_BITS + lane] =
-                    __ldcg(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
+                    __ldcv(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
                 res.fiterr_slot = slotv;
               }
               __syncwarp();
             } else if (nm.fit_count == 1) {
-              chosen = nm.one_row - T.row_base;  // generic_scheduler.go:144-146: no selectHost, counter untouched
+              // generic_scheduler.go:144-146: no selectHost, counter untouched
+              chosen_rank = min(R - 1, (nm.one_row / kSeg) / sps);
+              chosen = nm.one_row - s_peers[chosen_rank].table.row_base;
             } else {
               // (2) selectHost over group-start segment statistics patched with the changed rows
-              int32_t* smax = S.seg_max + g * nseg;
-              int32_t* scnt = S.seg_cnt + g * nseg;
+              int32_t* smax = S.seg_max + g * nsegT;
+              int32_t* scnt = S.seg_cnt + g * nsegT;
               int32_t m = cnew;
-              for (int i = lane; i < nseg; i += 32) m = max(m, smax[i]);
+              for (int i = lane; i < nsegT; i += 32) m = max(m, smax[i]);
               const int32_t gmax = warp_max(m);
-              for (int i = lane; i < nseg; i += 32) scnt[i] = (smax[i] == gmax) ? scnt[i] : 0;
+              for (int i = lane; i < nsegT; i += 32) scnt[i] = (smax[i] == gmax) ? scnt[i] : 0;
               __syncwarp();
               if (lane < ncr) {
-                const int sg = crow / kSeg;
-                if (cold == gmax) atomicAdd(&scnt[sg], -1);
-                if (cnew == gmax) atomicAdd(&scnt[sg], 1);
+                if (cold == gmax) atomicAdd(&scnt[cseg], -1);
+                if (cnew == gmax) atomicAdd(&scnt[cseg], 1);
               }
               __syncwarp();
               int32_t c = 0;
-              for (int i = lane; i < nseg; i += 32) c += scnt[i];
+              for (int i = lane; i < nsegT; i += 32) c += scnt[i];
               const int32_t k = warp_sum(c);
               if (k <= 0) break;  // every holder of the group-start maximum changed and fell below it
               int rem = (int)(last_index % (uint64_t)k);
               int found = -1;
-              for (int hi = nseg; hi > 0 && found < 0; hi -= 32) {
+              for (int hi = nsegT; hi > 0 && found < 0; hi -= 32) {
                 const int sg = hi - 1 - lane;  // lane 0 = highest segment
                 const int cnt = sg >= 0 ? scnt[sg] : 0;
                 int incl = cnt;
@@ -1085,22 +1163,27 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   rem -= total;
                 }
               }
-              int pick = -1;
+              int pick = -1, pick_rank = 0;
               if (found >= 0) {
                 // rank-select inside the segment, rows from the highest down: 8 rows per lane
-                const int base_row = found * kSeg;
+                pick_rank = found / sps;
+                const KsbPeer& P = s_peers[pick_rank];
+                const int base_row = (found - P.seg_base) * kSeg;
+                const size_t pn = P.table.n_pad;
                 int32_t v[kSeg / 32];
 #pragma unroll
                 for (int j = 0; j < kSeg / 32; ++j) {
                   const int r = base_row + j * 32 + lane;
-                  v[j] = r < T.n ? __ldcg(A.score + (size_t)g * np + r) : INT32_MIN;
+                  v[j] = r < P.table.n ? __ldcv(P.score + (size_t)g * pn + r) : INT32_MIN;
                 }
                 for (int i = 0; i < ncr; ++i) {  // fresh scores override the stash on changed rows
+                  const int cs = __shfl_sync(0xffffffffu, cseg, i);
+                  if (cs != found) continue;
                   const int cr = __shfl_sync(0xffffffffu, crow, i);
                   const int32_t cn = __shfl_sync(0xffffffffu, cnew, i);
                   const int32_t co = __shfl_sync(0xffffffffu, cold, i);
                   const int rel = cr - base_row;
-                  if (rel >= 0 && rel < kSeg && (rel & 31) == lane && !(cn == INT32_MIN && co == INT32_MIN)) {
+                  if ((rel & 31) == lane && !(cn == INT32_MIN && co == INT32_MIN)) {
 #pragma unroll
                     for (int j = 0; j < kSeg / 32; ++j)
                       if (j == (rel >> 5)) v[j] = cn;
@@ -1124,6 +1207,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
               if (pick >= 0) {
                 chosen = pick;
+                chosen_rank = pick_rank;
                 res.score = gmax;
               } else {
                 res.status = 3;  // only reachable after a barrier timeout
@@ -1134,52 +1218,75 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           KSB_T3(2);  // select
           // (3) the assume step on the chosen row
           if (chosen >= 0) {
+            const KsbPeer& P = s_peers[chosen_rank];
             uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
             if (A.commit) {
               int idx = -1;
               {
-                const bool mine = lane < ncr && S.rows[lane].row == chosen;
+                const bool mine = lane < ncr && S.rows[lane].row == chosen && S.rows[lane].pad == chosen_rank;
                 const uint32_t bal = __ballot_sync(0xffffffffu, mine);
                 if (bal) idx = __ffs(bal) - 1;
               }
-              const bool fast = counters_fast(h);
+              const bool fast = R == 1 && counters_fast(h);
               CounterLoads cl;
-              if (fast) cl = counters_load(T, chosen, pv, lane);  // in flight together with the cache fill
+              if (fast) cl = counters_load(P.table, chosen, pv, lane);  // in flight together with the cache fill
               if (idx < 0) {
                 idx = ncr;
-                cache_fill(T, chosen, S.rows + idx, lane);
+                cache_fill(P.table, chosen, S.rows + idx, lane);
+                if (lane == 31) S.rows[idx].pad = chosen_rank;
                 ncr += 1;
                 __syncwarp();
               }
               if (h->n_ext) {
                 if (lane == 0) {
-                  uint32_t rs_, base_;
-                  eval_cached(T, S.rows[idx], pv, 0u, &rs_, (int32_t*)&base_, picks);
+                  uint32_t rs_;
+                  int32_t base_;
+                  eval_cached(P.table, S.rows[idx], pv, 0u, &rs_, &base_, picks);
                 }
 #pragma unroll
                 for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
               }
-              commit_cached(T, S.rows + idx, pv, picks, lane);
-              if (fast) counters_store(T, chosen, pv, cl, lane);
-              else counters_slow(T, chosen, pv, lane);
+              commit_cached(P.table, S.rows + idx, pv, picks, lane);
+              if (fast) {
+                counters_store(P.table, chosen, pv, cl, lane);
+              } else {
+                // SelectorSpread columns are sharded with the rows; affinity tables are replicated on every rank
+                const size_t pn = P.table.n_pad;
+                for (int i = lane; i < h->n_spread_inc; i += 32) {
+                  uint32_t* pp = P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen;
+                  *pp = __ldcv(pp) + 1u;
+                }
+                for (int i = lane; i < h->n_commit; i += 32) {
+                  const uint64_t cm = pv.commits[2 * i];
+                  const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
+                  const uint32_t off = (uint32_t)cm;
+                  const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
+                  for (int q = 0; q < R; ++q) {
+                    int32_t* tb = s_peers[q].table.tables;
+                    if (d) tb[off + d] = __ldcv(tb + off + d) + delta;
+                    if ((cm >> 40) & 1ull) tb[off] = __ldcv(tb + off) + delta;
+                  }
+                }
+              }
               __syncwarp();
             } else if (h->n_ext) {
               if (lane == 0) {
                 EvalOut o;
-                eval_node<true>(T, chosen, pv, o, picks);
+                eval_node<true>(P.table, chosen, pv, o, picks);
               }
 #pragma unroll
               for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
             }
-            res.row = T.row_base + chosen;
+            res.row = P.table.row_base + chosen;
 #pragma unroll
             for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
           }
-          if (lane == 0) A.results[p0 + g] = res;
+          if (lane < R) s_peers[lane].results[p0 + g] = res;  // every rank keeps a copy of the results
           consumed = g + 1;
           KSB_T3(3);  // commit + result
         }
         if (lane == 0) s_consumed = consumed;
+        if (lane < R) *s_peers[lane].last_node_index = last_index;  // every rank's host reads its own copy
       }
       __syncthreads();
       KSB_T3(4);
@@ -1195,15 +1302,15 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       for (int i = tid; i < kMaxG * zs; i += kThreads) zn[i] = 0;
       int32_t* gh = A.ghist + (size_t)(slot ^ 1) * kMaxG * KSB_REASON_BITS;
       for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
-      KSB_T3(5);  // deferred FitError histograms + resets
+      KSB_T3(5);
       if (tid == 0)
         for (int i = 0; i < 6; ++i) A.counters[9 + i] += (uint64_t)t3[i];
 #undef KSB_T3
     }
     KSB_TICK(5);
-    grid_barrier(A, epoch);
+    grid_barrier(A, epoch, xepoch);
     KSB_TICK(6);
-    const int adv = __ldcg(A.group_done + slot);
+    const int adv = __ldcv(A.group_done + slot);
     if (adv <= 0 || __ldcg(A.error_flag) != 0) {  // only after a barrier timeout: stop instead of spinning
       if (tid == 0) atomicExch(A.error_flag, 1);
       break;
@@ -1212,7 +1319,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     gi += 1;
   }
   if (b == 0 && tid == 0) {
-    *A.last_node_index = last_index;
+    if (multi) *A.xstate = xepoch;
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)tk[i];  // block 0's cycles per stage
   }
 #undef KSB_TICK
@@ -1302,7 +1409,11 @@ constexpr size_t kNaFitCount = kNaError + 256;
 constexpr size_t kNaLastIndex = kNaFitCount + 256;
 constexpr size_t kNaGroupDone = kNaLastIndex + 256;
 constexpr size_t kNaCounters = kNaGroupDone + 256;
-constexpr size_t kNaGhist = kNaCounters + 256;  // counters: 15 x 8 bytes
+constexpr size_t kNaRelease = kNaCounters + 256;  // counters: 15 x 8 bytes
+constexpr size_t kNaXbar = kNaRelease + 256;
+constexpr size_t kNaXstate = kNaXbar + 256;
+constexpr size_t kNaPeer = kNaXstate + 256;
+constexpr size_t kNaGhist = kNaPeer + na_align(sizeof(KsbPeer));
 constexpr size_t kNaFitHist = kNaGhist + na_align(2 * (size_t)kMaxG * KSB_REASON_BITS * 4);
 constexpr size_t kNaTotal = kNaFitHist + na_align((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
 }  // namespace
@@ -1354,6 +1465,10 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->group_done = (int32_t*)(b + kNaGroupDone);
   a->counters = (uint64_t*)(b + kNaCounters);
   a->ghist = (int32_t*)(b + kNaGhist);
+  a->release = (uint32_t*)(b + kNaRelease);
+  a->xbar = (uint32_t*)(b + kNaXbar);
+  a->xstate = (uint32_t*)(b + kNaXstate);
+  a->peers = (const KsbPeer*)(b + kNaPeer);
   a->fiterr_hist = (int32_t*)(b + kNaFitHist);
   return 0;
 }

@@ -6,6 +6,21 @@
 
 #include "device_types.h"
 
+// One shard of the node table as seen from the GPU that runs phase 3 (rank 0). For rank 0 itself these are
+// its own buffers; for the other ranks they are CUDA-IPC mappings of the peer's buffers (NVLink P2P).
+struct KsbPeer {
+  KsbNodeTable table;
+  int4* raw;
+  int32_t* score;
+  uint32_t* reasons;
+  int32_t* seg_max;
+  int32_t* seg_cnt;
+  KsbResult* results;
+  uint64_t* last_node_index;
+  int32_t nseg;      // 256-row segments of this shard
+  int32_t seg_base;  // its first segment in the global numbering
+};
+
 struct KsbBatchArgs {
   KsbNodeTable table;
   const KsbPodHeader* headers;  // [n_pods]
@@ -34,6 +49,15 @@ struct KsbBatchArgs {
   int32_t* group_done;          // [2] pods consumed by the group, ping-pong
   uint64_t* counters;           // [16] groups run, groups cut short by a dropped speculation, stage cycles
   int32_t* ghist;               // [2][KSB_MAX_GROUP][KSB_REASON_BITS] reason histograms of no-fit pods, ping-pong
+  // sharding (n_ranks == 1: everything local). With n_ranks > 1 the reduction targets above (norms, zone_sum,
+  // ghist, group_done) and xbar point into rank 0's memory on every rank.
+  const KsbPeer* peers;         // [n_ranks], dereferenced by rank 0 only
+  uint32_t* xbar;               // cross-GPU barrier counter in rank 0's memory
+  uint32_t* release;            // local: epoch up to which this GPU's blocks may proceed
+  uint32_t* xstate;             // local: cross-GPU barrier epoch carried from launch to launch (xbar is never reset)
+  int32_t n_ranks, rank;
+  int32_t segs_per_shard;       // segments per shard (the last shard may hold fewer)
+  int32_t nseg_total;           // segments over all shards
 };
 
 extern "C" {

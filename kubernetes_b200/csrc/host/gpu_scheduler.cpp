@@ -48,13 +48,15 @@ void load_cluster(EngineHandle& h, const Session& s) {
   for (auto& b : s.existing_bufs) h.check(ksb_pod_add(h.get(), (const uint8_t*)b.data(), b.size()), "pod_add");
 }
 
-std::string run(Session& s, const json::Value& opt) {
+ksb_config config_from(const json::Value& opt) {
   ksb_config cfg;
   ksb_config_default(&cfg);
   cfg.device = (int32_t)opt.get_int("device", 0);
   cfg.label_words = (int32_t)opt.get_int("label_words", 4);
   cfg.hard_pod_affinity_weight = (int32_t)opt.get_int("hardPodAffinityWeight", 1);
   cfg.group_size = (int32_t)opt.get_int("group_size", 0);
+  cfg.shard_rank = (int32_t)opt.get_int("shard_rank", 0);
+  cfg.shard_count = (int32_t)opt.get_int("shard_count", 1);
   if (const json::Value* w = opt.find("weights"); w && !w->is_null()) {
     cfg.w_least_requested = (int32_t)w->get_int("LeastRequestedPriority", 1);
     cfg.w_balanced = (int32_t)w->get_int("BalancedResourceAllocation", 1);
@@ -64,18 +66,28 @@ std::string run(Session& s, const json::Value& opt) {
     cfg.w_inter_pod_affinity = (int32_t)w->get_int("InterPodAffinityPriority", 1);
     cfg.w_prefer_avoid = (int32_t)w->get_int("NodePreferAvoidPodsPriority", 10000);
   }
+  return cfg;
+}
+
+std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double load_ms);
+
+std::string run(Session& s, const json::Value& opt) {
+  ksb_config cfg = config_from(opt);
+  EngineHandle h(cfg);
+  ksb_set_last_node_index(h.get(), (uint64_t)opt.get_int("lastNodeIndex", 0));
+  auto tl0 = std::chrono::steady_clock::now();
+  load_cluster(h, s);
+  auto tl1 = std::chrono::steady_clock::now();
+  return run_on(h, s, opt, std::chrono::duration<double, std::milli>(tl1 - tl0).count());
+}
+
+std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double load_ms) {
   const int64_t batch = opt.get_int("batch", -1);  // -1: whole stream in one call; 0: Schedule + AssumePod per pod
   int64_t limit = opt.get_int("limit", -1);
   const bool want_results = opt.get_bool("results", true);
   const int replay_iters = (int)opt.get_int("replay_iters", 0);
   size_t np = s.cluster.pods.size();
   if (limit >= 0 && (size_t)limit < np) np = (size_t)limit;
-
-  EngineHandle h(cfg);
-  ksb_set_last_node_index(h.get(), (uint64_t)opt.get_int("lastNodeIndex", 0));
-  auto tl0 = std::chrono::steady_clock::now();
-  load_cluster(h, s);
-  auto tl1 = std::chrono::steady_clock::now();
 
   std::vector<ksb_result> results(np);
   std::vector<std::string> hosts(np), messages(np);
@@ -169,7 +181,7 @@ std::string run(Session& s, const json::Value& opt) {
   out += ",\"fit_errors\":" + std::to_string(fit_errors);
   out += ",\"errors\":" + std::to_string(errors);
   out += ",\"placement_hash\":\"" + std::to_string(hash) + "\"";
-  out += ",\"load_ms\":" + std::to_string(std::chrono::duration<double, std::milli>(tl1 - tl0).count());
+  out += ",\"load_ms\":" + std::to_string(load_ms);
   out += ",\"e2e_ms\":" + std::to_string(std::chrono::duration<double, std::milli>(t1 - t0).count());
   out += ",\"kernel_ms\":" + std::to_string(kernel_ms);
   out += ",\"encode_ms\":" + std::to_string(encode_ms);
@@ -279,5 +291,60 @@ char* ksbh_session_run(void* session, const char* options_json) {
 }
 
 void ksbh_free(char* p) { free(p); }
+
+// ---- a loaded engine kept open across calls (sharded runs: load, exchange IPC handles, then run) ----
+
+struct OpenEngine {
+  Session* s;
+  std::unique_ptr<EngineHandle> h;
+  double load_ms;
+};
+
+void* ksbh_engine_open(void* session, const char* options_json, char** err) {
+  try {
+    json::Value opt = json::parse(options_json && *options_json ? options_json : "{}");
+    auto oe = std::make_unique<OpenEngine>();
+    oe->s = (Session*)session;
+    ksb_config cfg = config_from(opt);
+    oe->h = std::make_unique<EngineHandle>(cfg);
+    auto t0 = std::chrono::steady_clock::now();
+    load_cluster(*oe->h, *oe->s);
+    oe->load_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return oe.release();
+  } catch (const std::exception& ex) {
+    if (err) *err = dup(ex.what());
+    return nullptr;
+  }
+}
+
+int ksbh_engine_shard_export(void* oe, int max_batch_pods, uint8_t* out, size_t cap, size_t* len, char** err) {
+  OpenEngine* e = (OpenEngine*)oe;
+  if (ksb_shard_export(e->h->get(), max_batch_pods, out, cap, len) != 0) {
+    if (err) *err = dup(ksb_last_error(e->h->get()));
+    return -1;
+  }
+  return 0;
+}
+
+int ksbh_engine_shard_connect(void* oe, const uint8_t* blobs, const uint64_t* offsets, int n_ranks, char** err) {
+  OpenEngine* e = (OpenEngine*)oe;
+  if (ksb_shard_connect(e->h->get(), blobs, offsets, n_ranks) != 0) {
+    if (err) *err = dup(ksb_last_error(e->h->get()));
+    return -1;
+  }
+  return 0;
+}
+
+char* ksbh_engine_run(void* oe, const char* options_json) {
+  OpenEngine* e = (OpenEngine*)oe;
+  try {
+    json::Value opt = json::parse(options_json && *options_json ? options_json : "{}");
+    return dup(run_on(*e->h, *e->s, opt, e->load_ms));
+  } catch (const std::exception& ex) {
+    return dup(std::string("{\"error\":") + esc(ex.what()) + "}");
+  }
+}
+
+void ksbh_engine_close(void* oe) { delete (OpenEngine*)oe; }
 
 }  // extern "C"

@@ -19,6 +19,7 @@ CABI_SYMBOLS = [
     "ksb_pod_add", "ksb_pod_remove", "ksb_selector_owner_upsert", "ksb_selector_owner_remove", "ksb_schedule",
     "ksb_schedule_batch", "ksb_node_name", "ksb_device_id", "ksb_fit_error_message", "ksb_get_last_node_index",
     "ksb_set_last_node_index", "ksb_get_stats", "ksb_replay_last_batch", "ksb_replay_last_batch_noalloc",
+    "ksb_shard_export", "ksb_shard_connect",
 ]
 
 
@@ -115,6 +116,69 @@ class Session:
         if self._s:
             host().ksbh_session_destroy(self._s)
             self._s = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class OpenEngine:
+    """A loaded engine kept open across calls (needed for sharded runs: load, exchange CUDA-IPC handles
+    between the ranks, then run). Wraps the ksbh_engine_* harness entry points."""
+
+    def __init__(self, session, **options):
+        h = host()
+        h.ksbh_engine_open.restype = ctypes.c_void_p
+        h.ksbh_engine_open.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p)]
+        h.ksbh_engine_run.restype = ctypes.c_void_p
+        h.ksbh_engine_run.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+        h.ksbh_engine_close.argtypes = [ctypes.c_void_p]
+        h.ksbh_engine_shard_export.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t,
+                                               ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_void_p)]
+        h.ksbh_engine_shard_connect.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.POINTER(ctypes.c_uint64),
+                                                ctypes.c_int, ctypes.POINTER(ctypes.c_void_p)]
+        self._session = session  # keep the session alive
+        err = ctypes.c_void_p()
+        self._e = h.ksbh_engine_open(session._s, json.dumps(options).encode(), ctypes.byref(err))
+        if not self._e:
+            raise RuntimeError("ksbh_engine_open: " + (ctypes.string_at(err).decode() if err else "unknown error"))
+
+    def shard_export(self, max_batch_pods):
+        h = host()
+        buf = ctypes.create_string_buffer(4096)
+        n = ctypes.c_size_t()
+        err = ctypes.c_void_p()
+        if h.ksbh_engine_shard_export(self._e, int(max_batch_pods), buf, 4096, ctypes.byref(n), ctypes.byref(err)) != 0:
+            raise RuntimeError("ksb_shard_export: " + (ctypes.string_at(err).decode() if err else "?"))
+        return buf.raw[:n.value]
+
+    def shard_connect(self, blobs):
+        h = host()
+        offs = [0]
+        for b in blobs:
+            offs.append(offs[-1] + len(b))
+        arr = (ctypes.c_uint64 * len(offs))(*offs)
+        err = ctypes.c_void_p()
+        if h.ksbh_engine_shard_connect(self._e, b"".join(blobs), arr, len(blobs), ctypes.byref(err)) != 0:
+            raise RuntimeError("ksb_shard_connect: " + (ctypes.string_at(err).decode() if err else "?"))
+
+    def run(self, **options):
+        h = host()
+        p = h.ksbh_engine_run(self._e, json.dumps(options).encode())
+        try:
+            out = json.loads(ctypes.string_at(p).decode())
+        finally:
+            h.ksbh_free(p)
+        if "error" in out and "pods" not in out:
+            raise RuntimeError("engine: " + out["error"])
+        return out
+
+    def close(self):
+        if self._e:
+            host().ksbh_engine_close(self._e)
+            self._e = None
 
     def __del__(self):
         try:
