@@ -30,13 +30,10 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
     off += (bytes + 255) & ~(size_t)255;
     return o;
   };
+  // fixed-size control fields first: their offsets must not depend on a shard's row count, because the
+  // other ranks address them inside rank 0's buffer with a layout computed from their own geometry
   L.norms = take(2 * (size_t)KSB_MAX_GROUP * sizeof(KsbNorms));
   L.zone_sum = take(2 * (size_t)KSB_MAX_GROUP * zone_stride * 4);
-  L.raw = take((size_t)G * n_pad * 16);
-  L.score = take((size_t)G * n_pad * 4);
-  L.reasons = take((size_t)G * n_pad * 4);
-  L.seg_max = take((size_t)G * nseg * 4);
-  L.seg_cnt = take((size_t)G * nseg * 4);
   L.barrier = take(4);
   L.error_flag = take(4);
   L.fiterr_count = take(4);
@@ -49,6 +46,11 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   L.xstate = take(4);
   L.peers = take(sizeof(KsbPeer) * KSB_MAX_RANKS);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
+  L.raw = take((size_t)G * n_pad * 16);
+  L.score = take((size_t)G * n_pad * 4);
+  L.reasons = take((size_t)G * n_pad * 4);
+  L.seg_max = take((size_t)G * nseg * 4);
+  L.seg_cnt = take((size_t)G * nseg * 4);
   L.total = off;
   return L;
 }
@@ -328,7 +330,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   CUDA_OK(cudaMemcpyAsync(&flags[0], a.error_flag, 4, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaMemcpyAsync(&flags[1], a.fiterr_count, 4, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaMemcpyAsync(&last_node_index, a.last_node_index, 8, cudaMemcpyDeviceToHost, stream));
-  uint64_t counters[15] = {0};
+  uint64_t counters[16] = {0};
   CUDA_OK(cudaMemcpyAsync(counters, a.counters, sizeof counters, cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaStreamSynchronize(stream));
   float ms = 0;
@@ -339,7 +341,12 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   stats.d2h_bytes += (size_t)np * sizeof(KsbResult) + 16;
   if (flags[0] != 0) {
     layout_dirty = true;  // device state is unknown: rebuild it from the host records next time
-    throw std::runtime_error("device kernel reported a barrier timeout");
+    throw std::runtime_error("device kernel stopped with error code " + std::to_string(flags[0]) +
+                             " (1-4: barrier wait timed out, 5: a group made no progress, 6: peer error); last stage marker " +
+                             std::to_string(counters[14] >> 16) + "/" + std::to_string((counters[14] >> 8) & 0xff) + "/" +
+                             std::to_string(counters[14] & 0xff) + "; first timeout at barrier " +
+                             std::to_string(counters[15] >> 32) + " block " + std::to_string((counters[15] >> 8) & 0xffffff) +
+                             " grid " + std::to_string(grid));
   }
   int nfe = std::min(flags[1], (int32_t)KSB_MAX_FITERR);
   if (nfe > 0) {

@@ -360,7 +360,7 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 
 // Spin until *p (read with `sys`) reaches `target`; a bounded wait turns a lost participant into an error.
 template <bool SYS>
-__device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, uint32_t target) {
+__device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, uint32_t target, int code) {
   uint32_t spins = 0;
   long long t0 = 0;
   while ((int32_t)((SYS ? ld_acquire_sys(p) : ld_acquire(p)) - target) < 0) {
@@ -368,7 +368,8 @@ __device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, u
       long long now = clock64();
       if (t0 == 0) t0 = now;
       if (now - t0 > 6000000000ll || ld_acquire((const uint32_t*)A.error_flag) != 0) {  // ~3 s
-        atomicExch(A.error_flag, 1);
+        if (atomicCAS(A.error_flag, 0, code) == 0)  // first failure: remember which barrier and who
+          A.counters[15] = ((uint64_t)(target / gridDim.x) << 32) | ((uint64_t)blockIdx.x << 8) | (uint64_t)code;
         break;
       }
     }
@@ -386,20 +387,20 @@ __device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, u
     if (A.n_ranks == 1) {
       __threadfence();
       atomicAdd(A.barrier, 1u);
-      spin_until<false>(A, A.barrier, epoch);
+      spin_until<false>(A, A.barrier, epoch, 1);
     } else {
       __threadfence_system();
       atomicAdd(A.barrier, 1u);
       if (blockIdx.x == 0) {
-        spin_until<false>(A, A.barrier, epoch);
+        spin_until<false>(A, A.barrier, epoch, 2);
         xepoch += (uint32_t)A.n_ranks;
         __threadfence_system();
         atomicAdd_system(A.xbar, 1u);
-        spin_until<true>(A, A.xbar, xepoch);
+        spin_until<true>(A, A.xbar, xepoch, 3);
         __threadfence_system();
         atomicExch(A.release, epoch);
       } else {
-        spin_until<false>(A, A.release, epoch);
+        spin_until<false>(A, A.release, epoch, 4);
       }
       __threadfence_system();
     }
@@ -776,11 +777,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   }
   long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long tmark = clock64();
-#define KSB_TICK(i)                      \
-  do {                                   \
-    long long now_ = clock64();          \
-    tk[i] += now_ - tmark;               \
-    tmark = now_;                        \
+#define KSB_TICK(i)                                                                          \
+  do {                                                                                       \
+    long long now_ = clock64();                                                              \
+    tk[i] += now_ - tmark;                                                                   \
+    tmark = now_;                                                                            \
+    if (blockIdx.x == 0 && threadIdx.x == 0 && *A.error_flag == 0) A.counters[14] = ((uint64_t)gi << 16) | (i); \
   } while (0)
   while (p0 < A.n_pods) {
     const int slot = gi & 1;
@@ -1215,6 +1217,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               last_index += 1;
             }
           }
+          if (lane == 0 && *A.error_flag == 0) A.counters[14] = ((uint64_t)gi << 16) | ((uint64_t)(g + 1) << 8) | 0x80u;
           KSB_T3(2);  // select
           // (3) the assume step on the chosen row
           if (chosen >= 0) {
@@ -1312,7 +1315,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     KSB_TICK(6);
     const int adv = __ldcv(A.group_done + slot);
     if (adv <= 0 || __ldcg(A.error_flag) != 0) {  // only after a barrier timeout: stop instead of spinning
-      if (tid == 0) atomicExch(A.error_flag, 1);
+      if (tid == 0) atomicCAS(A.error_flag, 0, adv <= 0 ? 5 : 6);
       break;
     }
     p0 += adv;
