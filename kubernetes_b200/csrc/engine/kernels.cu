@@ -108,10 +108,25 @@ struct EvalOut {
 };
 
 // least_requested.go:50-61
+// ((capacity - requested) * 10) / capacity, exactly, without the 64-bit integer division routine: the
+// quotient is in [0, 10], so a double estimate corrected by at most a couple of steps is exact.
 __device__ __forceinline__ int64_t unused_score(int64_t requested, int64_t capacity) {
   if (capacity == 0) return 0;
   if (requested > capacity) return 0;
-  return ((capacity - requested) * 10) / capacity;
+  if (capacity < 0) return ((capacity - requested) * 10) / capacity;  // never for real nodes; keep Go's semantics
+  const int64_t num = (capacity - requested) * 10;
+  if (num < 0) return num / capacity;  // negative request: not in [0, 10]
+  int64_t q = (int64_t)__ddiv_rn((double)num, (double)capacity);
+  int64_t r = num - q * capacity;
+  while (r < 0) {
+    --q;
+    r += capacity;
+  }
+  while (r >= capacity) {
+    ++q;
+    r -= capacity;
+  }
+  return q;
 }
 
 // The fork's per-node device selection (core/extended_resources.go:83-150), devices visited in
@@ -673,6 +688,78 @@ __device__ __forceinline__ void counters_slow(const KsbNodeTable& T, int r, cons
   }
 }
 
+// What the decider warp hands to the writer warp for one pod: the chosen row's mutable columns after the
+// assume step (a copy of the row-cache entry) and the result record.
+struct CommitRec {
+  int64_t q[31];
+  int32_t npods;
+  uint32_t avail[KSB_MAX_RES];
+  int32_t row;   // local row on shard `rank`, -1: nothing to write
+  int32_t rank;
+  KsbResult res;
+};
+
+// Decider side of the assume step: the row-cache entry only (shared memory).
+__device__ __forceinline__ void commit_cache_only(RowCache* c, const PodView& pv, const uint32_t* picks, int lane) {
+  const KsbPodHeader* h = pv.h;
+  int64_t add = 0;
+  switch (lane) {
+    case 4: add = h->add_cpu; break;
+    case 5: add = h->add_mem; break;
+    case 6: add = h->add_agpu; break;
+    case 7: add = h->add_eph; break;
+    case 8: add = h->nz_cpu; break;
+    case 9: add = h->nz_mem; break;
+    default: break;
+  }
+  if (lane >= 14 && lane < 18) add = h->scalar_add[lane - 14];
+  if (add != 0) c->q[lane] += add;
+  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30)
+    c->q[lane] = (int64_t)((uint64_t)c->q[lane] | pv.ports[3 * KSB_PORT_WORDS + (lane - 18)]);
+  if (lane == 31) {
+    c->npods += 1;
+    if (h->n_ext) {
+      uint32_t take[KSB_MAX_RES];
+#pragma unroll
+      for (int s = 0; s < KSB_MAX_RES; ++s) take[s] = 0;
+      for (int i = 0; i < h->n_ext; ++i)
+        if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
+#pragma unroll
+      for (int s = 0; s < KSB_MAX_RES; ++s) c->avail[s] &= ~take[s];
+    }
+  }
+}
+
+// Writer side: the row's mutable columns from the record to the table (NodeInfo.AddPod, node_info.go:329-356,
+// and the bind echo of device ids, pkg/registry/core/pod/storage/storage.go:180-187).
+__device__ __forceinline__ void write_through(const KsbNodeTable& T, const CommitRec& rec, const KsbPodHeader* h, int lane) {
+  const size_t np = T.n_pad;
+  const int r = rec.row;
+  int64_t* dst = nullptr;
+  switch (lane) {
+    case 4: dst = T.req_cpu + r; break;
+    case 5: dst = T.req_mem + r; break;
+    case 6: dst = T.req_agpu + r; break;
+    case 7: dst = T.req_eph + r; break;
+    case 8: dst = T.nz_cpu + r; break;
+    case 9: dst = T.nz_mem + r; break;
+    default: break;
+  }
+  if (lane >= 14 && lane < 18 && h->scalar_add[lane - 14] != 0) dst = T.req_scalar + (size_t)(lane - 14) * np + r;
+  if (dst) *dst = rec.q[lane];
+  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30) {
+    const int j = lane - 18;
+    uint64_t* pd = (j < 4 ? T.port_any : (j < 8 ? T.port_wild : T.port_exact)) + (size_t)(j & 3) * np + r;
+    *pd = (uint64_t)rec.q[lane];
+  }
+  if (lane == 31) {
+    T.num_pods[r] = rec.npods;
+    if (h->n_ext)
+#pragma unroll
+      for (int s = 0; s < KSB_MAX_RES; ++s) T.dev_avail[(size_t)s * np + r] = rec.avail[s];
+  }
+}
+
 // dynamic shared memory carve-up
 struct Smem {
   KsbPodHeader* hdr;   // [kMaxG]
@@ -687,6 +774,7 @@ struct Smem {
   int32_t* seg_cnt;    // [kSegCache]
   RowCache* rows;      // [kMaxG] block 0: rows changed in this group
   int32_t* fe_hist;    // [KSB_REASON_BITS] block 0: FitError histogram correction for changed rows
+  CommitRec* recs;     // [kMaxG] block 0: decider -> writer hand-off
 };
 
 __device__ __host__ __forceinline__ size_t smem_layout(size_t* offs, int zone_stride) {
@@ -700,14 +788,15 @@ __device__ __host__ __forceinline__ size_t smem_layout(size_t* offs, int zone_st
   take((size_t)kGroupPoolWords * 8);
   take(kMaxG * 4);
   take((size_t)kMaxG * zone_stride * 4);
-  take((size_t)kMaxG * kWarps * 8 * 4);
+  take((size_t)kMaxG * kWarps * 8 * 4);   // part: phase 1/2 reduction scratch ...
+  take((size_t)kMaxG * kWarps * 2 * 4);   // wstat: ... contiguous with part; phase 3 reuses both as S.recs
   take(sizeof(KsbNorms) * kMaxG);
   take(kMaxG * 4);
-  take((size_t)kMaxG * kWarps * 2 * 4);
   take((size_t)kSegCache * 4);
   take((size_t)kSegCache * 4);
   take(sizeof(RowCache) * kMaxG);
   take((size_t)kMaxG * KSB_REASON_BITS * 4);
+  static_assert(sizeof(CommitRec) * kMaxG <= (size_t)kMaxG * kWarps * 10 * 4, "commit records alias part + wstat");
   return off;
 }
 
@@ -720,13 +809,14 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
   s.pool_off = (int32_t*)(base + o[2]);
   s.zone = (int32_t*)(base + o[3]);
   s.part = (int32_t*)(base + o[4]);
-  s.norm = (KsbNorms*)(base + o[5]);
-  s.max_zone = (int32_t*)(base + o[6]);
-  s.wstat = (int32_t*)(base + o[7]);
+  s.wstat = (int32_t*)(base + o[5]);
+  s.norm = (KsbNorms*)(base + o[6]);
+  s.max_zone = (int32_t*)(base + o[7]);
   s.seg_max = (int32_t*)(base + o[8]);
   s.seg_cnt = (int32_t*)(base + o[9]);
   s.rows = (RowCache*)(base + o[10]);
   s.fe_hist = (int32_t*)(base + o[11]);
+  s.recs = (CommitRec*)(base + o[4]);
   return s;
 }
 
@@ -738,6 +828,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   __shared__ int32_t s_gc;            // pods in the current group
   __shared__ int32_t s_consumed;      // pods of the group that were committed
   __shared__ KsbPeer s_peers[KSB_MAX_RANKS];  // rank 0, block 0: the shard table, read once
+  __shared__ volatile int32_t s_ready[kMaxG]; // decider -> writer: record g is complete
+  __shared__ volatile int32_t s_stop;         // decider -> writer: pods decided in this group (-1: still deciding)
 
   const KsbNodeTable& T = A.table;
   const int tid = threadIdx.x;
@@ -751,6 +843,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const int G = A.group_size;
   const size_t np = T.n_pad;
   uint32_t epoch = 0, xepoch = 0;
+  uint64_t n_groups = 0, n_cut = 0;
   const bool multi = A.n_ranks > 1;
   uint64_t last_index = *A.last_node_index;  // used by warp 0 of block 0 only
   int p0 = 0;
@@ -776,6 +869,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     grid_barrier(A, epoch, xepoch);
   }
   long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long t3sum[6] = {0, 0, 0, 0, 0, 0};
   long long tmark = clock64();
 #define KSB_TICK(i)                                                                          \
   do {                                                                                       \
@@ -1029,6 +1123,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           S.seg_cnt[g * nsegT + i] = __ldcv(P.seg_cnt + (size_t)g * P.nseg + ls);
         }
       }
+      if (tid < kMaxG) s_ready[tid] = 0;
+      if (tid == 0) s_stop = -1;
       __syncthreads();
       long long t3[6] = {0, 0, 0, 0, 0, 0};
       long long m3 = clock64();
@@ -1117,7 +1213,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 }
                 __syncwarp();
                 A.fiterr_hist[(size_t)slotv * KSB_REASON_BITS + lane] =
-                    __ldcv(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
+                    __ldcg(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
                 res.fiterr_slot = slotv;
               }
               __syncwarp();
@@ -1143,7 +1239,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               for (int i = lane; i < nsegT; i += 32) c += scnt[i];
               const int32_t k = warp_sum(c);
               if (k <= 0) break;  // every holder of the group-start maximum changed and fell below it
-              int rem = (int)(last_index % (uint64_t)k);
+              int rem = (last_index >> 32) == 0 ? (int)((uint32_t)last_index % (uint32_t)k) : (int)(last_index % (uint64_t)k);
               int found = -1;
               for (int hi = nsegT; hi > 0 && found < 0; hi -= 32) {
                 const int sg = hi - 1 - lane;  // lane 0 = highest segment
@@ -1178,9 +1274,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   const int r = base_row + j * 32 + lane;
                   v[j] = r < P.table.n ? __ldcv(P.score + (size_t)g * pn + r) : INT32_MIN;
                 }
-                for (int i = 0; i < ncr; ++i) {  // fresh scores override the stash on changed rows
-                  const int cs = __shfl_sync(0xffffffffu, cseg, i);
-                  if (cs != found) continue;
+                uint32_t inseg = __ballot_sync(0xffffffffu, lane < ncr && cseg == found);
+                while (inseg) {  // fresh scores override the stash on changed rows of this segment
+                  const int i = __ffs(inseg) - 1;
+                  inseg &= inseg - 1;
                   const int cr = __shfl_sync(0xffffffffu, crow, i);
                   const int32_t cn = __shfl_sync(0xffffffffu, cnew, i);
                   const int32_t co = __shfl_sync(0xffffffffu, cold, i);
@@ -1219,7 +1316,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           }
           if (lane == 0 && *A.error_flag == 0) A.counters[14] = ((uint64_t)gi << 16) | ((uint64_t)(g + 1) << 8) | 0x80u;
           KSB_T3(2);  // select
-          // (3) the assume step on the chosen row
+          // (3) the assume step on the chosen row: the decider updates the row cache and hands the write-through
+          //     (table columns, class counters, result records) to the writer warp
+          CommitRec& rec = S.recs[g];
           if (chosen >= 0) {
             const KsbPeer& P = s_peers[chosen_rank];
             uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
@@ -1230,9 +1329,6 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 const uint32_t bal = __ballot_sync(0xffffffffu, mine);
                 if (bal) idx = __ffs(bal) - 1;
               }
-              const bool fast = R == 1 && counters_fast(h);
-              CounterLoads cl;
-              if (fast) cl = counters_load(P.table, chosen, pv, lane);  // in flight together with the cache fill
               if (idx < 0) {
                 idx = ncr;
                 cache_fill(P.table, chosen, S.rows + idx, lane);
@@ -1249,55 +1345,99 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
 #pragma unroll
                 for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
               }
-              commit_cached(P.table, S.rows + idx, pv, picks, lane);
-              if (fast) {
-                counters_store(P.table, chosen, pv, cl, lane);
-              } else {
-                // SelectorSpread columns are sharded with the rows; affinity tables are replicated on every rank
-                const size_t pn = P.table.n_pad;
-                for (int i = lane; i < h->n_spread_inc; i += 32) {
-                  uint32_t* pp = P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen;
-                  *pp = __ldcv(pp) + 1u;
-                }
-                for (int i = lane; i < h->n_commit; i += 32) {
-                  const uint64_t cm = pv.commits[2 * i];
-                  const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
-                  const uint32_t off = (uint32_t)cm;
-                  const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
-                  for (int q = 0; q < R; ++q) {
-                    int32_t* tb = s_peers[q].table.tables;
-                    if (d) tb[off + d] = __ldcv(tb + off + d) + delta;
-                    if ((cm >> 40) & 1ull) tb[off] = __ldcv(tb + off) + delta;
-                  }
-                }
-              }
+              commit_cache_only(S.rows + idx, pv, picks, lane);
               __syncwarp();
-            } else if (h->n_ext) {
-              if (lane == 0) {
-                EvalOut o;
-                eval_node<true>(P.table, chosen, pv, o, picks);
-              }
+              const RowCache& c = S.rows[idx];
+              if (lane < 31) {
+                rec.q[lane] = c.q[lane];
+              } else {
+                rec.npods = c.npods;
 #pragma unroll
-              for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+                for (int s2 = 0; s2 < KSB_MAX_RES; ++s2) rec.avail[s2] = c.avail[s2];
+                rec.row = chosen;
+                rec.rank = chosen_rank;
+              }
+            } else {
+              if (h->n_ext) {
+                if (lane == 0) {
+                  EvalOut o;
+                  eval_node<true>(P.table, chosen, pv, o, picks);
+                }
+#pragma unroll
+                for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+              }
+              if (lane == 31) rec.row = -1;
             }
             res.row = P.table.row_base + chosen;
 #pragma unroll
             for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
+          } else if (lane == 31) {
+            rec.row = -1;
           }
-          if (lane < R) s_peers[lane].results[p0 + g] = res;  // every rank keeps a copy of the results
+          if (lane == 0) rec.res = res;
+          __syncwarp();
+          __threadfence_block();
+          if (lane == 0) s_ready[g] = 1;
           consumed = g + 1;
-          KSB_T3(3);  // commit + result
+          KSB_T3(3);  // cache update + hand-off
         }
-        if (lane == 0) s_consumed = consumed;
+        if (lane == 0) {
+          s_consumed = consumed;
+          __threadfence_block();
+          s_stop = consumed;
+        }
         if (lane < R) *s_peers[lane].last_node_index = last_index;  // every rank's host reads its own copy
+      } else if (warp == 1) {
+        // writer warp: table write-through, class counters and result records of every decided pod, in order
+        for (int g = 0; g < Gc; ++g) {
+          while (s_ready[g] == 0) {
+            const int st = s_stop;
+            if (st >= 0 && g >= st) break;
+            __nanosleep(20);
+          }
+          if (s_ready[g] == 0) break;  // the group ended before this pod
+          __threadfence_block();
+          const CommitRec& rec = S.recs[g];
+          const KsbPodHeader* h = S.hdr + g;
+          if (rec.row >= 0) {
+            const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+            const KsbPeer& P = s_peers[rec.rank];
+            const int chosen = rec.row;
+            write_through(P.table, rec, h, lane);
+            if (R == 1 && counters_fast(h)) {
+              const CounterLoads cl = counters_load(P.table, chosen, pv, lane);
+              counters_store(P.table, chosen, pv, cl, lane);
+            } else {
+              // SelectorSpread columns are sharded with the rows; affinity tables are replicated on every rank
+              const size_t pn = P.table.n_pad;
+              for (int i = lane; i < h->n_spread_inc; i += 32) {
+                uint32_t* pp = P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen;
+                *pp = __ldcv(pp) + 1u;
+              }
+              for (int i = lane; i < h->n_commit; i += 32) {
+                const uint64_t cm = pv.commits[2 * i];
+                const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
+                const uint32_t off = (uint32_t)cm;
+                const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
+                for (int q = 0; q < R; ++q) {
+                  int32_t* tb = s_peers[q].table.tables;
+                  if (d) tb[off + d] = __ldcv(tb + off + d) + delta;
+                  if ((cm >> 40) & 1ull) tb[off] = __ldcv(tb + off) + delta;
+                }
+              }
+            }
+          }
+          if (lane < R) s_peers[lane].results[p0 + g] = rec.res;  // every rank keeps a copy of the results
+          __syncwarp();
+        }
       }
       __syncthreads();
       KSB_T3(4);
       // publish how far the group got; reset the other scratch half for the next group
       if (tid == 0) {
         A.group_done[slot] = s_consumed;
-        atomicAdd((unsigned long long*)A.counters, 1ull);
-        if (s_consumed < Gc) atomicAdd((unsigned long long*)A.counters + 1, 1ull);
+        n_groups += 1;  // block 0 / thread 0 is the only writer: kept in registers, stored once at the end
+        if (s_consumed < Gc) n_cut += 1;
       }
       KsbNorms* nn = A.norms + (size_t)(slot ^ 1) * kMaxG;
       for (int i = tid; i < kMaxG * 8; i += kThreads) reinterpret_cast<int32_t*>(nn)[i] = ((i & 7) == 7) ? -1 : 0;
@@ -1306,8 +1446,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       int32_t* gh = A.ghist + (size_t)(slot ^ 1) * kMaxG * KSB_REASON_BITS;
       for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
       KSB_T3(5);
-      if (tid == 0)
-        for (int i = 0; i < 6; ++i) A.counters[9 + i] += (uint64_t)t3[i];
+      for (int i = 0; i < 6; ++i) t3sum[i] += t3[i];
 #undef KSB_T3
     }
     KSB_TICK(5);
@@ -1324,6 +1463,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   if (b == 0 && tid == 0) {
     if (multi) *A.xstate = xepoch;
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)tk[i];  // block 0's cycles per stage
+    for (int i = 0; i < 6; ++i) A.counters[9 + i] = (uint64_t)t3sum[i];
+    if (A.rank == 0) {
+      A.counters[0] = n_groups;
+      A.counters[1] = n_cut;
+    }
   }
 #undef KSB_TICK
 }
