@@ -50,14 +50,6 @@ static bool is_scalar_resource(const std::string& n) {  // pkg/apis/core/v1/help
   return !default_ns || n.rfind("hugepages-", 0) == 0;
 }
 
-// toleration.go:37-56
-static bool tolerates(const Toleration& t, const Taint& taint) {
-  if (!t.effect.empty() && t.effect != taint.effect) return false;
-  if (!t.key.empty() && t.key != taint.key) return false;
-  if (t.op.empty() || t.op == "Equal") return t.value == taint.value;
-  return t.op == "Exists";
-}
-
 Engine::Engine(const ksb_config& c) : cfg(c) {
   W = cfg.label_words > 0 ? cfg.label_words : 4;
   if (W > 16) throw std::runtime_error("label_words must be <= 16");

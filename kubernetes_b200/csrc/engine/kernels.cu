@@ -52,7 +52,6 @@ constexpr int kSeg = 256;             // rows per segment (= per block iteration
 constexpr int kMaxG = KSB_MAX_GROUP;  // pods per group
 constexpr int kMaxPoolWords = 1024;   // pool words one pod may use (checked on the host)
 constexpr int kGroupPoolWords = 4096; // pool words staged per group
-constexpr int kMaxSeg = KSB_MAX_SEGMENTS;
 constexpr int kSegCache = KSB_SEG_CACHE;  // (pods in group) x (segments) entries of segment stats kept in shared memory
 
 template <bool CG, typename V>
@@ -564,71 +563,31 @@ __device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCach
   if (lane >= 22 && lane < 26) p = reinterpret_cast<const int64_t*>(T.port_wild + (size_t)(lane - 22) * np + r);
   if (lane >= 26 && lane < 30) p = reinterpret_cast<const int64_t*>(T.port_exact + (size_t)(lane - 26) * np + r);
   if (lane == 30) p = reinterpret_cast<const int64_t*>(T.avoid + r);
-  if (lane < 31) {
-    c->q[lane] = __ldcg(p);
-  } else {
-    c->apods = T.alloc_pods[r];
-    c->npods = __ldcg(T.num_pods + r);
-    c->flags = T.flags[r];
-    c->zone = T.zone[r];
-#pragma unroll
-    for (int s = 0; s < KSB_MAX_RES; ++s) c->avail[s] = __ldcg(T.dev_avail + (size_t)s * np + r);
-    c->row = r;
-  }
-}
-
-// One warp: the assume step (NodeInfo.AddPod, schedulercache/node_info.go:329-356) applied to the cache
-// entry and written through to the table; the class counters are bumped in global memory only (no pod
-// of the same group reads them).
-__device__ __forceinline__ void commit_cached(const KsbNodeTable& T, RowCache* c, const PodView& pv,
-                                              const uint32_t* picks, int lane) {
-  const KsbPodHeader* h = pv.h;
-  const size_t np = T.n_pad;
-  const int r = c->row;
-  int64_t add = 0;
-  int64_t* dst = nullptr;
+  // every load is issued before the first store to *c: the compiler cannot tell the generic pointers apart,
+  // so a store in between would put one L2 round trip per field on the commit path
+  const uint32_t* p2 = nullptr;
   switch (lane) {
-    case 4: add = h->add_cpu; dst = T.req_cpu + r; break;
-    case 5: add = h->add_mem; dst = T.req_mem + r; break;
-    case 6: add = h->add_agpu; dst = T.req_agpu + r; break;
-    case 7: add = h->add_eph; dst = T.req_eph + r; break;
-    case 8: add = h->nz_cpu; dst = T.nz_cpu + r; break;
-    case 9: add = h->nz_mem; dst = T.nz_mem + r; break;
+    case 0: p2 = reinterpret_cast<const uint32_t*>(T.alloc_pods + r); break;
+    case 1: p2 = reinterpret_cast<const uint32_t*>(T.num_pods + r); break;
+    case 2: p2 = T.flags + r; break;
+    case 3: p2 = T.zone + r; break;
     default: break;
   }
-  if (lane >= 14 && lane < 18) {
-    add = h->scalar_add[lane - 14];
-    dst = T.req_scalar + (size_t)(lane - 14) * np + r;
+  if (lane >= 4 && lane < 4 + KSB_MAX_RES) p2 = T.dev_avail + (size_t)(lane - 4) * np + r;
+  int64_t v = 0;
+  uint32_t v2 = 0;
+  if (lane < 31) v = __ldcg(p);
+  if (lane < 4 + KSB_MAX_RES) v2 = __ldcg(p2);
+  if (lane < 31) c->q[lane] = v;
+  switch (lane) {
+    case 0: c->apods = (int32_t)v2; break;
+    case 1: c->npods = (int32_t)v2; break;
+    case 2: c->flags = v2; break;
+    case 3: c->zone = v2; break;
+    default: break;
   }
-  if (dst && add != 0) {
-    c->q[lane] += add;
-    *dst = c->q[lane];
-  }
-  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30) {
-    const int j = lane - 18;  // pool ports[12..23] = add_any[4], add_wild[4], add_exact[4]
-    uint64_t v = (uint64_t)c->q[lane] | pv.ports[3 * KSB_PORT_WORDS + j];
-    c->q[lane] = (int64_t)v;
-    uint64_t* pd = (j < 4 ? T.port_any : (j < 8 ? T.port_wild : T.port_exact)) + (size_t)(j & 3) * np + r;
-    *pd = v;
-  }
-  if (lane == 31) {
-    c->npods += 1;
-    T.num_pods[r] = c->npods;
-    if (h->n_ext) {
-      // bind echo (pkg/registry/core/pod/storage/storage.go:180-187): the assigned devices leave `available`
-      uint32_t take[KSB_MAX_RES];
-#pragma unroll
-      for (int s = 0; s < KSB_MAX_RES; ++s) take[s] = 0;
-      for (int i = 0; i < h->n_ext; ++i)
-        if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
-#pragma unroll
-      for (int s = 0; s < KSB_MAX_RES; ++s)
-        if (take[s]) {
-          c->avail[s] &= ~take[s];
-          T.dev_avail[(size_t)s * np + r] = c->avail[s];
-        }
-    }
-  }
+  if (lane >= 4 && lane < 4 + KSB_MAX_RES) c->avail[lane - 4] = v2;
+  if (lane == 31) c->row = r;
 }
 
 // The class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
@@ -671,23 +630,6 @@ __device__ __forceinline__ void counters_store(const KsbNodeTable& T, int r, con
     if ((cm >> 40) & 1ull) T.tables[off] = L.tot_v + delta;  // slot 0: matching pods anywhere
   }
 }
-__device__ __forceinline__ void counters_slow(const KsbNodeTable& T, int r, const PodView& pv, int lane) {
-  const KsbPodHeader* h = pv.h;
-  const size_t np = T.n_pad;
-  for (int i = lane; i < h->n_spread_inc; i += 32) {
-    uint32_t* p = T.spread + (size_t)pv.spread_inc[i] * np + r;
-    *p = __ldcg(p) + 1u;
-  }
-  for (int i = lane; i < h->n_commit; i += 32) {
-    uint64_t cm = pv.commits[2 * i];
-    int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
-    uint32_t off = (uint32_t)cm;
-    uint32_t d = T.topo[((uint32_t)(cm >> 32) & 0xffu) * np + r];
-    if (d) T.tables[off + d] = __ldcg(T.tables + off + d) + delta;
-    if ((cm >> 40) & 1ull) T.tables[off] = __ldcg(T.tables + off) + delta;
-  }
-}
-
 // What the decider warp hands to the writer warp for one pod: the chosen row's mutable columns after the
 // assume step (a copy of the row-cache entry) and the result record.
 struct CommitRec {
@@ -876,7 +818,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     long long now_ = clock64();                                                              \
     tk[i] += now_ - tmark;                                                                   \
     tmark = now_;                                                                            \
-    if (blockIdx.x == 0 && threadIdx.x == 0 && *A.error_flag == 0) A.counters[14] = ((uint64_t)gi << 16) | (i); \
+    if (blockIdx.x == 0 && threadIdx.x == 0) A.counters[14] = ((uint64_t)gi << 16) | (i); \
   } while (0)
   while (p0 < A.n_pods) {
     const int slot = gi & 1;
@@ -1138,6 +1080,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       if (warp == 0) {
         int ncr = 0;       // rows in the cache (uniform across the warp)
         int consumed = 0;
+        // group-start results of the NEXT pod on the cached rows, requested one pod ahead so that their L2
+        // round trip overlaps the current pod's commit
+        int4 nx_raw = make_int4(INT32_MIN, 0, 0, 0);
+        uint32_t nx_reasons = 0;
+        int32_t nx_score = INT32_MIN;
         for (int g = 0; g < Gc; ++g) {
           const KsbPodHeader* h = S.hdr + g;
           const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
@@ -1167,10 +1114,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               crank = c.pad;
               const KsbPeer& P = s_peers[crank];
               cseg = P.seg_base + crow / kSeg;
-              const size_t pn = P.table.n_pad;
-              const int4 raw0 = __ldcv(P.raw + (size_t)g * pn + crow);
-              old_reasons = __ldcv(P.reasons + (size_t)g * pn + crow);
-              if (prio) cold = __ldcv(P.score + (size_t)g * pn + crow);
+              const int4 raw0 = nx_raw;
+              old_reasons = nx_reasons;
+              if (prio) cold = nx_score;
               int32_t base;
               eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr);
               const bool was_fit = raw0.x != INT32_MIN;
@@ -1314,21 +1260,37 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               last_index += 1;
             }
           }
-          if (lane == 0 && *A.error_flag == 0) A.counters[14] = ((uint64_t)gi << 16) | ((uint64_t)(g + 1) << 8) | 0x80u;
           KSB_T3(2);  // select
           // (3) the assume step on the chosen row: the decider updates the row cache and hands the write-through
           //     (table columns, class counters, result records) to the writer warp
           CommitRec& rec = S.recs[g];
+          int idx = -1;
+          if (chosen >= 0 && A.commit) {
+            const bool mine = lane < ncr && S.rows[lane].row == chosen && S.rows[lane].pad == chosen_rank;
+            const uint32_t bal = __ballot_sync(0xffffffffu, mine);
+            if (bal) idx = __ffs(bal) - 1;
+          }
+          if (g + 1 < Gc) {
+            int prow = -1, prank = 0;
+            if (lane < ncr) {
+              prow = S.rows[lane].row;
+              prank = S.rows[lane].pad;
+            } else if (lane == ncr && chosen >= 0 && A.commit && idx < 0) {
+              prow = chosen;  // the row this pod is about to add to the cache
+              prank = chosen_rank;
+            }
+            if (prow >= 0) {
+              const KsbPeer& P = s_peers[prank];
+              const size_t at = (size_t)(g + 1) * P.table.n_pad + prow;
+              nx_raw = __ldcv(P.raw + at);
+              nx_reasons = __ldcv(P.reasons + at);
+              nx_score = __ldcv(P.score + at);
+            }
+          }
           if (chosen >= 0) {
             const KsbPeer& P = s_peers[chosen_rank];
             uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
             if (A.commit) {
-              int idx = -1;
-              {
-                const bool mine = lane < ncr && S.rows[lane].row == chosen && S.rows[lane].pad == chosen_rank;
-                const uint32_t bal = __ballot_sync(0xffffffffu, mine);
-                if (bal) idx = __ffs(bal) - 1;
-              }
               if (idx < 0) {
                 idx = ncr;
                 cache_fill(P.table, chosen, S.rows + idx, lane);
