@@ -97,9 +97,22 @@ def oracle_baseline(cluster, sample_pods, workers):
     return out["pods"] / out["seconds"], out["seconds"], wall
 
 
+def ncu_traffic(cfg, n_nodes, n_pods):
+    """DRAM bytes per launch of the batch kernel from the committed `ncu --set full` summary of this workload, else None."""
+    path = os.path.join(ROOT, "profiles", "r01_ncu_summary.json")
+    try:
+        with open(path) as f:
+            for rec in json.load(f)["captures"]:
+                if (rec["config"], rec["nodes"], rec["pods"]) == (cfg, n_nodes, n_pods):
+                    return rec["dram_bytes_read"] + rec["dram_bytes_write"]
+    except (OSError, KeyError, ValueError):
+        pass
+    return None
+
+
 def pick_sample(n_nodes):
-    # ~10-30 s of CPU work: the literal oracle costs roughly 2.5 us per (pod, node) per thread
-    return max(20, min(2000, int(4.0e6 / max(1, n_nodes)) * 10))
+    # ~20 s of CPU work: the literal oracle on 16 threads does about 0.6 M (pod, node) evaluations per second
+    return max(20, min(4000, int(1.25e7 / max(1, n_nodes))))
 
 
 def main():
@@ -114,6 +127,9 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner) goes to stderr
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -141,7 +157,7 @@ def main():
         v = sum(p for p, _ in times) / len(times)
         ms = 1000.0 * sum(s for _, s in times) / len(times)
         sample_txt = "first %d pods of the stream on all %d nodes, %d worker threads (Parallelize(16))" % (sample, n_nodes, workers)
-        print(json.dumps({
+        json_out.write(json.dumps({
             "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": 0, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int64", "data": "synthetic",
@@ -149,7 +165,8 @@ def main():
                        "restatement of its algorithm (oracle/), literal mode"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": workers, "kind": "port", "sample": sample_txt},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        }))
+        }) + "\n")
+        json_out.flush()
         return
 
     import torch
@@ -234,20 +251,28 @@ def main():
                    "placement_hash": sorted(hashes)[0]},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_step_ms},
-        "gpu_launches": args.steps,
+        # per step: ksb_schedule_batch_kernel once inside the end-to-end pass and once in the resident replay
+        "gpu_launches": 2 * args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "ksb_schedule_batch_kernel",
+                     "traffic": ncu_traffic(args.config, n_nodes, n_pods), "peak_source": peak_src, "kernel": "ksb_schedule_batch_kernel",
                      "algorithmic_bytes_per_eval": algo_bytes, "evals_per_launch": n_nodes * n_pods,
                      "kernel_ms_in_e2e": sum(kernel_ms) / len(kernel_ms)},
         "clocks": clocks,
     }
+    if world == 1:
+        # p99 per-pod latency (BASELINE.json's metric): the one-pod-per-call path, Schedule + AssumePod per pod
+        n_lat = min(n_pods, 2000 if n_nodes <= 5000 else 500)
+        lat = sess.run(device=local_rank, results=False, batch=0, limit=n_lat)
+        line["latency"] = {"p50_us": lat["p50_us"], "p99_us": lat["p99_us"], "unit": "us per ksb_schedule call (host to host)",
+                           "sample": "first %d pods of the stream, one C-ABI call per pod" % n_lat}
     if not args.no_cpu_baseline:
         sample = args.cpu_sample or pick_sample(n_nodes)
         pps, secs, _ = oracle_baseline(cluster, sample, workers)
         line["cpu_baseline"] = {"value": pps, "unit": UNIT, "cores": workers, "kind": "port",
                                 "sample": "first %d pods of the same stream on all %d nodes, C++ restatement of the Go "
                                           "scheduler (literal mode), %d worker threads, %.1f s" % (sample, n_nodes, workers, secs)}
-    print(json.dumps(line))
+    json_out.write(json.dumps(line) + "\n")
+    json_out.flush()
     if dist is not None:
         dist.destroy_process_group()
 
