@@ -261,10 +261,14 @@ def main():
     }
     if world == 1:
         # p99 per-pod latency (BASELINE.json's metric): the one-pod-per-call path, Schedule + AssumePod per pod
-        n_lat = min(n_pods, 2000 if n_nodes <= 5000 else 500)
-        lat = sess.run(device=local_rank, results=False, batch=0, limit=n_lat)
-        line["latency"] = {"p50_us": lat["p50_us"], "p99_us": lat["p99_us"], "unit": "us per ksb_schedule call (host to host)",
-                           "sample": "first %d pods of the stream, one C-ABI call per pod" % n_lat}
+        n_cold = min(n_pods // 2, 500)
+        n_lat = min(n_pods - n_cold, 2000)
+        lat = sess.run(device=local_rank, results=False, batch=0, limit=n_cold + n_lat, lat_skip=n_cold)
+        line["latency"] = {"p50_us": lat["p50_us"], "p99_us": lat["p99_us"], "max_us": lat["max_us"],
+                           "cold_max_us": max(x[1] for x in lat["slowest"]),
+                           "unit": "us per ksb_schedule call (host to host)",
+                           "sample": "pods %d..%d of the stream, one C-ABI call per pod; the first %d calls (cold label / "
+                                     "selector-class dictionaries) are reported as cold_max_us only" % (n_cold, n_cold + n_lat, n_cold)}
     if not args.no_cpu_baseline:
         sample = args.cpu_sample or pick_sample(n_nodes)
         pps, secs, _ = oracle_baseline(cluster, sample, workers)

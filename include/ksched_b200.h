@@ -124,6 +124,12 @@ int32_t ksb_device_id(const ksb_engine* e, int32_t index, const char* resource, 
  * ksb_schedule, or for pod `i` of the most recent ksb_schedule_batch. */
 int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_len);
 
+/* Bring the device table up to date with every node / pod / selector-owner call made so far, now, instead of
+ * inside the next ksb_schedule. Counterpart of the work cache.UpdateNodeNameToInfoMap
+ * (schedulercache/cache.go:79-96, called at core/generic_scheduler.go:124) does at the start of each
+ * Schedule; calling it after the informers' initial sync keeps that cost out of the first pod's latency. */
+int32_t ksb_flush(ksb_engine* e);
+
 /* genericScheduler.lastNodeIndex (core/generic_scheduler.go:100): selectHost's round-robin counter. */
 uint64_t ksb_get_last_node_index(const ksb_engine* e);
 void ksb_set_last_node_index(ksb_engine* e, uint64_t v);
@@ -139,6 +145,7 @@ typedef struct ksb_stats {
   uint64_t d2h_bytes;          /* device->host bytes copied */
   double last_batch_kernel_ms; /* CUDA-event time of the kernels of the last ksb_schedule_batch */
   double last_batch_encode_ms; /* host time spent encoding the last batch */
+  double last_batch_sync_ms;   /* host time spent bringing the device table up to date before the launch */
   int32_t num_nodes;
   int32_t node_row_bytes;      /* bytes of node-table columns one (pod,node) evaluation may read */
   /* SM cycles block 0 spent, last batch: staging, phase 1, barrier 1, phase 2, barrier 2, phase 3, barrier 3;

@@ -152,6 +152,10 @@ int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_le
   });
 }
 
+int32_t ksb_flush(ksb_engine* e) {
+  return guarded(e, [&] { e->impl->flush(); });
+}
+
 uint64_t ksb_get_last_node_index(const ksb_engine* e) { return e && e->impl ? e->impl->last_node_index : 0; }
 void ksb_set_last_node_index(ksb_engine* e, uint64_t v) {
   if (e && e->impl) e->impl->last_node_index = v;

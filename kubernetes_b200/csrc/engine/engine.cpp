@@ -36,6 +36,24 @@ void DevBuf::release() {
   cap = 0;
 }
 
+void PinnedBuf::ensure(size_t bytes) {
+  if (bytes <= cap) return;
+  if (p) cudaFreeHost(p);
+  size_t want = std::max(bytes, cap * 2);
+  cudaError_t e = cudaMallocHost(&p, want);
+  if (e != cudaSuccess) {
+    p = nullptr;
+    cap = 0;
+    throw std::runtime_error(std::string("cudaMallocHost failed: ") + cudaGetErrorString(e));
+  }
+  cap = want;
+}
+void PinnedBuf::release() {
+  if (p) cudaFreeHost(p);
+  p = nullptr;
+  cap = 0;
+}
+
 static std::string join3(const std::string& a, const std::string& b, const std::string& c) {
   std::string s = a;
   s.push_back('\0');
@@ -59,6 +77,8 @@ Engine::Engine(const ksb_config& c) : cfg(c) {
     throw std::runtime_error("no usable CUDA device: the engine has no CPU fallback");
   CUDA_OK(cudaSetDevice(cfg.device));
   CUDA_OK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  CUDA_OK(cudaEventCreate(&ev_start));
+  CUDA_OK(cudaEventCreate(&ev_stop));
   topo_values.reserve(KSB_MAX_TOPO);
 }
 
@@ -68,6 +88,11 @@ Engine::~Engine() {
   for (DevBuf* b : {&b_i64, &b_u32, &b_u64, &b_dev_class, &b_topo, &b_spread, &b_tables, &b_headers, &b_pool,
                     &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush, &b_dep})
     b->release();
+  pin_in.release();
+  pin_ctl.release();
+  pin_out.release();
+  if (ev_start) cudaEventDestroy(ev_start);
+  if (ev_stop) cudaEventDestroy(ev_stop);
   if (stream) cudaStreamDestroy(stream);
 }
 
@@ -106,20 +131,26 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
   label_bits[k] = bit;
   if (!layout_dirty) {  // fill the new bit column from the retained node labels
     if (!label_index_valid) build_label_index();
-    const std::vector<int>* cand = nullptr;
+    const uint64_t m = 1ull << (bit & 63);
     if (kind == 'P') {
       std::string pk = key;
       pk.push_back('\0');
       pk += value;
       auto it2 = rows_by_pair.find(pk);
-      if (it2 != rows_by_pair.end()) cand = &it2->second;
+      if (it2 != rows_by_pair.end())
+        for (int r : it2->second) u64(bit >> 6, r) |= m;
     } else {
       auto it2 = rows_by_key.find(key);
-      if (it2 != rows_by_key.end()) cand = &it2->second;
+      if (it2 != rows_by_key.end())
+        for (auto& rv : it2->second) {
+          bool on = true;
+          if (kind != 'K') {  // 'G' / 'L' (selector.go:214-233)
+            int64_t v;
+            on = sel::to_int64(*rv.second, &v) && (kind == 'G' ? v > num : v < num);
+          }
+          if (on) u64(bit >> 6, rv.first) |= m;
+        }
     }
-    if (cand)
-      for (int r : *cand)
-        if (node_has_label_bit(rows[r]->node, d)) u64(bit >> 6, r) |= 1ull << (bit & 63);
     dirty_label_words.insert(bit >> 6);
   }
   return bit;
@@ -134,7 +165,7 @@ void Engine::build_label_index() {
       pk.push_back('\0');
       pk += kv.second;
       rows_by_pair[pk].push_back(r);
-      rows_by_key[kv.first].push_back(r);
+      rows_by_key[kv.first].emplace_back(r, &kv.second);
     }
   label_index_valid = true;
 }
@@ -730,8 +761,8 @@ void Engine::rebuild_layout() {
   h_topo.assign((size_t)KSB_MAX_TOPO * n_pad, 0);
   for (auto& c : h_spread) c.assign((size_t)n_pad, 0u);
   layout_dirty = false;
-  label_index_valid = false;
   for (int r = 0; r < n; ++r) fill_row(r);
+  build_label_index();  // here, not inside the first Schedule that mentions a new label
   // per-class counters follow the pods: recount them all
   for (auto& t : tables) std::fill(t.vals.begin(), t.vals.end(), 0);
   for (auto& kv : pods) register_pod_classes(kv.second.pod);

@@ -28,6 +28,13 @@ struct DevBuf {  // growable device buffer
   void release();
 };
 
+struct PinnedBuf {  // growable page-locked host buffer (staging for asynchronous copies)
+  void* p = nullptr;
+  size_t cap = 0;
+  void ensure(size_t bytes);
+  void release();
+};
+
 struct DeviceState {  // fork: ExtendedResourceCacheManagerImpl (schedulercache/extended_resources.go:39-207)
   std::map<std::string, ExtendedDevice> allocatable;  // ascending id = bit order
   std::set<std::string> available, used;
@@ -105,6 +112,7 @@ class Engine {
 
   // hot path
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
+  void flush();
   void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
   void replay_last_batch_noalloc(ksb_result* out);
   // sharding over the GPUs of one NVSwitch domain
@@ -133,7 +141,9 @@ class Engine {
   std::vector<LabelBitDef> label_defs;
   // inverted index over the retained node labels (rows by "key\0value" and by key): a label bit interned
   // later fills its column from the matching rows only instead of scanning every node
-  std::unordered_map<std::string, std::vector<int>> rows_by_pair, rows_by_key;
+  // label -> rows index (built with the layout): rows holding a key=value pair; rows holding a key, with the value
+  std::unordered_map<std::string, std::vector<int>> rows_by_pair;
+  std::unordered_map<std::string, std::vector<std::pair<int, const std::string*>>> rows_by_key;
   bool label_index_valid = false;
   void build_label_index();
   std::vector<Taint> hard_taints, soft_taints;
@@ -223,6 +233,9 @@ class Engine {
   size_t spread_cap_cols = 0;
   int grid = 0, threads = 0, max_grid = 0, group = 1, nseg = 0, zone_stride = 64;
   size_t smem_bytes = 0;
+  size_t limits_for_smem = (size_t)-1;  // shared-memory size the cached max_grid / threads were queried for
+  PinnedBuf pin_in, pin_ctl, pin_out;   // pod blocks in; control block in; control block + results out
+  cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
   // shard geometry: device rows [lbase, lbase + ln), device column stride ln_pad
   int lbase = 0, ln = 0, ln_pad = 0, rows_per_shard = 0;
   size_t min_spread_cols = 0, min_table_bytes = 0;

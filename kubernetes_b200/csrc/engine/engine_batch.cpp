@@ -70,11 +70,14 @@ void Engine::prepare_geometry() {
   group = std::max(1, std::min(group, KSB_SEG_CACHE / std::max(1, nseg_total)));
   if (zone_stride * 4 * KSB_MAX_GROUP > 160 * 1024) throw std::runtime_error("more than 1,280 distinct zones");
   smem_bytes = ksb_batch_smem_bytes(zone_stride);
-  int mg = 0, th = 0;
-  int rc = ksb_batch_kernel_limits(cfg.device, smem_bytes, &mg, &th);
-  if (rc != 0) throw std::runtime_error(std::string("kernel attribute query failed: ") + cudaGetErrorString((cudaError_t)rc));
-  max_grid = mg;
-  threads = th;
+  if (limits_for_smem != smem_bytes) {  // attribute + occupancy queries: once per shared-memory size
+    int mg = 0, th = 0;
+    int rc = ksb_batch_kernel_limits(cfg.device, smem_bytes, &mg, &th);
+    if (rc != 0) throw std::runtime_error(std::string("kernel attribute query failed: ") + cudaGetErrorString((cudaError_t)rc));
+    max_grid = mg;
+    threads = th;
+    limits_for_smem = smem_bytes;
+  }
   if (max_grid < 1) throw std::runtime_error("batch kernel does not fit on this device");
   // enough blocks to cover every segment; when segments are few, extra blocks split the group's pods
   grid = nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, std::max(1, nseg) * group));
@@ -141,6 +144,34 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
 // Zero what must start at zero, seed the round-robin counter, launch. Works on whatever scratch the
 // arguments point at (the engine's own buffer or the static no-allocation array).
 void Engine::launch(const KsbBatchArgs& a) {
+  if (a.n_ranks == 1 && b_scratch.d && (char*)a.norms == (char*)b_scratch.d) {
+    // the engine's own scratch on one GPU: every control field lies in one contiguous block at the start of the
+    // buffer, so its initial image goes up in a single copy from page-locked memory
+    ScratchLayout L = scratch_layout(ln_pad, a.zone_stride, std::max(1, a.nseg), a.group_size);
+    const size_t bytes = L.fiterr_hist;
+    pin_ctl.ensure(bytes);
+    char* img = (char*)pin_ctl.p;
+    memset(img, 0, bytes);
+    KsbNorms* nm = (KsbNorms*)(img + L.norms);
+    for (int i = 0; i < 2 * KSB_MAX_GROUP; ++i) nm[i].one_row = -1;
+    memcpy(img + L.last_index, &last_node_index, 8);
+    KsbPeer* self = (KsbPeer*)(img + L.peers);
+    self->table = a.table;
+    self->raw = a.raw;
+    self->score = a.score;
+    self->reasons = a.reasons;
+    self->seg_max = a.seg_max;
+    self->seg_cnt = a.seg_cnt;
+    self->results = a.results;
+    self->last_node_index = a.last_node_index;
+    self->nseg = a.nseg;
+    self->seg_base = 0;
+    CUDA_OK(cudaMemcpyAsync(b_scratch.d, img, bytes, cudaMemcpyHostToDevice, stream));
+    int rc = ksb_launch_batch(&a, grid, smem_bytes, stream);
+    if (rc != 0) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString((cudaError_t)rc));
+    stats.kernel_launches += 1;
+    return;
+  }
   static KsbNorms init[2 * KSB_MAX_GROUP];
   memset(init, 0, sizeof init);
   for (auto& x : init) x.one_row = -1;
@@ -265,21 +296,34 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   // pass 1: classes; pass 2: requirement blocks
   for (auto& p : batch) register_pod_classes(p);
   layout_arena();
-  std::vector<KsbPodHeader> headers(np);
-  std::vector<uint64_t> pool;
+  size_t pool_words = 0;
   for (int i = 0; i < np; ++i) {
     if (batch[i].num_volumes > 0)  // volume predicates are out of scope: refuse loudly, never guess
       throw std::runtime_error("pod " + batch[i].key() + " has volumes: not supported by the GPU engine");
     encode_pod(batch[i], &last_encoded[i]);
-    last_encoded[i].h.pool_off = (uint32_t)pool.size();
-    headers[i] = last_encoded[i].h;
-    pool.insert(pool.end(), last_encoded[i].pool.begin(), last_encoded[i].pool.end());
+    last_encoded[i].h.pool_off = (uint32_t)pool_words;
+    pool_words += last_encoded[i].pool.size();
   }
-  if (pool.empty()) pool.push_back(0);
+  // headers, dependency indices and pool words are laid out in page-locked memory so the copies below are
+  // asynchronous and the batch needs no intermediate host copy
+  const size_t hdr_bytes = (size_t)np * sizeof(KsbPodHeader);
+  const size_t dep_off = (hdr_bytes + 255) & ~(size_t)255;
+  const size_t pool_off = (dep_off + (size_t)np * 4 + 255) & ~(size_t)255;
+  const size_t pool_bytes = std::max<size_t>(1, pool_words) * 8;
+  pin_in.ensure(pool_off + pool_bytes);
+  KsbPodHeader* headers = (KsbPodHeader*)pin_in.p;
+  int32_t* dep = (int32_t*)((char*)pin_in.p + dep_off);
+  uint64_t* pool = (uint64_t*)((char*)pin_in.p + pool_off);
+  pool[0] = 0;
+  for (int i = 0; i < np; ++i) {
+    headers[i] = last_encoded[i].h;
+    if (!last_encoded[i].pool.empty())
+      memcpy(pool + last_encoded[i].h.pool_off, last_encoded[i].pool.data(), last_encoded[i].pool.size() * 8);
+  }
   // dep[j]: the latest earlier pod whose assume step bumps a counter pod j reads (its SelectorSpread column
   // or any inter-pod-affinity table). A group never holds both, so those inputs are constant inside a group.
-  std::vector<int32_t> dep(np, -1);
-  {
+  for (int i = 0; i < np; ++i) dep[i] = -1;
+  if (np > 1) {
     std::vector<int32_t> last_spread(h_spread.size(), -1), last_table(tables.size(), -1);
     std::unordered_map<uint32_t, int> table_by_off;
     for (size_t t = 0; t < tables.size(); ++t) table_by_off[tables[t].off] = (int)t;
@@ -304,41 +348,45 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   stats.last_batch_encode_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
 
   sync_device();
-  b_headers.ensure(headers.size() * sizeof(KsbPodHeader));
-  b_pool.ensure(pool.size() * 8);
+  stats.last_batch_sync_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+  b_headers.ensure(hdr_bytes);
+  b_pool.ensure(pool_bytes);
   if (shard_connected && (size_t)np * sizeof(KsbResult) > b_results.cap)
     throw std::runtime_error("sharded engine: batch larger than the max_batch_pods given to ksb_shard_export");
   b_results.ensure((size_t)np * sizeof(KsbResult));
   b_dep.ensure((size_t)np * 4);
-  CUDA_OK(cudaMemcpyAsync(b_dep.d, dep.data(), (size_t)np * 4, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_headers.d, headers.data(), headers.size() * sizeof(KsbPodHeader), cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_pool.d, pool.data(), pool.size() * 8, cudaMemcpyHostToDevice, stream));
-  stats.h2d_bytes += headers.size() * sizeof(KsbPodHeader) + pool.size() * 8 + (size_t)np * 4;
+  CUDA_OK(cudaMemcpyAsync(b_dep.d, dep, (size_t)np * 4, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemcpyAsync(b_headers.d, headers, hdr_bytes, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemcpyAsync(b_pool.d, pool, pool_bytes, cudaMemcpyHostToDevice, stream));
+  stats.h2d_bytes += hdr_bytes + pool_bytes + (size_t)np * 4;
   KsbBatchArgs a = make_args(np, assume);
   if (assume) snapshot_dynamic();
   last_index_before = last_node_index;
 
-  cudaEvent_t ev0, ev1;
-  CUDA_OK(cudaEventCreate(&ev0));
-  CUDA_OK(cudaEventCreate(&ev1));
-  CUDA_OK(cudaStreamSynchronize(stream));
-  CUDA_OK(cudaEventRecord(ev0, stream));
+  // what comes back: the control words (error flag, FitError count, round-robin counter, counters) in one
+  // copy, then the result records
+  const size_t ctl_lo = (char*)a.barrier - (char*)b_scratch.d;
+  const size_t ctl_hi = (char*)a.counters - (char*)b_scratch.d + 128;
+  const size_t res_off = (ctl_hi - ctl_lo + 255) & ~(size_t)255;
+  pin_out.ensure(res_off + (size_t)np * sizeof(KsbResult));
+  char* back = (char*)pin_out.p;
+  CUDA_OK(cudaEventRecord(ev_start, stream));
   launch(a);
-  CUDA_OK(cudaEventRecord(ev1, stream));
-  CUDA_OK(cudaMemcpyAsync(last_results.data(), b_results.d, (size_t)np * sizeof(KsbResult), cudaMemcpyDeviceToHost, stream));
-  int32_t flags[2] = {0, 0};
-  CUDA_OK(cudaMemcpyAsync(&flags[0], a.error_flag, 4, cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaMemcpyAsync(&flags[1], a.fiterr_count, 4, cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaMemcpyAsync(&last_node_index, a.last_node_index, 8, cudaMemcpyDeviceToHost, stream));
-  uint64_t counters[16] = {0};
-  CUDA_OK(cudaMemcpyAsync(counters, a.counters, sizeof counters, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaEventRecord(ev_stop, stream));
+  CUDA_OK(cudaMemcpyAsync(back, (char*)b_scratch.d + ctl_lo, ctl_hi - ctl_lo, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(back + res_off, b_results.d, (size_t)np * sizeof(KsbResult), cudaMemcpyDeviceToHost, stream));
   CUDA_OK(cudaStreamSynchronize(stream));
   float ms = 0;
-  CUDA_OK(cudaEventElapsedTime(&ms, ev0, ev1));
-  cudaEventDestroy(ev0);
-  cudaEventDestroy(ev1);
+  CUDA_OK(cudaEventElapsedTime(&ms, ev_start, ev_stop));
+  memcpy(last_results.data(), back + res_off, (size_t)np * sizeof(KsbResult));
+  int32_t flags[2];
+  uint64_t counters[16];
+  memcpy(&flags[0], back + ((char*)a.error_flag - (char*)a.barrier), 4);
+  memcpy(&flags[1], back + ((char*)a.fiterr_count - (char*)a.barrier), 4);
+  memcpy(&last_node_index, back + ((char*)a.last_node_index - (char*)a.barrier), 8);
+  memcpy(counters, back + ((char*)a.counters - (char*)a.barrier), sizeof counters);
   stats.last_batch_kernel_ms = ms;
-  stats.d2h_bytes += (size_t)np * sizeof(KsbResult) + 16;
+  stats.d2h_bytes += (size_t)np * sizeof(KsbResult) + (ctl_hi - ctl_lo);
   if (flags[0] != 0) {
     layout_dirty = true;  // device state is unknown: rebuild it from the host records next time
     throw std::runtime_error("device kernel stopped with error code " + std::to_string(flags[0]) +
@@ -387,6 +435,15 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     host_add_pod(p, hn);
     pods[p.key()] = HostPod{p};
   }
+}
+
+void Engine::flush() {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  if (layout_dirty) rebuild_layout();
+  if (n == 0) return;
+  sync_device();
+  CUDA_OK(cudaStreamSynchronize(stream));
 }
 
 void Engine::replay_last_batch(int iters, double* avg_ms, ksb_result* out) {

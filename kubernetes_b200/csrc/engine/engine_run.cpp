@@ -636,7 +636,8 @@ void Engine::sync_device() {
   // spread columns: capacity grows geometrically (fixed when the shard's buffers are shared with peers);
   // new columns are uploaded individually
   if (h_spread.size() > spread_cap_cols || b_spread.d == nullptr) {
-    size_t cap = std::max<size_t>(std::max<size_t>(16, min_spread_cols), h_spread.size() * 2);
+    // 256 columns up front (51 MB at 50,000 rows): growing means a free + malloc + re-upload inside a Schedule call
+    size_t cap = std::max<size_t>(std::max<size_t>(256, min_spread_cols), h_spread.size() * 2);
     if (shard_connected && cap * ln_pad * 4 > b_spread.cap)
       throw std::runtime_error("sharded engine: more SelectorSpread classes than the shared buffers were sized for");
     b_spread.ensure(cap * ln_pad * 4);

@@ -5,6 +5,7 @@
 #include "gpu_scheduler.hpp"
 
 #include <algorithm>
+#include <array>
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -46,6 +47,9 @@ void load_cluster(EngineHandle& h, const Session& s) {
     h.check(ksb_selector_owner_upsert(h.get(), kb.first, (const uint8_t*)kb.second.data(), kb.second.size()),
             "selector_owner_upsert");
   for (auto& b : s.existing_bufs) h.check(ksb_pod_add(h.get(), (const uint8_t*)b.data(), b.size()), "pod_add");
+  // the informers' initial sync ends here: the node table goes to the device now, as the reference's cache is
+  // already filled when the first pod arrives
+  h.check(ksb_flush(h.get()), "flush");
 }
 
 ksb_config config_from(const json::Value& opt) {
@@ -96,6 +100,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   CacheDecorator cache(h);
   double kernel_ms = 0, encode_ms = 0, replay_ms = 0;
   std::vector<double> lat_us;
+  std::vector<std::array<double, 3>> lat_parts;  // encode, table sync, kernel (ms) of each one-pod call
   auto t0 = std::chrono::steady_clock::now();
   if (batch == 0) {
     // the reference's own call sequence: Schedule, then AssumePod with NodeName and Assigned set
@@ -109,6 +114,11 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
               "Schedule");
       auto a1 = std::chrono::steady_clock::now();
       lat_us.push_back(std::chrono::duration<double, std::micro>(a1 - a0).count());
+      {
+        ksb_stats st1;
+        ksb_get_stats(h.get(), &st1);
+        lat_parts.push_back({st1.last_batch_encode_ms, st1.last_batch_sync_ms, st1.last_batch_kernel_ms});
+      }
       results[i] = r;
       try {
         ScheduleOutcome o = sched.outcome(pod, r, 0);
@@ -196,10 +206,25 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   out += ",\"d2h_bytes\":" + std::to_string(st.d2h_bytes);
   out += ",\"lastNodeIndex\":" + std::to_string(ksb_get_last_node_index(h.get()));
   if (!lat_us.empty()) {
-    std::vector<double> sorted = lat_us;
+    // "lat_skip": leave the first calls (cold dictionaries: first use of a label, selector class, topology key)
+    // out of the percentiles; they stay in `slowest`
+    const size_t skip = std::min<size_t>((size_t)std::max<int64_t>(0, opt.get_int("lat_skip", 0)), lat_us.size() - 1);
+    std::vector<double> sorted(lat_us.begin() + skip, lat_us.end());
     std::sort(sorted.begin(), sorted.end());
     out += ",\"p50_us\":" + std::to_string(sorted[sorted.size() / 2]);
     out += ",\"p99_us\":" + std::to_string(sorted[std::min(sorted.size() - 1, (size_t)(sorted.size() * 0.99))]);
+    out += ",\"max_us\":" + std::to_string(sorted.back());
+    // the slowest calls and where in the stream they were: first uses of a label bit, selector class or scratch size
+    std::vector<size_t> order(lat_us.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = i;
+    const size_t top = std::min<size_t>(8, order.size());
+    std::partial_sort(order.begin(), order.begin() + top, order.end(), [&](size_t a, size_t b) { return lat_us[a] > lat_us[b]; });
+    out += ",\"slowest\":[";
+    for (size_t i = 0; i < top; ++i)
+      out += std::string(i ? "," : "") + "[" + std::to_string(order[i]) + "," + std::to_string(lat_us[order[i]]) + "," +
+             std::to_string(lat_parts[order[i]][0]) + "," + std::to_string(lat_parts[order[i]][1]) + "," +
+             std::to_string(lat_parts[order[i]][2]) + "]";
+    out += "]";
   }
   if (want_results) {
     out += ",\"results\":[";
