@@ -108,13 +108,20 @@ struct EvalOut {
 
 // least_requested.go:50-61
 // ((capacity - requested) * 10) / capacity, exactly, without the 64-bit integer division routine: the
-// quotient is in [0, 10], so a double estimate corrected by at most a couple of steps is exact.
+// quotient is in [0, 10].
 __device__ __forceinline__ int64_t unused_score(int64_t requested, int64_t capacity) {
   if (capacity == 0) return 0;
   if (requested > capacity) return 0;
   if (capacity < 0) return ((capacity - requested) * 10) / capacity;  // never for real nodes; keep Go's semantics
   const int64_t num = (capacity - requested) * 10;
   if (num < 0) return num / capacity;  // negative request: not in [0, 10]
+  if (capacity < (1ll << 59)) {
+    // the quotient is the number of s in 1..10 with s * capacity <= num: ten independent compares, no division
+    int32_t cnt = 0;
+#pragma unroll
+    for (int s = 1; s <= 10; ++s) cnt += (num >= (int64_t)s * capacity) ? 1 : 0;
+    return cnt;
+  }
   int64_t q = (int64_t)__ddiv_rn((double)num, (double)capacity);
   int64_t r = num - q * capacity;
   while (r < 0) {
@@ -543,50 +550,19 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCach
 // One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads).
 __device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCache* c, int lane) {
   const size_t np = T.n_pad;
-  const int64_t* p = nullptr;
-  switch (lane) {
-    case 0: p = T.alloc_cpu + r; break;
-    case 1: p = T.alloc_mem + r; break;
-    case 2: p = T.alloc_agpu + r; break;
-    case 3: p = T.alloc_eph + r; break;
-    case 4: p = T.req_cpu + r; break;
-    case 5: p = T.req_mem + r; break;
-    case 6: p = T.req_agpu + r; break;
-    case 7: p = T.req_eph + r; break;
-    case 8: p = T.nz_cpu + r; break;
-    case 9: p = T.nz_mem + r; break;
-    default: break;
-  }
-  if (lane >= 10 && lane < 14) p = T.alloc_scalar + (size_t)(lane - 10) * np + r;
-  if (lane >= 14 && lane < 18) p = T.req_scalar + (size_t)(lane - 14) * np + r;
-  if (lane >= 18 && lane < 22) p = reinterpret_cast<const int64_t*>(T.port_any + (size_t)(lane - 18) * np + r);
-  if (lane >= 22 && lane < 26) p = reinterpret_cast<const int64_t*>(T.port_wild + (size_t)(lane - 22) * np + r);
-  if (lane >= 26 && lane < 30) p = reinterpret_cast<const int64_t*>(T.port_exact + (size_t)(lane - 26) * np + r);
-  if (lane == 30) p = reinterpret_cast<const int64_t*>(T.avoid + r);
-  // every load is issued before the first store to *c: the compiler cannot tell the generic pointers apart,
-  // so a store in between would put one L2 round trip per field on the commit path
-  const uint32_t* p2 = nullptr;
-  switch (lane) {
-    case 0: p2 = reinterpret_cast<const uint32_t*>(T.alloc_pods + r); break;
-    case 1: p2 = reinterpret_cast<const uint32_t*>(T.num_pods + r); break;
-    case 2: p2 = T.flags + r; break;
-    case 3: p2 = T.zone + r; break;
-    default: break;
-  }
-  if (lane >= 4 && lane < 4 + KSB_MAX_RES) p2 = T.dev_avail + (size_t)(lane - 4) * np + r;
+  // columns of one family are consecutive, n_pad apart, in the order of q[] (device_types.h): lanes 0..17 the
+  // int64 family from alloc_cpu on, lanes 18..29 the twelve port words, lane 30 preferAvoid (the column before them)
+  const int64_t* p = lane < 18 ? T.alloc_cpu + (size_t)lane * np + r
+                               : reinterpret_cast<const int64_t*>(T.port_any) + (ptrdiff_t)(lane == 30 ? -1 : lane - 18) * (ptrdiff_t)np + r;
+  // lanes 0..5: the u32 family from alloc_pods on (alloc_pods, num_pods, flags, zone, dev_avail[2])
+  const uint32_t* p2 = reinterpret_cast<const uint32_t*>(T.alloc_pods) + (size_t)(lane < 4 + KSB_MAX_RES ? lane : 0) * np + r;
   int64_t v = 0;
   uint32_t v2 = 0;
   if (lane < 31) v = __ldcg(p);
   if (lane < 4 + KSB_MAX_RES) v2 = __ldcg(p2);
   if (lane < 31) c->q[lane] = v;
-  switch (lane) {
-    case 0: c->apods = (int32_t)v2; break;
-    case 1: c->npods = (int32_t)v2; break;
-    case 2: c->flags = v2; break;
-    case 3: c->zone = v2; break;
-    default: break;
-  }
-  if (lane >= 4 && lane < 4 + KSB_MAX_RES) c->avail[lane - 4] = v2;
+  // apods, npods, flags, zone, avail[0..1] are consecutive 32-bit fields of the entry
+  if (lane < 4 + KSB_MAX_RES) reinterpret_cast<uint32_t*>(&c->apods)[lane] = v2;
   if (lane == 31) c->row = r;
 }
 
@@ -641,34 +617,37 @@ struct CommitRec {
   KsbResult res;
 };
 
-// Decider side of the assume step: the row-cache entry only (shared memory).
-__device__ __forceinline__ void commit_cache_only(RowCache* c, const PodView& pv, const uint32_t* picks, int lane) {
+// Decider side of the assume step (NodeInfo.AddPod, schedulercache/node_info.go:329-356): the row-cache entry and,
+// in the same pass, the record the writer warp copies to the table. Lane l owns q[l]; the header's int64 fields
+// are read as an array (req 0..3, nz 4..5, add 6..9, scalar_req 10..13, scalar_add 14..17).
+__device__ __forceinline__ void commit_and_record(RowCache* c, CommitRec* rec, const PodView& pv, const uint32_t* picks,
+                                                  int row, int rank, int lane) {
   const KsbPodHeader* h = pv.h;
-  int64_t add = 0;
-  switch (lane) {
-    case 4: add = h->add_cpu; break;
-    case 5: add = h->add_mem; break;
-    case 6: add = h->add_agpu; break;
-    case 7: add = h->add_eph; break;
-    case 8: add = h->nz_cpu; break;
-    case 9: add = h->nz_mem; break;
-    default: break;
-  }
-  if (lane >= 14 && lane < 18) add = h->scalar_add[lane - 14];
-  if (add != 0) c->q[lane] += add;
-  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30)
-    c->q[lane] = (int64_t)((uint64_t)c->q[lane] | pv.ports[3 * KSB_PORT_WORDS + (lane - 18)]);
-  if (lane == 31) {
-    c->npods += 1;
-    if (h->n_ext) {
-      uint32_t take[KSB_MAX_RES];
+  const int64_t* hq = reinterpret_cast<const int64_t*>(h);
+  if (lane < 31) {
+    const int ai = (lane >= 4 && lane < 8) ? lane + 2 : ((lane == 8 || lane == 9) ? lane - 4 : ((lane >= 14 && lane < 18) ? lane : -1));
+    int64_t v = c->q[lane];
+    if (ai >= 0) v += hq[ai];
+    if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30) v = (int64_t)((uint64_t)v | pv.ports[3 * KSB_PORT_WORDS + (lane - 18)]);
+    c->q[lane] = v;
+    rec->q[lane] = v;
+  } else {
+    const int32_t npods = c->npods + 1;
+    c->npods = npods;
+    rec->npods = npods;
+    uint32_t take[KSB_MAX_RES];
 #pragma unroll
-      for (int s = 0; s < KSB_MAX_RES; ++s) take[s] = 0;
-      for (int i = 0; i < h->n_ext; ++i)
-        if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
+    for (int s = 0; s < KSB_MAX_RES; ++s) take[s] = 0;
+    for (int i = 0; i < h->n_ext; ++i)
+      if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
 #pragma unroll
-      for (int s = 0; s < KSB_MAX_RES; ++s) c->avail[s] &= ~take[s];
+    for (int s = 0; s < KSB_MAX_RES; ++s) {
+      const uint32_t av = c->avail[s] & ~take[s];
+      c->avail[s] = av;
+      rec->avail[s] = av;
     }
+    rec->row = row;
+    rec->rank = rank;
   }
 }
 
@@ -677,23 +656,10 @@ __device__ __forceinline__ void commit_cache_only(RowCache* c, const PodView& pv
 __device__ __forceinline__ void write_through(const KsbNodeTable& T, const CommitRec& rec, const KsbPodHeader* h, int lane) {
   const size_t np = T.n_pad;
   const int r = rec.row;
-  int64_t* dst = nullptr;
-  switch (lane) {
-    case 4: dst = T.req_cpu + r; break;
-    case 5: dst = T.req_mem + r; break;
-    case 6: dst = T.req_agpu + r; break;
-    case 7: dst = T.req_eph + r; break;
-    case 8: dst = T.nz_cpu + r; break;
-    case 9: dst = T.nz_mem + r; break;
-    default: break;
-  }
-  if (lane >= 14 && lane < 18 && h->scalar_add[lane - 14] != 0) dst = T.req_scalar + (size_t)(lane - 14) * np + r;
-  if (dst) *dst = rec.q[lane];
-  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30) {
-    const int j = lane - 18;
-    uint64_t* pd = (j < 4 ? T.port_any : (j < 8 ? T.port_wild : T.port_exact)) + (size_t)(j & 3) * np + r;
-    *pd = (uint64_t)rec.q[lane];
-  }
+  // requested / nonzero columns (lanes 4..9) and touched scalar columns (14..17): q[] order = column order
+  const bool own = (lane >= 4 && lane < 10) || (lane >= 14 && lane < 18 && h->scalar_add[lane - 14] != 0);
+  if (own) T.alloc_cpu[(size_t)lane * np + r] = rec.q[lane];
+  if ((h->flags & PF_HAS_PORTS) && lane >= 18 && lane < 30) T.port_any[(size_t)(lane - 18) * np + r] = (uint64_t)rec.q[lane];
   if (lane == 31) {
     T.num_pods[r] = rec.npods;
     if (h->n_ext)
@@ -1299,26 +1265,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 __syncwarp();
               }
               if (h->n_ext) {
-                if (lane == 0) {
-                  uint32_t rs_;
-                  int32_t base_;
-                  eval_cached(P.table, S.rows[idx], pv, 0u, &rs_, &base_, picks);
-                }
+                if (lane == 0)  // the chosen row fits, so the device selection succeeds: only its picks are needed
+                  select_devices(P.table, chosen, pv, S.rows[idx].flags, S.rows[idx].avail, picks);
 #pragma unroll
                 for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
               }
-              commit_cache_only(S.rows + idx, pv, picks, lane);
-              __syncwarp();
-              const RowCache& c = S.rows[idx];
-              if (lane < 31) {
-                rec.q[lane] = c.q[lane];
-              } else {
-                rec.npods = c.npods;
-#pragma unroll
-                for (int s2 = 0; s2 < KSB_MAX_RES; ++s2) rec.avail[s2] = c.avail[s2];
-                rec.row = chosen;
-                rec.rank = chosen_rank;
-              }
+              commit_and_record(S.rows + idx, &rec, pv, picks, chosen, chosen_rank, lane);
             } else {
               if (h->n_ext) {
                 if (lane == 0) {
