@@ -19,7 +19,7 @@ namespace ksb {
 
 namespace {
 struct ScratchLayout {
-  size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, barrier, error_flag, fiterr_count, last_index,
+  size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, seg_mask, barrier, error_flag, fiterr_count, last_index,
       group_done, counters, ghist, release, xbar, xstate, peers, fiterr_hist, total;
 };
 ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
@@ -51,6 +51,7 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   L.reasons = take((size_t)G * n_pad * 4);
   L.seg_max = take((size_t)G * nseg * 4);
   L.seg_cnt = take((size_t)G * nseg * 4);
+  L.seg_mask = take((size_t)G * nseg * 32);
   L.total = off;
   return L;
 }
@@ -111,6 +112,7 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.reasons = (uint32_t*)(base + L.reasons);
   a.seg_max = (int32_t*)(base + L.seg_max);
   a.seg_cnt = (int32_t*)(base + L.seg_cnt);
+  a.seg_mask = (uint32_t*)(base + L.seg_mask);
   a.barrier = (uint32_t*)(base + L.barrier);
   a.error_flag = (int32_t*)(base + L.error_flag);
   a.fiterr_count = (int32_t*)(base + L.fiterr_count);
@@ -162,6 +164,7 @@ void Engine::launch(const KsbBatchArgs& a) {
     self->reasons = a.reasons;
     self->seg_max = a.seg_max;
     self->seg_cnt = a.seg_cnt;
+    self->seg_mask = a.seg_mask;
     self->results = a.results;
     self->last_node_index = a.last_node_index;
     self->nseg = a.nseg;
@@ -197,6 +200,7 @@ void Engine::launch(const KsbBatchArgs& a) {
     self.reasons = a.reasons;
     self.seg_max = a.seg_max;
     self.seg_cnt = a.seg_cnt;
+    self.seg_mask = a.seg_mask;
     self.results = a.results;
     self.last_node_index = a.last_node_index;
     self.nseg = a.nseg;
@@ -211,6 +215,7 @@ void Engine::launch(const KsbBatchArgs& a) {
     pt[0].reasons = a.reasons;
     pt[0].seg_max = a.seg_max;
     pt[0].seg_cnt = a.seg_cnt;
+    pt[0].seg_mask = a.seg_mask;
     pt[0].results = a.results;
     pt[0].last_node_index = a.last_node_index;
     pt[0].nseg = a.nseg;
@@ -231,6 +236,7 @@ void Engine::launch(const KsbBatchArgs& a) {
       P.reasons = (uint32_t*)(sb + Lq.reasons);
       P.seg_max = (int32_t*)(sb + Lq.seg_max);
       P.seg_cnt = (int32_t*)(sb + Lq.seg_cnt);
+      P.seg_mask = (uint32_t*)(sb + Lq.seg_mask);
       P.last_node_index = (uint64_t*)(sb + Lq.last_index);
       P.results = (KsbResult*)m.p[8];
       P.nseg = nseg_q;

@@ -668,6 +668,46 @@ __device__ __forceinline__ void write_through(const KsbNodeTable& T, const Commi
   }
 }
 
+// Position of the (n+1)-th set bit of w counted from bit 31 downwards (w has more than n set bits).
+__device__ __forceinline__ int nth_set_from_top(uint32_t w, int n) {
+  uint32_t r = __brev(w);  // n-th set bit from the bottom of r
+  int p = 0;
+#pragma unroll
+  for (int width = 16; width >= 1; width >>= 1) {
+    const int c = __popc(r & ((1u << width) - 1u));
+    if (n >= c) {
+      n -= c;
+      p += width;
+      r >>= width;
+    }
+  }
+  return 31 - p;
+}
+
+// One warp: cnt[lo..hi) holds non-negative counts; walking the entries from hi-1 down to lo, find the entry in
+// which the rem-th item (0-based) lies. Returns its index and leaves in `rem` the item's rank inside that entry;
+// -1 if the counts hold fewer than rem+1 items.
+__device__ __forceinline__ int desc_select(const int32_t* cnt, int lo, int hi, int& rem, int lane) {
+  for (int top = hi; top > lo; top -= 32) {
+    const int i = top - 1 - lane;  // lane 0 = highest entry
+    const int c = i >= lo ? cnt[i] : 0;
+    int incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    const uint32_t hit = __ballot_sync(0xffffffffu, rem >= incl - c && rem < incl);
+    if (hit) {
+      const int src = __ffs(hit) - 1;
+      rem -= __shfl_sync(0xffffffffu, incl - c, src);
+      return top - 1 - src;
+    }
+    rem -= __shfl_sync(0xffffffffu, incl, 31);
+  }
+  return -1;
+}
+
 // dynamic shared memory carve-up
 struct Smem {
   KsbPodHeader* hdr;   // [kMaxG]
@@ -677,11 +717,12 @@ struct Smem {
   int32_t* part;       // [kMaxG][kWarps][8] per-warp partials of the Reduce inputs
   KsbNorms* norm;      // [kMaxG]
   int32_t* max_zone;   // [kMaxG]
-  int32_t* wstat;      // [kMaxG][kWarps][2] per-warp (max, count) of one segment
+  int32_t* wstat;      // [kMaxG][kWarps][3] per-warp (max, count, holder mask) of one segment
   int32_t* seg_max;    // [kSegCache] block 0: [pod][segment]
   int32_t* seg_cnt;    // [kSegCache]
   RowCache* rows;      // [kMaxG] block 0: rows changed in this group
   int32_t* fe_hist;    // [KSB_REASON_BITS] block 0: FitError histogram correction for changed rows
+  int32_t* bsum;       // block 0: [pod][32-segment block] holders of the pod's maximum, per block of segments
   CommitRec* recs;     // [kMaxG] block 0: decider -> writer hand-off
 };
 
@@ -697,19 +738,20 @@ __device__ __host__ __forceinline__ size_t smem_layout(size_t* offs, int zone_st
   take(kMaxG * 4);
   take((size_t)kMaxG * zone_stride * 4);
   take((size_t)kMaxG * kWarps * 8 * 4);   // part: phase 1/2 reduction scratch ...
-  take((size_t)kMaxG * kWarps * 2 * 4);   // wstat: ... contiguous with part; phase 3 reuses both as S.recs
+  take((size_t)kMaxG * kWarps * 3 * 4);   // wstat: ... contiguous with part; phase 3 reuses both as S.recs
   take(sizeof(KsbNorms) * kMaxG);
   take(kMaxG * 4);
   take((size_t)kSegCache * 4);
   take((size_t)kSegCache * 4);
   take(sizeof(RowCache) * kMaxG);
   take((size_t)kMaxG * KSB_REASON_BITS * 4);
-  static_assert(sizeof(CommitRec) * kMaxG <= (size_t)kMaxG * kWarps * 10 * 4, "commit records alias part + wstat");
+  take((size_t)(kSegCache / 32 + kMaxG) * 4);  // bsum
+  static_assert(sizeof(CommitRec) * kMaxG <= (size_t)kMaxG * kWarps * 11 * 4, "commit records alias part + wstat");
   return off;
 }
 
 __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
-  size_t o[12];
+  size_t o[13];
   smem_layout(o, zone_stride);
   Smem s;
   s.hdr = (KsbPodHeader*)(base + o[0]);
@@ -724,6 +766,7 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
   s.seg_cnt = (int32_t*)(base + o[9]);
   s.rows = (RowCache*)(base + o[10]);
   s.fe_hist = (int32_t*)(base + o[11]);
+  s.bsum = (int32_t*)(base + o[12]);
   s.recs = (CommitRec*)(base + o[4]);
   return s;
 }
@@ -738,6 +781,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   __shared__ KsbPeer s_peers[KSB_MAX_RANKS];  // rank 0, block 0: the shard table, read once
   __shared__ volatile int32_t s_ready[kMaxG]; // decider -> writer: record g is complete
   __shared__ volatile int32_t s_stop;         // decider -> writer: pods decided in this group (-1: still deciding)
+  __shared__ int32_t s_gmax0[kMaxG], s_k0[kMaxG];  // block 0: per pod, maximum score at group start and its holders
+  __shared__ uint32_t s_words[kWarps];         // block 0: holder mask of the segment being searched
 
   const KsbNodeTable& T = A.table;
   const int tid = threadIdx.x;
@@ -978,10 +1023,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             A.score[(size_t)g * np + r] = s;
           }
           int32_t wm = warp_max(s);
-          int32_t wc = warp_sum((s == wm && s != INT32_MIN) ? 1 : 0);
+          const uint32_t wmask = __ballot_sync(0xffffffffu, s == wm && s != INT32_MIN);
           if (lane == 0) {
-            S.wstat[(g * kWarps + warp) * 2] = wm;
-            S.wstat[(g * kWarps + warp) * 2 + 1] = wc;
+            S.wstat[(g * kWarps + warp) * 3] = wm;
+            S.wstat[(g * kWarps + warp) * 3 + 1] = __popc(wmask);
+            S.wstat[(g * kWarps + warp) * 3 + 2] = (int32_t)wmask;
           }
         }
         __syncthreads();
@@ -992,7 +1038,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           if (prio) {
             int32_t m = INT32_MIN, c = 0;
             for (int w = 0; w < kWarps; ++w) {
-              int32_t wm = S.wstat[(g * kWarps + w) * 2], wc = S.wstat[(g * kWarps + w) * 2 + 1];
+              int32_t wm = S.wstat[(g * kWarps + w) * 3], wc = S.wstat[(g * kWarps + w) * 3 + 1];
               if (wm > m) {
                 m = wm;
                 c = wc;
@@ -1003,6 +1049,14 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (m == INT32_MIN) c = 0;
             A.seg_max[(size_t)g * nseg + seg] = m;
             A.seg_cnt[(size_t)g * nseg + seg] = c;
+            // which rows hold the segment's maximum: word w = rows 32w..32w+31 of the segment
+            uint32_t mw[kWarps];
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w)
+              mw[w] = (S.wstat[(g * kWarps + w) * 3] == m && m != INT32_MIN) ? (uint32_t)S.wstat[(g * kWarps + w) * 3 + 2] : 0u;
+            uint4* mp = reinterpret_cast<uint4*>(A.seg_mask + ((size_t)g * nseg + seg) * kWarps);
+            mp[0] = make_uint4(mw[0], mw[1], mw[2], mw[3]);
+            mp[1] = make_uint4(mw[4], mw[5], mw[6], mw[7]);
           }
         }
         __syncthreads();
@@ -1018,17 +1072,42 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       const int nsegT = A.nseg_total;
       const int sps = A.segs_per_shard;
       const int R = A.n_ranks;
-      // prefetch the segment statistics of every pod that will be ranked by score
-      for (int g = 0; g < Gc; ++g) {
+      // Segment statistics of every pod that will be ranked by score, one pod per warp: copy them to shared memory,
+      // then the pod's maximum over all segments, the number of rows holding it (k0), the count array with
+      // non-maximal segments zeroed, and its sums over blocks of 32 segments for the two-level rank-select
+      const int nb = (nsegT + 31) >> 5;
+      for (int g = warp; g < Gc; g += kWarps) {
         const KsbPodHeader* h = S.hdr + g;
         const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[g].fit_count >= 2;
         if (!prio) continue;
-        for (int i = tid; i < nsegT; i += kThreads) {
+        int32_t* smax = S.seg_max + g * nsegT;
+        int32_t* scnt = S.seg_cnt + g * nsegT;
+        int32_t m = INT32_MIN;
+        for (int i = lane; i < nsegT; i += 32) {
           const int q = i / sps;
           const KsbPeer& P = s_peers[q];
           const int ls = i - q * sps;
-          S.seg_max[g * nsegT + i] = __ldcv(P.seg_max + (size_t)g * P.nseg + ls);
-          S.seg_cnt[g * nsegT + i] = __ldcv(P.seg_cnt + (size_t)g * P.nseg + ls);
+          const int32_t v = __ldcv(P.seg_max + (size_t)g * P.nseg + ls);
+          smax[i] = v;
+          scnt[i] = __ldcv(P.seg_cnt + (size_t)g * P.nseg + ls);
+          m = max(m, v);
+        }
+        const int32_t gmax0 = warp_max(m);
+        int32_t k0 = 0;
+        for (int j = 0; j < nb; ++j) {
+          const int i = j * 32 + lane;
+          int32_t c = 0;
+          if (i < nsegT) {
+            c = (smax[i] == gmax0) ? scnt[i] : 0;
+            scnt[i] = c;
+          }
+          c = warp_sum(c);
+          if (lane == 0) S.bsum[g * nb + j] = c;
+          k0 += c;
+        }
+        if (lane == 0) {
+          s_gmax0[g] = gmax0;
+          s_k0[g] = k0;
         }
       }
       if (tid < kMaxG) s_ready[tid] = 0;
@@ -1134,85 +1213,79 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               chosen_rank = min(R - 1, (nm.one_row / kSeg) / sps);
               chosen = nm.one_row - s_peers[chosen_rank].table.row_base;
             } else {
-              // (2) selectHost over group-start segment statistics patched with the changed rows
+              // (2) selectHost (generic_scheduler.go:177-192): lastNodeIndex % k over the rows tied at the maximum, in
+              //     descending row order, from the group-start statistics patched with the changed rows
               int32_t* smax = S.seg_max + g * nsegT;
               int32_t* scnt = S.seg_cnt + g * nsegT;
-              int32_t m = cnew;
-              for (int i = lane; i < nsegT; i += 32) m = max(m, smax[i]);
-              const int32_t gmax = warp_max(m);
-              for (int i = lane; i < nsegT; i += 32) scnt[i] = (smax[i] == gmax) ? scnt[i] : 0;
-              __syncwarp();
-              if (lane < ncr) {
-                if (cold == gmax) atomicAdd(&scnt[cseg], -1);
-                if (cnew == gmax) atomicAdd(&scnt[cseg], 1);
-              }
-              __syncwarp();
-              int32_t c = 0;
-              for (int i = lane; i < nsegT; i += 32) c += scnt[i];
-              const int32_t k = warp_sum(c);
-              if (k <= 0) break;  // every holder of the group-start maximum changed and fell below it
-              int rem = (last_index >> 32) == 0 ? (int)((uint32_t)last_index % (uint32_t)k) : (int)(last_index % (uint64_t)k);
-              int found = -1;
-              for (int hi = nsegT; hi > 0 && found < 0; hi -= 32) {
-                const int sg = hi - 1 - lane;  // lane 0 = highest segment
-                const int cnt = sg >= 0 ? scnt[sg] : 0;
-                int incl = cnt;
-#pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                  int t = __shfl_up_sync(0xffffffffu, incl, d);
-                  if (lane >= d) incl += t;
-                }
-                const int total = __shfl_sync(0xffffffffu, incl, 31);
-                const bool here = rem >= incl - cnt && rem < incl;
-                const uint32_t bal = __ballot_sync(0xffffffffu, here);
-                if (bal) {
-                  const int src = __ffs(bal) - 1;
-                  found = __shfl_sync(0xffffffffu, sg, src);
-                  rem -= __shfl_sync(0xffffffffu, incl - cnt, src);
-                } else {
-                  rem -= total;
-                }
-              }
+              int32_t* bsum = S.bsum + g * nb;
+              const int32_t gmax0 = s_gmax0[g];
+              const int32_t gmax = max(gmax0, warp_max(cnew));
               int pick = -1, pick_rank = 0;
-              if (found >= 0) {
-                // rank-select inside the segment, rows from the highest down: 8 rows per lane
-                pick_rank = found / sps;
-                const KsbPeer& P = s_peers[pick_rank];
-                const int base_row = (found - P.seg_base) * kSeg;
-                const size_t pn = P.table.n_pad;
-                int32_t v[kSeg / 32];
-#pragma unroll
-                for (int j = 0; j < kSeg / 32; ++j) {
-                  const int r = base_row + j * 32 + lane;
-                  v[j] = r < P.table.n ? __ldcv(P.score + (size_t)g * pn + r) : INT32_MIN;
+              if (gmax > gmax0) {
+                // a changed row now beats every row of the snapshot: the ties are changed rows only
+                const bool cand = lane < ncr && cnew == gmax;
+                const uint32_t cb = __ballot_sync(0xffffffffu, cand);
+                const int k = __popc(cb);
+                const int rem = (int)(last_index % (uint64_t)k);
+                const int grow = cand ? s_peers[crank].table.row_base + crow : -1;
+                int above = 0;
+                for (uint32_t mm = cb; mm; mm &= mm - 1) {
+                  const int gr = __shfl_sync(0xffffffffu, grow, __ffs(mm) - 1);
+                  above += (gr > grow) ? 1 : 0;
                 }
-                uint32_t inseg = __ballot_sync(0xffffffffu, lane < ncr && cseg == found);
-                while (inseg) {  // fresh scores override the stash on changed rows of this segment
-                  const int i = __ffs(inseg) - 1;
-                  inseg &= inseg - 1;
-                  const int cr = __shfl_sync(0xffffffffu, crow, i);
-                  const int32_t cn = __shfl_sync(0xffffffffu, cnew, i);
-                  const int32_t co = __shfl_sync(0xffffffffu, cold, i);
-                  const int rel = cr - base_row;
-                  if ((rel & 31) == lane && !(cn == INT32_MIN && co == INT32_MIN)) {
-#pragma unroll
-                    for (int j = 0; j < kSeg / 32; ++j)
-                      if (j == (rel >> 5)) v[j] = cn;
-                  }
+                const uint32_t hit = __ballot_sync(0xffffffffu, cand && above == rem);
+                const int src = __ffs(hit) - 1;
+                pick = __shfl_sync(0xffffffffu, crow, src);
+                pick_rank = __shfl_sync(0xffffffffu, crank, src);
+              } else {
+                const int delta = (lane < ncr) ? ((cnew == gmax ? 1 : 0) - (cold == gmax ? 1 : 0)) : 0;
+                if (delta != 0) {
+                  atomicAdd(&scnt[cseg], delta);
+                  atomicAdd(&bsum[cseg >> 5], delta);
                 }
-#pragma unroll
-                for (int j = kSeg / 32 - 1; j >= 0; --j) {
-                  const uint32_t bal = __ballot_sync(0xffffffffu, v[j] == gmax);
-                  const int cnt = __popc(bal);
-                  if (pick < 0) {
-                    if (rem < cnt) {
-                      // the tie with exactly `rem` ties above it in this 32-row slice
-                      const bool me = ((bal >> lane) & 1u) && __popc(bal >> 1 >> lane) == rem;
-                      const int bit = __ffs(__ballot_sync(0xffffffffu, me)) - 1;
-                      pick = base_row + j * 32 + bit;
-                    } else {
-                      rem -= cnt;
+                const int32_t k = s_k0[g] + warp_sum(delta);
+                if (k <= 0) break;  // every holder of the group-start maximum changed and fell below it
+                __syncwarp();
+                int rem = (last_index >> 32) == 0 ? (int)((uint32_t)last_index % (uint32_t)k) : (int)(last_index % (uint64_t)k);
+                // level 1: the block of 32 segments, from the top; level 2: the segment inside it
+                int blk = 0;
+                if (nb > 1) blk = desc_select(bsum, 0, nb, rem, lane);
+                const int found = blk < 0 ? -1 : desc_select(scnt, blk * 32, min(nsegT, blk * 32 + 32), rem, lane);
+                if (found >= 0) {
+                  // level 3: the row inside the segment, from its holder mask (phase 2) patched with the changed rows
+                  pick_rank = min(R - 1, found / sps);
+                  const KsbPeer& P = s_peers[pick_rank];
+                  const int base_row = (found - P.seg_base) * kSeg;
+                  uint32_t word = 0;
+                  if (lane < kWarps && smax[found] == gmax)
+                    word = __ldcv(P.seg_mask + ((size_t)g * P.nseg + (found - P.seg_base)) * kWarps + lane);
+                  const uint32_t inseg = __ballot_sync(0xffffffffu, lane < ncr && cseg == found && crank == pick_rank);
+                  if (inseg) {
+                    if (lane < kWarps) s_words[lane] = word;
+                    __syncwarp();
+                    if ((inseg >> lane) & 1u) {
+                      const int rel = crow - base_row;
+                      if (cnew == gmax) atomicOr(&s_words[rel >> 5], 1u << (rel & 31));
+                      else atomicAnd(&s_words[rel >> 5], ~(1u << (rel & 31)));
                     }
+                    __syncwarp();
+                    if (lane < kWarps) word = s_words[lane];
+                  }
+                  // words from the top: lane w holds rows 32w..32w+31; ties above lane w = holders in words > w
+                  const int cw = __popc(word);
+                  int above = 0;
+#pragma unroll
+                  for (int w = 1; w < kWarps; ++w) {
+                    const int t = __shfl_down_sync(0xffffffffu, cw, w);
+                    if (lane + w < kWarps) above += t;
+                  }
+                  const uint32_t hit = __ballot_sync(0xffffffffu, lane < kWarps && rem >= above && rem < above + cw);
+                  if (hit) {
+                    const int src = __ffs(hit) - 1;
+                    const uint32_t wsel = __shfl_sync(0xffffffffu, word, src);
+                    const int skip = rem - __shfl_sync(0xffffffffu, above, src);
+                    const int bit = nth_set_from_top(wsel, skip);
+                    pick = base_row + src * 32 + bit;
                   }
                 }
               }
@@ -1464,7 +1537,8 @@ constexpr size_t kNaScore = kNaRawBase + na_align((size_t)KSB_NOALLOC_MAX_ROWS *
 constexpr size_t kNaReasons = kNaScore + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
 constexpr size_t kNaSegMax = kNaReasons + na_align((size_t)KSB_NOALLOC_MAX_ROWS * 4);
 constexpr size_t kNaSegCnt = kNaSegMax + na_align(kNaSegs * 4);
-constexpr size_t kNaBarrier = kNaSegCnt + na_align(kNaSegs * 4);
+constexpr size_t kNaSegMask = kNaSegCnt + na_align(kNaSegs * 4);
+constexpr size_t kNaBarrier = kNaSegMask + na_align(kNaSegs * 32);
 constexpr size_t kNaError = kNaBarrier + 256;
 constexpr size_t kNaFitCount = kNaError + 256;
 constexpr size_t kNaLastIndex = kNaFitCount + 256;
@@ -1519,6 +1593,7 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->reasons = (uint32_t*)(b + kNaReasons);
   a->seg_max = (int32_t*)(b + kNaSegMax);
   a->seg_cnt = (int32_t*)(b + kNaSegCnt);
+  a->seg_mask = (uint32_t*)(b + kNaSegMask);
   a->barrier = (uint32_t*)(b + kNaBarrier);
   a->error_flag = (int32_t*)(b + kNaError);
   a->fiterr_count = (int32_t*)(b + kNaFitCount);

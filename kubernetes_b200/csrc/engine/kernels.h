@@ -15,6 +15,7 @@ struct KsbPeer {
   uint32_t* reasons;
   int32_t* seg_max;
   int32_t* seg_cnt;
+  uint32_t* seg_mask;
   KsbResult* results;
   uint64_t* last_node_index;
   int32_t nseg;      // 256-row segments of this shard
@@ -41,6 +42,7 @@ struct KsbBatchArgs {
   uint32_t* reasons;            // [group_size][n_pad] failure-reason masks
   int32_t* seg_max;             // [group_size][nseg]
   int32_t* seg_cnt;             // [group_size][nseg]
+  uint32_t* seg_mask;           // [group_size][nseg][8] rows of the segment that hold its maximum, one bit per row
   uint32_t* barrier;            // grid barrier counter, zero at launch
   int32_t* error_flag;
   int32_t* fiterr_count;
