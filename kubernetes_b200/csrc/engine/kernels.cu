@@ -44,6 +44,12 @@
 #include "device_types.h"
 #include "kernels.h"
 
+// 1: the decider warp also reads the cycle counter between its per-pod steps (ksb_stats.stage_cycles[8..10]);
+// costs a few percent of phase 3, so it is a build option (make FINE_TIMING=1)
+#ifndef KSB_FINE_TIMING
+#define KSB_FINE_TIMING 0
+#endif
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -501,7 +507,7 @@ constexpr uint32_t kDynMask = 0x1ffu | (1u << RB_PORTS) | (0xfu << RB_EXT0) | (1
 // Must stay in step with eval_node (the group-size tests compare the two paths bit for bit).
 __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCache& c, const PodView& pv,
                                             uint32_t static_reasons, uint32_t* reasons_out, int32_t* base_out,
-                                            uint32_t* picks) {
+                                            uint32_t* picks, bool want_score) {
   const KsbPodHeader* h = pv.h;
   const uint32_t pf = h->flags;
   uint32_t reasons = static_reasons;
@@ -531,6 +537,9 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCach
     uint32_t local[KSB_MAX_EXT];
     reasons |= select_devices(T, c.row, pv, c.flags, c.avail, picks ? picks : local);
   }
+  *reasons_out = reasons;
+  *base_out = 0;
+  if (!want_score) return;
   const int64_t acpu = c.q[0], amem = c.q[1];
   const int64_t cpu = h->nz_cpu + c.q[8];
   const int64_t mem = h->nz_mem + c.q[9];
@@ -544,7 +553,6 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCach
   }
   const int32_t av = ((uint64_t)c.q[30] & h->avoid_mask) ? 0 : 10;
   *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
-  *reasons_out = reasons;
 }
 
 // One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads).
@@ -1115,19 +1123,23 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       __syncthreads();
       long long t3[6] = {0, 0, 0, 0, 0, 0};
       long long m3 = clock64();
+#if KSB_FINE_TIMING
 #define KSB_T3(i)                      \
   do {                                 \
     long long now_ = clock64();        \
     t3[i] += now_ - m3;                \
     m3 = now_;                         \
   } while (0)
+#else
+#define KSB_T3(i) ((void)m3)
+#endif
       KSB_T3(0);
       if (warp == 0) {
         int ncr = 0;       // rows in the cache (uniform across the warp)
         int consumed = 0;
         // group-start results of the NEXT pod on the cached rows, requested one pod ahead so that their L2
         // round trip overlaps the current pod's commit
-        int4 nx_raw = make_int4(INT32_MIN, 0, 0, 0);
+        int32_t nx_base = INT32_MIN;  // raw.x: the base score at group start, INT32_MIN = the row did not fit
         uint32_t nx_reasons = 0;
         int32_t nx_score = INT32_MIN;
         for (int g = 0; g < Gc; ++g) {
@@ -1139,7 +1151,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           KsbResult res;
           res.status = 0;
           res.row = -1;
-          res.num_filtered = nm.fit_count;
+          res.num_filtered = nm.fit_count;  // lowered below when rows left the filtered list inside the group
           res.fiterr_slot = -1;
           res.score = 0;
 #pragma unroll
@@ -1159,21 +1171,40 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               crank = c.pad;
               const KsbPeer& P = s_peers[crank];
               cseg = P.seg_base + crow / kSeg;
-              const int4 raw0 = nx_raw;
+              const int32_t base0 = nx_base;
               old_reasons = nx_reasons;
               if (prio) cold = nx_score;
               int32_t base;
-              eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr);
-              const bool was_fit = raw0.x != INT32_MIN;
+              eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
+              const bool was_fit = base0 != INT32_MIN;
               flip = was_fit && new_reasons != 0;  // a fit row turned unfit: the Reduce inputs may have moved
               if (prio && was_fit && new_reasons == 0)
-                cnew = final_score(T, nm, S.zone + g * zs, S.max_zone[g], base, raw0.y, (int32_t)((uint32_t)raw0.z >> 24),
-                                   (uint32_t)raw0.z & 0xffffffu, raw0.w, c.zone);
-              else
-                cold = INT32_MIN;
-              if (!was_fit) cold = INT32_MIN;
+                // final_score = base + terms that depend only on group-start values: the new total is the old one
+                // with the base score exchanged
+                cnew = (int32_t)((uint32_t)cold - (uint32_t)base0 + (uint32_t)base);
+              if (!prio || !was_fit) cold = INT32_MIN;
             }
-            if (__any_sync(0xffffffffu, flip)) break;  // speculation dropped: this pod opens the next group
+            int fit_now = nm.fit_count;
+            {
+              // A row that fit at group start and no longer does leaves the filtered list. The Reduce inputs of the
+              // snapshot stay valid if the row cannot have been a holder of any of them: then it simply stops being
+              // a candidate. Otherwise speculation is dropped and this pod opens the next group.
+              const uint32_t fb = __ballot_sync(0xffffffffu, flip);
+              if (fb) {
+                bool safe = true;
+                if (flip) {
+                  const KsbPeer& P = s_peers[crank];
+                  const int4 raw = __ldcv(P.raw + (size_t)g * P.table.n_pad + crow);
+                  const int32_t na = raw.y, tt = (int32_t)((uint32_t)raw.z >> 24), ipa = raw.w;
+                  const uint32_t sc = (uint32_t)raw.z & 0xffffffu;
+                  safe = (nm.max_na == 0 || na < nm.max_na) && (nm.max_tt == 0 || tt < nm.max_tt) && sc == 0 &&
+                         (nm.ipa_max == nm.ipa_min || (ipa > nm.ipa_min && ipa < nm.ipa_max));
+                }
+                fit_now -= __popc(fb);
+                if (!__all_sync(0xffffffffu, safe) || fit_now < 2) break;
+              }
+            }
+            res.num_filtered = fit_now;
             KSB_T3(1);  // changed rows
 
             if (nm.fit_count >= 2 && (h->flags & PF_PRIO_ERROR)) {
@@ -1321,7 +1352,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (prow >= 0) {
               const KsbPeer& P = s_peers[prank];
               const size_t at = (size_t)(g + 1) * P.table.n_pad + prow;
-              nx_raw = __ldcv(P.raw + at);
+              nx_base = __ldcv(&P.raw[at].x);
               nx_reasons = __ldcv(P.reasons + at);
               nx_score = __ldcv(P.score + at);
             }
