@@ -94,7 +94,8 @@ struct KsbNodeTable {
 struct KsbExtEntry {
   int32_t num;
   uint8_t rslot;  // 255: resource name unknown to every node
-  uint8_t pad[3];
+  uint8_t pad;
+  uint16_t cls_id;  // interned (resource slot, device-class mask); 0 = not interned. Equal ids = equal masks.
 };
 
 struct __attribute__((aligned(16))) KsbPodHeader {

@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <array>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -141,6 +142,7 @@ class Engine {
   std::vector<LabelBitDef> label_defs;
   // inverted index over the retained node labels (rows by "key\0value" and by key): a label bit interned
   // later fills its column from the matching rows only instead of scanning every node
+  std::map<std::array<uint64_t, KSB_CLASS_WORDS + 1>, uint16_t> ext_mask_ids;  // (device-class mask, slot) -> id
   // label -> rows index (built with the layout): rows holding a key=value pair; rows holding a key, with the value
   std::unordered_map<std::string, std::vector<int>> rows_by_pair;
   std::unordered_map<std::string, std::vector<std::pair<int, const std::string*>>> rows_by_key;

@@ -366,6 +366,15 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
       }
     }
     extcls.insert(extcls.end(), cm, cm + KSB_CLASS_WORDS);
+    // equal (slot, mask) pairs get one id: the kernel keeps per-row match masks under it while a group commits
+    std::array<uint64_t, KSB_CLASS_WORDS + 1> key;
+    for (int w = 0; w < KSB_CLASS_WORDS; ++w) key[w] = cm[w];
+    key[KSB_CLASS_WORDS] = h.ext[i].rslot;
+    auto kid = ext_mask_ids.find(key);
+    if (kid == ext_mask_ids.end() && ext_mask_ids.size() < 65535)
+      kid = ext_mask_ids.emplace(key, (uint16_t)(ext_mask_ids.size() + 1)).first;
+    h.ext[i].cls_id = kid == ext_mask_ids.end() ? 0 : kid->second;
+    h.ext[i].pad = 0;
   }
   // --- SelectorSpread class (selector_spreading.go:64-113)
   h.spread_col = spread_class_of(p, sig);

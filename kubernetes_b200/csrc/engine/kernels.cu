@@ -187,6 +187,44 @@ __device__ __forceinline__ uint32_t select_devices(const KsbNodeTable& T, int r,
   return 0;
 }
 
+// Position of the (n+1)-th set bit of w counted from bit 0 upwards (w has more than n set bits).
+__device__ __forceinline__ int nth_set_from_bottom(uint32_t w, int n) {
+  int p = 0;
+#pragma unroll
+  for (int width = 16; width >= 1; width >>= 1) {
+    const int c = __popc(w & ((1u << width) - 1u));
+    if (n >= c) {
+      n -= c;
+      p += width;
+      w >>= width;
+    }
+  }
+  return p;
+}
+
+// Devices of row r, resource slot rs, whose attribute class is in the mask cm (isDeviceAMatch,
+// core/extended_resources.go:152-167, precomputed per class on the host). One thread.
+__device__ __forceinline__ uint32_t device_match_mask(const KsbNodeTable& T, int r, int rs, const uint64_t* cm) {
+  const uint4* cls4 = reinterpret_cast<const uint4*>(T.dev_class + ((size_t)rs * T.n_pad + r) * KSB_MAX_DEV);
+  uint4 v[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) v[q] = cls4[q];  // device classes are static: never rewritten by the kernel
+  uint32_t match = 0;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t w[4] = {v[q].x, v[q].y, v[q].z, v[q].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const uint32_t c = (w[j] >> (16 * half)) & 0xffffu;
+        match |= (uint32_t)((cm[c >> 6] >> (c & 63)) & 1ull) << (q * 8 + j * 2 + half);
+      }
+    }
+  }
+  return match;
+}
+
 __device__ __forceinline__ bool eval_expr(const uint64_t* lab, const uint64_t* mask, uint32_t kind, int W) {
   bool any = false, all = true;
   for (int w = 0; w < W; ++w) {
@@ -498,14 +536,54 @@ struct RowCache {
   uint32_t flags, zone;
   uint32_t avail[KSB_MAX_RES];
   int32_t row, pad;
+  // per extended-resource entry slot: which devices of the row match the class mask interned as `mid` (0: none kept)
+  uint32_t mm[KSB_MAX_EXT];
+  uint16_t mid[KSB_MAX_EXT];
 };
 
 // reason bits that depend on columns a bind changes; every other bit of a row is constant inside a group
 constexpr uint32_t kDynMask = 0x1ffu | (1u << RB_PORTS) | (0xfu << RB_EXT0) | (1u << RB_EXT_LIMITS);
 
+// select_devices on a row-cache entry: the per-device class test is taken from the entry when an earlier pod of the
+// group with the same interned class mask already ran it on this row. Same results as select_devices.
+__device__ __forceinline__ uint32_t select_devices_cached(const KsbNodeTable& T, RowCache* c, const PodView& pv, uint32_t* picks) {
+  const KsbPodHeader* h = pv.h;
+  uint32_t avail[KSB_MAX_RES];
+#pragma unroll
+  for (int s = 0; s < KSB_MAX_RES; ++s) avail[s] = c->avail[s];
+  for (int i = 0; i < h->n_ext; ++i) {
+    if ((h->flags & PF_EXT_LIMITS_ERROR) && i == h->ext_err_entry) return 1u << RB_EXT_LIMITS;
+    const int rs = h->ext[i].rslot;
+    const int num = h->ext[i].num;
+    if (rs == 255 || !(c->flags & (256u << rs))) return 1u << (RB_EXT0 + i);  // available[rName] missing
+    uint32_t sel = 0;
+    if (num > 0) {
+      const uint16_t id = h->ext[i].cls_id;
+      uint32_t match;
+      if (id != 0 && c->mid[i] == id) {
+        match = c->mm[i];
+      } else {
+        match = device_match_mask(T, c->row, rs, pv.extcls + i * KSB_CLASS_WORDS);
+        c->mm[i] = match;
+        c->mid[i] = id;
+      }
+      const uint32_t m = avail[rs] & match;
+      if (__popc(m) < num) return 1u << (RB_EXT0 + i);
+      // the first `num` matching available devices in ascending id order
+      const int last = nth_set_from_bottom(m, num - 1);
+      sel = m & (0xffffffffu >> (31 - last));
+    } else if (num != 0) {
+      return 1u << (RB_EXT0 + i);  // a negative count never equals the number taken
+    }
+    picks[i] = sel;
+    avail[rs] &= ~sel;
+  }
+  return 0;
+}
+
 // The part of eval_node that can change while a group is committed, computed from the row cache.
 // Must stay in step with eval_node (the group-size tests compare the two paths bit for bit).
-__device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCache& c, const PodView& pv,
+__device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, const PodView& pv,
                                             uint32_t static_reasons, uint32_t* reasons_out, int32_t* base_out,
                                             uint32_t* picks, bool want_score) {
   const KsbPodHeader* h = pv.h;
@@ -535,7 +613,7 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, const RowCach
   }
   if (reasons == 0 && h->n_ext) {
     uint32_t local[KSB_MAX_EXT];
-    reasons |= select_devices(T, c.row, pv, c.flags, c.avail, picks ? picks : local);
+    reasons |= select_devices_cached(T, &c, pv, picks ? picks : local);
   }
   *reasons_out = reasons;
   *base_out = 0;
@@ -572,6 +650,7 @@ __device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCach
   // apods, npods, flags, zone, avail[0..1] are consecutive 32-bit fields of the entry
   if (lane < 4 + KSB_MAX_RES) reinterpret_cast<uint32_t*>(&c->apods)[lane] = v2;
   if (lane == 31) c->row = r;
+  if (lane >= 24 && lane < 24 + KSB_MAX_EXT) c->mid[lane - 24] = 0;
 }
 
 // The class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
@@ -1166,7 +1245,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             int crow = -1, crank = 0, cseg = -1;  // local row, shard, global segment
             bool flip = false;
             if (lane < ncr) {
-              const RowCache& c = S.rows[lane];
+              RowCache& c = S.rows[lane];
               crow = c.row;
               crank = c.pad;
               const KsbPeer& P = s_peers[crank];
@@ -1369,8 +1448,24 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 __syncwarp();
               }
               if (h->n_ext) {
-                if (lane == 0)  // the chosen row fits, so the device selection succeeds: only its picks are needed
-                  select_devices(P.table, chosen, pv, S.rows[idx].flags, S.rows[idx].avail, picks);
+                // the chosen row fits, so the device selection succeeds: only its picks are needed. Class tests the
+                // entry does not hold yet are run by the whole warp, one device per lane.
+                RowCache* ce = S.rows + idx;
+                for (int i = 0; i < h->n_ext; ++i) {
+                  const int rs = h->ext[i].rslot;
+                  const uint16_t id = h->ext[i].cls_id;
+                  if (rs < KSB_MAX_RES && h->ext[i].num > 0 && id != 0 && ce->mid[i] != id) {
+                    const uint32_t cls = P.table.dev_class[((size_t)rs * P.table.n_pad + chosen) * KSB_MAX_DEV + lane];
+                    const uint64_t* cm = pv.extcls + i * KSB_CLASS_WORDS;
+                    const uint32_t match = __ballot_sync(0xffffffffu, ((cm[cls >> 6] >> (cls & 63)) & 1ull) != 0);
+                    if (lane == 0) {
+                      ce->mm[i] = match;
+                      ce->mid[i] = id;
+                    }
+                  }
+                }
+                __syncwarp();
+                if (lane == 0) select_devices_cached(P.table, ce, pv, picks);
 #pragma unroll
                 for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
               }
