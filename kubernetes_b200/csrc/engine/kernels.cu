@@ -429,7 +429,9 @@ __device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, u
   uint32_t spins = 0;
   long long t0 = 0;
   while ((int32_t)((SYS ? ld_acquire_sys(p) : ld_acquire(p)) - target) < 0) {
-    if ((++spins & 1023u) == 0) {
+    ++spins;
+    if (spins > 64u) __nanosleep(256);  // a long wait (the serial phase): stop hammering the counter's L2 slice
+    if ((spins & 1023u) == 0) {
       long long now = clock64();
       if (t0 == 0) t0 = now;
       if (now - t0 > 6000000000ll || ld_acquire((const uint32_t*)A.error_flag) != 0) {  // ~3 s
