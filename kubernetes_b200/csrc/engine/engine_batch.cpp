@@ -570,6 +570,7 @@ std::string Engine::shard_export(int max_batch_pods) {
   min_spread_cols = 1024;
   min_table_bytes = (size_t)4 << 20;
   spread_cap_cols = 0;
+  b_spread.release();  // re-created at the shared capacity by sync_device (an earlier ksb_flush sized it smaller)
   arena_dirty = true;
   sync_device();
   prepare_geometry();
