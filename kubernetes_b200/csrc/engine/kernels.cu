@@ -961,25 +961,21 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     KsbNorms* norms = A.norms + (size_t)slot * kMaxG;
     int32_t* zsum = A.zone_sum + (size_t)slot * kMaxG * zs;
 
-    // work split for phases 1 and 2: a block owns segments (all pods) when there are at least as many
-    // segments as blocks; otherwise several blocks share a segment and split the group's pods
-    int seg_first = b, seg_step = nblk, pod_first = 0, pod_step = 1;
-    bool active = true;
-    if (nseg < nblk) {
-      const int parts = min(Gc, nblk / nseg);
-      seg_first = b % nseg;
-      seg_step = nseg;  // exactly one segment
-      pod_first = b / nseg;
-      pod_step = parts;
-      active = pod_first < parts;
-    }
+    // work split for phases 1 and 2: the (segment, pod) pairs, pod index fastest, are dealt to the blocks in
+    // contiguous runs of equal length, so every block is busy whatever the ratio of segments to blocks
+    const int items = nseg * Gc;
+    const int it0 = (int)((long long)items * b / nblk), it1 = (int)((long long)items * (b + 1) / nblk);
+    const bool active = it1 > it0;
+    const int seg_lo = active ? it0 / Gc : 0, seg_hi = active ? (it1 - 1) / Gc : -1;
 
     // ---- phase 1: predicates + Map
     if (active) {
-      for (int seg = seg_first; seg < nseg; seg += seg_step) {
+      for (int seg = seg_lo; seg <= seg_hi; ++seg) {
         const int r = seg * kSeg + tid;
         const bool live = r < T.n;
-        for (int g = pod_first; g < Gc; g += pod_step) {
+        const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
+        const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
+        for (int g = g_lo; g <= g_hi; ++g) {
           const KsbPodHeader* h = S.hdr + g;
           int32_t fit = 0, mna = 0, mtt = 0, msc = 0, imax = 0, imin = 0, hz = 0, one = -1;
           if (live && !(h->flags & PF_SCHED_ERROR)) {
@@ -1076,11 +1072,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     }
     __syncthreads();
     if (active) {
-      for (int seg = seg_first; seg < nseg; seg += seg_step) {
+      for (int seg = seg_lo; seg <= seg_hi; ++seg) {
         const int r = seg * kSeg + tid;
         const bool live = r < T.n;
         const uint32_t zone = live ? T.zone[r] : 0u;
-        for (int g = pod_first; g < Gc; g += pod_step) {
+        const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
+        const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
+        for (int g = g_lo; g <= g_hi; ++g) {
           const KsbPodHeader* h = S.hdr + g;
           const KsbNorms nm = S.norm[g];
           const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && nm.fit_count >= 2;
@@ -1120,7 +1118,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           }
         }
         __syncthreads();
-        if (tid < Gc && tid >= pod_first && (tid - pod_first) % pod_step == 0) {
+        if (tid >= g_lo && tid <= g_hi) {
           const int g = tid;
           const KsbPodHeader* h = S.hdr + g;
           const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[g].fit_count >= 2;
