@@ -236,11 +236,84 @@ __device__ __forceinline__ bool eval_expr(const uint64_t* lab, const uint64_t* m
   return kind == EK_ANY ? any : (kind == EK_NONE ? !any : all);
 }
 
+// The columns of one row that almost every pod reads. Phase 1 evaluates many pods of a group on the same row, so
+// they are loaded once per row and kept in registers across the pods.
+constexpr int kLabFast = 4;  // label words held in registers (the default label_words)
+struct RowCommon {
+  int64_t acpu, amem, rcpu, rmem, ncpu, nmem;
+  uint64_t hard, soft, avoid;
+  uint64_t lab[kLabFast];
+  int32_t num_pods, alloc_pods;
+  uint32_t nflags, zone;
+};
+
+template <bool CG>
+__device__ __forceinline__ void load_row_common(const KsbNodeTable& T, int r, RowCommon& rc) {
+  const size_t np = T.n_pad;
+  rc.num_pods = ldx<CG>(T.num_pods + r);
+  rc.alloc_pods = T.alloc_pods[r];
+  rc.acpu = T.alloc_cpu[r];
+  rc.amem = T.alloc_mem[r];
+  rc.rcpu = ldx<CG>(T.req_cpu + r);
+  rc.rmem = ldx<CG>(T.req_mem + r);
+  rc.ncpu = ldx<CG>(T.nz_cpu + r);
+  rc.nmem = ldx<CG>(T.nz_mem + r);
+  rc.nflags = T.flags[r];
+  rc.zone = T.zone[r];
+  rc.hard = T.taint_hard[r];
+  rc.soft = T.taint_soft[r];
+  rc.avoid = T.avoid[r];
+#pragma unroll
+  for (int w = 0; w < kLabFast; ++w) rc.lab[w] = w < T.W ? T.labels[w * np + r] : 0ull;
+}
+
+// eval_expr for label_words == kLabFast: the row's label words come from registers
+__device__ __forceinline__ bool eval_expr4(const uint64_t (&lab)[kLabFast], const uint64_t* mask, uint32_t kind) {
+  bool any = false, all = true;
+#pragma unroll
+  for (int w = 0; w < kLabFast; ++w) {
+    const uint64_t m = mask[w];
+    const uint64_t x = lab[w] & m;
+    any |= (x != 0);
+    all &= (x == m);
+  }
+  return kind == EK_ANY ? any : (kind == EK_NONE ? !any : all);
+}
+
+// PodMatchNodeSelector (predicates.go:691-761) and the NodeAffinityPriority Map (node_affinity.go:34-75) over the
+// pod's compiled expressions; EXPR(e) evaluates expression e on the row's labels.
+#define KSB_LABEL_RULES(EXPR)                                                    \
+  do {                                                                           \
+    int e = 0;                                                                   \
+    bool match = true;                                                           \
+    if (pf & PF_NODE_SELECTOR) {                                                 \
+      match = EXPR(0);                                                           \
+      e = 1;                                                                     \
+    }                                                                            \
+    if (pf & PF_HAS_REQUIRED) {                                                  \
+      bool any = false;                                                          \
+      for (int t = 0; t < h->n_req_terms; ++t) {                                 \
+        bool all = true;                                                         \
+        const int end = h->term_end[t];                                          \
+        for (; e < end; ++e) all &= EXPR(e);                                     \
+        any |= all;                                                              \
+      }                                                                          \
+      match &= any;                                                              \
+    }                                                                            \
+    if (!match) reasons |= 1u << RB_SELECTOR;                                    \
+    for (int t = 0; t < h->n_pref; ++t) {                                        \
+      bool all = true;                                                           \
+      const int end = h->pref_end[t];                                            \
+      for (; e < end; ++e) all &= EXPR(e);                                       \
+      if (all) na += h->pref_weight[t];                                          \
+    }                                                                            \
+  } while (0)
+
 // Everything the reference computes for one (pod, node): podFitsOnNode's predicates
 // (core/generic_scheduler.go:402-501) and the Map functions of PrioritizeNodes (:557-574).
 // CG = true reads the columns the kernel mutates straight from L2 (phase 3, rows just rewritten).
 template <bool CG>
-__device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const PodView& pv, EvalOut& o,
+__device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const RowCommon& rc, const PodView& pv, EvalOut& o,
                                           uint32_t* picks) {
   const KsbPodHeader* h = pv.h;
   const size_t np = T.n_pad;
@@ -248,15 +321,15 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
   const uint32_t pf = h->flags;
 
   // --- PodFitsResources (predicates.go:630-687)
-  const int32_t num_pods = ldx<CG>(T.num_pods + r);
-  const int32_t alloc_pods = T.alloc_pods[r];
-  const int64_t acpu = T.alloc_cpu[r], amem = T.alloc_mem[r];
-  const int64_t ncpu = ldx<CG>(T.nz_cpu + r), nmem = ldx<CG>(T.nz_mem + r);
-  const uint32_t nflags = T.flags[r];
+  const int32_t num_pods = rc.num_pods;
+  const int32_t alloc_pods = rc.alloc_pods;
+  const int64_t acpu = rc.acpu, amem = rc.amem;
+  const int64_t ncpu = rc.ncpu, nmem = rc.nmem;
+  const uint32_t nflags = rc.nflags;
   if (num_pods + 1 > alloc_pods) reasons |= 1u << RB_PODS;
   if (pf & PF_HAS_REQUEST) {
-    if (acpu < h->req_cpu + ldx<CG>(T.req_cpu + r)) reasons |= 1u << RB_CPU;
-    if (amem < h->req_mem + ldx<CG>(T.req_mem + r)) reasons |= 1u << RB_MEM;
+    if (acpu < h->req_cpu + rc.rcpu) reasons |= 1u << RB_CPU;
+    if (amem < h->req_mem + rc.rmem) reasons |= 1u << RB_MEM;
     if (T.alloc_agpu[r] < h->req_agpu + ldx<CG>(T.req_agpu + r)) reasons |= 1u << RB_AGPU;
     if (T.alloc_eph[r] < h->req_eph + ldx<CG>(T.req_eph + r)) reasons |= 1u << RB_EPH;
     uint32_t sm = h->scalar_mask;
@@ -282,38 +355,26 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
   // --- PodMatchNodeSelector (predicates.go:691-761) and NodeAffinityPriority Map (node_affinity.go:34-75)
   int32_t na = 0;
   if (h->n_exprs) {
-    uint64_t lab[16];
     const int W = T.W;
-    for (int w = 0; w < W; ++w) lab[w] = T.labels[w * np + r];
-    int e = 0;
-    bool match = true;
-    if (pf & PF_NODE_SELECTOR) {
-      match = eval_expr(lab, pv.exprs, (h->expr_kind[0]) & 3u, W);
-      e = 1;
+#define KSB_KIND(e) ((h->expr_kind[(e) >> 4] >> (((e) & 15) * 2)) & 3u)
+    if (W == kLabFast) {
+#define KSB_EXPR_FAST(e) eval_expr4(rc.lab, pv.exprs + (e) * kLabFast, KSB_KIND(e))
+      KSB_LABEL_RULES(KSB_EXPR_FAST);
+#undef KSB_EXPR_FAST
+    } else {
+      uint64_t lab[16];
+      for (int w = 0; w < W; ++w) lab[w] = T.labels[w * np + r];
+#define KSB_EXPR_GEN(e) eval_expr(lab, pv.exprs + (e) * W, KSB_KIND(e), W)
+      KSB_LABEL_RULES(KSB_EXPR_GEN);
+#undef KSB_EXPR_GEN
     }
-    if (pf & PF_HAS_REQUIRED) {
-      bool any = false;
-      for (int t = 0; t < h->n_req_terms; ++t) {
-        bool all = true;
-        int end = h->term_end[t];
-        for (; e < end; ++e) all &= eval_expr(lab, pv.exprs + e * W, (h->expr_kind[e >> 4] >> ((e & 15) * 2)) & 3u, W);
-        any |= all;
-      }
-      match &= any;
-    }
-    if (!match) reasons |= 1u << RB_SELECTOR;
-    for (int t = 0; t < h->n_pref; ++t) {
-      bool all = true;
-      int end = h->pref_end[t];
-      for (; e < end; ++e) all &= eval_expr(lab, pv.exprs + e * W, (h->expr_kind[e >> 4] >> ((e & 15) * 2)) & 3u, W);
-      if (all) na += h->pref_weight[t];
-    }
+#undef KSB_KIND
   } else if ((pf & PF_HAS_REQUIRED)) {
     reasons |= 1u << RB_SELECTOR;  // required affinity with no usable term matches nothing
   }
   // --- PodToleratesNodeTaints (predicates.go:1349-1373) and TaintTolerationPriority Map (taint_toleration.go:55-73)
-  if (T.taint_hard[r] & h->hard_untol) reasons |= 1u << RB_TAINTS;
-  const int32_t tt = __popcll(T.taint_soft[r] & h->soft_untol);
+  if (rc.hard & h->hard_untol) reasons |= 1u << RB_TAINTS;
+  const int32_t tt = __popcll(rc.soft & h->soft_untol);
   // --- pressure / conditions (predicates.go:1382-1441)
   if ((pf & PF_BEST_EFFORT) && (nflags & NF_MEM_PRESSURE)) reasons |= 1u << RB_MEM_PRESSURE;
   if (nflags & NF_DISK_PRESSURE) reasons |= 1u << RB_DISK_PRESSURE;
@@ -371,7 +432,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
     double diff = fabs(__dsub_rn(cf, mf));
     bra = (int32_t)(__dmul_rn(__dsub_rn(1.0, diff), 10.0));
   }
-  const int32_t av = (T.avoid[r] & h->avoid_mask) ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
+  const int32_t av = (rc.avoid & h->avoid_mask) ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
   o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
   o.na = na;
   o.tt = tt;
@@ -383,7 +444,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Po
     if (d) ipa += (int64_t)pv.score[2 * i + 1] * (int64_t)ldx<CG>(T.tables + (uint32_t)c + d);
   }
   o.ipa = (int32_t)ipa;
-  o.zone = T.zone[r];
+  o.zone = rc.zone;
   o.reasons = reasons;
 }
 
@@ -975,13 +1036,15 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         const bool live = r < T.n;
         const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
         const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
+        RowCommon rc;
+        if (live) load_row_common<false>(T, r, rc);
         for (int g = g_lo; g <= g_hi; ++g) {
           const KsbPodHeader* h = S.hdr + g;
           int32_t fit = 0, mna = 0, mtt = 0, msc = 0, imax = 0, imin = 0, hz = 0, one = -1;
           if (live && !(h->flags & PF_SCHED_ERROR)) {
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
             EvalOut o;
-            eval_node<false>(T, r, pv, o, nullptr);
+            eval_node<false>(T, r, rc, pv, o, nullptr);
             int4 raw;
             if (o.reasons == 0) {
               fit = 1;
@@ -1474,7 +1537,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               if (h->n_ext) {
                 if (lane == 0) {
                   EvalOut o;
-                  eval_node<true>(P.table, chosen, pv, o, picks);
+                  RowCommon rc;
+                  load_row_common<true>(P.table, chosen, rc);
+                  eval_node<true>(P.table, chosen, rc, pv, o, picks);
                 }
 #pragma unroll
                 for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
