@@ -49,6 +49,8 @@ typedef struct ksb_config {
   int32_t shard_rank;               /* node-table shard held by this engine (0 when unsharded) */
   int32_t shard_count;              /* number of shards (1 when unsharded) */
   int32_t group_size;               /* pods evaluated per speculative group (0 = default) */
+  int32_t pipeline;                 /* overlap a group's commit with the next group's evaluation: 0 = automatic
+                                       (on from 16,384 node rows, one GPU), 1 = on, -1 = off */
 } ksb_config;
 
 /* Fill *cfg with the DefaultProvider values (algorithmprovider/defaults/defaults.go:217-257). */

@@ -44,6 +44,7 @@ void ksb_config_default(ksb_config* c) {
   c->shard_rank = 0;
   c->shard_count = 1;
   c->group_size = 0;
+  c->pipeline = 0;
 }
 
 ksb_engine* ksb_create(const ksb_config* cfg, char* err, size_t err_len) {

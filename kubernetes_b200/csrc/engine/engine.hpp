@@ -235,6 +235,7 @@ class Engine {
   size_t spread_cap_cols = 0;
   int grid = 0, threads = 0, max_grid = 0, group = 1, nseg = 0, zone_stride = 64;
   size_t smem_bytes = 0;
+  bool pipe = false;  // the next launch overlaps commit and evaluation (prepare_geometry)
   size_t limits_for_smem = (size_t)-1;  // shared-memory size the cached max_grid / threads were queried for
   PinnedBuf pin_in, pin_ctl, pin_out;   // pod blocks in; control block in; control block + results out
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;

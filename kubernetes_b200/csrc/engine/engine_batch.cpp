@@ -22,7 +22,7 @@ struct ScratchLayout {
   size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, seg_mask, barrier, error_flag, fiterr_count, last_index,
       group_done, counters, ghist, release, xbar, xstate, peers, fiterr_hist, total;
 };
-ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
+ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int halves = 1) {
   ScratchLayout L;
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -38,7 +38,7 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   L.error_flag = take(4);
   L.fiterr_count = take(4);
   L.last_index = take(8);
-  L.group_done = take(8);
+  L.group_done = take(32);
   L.counters = take(128);
   L.ghist = take(2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4);
   L.release = take(4);
@@ -46,12 +46,12 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G) {
   L.xstate = take(4);
   L.peers = take(sizeof(KsbPeer) * KSB_MAX_RANKS);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
-  L.raw = take((size_t)G * n_pad * 16);
-  L.score = take((size_t)G * n_pad * 4);
-  L.reasons = take((size_t)G * n_pad * 4);
-  L.seg_max = take((size_t)G * nseg * 4);
-  L.seg_cnt = take((size_t)G * nseg * 4);
-  L.seg_mask = take((size_t)G * nseg * 32);
+  L.raw = take(halves * (size_t)G * n_pad * 16);
+  L.score = take(halves * (size_t)G * n_pad * 4);
+  L.reasons = take(halves * (size_t)G * n_pad * 4);
+  L.seg_max = take(halves * (size_t)G * nseg * 4);
+  L.seg_cnt = take(halves * (size_t)G * nseg * 4);
+  L.seg_mask = take(halves * (size_t)G * nseg * 32);
   L.total = off;
   return L;
 }
@@ -69,6 +69,10 @@ void Engine::prepare_geometry() {
   group = std::max(1, std::min(group, 16384 / zone_stride));
   if (nseg_total > KSB_MAX_SEGMENTS) throw std::runtime_error("more than 524,288 node rows");
   group = std::max(1, std::min(group, KSB_SEG_CACHE / std::max(1, nseg_total)));
+  // pipelined launches: the row cache holds the previous group's rows next to the current one's
+  pipe = R == 1 && cfg.pipeline >= 0 && (cfg.pipeline > 0 || ln >= 16384);
+  if (pipe) group = std::min(group, KSB_MAX_GROUP / 2);
+  if (group < 2) pipe = false;
   if (zone_stride * 4 * KSB_MAX_GROUP > 160 * 1024) throw std::runtime_error("more than 1,280 distinct zones");
   smem_bytes = ksb_batch_smem_bytes(zone_stride);
   if (limits_for_smem != smem_bytes) {  // attribute + occupancy queries: once per shared-memory size
@@ -82,7 +86,8 @@ void Engine::prepare_geometry() {
   if (max_grid < 1) throw std::runtime_error("batch kernel does not fit on this device");
   // enough blocks to cover every segment; when segments are few, extra blocks split the group's pods
   grid = nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, std::max(1, nseg) * group));
-  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group);
+  if (pipe && grid < 2) pipe = false;
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
   if (shard_connected && L.total > b_scratch.cap)
     throw std::runtime_error("sharded engine: scratch outgrew the shared buffer (re-run ksb_shard_export/connect)");
   b_scratch.ensure(L.total);
@@ -91,7 +96,7 @@ void Engine::prepare_geometry() {
 KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   const int R = std::max(1, cfg.shard_count);
   prepare_geometry();
-  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group);
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
   char* base = (char*)b_scratch.d;
   KsbBatchArgs a;
   memset(&a, 0, sizeof a);
@@ -103,6 +108,7 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.zone_stride = zone_stride;
   a.commit = commit ? 1 : 0;
   a.group_size = group;
+  a.pipeline = (pipe && n_pods > group) ? 1 : 0;  // a batch of one group gains nothing from the extra iteration
   a.nseg = nseg;
   a.results = (KsbResult*)b_results.d;
   a.norms = (KsbNorms*)(base + L.norms);
@@ -149,7 +155,7 @@ void Engine::launch(const KsbBatchArgs& a) {
   if (a.n_ranks == 1 && b_scratch.d && (char*)a.norms == (char*)b_scratch.d) {
     // the engine's own scratch on one GPU: every control field lies in one contiguous block at the start of the
     // buffer, so its initial image goes up in a single copy from page-locked memory
-    ScratchLayout L = scratch_layout(ln_pad, a.zone_stride, std::max(1, a.nseg), a.group_size);
+    ScratchLayout L = scratch_layout(ln_pad, a.zone_stride, std::max(1, a.nseg), a.group_size, a.pipeline ? 2 : 1);
     const size_t bytes = L.fiterr_hist;
     pin_ctl.ensure(bytes);
     char* img = (char*)pin_ctl.p;
@@ -182,7 +188,7 @@ void Engine::launch(const KsbBatchArgs& a) {
     CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
     CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)KSB_MAX_GROUP * a.zone_stride * 4, stream));
     CUDA_OK(cudaMemsetAsync(a.ghist, 0, 2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4, stream));
-    CUDA_OK(cudaMemsetAsync(a.group_done, 0, 8, stream));
+    CUDA_OK(cudaMemsetAsync(a.group_done, 0, 32, stream));
   }
   CUDA_OK(cudaMemsetAsync(a.barrier, 0, 4, stream));
   CUDA_OK(cudaMemsetAsync(a.error_flag, 0, 4, stream));
@@ -411,7 +417,8 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   stats.pods_scheduled += np;
   stats.groups += counters[0];
   stats.group_restarts += counters[1];
-  for (int i = 0; i < 13; ++i) stats.stage_cycles[i] = counters[2 + i];
+  for (int i = 0; i < 12; ++i) stats.stage_cycles[i] = counters[2 + i];
+  stats.stage_cycles[12] = 0;  // counters[14] is the progress marker of the timeout diagnostics, not a duration
 
   for (int i = 0; i < np; ++i) {
     const KsbResult& r = last_results[i];

@@ -508,14 +508,15 @@ __device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, u
 // counter (cooperative launch guarantees co-residency). Across GPUs: block 0 of each rank, once its own
 // grid has arrived, bumps a counter in rank 0's memory over NVLink and waits for all ranks, then releases
 // its grid. With one rank it is a plain grid barrier.
-__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch) {
+// `wait` false (one rank only): arrive without waiting; the block contributes nothing to the phase that ends here.
+__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true) {
   __syncthreads();
   if (threadIdx.x == 0) {
     epoch += gridDim.x;
     if (A.n_ranks == 1) {
       __threadfence();
       atomicAdd(A.barrier, 1u);
-      spin_until<false>(A, A.barrier, epoch, 1);
+      if (wait) spin_until<false>(A, A.barrier, epoch, 1);
     } else {
       __threadfence_system();
       atomicAdd(A.barrier, 1u);
@@ -788,8 +789,12 @@ __device__ __forceinline__ void commit_and_record(RowCache* c, CommitRec* rec, c
     uint32_t take[KSB_MAX_RES];
 #pragma unroll
     for (int s = 0; s < KSB_MAX_RES; ++s) take[s] = 0;
-    for (int i = 0; i < h->n_ext; ++i)
-      if (h->ext[i].rslot < KSB_MAX_RES) take[h->ext[i].rslot] |= picks[i];
+    for (int i = 0; i < h->n_ext; ++i) {
+      const int rs = h->ext[i].rslot;
+#pragma unroll
+      for (int s = 0; s < KSB_MAX_RES; ++s)  // no dynamic index: the array stays in registers
+        if (rs == s) take[s] |= picks[i];
+    }
 #pragma unroll
     for (int s = 0; s < KSB_MAX_RES; ++s) {
       const uint32_t av = c->avail[s] & ~take[s];
@@ -923,6 +928,9 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
 
 }  // namespace
 
+// PIPE: the pipelined schedule (see `pipe` below) as a separate instantiation, so that the plain one carries none
+// of its state in registers.
+template <bool PIPE>
 __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const Smem S = carve(smem_raw, A.zone_stride);
@@ -933,6 +941,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   __shared__ volatile int32_t s_stop;         // decider -> writer: pods decided in this group (-1: still deciding)
   __shared__ int32_t s_gmax0[kMaxG], s_k0[kMaxG];  // block 0: per pod, maximum score at group start and its holders
   __shared__ uint32_t s_words[kWarps];         // block 0: holder mask of the segment being searched
+  __shared__ uint32_t s_b1_target;             // block 0, pipelined: barrier count at which the evaluation has read the table
 
   const KsbNodeTable& T = A.table;
   const int tid = threadIdx.x;
@@ -946,11 +955,33 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const int G = A.group_size;
   const size_t np = T.n_pad;
   uint32_t epoch = 0, xepoch = 0;
-  uint64_t n_groups = 0, n_cut = 0;
   const bool multi = A.n_ranks > 1;
   uint64_t last_index = *A.last_node_index;  // used by warp 0 of block 0 only
-  int p0 = 0;
   int gi = 0;
+  // Pipelined launches (A.pipeline, one rank): in iteration k block 0 commits the group evaluated in iteration k-1
+  // ("commit side") while the other blocks evaluate the next one ("evaluation side") against the table as it stood
+  // before that commit; the commit's table writes are held back until the evaluation has read the table.
+  constexpr bool pipe = PIPE;
+  const bool committer = b == 0 && A.rank == 0;
+  const bool lag = pipe && committer;  // this block works on the commit-side group
+  int ev_p0 = 0, ev_slot = 0;          // evaluation side: first pod and scratch half of the group
+  bool cm_valid = false, cm_carry = false;  // commit side: a group is pending; it was evaluated next to another commit
+  int cm_p0 = 0, cm_G = 0, cm_slot = 0, cm_floor = 0;
+  int ncr_keep = 0;  // block 0, warp 0: rows in the row cache, carried from group to group when pipelined
+  // The block that shares an SM with block 0 would compete with the decider warp for issue slots: it sits the
+  // evaluation out. group_done[4] = block 0's SM, group_done[5] = index of that block (0: none).
+  int shun_b = 0;
+  if (pipe) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    if (b == 0 && tid == 0) A.group_done[4] = (int32_t)smid;
+    grid_barrier(A, epoch, xepoch);
+    if (b != 0 && tid == 0 && (int32_t)smid == __ldcv(A.group_done + 4)) A.group_done[5] = b;
+    grid_barrier(A, epoch, xepoch);
+    shun_b = __ldcv(A.group_done + 5);
+    if (nblk < 4) shun_b = 0;
+  }
+  int cm_gid = 0;    // block 0: sequence number of the group being committed (row-cache tags)
 
   if (blockIdx.x == 0 && A.rank == 0) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(A.peers);
@@ -971,20 +1002,43 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     }
     grid_barrier(A, epoch, xepoch);
   }
-  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  long long t3sum[6] = {0, 0, 0, 0, 0, 0};
-  long long tmark = clock64();
-#define KSB_TICK(i)                                                                          \
-  do {                                                                                       \
-    long long now_ = clock64();                                                              \
-    tk[i] += now_ - tmark;                                                                   \
-    tmark = now_;                                                                            \
-    if (blockIdx.x == 0 && threadIdx.x == 0) A.counters[14] = ((uint64_t)gi << 16) | (i); \
+  // measurement state lives in shared memory (thread 0 of each block updates it; block 0's copy is reported): kept
+  // in registers it would cost every thread of the kernel some thirty of them
+  __shared__ long long s_tk[16];  // [0..7] cycles per stage, [8] time mark, [9] groups, [10] groups cut short
+  if (tid < 16) s_tk[tid] = 0;
+  __syncthreads();
+  if (tid == 0) s_tk[8] = clock64();
+#define KSB_TICK(i)                                               \
+  do {                                                            \
+    if (threadIdx.x == 0) {                                       \
+      const long long now_ = clock64();                           \
+      s_tk[i] += now_ - s_tk[8];                                  \
+      s_tk[8] = now_;                                             \
+      if (blockIdx.x == 0) A.counters[14] = ((uint64_t)gi << 16) | (i); \
+    }                                                             \
   } while (0)
-  while (p0 < A.n_pods) {
-    const int slot = gi & 1;
+  while (ev_p0 < A.n_pods || cm_valid) {
+    const bool ev_valid = ev_p0 < A.n_pods;
+    const bool have_group = lag ? cm_valid : ev_valid;  // this block has a group to stage
+    const int p0 = lag ? cm_p0 : ev_p0;
+    const int slot = lag ? cm_slot : ev_slot;
+    // pods may join the group only if every counter they read was last written before `dep_floor`: the start of
+    // the group itself, or of the group being committed next to this evaluation
+    const int dep_floor = lag ? cm_floor : ((pipe && cm_valid) ? cm_p0 : ev_p0);
+    const size_t half = pipe ? (size_t)slot * (size_t)G : 0;  // first pod index of this group's scratch half
+    // this group's half of the per-(pod, row) and per-(pod, segment) scratch arrays (recomputed where used: held in
+    // registers across the loop body they cost more than the multiply)
+#define raw_s (A.raw + half * np)
+#define score_s (A.score + half * np)
+#define reasons_s (A.reasons + half * np)
+#define seg_max_s (A.seg_max + half * nseg)
+#define seg_cnt_s (A.seg_cnt + half * nseg)
+#define seg_mask_s (A.seg_mask + half * nseg * kWarps)
     // ---- stage the group's requirement blocks; every block derives the same group extent
-    {
+    if (!have_group) {
+      if (tid == 0) s_gc = 0;
+      __syncthreads();
+    } else {
       const int avail = min(G, A.n_pods - p0);
       const uint4* src = reinterpret_cast<const uint4*>(A.headers + p0);
       uint4* dst = reinterpret_cast<uint4*>(S.hdr);
@@ -996,18 +1050,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         if (lane < avail) {
           const KsbPodHeader* h = S.hdr + lane;
           int rel_end = (int)(h->pool_off - S.hdr[0].pool_off) + pool_words(h, T.W);
-          ok = rel_end <= kGroupPoolWords && (lane == 0 || __ldg(A.dep + p0 + lane) < p0);
+          ok = rel_end <= kGroupPoolWords && __ldg(A.dep + p0 + lane) < dep_floor;
           S.pool_off[lane] = (int32_t)(h->pool_off - S.hdr[0].pool_off);
         }
         uint32_t bal = __ballot_sync(0xffffffffu, ok);
         int gc = __ffs(~bal) - 1;  // leading run of admissible pods
         if (gc < 0) gc = 32;
-        if (lane == 0) s_gc = max(1, min(gc, avail));
+        // pipelined: 0 when the first pod itself depends on the group being committed (the evaluation waits a turn)
+        if (lane == 0) s_gc = pipe ? min(gc, avail) : max(1, min(gc, avail));
       }
       __syncthreads();
       const int gc = s_gc;
-      const KsbPodHeader* hl = S.hdr + (gc - 1);
-      const int words = S.pool_off[gc - 1] + pool_words(hl, T.W);
+      const KsbPodHeader* hl = S.hdr + max(0, gc - 1);
+      const int words = gc > 0 ? S.pool_off[gc - 1] + pool_words(hl, T.W) : 0;
       const uint64_t* psrc = A.pool + S.hdr[0].pool_off;
       for (int i = tid; i < words; i += kThreads) S.pool[i] = psrc[i];
       for (int i = tid; i < gc * zs; i += kThreads) S.zone[i] = 0;
@@ -1018,6 +1073,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       __syncthreads();
     }
     const int Gc = s_gc;
+    if (pipe && b == 1 && tid == 0) A.group_done[2 + ev_slot] = Gc;  // block 0 learns the evaluated group's size from here
+    const bool do_eval = !lag && Gc > 0 && !(shun_b != 0 && b == shun_b);
     KSB_TICK(0);
     KsbNorms* norms = A.norms + (size_t)slot * kMaxG;
     int32_t* zsum = A.zone_sum + (size_t)slot * kMaxG * zs;
@@ -1025,7 +1082,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     // work split for phases 1 and 2: the (segment, pod) pairs, pod index fastest, are dealt to the blocks in
     // contiguous runs of equal length, so every block is busy whatever the ratio of segments to blocks
     const int items = nseg * Gc;
-    const int it0 = (int)((long long)items * b / nblk), it1 = (int)((long long)items * (b + 1) / nblk);
+    // pipelined: block 0 does not evaluate, nor does the block on its SM
+    const int eb = pipe ? b - 1 - ((shun_b != 0 && b > shun_b) ? 1 : 0) : b;
+    const int enb = pipe ? nblk - 1 - (shun_b != 0 ? 1 : 0) : nblk;
+    const int it0 = do_eval ? (int)((long long)items * eb / enb) : 0;
+    const int it1 = do_eval ? (int)((long long)items * (eb + 1) / enb) : 0;
     const bool active = it1 > it0;
     const int seg_lo = active ? it0 / Gc : 0, seg_hi = active ? (it1 - 1) / Gc : -1;
 
@@ -1062,8 +1123,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             } else {
               raw = make_int4(INT32_MIN, 0, 0, 0);
             }
-            A.raw[(size_t)g * np + r] = raw;
-            A.reasons[(size_t)g * np + r] = o.reasons;
+            raw_s[(size_t)g * np + r] = raw;
+            reasons_s[(size_t)g * np + r] = o.reasons;
           }
           fit = warp_sum(fit);
           mna = warp_max(mna);
@@ -1120,7 +1181,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
     }
     KSB_TICK(1);
-    grid_barrier(A, epoch, xepoch);
+    grid_barrier(A, epoch, xepoch, !lag);
+    if (lag && tid == 0) s_b1_target = epoch;  // the writer warp holds its table writes until this barrier is complete
     KSB_TICK(2);
 
     // ---- phase 2: Reduce + weighted sum; per-segment (max, tie count) of every pod
@@ -1148,7 +1210,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           if (nm.fit_count == 0 && !(h->flags & PF_SCHED_ERROR)) {
             // no node fits: histogram of failure reasons for FitError.Error() (generic_scheduler.go:70-88),
             // one ballot per reason bit present in the warp; lane b owns bit b
-            const uint32_t m = live ? A.reasons[(size_t)g * np + r] : 0u;
+            const uint32_t m = live ? reasons_s[(size_t)g * np + r] : 0u;
             uint32_t un = __reduce_or_sync(0xffffffffu, m);
             int32_t acc = 0;
             while (un) {
@@ -1166,11 +1228,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           if (!prio) continue;  // uniform per (block, g)
           int32_t s = INT32_MIN;
           if (live) {
-            int4 raw = A.raw[(size_t)g * np + r];
+            int4 raw = raw_s[(size_t)g * np + r];
             if (raw.x != INT32_MIN)
               s = final_score(T, nm, S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
                               (uint32_t)raw.z & 0xffffffu, raw.w, zone);
-            A.score[(size_t)g * np + r] = s;
+            score_s[(size_t)g * np + r] = s;
           }
           int32_t wm = warp_max(s);
           const uint32_t wmask = __ballot_sync(0xffffffffu, s == wm && s != INT32_MIN);
@@ -1197,14 +1259,14 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
             }
             if (m == INT32_MIN) c = 0;
-            A.seg_max[(size_t)g * nseg + seg] = m;
-            A.seg_cnt[(size_t)g * nseg + seg] = c;
+            seg_max_s[(size_t)g * nseg + seg] = m;
+            seg_cnt_s[(size_t)g * nseg + seg] = c;
             // which rows hold the segment's maximum: word w = rows 32w..32w+31 of the segment
             uint32_t mw[kWarps];
 #pragma unroll
             for (int w = 0; w < kWarps; ++w)
               mw[w] = (S.wstat[(g * kWarps + w) * 3] == m && m != INT32_MIN) ? (uint32_t)S.wstat[(g * kWarps + w) * 3 + 2] : 0u;
-            uint4* mp = reinterpret_cast<uint4*>(A.seg_mask + ((size_t)g * nseg + seg) * kWarps);
+            uint4* mp = reinterpret_cast<uint4*>(seg_mask_s + ((size_t)g * nseg + seg) * kWarps);
             mp[0] = make_uint4(mw[0], mw[1], mw[2], mw[3]);
             mp[1] = make_uint4(mw[4], mw[5], mw[6], mw[7]);
           }
@@ -1213,12 +1275,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
     }
     KSB_TICK(3);
-    grid_barrier(A, epoch, xepoch);
+    if (!pipe) grid_barrier(A, epoch, xepoch);  // pipelined: block 0 decides while the others are in phases 1-2
     KSB_TICK(4);
 
     // ---- phase 3: block 0 of rank 0 commits the group's pods in order. Rows of other shards are reached
     //      through the peer table (NVLink P2P loads/stores); with one rank every peer access is local.
-    if (b == 0 && A.rank == 0) {
+    if (committer && Gc > 0) {
       const int nsegT = A.nseg_total;
       const int sps = A.segs_per_shard;
       const int R = A.n_ranks;
@@ -1237,9 +1299,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           const int q = i / sps;
           const KsbPeer& P = s_peers[q];
           const int ls = i - q * sps;
-          const int32_t v = __ldcv(P.seg_max + (size_t)g * P.nseg + ls);
+          const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + ls);
           smax[i] = v;
-          scnt[i] = __ldcv(P.seg_cnt + (size_t)g * P.nseg + ls);
+          scnt[i] = __ldcv(P.seg_cnt + (half + g) * P.nseg + ls);
           m = max(m, v);
         }
         const int32_t gmax0 = warp_max(m);
@@ -1263,9 +1325,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       if (tid < kMaxG) s_ready[tid] = 0;
       if (tid == 0) s_stop = -1;
       __syncthreads();
+#if KSB_FINE_TIMING
       long long t3[6] = {0, 0, 0, 0, 0, 0};
       long long m3 = clock64();
-#if KSB_FINE_TIMING
 #define KSB_T3(i)                      \
   do {                                 \
     long long now_ = clock64();        \
@@ -1273,17 +1335,44 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     m3 = now_;                         \
   } while (0)
 #else
-#define KSB_T3(i) ((void)m3)
+#define KSB_T3(i) ((void)0)
 #endif
       KSB_T3(0);
       if (warp == 0) {
-        int ncr = 0;       // rows in the cache (uniform across the warp)
+        // Rows in the cache (uniform across the warp). Pipelined: this group was evaluated before the previous
+        // group's rows reached the table, so those rows (tagged with that group's number) stay in the cache and count
+        // as changed from the first pod on; older entries are dropped.
+        int ncr = 0;
+        cm_gid += 1;
+        if (pipe && cm_carry) {
+          const int prev = cm_gid - 1;
+          int keep = 0;
+          for (int i = 0; i < ncr_keep; ++i) {
+            if ((S.rows[i].pad >> 8) == prev) {
+              if (keep != i) {
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + i);
+                uint32_t* dst = reinterpret_cast<uint32_t*>(S.rows + keep);
+                for (int w = lane; w < (int)(sizeof(RowCache) / 4); w += 32) dst[w] = src[w];
+              }
+              keep += 1;
+            }
+            __syncwarp();
+          }
+          ncr = keep;
+        }
         int consumed = 0;
         // group-start results of the NEXT pod on the cached rows, requested one pod ahead so that their L2
         // round trip overlaps the current pod's commit
         int32_t nx_base = INT32_MIN;  // raw.x: the base score at group start, INT32_MIN = the row did not fit
         uint32_t nx_reasons = 0;
         int32_t nx_score = INT32_MIN;
+        if (lane < ncr) {  // carried rows: the first pod's values
+          const KsbPeer& P = s_peers[S.rows[lane].pad & 0xff];
+          const size_t at = half * P.table.n_pad + S.rows[lane].row;
+          nx_base = __ldcv(&P.raw[at].x);
+          nx_reasons = __ldcv(P.reasons + at);
+          nx_score = __ldcv(P.score + at);
+        }
         for (int g = 0; g < Gc; ++g) {
           const KsbPodHeader* h = S.hdr + g;
           const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
@@ -1310,7 +1399,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (lane < ncr) {
               RowCache& c = S.rows[lane];
               crow = c.row;
-              crank = c.pad;
+              crank = c.pad & 0xff;
               const KsbPeer& P = s_peers[crank];
               cseg = P.seg_base + crow / kSeg;
               const int32_t base0 = nx_base;
@@ -1336,7 +1425,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 bool safe = true;
                 if (flip) {
                   const KsbPeer& P = s_peers[crank];
-                  const int4 raw = __ldcv(P.raw + (size_t)g * P.table.n_pad + crow);
+                  const int4 raw = __ldcv(P.raw + (half + g) * P.table.n_pad + crow);
                   const int32_t na = raw.y, tt = (int32_t)((uint32_t)raw.z >> 24), ipa = raw.w;
                   const uint32_t sc = (uint32_t)raw.z & 0xffffffu;
                   safe = (nm.max_na == 0 || na < nm.max_na) && (nm.max_tt == 0 || tt < nm.max_tt) && sc == 0 &&
@@ -1431,7 +1520,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   const int base_row = (found - P.seg_base) * kSeg;
                   uint32_t word = 0;
                   if (lane < kWarps && smax[found] == gmax)
-                    word = __ldcv(P.seg_mask + ((size_t)g * P.nseg + (found - P.seg_base)) * kWarps + lane);
+                    word = __ldcv(P.seg_mask + ((half + g) * P.nseg + (found - P.seg_base)) * kWarps + lane);
                   const uint32_t inseg = __ballot_sync(0xffffffffu, lane < ncr && cseg == found && crank == pick_rank);
                   if (inseg) {
                     if (lane < kWarps) s_words[lane] = word;
@@ -1478,7 +1567,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           CommitRec& rec = S.recs[g];
           int idx = -1;
           if (chosen >= 0 && A.commit) {
-            const bool mine = lane < ncr && S.rows[lane].row == chosen && S.rows[lane].pad == chosen_rank;
+            const bool mine = lane < ncr && S.rows[lane].row == chosen && (S.rows[lane].pad & 0xff) == chosen_rank;
             const uint32_t bal = __ballot_sync(0xffffffffu, mine);
             if (bal) idx = __ffs(bal) - 1;
           }
@@ -1486,14 +1575,14 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             int prow = -1, prank = 0;
             if (lane < ncr) {
               prow = S.rows[lane].row;
-              prank = S.rows[lane].pad;
+              prank = S.rows[lane].pad & 0xff;
             } else if (lane == ncr && chosen >= 0 && A.commit && idx < 0) {
               prow = chosen;  // the row this pod is about to add to the cache
               prank = chosen_rank;
             }
             if (prow >= 0) {
               const KsbPeer& P = s_peers[prank];
-              const size_t at = (size_t)(g + 1) * P.table.n_pad + prow;
+              const size_t at = (half + g + 1) * P.table.n_pad + prow;
               nx_base = __ldcv(&P.raw[at].x);
               nx_reasons = __ldcv(P.reasons + at);
               nx_score = __ldcv(P.score + at);
@@ -1506,10 +1595,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               if (idx < 0) {
                 idx = ncr;
                 cache_fill(P.table, chosen, S.rows + idx, lane);
-                if (lane == 31) S.rows[idx].pad = chosen_rank;
                 ncr += 1;
-                __syncwarp();
               }
+              if (lane == 31) S.rows[idx].pad = chosen_rank | (cm_gid << 8);  // shard, and the group that last changed it
+              __syncwarp();
               if (h->n_ext) {
                 // the chosen row fits, so the device selection succeeds: only its picks are needed. Class tests the
                 // entry does not hold yet are run by the whole warp, one device per lane.
@@ -1559,6 +1648,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           consumed = g + 1;
           KSB_T3(3);  // cache update + hand-off
         }
+        ncr_keep = ncr;
         if (lane == 0) {
           s_consumed = consumed;
           __threadfence_block();
@@ -1567,6 +1657,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         if (lane < R) *s_peers[lane].last_node_index = last_index;  // every rank's host reads its own copy
       } else if (warp == 1) {
         // writer warp: table write-through, class counters and result records of every decided pod, in order
+        bool table_open = false;
         for (int g = 0; g < Gc; ++g) {
           while (s_ready[g] == 0) {
             const int st = s_stop;
@@ -1577,7 +1668,14 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           __threadfence_block();
           const CommitRec& rec = S.recs[g];
           const KsbPodHeader* h = S.hdr + g;
+          if (lane < R) s_peers[lane].results[p0 + g] = rec.res;  // every rank keeps a copy of the results
           if (rec.row >= 0) {
+            if (pipe && !table_open) {
+              // pipelined: the evaluation side is still reading the table until every block has passed barrier 1
+              if (lane == 0) spin_until<false>(A, A.barrier, s_b1_target, 7);
+              __syncwarp();
+              table_open = true;
+            }
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
             const KsbPeer& P = s_peers[rec.rank];
             const int chosen = rec.row;
@@ -1605,49 +1703,102 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
             }
           }
-          if (lane < R) s_peers[lane].results[p0 + g] = rec.res;  // every rank keeps a copy of the results
           __syncwarp();
         }
       }
       __syncthreads();
       KSB_T3(4);
-      // publish how far the group got; reset the other scratch half for the next group
+      // publish how far the group got
       if (tid == 0) {
         A.group_done[slot] = s_consumed;
-        n_groups += 1;  // block 0 / thread 0 is the only writer: kept in registers, stored once at the end
-        if (s_consumed < Gc) n_cut += 1;
+        s_tk[9] += 1;
+        if (s_consumed < Gc) s_tk[10] += 1;
       }
-      KsbNorms* nn = A.norms + (size_t)(slot ^ 1) * kMaxG;
-      for (int i = tid; i < kMaxG * 8; i += kThreads) reinterpret_cast<int32_t*>(nn)[i] = ((i & 7) == 7) ? -1 : 0;
-      int32_t* zn = A.zone_sum + (size_t)(slot ^ 1) * kMaxG * zs;
-      for (int i = tid; i < kMaxG * zs; i += kThreads) zn[i] = 0;
-      int32_t* gh = A.ghist + (size_t)(slot ^ 1) * kMaxG * KSB_REASON_BITS;
-      for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
+      if (!pipe) {  // reset the other scratch half for the next group
+        KsbNorms* nn = A.norms + (size_t)(slot ^ 1) * kMaxG;
+        for (int i = tid; i < kMaxG * 8; i += kThreads) reinterpret_cast<int32_t*>(nn)[i] = ((i & 7) == 7) ? -1 : 0;
+        int32_t* zn = A.zone_sum + (size_t)(slot ^ 1) * kMaxG * zs;
+        for (int i = tid; i < kMaxG * zs; i += kThreads) zn[i] = 0;
+        int32_t* gh = A.ghist + (size_t)(slot ^ 1) * kMaxG * KSB_REASON_BITS;
+        for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
+      }
       KSB_T3(5);
-      for (int i = 0; i < 6; ++i) t3sum[i] += t3[i];
+#if KSB_FINE_TIMING
+      if (tid == 0)
+        for (int i = 0; i < 6; ++i) A.counters[9 + i] += (uint64_t)t3[i];
+#endif
 #undef KSB_T3
     }
     KSB_TICK(5);
+    if (pipe && committer && Gc > 0) {
+      // this group's scratch half is free again (its contents were copied to shared memory before phase 3)
+      KsbNorms* nn = A.norms + (size_t)slot * kMaxG;
+      for (int i = tid; i < kMaxG * 8; i += kThreads) reinterpret_cast<int32_t*>(nn)[i] = ((i & 7) == 7) ? -1 : 0;
+      int32_t* zn = A.zone_sum + (size_t)slot * kMaxG * zs;
+      for (int i = tid; i < kMaxG * zs; i += kThreads) zn[i] = 0;
+      int32_t* gh = A.ghist + (size_t)slot * kMaxG * KSB_REASON_BITS;
+      for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
+    }
+    // pipelined: the evaluation side has read the table and finished phase 2; the commit side has decided and written
     grid_barrier(A, epoch, xepoch);
     KSB_TICK(6);
-    const int adv = __ldcv(A.group_done + slot);
-    if (adv <= 0 || __ldcg(A.error_flag) != 0) {  // only after a barrier timeout: stop instead of spinning
-      if (tid == 0) atomicCAS(A.error_flag, 0, adv <= 0 ? 5 : 6);
-      break;
+    if (__ldcg(A.error_flag) != 0) break;  // only after a barrier timeout: stop instead of spinning
+    if (!pipe) {
+      const int adv = __ldcv(A.group_done + slot);
+      if (adv <= 0) {
+        if (tid == 0) atomicCAS(A.error_flag, 0, 5);
+        break;
+      }
+      ev_p0 += adv;
+      ev_slot ^= 1;
+    } else {
+      // every block draws the same conclusions from the two published numbers
+      const int ge = ev_valid ? __ldcv(A.group_done + 2 + ev_slot) : 0;  // pods evaluated in this iteration
+      const int adv = cm_valid ? __ldcv(A.group_done + cm_slot) : 0;     // pods committed in this iteration
+      if (cm_valid && adv < cm_G) {
+        // speculation was dropped inside the committed group: everything evaluated after it is void. The next
+        // evaluation starts at the first uncommitted pod, against a table that holds every commit so far.
+        if (committer) {  // the void evaluation's half of the reduction scratch
+          KsbNorms* nn = A.norms + (size_t)(cm_slot ^ 1) * kMaxG;
+          for (int i = tid; i < kMaxG * 8; i += kThreads) reinterpret_cast<int32_t*>(nn)[i] = ((i & 7) == 7) ? -1 : 0;
+          int32_t* zn = A.zone_sum + (size_t)(cm_slot ^ 1) * kMaxG * zs;
+          for (int i = tid; i < kMaxG * zs; i += kThreads) zn[i] = 0;
+          int32_t* gh = A.ghist + (size_t)(cm_slot ^ 1) * kMaxG * KSB_REASON_BITS;
+          for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
+        }
+        grid_barrier(A, epoch, xepoch);
+        ev_p0 = cm_p0 + adv;
+        cm_valid = false;
+      } else if (ge > 0) {
+        cm_carry = cm_valid;
+        cm_floor = cm_valid ? cm_p0 : ev_p0;
+        cm_p0 = ev_p0;
+        cm_G = ge;
+        cm_slot = ev_slot;
+        cm_valid = true;
+        ev_p0 += ge;
+        ev_slot ^= 1;
+      } else {
+        cm_valid = false;  // nothing was evaluated: end of the stream, or the first pod waits for the commit above
+      }
     }
-    p0 += adv;
     gi += 1;
   }
   if (b == 0 && tid == 0) {
     if (multi) *A.xstate = xepoch;
-    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)tk[i];  // block 0's cycles per stage
-    for (int i = 0; i < 6; ++i) A.counters[9 + i] = (uint64_t)t3sum[i];
+    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[i];  // block 0's cycles per stage
     if (A.rank == 0) {
-      A.counters[0] = n_groups;
-      A.counters[1] = n_cut;
+      A.counters[0] = (uint64_t)s_tk[9];
+      A.counters[1] = (uint64_t)s_tk[10];
     }
   }
 #undef KSB_TICK
+#undef raw_s
+#undef score_s
+#undef reasons_s
+#undef seg_max_s
+#undef seg_cnt_s
+#undef seg_mask_s
 }
 
 // Applies the assume step for a pod placed outside a batch (ksb_pod_add after ksb_schedule).
@@ -1672,18 +1823,25 @@ extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
 
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
   void* params[] = {(void*)args};
-  cudaError_t e = cudaLaunchCooperativeKernel((const void*)ksb_schedule_batch_kernel, dim3(grid), dim3(kThreads), params,
+  const void* fn = args->pipeline ? (const void*)ksb_schedule_batch_kernel<true> : (const void*)ksb_schedule_batch_kernel<false>;
+  cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,
                                               smem_bytes, stream);
   return (int)e;
 }
 
 extern "C" int ksb_batch_kernel_limits(int device, size_t smem_bytes, int* max_grid, int* threads) {
   int per_sm = 0, sms = 0;
-  cudaError_t e = cudaFuncSetAttribute(ksb_schedule_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  cudaError_t e = cudaFuncSetAttribute(ksb_schedule_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem_bytes);
   if (e != cudaSuccess) return (int)e;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ksb_schedule_batch_kernel, kThreads, smem_bytes);
+  e = cudaFuncSetAttribute(ksb_schedule_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return (int)e;
+  int per_sm_pipe = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ksb_schedule_batch_kernel<false>, kThreads, smem_bytes);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_pipe, ksb_schedule_batch_kernel<true>, kThreads, smem_bytes);
+  if (e != cudaSuccess) return (int)e;
+  per_sm = per_sm < per_sm_pipe ? per_sm : per_sm_pipe;  // one grid size serves both instantiations
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (e != cudaSuccess) return (int)e;
   *max_grid = per_sm * sms;

@@ -32,7 +32,8 @@ struct KsbBatchArgs {
   int32_t commit;               // 1: apply the assume step after each pod (ksb_schedule_batch)
   int32_t group_size;           // pods per group, 1..KSB_MAX_GROUP
   int32_t nseg;                 // 256-row segments in this shard
-  int32_t pad0;
+  int32_t pipeline;             // 1: block 0 commits group k-1 while the other blocks evaluate group k (one rank only);
+                                // raw/score/reasons/seg_* then hold two halves, one per parity of the group
   KsbResult* results;           // [n_pods]
   // scratch (global memory beyond inputs and outputs)
   KsbNorms* norms;              // [2][KSB_MAX_GROUP] ping-pong per group
@@ -48,7 +49,7 @@ struct KsbBatchArgs {
   int32_t* fiterr_count;
   int32_t* fiterr_hist;         // [KSB_MAX_FITERR][KSB_REASON_BITS]
   uint64_t* last_node_index;    // genericScheduler.lastNodeIndex
-  int32_t* group_done;          // [2] pods consumed by the group, ping-pong
+  int32_t* group_done;          // [8] pods consumed by the group, ping-pong; pipelined: [2..3] size of the group evaluated, [4] block 0's SM, [5] the block sharing it
   uint64_t* counters;           // [16] groups run, groups cut short by a dropped speculation, stage cycles
   int32_t* ghist;               // [2][KSB_MAX_GROUP][KSB_REASON_BITS] reason histograms of no-fit pods, ping-pong
   // sharding (n_ranks == 1: everything local). With n_ranks > 1 the reduction targets above (norms, zone_sum,

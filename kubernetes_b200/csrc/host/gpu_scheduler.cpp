@@ -59,6 +59,7 @@ ksb_config config_from(const json::Value& opt) {
   cfg.label_words = (int32_t)opt.get_int("label_words", 4);
   cfg.hard_pod_affinity_weight = (int32_t)opt.get_int("hardPodAffinityWeight", 1);
   cfg.group_size = (int32_t)opt.get_int("group_size", 0);
+  cfg.pipeline = (int32_t)opt.get_int("pipeline", 0);
   cfg.shard_rank = (int32_t)opt.get_int("shard_rank", 0);
   cfg.shard_count = (int32_t)opt.get_int("shard_count", 1);
   if (const json::Value* w = opt.find("weights"); w && !w->is_null()) {

@@ -27,7 +27,7 @@ class KsbConfig(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "device", "w_least_requested", "w_balanced", "w_selector_spread", "w_node_affinity", "w_taint_toleration",
         "w_inter_pod_affinity", "w_prefer_avoid", "hard_pod_affinity_weight", "label_words", "shard_rank", "shard_count",
-        "group_size")]
+        "group_size", "pipeline")]
 
 
 class KsbResult(ctypes.Structure):

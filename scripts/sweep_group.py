@@ -7,12 +7,13 @@ from kubernetes_b200 import lib, workloads
 
 cfg, nodes, pods = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
 sizes = [int(x) for x in sys.argv[4].split(",")] if len(sys.argv) > 4 else [1, 2, 4, 8, 16, 32]
+pipeline = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 cluster = workloads.generate(cfg, nodes, pods)
 sess = lib.Session(cluster=cluster)
 sess.run(results=False)
 for g in sizes:
-    out = sess.run(results=False, group_size=g, replay_iters=2)
-    print(json.dumps({"cfg": cfg, "nodes": nodes, "pods": pods, "G": g, "kernel_ms": round(out["kernel_ms"], 2),
+    out = sess.run(results=False, group_size=g, replay_iters=2, pipeline=pipeline)
+    print(json.dumps({"cfg": cfg, "nodes": nodes, "pods": pods, "G": g, "pipeline": pipeline, "kernel_ms": round(out["kernel_ms"], 2),
                       "replay_ms": round(out["replay_ms"], 2), "us_per_pod": round(1000 * out["replay_ms"] / pods, 2),
                       "groups": out["groups"], "restarts": out["group_restarts"], "encode_ms": round(out["encode_ms"], 1),
                       "e2e_ms": round(out["e2e_ms"], 1), "hash": out["placement_hash"][-6:],

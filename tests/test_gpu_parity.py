@@ -73,6 +73,34 @@ def test_group_sizes_agree(cfg, nodes, pods):
     assert all(v == (base["placement_hash"], base["lastNodeIndex"]) for v in seen.values()), (seen, base["placement_hash"])
 
 
+@pytest.mark.parametrize("cfg,nodes,pods", [(1, 100, 1000), (2, 150, 2000), (3, 400, 2500), (5, 150, 1200)])
+def test_pipelined_batch_matches_oracle(cfg, nodes, pods):
+    """Commit of group k-1 overlapped with the evaluation of group k (forced on; automatic only from 16,384 rows)."""
+    cluster = workloads.generate(cfg, nodes, pods)
+    compare(cluster, "cfg%d pipelined" % cfg, gpu_opts={"pipeline": 1})
+
+
+@pytest.mark.parametrize("cfg,nodes,pods", [(1, 64, 800), (2, 60, 900), (3, 700, 3000), (5, 120, 900)])
+def test_pipelined_group_sizes_agree(cfg, nodes, pods):
+    cluster = workloads.generate(cfg, nodes, pods)
+    sess = lib.Session(cluster=cluster)
+    base = sess.run(results=False, group_size=1, pipeline=-1)
+    seen = {}
+    for g in (2, 3, 7, 16):
+        out = sess.run(results=False, group_size=g, pipeline=1)
+        seen[g] = (out["placement_hash"], out["lastNodeIndex"])
+    sess.close()
+    assert all(v == (base["placement_hash"], base["lastNodeIndex"]) for v in seen.values()), (seen, base["placement_hash"])
+
+
+def test_pipelined_tight_cluster():
+    cluster = workloads.generate(1, 12, 700)
+    for n in cluster["nodes"]:
+        n["allocatable"]["pods"] = 40
+    got, want = compare(cluster, "tight cfg1 pipelined", gpu_opts={"pipeline": 1})
+    assert any(r["status"] == 2 for r in want["results"])
+
+
 def test_full_node_and_tight_cluster_forces_restarts():
     """A small, nearly full cluster: rows turn unfit inside groups, so speculation is dropped often."""
     cluster = workloads.generate(1, 12, 700)
