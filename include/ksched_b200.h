@@ -132,6 +132,14 @@ int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_le
  * Schedule; calling it after the informers' initial sync keeps that cost out of the first pod's latency. */
 int32_t ksb_flush(ksb_engine* e);
 
+/* FailedPredicateMap of the most recent single-pod ksb_schedule (core/generic_scheduler.go:283-362, the map that
+ * FitError carries and nodesWherePreemptionMightHelp :957-991 reads): masks[i] has bit b set when node row i failed
+ * for reason b; 0 = the node fitted. `n` must be at least the number of node rows (ksb_result.num_nodes). */
+int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n);
+/* Text of failure reason `bit` as predicates/error.go:33-54, :84-86 spells it ("Insufficient cpu",
+ * "MatchNodeSelector", ...); for the extended-resource bits, the text for the pod of the last call. Empty if unused. */
+int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len);
+
 /* genericScheduler.lastNodeIndex (core/generic_scheduler.go:100): selectHost's round-robin counter. */
 uint64_t ksb_get_last_node_index(const ksb_engine* e);
 void ksb_set_last_node_index(ksb_engine* e, uint64_t v);

@@ -153,6 +153,23 @@ int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_le
   });
 }
 
+int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n) {
+  return guarded(e, [&] {
+    if (!masks) throw std::runtime_error("masks must not be null");
+    e->impl->failed_predicates(masks, n);
+  });
+}
+
+int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len) {
+  return guarded(e, [&] {
+    std::string t = e->impl->reason_name(bit);
+    if (buf && buf_len) {
+      strncpy(buf, t.c_str(), buf_len - 1);
+      buf[buf_len - 1] = 0;
+    }
+  });
+}
+
 int32_t ksb_flush(ksb_engine* e) {
   return guarded(e, [&] { e->impl->flush(); });
 }

@@ -114,6 +114,8 @@ class Engine {
   // hot path
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void flush();
+  void failed_predicates(uint32_t* out, int32_t n_out);
+  std::string reason_name(int bit);
   void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
   void replay_last_batch_noalloc(ksb_result* out);
   // sharding over the GPUs of one NVSwitch domain
@@ -236,6 +238,7 @@ class Engine {
   int grid = 0, threads = 0, max_grid = 0, group = 1, nseg = 0, zone_stride = 64;
   size_t smem_bytes = 0;
   bool pipe = false;  // the next launch overlaps commit and evaluation (prepare_geometry)
+  bool batch_pipe_ok = true;  // the last encoded batch has few pods that depend on a very recent pod
   size_t limits_for_smem = (size_t)-1;  // shared-memory size the cached max_grid / threads were queried for
   PinnedBuf pin_in, pin_ctl, pin_out;   // pod blocks in; control block in; control block + results out
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;

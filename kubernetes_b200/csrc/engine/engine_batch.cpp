@@ -108,7 +108,7 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.zone_stride = zone_stride;
   a.commit = commit ? 1 : 0;
   a.group_size = group;
-  a.pipeline = (pipe && n_pods > group) ? 1 : 0;  // a batch of one group gains nothing from the extra iteration
+  a.pipeline = (pipe && n_pods > group && (batch_pipe_ok || cfg.pipeline > 0)) ? 1 : 0;  // a batch of one group gains nothing from the extra iteration
   a.nseg = nseg;
   a.results = (KsbResult*)b_results.d;
   a.norms = (KsbNorms*)(base + L.norms);
@@ -355,6 +355,14 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
       for (int c : e.spread_inc) last_spread[c] = i;
       for (auto& c : e.commits) last_table[c.table] = i;
     }
+  }
+  // The pipelined schedule evaluates a group next to the commit of the one before it, so a pod may not read a
+  // counter written by either. Streams where many pods depend on a very recent pod (dense inter-pod affinity) would
+  // stall it at every group: those batches run the plain schedule.
+  {
+    int recent = 0;
+    for (int i = 0; i < np; ++i) recent += (dep[i] >= 0 && dep[i] >= i - KSB_MAX_GROUP) ? 1 : 0;
+    batch_pipe_ok = recent * 10 <= np;
   }
   auto t1 = std::chrono::steady_clock::now();
   stats.last_batch_encode_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -634,6 +642,41 @@ void Engine::shard_connect(const std::vector<std::string>& blobs) {
 }
 
 // FitError.Error() (generic_scheduler.go:70-88)
+// FailedPredicateMap of the most recent ksb_schedule (core/generic_scheduler.go:283-362): one reason mask per node
+// row, bit b = failure reason b (ksb_reason_name). Kept on the device by the launch; copied on demand.
+void Engine::failed_predicates(uint32_t* out, int32_t n_out) {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  if (cfg.shard_count > 1) throw std::runtime_error("ksb_failed_predicates: not available on a sharded engine");
+  if (last_results.size() != 1) throw std::runtime_error("ksb_failed_predicates: the last call was not a single-pod ksb_schedule");
+  if (n_out < n) throw std::runtime_error("ksb_failed_predicates: buffer holds fewer entries than there are node rows");
+  if (n == 0) return;
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
+  CUDA_OK(cudaMemcpyAsync(out, (char*)b_scratch.d + L.reasons, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));
+  stats.d2h_bytes += (size_t)n * 4;
+}
+
+std::string Engine::reason_name(int bit) {
+  std::lock_guard<std::mutex> g(mu);
+  static const char* fixed[KSB_REASON_BITS] = {
+      "Insufficient pods", "Insufficient cpu", "Insufficient memory", "Insufficient alpha.kubernetes.io/nvidia-gpu",
+      "Insufficient ephemeral-storage", nullptr, nullptr, nullptr, nullptr, "HostName", "PodFitsHostPorts",
+      "MatchNodeSelector", "PodToleratesNodeTaints", "NodeUnderMemoryPressure", "NodeUnderDiskPressure", "NodeNotReady",
+      "NodeOutOfDisk", "NodeNetworkUnavailable", "NodeUnschedulable", "MatchInterPodAffinity",
+      "ExistingPodsAntiAffinityRulesNotMatch", "PodAffinityRulesNotMatch", "PodAntiAffinityRulesNotMatch", nullptr, nullptr,
+      nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  if (bit < 0 || bit >= KSB_REASON_BITS) throw std::runtime_error("reason bit out of range");
+  if (fixed[bit]) return fixed[bit];
+  if (bit >= RB_SCALAR0 && bit <= RB_SCALAR3)
+    return bit - RB_SCALAR0 < (int)scalar_names.size() ? "Insufficient " + scalar_names[bit - RB_SCALAR0] : std::string();
+  if (!last_encoded.empty()) {  // per-pod texts of the fork's extended-resource entries
+    if (bit >= RB_EXT0 && bit <= RB_EXT3) return last_encoded[0].ext_reasons[bit - RB_EXT0];
+    if (bit == RB_EXT_LIMITS) return last_encoded[0].ext_reasons[KSB_MAX_EXT];
+  }
+  return std::string();
+}
+
 std::string Engine::fit_error_message(int i) {
   std::lock_guard<std::mutex> g(mu);
   if (i < 0 || i >= (int)last_results.size()) throw std::runtime_error("pod index out of range");

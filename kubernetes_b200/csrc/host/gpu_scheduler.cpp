@@ -97,6 +97,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   std::vector<ksb_result> results(np);
   std::vector<std::string> hosts(np), messages(np);
   std::vector<ExtendedResourceBinding> bindings(np);
+  std::vector<std::string> failed_json(np);  // "failed_predicates": per pod, {node: [reasons]} of the nodes that did not fit
+  const bool want_failed = opt.get_bool("failed_predicates", false);
   GpuScheduler sched(h);
   CacheDecorator cache(h);
   double kernel_ms = 0, encode_ms = 0, replay_ms = 0;
@@ -121,6 +123,31 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
         lat_parts.push_back({st1.last_batch_encode_ms, st1.last_batch_sync_ms, st1.last_batch_kernel_ms});
       }
       results[i] = r;
+      if (want_failed && r.num_nodes > 0) {
+        // FailedPredicateMap (core/generic_scheduler.go:283-362) of this call, node name -> reason texts
+        std::vector<uint32_t> masks((size_t)r.num_nodes);
+        h.check(ksb_failed_predicates(h.get(), masks.data(), r.num_nodes), "failed_predicates");
+        std::string fj = "{";
+        bool first_node = true;
+        for (int32_t row = 0; row < r.num_nodes; ++row) {
+          if (!masks[row]) continue;
+          const char* nm = nullptr;
+          size_t nl = 0;
+          h.check(ksb_node_name(h.get(), row, &nm, &nl), "node_name");
+          fj += std::string(first_node ? "" : ",") + esc(std::string(nm, nl)) + ":[";
+          first_node = false;
+          bool first_reason = true;
+          for (int bit = 0; bit < 32; ++bit) {
+            if (!((masks[row] >> bit) & 1u)) continue;
+            char buf[160];
+            h.check(ksb_reason_name(h.get(), bit, buf, sizeof buf), "reason_name");
+            fj += std::string(first_reason ? "" : ",") + esc(buf);
+            first_reason = false;
+          }
+          fj += "]";
+        }
+        failed_json[i] = fj + "}";
+      }
       try {
         ScheduleOutcome o = sched.outcome(pod, r, 0);
         hosts[i] = o.host;
@@ -233,7 +260,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
       if (i) out += ",";
       out += "{\"host\":" + esc(hosts[i]) + ",\"status\":" + std::to_string(results[i].status) +
              ",\"filtered\":" + std::to_string(results[i].num_filtered) + ",\"score\":" + std::to_string(results[i].score) +
-             ",\"message\":" + esc(messages[i]) + ",\"devices\":{";
+             ",\"message\":" + esc(messages[i]) + (failed_json[i].empty() ? std::string() : ",\"failed\":" + failed_json[i]) +
+             ",\"devices\":{";
       bool first = true;
       for (auto& kv : bindings[i]) {
         if (!first) out += ",";
