@@ -104,6 +104,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   double kernel_ms = 0, encode_ms = 0, replay_ms = 0;
   std::vector<double> lat_us;
   std::vector<std::array<double, 3>> lat_parts;  // encode, table sync, kernel (ms) of each one-pod call
+  ksb_stats st0;  // bytes copied before the timed region (cluster load, ksb_flush) are not this run's
+  ksb_get_stats(h.get(), &st0);
   auto t0 = std::chrono::steady_clock::now();
   if (batch == 0) {
     // the reference's own call sequence: Schedule, then AssumePod with NodeName and Assigned set
@@ -192,6 +194,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
     }
   }
   auto t1 = std::chrono::steady_clock::now();
+  ksb_stats st_e2e;
+  ksb_get_stats(h.get(), &st_e2e);
   if (replay_iters > 0 && batch < 0) {
     std::vector<ksb_result> again(np);
     h.check(ksb_replay_last_batch(h.get(), replay_iters, &replay_ms, again.data()), "replay");
@@ -230,8 +234,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   out += "]";
   out += ",\"groups\":" + std::to_string(st.groups);
   out += ",\"group_restarts\":" + std::to_string(st.group_restarts);
-  out += ",\"h2d_bytes\":" + std::to_string(st.h2d_bytes);
-  out += ",\"d2h_bytes\":" + std::to_string(st.d2h_bytes);
+  out += ",\"h2d_bytes\":" + std::to_string(st_e2e.h2d_bytes - st0.h2d_bytes);
+  out += ",\"d2h_bytes\":" + std::to_string(st_e2e.d2h_bytes - st0.d2h_bytes);
   out += ",\"lastNodeIndex\":" + std::to_string(ksb_get_last_node_index(h.get()));
   if (!lat_us.empty()) {
     // "lat_skip": leave the first calls (cold dictionaries: first use of a label, selector class, topology key)
