@@ -156,6 +156,8 @@ typedef struct ksb_stats {
   double last_batch_kernel_ms; /* CUDA-event time of the kernels of the last ksb_schedule_batch */
   double last_batch_encode_ms; /* host time spent encoding the last batch */
   double last_batch_sync_ms;   /* host time spent bringing the device table up to date before the launch */
+  double last_batch_decode_ms; /* host time spent decoding the wire records of the last batch */
+  double last_batch_post_ms;   /* host time spent mirroring the last batch's placements into the host records */
   int32_t num_nodes;
   int32_t node_row_bytes;      /* bytes of node-table columns one (pod,node) evaluation may read */
   /* SM cycles block 0 spent, last batch: staging, phase 1, barrier 1, phase 2, barrier 2, phase 3, barrier 3;

@@ -1,4 +1,6 @@
 // extern "C" surface of include/ksched_b200.h over ksb::Engine.
+#include <chrono>
+#include <thread>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -114,13 +116,36 @@ int32_t ksb_schedule(ksb_engine* e, const uint8_t* pod, size_t len, ksb_result* 
 
 int32_t ksb_schedule_batch(ksb_engine* e, const uint8_t* pods, const uint64_t* offsets, int32_t n, ksb_result* out) {
   return guarded(e, [&] {
-    std::vector<ksb::Pod> batch;
-    batch.reserve(n);
-    for (int32_t i = 0; i < n; ++i) {
-      ksb::wire::Reader r(pods + offsets[i], (size_t)(offsets[i + 1] - offsets[i]));
-      batch.push_back(ksb::wire::get_pod(r));
+    auto t0 = std::chrono::steady_clock::now();
+    // wire records are independent: decode them on a few host threads when the batch is large
+    std::vector<ksb::Pod> batch((size_t)std::max(0, n));
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const int nthreads = n >= 4096 ? (int)std::min(8u, hw) : 1;
+    std::vector<std::string> errors((size_t)nthreads);
+    auto decode_range = [&](int t) {
+      try {
+        const int32_t lo = (int32_t)((int64_t)n * t / nthreads), hi = (int32_t)((int64_t)n * (t + 1) / nthreads);
+        for (int32_t i = lo; i < hi; ++i) {
+          ksb::wire::Reader r(pods + offsets[i], (size_t)(offsets[i + 1] - offsets[i]));
+          batch[i] = ksb::wire::get_pod(r);
+        }
+      } catch (const std::exception& ex) {
+        errors[t] = ex.what();
+        if (errors[t].empty()) errors[t] = "decode error";
+      }
+    };
+    if (nthreads == 1) {
+      decode_range(0);
+    } else {
+      std::vector<std::thread> pool;
+      for (int t = 0; t < nthreads; ++t) pool.emplace_back(decode_range, t);
+      for (auto& th : pool) th.join();
     }
+    for (auto& msg : errors)
+      if (!msg.empty()) throw std::runtime_error(msg);
+    const double decode_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     e->impl->schedule_batch(batch, out, true);
+    e->impl->stats.last_batch_decode_ms = decode_ms;
   });
 }
 

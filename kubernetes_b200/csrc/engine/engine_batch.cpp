@@ -428,6 +428,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   for (int i = 0; i < 12; ++i) stats.stage_cycles[i] = counters[2 + i];
   stats.stage_cycles[12] = 0;  // counters[14] is the progress marker of the timeout diagnostics, not a duration
 
+  auto tp0 = std::chrono::steady_clock::now();
   for (int i = 0; i < np; ++i) {
     const KsbResult& r = last_results[i];
     out[i].status = r.status;
@@ -456,6 +457,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     host_add_pod(p, hn);
     pods[p.key()] = HostPod{p};
   }
+  stats.last_batch_post_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
 }
 
 void Engine::flush() {

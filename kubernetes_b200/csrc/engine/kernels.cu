@@ -1073,7 +1073,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       __syncthreads();
     }
     const int Gc = s_gc;
-    if (pipe && b == 1 && tid == 0) A.group_done[2 + ev_slot] = Gc;  // block 0 learns the evaluated group's size from here
+    // Block 0 learns the evaluated group's size from here. Both published numbers are indexed by the parity of the
+    // iteration, not of the group: a block that runs ahead into the next iteration then never overwrites a value that a
+    // slower block has yet to read (scratch halves do not alternate in an iteration that evaluates nothing).
+    if (pipe && b == 1 && tid == 0) A.group_done[2 + (gi & 1)] = Gc;
     const bool do_eval = !lag && Gc > 0 && !(shun_b != 0 && b == shun_b);
     KSB_TICK(0);
     KsbNorms* norms = A.norms + (size_t)slot * kMaxG;
@@ -1710,7 +1713,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       KSB_T3(4);
       // publish how far the group got
       if (tid == 0) {
-        A.group_done[slot] = s_consumed;
+        A.group_done[gi & 1] = s_consumed;
         s_tk[9] += 1;
         if (s_consumed < Gc) s_tk[10] += 1;
       }
@@ -1744,7 +1747,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     KSB_TICK(6);
     if (__ldcg(A.error_flag) != 0) break;  // only after a barrier timeout: stop instead of spinning
     if (!pipe) {
-      const int adv = __ldcv(A.group_done + slot);
+      const int adv = __ldcv(A.group_done + (gi & 1));
       if (adv <= 0) {
         if (tid == 0) atomicCAS(A.error_flag, 0, 5);
         break;
@@ -1753,8 +1756,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       ev_slot ^= 1;
     } else {
       // every block draws the same conclusions from the two published numbers
-      const int ge = ev_valid ? __ldcv(A.group_done + 2 + ev_slot) : 0;  // pods evaluated in this iteration
-      const int adv = cm_valid ? __ldcv(A.group_done + cm_slot) : 0;     // pods committed in this iteration
+      const int ge = ev_valid ? __ldcv(A.group_done + 2 + (gi & 1)) : 0;  // pods evaluated in this iteration
+      const int adv = cm_valid ? __ldcv(A.group_done + (gi & 1)) : 0;    // pods committed in this iteration
       if (cm_valid && adv < cm_G) {
         // speculation was dropped inside the committed group: everything evaluated after it is void. The next
         // evaluation starts at the first uncommitted pod, against a table that holds every commit so far.

@@ -101,7 +101,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   const bool want_failed = opt.get_bool("failed_predicates", false);
   GpuScheduler sched(h);
   CacheDecorator cache(h);
-  double kernel_ms = 0, encode_ms = 0, replay_ms = 0;
+  double kernel_ms = 0, encode_ms = 0, replay_ms = 0, decode_ms = 0, post_ms = 0, sync_ms = 0;
   std::vector<double> lat_us;
   std::vector<std::array<double, 3>> lat_parts;  // encode, table sync, kernel (ms) of each one-pod call
   ksb_stats st0;  // bytes copied before the timed region (cluster load, ksb_flush) are not this run's
@@ -178,6 +178,9 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
       ksb_get_stats(h.get(), &st);
       kernel_ms += st.last_batch_kernel_ms;
       encode_ms += st.last_batch_encode_ms;
+      decode_ms += st.last_batch_decode_ms;
+      post_ms += st.last_batch_post_ms;
+      sync_ms += st.last_batch_sync_ms;
       if (want_results || b1 == np) {
         for (size_t i = b0; i < b1; ++i) {
           if (!want_results && results[i].status != KSB_SCHEDULED) continue;
@@ -228,6 +231,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   out += ",\"kernel_ms\":" + std::to_string(kernel_ms);
   out += ",\"encode_ms\":" + std::to_string(encode_ms);
   out += ",\"replay_ms\":" + std::to_string(replay_ms);
+  out += ",\"decode_ms\":" + std::to_string(decode_ms) + ",\"post_ms\":" + std::to_string(post_ms) + ",\"sync_ms\":" + std::to_string(sync_ms);
   out += ",\"kernel_launches\":" + std::to_string(st.kernel_launches);
   out += ",\"stage_cycles\":[";
   for (int i = 0; i < 13; ++i) out += (i ? "," : "") + std::to_string(st.stage_cycles[i]);

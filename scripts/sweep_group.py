@@ -16,6 +16,6 @@ for g in sizes:
     print(json.dumps({"cfg": cfg, "nodes": nodes, "pods": pods, "G": g, "pipeline": pipeline, "kernel_ms": round(out["kernel_ms"], 2),
                       "replay_ms": round(out["replay_ms"], 2), "us_per_pod": round(1000 * out["replay_ms"] / pods, 2),
                       "groups": out["groups"], "restarts": out["group_restarts"], "encode_ms": round(out["encode_ms"], 1),
-                      "e2e_ms": round(out["e2e_ms"], 1), "hash": out["placement_hash"][-6:],
+                      "e2e_ms": round(out["e2e_ms"], 1), "decode_ms": round(out["decode_ms"], 1), "post_ms": round(out["post_ms"], 1), "sync_ms": round(out["sync_ms"], 1), "hash": out["placement_hash"][-6:],
                       "stage_us_per_pod": [round(c / 1965.0 / pods, 2) for c in out["stage_cycles"]]}))
 sess.close()

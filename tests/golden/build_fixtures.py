@@ -323,6 +323,11 @@ def main():
         BUILDERS.extend(golden_more.builders(globals()))
     except ImportError:
         pass
+    try:
+        import golden_extra  # noqa: F401  (third batch)
+        BUILDERS.extend(golden_extra.builders(globals()))
+    except ImportError:
+        pass
     for b in BUILDERS:
         b()
     out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "reference_vectors.json")

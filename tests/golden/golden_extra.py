@@ -1,0 +1,135 @@
+"""Third batch of transcriptions of the reference's own tests (see build_fixtures.py): the small predicate and
+priority tables, and the cache aggregates. Each builder cites its source."""
+
+
+def builders(g):
+    node, pod, ctr, expr = g["node"], g["pod"], g["ctr"], g["expr"]
+    priority, predicate, CASES = g["priority"], g["predicate"], g["CASES"]
+
+    # ----------------------------------------------------------------- NodePreferAvoidPodsPriority
+    # algorithm/priorities/node_prefer_avoid_pods_test.go:30-145
+    def build_prefer_avoid():
+        src = "algorithm/priorities/node_prefer_avoid_pods_test.go:84-128"
+        nodes = lambda: [node("machine1", avoid=[{"kind": "ReplicationController", "uid": "abcdef123456"}]),
+                         node("machine2", avoid=[{"kind": "ReplicaSet", "uid": "qwert12345"}]),
+                         node("machine3")]
+        P = "NodePreferAvoidPodsPriority"
+        priority(P, src, "pod managed by ReplicationController should avoid a node, this node get lowest priority score",
+                 pod(ns="default", controller={"kind": "ReplicationController", "uid": "abcdef123456"}), nodes(), [],
+                 [("machine1", 0), ("machine2", 10), ("machine3", 10)])
+        priority(P, src, "ownership by random controller should be ignored",
+                 pod(ns="default", controller={"kind": "RandomController", "uid": "abcdef123456"}), nodes(), [],
+                 [("machine1", 10), ("machine2", 10), ("machine3", 10)])
+        # an owner reference without Controller=true is not a controller reference: the pod has none
+        priority(P, src, "owner without Controller field set should be ignored", pod(ns="default"), nodes(), [],
+                 [("machine1", 10), ("machine2", 10), ("machine3", 10)])
+        priority(P, src, "pod managed by ReplicaSet should avoid a node, this node get lowest priority score",
+                 pod(ns="default", controller={"kind": "ReplicaSet", "uid": "qwert12345"}), nodes(), [],
+                 [("machine1", 10), ("machine2", 0), ("machine3", 10)])
+
+    # ----------------------------------------------------------------- hard pod affinity symmetric weight
+    # algorithm/priorities/interpod_affinity_test.go:529-612
+    def build_hard_affinity_weight():
+        src = "algorithm/priorities/interpod_affinity_test.go:566-594"
+        hard = {"podAffinity": {"required": [{"selector": {"matchExpressions": [expr("service", "In", "S1")]},
+                                              "topologyKey": "region"}]}}
+        nodes = lambda: [node("machine1", labels={"region": "China"}), node("machine2", labels={"region": "India"}),
+                         node("machine3", labels={"az": "az1"})]
+        existing = lambda: [pod("machine1", affinity=hard), pod("machine2", affinity=hard)]
+        for weight, scores, test in [
+                (1, [("machine1", 10), ("machine2", 10), ("machine3", 0)],
+                 "Hard Pod Affinity symmetry: weight 1 by default, nodes matching the symmetry rules get a high score"),
+                (0, [("machine1", 0), ("machine2", 0), ("machine3", 0)],
+                 "Hard Pod Affinity symmetry: closed (weight 0), matching nodes score like the others")]:
+            priority("InterPodAffinityPriority", src, test, pod(labels={"service": "S1"}), nodes(), existing(), scores,
+                     )
+            CASES[-1]["hardPodAffinityWeight"] = weight
+
+    # ----------------------------------------------------------------- PodFitsHost
+    # algorithm/predicates/predicates_test.go:458-516
+    def build_fits_host():
+        src = "algorithm/predicates/predicates_test.go:465-496"
+        predicate("PodFitsHost", src, "no host specified", pod(), node(""), fits=True)
+        predicate("PodFitsHost", src, "host matches", pod(nodeName="foo"), node("foo"), fits=True)
+        predicate("PodFitsHost", src, "host doesn't match", pod(nodeName="bar"), node("foo"), fits=False,
+                  reasons=["HostName"])
+
+    # ----------------------------------------------------------------- memory / disk pressure, node conditions
+    # algorithm/predicates/predicates_test.go:3422-3686
+    def build_pressure_and_conditions():
+        cond = lambda *pairs: [{"type": t, "status": s} for t, s in pairs]
+        src = "algorithm/predicates/predicates_test.go:3481-3506"
+        best_effort = lambda: pod(containers=[{}])
+        burstable = lambda: pod(containers=[ctr(100, 100, requests={"alpha.kubernetes.io/nvidia-gpu": 100, "pods": 100})])
+        no_mp = lambda: node("n", conditions=cond(("Ready", "True")))
+        mp = lambda: node("n", conditions=cond(("MemoryPressure", "True")))
+        M = "CheckNodeMemoryPressure"
+        predicate(M, src, "best-effort pod schedulable on node without memory pressure condition on", best_effort(), no_mp())
+        predicate(M, src, "best-effort pod not schedulable on node with memory pressure condition on", best_effort(), mp(),
+                  fits=False, reasons=["NodeUnderMemoryPressure"])
+        predicate(M, src, "non best-effort pod schedulable on node with memory pressure condition on", burstable(), mp())
+        predicate(M, src, "non best-effort pod schedulable on node without memory pressure condition on", burstable(), no_mp())
+        src = "algorithm/predicates/predicates_test.go:3565-3580"
+        D = "CheckNodeDiskPressure"
+        predicate(D, src, "pod schedulable on node without pressure condition on", pod(containers=[{}]),
+                  node("n", conditions=cond(("Ready", "True"))))
+        predicate(D, src, "pod not schedulable on node with pressure condition on", pod(containers=[{}]),
+                  node("n", conditions=cond(("DiskPressure", "True"))), fits=False, reasons=["NodeUnderDiskPressure"])
+        # TestNodeConditionPredicate pins fit only; the reason texts follow predicates.go:1414-1441 and error.go:44-48
+        src = "algorithm/predicates/predicates_test.go:3598-3660"
+        C = "CheckNodeCondition"
+        table = [
+            ("node1", cond(("Ready", "True")), False, []),
+            ("node2", cond(("Ready", "False")), False, ["NodeNotReady"]),
+            ("node3", cond(("OutOfDisk", "True")), False, ["NodeOutOfDisk"]),
+            ("node4", cond(("OutOfDisk", "False")), False, []),
+            ("node5", cond(("Ready", "True"), ("OutOfDisk", "True")), False, ["NodeOutOfDisk"]),
+            ("node6", cond(("Ready", "True"), ("OutOfDisk", "False")), False, []),
+            ("node7", cond(("Ready", "False"), ("OutOfDisk", "True")), False, ["NodeNotReady", "NodeOutOfDisk"]),
+            ("node8", cond(("Ready", "False"), ("OutOfDisk", "False")), False, ["NodeNotReady"]),
+            ("node9", [], True, ["NodeUnschedulable"]),
+            ("node10", [], False, []),
+            ("node11", [], False, []),
+        ]
+        for name, conditions, unsched, reasons in table:
+            n = node(name, conditions=conditions)
+            if unsched:
+                n["unschedulable"] = True
+            predicate(C, src, name, pod(), n, fits=not reasons, reasons=sorted(reasons))
+
+    # ----------------------------------------------------------------- cache aggregates
+    # schedulercache/cache_test.go:48-189 (TestAssumePodScheduled): NodeInfo after AssumePod of the listed pods
+    def build_assume_pod():
+        src = "schedulercache/cache_test.go:48-189"
+        port = lambda p: {"hostIP": "127.0.0.1", "hostPort": p, "protocol": "TCP"}
+
+        def base(name, cpu, mem, ext, ports):
+            req = {}
+            if cpu is not None:
+                req["cpu"] = cpu
+            if mem is not None:
+                req["memory"] = mem
+            if ext:
+                req[ext[0]] = ext[1]
+            return pod("node", ns="node-namespace", name=name, containers=[ctr(requests=req, ports=ports)])
+
+        tp = [base("test", 100, 500, None, [port(80)]), base("test-1", 100, 500, None, [port(80)]),
+              base("test-2", 200, 1024, None, [port(8080)]), base("test-nonzero", None, None, None, [port(80)]),
+              base("test", 100, 500, ("example.com/foo", 3), [port(80)]),
+              base("test-2", 200, 1024, ("example.com/foo", 5), [port(8080)]),
+              base("test", 100, 500, ("random-invalid-extended-key", 100), [{}])]
+        table = [
+            ([0], (100, 500, {}), (100, 500), ["TCP/127.0.0.1/80"]),
+            ([1, 2], (300, 1524, {}), (300, 1524), ["TCP/127.0.0.1/80", "TCP/127.0.0.1/8080"]),
+            ([3], (0, 0, {}), (100, 200 * 1024 * 1024), ["TCP/127.0.0.1/80"]),
+            ([4], (100, 500, {"example.com/foo": 3}), (100, 500), ["TCP/127.0.0.1/80"]),
+            ([4, 5], (300, 1524, {"example.com/foo": 8}), (300, 1524), ["TCP/127.0.0.1/80", "TCP/127.0.0.1/8080"]),
+            ([6], (100, 500, {}), (100, 500), []),
+        ]
+        for i, (idx, req, nz, ports) in enumerate(table):
+            CASES.append({"op": "node_info", "source": src, "test": "TestAssumePodScheduled #%d" % i, "node": "node",
+                          "cluster": {"nodes": [], "existingPods": [tp[k] for k in idx]}, "forget": [],
+                          "expect": {"requested": {"cpu": req[0], "memory": req[1], "gpu": 0, "ephemeral": 0, "scalars": req[2]},
+                                     "nonzero": {"cpu": nz[0], "memory": nz[1]}, "pods": len(idx), "usedPorts": ports}})
+
+    return [build_prefer_avoid, build_hard_affinity_weight, build_fits_host, build_pressure_and_conditions, build_assume_pod]

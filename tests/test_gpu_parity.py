@@ -93,6 +93,20 @@ def test_pipelined_group_sizes_agree(cfg, nodes, pods):
     assert all(v == (base["placement_hash"], base["lastNodeIndex"]) for v in seen.values()), (seen, base["placement_hash"])
 
 
+@pytest.mark.parametrize("cfg,nodes,pods", [(3, 700, 3000), (5, 120, 900)])
+def test_pipelined_is_repeatable(cfg, nodes, pods):
+    """The pipelined schedule has blocks in different iterations at the same time; its published group sizes must not
+    be overwritten early (iterations that evaluate nothing are the delicate case: cfg5 has many)."""
+    cluster = workloads.generate(cfg, nodes, pods)
+    sess = lib.Session(cluster=cluster)
+    base = sess.run(results=False, pipeline=-1)
+    for _ in range(6):
+        for g in (4, 16):
+            out = sess.run(results=False, pipeline=1, group_size=g)
+            assert (out["placement_hash"], out["lastNodeIndex"]) == (base["placement_hash"], base["lastNodeIndex"])
+    sess.close()
+
+
 def test_pipelined_tight_cluster():
     cluster = workloads.generate(1, 12, 700)
     for n in cluster["nodes"]:
@@ -184,7 +198,7 @@ def test_golden_priorities_on_gpu():
         best = max(scores.values())
         winners = {h for h, s in scores.items() if s == best}
         sess = lib.Session(cluster=cl)
-        out = sess.run(weights=weights)
+        out = sess.run(weights=weights, hardPodAffinityWeight=c.get("hardPodAffinityWeight", 1))
         sess.close()
         r = out["results"][0]
         if r["status"] != 0 or r["filtered"] != len(scores):
