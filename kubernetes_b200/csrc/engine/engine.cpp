@@ -88,7 +88,8 @@ Engine::~Engine() {
   for (DevBuf* b : {&b_i64, &b_u32, &b_u64, &b_dev_class, &b_topo, &b_spread, &b_tables, &b_headers, &b_pool,
                     &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush, &b_dep})
     b->release();
-  pin_in.release();
+  pin_chunk[0].release();
+  pin_chunk[1].release();
   pin_ctl.release();
   pin_out.release();
   if (ev_start) cudaEventDestroy(ev_start);

@@ -114,6 +114,7 @@ class Engine {
   // hot path
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void flush();
+  void grow_keep(DevBuf& b, size_t bytes);
   void failed_predicates(uint32_t* out, int32_t n_out);
   std::string reason_name(int bit);
   void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
@@ -240,7 +241,8 @@ class Engine {
   bool pipe = false;  // the next launch overlaps commit and evaluation (prepare_geometry)
   bool batch_pipe_ok = true;  // the last encoded batch has few pods that depend on a very recent pod
   size_t limits_for_smem = (size_t)-1;  // shared-memory size the cached max_grid / threads were queried for
-  PinnedBuf pin_in, pin_ctl, pin_out;   // pod blocks in; control block in; control block + results out
+  PinnedBuf pin_chunk[2], pin_ctl, pin_out;  // pod blocks in (two chunks in flight); control block in; control block + results out
+  std::vector<int32_t> last_dep;              // dependency indices of the last batch, relative to the batch
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
   // shard geometry: device rows [lbase, lbase + ln), device column stride ln_pad
   int lbase = 0, ln = 0, ln_pad = 0, rows_per_shard = 0;

@@ -305,159 +305,260 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     for (int i = 0; i < np; ++i) out[i].status = KSB_NO_NODES;
     return;
   }
-  // pass 1: classes; pass 2: requirement blocks
+  for (auto& p : batch)
+    if (p.num_volumes > 0)  // volume predicates are out of scope: refuse loudly, never guess, before anything is placed
+      throw std::runtime_error("pod " + p.key() + " has volumes: not supported by the GPU engine");
+  // pass 1: classes (every pod of the batch, so that commit lists name every class a later pod introduces)
   for (auto& p : batch) register_pod_classes(p);
   layout_arena();
-  size_t pool_words = 0;
-  for (int i = 0; i < np; ++i) {
-    if (batch[i].num_volumes > 0)  // volume predicates are out of scope: refuse loudly, never guess
-      throw std::runtime_error("pod " + batch[i].key() + " has volumes: not supported by the GPU engine");
-    encode_pod(batch[i], &last_encoded[i]);
-    last_encoded[i].h.pool_off = (uint32_t)pool_words;
-    pool_words += last_encoded[i].pool.size();
-  }
-  // headers, dependency indices and pool words are laid out in page-locked memory so the copies below are
-  // asynchronous and the batch needs no intermediate host copy
-  const size_t hdr_bytes = (size_t)np * sizeof(KsbPodHeader);
-  const size_t dep_off = (hdr_bytes + 255) & ~(size_t)255;
-  const size_t pool_off = (dep_off + (size_t)np * 4 + 255) & ~(size_t)255;
-  const size_t pool_bytes = std::max<size_t>(1, pool_words) * 8;
-  pin_in.ensure(pool_off + pool_bytes);
-  KsbPodHeader* headers = (KsbPodHeader*)pin_in.p;
-  int32_t* dep = (int32_t*)((char*)pin_in.p + dep_off);
-  uint64_t* pool = (uint64_t*)((char*)pin_in.p + pool_off);
-  pool[0] = 0;
-  for (int i = 0; i < np; ++i) {
-    headers[i] = last_encoded[i].h;
-    if (!last_encoded[i].pool.empty())
-      memcpy(pool + last_encoded[i].h.pool_off, last_encoded[i].pool.data(), last_encoded[i].pool.size() * 8);
-  }
+
+  // Large batches on one GPU go to the device in chunks: while the kernel of chunk c runs, the host encodes chunk
+  // c+1 and mirrors the placements of chunk c-1 into its records. Device work stays strictly ordered on one stream
+  // (uploads and the next launch are issued only after the previous chunk's results are back), so the placements
+  // are those of one launch over the whole batch.
+  constexpr int kChunk = 8192;
+  const bool chunked = assume && cfg.shard_count <= 1 && np >= 3 * kChunk;
+  const int chunk_len = chunked ? kChunk : np;
+  const int n_chunks = (np + chunk_len - 1) / chunk_len;
+
   // dep[j]: the latest earlier pod whose assume step bumps a counter pod j reads (its SelectorSpread column
   // or any inter-pod-affinity table). A group never holds both, so those inputs are constant inside a group.
-  for (int i = 0; i < np; ++i) dep[i] = -1;
-  if (np > 1) {
-    std::vector<int32_t> last_spread(h_spread.size(), -1), last_table(tables.size(), -1);
-    std::unordered_map<uint32_t, int> table_by_off;
+  last_dep.assign(np, -1);
+  std::vector<int32_t> last_spread(h_spread.size(), -1), last_table(tables.size(), -1);
+  std::unordered_map<uint32_t, int> table_by_off;
+  if (np > 1)
     for (size_t t = 0; t < tables.size(); ++t) table_by_off[tables[t].off] = (int)t;
-    for (int i = 0; i < np; ++i) {
+  size_t pool_words = 0;  // words of every pod encoded so far (pool offsets are relative to the whole batch)
+  double encode_ms = 0, post_ms = 0, kernel_ms = 0, sync_ms = 0;
+  int recent_deps = 0;
+
+  struct Staged {
+    size_t hdr_bytes = 0, dep_off = 0, pool_off = 0, pool_words = 0, pool_first = 0;
+  };
+  Staged staged[2];
+
+  // encode pods [c0, c1) into page-locked staging buffer `which`
+  auto encode_chunk = [&](int c0, int c1, int which) {
+    auto te0 = std::chrono::steady_clock::now();
+    const int len = c1 - c0;
+    const size_t first_word = pool_words;
+    for (int i = c0; i < c1; ++i) {
+      encode_pod(batch[i], &last_encoded[i]);
+      last_encoded[i].h.pool_off = (uint32_t)pool_words;
+      pool_words += last_encoded[i].pool.size();
+    }
+    if (arena_dirty && c0 > 0) throw std::runtime_error("internal: the counter arena changed in the middle of a batch");
+    Staged& st = staged[which];
+    st.hdr_bytes = (size_t)len * sizeof(KsbPodHeader);
+    st.dep_off = (st.hdr_bytes + 255) & ~(size_t)255;
+    st.pool_off = (st.dep_off + (size_t)len * 4 + 255) & ~(size_t)255;
+    st.pool_first = first_word;
+    st.pool_words = pool_words - first_word;
+    pin_chunk[which].ensure(st.pool_off + std::max<size_t>(1, st.pool_words) * 8);
+    KsbPodHeader* headers = (KsbPodHeader*)pin_chunk[which].p;
+    int32_t* dep = (int32_t*)((char*)pin_chunk[which].p + st.dep_off);
+    uint64_t* pool = (uint64_t*)((char*)pin_chunk[which].p + st.pool_off);
+    pool[0] = 0;
+    for (int i = c0; i < c1; ++i) {
       const EncodedPod& e = last_encoded[i];
+      headers[i - c0] = e.h;
+      if (!e.pool.empty()) memcpy(pool + (e.h.pool_off - first_word), e.pool.data(), e.pool.size() * 8);
       int32_t d = -1;
-      if (e.h.spread_col >= 0) d = std::max(d, last_spread[e.h.spread_col]);
-      const uint64_t* pw = e.pool.data() + (size_t)e.h.n_exprs * W + ((e.h.flags & PF_HAS_PORTS) ? 6 * KSB_PORT_WORDS : 0) +
-                           (size_t)e.h.n_ext * KSB_CLASS_WORDS;
-      for (int c = 0; c < e.h.n_checks; ++c) {
-        if (((pw[c] >> 40) & 0xff) == CM_FAIL_ALWAYS) continue;
-        d = std::max(d, last_table[table_by_off.at((uint32_t)pw[c])]);
+      if (np > 1) {
+        if (e.h.spread_col >= 0) d = std::max(d, last_spread[e.h.spread_col]);
+        const uint64_t* pw = e.pool.data() + (size_t)e.h.n_exprs * W + ((e.h.flags & PF_HAS_PORTS) ? 6 * KSB_PORT_WORDS : 0) +
+                             (size_t)e.h.n_ext * KSB_CLASS_WORDS;
+        for (int c = 0; c < e.h.n_checks; ++c) {
+          if (((pw[c] >> 40) & 0xff) == CM_FAIL_ALWAYS) continue;
+          d = std::max(d, last_table[table_by_off.at((uint32_t)pw[c])]);
+        }
+        pw += e.h.n_checks;
+        for (int c = 0; c < e.h.n_score; ++c) d = std::max(d, last_table[table_by_off.at((uint32_t)pw[2 * c])]);
+        for (int c : e.spread_inc) last_spread[c] = i;
+        for (auto& c : e.commits) last_table[c.table] = i;
       }
-      pw += e.h.n_checks;
-      for (int c = 0; c < e.h.n_score; ++c) d = std::max(d, last_table[table_by_off.at((uint32_t)pw[2 * c])]);
-      dep[i] = d;
-      for (int c : e.spread_inc) last_spread[c] = i;
-      for (auto& c : e.commits) last_table[c.table] = i;
+      last_dep[i] = d;
+      dep[i - c0] = d >= c0 ? d - c0 : -1;  // relative to the launch; pods of earlier chunks are committed by then
+      recent_deps += (d >= 0 && d >= i - KSB_MAX_GROUP) ? 1 : 0;
     }
-  }
-  // The pipelined schedule evaluates a group next to the commit of the one before it, so a pod may not read a
-  // counter written by either. Streams where many pods depend on a very recent pod (dense inter-pod affinity) would
-  // stall it at every group: those batches run the plain schedule.
-  {
-    int recent = 0;
-    for (int i = 0; i < np; ++i) recent += (dep[i] >= 0 && dep[i] >= i - KSB_MAX_GROUP) ? 1 : 0;
-    batch_pipe_ok = recent * 10 <= np;
-  }
-  auto t1 = std::chrono::steady_clock::now();
-  stats.last_batch_encode_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    encode_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - te0).count();
+  };
 
-  sync_device();
-  stats.last_batch_sync_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
-  b_headers.ensure(hdr_bytes);
-  b_pool.ensure(pool_bytes);
-  if (shard_connected && (size_t)np * sizeof(KsbResult) > b_results.cap)
-    throw std::runtime_error("sharded engine: batch larger than the max_batch_pods given to ksb_shard_export");
-  b_results.ensure((size_t)np * sizeof(KsbResult));
-  b_dep.ensure((size_t)np * 4);
-  CUDA_OK(cudaMemcpyAsync(b_dep.d, dep, (size_t)np * 4, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_headers.d, headers, hdr_bytes, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemcpyAsync(b_pool.d, pool, pool_bytes, cudaMemcpyHostToDevice, stream));
-  stats.h2d_bytes += hdr_bytes + pool_bytes + (size_t)np * 4;
-  KsbBatchArgs a = make_args(np, assume);
-  if (assume) snapshot_dynamic();
-  last_index_before = last_node_index;
+  KsbBatchArgs a;
+  size_t ctl_lo = 0, ctl_hi = 0, res_off = 0;
+  // upload staged chunk `which` (pods [c0, c1)) and launch the kernel on it; the stream is idle when this is called
+  auto launch_chunk = [&](int c0, int c1, int which) {
+    auto ts0 = std::chrono::steady_clock::now();
+    const int len = c1 - c0;
+    const Staged& st = staged[which];
+    // The pipelined schedule evaluates a group next to the commit of the one before it, so a pod may not read a
+    // counter written by either. Streams where many pods depend on a very recent pod (dense inter-pod affinity)
+    // would stall it at every group: those run the plain schedule.
+    batch_pipe_ok = recent_deps * 10 <= c1;
+    sync_device();
+    sync_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ts0).count();
+    b_headers.ensure((size_t)np * sizeof(KsbPodHeader));  // whole-batch buffers: the replay entry points run them in one launch
+    b_dep.ensure((size_t)np * 4);
+    if (shard_connected && (size_t)np * sizeof(KsbResult) > b_results.cap)
+      throw std::runtime_error("sharded engine: batch larger than the max_batch_pods given to ksb_shard_export");
+    b_results.ensure((size_t)np * sizeof(KsbResult));
+    if (c0 == 0) {
+      // pool size of the whole batch, estimated from the first chunk; grown with its contents kept if that falls short
+      const size_t guess = n_chunks == 1 ? st.pool_words : (st.pool_words * (size_t)np / (size_t)len) * 5 / 4 + 4096;
+      b_pool.ensure(std::max<size_t>(1, guess) * 8);
+    }
+    grow_keep(b_pool, std::max<size_t>(1, st.pool_first + st.pool_words) * 8);
+    char* src = (char*)pin_chunk[which].p;
+    CUDA_OK(cudaMemcpyAsync((KsbPodHeader*)b_headers.d + c0, src, st.hdr_bytes, cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaMemcpyAsync((int32_t*)b_dep.d + c0, src + st.dep_off, (size_t)len * 4, cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaMemcpyAsync((uint64_t*)b_pool.d + st.pool_first, src + st.pool_off, std::max<size_t>(1, st.pool_words) * 8,
+                            cudaMemcpyHostToDevice, stream));
+    stats.h2d_bytes += st.hdr_bytes + st.pool_words * 8 + (size_t)len * 4;
+    a = make_args(len, assume);
+    a.headers = (const KsbPodHeader*)b_headers.d + c0;
+    a.dep = (const int32_t*)b_dep.d + c0;
+    a.results = (KsbResult*)b_results.d + c0;
+    if (c0 == 0) {
+      if (assume) snapshot_dynamic();
+      last_index_before = last_node_index;
+    }
+    // what comes back: the control words (error flag, FitError count, round-robin counter, counters) in one
+    // copy, then the result records
+    ctl_lo = (char*)a.barrier - (char*)b_scratch.d;
+    ctl_hi = (char*)a.counters - (char*)b_scratch.d + 128;
+    res_off = (ctl_hi - ctl_lo + 255) & ~(size_t)255;
+    pin_out.ensure(res_off + (size_t)len * sizeof(KsbResult));
+    CUDA_OK(cudaEventRecord(ev_start, stream));
+    launch(a);
+    CUDA_OK(cudaEventRecord(ev_stop, stream));
+    char* back = (char*)pin_out.p;
+    CUDA_OK(cudaMemcpyAsync(back, (char*)b_scratch.d + ctl_lo, ctl_hi - ctl_lo, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaMemcpyAsync(back + res_off, (KsbResult*)b_results.d + c0, (size_t)len * sizeof(KsbResult), cudaMemcpyDeviceToHost,
+                            stream));
+  };
 
-  // what comes back: the control words (error flag, FitError count, round-robin counter, counters) in one
-  // copy, then the result records
-  const size_t ctl_lo = (char*)a.barrier - (char*)b_scratch.d;
-  const size_t ctl_hi = (char*)a.counters - (char*)b_scratch.d + 128;
-  const size_t res_off = (ctl_hi - ctl_lo + 255) & ~(size_t)255;
-  pin_out.ensure(res_off + (size_t)np * sizeof(KsbResult));
-  char* back = (char*)pin_out.p;
-  CUDA_OK(cudaEventRecord(ev_start, stream));
-  launch(a);
-  CUDA_OK(cudaEventRecord(ev_stop, stream));
-  CUDA_OK(cudaMemcpyAsync(back, (char*)b_scratch.d + ctl_lo, ctl_hi - ctl_lo, cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaMemcpyAsync(back + res_off, b_results.d, (size_t)np * sizeof(KsbResult), cudaMemcpyDeviceToHost, stream));
-  CUDA_OK(cudaStreamSynchronize(stream));
-  float ms = 0;
-  CUDA_OK(cudaEventElapsedTime(&ms, ev_start, ev_stop));
-  memcpy(last_results.data(), back + res_off, (size_t)np * sizeof(KsbResult));
-  int32_t flags[2];
-  uint64_t counters[16];
-  memcpy(&flags[0], back + ((char*)a.error_flag - (char*)a.barrier), 4);
-  memcpy(&flags[1], back + ((char*)a.fiterr_count - (char*)a.barrier), 4);
-  memcpy(&last_node_index, back + ((char*)a.last_node_index - (char*)a.barrier), 8);
-  memcpy(counters, back + ((char*)a.counters - (char*)a.barrier), sizeof counters);
-  stats.last_batch_kernel_ms = ms;
-  stats.d2h_bytes += (size_t)np * sizeof(KsbResult) + (ctl_hi - ctl_lo);
-  if (flags[0] != 0) {
-    layout_dirty = true;  // device state is unknown: rebuild it from the host records next time
-    throw std::runtime_error("device kernel stopped with error code " + std::to_string(flags[0]) +
-                             " (1-4: barrier wait timed out, 5: a group made no progress, 6: peer error); last stage marker " +
-                             std::to_string(counters[14] >> 16) + "/" + std::to_string((counters[14] >> 8) & 0xff) + "/" +
-                             std::to_string(counters[14] & 0xff) + "; first timeout at barrier " +
-                             std::to_string(counters[15] >> 32) + " block " + std::to_string((counters[15] >> 8) & 0xffffff) +
-                             " grid " + std::to_string(grid));
+  uint64_t counters[16] = {0};
+  // wait for the chunk launched last and take its results
+  auto wait_chunk = [&](int c0, int c1) {
+    const int len = c1 - c0;
+    CUDA_OK(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CUDA_OK(cudaEventElapsedTime(&ms, ev_start, ev_stop));
+    kernel_ms += ms;
+    char* back = (char*)pin_out.p;
+    memcpy(last_results.data() + c0, back + res_off, (size_t)len * sizeof(KsbResult));
+    int32_t flags[2];
+    memcpy(&flags[0], back + ((char*)a.error_flag - (char*)a.barrier), 4);
+    memcpy(&flags[1], back + ((char*)a.fiterr_count - (char*)a.barrier), 4);
+    memcpy(&last_node_index, back + ((char*)a.last_node_index - (char*)a.barrier), 8);
+    memcpy(counters, back + ((char*)a.counters - (char*)a.barrier), sizeof counters);
+    stats.d2h_bytes += (size_t)len * sizeof(KsbResult) + (ctl_hi - ctl_lo);
+    if (flags[0] != 0) {
+      layout_dirty = true;  // device state is unknown: rebuild it from the host records next time
+      throw std::runtime_error("device kernel stopped with error code " + std::to_string(flags[0]) +
+                               " (1-4, 7: barrier wait timed out, 5: a group made no progress, 6: peer error); last stage marker " +
+                               std::to_string(counters[14] >> 16) + "/" + std::to_string((counters[14] >> 8) & 0xff) + "/" +
+                               std::to_string(counters[14] & 0xff) + "; first timeout at barrier " +
+                               std::to_string(counters[15] >> 32) + " block " + std::to_string((counters[15] >> 8) & 0xffffff) +
+                               " grid " + std::to_string(grid));
+    }
+    // reason histograms of the chunk's no-fit pods, appended to the batch's; slots are renumbered accordingly
+    const int base = (int)(last_fiterr_hist.size() / KSB_REASON_BITS);
+    const int nfe = std::min(flags[1], (int32_t)KSB_MAX_FITERR);
+    if (nfe > 0) {
+      last_fiterr_hist.resize((size_t)(base + nfe) * KSB_REASON_BITS);
+      CUDA_OK(cudaMemcpy(last_fiterr_hist.data() + (size_t)base * KSB_REASON_BITS, a.fiterr_hist, (size_t)nfe * KSB_REASON_BITS * 4,
+                         cudaMemcpyDeviceToHost));
+      stats.d2h_bytes += (size_t)nfe * KSB_REASON_BITS * 4;
+    }
+    for (int i = c0; i < c1; ++i) {
+      KsbResult& r = last_results[i];
+      if (r.fiterr_slot >= 0) r.fiterr_slot = r.fiterr_slot < nfe ? r.fiterr_slot + base : -1;
+    }
+    stats.pods_scheduled += len;
+    stats.groups += counters[0];
+    stats.group_restarts += counters[1];
+  };
+
+  // results to the caller; the device's assume step mirrored on the host records (scheduler.go:478, storage.go:180-187)
+  auto post_chunk = [&](int c0, int c1) {
+    auto tp0 = std::chrono::steady_clock::now();
+    for (int i = c0; i < c1; ++i) {
+      const KsbResult& r = last_results[i];
+      out[i].status = r.status;
+      out[i].node_index = r.row;
+      out[i].num_filtered = r.num_filtered;
+      out[i].score = r.score;
+      for (int j = 0; j < KSB_MAX_EXT; ++j) out[i].device_mask[j] = r.device_mask[j];
+      if (!assume || r.status != KSB_SCHEDULED) continue;
+      HostNode& hn = *rows[r.row];
+      Pod& p = batch[i];
+      p.node_name = hn.node.name;
+      for (size_t j = 0; j < p.extended.size(); ++j) {
+        p.extended[j].assigned.clear();
+        if (p.extended[j].limits.size() != 1) continue;
+        auto ds = hn.ext.find(p.extended[j].limits.begin()->first);
+        if (ds == hn.ext.end()) continue;
+        int bit = 0;
+        for (auto& dev : ds->second.allocatable) {
+          if ((r.device_mask[j] >> bit) & 1u) p.extended[j].assigned.push_back(dev.first);
+          ++bit;
+        }
+      }
+      apply_node_part_host(r.row, last_encoded[i], r.device_mask);
+      apply_class_part_host(r.row, last_encoded[i].commits, last_encoded[i].spread_inc, +1);
+      host_add_pod(p, hn);
+      pods[p.key()] = HostPod{p};
+    }
+    post_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
+  };
+
+  auto bounds = [&](int c, int* c0, int* c1) {
+    *c0 = c * chunk_len;
+    *c1 = std::min(np, *c0 + chunk_len);
+  };
+  int c0 = 0, c1 = 0, n0 = 0, n1 = 0;
+  bounds(0, &c0, &c1);
+  encode_chunk(c0, c1, 0);
+  launch_chunk(c0, c1, 0);
+  for (int c = 0; c < n_chunks; ++c) {
+    bounds(c, &c0, &c1);
+    const bool more = c + 1 < n_chunks;
+    if (more) {
+      bounds(c + 1, &n0, &n1);
+      encode_chunk(n0, n1, (c + 1) & 1);  // next to the kernel of chunk c
+    }
+    wait_chunk(c0, c1);
+    if (more) launch_chunk(n0, n1, (c + 1) & 1);
+    post_chunk(c0, c1);  // next to the kernel of chunk c+1
   }
-  int nfe = std::min(flags[1], (int32_t)KSB_MAX_FITERR);
-  if (nfe > 0) {
-    last_fiterr_hist.resize((size_t)nfe * KSB_REASON_BITS);
-    CUDA_OK(cudaMemcpy(last_fiterr_hist.data(), a.fiterr_hist, last_fiterr_hist.size() * 4, cudaMemcpyDeviceToHost));
-    stats.d2h_bytes += last_fiterr_hist.size() * 4;
+  if (n_chunks > 1) {
+    // the replay entry points run the whole batch in one launch: dependency indices relative to the batch
+    CUDA_OK(cudaMemcpyAsync(b_dep.d, last_dep.data(), (size_t)np * 4, cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    batch_pipe_ok = recent_deps * 10 <= np;
   }
-  stats.pods_scheduled += np;
-  stats.groups += counters[0];
-  stats.group_restarts += counters[1];
-  for (int i = 0; i < 12; ++i) stats.stage_cycles[i] = counters[2 + i];
+  for (int i = 0; i < 12; ++i) stats.stage_cycles[i] = counters[2 + i];  // of the last launch
   stats.stage_cycles[12] = 0;  // counters[14] is the progress marker of the timeout diagnostics, not a duration
+  stats.last_batch_encode_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() -
+                               kernel_ms - post_ms - sync_ms;
+  if (n_chunks > 1) stats.last_batch_encode_ms = encode_ms;  // overlapped with kernels: report the work, not the wait
+  stats.last_batch_sync_ms = sync_ms;
+  stats.last_batch_kernel_ms = kernel_ms;
+  stats.last_batch_post_ms = post_ms;
+}
 
-  auto tp0 = std::chrono::steady_clock::now();
-  for (int i = 0; i < np; ++i) {
-    const KsbResult& r = last_results[i];
-    out[i].status = r.status;
-    out[i].node_index = r.row;
-    out[i].num_filtered = r.num_filtered;
-    out[i].score = r.score;
-    for (int j = 0; j < KSB_MAX_EXT; ++j) out[i].device_mask[j] = r.device_mask[j];
-    if (!assume || r.status != KSB_SCHEDULED) continue;
-    // mirror the device's assume step on the host records (scheduler.go:478, storage.go:180-187)
-    HostNode& hn = *rows[r.row];
-    Pod& p = batch[i];
-    p.node_name = hn.node.name;
-    for (size_t j = 0; j < p.extended.size(); ++j) {
-      p.extended[j].assigned.clear();
-      if (p.extended[j].limits.size() != 1) continue;
-      auto ds = hn.ext.find(p.extended[j].limits.begin()->first);
-      if (ds == hn.ext.end()) continue;
-      int bit = 0;
-      for (auto& dev : ds->second.allocatable) {
-        if ((r.device_mask[j] >> bit) & 1u) p.extended[j].assigned.push_back(dev.first);
-        ++bit;
-      }
-    }
-    apply_node_part_host(r.row, last_encoded[i], r.device_mask);
-    apply_class_part_host(r.row, last_encoded[i].commits, last_encoded[i].spread_inc, +1);
-    host_add_pod(p, hn);
-    pods[p.key()] = HostPod{p};
+// Grow a device buffer and keep what it holds (the stream must be idle: the old block is freed).
+void Engine::grow_keep(DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return;
+  DevBuf nb;
+  nb.ensure(std::max(bytes, b.cap * 2));
+  if (b.d) {
+    CUDA_OK(cudaMemcpyAsync(nb.d, b.d, b.cap, cudaMemcpyDeviceToDevice, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    b.release();
   }
-  stats.last_batch_post_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
+  b = nb;
 }
 
 void Engine::flush() {
@@ -499,6 +600,12 @@ void Engine::replay_last_batch(int iters, double* avg_ms, ksb_result* out) {
   cudaEventDestroy(ev1);
   last_node_index = saved_index;
   *avg_ms = total / std::max(1, iters);
+  {  // stage cycles and group counts of the replayed launch (the whole batch in one launch)
+    uint64_t counters[16] = {0};
+    CUDA_OK(cudaMemcpy(counters, a.counters, sizeof counters, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 12; ++i) stats.stage_cycles[i] = counters[2 + i];
+    stats.stage_cycles[12] = 0;
+  }
   if (out) {
     std::vector<KsbResult> res(np);
     CUDA_OK(cudaMemcpy(res.data(), b_results.d, (size_t)np * sizeof(KsbResult), cudaMemcpyDeviceToHost));
