@@ -107,6 +107,28 @@ def test_pipelined_is_repeatable(cfg, nodes, pods):
     sess.close()
 
 
+def test_chunked_batch_matches_single_launches():
+    """Batches of 12,288 pods or more go to the device in chunks overlapped with host work; the placements must be
+    those of one launch (the replay runs the whole batch in a single launch and is compared pod by pod) and of
+    small separate batches."""
+    cluster = workloads.generate(3, 1500, 26000)
+    sess = lib.Session(cluster=cluster)
+    a = sess.run(results=False, replay_iters=1)
+    b = sess.run(results=False, batch=6000)
+    sess.close()
+    assert a["placement_hash"] == b["placement_hash"]
+    assert a["lastNodeIndex"] == b["lastNodeIndex"]
+    assert a["fit_errors"] == b["fit_errors"]
+
+
+def test_chunked_batch_matches_oracle_with_fit_errors():
+    """A chunked batch on a cluster that fills up: FitError texts of pods in later chunks come from reason histograms
+    that are collected per launch and renumbered."""
+    cluster = workloads.generate(1, 120, 14000)
+    got, want = compare(cluster, "cfg1 chunked", oracle_opts={"workers": 8})
+    assert sum(1 for r in want["results"] if r["status"] == 2) > 1000
+
+
 def test_pipelined_tight_cluster():
     cluster = workloads.generate(1, 12, 700)
     for n in cluster["nodes"]:
