@@ -9,8 +9,10 @@ sys.path.insert(0, ".")
 from kubernetes_b200 import lib, workloads
 from tests import oracle_lib
 
-for cfg in [int(x) for x in sys.argv[1:]] or [1, 2, 3]:
-    nodes, pods = workloads.CONFIG_SIZES[cfg]
+for spec in sys.argv[1:] or ["1", "2", "3"]:  # "cfg" (BASELINE.json size) or "cfg:nodes:pods"
+    parts = [int(x) for x in spec.split(":")]
+    cfg = parts[0]
+    nodes, pods = parts[1:3] if len(parts) == 3 else workloads.CONFIG_SIZES[cfg]
     cluster = workloads.generate(cfg, nodes, pods)
     t0 = time.time()
     want = oracle_lib.call({"op": "stream", "cluster": cluster, "workers": 16})
