@@ -214,7 +214,7 @@ def main():
         kernel_ms.append(out["kernel_ms"])
         replay_ms.append(out["replay_ms"])
         h2d, d2h = out["h2d_bytes"], out["d2h_bytes"]
-        launches += 1
+        launches += int(out.get("kernel_launches", 1))  # the engine's own count: chunk launches of the e2e pass + the replay
         hashes.add(out["placement_hash"])
         scheduled, fit_errors = out["scheduled"], out["fit_errors"]
         groups, restarts = out["groups"], out["group_restarts"]
@@ -251,8 +251,9 @@ def main():
                    "placement_hash": sorted(hashes)[0]},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_step_ms},
-        # per step: ksb_schedule_batch_kernel once inside the end-to-end pass and once in the resident replay
-        "gpu_launches": 2 * args.steps,
+        # ksb_schedule_batch_kernel launches inside the timed steps, as counted by the engine: one per 4,096-pod chunk
+        # of each end-to-end pass plus one per resident replay
+        "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": ncu_traffic(args.config, n_nodes, n_pods), "peak_source": peak_src, "kernel": "ksb_schedule_batch_kernel",
                      "algorithmic_bytes_per_eval": algo_bytes, "evals_per_launch": n_nodes * n_pods,
@@ -269,6 +270,15 @@ def main():
                            "unit": "us per ksb_schedule call (host to host)",
                            "sample": "pods %d..%d of the stream, one C-ABI call per pod; the first %d calls (cold label / "
                                      "selector-class dictionaries) are reported as cold_max_us only" % (n_cold, n_cold + n_lat, n_cold)}
+    if world == 1:
+        # batch mode: the queue drained 64 pods at a time; a call's duration is the latency of each of its pods
+        bsz = 64
+        n_b = min(n_pods, 64 * 160)
+        bl = sess.run(device=local_rank, results=False, batch=bsz, limit=n_b)
+        if "batch_call_p50_us" in bl:
+            line["latency"]["batch%d" % bsz] = {"call_p50_us": bl["batch_call_p50_us"], "call_p99_us": bl["batch_call_p99_us"],
+                                                 "calls": bl["batch_calls"],
+                                                 "pods_per_s": n_b / (bl["e2e_ms"] / 1000.0)}
     if not args.no_cpu_baseline:
         sample = args.cpu_sample or pick_sample(n_nodes)
         pps, secs, _ = oracle_baseline(cluster, sample, workers)

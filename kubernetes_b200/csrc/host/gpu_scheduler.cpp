@@ -103,6 +103,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   CacheDecorator cache(h);
   double kernel_ms = 0, encode_ms = 0, replay_ms = 0, decode_ms = 0, post_ms = 0, sync_ms = 0;
   std::vector<double> lat_us;
+  std::vector<double> call_us;  // batch mode: duration of each ksb_schedule_batch call
   std::vector<std::array<double, 3>> lat_parts;  // encode, table sync, kernel (ms) of each one-pod call
   ksb_stats st0;  // bytes copied before the timed region (cluster load, ksb_flush) are not this run's
   ksb_get_stats(h.get(), &st0);
@@ -171,9 +172,11 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
     size_t step = batch < 0 ? np : (size_t)batch;
     for (size_t b0 = 0; b0 < np; b0 += step) {
       size_t b1 = std::min(np, b0 + step);
+      auto c0 = std::chrono::steady_clock::now();
       h.check(ksb_schedule_batch(h.get(), (const uint8_t*)s.pod_stream.data(), s.pod_offsets.data() + b0, (int32_t)(b1 - b0),
                                  results.data() + b0),
               "ScheduleBatch");
+      call_us.push_back(std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - c0).count());
       ksb_stats st;
       ksb_get_stats(h.get(), &st);
       kernel_ms += st.last_batch_kernel_ms;
@@ -261,6 +264,14 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
              std::to_string(lat_parts[order[i]][0]) + "," + std::to_string(lat_parts[order[i]][1]) + "," +
              std::to_string(lat_parts[order[i]][2]) + "]";
     out += "]";
+  }
+  if (call_us.size() > 1) {
+    // batch mode: every pod of a call completes when the call returns, so a call's duration is its pods' latency
+    std::vector<double> sorted = call_us;
+    std::sort(sorted.begin(), sorted.end());
+    out += ",\"batch_call_p50_us\":" + std::to_string(sorted[sorted.size() / 2]);
+    out += ",\"batch_call_p99_us\":" + std::to_string(sorted[std::min(sorted.size() - 1, (size_t)(sorted.size() * 0.99))]);
+    out += ",\"batch_calls\":" + std::to_string(sorted.size());
   }
   if (want_results) {
     out += ",\"results\":[";
