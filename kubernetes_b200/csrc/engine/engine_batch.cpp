@@ -317,7 +317,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   // (uploads and the next launch are issued only after the previous chunk's results are back), so the placements
   // are those of one launch over the whole batch.
   constexpr int kChunk = KSB_MAX_FITERR;  // 4,096: every no-fit pod of a chunk keeps its reason histogram
-  const bool chunked = assume && cfg.shard_count <= 1 && np >= 3 * kChunk;
+  const bool chunked = assume && cfg.shard_count <= 1 && np >= 2 * kChunk;
   const int chunk_len = chunked ? kChunk : np;
   const int n_chunks = (np + chunk_len - 1) / chunk_len;
 

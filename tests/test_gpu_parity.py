@@ -108,7 +108,7 @@ def test_pipelined_is_repeatable(cfg, nodes, pods):
 
 
 def test_chunked_batch_matches_single_launches():
-    """Batches of 12,288 pods or more go to the device in chunks overlapped with host work; the placements must be
+    """Batches of 8,192 pods or more go to the device in chunks overlapped with host work; the placements must be
     those of one launch (the replay runs the whole batch in a single launch and is compared pod by pod) and of
     small separate batches."""
     cluster = workloads.generate(3, 1500, 26000)
