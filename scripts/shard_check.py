@@ -29,7 +29,8 @@ dist.barrier()
 out = eng.run(results=False, replay_iters=2)
 res = {"rank": rank, "hash": out["placement_hash"], "kernel_ms": round(out["kernel_ms"], 2),
        "replay_ms": round(out["replay_ms"], 2), "groups": out["groups"], "restarts": out["group_restarts"],
-       "scheduled": out["scheduled"], "lastNodeIndex": out["lastNodeIndex"]}
+       "scheduled": out["scheduled"], "lastNodeIndex": out["lastNodeIndex"],
+       "stage_us_per_pod": [round(c / 1965.0 / pods, 2) for c in out["stage_cycles"]]}
 all_res = [None] * world
 dist.all_gather_object(all_res, res)
 if rank == 0:
