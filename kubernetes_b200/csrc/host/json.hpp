@@ -55,6 +55,13 @@ struct Value {
     if (v->kind == Bool) return v->b ? 1 : 0;
     throw std::runtime_error(std::string("json: key '") + key + "' is not a number");
   }
+  double get_num(const char* key, double dflt = 0.0) const {
+    const Value* v = find(key);
+    if (!v || v->is_null()) return dflt;
+    if (v->kind == Int) return (double)v->i;
+    if (v->kind == Double) return v->d;
+    throw std::runtime_error(std::string("json: key '") + key + "' is not a number");
+  }
   bool get_bool(const char* key, bool dflt = false) const {
     const Value* v = find(key);
     if (!v || v->is_null()) return dflt;

@@ -293,6 +293,119 @@ struct SchedulerCache {
     return true;
   }
   bool RemovePod(const Pod& p) { return ForgetPod(p); }
+
+  // ---- the full pod state machine (cache.go:118-312, expiry :426-462): Initial -> Assumed -> Added -> Deleted /
+  //      Expired. Every transition returns the reference's error text, "" on success. Time is seconds.
+  struct PodState {
+    std::shared_ptr<const Pod> pod;
+    bool bindingFinished = false;
+    bool hasDeadline = false;
+    double deadline = 0;
+  };
+  std::map<std::string, PodState> states;
+  std::set<std::string> assumedPods;
+  double ttl = 30;
+
+  void add_pod_(std::shared_ptr<const Pod> sp) {  // addPod :262-270
+    nodes[sp->node_name].AddPod(sp);
+    podStates[sp->key()] = sp;
+  }
+  void remove_pod_(const Pod& p) {  // removePod :283-293 (subtracts the resources of the object it is given)
+    auto it = nodes.find(p.node_name);
+    if (it == nodes.end()) return;
+    it->second.RemovePod(p);
+    if (it->second.pods.empty() && !it->second.node) nodes.erase(it);
+    podStates.erase(p.key());
+  }
+  std::string assume(const Pod& p) {  // :118-137
+    const std::string key = p.key();
+    if (states.count(key)) return "pod " + key + " state wasn't initial but get assumed";
+    auto sp = std::make_shared<const Pod>(p);
+    add_pod_(sp);
+    states[key].pod = sp;
+    assumedPods.insert(key);
+    return "";
+  }
+  std::string finish_binding(const Pod& p, double now) {  // :139-160
+    auto it = states.find(p.key());
+    if (it != states.end() && assumedPods.count(p.key())) {
+      it->second.bindingFinished = true;
+      it->second.hasDeadline = true;
+      it->second.deadline = now + ttl;
+    }
+    return "";
+  }
+  std::string forget(const Pod& p) {  // :162-190
+    const std::string key = p.key();
+    auto it = states.find(key);
+    if (it != states.end() && it->second.pod->node_name != p.node_name)
+      return "pod " + key + " state was assumed on a different node";
+    if (it != states.end() && assumedPods.count(key)) {
+      remove_pod_(p);
+      assumedPods.erase(key);
+      states.erase(key);
+      return "";
+    }
+    return "pod " + key + " state wasn't assumed but get forgotten";
+  }
+  std::string add(const Pod& p) {  // :223-257
+    const std::string key = p.key();
+    auto it = states.find(key);
+    auto sp = std::make_shared<const Pod>(p);
+    if (it != states.end() && assumedPods.count(key)) {
+      if (it->second.pod->node_name != p.node_name) {  // added to a different node than it was assumed to
+        remove_pod_(*it->second.pod);
+        add_pod_(sp);
+      }
+      assumedPods.erase(key);
+      it->second.hasDeadline = false;
+      it->second.pod = sp;
+      return "";
+    }
+    if (it == states.end()) {  // expired (or never seen): add it back
+      add_pod_(sp);
+      states[key].pod = sp;
+      return "";
+    }
+    return "pod was already in added state. Pod key: " + key;
+  }
+  std::string update(const Pod& oldp, const Pod& newp) {  // :259-285
+    const std::string key = oldp.key();
+    auto it = states.find(key);
+    if (it != states.end() && !assumedPods.count(key)) {
+      if (it->second.pod->node_name != newp.node_name)
+        return "fatal: pod " + key + " updated on a different node than previously added to";
+      remove_pod_(oldp);
+      add_pod_(std::make_shared<const Pod>(newp));
+      return "";
+    }
+    return "pod " + key + " state wasn't added but get updated";
+  }
+  std::string remove(const Pod& p) {  // :287-312
+    const std::string key = p.key();
+    auto it = states.find(key);
+    if (it != states.end() && !assumedPods.count(key)) {
+      if (it->second.pod->node_name != p.node_name)
+        return "fatal: pod " + key + " removed from a different node than previously added to";
+      remove_pod_(*it->second.pod);
+      states.erase(key);
+      return "";
+    }
+    return "pod state wasn't added but get removed. Pod key: " + key;
+  }
+  bool is_assumed(const Pod& p) const { return assumedPods.count(p.key()) != 0; }  // :314-328
+  void cleanup(double now) {  // cleanupAssumedPods :431-453, expirePod :455-462
+    std::vector<std::string> keys(assumedPods.begin(), assumedPods.end());
+    for (auto& key : keys) {
+      PodState& ps = states.at(key);
+      if (!ps.bindingFinished) continue;
+      if (now > ps.deadline) {
+        remove_pod_(*ps.pod);
+        assumedPods.erase(key);
+        states.erase(key);
+      }
+    }
+  }
 };
 
 }  // namespace oracle

@@ -236,18 +236,14 @@ static std::string run_device_match(const json::Value& req) {
 }
 
 // Dump one node's NodeInfo aggregates after loading the cluster (cache tests).
-static std::string run_node_info(const json::Value& req) {
-  ksb::Cluster cl = ksb::cluster_from_json(*req.find("cluster"));
-  Oracle o;
-  o.load(cl);
-  for (auto& p : req.get_arr("forget")) o.cache.ForgetPod(ksb::pod_from_json(p));
-  const NodeInfo& ni = o.cache.nodes.at(req.get_str("node"));
+static std::string node_info_json(const NodeInfo& ni) {
   std::string out = "{";
   out += "\"requested\":{\"cpu\":" + std::to_string(ni.requested.MilliCPU) + ",\"memory\":" +
          std::to_string(ni.requested.Memory) + ",\"gpu\":" + std::to_string(ni.requested.NvidiaGPU) +
          ",\"ephemeral\":" + std::to_string(ni.requested.EphemeralStorage) + ",\"scalars\":{";
   bool first = true;
   for (auto& kv : ni.requested.Scalar) {
+    if (kv.second == 0) continue;  // a name whose pods are all gone: the Go map keeps a zero entry, nothing reads it
     if (!first) out += ",";
     first = false;
     json::escape_to(out, kv.first);
@@ -280,6 +276,56 @@ static std::string run_node_info(const json::Value& req) {
   return out;
 }
 
+static std::string run_node_info(const json::Value& req) {
+  ksb::Cluster cl = ksb::cluster_from_json(*req.find("cluster"));
+  Oracle o;
+  o.load(cl);
+  for (auto& p : req.get_arr("forget")) o.cache.ForgetPod(ksb::pod_from_json(p));
+  return node_info_json(o.cache.nodes.at(req.get_str("node")));
+}
+
+// The cache state machine driven by a list of operations (schedulercache/cache.go:118-312, :426-462):
+// {"ttl": seconds, "ops": [{"do": "assume"|"finish"|"forget"|"add"|"update"|"remove"|"cleanup"|"add_node"|
+// "remove_node", "pod": {...}, "old": {...}, "node": {...}, "name": "...", "now": seconds}], "report": [node names]}
+// -> {"errors": [text per op, "" = nil], "assumed": [per op, for "is_assumed" ops], "nodes": {name: NodeInfo | null}}.
+static std::string run_cache_ops(const json::Value& req) {
+  SchedulerCache c;
+  c.ttl = req.get_num("ttl", 30.0);
+  std::string errors = "[";
+  bool first = true;
+  for (auto& op : req.get_arr("ops")) {
+    const std::string what = op.get_str("do");
+    std::string err;
+    if (what == "assume") err = c.assume(ksb::pod_from_json(*op.find("pod")));
+    else if (what == "finish") err = c.finish_binding(ksb::pod_from_json(*op.find("pod")), op.get_num("now", 0.0));
+    else if (what == "forget") err = c.forget(ksb::pod_from_json(*op.find("pod")));
+    else if (what == "add") err = c.add(ksb::pod_from_json(*op.find("pod")));
+    else if (what == "update") err = c.update(ksb::pod_from_json(*op.find("old")), ksb::pod_from_json(*op.find("pod")));
+    else if (what == "remove") err = c.remove(ksb::pod_from_json(*op.find("pod")));
+    else if (what == "cleanup") c.cleanup(op.get_num("now", 0.0));
+    else if (what == "is_assumed") err = c.is_assumed(ksb::pod_from_json(*op.find("pod"))) ? "assumed" : "not assumed";
+    else if (what == "add_node") c.AddNode(ksb::node_from_json(*op.find("node")));
+    else if (what == "remove_node") c.RemoveNode(op.get_str("name"));
+    else err = "unknown op " + what;
+    if (!first) errors += ",";
+    first = false;
+    json::escape_to(errors, err);
+  }
+  errors += "]";
+  std::string out = "{\"errors\":" + errors + ",\"nodes\":{";
+  first = true;
+  for (auto& nv : req.get_arr("report")) {
+    const std::string name = nv.s;
+    if (!first) out += ",";
+    first = false;
+    json::escape_to(out, name);
+    auto it = c.nodes.find(name);
+    out += ":" + (it == c.nodes.end() ? std::string("null") : node_info_json(it->second));
+  }
+  out += "}}";
+  return out;
+}
+
 extern "C" {
 
 // Generic entry: {"op": "stream" | "priority" | "predicate" | "device_match" | "node_info", ...}.
@@ -294,6 +340,7 @@ char* oracle_call(const char* json_in) {
     else if (op == "predicate") out = run_predicate(req);
     else if (op == "device_match") out = run_device_match(req);
     else if (op == "node_info") out = run_node_info(req);
+    else if (op == "cache_ops") out = run_cache_ops(req);
     else out = "{\"error\":\"unknown op\"}";
   } catch (const std::exception& e) {
     out = "{\"error\":";

@@ -132,4 +132,81 @@ def builders(g):
                           "expect": {"requested": {"cpu": req[0], "memory": req[1], "gpu": 0, "ephemeral": 0, "scalars": req[2]},
                                      "nonzero": {"cpu": nz[0], "memory": nz[1]}, "pods": len(idx), "usedPorts": ports}})
 
-    return [build_prefer_avoid, build_hard_affinity_weight, build_fits_host, build_pressure_and_conditions, build_assume_pod]
+    # ----------------------------------------------------------------- cache state machine
+    # schedulercache/cache_test.go:200-690: Assume / FinishBinding / Add / Update / Remove / Forget / expiry.
+    # Times are seconds from the test's `now`; ttl = 10 s as in the tests.
+    def build_cache_ops():
+        port = lambda p, ip="127.0.0.1": {"hostIP": ip, "hostPort": p, "protocol": "TCP"}
+
+        def base(node_, name, cpu, mem, ports):
+            return pod(node_, ns="node-namespace", name=name, containers=[ctr(requests={"cpu": cpu, "memory": mem}, ports=ports)])
+
+        def info(cpu, mem, npods, ports):
+            return {"requested": {"cpu": cpu, "memory": mem, "gpu": 0, "ephemeral": 0, "scalars": {}},
+                    "nonzero": {"cpu": cpu, "memory": mem}, "pods": npods, "usedPorts": ports, "available": {}}
+
+        def case(src, test, ops, nodes, ttl=10):
+            CASES.append({"op": "cache_ops", "source": src, "test": test, "ttl": ttl, "ops": ops, "report": sorted(nodes),
+                          "expect": {"errors": [""] * len(ops), "nodes": nodes}})
+
+        assume = lambda p, t: [{"do": "assume", "pod": p}, {"do": "finish", "pod": p, "now": t}]
+        t1 = base("node", "test-1", 100, 500, [port(80)])
+        t2 = base("node", "test-2", 200, 1024, [port(8080)])
+        src = "schedulercache/cache_test.go:200-256"
+        case(src, "TestExpirePod #0: assumed pod would expire", assume(t1, 0) + [{"do": "cleanup", "now": 20}], {"node": None})
+        case(src, "TestExpirePod #1: first one would expire, second one would not",
+             assume(t1, 0) + assume(t2, 15) + [{"do": "cleanup", "now": 20}], {"node": info(200, 1024, 1, ["TCP/127.0.0.1/8080"])})
+        src = "schedulercache/cache_test.go:258-309"
+        case(src, "TestAddPodWillConfirm: the Add()ed pod is confirmed, the other assumed pod expires",
+             assume(t1, 0) + assume(t2, 0) + [{"do": "add", "pod": t1}, {"do": "cleanup", "now": 20}],
+             {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])})
+        src = "schedulercache/cache_test.go:311-372"
+        wild = lambda p: {"hostPort": p}
+        assumed = base("assumed-node-1", "test-1", 100, 500, [wild(80)])
+        added = base("actual-node", "test-1", 100, 500, [wild(80)])
+        updated = base("actual-node", "test-1", 200, 500, [wild(90)])
+        case(src, "TestAddPodWillReplaceAssumed: added to another node than assumed, then updated",
+             assume(assumed, 0) + [{"do": "add", "pod": added}, {"do": "update", "old": added, "pod": updated}],
+             {"assumed-node-1": None, "actual-node": info(200, 500, 1, ["TCP/0.0.0.0/90"])})
+        src = "schedulercache/cache_test.go:374-420"
+        t = base("node", "test", 100, 500, [port(80)])
+        u = base("node", "test", 200, 1024, [port(8080)])
+        case(src, "TestAddPodAfterExpiration: expired, then added back",
+             assume(t, 0) + [{"do": "cleanup", "now": 20}, {"do": "add", "pod": t}], {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])})
+        src = "schedulercache/cache_test.go:422-488"
+        case(src, "TestUpdatePod: added, updated once", [{"do": "add", "pod": t}, {"do": "update", "old": t, "pod": u}],
+             {"node": info(200, 1024, 1, ["TCP/127.0.0.1/8080"])})
+        case(src, "TestUpdatePod: added, updated twice",
+             [{"do": "add", "pod": t}, {"do": "update", "old": t, "pod": u}, {"do": "update", "old": u, "pod": t}],
+             {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])})
+        src = "schedulercache/cache_test.go:490-565"
+        case(src, "TestExpireAddUpdatePod: assumed, expired, added, updated twice",
+             assume(t, 0) + [{"do": "cleanup", "now": 20}, {"do": "add", "pod": t}, {"do": "update", "old": t, "pod": u},
+                             {"do": "update", "old": u, "pod": t}], {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])})
+        src = "schedulercache/cache_test.go:567-608"
+        case(src, "TestRemovePod: after Add", [{"do": "add", "pod": t}], {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])}, ttl=1)
+        case(src, "TestRemovePod: after Add and Remove", [{"do": "add", "pod": t}, {"do": "remove", "pod": t}], {"node": None}, ttl=1)
+        src = "schedulercache/cache_test.go:610-670"
+        ops = assume(t, 0) + [{"do": "is_assumed", "pod": t}, {"do": "forget", "pod": t}, {"do": "is_assumed", "pod": t},
+                              {"do": "cleanup", "now": 20}]
+        CASES.append({"op": "cache_ops", "source": src, "test": "TestForgetPod", "ttl": 10, "ops": ops, "report": ["node"],
+                      "expect": {"errors": ["", "", "assumed", "", "not assumed", ""], "nodes": {"node": None}}})
+        # error returns of the state machine (cache.go:127-129, :176-178, :188-190, :252-254, :281-283, :308-310)
+        src = "schedulercache/cache.go:118-312"
+        k = "node-namespace/test"
+        other = base("elsewhere", "test", 100, 500, [port(80)])
+        ops = [{"do": "assume", "pod": t}, {"do": "assume", "pod": t}, {"do": "update", "old": t, "pod": u},
+               {"do": "remove", "pod": t}, {"do": "forget", "pod": other}, {"do": "add", "pod": t}, {"do": "add", "pod": t},
+               {"do": "forget", "pod": t}]
+        CASES.append({"op": "cache_ops", "source": src, "test": "error texts of invalid transitions", "ttl": 10, "ops": ops,
+                      "report": ["node"],
+                      "expect": {"errors": ["", "pod %s state wasn't initial but get assumed" % k,
+                                            "pod %s state wasn't added but get updated" % k,
+                                            "pod state wasn't added but get removed. Pod key: %s" % k,
+                                            "pod %s state was assumed on a different node" % k, "",
+                                            "pod was already in added state. Pod key: %s" % k,
+                                            "pod %s state wasn't assumed but get forgotten" % k],
+                                 "nodes": {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])}}})
+
+    return [build_prefer_avoid, build_hard_affinity_weight, build_fits_host, build_pressure_and_conditions, build_assume_pod,
+            build_cache_ops]

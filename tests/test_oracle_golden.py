@@ -47,6 +47,9 @@ def check_case(c, call):
     elif c["op"] == "node_info":
         for k, v in exp.items():
             assert out[k] == v, (k, out, c["source"], c["test"])
+    elif c["op"] == "cache_ops":
+        assert out["errors"] == exp["errors"], (out["errors"], c["source"], c["test"])
+        assert out["nodes"] == exp["nodes"], (out["nodes"], c["source"], c["test"])
     else:
         raise AssertionError("unknown op " + c["op"])
 
