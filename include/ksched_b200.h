@@ -140,6 +140,14 @@ int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n);
  * "MatchNodeSelector", ...); for the extended-resource bits, the text for the pod of the last call. Empty if unused. */
 int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len);
 
+/* The NodeInfo aggregates the cache keeps for node `name` (schedulercache/node_info.go:35-78), as the JSON object
+ * {"requested": {"cpu", "memory", "gpu", "ephemeral", "scalars": {name: n}}, "nonzero": {"cpu", "memory"}, "pods": n,
+ * "usedPorts": ["proto/ip/port"], "available": {resource: [device ids]}}, or "null" when no NodeInfo exists under that
+ * name (cache.go:283-293 drops it with its last pod when the Node object is gone). The device columns of the row are
+ * read back and compared with the host records first; a difference is an error. *len receives the text length;
+ * returns 1 if buf was too small. */
+int32_t ksb_node_info(ksb_engine* e, const char* name, size_t name_len, char* buf, size_t buf_len, size_t* len);
+
 /* genericScheduler.lastNodeIndex (core/generic_scheduler.go:100): selectHost's round-robin counter. */
 uint64_t ksb_get_last_node_index(const ksb_engine* e);
 void ksb_set_last_node_index(ksb_engine* e, uint64_t v);

@@ -195,6 +195,20 @@ int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len) {
   });
 }
 
+int32_t ksb_node_info(ksb_engine* e, const char* name, size_t name_len, char* buf, size_t buf_len, size_t* len) {
+  bool small = false;
+  int32_t rc = guarded(e, [&] {
+    std::string t = e->impl->node_info_json(std::string(name ? name : "", name_len));
+    if (len) *len = t.size();
+    if (!buf || buf_len < t.size() + 1) {
+      small = true;
+      return;
+    }
+    memcpy(buf, t.c_str(), t.size() + 1);
+  });
+  return rc != 0 ? rc : (small ? 1 : 0);
+}
+
 int32_t ksb_flush(ksb_engine* e) {
   return guarded(e, [&] { e->impl->flush(); });
 }

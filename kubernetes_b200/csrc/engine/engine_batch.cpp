@@ -903,6 +903,78 @@ void Engine::pod_remove(const std::string& ns, const std::string& name) {
   arena_dirty = true;
 }
 
+// NodeInfo aggregates of one node as JSON (the fields schedulercache's tests compare: cache_test.go:30-44): requested,
+// nonzero, pod count, used ports, available device ids. "null" when the cache holds no NodeInfo under that name. For a
+// node that has a row on this GPU the device columns are read back and must agree with the host records.
+std::string Engine::node_info_json(const std::string& name) {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  auto it = nodes.find(name);
+  if (it == nodes.end()) return "null";
+  if (it->second.has_node) {
+    if (layout_dirty) rebuild_layout();
+    if (n > 0) sync_device();
+    CUDA_OK(cudaStreamSynchronize(stream));
+  }
+  it = nodes.find(name);
+  const HostNode& hn = it->second;
+  const int lrow = hn.row - lbase;
+  if (hn.has_node && hn.row >= 0 && lrow >= 0 && lrow < ln) {
+    int64_t dv[6];
+    const int cols[6] = {I64_REQ_CPU, I64_REQ_MEM, I64_REQ_AGPU, I64_REQ_EPH, I64_NZ_CPU, I64_NZ_MEM};
+    for (int i = 0; i < 6; ++i)
+      CUDA_OK(cudaMemcpy(&dv[i], (int64_t*)b_i64.d + (size_t)cols[i] * ln_pad + lrow, 8, cudaMemcpyDeviceToHost));
+    int32_t dpods = 0;
+    CUDA_OK(cudaMemcpy(&dpods, (int32_t*)b_u32.d + (size_t)U32_NUM_PODS * ln_pad + lrow, 4, cudaMemcpyDeviceToHost));
+    const int64_t hv[6] = {hn.req_cpu, hn.req_mem, hn.req_agpu, hn.req_eph, hn.nz_cpu, hn.nz_mem};
+    for (int i = 0; i < 6; ++i)
+      if (dv[i] != hv[i])
+        throw std::runtime_error("node " + name + ": device column " + std::to_string(cols[i]) + " holds " + std::to_string(dv[i]) +
+                                 ", host record " + std::to_string(hv[i]));
+    if (dpods != (int32_t)hn.pod_keys.size())
+      throw std::runtime_error("node " + name + ": device pod count " + std::to_string(dpods) + ", host record " +
+                               std::to_string(hn.pod_keys.size()));
+  }
+  auto esc = [](const std::string& t) {
+    std::string o = "\"";
+    for (char c : t) {
+      if (c == '"' || c == '\\') o.push_back('\\');
+      o.push_back(c);
+    }
+    return o + "\"";
+  };
+  std::string out = "{\"requested\":{\"cpu\":" + std::to_string(hn.req_cpu) + ",\"memory\":" + std::to_string(hn.req_mem) +
+                    ",\"gpu\":" + std::to_string(hn.req_agpu) + ",\"ephemeral\":" + std::to_string(hn.req_eph) + ",\"scalars\":{";
+  bool first = true;
+  for (auto& kv : hn.req_scalar) {
+    if (kv.second == 0) continue;
+    out += std::string(first ? "" : ",") + esc(kv.first) + ":" + std::to_string(kv.second);
+    first = false;
+  }
+  out += "}},\"nonzero\":{\"cpu\":" + std::to_string(hn.nz_cpu) + ",\"memory\":" + std::to_string(hn.nz_mem) + "},\"pods\":" +
+         std::to_string(hn.pod_keys.size()) + ",\"usedPorts\":[";
+  first = true;
+  for (auto& p : hn.used_ports) {
+    out += std::string(first ? "" : ",") + esc(p);
+    first = false;
+  }
+  out += "],\"available\":{";
+  first = true;
+  for (auto& kv : hn.ext) {
+    if (!kv.second.domain_present) continue;
+    out += std::string(first ? "" : ",") + esc(kv.first) + ":[";
+    first = false;
+    bool f2 = true;
+    for (auto& id : kv.second.available) {
+      out += std::string(f2 ? "" : ",") + esc(id);
+      f2 = false;
+    }
+    out += "]";
+  }
+  out += "}}";
+  return out;
+}
+
 const std::string* Engine::node_name_at(int row) const {
   if (row < 0 || row >= (int)rows.size()) return nullptr;
   return &rows[row]->node.name;

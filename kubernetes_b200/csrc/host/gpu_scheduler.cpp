@@ -161,7 +161,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
           auto it = o.binding.find(e.name);
           if (it != o.binding.end()) e.assigned = it->second;
         }
-        cache.AssumePod(assumed);
+        const std::string cache_err = cache.AssumePod(assumed);
+        if (!cache_err.empty()) throw std::runtime_error(cache_err);
       } catch (const FitError& fe) {
         messages[i] = fe.what();
       } catch (const std::exception& ex) {
@@ -364,6 +365,59 @@ char* ksbh_session_run(void* session, const char* options_json) {
 }
 
 void ksbh_free(char* p) { free(p); }
+
+// The cache state machine driven by a list of operations on a fresh engine; same request and reply as the oracle's
+// "cache_ops" (oracle/oracle_capi.cpp): {"ttl", "ops": [{"do", "pod", "old", "node", "name", "now"}], "report": [...]}.
+char* ksbh_cache_ops(const char* request_json) {
+  try {
+    json::Value req = json::parse(request_json);
+    ksb_config cfg = config_from(req);
+    EngineHandle h(cfg);
+    CacheDecorator c(h, req.get_num("ttl", 30.0));
+    std::string errors = "[";
+    bool first = true;
+    for (auto& op : req.get_arr("ops")) {
+      const std::string what = op.get_str("do");
+      std::string err;
+      if (what == "assume") err = c.AssumePod(pod_from_json(*op.find("pod")));
+      else if (what == "finish") err = c.FinishBinding(pod_from_json(*op.find("pod")), op.get_num("now", 0.0));
+      else if (what == "forget") err = c.ForgetPod(pod_from_json(*op.find("pod")));
+      else if (what == "add") err = c.AddPod(pod_from_json(*op.find("pod")));
+      else if (what == "update") err = c.UpdatePod(pod_from_json(*op.find("old")), pod_from_json(*op.find("pod")));
+      else if (what == "remove") err = c.RemovePod(pod_from_json(*op.find("pod")));
+      else if (what == "cleanup") c.CleanupAssumedPods(op.get_num("now", 0.0));
+      else if (what == "is_assumed") err = c.IsAssumedPod(pod_from_json(*op.find("pod"))) ? "assumed" : "not assumed";
+      else if (what == "add_node") c.AddNode(node_from_json(*op.find("node")));
+      else if (what == "remove_node") {
+        Node n;
+        n.name = op.get_str("name");
+        c.RemoveNode(n);
+      } else err = "unknown op " + what;
+      errors += std::string(first ? "" : ",") + esc(err);
+      first = false;
+    }
+    errors += "]";
+    std::string out = "{\"errors\":" + errors + ",\"nodes\":{";
+    first = true;
+    for (auto& nv : req.get_arr("report")) {
+      const std::string name = nv.s;
+      std::vector<char> buf(1 << 16);
+      size_t len = 0;
+      int32_t rc = ksb_node_info(h.get(), name.data(), name.size(), buf.data(), buf.size(), &len);
+      if (rc == 1) {
+        buf.resize(len + 1);
+        rc = ksb_node_info(h.get(), name.data(), name.size(), buf.data(), buf.size(), &len);
+      }
+      h.check(rc, "node_info");
+      out += std::string(first ? "" : ",") + esc(name) + ":" + std::string(buf.data(), len);
+      first = false;
+    }
+    out += "}}";
+    return dup(out);
+  } catch (const std::exception& ex) {
+    return dup(std::string("{\"error\":") + esc(ex.what()) + "}");
+  }
+}
 
 // ---- a loaded engine kept open across calls (sharded runs: load, exchange IPC handles, then run) ----
 

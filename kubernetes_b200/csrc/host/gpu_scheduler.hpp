@@ -13,6 +13,7 @@
 #pragma once
 #include <map>
 #include <stdexcept>
+#include <set>
 #include <string>
 #include <vector>
 
@@ -56,19 +57,120 @@ class EngineHandle {
 
 // schedulercache.Cache decorator: every mutation the Go scheduler applies to its own cache is
 // forwarded to the engine. Method names follow interface.go:61-121.
+// schedulercache.Cache over the engine: the pod state machine of cache.go:118-312 (Initial -> Assumed -> Added ->
+// Deleted / Expired, expiry :426-462) kept on the host, the node aggregates in the engine. Every transition returns
+// the reference's error text ("" = nil) instead of throwing, as the Go methods return `error`. Time is in seconds
+// and injected, as the reference's tests do with finishBinding / cleanupAssumedPods.
 class CacheDecorator {
  public:
-  explicit CacheDecorator(EngineHandle& h) : h_(h) {}
+  explicit CacheDecorator(EngineHandle& h, double ttl_seconds = 30.0) : h_(h), ttl_(ttl_seconds) {}
   void AddNode(const Node& n) { upsert(n); }
   void UpdateNode(const Node& /*old*/, const Node& n) { upsert(n); }
   void RemoveNode(const Node& n) { h_.check(ksb_node_remove(h_.get(), n.name.data(), n.name.size()), "RemoveNode"); }
-  void AssumePod(const Pod& p) { add(p, "AssumePod"); }
-  void AddPod(const Pod& p) { add(p, "AddPod"); }
-  void ForgetPod(const Pod& p) { remove(p, "ForgetPod"); }
-  void RemovePod(const Pod& p) { remove(p, "RemovePod"); }
+
+  std::string AssumePod(const Pod& p) {  // :118-137
+    const std::string key = p.key();
+    if (states_.count(key)) return "pod " + key + " state wasn't initial but get assumed";
+    add(p, "AssumePod");
+    states_[key].pod = p;
+    assumed_.insert(key);
+    return "";
+  }
+  std::string FinishBinding(const Pod& p, double now) {  // :139-160
+    auto it = states_.find(p.key());
+    if (it != states_.end() && assumed_.count(p.key())) {
+      it->second.binding_finished = true;
+      it->second.has_deadline = true;
+      it->second.deadline = now + ttl_;
+    }
+    return "";
+  }
+  std::string ForgetPod(const Pod& p) {  // :162-190
+    const std::string key = p.key();
+    auto it = states_.find(key);
+    if (it != states_.end() && it->second.pod.node_name != p.node_name) return "pod " + key + " state was assumed on a different node";
+    if (it != states_.end() && assumed_.count(key)) {
+      remove(p, "ForgetPod");
+      assumed_.erase(key);
+      states_.erase(key);
+      return "";
+    }
+    return "pod " + key + " state wasn't assumed but get forgotten";
+  }
+  std::string AddPod(const Pod& p) {  // :223-257
+    const std::string key = p.key();
+    auto it = states_.find(key);
+    if (it != states_.end() && assumed_.count(key)) {
+      if (it->second.pod.node_name != p.node_name) {  // added to a different node than it was assumed to
+        remove(it->second.pod, "AddPod");
+        add(p, "AddPod");
+      }
+      assumed_.erase(key);
+      it->second.has_deadline = false;
+      it->second.pod = p;
+      return "";
+    }
+    if (it == states_.end()) {  // expired, or never seen: add it (back)
+      add(p, "AddPod");
+      states_[key].pod = p;
+      return "";
+    }
+    return "pod was already in added state. Pod key: " + key;
+  }
+  std::string UpdatePod(const Pod& oldp, const Pod& newp) {  // :259-285
+    const std::string key = oldp.key();
+    auto it = states_.find(key);
+    if (it != states_.end() && !assumed_.count(key)) {
+      if (it->second.pod.node_name != newp.node_name)
+        return "fatal: pod " + key + " updated on a different node than previously added to";
+      remove(oldp, "UpdatePod");
+      add(newp, "UpdatePod");
+      return "";
+    }
+    return "pod " + key + " state wasn't added but get updated";
+  }
+  std::string RemovePod(const Pod& p) {  // :287-312
+    const std::string key = p.key();
+    auto it = states_.find(key);
+    if (it != states_.end() && !assumed_.count(key)) {
+      if (it->second.pod.node_name != p.node_name)
+        return "fatal: pod " + key + " removed from a different node than previously added to";
+      remove(it->second.pod, "RemovePod");
+      states_.erase(key);
+      return "";
+    }
+    return "pod state wasn't added but get removed. Pod key: " + key;
+  }
+  bool IsAssumedPod(const Pod& p) const { return assumed_.count(p.key()) != 0; }  // :314-328
+  void CleanupAssumedPods(double now) {  // :431-462
+    std::vector<std::string> keys(assumed_.begin(), assumed_.end());
+    for (auto& key : keys) {
+      State& st = states_.at(key);
+      if (!st.binding_finished) continue;  // binding still in progress
+      if (now > st.deadline) {
+        remove(st.pod, "expirePod");
+        assumed_.erase(key);
+        states_.erase(key);
+      }
+    }
+  }
+  // Pods the engine placed and assumed itself (ksb_schedule_batch) enter the state machine as assumed.
+  void NoteAssumed(const Pod& p) {
+    states_[p.key()].pod = p;
+    assumed_.insert(p.key());
+  }
 
  private:
+  struct State {
+    Pod pod;
+    bool binding_finished = false;
+    bool has_deadline = false;
+    double deadline = 0;
+  };
   EngineHandle& h_;
+  double ttl_;
+  std::map<std::string, State> states_;
+  std::set<std::string> assumed_;
   void upsert(const Node& n) {
     wire::Writer w;
     wire::put(w, n);

@@ -18,7 +18,7 @@ CABI_SYMBOLS = [
     "ksb_config_default", "ksb_create", "ksb_destroy", "ksb_last_error", "ksb_node_upsert", "ksb_node_remove",
     "ksb_pod_add", "ksb_pod_remove", "ksb_selector_owner_upsert", "ksb_selector_owner_remove", "ksb_schedule",
     "ksb_schedule_batch", "ksb_node_name", "ksb_device_id", "ksb_fit_error_message", "ksb_get_last_node_index",
-    "ksb_set_last_node_index", "ksb_failed_predicates", "ksb_reason_name", "ksb_flush", "ksb_get_stats", "ksb_replay_last_batch", "ksb_replay_last_batch_noalloc",
+    "ksb_set_last_node_index", "ksb_failed_predicates", "ksb_reason_name", "ksb_node_info", "ksb_flush", "ksb_get_stats", "ksb_replay_last_batch", "ksb_replay_last_batch_noalloc",
     "ksb_shard_export", "ksb_shard_connect",
 ]
 
@@ -82,8 +82,24 @@ def host():
         lib.ksbh_session_run.restype = ctypes.c_void_p
         lib.ksbh_session_run.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
         lib.ksbh_free.argtypes = [ctypes.c_void_p]
+        lib.ksbh_cache_ops.restype = ctypes.c_void_p
+        lib.ksbh_cache_ops.argtypes = [ctypes.c_char_p]
         _host = lib
     return _host
+
+
+def cache_ops(request):
+    """Drive the scheduler-cache state machine (host mirror of schedulercache.Cache over a fresh engine) with a list of
+    operations; same request and reply as the oracle's "cache_ops" op."""
+    h = host()
+    p = h.ksbh_cache_ops(json.dumps(request).encode())
+    try:
+        out = json.loads(ctypes.string_at(p).decode())
+    finally:
+        h.ksbh_free(p)
+    if "error" in out:
+        raise RuntimeError("engine: " + out["error"])
+    return out
 
 
 class Session:
