@@ -208,5 +208,35 @@ def builders(g):
                                             "pod %s state wasn't assumed but get forgotten" % k],
                                  "nodes": {"node": info(100, 500, 1, ["TCP/127.0.0.1/80"])}}})
 
+    # ----------------------------------------------------------------- fork: device bookkeeping of the cache
+    # schedulercache/node_info_test.go:111-186 (TestAddAndRemovePodExtendedResources), driven through the cache
+    # (the Go test calls NodeInfo.AddPod directly; pods get names here because the cache keys them)
+    def build_device_cache():
+        src = "schedulercache/node_info_test.go:111-186"
+        r1, r2 = "nvidia.com/gpu", "nvidia.com/bar"
+        ids = ["someId%d" % i for i in range(32)]
+        devs = lambda: [{"id": i, "health": "Healthy", "attributes": {}} for i in ids]
+        n = node("n", extendedResources={r1: devs(), r2: devs()})
+        pods_ = []
+        for i in range(16):
+            pods_.append(pod("n", ns="d", name="p%d" % i, containers=[{}],
+                             extendedResources=[{"name": "foo", "limits": {r1: 1}, "assigned": ["someId%d" % i]}]))
+        for i in range(16, 24):
+            pods_.append(pod("n", ns="d", name="p%d" % i, containers=[{}],
+                             extendedResources=[{"name": "foo", "limits": {r1: 2}, "assigned": ["someId%d" % i, "someId%d" % (i + 8)]}]))
+        adds = [{"do": "add_node", "node": n}] + [{"do": "add", "pod": p} for p in pods_]
+        removes = [{"do": "remove", "pod": p} for p in pods_]
+        mib200 = 200 * 1024 * 1024
+
+        def info(npods, avail1):
+            return {"requested": {"cpu": 0, "memory": 0, "gpu": 0, "ephemeral": 0, "scalars": {}},
+                    "nonzero": {"cpu": 100 * npods, "memory": mib200 * npods}, "pods": npods, "usedPorts": [],
+                    "available": {r2: sorted(ids), r1: sorted(avail1)}}
+
+        for test, ops, expect in [("after adding 24 pods every nvidia.com/gpu device is used", adds, info(24, [])),
+                                  ("after removing them all 32 devices are available again", adds + removes, info(0, ids))]:
+            CASES.append({"op": "cache_ops", "source": src, "test": "TestAddAndRemovePodExtendedResources: " + test, "ttl": 30,
+                          "ops": ops, "report": ["n"], "expect": {"errors": [""] * len(ops), "nodes": {"n": expect}}})
+
     return [build_prefer_avoid, build_hard_affinity_weight, build_fits_host, build_pressure_and_conditions, build_assume_pod,
-            build_cache_ops]
+            build_cache_ops, build_device_cache]
