@@ -45,6 +45,7 @@ static void result_to_json(std::string& out, const ScheduleResult& r) {
 
 static void apply_options(Oracle& o, const json::Value& v) {
   o.workers = (int)v.get_int("workers", 1);
+  o.indexed = v.get_bool("indexed", false);
   o.hardPodAffinityWeight = (int)v.get_int("hardPodAffinityWeight", 1);
   o.lastNodeIndex = (uint64_t)v.get_int("lastNodeIndex", 0);
   if (const json::Value* w = v.find("weights"); w && !w->is_null()) {

@@ -511,6 +511,87 @@ struct Oracle {
     return true;
   }
 
+  // ---------------- indexed mode (SURVEY.md §8c "two oracle modes")
+  // The literal functions above cost O(nodes x pods) per scheduled pod: every node rescans every pod. Indexed mode
+  // scans the pods once per Schedule and keeps, per affinity term, the set of topology values that hold a matching
+  // pod; a node then needs one label lookup per term. Same decisions by construction; any situation in which the
+  // literal code's answer depends on its scan order (a hard error: empty topology key, unparsable selector, a pod on
+  // an unknown node) switches that Schedule call back to the literal functions. tests/test_oracle_indexed.py
+  // checks that both modes give the same results on seeded instances.
+  bool indexed = false;
+  struct TermIndex {
+    bool exists = false;           // some pod matches the term's namespaces + selector
+    std::set<std::string> values;  // topology values (under the term's key) of the nodes holding such pods
+  };
+  struct IpaIndex {
+    bool usable = false;
+    std::map<std::string, std::set<std::string>> anti_by_key;  // existing pods' matching anti-affinity terms
+    std::vector<TermIndex> aff, anti;                         // the incoming pod's own required terms
+  };
+  static const std::string* topo_value(const Node& n, const std::string& key) {
+    if (key.empty() || !n.has_labels) return nullptr;
+    auto it = n.labels.find(key);
+    return it == n.labels.end() ? nullptr : &it->second;
+  }
+  IpaIndex build_ipa_index(const PredicateMeta& meta, const std::vector<PodPtr>& allPods, const std::vector<TermProbe>& affTerms,
+                           const std::vector<TermProbe>& antiTerms) const {
+    IpaIndex ix;
+    for (auto& t : meta.matchingAntiAffinityTerms) {
+      if (t.topology_key.empty()) return ix;  // the literal path raises an error at the first such term it meets
+      if (const std::string* v = topo_value(*t.node, t.topology_key)) ix.anti_by_key[t.topology_key].insert(*v);
+    }
+    auto index_terms = [&](const std::vector<TermProbe>& probes, std::vector<TermIndex>* out) {
+      for (auto& tp : probes) {
+        if (tp.term->topology_key.empty() || tp.sel_err) return false;
+        TermIndex ti;
+        for (auto& ep : allPods) {
+          if (!pod_matches_ns_and_selector(*ep, tp.nss, tp.sel)) continue;
+          ti.exists = true;
+          NodePtr en = get_node(ep->node_name);
+          if (!en) return false;
+          if (const std::string* v = topo_value(*en, tp.term->topology_key)) ti.values.insert(*v);
+        }
+        out->push_back(std::move(ti));
+      }
+      return true;
+    };
+    if (!index_terms(affTerms, &ix.aff) || !index_terms(antiTerms, &ix.anti)) return ix;
+    ix.usable = true;
+    return ix;
+  }
+  // inter_pod_affinity_matches over the index (never errors: the index is only usable when the literal path cannot)
+  void inter_pod_affinity_matches_indexed(const Pod& pod, const NodeInfo& ni, const IpaIndex& ix,
+                                          const std::vector<TermProbe>& affTerms, const std::vector<TermProbe>& antiTerms,
+                                          std::vector<std::string>* fails) const {
+    const Node& node = *ni.node;
+    auto in_domain = [&](const std::string& key, const std::set<std::string>& values) {
+      const std::string* v = topo_value(node, key);
+      return v && values.count(*v);
+    };
+    for (auto& kv : ix.anti_by_key)
+      if (in_domain(kv.first, kv.second)) {
+        fails->push_back("MatchInterPodAffinity");
+        fails->push_back("ExistingPodsAntiAffinityRulesNotMatch");
+        return;
+      }
+    if (!pod.affinity.present || (!pod.affinity.pod.present && !pod.affinity.anti.present)) return;
+    for (size_t i = 0; i < ix.aff.size(); ++i) {
+      const TermProbe& tp = affTerms[i];
+      if (in_domain(tp.term->topology_key, ix.aff[i].values)) continue;
+      if (ix.aff[i].exists || !pod_matches_ns_and_selector(pod, tp.nss, tp.sel)) {
+        fails->push_back("MatchInterPodAffinity");
+        fails->push_back("PodAffinityRulesNotMatch");
+        return;
+      }
+    }
+    for (size_t i = 0; i < ix.anti.size(); ++i)
+      if (in_domain(antiTerms[i].term->topology_key, ix.anti[i].values)) {
+        fails->push_back("MatchInterPodAffinity");
+        fails->push_back("PodAntiAffinityRulesNotMatch");
+        return;
+      }
+  }
+
   // ---------------- fork: device matching (core/extended_resources.go)
 
   // :152-167
@@ -723,6 +804,7 @@ struct Oracle {
     bool hasAff = pod.affinity.present && pod.affinity.pod.present;
     bool hasAnti = pod.affinity.present && pod.affinity.anti.present;
     std::map<std::string, double> counts;
+    std::map<std::string, std::map<std::string, double>> domains;  // indexed mode: weight per (topology key, value)
     bool failed = false;
     auto process_term = [&](const ksb::PodAffinityTerm& term, const Pod& defining, const Pod& toCheck,
                             const Node& fixedNode, double weight) {
@@ -734,9 +816,14 @@ struct Oracle {
         failed = true;
         return;
       }
-      if (pod_matches_ns_and_selector(toCheck, nss, sel))
-        for (auto& n : nodes)
-          if (nodes_have_same_topology_key(*n, fixedNode, term.topology_key)) counts[n->name] += weight;
+      if (pod_matches_ns_and_selector(toCheck, nss, sel)) {
+        if (indexed) {  // one entry per (topology key, value) instead of one pass over the nodes per matching term
+          if (const std::string* v = topo_value(fixedNode, term.topology_key)) domains[term.topology_key][*v] += weight;
+        } else {
+          for (auto& n : nodes)
+            if (nodes_have_same_topology_key(*n, fixedNode, term.topology_key)) counts[n->name] += weight;
+        }
+      }
     };
     auto process_terms = [&](const std::vector<ksb::WeightedPodAffinityTerm>& terms, const Pod& defining,
                              const Pod& toCheck, const Node& fixedNode, int mult) {
@@ -766,6 +853,13 @@ struct Oracle {
       }
     }
     if (failed) return false;
+    if (indexed)  // the weights are integers: their sum is exact in any order
+      for (auto& n : nodes)
+        for (auto& kv : domains)
+          if (const std::string* v = topo_value(*n, kv.first)) {
+            auto hit = kv.second.find(*v);
+            if (hit != kv.second.end()) counts[n->name] += hit->second;
+          }
     double maxCount = 0, minCount = 0;
     for (auto& n : nodes) {
       double c = counts.count(n->name) ? counts[n->name] : 0.0;
@@ -805,7 +899,7 @@ struct Oracle {
   // Returns false on a hard error.
   bool pod_fits_on_node(const Pod& pod, const PredicateMeta& meta, const NodeInfo& ni, const std::vector<PodPtr>& allPods,
                         const std::vector<TermProbe>& affTerms, const std::vector<TermProbe>& antiTerms,
-                        std::vector<std::string>* fails, std::string* err) const {
+                        std::vector<std::string>* fails, std::string* err, const IpaIndex* ix = nullptr) const {
     if (!ni.node) {
       *err = "node not found";
       return false;
@@ -830,7 +924,8 @@ struct Oracle {
     if (meta.bestEffort && ni.memoryPressure == "True") fails->push_back("NodeUnderMemoryPressure");
     if (ni.diskPressure == "True") fails->push_back("NodeUnderDiskPressure");
     check_node_condition(ni, fails);
-    if (!inter_pod_affinity_matches(pod, meta, ni, allPods, affTerms, antiTerms, fails, err)) return false;
+    if (ix && ix->usable) inter_pod_affinity_matches_indexed(pod, ni, *ix, affTerms, antiTerms, fails);
+    else if (!inter_pod_affinity_matches(pod, meta, ni, allPods, affTerms, antiTerms, fails, err)) return false;
     return true;
   }
 
@@ -875,6 +970,8 @@ struct Oracle {
       for (auto& t : required_terms(pod.affinity.pod)) affTerms.push_back(probe(pod, t));
       for (auto& t : required_terms(pod.affinity.anti)) antiTerms.push_back(probe(pod, t));
     }
+    IpaIndex ipaIndex;
+    if (indexed) ipaIndex = build_ipa_index(meta, allPods, affTerms, antiTerms);
     int N = (int)nodes.size();
     std::vector<char> fits(N, 0);
     std::vector<std::vector<std::string>> fails(N);
@@ -883,7 +980,7 @@ struct Oracle {
     parallelize(workers, N, [&](int i) {
       const NodeInfo& ni = cachedNodeInfoMap.at(nodes[i]->name);
       std::string err;
-      if (!pod_fits_on_node(pod, meta, ni, allPods, affTerms, antiTerms, &fails[i], &err)) {
+      if (!pod_fits_on_node(pod, meta, ni, allPods, affTerms, antiTerms, &fails[i], &err, indexed ? &ipaIndex : nullptr)) {
         has_err[i] = 1;
         errs[i] = err;
         return;
