@@ -10,12 +10,13 @@ from kubernetes_b200 import lib, workloads
 from tests import oracle_lib
 
 for spec in sys.argv[1:] or ["1", "2", "3"]:  # "cfg" (BASELINE.json size) or "cfg:nodes:pods"
-    parts = [int(x) for x in spec.split(":")]
+    indexed = spec.endswith("i")  # "5i": the oracle's indexed mode (inter-pod affinity without the O(nodes x pods) rescans)
+    parts = [int(x) for x in spec.rstrip("i").split(":")]
     cfg = parts[0]
     nodes, pods = parts[1:3] if len(parts) == 3 else workloads.CONFIG_SIZES[cfg]
     cluster = workloads.generate(cfg, nodes, pods)
     t0 = time.time()
-    want = oracle_lib.call({"op": "stream", "cluster": cluster, "workers": 16})
+    want = oracle_lib.call({"op": "stream", "cluster": cluster, "workers": 16, "indexed": indexed})
     t_oracle = time.time() - t0
     assert not want.get("error"), want.get("error")
     sess = lib.Session(cluster=cluster)
@@ -30,7 +31,7 @@ for spec in sys.argv[1:] or ["1", "2", "3"]:  # "cfg" (BASELINE.json size) or "c
             same = g["message"] == w["message"]
         if not same:
             bad.append(i)
-    print(json.dumps({"config": cfg, "nodes": nodes, "pods": pods, "compared": len(want["results"]),
+    print(json.dumps({"config": cfg, "oracle_mode": "indexed" if indexed else "literal", "nodes": nodes, "pods": pods, "compared": len(want["results"]),
                       "mismatches": len(bad), "first_mismatches": bad[:5],
                       "last_node_index_equal": got["lastNodeIndex"] == want["lastNodeIndex"],
                       "scheduled": got["scheduled"], "fit_errors": got["fit_errors"],
