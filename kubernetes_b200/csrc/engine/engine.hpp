@@ -240,6 +240,9 @@ class Engine {
   int grid = 0, threads = 0, max_grid = 0, group = 1, nseg = 0, zone_stride = 64;
   size_t smem_bytes = 0;
   bool pipe = false;  // the next launch overlaps commit and evaluation (prepare_geometry)
+  std::vector<char> one_pod_buf;
+  const char* one_pod_src = nullptr;  // one-pod call in flight: its staged header | dependency | pool block ...
+  size_t one_pod_bytes = 0;           // ... and size (0: the pod block was uploaded to its own buffers)
   bool batch_pipe_ok = true;  // the last encoded batch has few pods that depend on a very recent pod
   size_t limits_for_smem = (size_t)-1;  // shared-memory size the cached max_grid / threads were queried for
   PinnedBuf pin_chunk[2], pin_ctl, pin_out;  // pod blocks in (two chunks in flight); control block in; control block + results out

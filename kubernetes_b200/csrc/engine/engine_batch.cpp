@@ -18,9 +18,11 @@ namespace ksb {
   } while (0)
 
 namespace {
+constexpr size_t kPodSlotDep = (sizeof(KsbPodHeader) + 15) & ~(size_t)15;  // offsets inside the one-pod slot
+constexpr size_t kPodSlotPool = kPodSlotDep + 16;
 struct ScratchLayout {
   size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, seg_mask, barrier, error_flag, fiterr_count, last_index,
-      group_done, counters, ghist, release, xbar, xstate, peers, fiterr_hist, total;
+      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, total;
 };
 ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int halves = 1) {
   ScratchLayout L;
@@ -40,11 +42,14 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   L.last_index = take(8);
   L.group_done = take(32);
   L.counters = take(128);
+  L.res_slot = take(sizeof(KsbResult));  // one-pod calls: the result record, read back with the control words
   L.ghist = take(2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4);
   L.release = take(4);
   L.xbar = take(4);
   L.xstate = take(4);
   L.peers = take(sizeof(KsbPeer) * KSB_MAX_RANKS);
+  // one-pod calls: header, dependency index and pool words travel inside the control block's single upload
+  L.pod_slot = take(kPodSlotPool + (size_t)ksb_max_pool_words() * 8);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
   L.raw = take(halves * (size_t)G * n_pad * 16);
   L.score = take(halves * (size_t)G * n_pad * 4);
@@ -156,10 +161,12 @@ void Engine::launch(const KsbBatchArgs& a) {
     // the engine's own scratch on one GPU: every control field lies in one contiguous block at the start of the
     // buffer, so its initial image goes up in a single copy from page-locked memory
     ScratchLayout L = scratch_layout(ln_pad, a.zone_stride, std::max(1, a.nseg), a.group_size, a.pipeline ? 2 : 1);
-    const size_t bytes = L.fiterr_hist;
-    pin_ctl.ensure(bytes);
+    // the one-pod slot is the tail of the block: uploaded only when a one-pod call staged its pod there
+    const size_t bytes = L.pod_slot + (one_pod_bytes ? one_pod_bytes : 0);
+    pin_ctl.ensure(L.fiterr_hist);
     char* img = (char*)pin_ctl.p;
-    memset(img, 0, bytes);
+    memset(img, 0, L.pod_slot);
+    if (one_pod_bytes) memcpy(img + L.pod_slot, one_pod_src, one_pod_bytes);
     KsbNorms* nm = (KsbNorms*)(img + L.norms);
     for (int i = 0; i < 2 * KSB_MAX_GROUP; ++i) nm[i].one_row = -1;
     memcpy(img + L.last_index, &last_node_index, 8);
@@ -386,6 +393,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
 
   KsbBatchArgs a;
   size_t ctl_lo = 0, ctl_hi = 0, res_off = 0;
+  const bool one_call = np == 1 && !assume && cfg.shard_count <= 1;
   // upload staged chunk `which` (pods [c0, c1)) and launch the kernel on it; the stream is idle when this is called
   auto launch_chunk = [&](int c0, int c1, int which) {
     auto ts0 = std::chrono::steady_clock::now();
@@ -397,6 +405,35 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     batch_pipe_ok = recent_deps * 10 <= c1;
     sync_device();
     sync_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ts0).count();
+    char* src = (char*)pin_chunk[which].p;
+    if (one_call) {
+      // ksb_schedule: the pod's block rides in the control block's upload and its result record comes back with the
+      // control words, so the call costs one copy each way
+      a = make_args(len, assume);
+      ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
+      one_pod_buf.assign(kPodSlotPool + std::max<size_t>(1, st.pool_words) * 8, 0);
+      memcpy(one_pod_buf.data(), src, sizeof(KsbPodHeader));
+      memcpy(one_pod_buf.data() + kPodSlotDep, src + st.dep_off, 4);
+      memcpy(one_pod_buf.data() + kPodSlotPool, src + st.pool_off, std::max<size_t>(1, st.pool_words) * 8);
+      one_pod_src = one_pod_buf.data();
+      one_pod_bytes = one_pod_buf.size();
+      char* base = (char*)b_scratch.d;
+      a.headers = (const KsbPodHeader*)(base + L.pod_slot);
+      a.dep = (const int32_t*)(base + L.pod_slot + kPodSlotDep);
+      a.pool = (const uint64_t*)(base + L.pod_slot + kPodSlotPool);
+      a.results = (KsbResult*)(base + L.res_slot);
+      stats.h2d_bytes += one_pod_bytes;
+      last_index_before = last_node_index;
+      ctl_lo = (char*)a.barrier - base;
+      ctl_hi = (char*)a.results - base + sizeof(KsbResult);
+      res_off = (char*)a.results - (char*)a.barrier;
+      pin_out.ensure(ctl_hi - ctl_lo);
+      launch(a);
+      one_pod_bytes = 0;
+      CUDA_OK(cudaMemcpyAsync(pin_out.p, base + ctl_lo, ctl_hi - ctl_lo, cudaMemcpyDeviceToHost, stream));
+      return;
+    }
+    one_pod_bytes = 0;
     b_headers.ensure((size_t)np * sizeof(KsbPodHeader));  // whole-batch buffers: the replay entry points run them in one launch
     b_dep.ensure((size_t)np * 4);
     if (shard_connected && (size_t)np * sizeof(KsbResult) > b_results.cap)
@@ -408,7 +445,6 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
       b_pool.ensure(std::max<size_t>(1, guess) * 8);
     }
     grow_keep(b_pool, std::max<size_t>(1, st.pool_first + st.pool_words) * 8);
-    char* src = (char*)pin_chunk[which].p;
     CUDA_OK(cudaMemcpyAsync((KsbPodHeader*)b_headers.d + c0, src, st.hdr_bytes, cudaMemcpyHostToDevice, stream));
     CUDA_OK(cudaMemcpyAsync((int32_t*)b_dep.d + c0, src + st.dep_off, (size_t)len * 4, cudaMemcpyHostToDevice, stream));
     CUDA_OK(cudaMemcpyAsync((uint64_t*)b_pool.d + st.pool_first, src + st.pool_off, std::max<size_t>(1, st.pool_words) * 8,
@@ -443,7 +479,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     const int len = c1 - c0;
     CUDA_OK(cudaStreamSynchronize(stream));
     float ms = 0;
-    CUDA_OK(cudaEventElapsedTime(&ms, ev_start, ev_stop));
+    if (!one_call) CUDA_OK(cudaEventElapsedTime(&ms, ev_start, ev_stop));  // one-pod calls are not timed on the device
     kernel_ms += ms;
     char* back = (char*)pin_out.p;
     memcpy(last_results.data() + c0, back + res_off, (size_t)len * sizeof(KsbResult));
