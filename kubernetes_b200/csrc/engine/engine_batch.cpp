@@ -156,7 +156,19 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
 
 // Zero what must start at zero, seed the round-robin counter, launch. Works on whatever scratch the
 // arguments point at (the engine's own buffer or the static no-allocation array).
-void Engine::launch(const KsbBatchArgs& a) {
+void Engine::launch(const KsbBatchArgs& a_in) {
+  KsbBatchArgs a = a_in;
+  a.self.table = a.table;  // this GPU's shard as a peer entry, passed in the kernel's parameters
+  a.self.raw = a.raw;
+  a.self.score = a.score;
+  a.self.reasons = a.reasons;
+  a.self.seg_max = a.seg_max;
+  a.self.seg_cnt = a.seg_cnt;
+  a.self.seg_mask = a.seg_mask;
+  a.self.results = a.results;
+  a.self.last_node_index = a.last_node_index;
+  a.self.nseg = a.nseg;
+  a.self.seg_base = 0;
   if (a.n_ranks == 1 && b_scratch.d && (char*)a.norms == (char*)b_scratch.d) {
     // the engine's own scratch on one GPU: every control field lies in one contiguous block at the start of the
     // buffer, so its initial image goes up in a single copy from page-locked memory

@@ -930,13 +930,15 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
 
 // PIPE: the pipelined schedule (see `pipe` below) as a separate instantiation, so that the plain one carries none
 // of its state in registers.
-template <bool PIPE>
+template <bool PIPE, bool MULTI>
 __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const Smem S = carve(smem_raw, A.zone_stride);
   __shared__ int32_t s_gc;            // pods in the current group
   __shared__ int32_t s_consumed;      // pods of the group that were committed
   __shared__ KsbPeer s_peers[KSB_MAX_RANKS];  // rank 0, block 0: the shard table, read once
+  // one rank: the only shard is this GPU's own, described by the kernel parameters themselves
+#define PEER(x) (MULTI ? s_peers[(x)] : A.self)
   __shared__ volatile int32_t s_ready[kMaxG]; // decider -> writer: record g is complete
   __shared__ volatile int32_t s_stop;         // decider -> writer: pods decided in this group (-1: still deciding)
   __shared__ int32_t s_gmax0[kMaxG], s_k0[kMaxG];  // block 0: per pod, maximum score at group start and its holders
@@ -955,7 +957,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const int G = A.group_size;
   const size_t np = T.n_pad;
   uint32_t epoch = 0, xepoch = 0;
-  const bool multi = A.n_ranks > 1;
+  constexpr bool multi = MULTI;
   uint64_t last_index = *A.last_node_index;  // used by warp 0 of block 0 only
   int gi = 0;
   // Pipelined launches (A.pipeline, one rank): in iteration k block 0 commits the group evaluated in iteration k-1
@@ -983,7 +985,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   }
   int cm_gid = 0;    // block 0: sequence number of the group being committed (row-cache tags)
 
-  if (blockIdx.x == 0 && A.rank == 0) {
+  if (MULTI && blockIdx.x == 0 && A.rank == 0) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(A.peers);
     uint32_t* dst = reinterpret_cast<uint32_t*>(s_peers);
     for (int i = threadIdx.x; i < A.n_ranks * (int)(sizeof(KsbPeer) / 4); i += kThreads) dst[i] = src[i];
@@ -1286,7 +1288,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     if (committer && Gc > 0) {
       const int nsegT = A.nseg_total;
       const int sps = A.segs_per_shard;
-      const int R = A.n_ranks;
+      const int R = MULTI ? A.n_ranks : 1;
       // Segment statistics of every pod that will be ranked by score, one pod per warp: copy them to shared memory,
       // then the pod's maximum over all segments, the number of rows holding it (k0), the count array with
       // non-maximal segments zeroed, and its sums over blocks of 32 segments for the two-level rank-select
@@ -1300,7 +1302,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         int32_t m = INT32_MIN;
         for (int i = lane; i < nsegT; i += 32) {
           const int q = i / sps;
-          const KsbPeer& P = s_peers[q];
+          const KsbPeer& P = PEER(q);
           const int ls = i - q * sps;
           const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + ls);
           smax[i] = v;
@@ -1370,7 +1372,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         uint32_t nx_reasons = 0;
         int32_t nx_score = INT32_MIN;
         if (lane < ncr) {  // carried rows: the first pod's values
-          const KsbPeer& P = s_peers[S.rows[lane].pad & 0xff];
+          const KsbPeer& P = PEER(S.rows[lane].pad & 0xff);
           const size_t at = half * P.table.n_pad + S.rows[lane].row;
           nx_base = __ldcv(&P.raw[at].x);
           nx_reasons = __ldcv(P.reasons + at);
@@ -1403,7 +1405,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               RowCache& c = S.rows[lane];
               crow = c.row;
               crank = c.pad & 0xff;
-              const KsbPeer& P = s_peers[crank];
+              const KsbPeer& P = PEER(crank);
               cseg = P.seg_base + crow / kSeg;
               const int32_t base0 = nx_base;
               old_reasons = nx_reasons;
@@ -1427,7 +1429,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               if (fb) {
                 bool safe = true;
                 if (flip) {
-                  const KsbPeer& P = s_peers[crank];
+                  const KsbPeer& P = PEER(crank);
                   const int4 raw = __ldcv(P.raw + (half + g) * P.table.n_pad + crow);
                   const int32_t na = raw.y, tt = (int32_t)((uint32_t)raw.z >> 24), ipa = raw.w;
                   const uint32_t sc = (uint32_t)raw.z & 0xffffffu;
@@ -1476,7 +1478,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             } else if (nm.fit_count == 1) {
               // generic_scheduler.go:144-146: no selectHost, counter untouched
               chosen_rank = min(R - 1, (nm.one_row / kSeg) / sps);
-              chosen = nm.one_row - s_peers[chosen_rank].table.row_base;
+              chosen = nm.one_row - PEER(chosen_rank).table.row_base;
             } else {
               // (2) selectHost (generic_scheduler.go:177-192): lastNodeIndex % k over the rows tied at the maximum, in
               //     descending row order, from the group-start statistics patched with the changed rows
@@ -1492,7 +1494,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 const uint32_t cb = __ballot_sync(0xffffffffu, cand);
                 const int k = __popc(cb);
                 const int rem = (int)(last_index % (uint64_t)k);
-                const int grow = cand ? s_peers[crank].table.row_base + crow : -1;
+                const int grow = cand ? PEER(crank).table.row_base + crow : -1;
                 int above = 0;
                 for (uint32_t mm = cb; mm; mm &= mm - 1) {
                   const int gr = __shfl_sync(0xffffffffu, grow, __ffs(mm) - 1);
@@ -1519,7 +1521,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 if (found >= 0) {
                   // level 3: the row inside the segment, from its holder mask (phase 2) patched with the changed rows
                   pick_rank = min(R - 1, found / sps);
-                  const KsbPeer& P = s_peers[pick_rank];
+                  const KsbPeer& P = PEER(pick_rank);
                   const int base_row = (found - P.seg_base) * kSeg;
                   uint32_t word = 0;
                   if (lane < kWarps && smax[found] == gmax)
@@ -1584,7 +1586,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               prank = chosen_rank;
             }
             if (prow >= 0) {
-              const KsbPeer& P = s_peers[prank];
+              const KsbPeer& P = PEER(prank);
               const size_t at = (half + g + 1) * P.table.n_pad + prow;
               nx_base = __ldcv(&P.raw[at].x);
               nx_reasons = __ldcv(P.reasons + at);
@@ -1592,7 +1594,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             }
           }
           if (chosen >= 0) {
-            const KsbPeer& P = s_peers[chosen_rank];
+            const KsbPeer& P = PEER(chosen_rank);
             uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
             if (A.commit) {
               if (idx < 0) {
@@ -1657,7 +1659,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           __threadfence_block();
           s_stop = consumed;
         }
-        if (lane < R) *s_peers[lane].last_node_index = last_index;  // every rank's host reads its own copy
+        if (lane < R) *PEER(lane).last_node_index = last_index;  // every rank's host reads its own copy
       } else if (warp == 1) {
         // writer warp: table write-through, class counters and result records of every decided pod, in order
         bool table_open = false;
@@ -1671,7 +1673,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           __threadfence_block();
           const CommitRec& rec = S.recs[g];
           const KsbPodHeader* h = S.hdr + g;
-          if (lane < R) s_peers[lane].results[p0 + g] = rec.res;  // every rank keeps a copy of the results
+          if (lane < R) PEER(lane).results[p0 + g] = rec.res;  // every rank keeps a copy of the results
           if (rec.row >= 0) {
             if (pipe && !table_open) {
               // pipelined: the evaluation side is still reading the table until every block has passed barrier 1
@@ -1680,7 +1682,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               table_open = true;
             }
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
-            const KsbPeer& P = s_peers[rec.rank];
+            const KsbPeer& P = PEER(rec.rank);
             const int chosen = rec.row;
             write_through(P.table, rec, h, lane);
             if (R == 1 && counters_fast(h)) {
@@ -1699,7 +1701,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 const uint32_t off = (uint32_t)cm;
                 const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
                 for (int q = 0; q < R; ++q) {
-                  int32_t* tb = s_peers[q].table.tables;
+                  int32_t* tb = PEER(q).table.tables;
                   if (d) tb[off + d] = __ldcv(tb + off + d) + delta;
                   if ((cm >> 40) & 1ull) tb[off] = __ldcv(tb + off) + delta;
                 }
@@ -1796,6 +1798,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     }
   }
 #undef KSB_TICK
+#undef PEER
 #undef raw_s
 #undef score_s
 #undef reasons_s
@@ -1826,7 +1829,8 @@ extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
 
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
   void* params[] = {(void*)args};
-  const void* fn = args->pipeline ? (const void*)ksb_schedule_batch_kernel<true> : (const void*)ksb_schedule_batch_kernel<false>;
+  const void* fn = args->n_ranks > 1 ? (const void*)ksb_schedule_batch_kernel<false, true>
+                   : (args->pipeline ? (const void*)ksb_schedule_batch_kernel<true, false> : (const void*)ksb_schedule_batch_kernel<false, false>);
   cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,
                                               smem_bytes, stream);
   return (int)e;
@@ -1834,17 +1838,19 @@ extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_
 
 extern "C" int ksb_batch_kernel_limits(int device, size_t smem_bytes, int* max_grid, int* threads) {
   int per_sm = 0, sms = 0;
-  cudaError_t e = cudaFuncSetAttribute(ksb_schedule_batch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem_bytes);
-  if (e != cudaSuccess) return (int)e;
-  e = cudaFuncSetAttribute(ksb_schedule_batch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
-  if (e != cudaSuccess) return (int)e;
-  int per_sm_pipe = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ksb_schedule_batch_kernel<false>, kThreads, smem_bytes);
-  if (e != cudaSuccess) return (int)e;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_pipe, ksb_schedule_batch_kernel<true>, kThreads, smem_bytes);
-  if (e != cudaSuccess) return (int)e;
-  per_sm = per_sm < per_sm_pipe ? per_sm : per_sm_pipe;  // one grid size serves both instantiations
+  // the three instantiations (plain, pipelined, sharded) share one grid size: the smallest occupancy of the three
+  const void* fns[3] = {(const void*)ksb_schedule_batch_kernel<false, false>, (const void*)ksb_schedule_batch_kernel<true, false>,
+                        (const void*)ksb_schedule_batch_kernel<false, true>};
+  cudaError_t e = cudaSuccess;
+  per_sm = 1 << 30;
+  for (const void* fn : fns) {
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+    if (e != cudaSuccess) return (int)e;
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kThreads, smem_bytes);
+    if (e != cudaSuccess) return (int)e;
+    per_sm = occ < per_sm ? occ : per_sm;
+  }
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (e != cudaSuccess) return (int)e;
   *max_grid = per_sm * sms;

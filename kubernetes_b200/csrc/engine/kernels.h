@@ -61,6 +61,9 @@ struct KsbBatchArgs {
   int32_t n_ranks, rank;
   int32_t segs_per_shard;       // segments per shard (the last shard may hold fewer)
   int32_t nseg_total;           // segments over all shards
+  // this GPU's own shard in the form of a peer entry (filled at launch). With one rank phase 3 reads it from the
+  // kernel's parameter space instead of going through the peer table in shared memory.
+  KsbPeer self;
 };
 
 extern "C" {
