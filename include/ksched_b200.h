@@ -142,7 +142,8 @@ int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len);
 
 /* The NodeInfo aggregates the cache keeps for node `name` (schedulercache/node_info.go:35-78), as the JSON object
  * {"requested": {"cpu", "memory", "gpu", "ephemeral", "scalars": {name: n}}, "nonzero": {"cpu", "memory"}, "pods": n,
- * "usedPorts": ["proto/ip/port"], "available": {resource: [device ids]}}, or "null" when no NodeInfo exists under that
+ * "usedPorts": ["proto/ip/port"], "allocatable": {"cpu", "memory", "pods", "scalars": {name: n}},
+ * "available": {resource: [device ids]}}, or "null" when no NodeInfo exists under that
  * name (cache.go:283-293 drops it with its last pod when the Node object is gone). The device columns of the row are
  * read back and compared with the host records first; a difference is an error. *len receives the text length;
  * returns 1 if buf was too small. */

@@ -1006,7 +1006,26 @@ std::string Engine::node_info_json(const std::string& name) {
     out += std::string(first ? "" : ",") + esc(p);
     first = false;
   }
-  out += "],\"available\":{";
+  {  // allocatable as the row holds it; none once the Node object is gone
+    const bool live = hn.has_node && hn.row >= 0;
+    out += "],\"allocatable\":{\"cpu\":" + std::to_string(live ? i64(I64_ALLOC_CPU, hn.row) : 0) + ",\"memory\":" +
+           std::to_string(live ? i64(I64_ALLOC_MEM, hn.row) : 0) + ",\"pods\":" +
+           std::to_string(live ? (int64_t)u32(U32_ALLOC_PODS, hn.row) : 0) + ",\"scalars\":{";
+    first = true;
+    if (live) {
+      std::map<std::string, int64_t> named;
+      for (size_t k = 0; k < scalar_names.size() && k < KSB_MAX_SCALARS; ++k) {
+        const int64_t v = i64(I64_ALLOC_SCALAR + (int)k, hn.row);
+        if (v != 0 || hn.node.allocatable.count(scalar_names[k])) named[scalar_names[k]] = v;
+      }
+      for (auto& kv : named) {
+        out += std::string(first ? "" : ",") + esc(kv.first) + ":" + std::to_string(kv.second);
+        first = false;
+      }
+    }
+    out += "}}";
+  }
+  out += ",\"available\":{";
   first = true;
   for (auto& kv : hn.ext) {
     if (!kv.second.domain_present) continue;

@@ -387,7 +387,7 @@ char* ksbh_cache_ops(const char* request_json) {
       else if (what == "remove") err = c.RemovePod(pod_from_json(*op.find("pod")));
       else if (what == "cleanup") c.CleanupAssumedPods(op.get_num("now", 0.0));
       else if (what == "is_assumed") err = c.IsAssumedPod(pod_from_json(*op.find("pod"))) ? "assumed" : "not assumed";
-      else if (what == "add_node") c.AddNode(node_from_json(*op.find("node")));
+      else if (what == "add_node" || what == "update_node") c.AddNode(node_from_json(*op.find("node")));
       else if (what == "remove_node") {
         Node n;
         n.name = op.get_str("name");

@@ -258,7 +258,22 @@ static std::string node_info_json(const NodeInfo& ni) {
     first = false;
     json::escape_to(out, p);
   }
-  out += "],\"available\":{";
+  // allocatable as SetNode left it (node_info.go:469-491); RemoveNode empties it (:494-506)
+  {
+    const Resource none;
+    const Resource& al = ni.node ? ni.allocatable : none;
+    out += "],\"allocatable\":{\"cpu\":" + std::to_string(al.MilliCPU) + ",\"memory\":" + std::to_string(al.Memory) +
+           ",\"pods\":" + std::to_string(al.AllowedPodNumber) + ",\"scalars\":{";
+    first = true;
+    for (auto& kv : al.Scalar) {
+      if (!first) out += ",";
+      first = false;
+      json::escape_to(out, kv.first);
+      out += ":" + std::to_string(kv.second);
+    }
+    out += "}}";
+  }
+  out += ",\"available\":{";
   first = true;
   for (auto& kv : ni.ext.available) {
     if (!first) out += ",";
@@ -305,7 +320,7 @@ static std::string run_cache_ops(const json::Value& req) {
     else if (what == "remove") err = c.remove(ksb::pod_from_json(*op.find("pod")));
     else if (what == "cleanup") c.cleanup(op.get_num("now", 0.0));
     else if (what == "is_assumed") err = c.is_assumed(ksb::pod_from_json(*op.find("pod"))) ? "assumed" : "not assumed";
-    else if (what == "add_node") c.AddNode(ksb::node_from_json(*op.find("node")));
+    else if (what == "add_node" || what == "update_node") c.AddNode(ksb::node_from_json(*op.find("node")));
     else if (what == "remove_node") c.RemoveNode(op.get_str("name"));
     else err = "unknown op " + what;
     if (!first) errors += ",";

@@ -143,7 +143,8 @@ def builders(g):
 
         def info(cpu, mem, npods, ports):
             return {"requested": {"cpu": cpu, "memory": mem, "gpu": 0, "ephemeral": 0, "scalars": {}},
-                    "nonzero": {"cpu": cpu, "memory": mem}, "pods": npods, "usedPorts": ports, "available": {}}
+                    "nonzero": {"cpu": cpu, "memory": mem}, "pods": npods, "usedPorts": ports,
+                    "allocatable": {"cpu": 0, "memory": 0, "pods": 0, "scalars": {}}, "available": {}}
 
         def case(src, test, ops, nodes, ttl=10):
             CASES.append({"op": "cache_ops", "source": src, "test": test, "ttl": ttl, "ops": ops, "report": sorted(nodes),
@@ -231,6 +232,7 @@ def builders(g):
         def info(npods, avail1):
             return {"requested": {"cpu": 0, "memory": 0, "gpu": 0, "ephemeral": 0, "scalars": {}},
                     "nonzero": {"cpu": 100 * npods, "memory": mib200 * npods}, "pods": npods, "usedPorts": [],
+                    "allocatable": {"cpu": 0, "memory": 0, "pods": 0, "scalars": {}},
                     "available": {r2: sorted(ids), r1: sorted(avail1)}}
 
         for test, ops, expect in [("after adding 24 pods every nvidia.com/gpu device is used", adds, info(24, [])),
@@ -238,5 +240,33 @@ def builders(g):
             CASES.append({"op": "cache_ops", "source": src, "test": "TestAddAndRemovePodExtendedResources: " + test, "ttl": 30,
                           "ops": ops, "report": ["n"], "expect": {"errors": [""] * len(ops), "nodes": {"n": expect}}})
 
+    # ----------------------------------------------------------------- node add / update / remove
+    # schedulercache/cache_test.go:700-893 (TestNodeOperators). Quantities as the API reads them: memory "100m" and
+    # "50m" are fractions of a byte and round up to 1 (Quantity.Value()).
+    def build_node_operators():
+        src = "schedulercache/cache_test.go:700-893"
+        taint = [{"key": "test-key", "value": "test-value", "effect": "PreferNoSchedule"}]
+        mk_node = lambda mem: node("test-node", alloc={"cpu": 1000, "memory": mem, "example.com/foo": 1}, taints=taint)
+        with_port = pod("test-node", name="pod1", containers=[ctr(500, 1, ports=[{"hostPort": 80}])])
+        plain = lambda name: pod("test-node", name=name, containers=[ctr(500, 1)])
+
+        def info(npods, ports, alloc):
+            return {"requested": {"cpu": 500 * npods, "memory": npods, "gpu": 0, "ephemeral": 0, "scalars": {}},
+                    "nonzero": {"cpu": 500 * npods, "memory": npods}, "pods": npods, "usedPorts": ports,
+                    "allocatable": alloc, "available": {}}
+
+        full = {"cpu": 1000, "memory": 1, "pods": 0, "scalars": {"example.com/foo": 1}}
+        none = {"cpu": 0, "memory": 0, "pods": 0, "scalars": {}}
+        for label, pods_, ports in [("one pod with a host port", [with_port], ["TCP/0.0.0.0/80"]),
+                                    ("two pods", [plain("pod1"), plain("pod2")], [])]:
+            adds = [{"do": "add_node", "node": mk_node(1)}] + [{"do": "add", "pod": p} for p in pods_]
+            for step, ops, alloc in [("case 1: node and pods added", adds, full),
+                                     ("case 3: node updated", adds + [{"do": "update_node", "node": mk_node(1)}], full),
+                                     ("case 4: a removed node keeps its NodeInfo while pods remain",
+                                      adds + [{"do": "remove_node", "name": "test-node"}], none)]:
+                CASES.append({"op": "cache_ops", "source": src, "test": "TestNodeOperators (%s) %s" % (label, step), "ttl": 1,
+                              "ops": ops, "report": ["test-node"],
+                              "expect": {"errors": [""] * len(ops), "nodes": {"test-node": info(len(pods_), ports, alloc)}}})
+
     return [build_prefer_avoid, build_hard_affinity_weight, build_fits_host, build_pressure_and_conditions, build_assume_pod,
-            build_cache_ops, build_device_cache]
+            build_cache_ops, build_device_cache, build_node_operators]
