@@ -9,7 +9,7 @@
 //            fork's device matching (core/extended_resources.go:83-150) and the Map half of every
 //            priority, + grid-wide reductions of the Reduce inputs
 //   phase 2  PrioritizeNodes    core/generic_scheduler.go:509-640  -> final integer score per node,
-//            per 256-row segment (max, tie count)
+//            per 256-row segment (max, tie count, holder mask)
 //   phase 3  selectHost         core/generic_scheduler.go:177-192  -> round-robin pick among the
 //            max-score ties in descending name (= row) order, then the assume step (scheduler.go:478 ->
 //            schedulercache/node_info.go:329-356) on the chosen row.
@@ -19,24 +19,31 @@
 //      pod, the latest earlier pod that writes anything it reads (`dep`), and a group never contains
 //      both, so inside a group these inputs are constant;
 //  (b) the rows of nodes chosen earlier in the group: phase 3 re-evaluates exactly those rows against
-//      the current table. Binding only ever adds load, so a row can only turn from fit to unfit; if
-//      that happens for a row that was fit at group start, the Reduce inputs (maxima, zone sums, fit
-//      count) may have moved, the speculation is dropped and the group ends before that pod, which is
-//      then re-evaluated from scratch as the first pod of the next group. Otherwise every unchanged
-//      row keeps its group-start score, the changed rows get fresh ones, and the per-segment tie counts
-//      are patched before the rank-select.
+//      the current table. Binding only ever adds load, so a row can only turn from fit to unfit. A row
+//      that was fit at group start and no longer is leaves the candidate set if it cannot have held any
+//      Reduce input (maxima, zone sums, inter-pod extremes); otherwise, or when the maximum lost all its
+//      holders, the speculation is dropped and the group ends before that pod, which is then evaluated
+//      from scratch as the first pod of the next group. Every unchanged row keeps its group-start
+//      score, a changed row's score is its group-start score with the base part exchanged, and the tie
+//      counts are patched before the rank-select.
 // With group size 1 this degenerates to evaluating every pod against the live table.
 //
-// Phase 3 is a single warp: the changed rows' mutable columns live in a shared-memory row cache (filled
-// when a row is first chosen, updated by every later commit), so re-evaluating a pod on them costs no
-// memory round trip; the group's segment statistics are prefetched into shared memory; FitError
-// histograms are deferred to the end of the group and built by all warps.
+// Phase 3 is a decider warp and a writer warp: the changed rows' mutable columns live in a shared-memory
+// row cache (filled when a row is first chosen, updated by every later commit), so re-evaluating a pod
+// on them costs no memory round trip; all warps first bring the group's segment statistics into shared
+// memory and reduce them to a maximum, tie count and block sums per pod; the row inside a segment comes
+// from the segment's holder mask (phase 2); the writer warp takes the table write-through, the class
+// counters and the result records off the decider's chain; FitError histograms are built in phase 2.
+//
+// Three instantiations: plain; pipelined (one rank: block 0 commits group k-1 while the other blocks
+// evaluate group k, see `pipe` in the kernel); sharded (several GPUs, rows of other shards reached over
+// NVLink peer mappings).
 //
 // The work is integer/bit work over a structure-of-arrays node table: one thread per node, coalesced
-// 4/8-byte column loads (re-reads across the pods of a group hit L1), requirement blocks staged in
-// shared memory, reductions by warp shuffle (redux) + one atomic per block. No tensor cores: nothing
-// here is a dense contraction. float64 priorities use __d*_rn so no FMA is ever formed (Go on amd64
-// never fuses; the file is also compiled with -fmad=false).
+// 4/8-byte column loads with the common columns of a row kept in registers across the pods of a group,
+// requirement blocks staged in shared memory, reductions by warp shuffle (redux) + one atomic per
+// block. No tensor cores: nothing here is a dense contraction. float64 priorities use __d*_rn so no FMA
+// is ever formed (Go on amd64 never fuses; the file is also compiled with -fmad=false).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
