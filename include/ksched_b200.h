@@ -169,8 +169,9 @@ typedef struct ksb_stats {
   double last_batch_post_ms;   /* host time spent mirroring the last batch's placements into the host records */
   int32_t num_nodes;
   int32_t node_row_bytes;      /* bytes of node-table columns one (pod,node) evaluation may read */
-  /* SM cycles block 0 spent, last batch: staging, phase 1, barrier 1, phase 2, barrier 2, phase 3, barrier 3;
-   * then inside phase 3: prefetch, changed rows, select, commit, wait, deferred FitError histograms */
+  /* SM cycles block 0 spent in the last launch (after ksb_replay_last_batch: the replayed launch): staging, phase 1,
+   * barrier 1, phase 2, barrier 2, phase 3, barrier 3; then, only in a build with FINE_TIMING=1, inside phase 3:
+   * segment-statistics prologue, changed rows, select, commit, wait for the writer warp; the last entry is unused. */
   uint64_t stage_cycles[13];
 } ksb_stats;
 int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out);
