@@ -159,7 +159,7 @@ def main():
         sample_txt = "first %d pods of the stream on all %d nodes, %d worker threads (Parallelize(16))" % (sample, n_nodes, workers)
         json_out.write(json.dumps({
             "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": 0, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int64", "data": "synthetic",
             "config": {"workload": workload, "note": "reference is Go and no Go toolchain exists here: this is the C++ "
                        "restatement of its algorithm (oracle/), literal mode"},
@@ -240,7 +240,7 @@ def main():
     achieved = algo_bytes * n_nodes * n_pods / (step_ms / 1000.0) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak", "vs_baseline": None,
+        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "int64",
         "data": "synthetic",
         "config": {"workload": workload, "nodes": n_nodes, "pods": n_pods, "scheduled": scheduled, "fit_errors": fit_errors,
@@ -255,7 +255,7 @@ def main():
         # of each end-to-end pass plus one per resident replay
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic(args.config, n_nodes, n_pods), "peak_source": peak_src, "kernel": "ksb_schedule_batch_kernel",
+                     "traffic": ncu_traffic(args.config, n_nodes, n_pods) if world == 1 else None, "peak_source": peak_src, "kernel": "ksb_schedule_batch_kernel",
                      "algorithmic_bytes_per_eval": algo_bytes, "evals_per_launch": n_nodes * n_pods,
                      "kernel_ms_in_e2e": sum(kernel_ms) / len(kernel_ms)},
         "clocks": clocks,

@@ -1,5 +1,6 @@
 // extern "C" surface of include/ksched_b200.h over ksb::Engine.
 #include <chrono>
+#include <mutex>
 #include <thread>
 #include <cstring>
 #include <stdexcept>
@@ -12,6 +13,7 @@
 
 struct ksb_engine {
   ksb::Engine* impl;
+  std::mutex err_mu;  // mutators may fail on several threads at once (include/ksched_b200.h "Threading")
   std::string err;
 };
 
@@ -23,6 +25,7 @@ int32_t guarded(ksb_engine* e, F&& f) {
     f();
     return 0;
   } catch (const std::exception& ex) {
+    std::lock_guard<std::mutex> g(e->err_mu);
     e->err = ex.what();
     return -1;
   }
@@ -69,7 +72,15 @@ void ksb_destroy(ksb_engine* e) {
   delete e;
 }
 
-const char* ksb_last_error(const ksb_engine* e) { return e ? e->err.c_str() : "null engine"; }
+const char* ksb_last_error(const ksb_engine* e) {
+  if (!e) return "null engine";
+  // a per-thread copy: the engine's text may be replaced by a failing call on another thread
+  static thread_local std::string mine;
+  ksb_engine* m = const_cast<ksb_engine*>(e);
+  std::lock_guard<std::mutex> g(m->err_mu);
+  mine = m->err;
+  return mine.c_str();
+}
 
 int32_t ksb_node_upsert(ksb_engine* e, const uint8_t* buf, size_t len) {
   return guarded(e, [&] {

@@ -417,6 +417,7 @@ static void reslist_to_aggregates(const ResourceList& rl, int64_t* cpu, int64_t*
 
 void Engine::node_upsert(const Node& nd) {
   std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;  // the replay entry points are only valid right after the batch
   HostNode& hn = nodes[nd.name];
   bool was_listed = hn.has_node;
   hn.node = nd;
@@ -472,6 +473,7 @@ void Engine::node_upsert(const Node& nd) {
 
 void Engine::node_remove(const std::string& name) {
   std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;  // the replay entry points are only valid right after the batch
   auto it = nodes.find(name);
   if (it == nodes.end()) return;
   it->second.has_node = false;  // cache.go:373-387: the NodeInfo survives while it still holds pods
@@ -481,6 +483,7 @@ void Engine::node_remove(const std::string& name) {
 
 void Engine::owner_upsert(int kind, const SelectorOwner& o) {
   std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;  // the replay entry points are only valid right after the batch
   if (kind < 0 || kind > 3) throw std::runtime_error("selector owner kind out of range");
   bool found = false;
   for (auto& x : owners[kind])
@@ -494,6 +497,7 @@ void Engine::owner_upsert(int kind, const SelectorOwner& o) {
 
 void Engine::owner_remove(int kind, const std::string& ns, const std::string& name) {
   std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;  // the replay entry points are only valid right after the batch
   if (kind < 0 || kind > 3) return;
   auto& v = owners[kind];
   v.erase(std::remove_if(v.begin(), v.end(), [&](const SelectorOwner& x) { return x.ns == ns && x.name == name; }),
@@ -745,6 +749,7 @@ void Engine::fill_row(int row) {
 
 // Rebuild every column from the host records (node set changed).
 void Engine::rebuild_layout() {
+  have_snapshot = false;  // rows move: a table snapshot taken before no longer lines up
   rows.clear();
   for (auto& kv : nodes) {
     kv.second.row = -1;

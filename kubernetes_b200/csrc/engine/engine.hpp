@@ -273,6 +273,8 @@ class Engine {
   void setup_table_pointers();
   KsbBatchArgs make_args(int n_pods, bool commit);
   void launch(const KsbBatchArgs& a);
+  std::vector<KsbNorms> launch_norms;  // host staging of launch(): per engine, the copies are issued under `mu`
+  KsbPeer launch_self{};
 
   // ---- encoder
   void register_pod_classes(const Pod& p);

@@ -4,6 +4,7 @@
 #include <chrono>
 #include <cstring>
 #include <stdexcept>
+#include <unordered_set>
 
 #include "engine.hpp"
 
@@ -200,11 +201,15 @@ void Engine::launch(const KsbBatchArgs& a_in) {
     stats.kernel_launches += 1;
     return;
   }
-  static KsbNorms init[2 * KSB_MAX_GROUP];
-  memset(init, 0, sizeof init);
-  for (auto& x : init) x.one_row = -1;
+  // host staging of this launch lives in the engine (launch_norms, launch_self), never in function statics:
+  // several engines of one process may launch from different threads
+  launch_norms.assign(2 * KSB_MAX_GROUP, KsbNorms());
+  for (auto& x : launch_norms) {
+    memset(&x, 0, sizeof x);
+    x.one_row = -1;
+  }
   if (a.n_ranks == 1) {  // sharded: rank 0's kernel clears these itself, behind the opening barrier
-    CUDA_OK(cudaMemcpyAsync(a.norms, init, sizeof init, cudaMemcpyHostToDevice, stream));
+    CUDA_OK(cudaMemcpyAsync(a.norms, launch_norms.data(), launch_norms.size() * sizeof(KsbNorms), cudaMemcpyHostToDevice, stream));
     CUDA_OK(cudaMemsetAsync(a.zone_sum, 0, 2 * (size_t)KSB_MAX_GROUP * a.zone_stride * 4, stream));
     CUDA_OK(cudaMemsetAsync(a.ghist, 0, 2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4, stream));
     CUDA_OK(cudaMemsetAsync(a.group_done, 0, 32, stream));
@@ -215,7 +220,7 @@ void Engine::launch(const KsbBatchArgs& a_in) {
   CUDA_OK(cudaMemsetAsync(a.counters, 0, 128, stream));
   CUDA_OK(cudaMemcpyAsync(a.last_node_index, &last_node_index, 8, cudaMemcpyHostToDevice, stream));
   CUDA_OK(cudaMemsetAsync(a.release, 0, 4, stream));
-  static KsbPeer self;  // what rank 0 sees of this (only) shard: its own buffers
+  KsbPeer& self = launch_self;  // what rank 0 sees of this (only) shard: its own buffers
   if (a.n_ranks == 1) {
     CUDA_OK(cudaMemsetAsync(a.xbar, 0, 4, stream));
     CUDA_OK(cudaMemsetAsync(a.xstate, 0, 4, stream));
@@ -327,6 +332,15 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   for (auto& p : batch)
     if (p.num_volumes > 0)  // volume predicates are out of scope: refuse loudly, never guess, before anything is placed
       throw std::runtime_error("pod " + p.key() + " has volumes: not supported by the GPU engine");
+  if (assume) {
+    // ksb_schedule_batch == n x {ksb_schedule; ksb_pod_add}: a key that is already cached, or repeated inside the
+    // batch, is the error ksb_pod_add reports (cache.go:127-129); refuse before anything is placed
+    std::unordered_set<std::string> seen;
+    for (auto& p : batch) {
+      const std::string k = p.key();
+      if (pods.count(k) || !seen.insert(k).second) throw std::runtime_error("pod " + k + " is already in the cache");
+    }
+  }
   // pass 1: classes (every pod of the batch, so that commit lists name every class a later pod introduces)
   for (auto& p : batch) register_pod_classes(p);
   layout_arena();
@@ -569,16 +583,26 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   bounds(0, &c0, &c1);
   encode_chunk(c0, c1, 0);
   launch_chunk(c0, c1, 0);
-  for (int c = 0; c < n_chunks; ++c) {
-    bounds(c, &c0, &c1);
-    const bool more = c + 1 < n_chunks;
-    if (more) {
-      bounds(c + 1, &n0, &n1);
-      encode_chunk(n0, n1, (c + 1) & 1);  // next to the kernel of chunk c
+  try {
+    for (int c = 0; c < n_chunks; ++c) {
+      bounds(c, &c0, &c1);
+      const bool more = c + 1 < n_chunks;
+      if (more) {
+        bounds(c + 1, &n0, &n1);
+        encode_chunk(n0, n1, (c + 1) & 1);  // next to the kernel of chunk c
+      }
+      wait_chunk(c0, c1);
+      if (more) launch_chunk(n0, n1, (c + 1) & 1);
+      post_chunk(c0, c1);  // next to the kernel of chunk c+1
     }
-    wait_chunk(c0, c1);
-    if (more) launch_chunk(n0, n1, (c + 1) & 1);
-    post_chunk(c0, c1);  // next to the kernel of chunk c+1
+  } catch (...) {
+    // A limit met while encoding a later chunk (label universe, expression or pool caps) or a device error: a kernel
+    // may be in flight and the device table may hold commits the host records do not. Drain the stream and have the
+    // table rebuilt from the host records, which hold exactly the chunks posted so far (reported in `out`).
+    cudaStreamSynchronize(stream);
+    layout_dirty = true;
+    have_snapshot = false;
+    throw;
   }
   if (n_chunks > 1) {
     // the replay entry points run the whole batch in one launch: dependency indices relative to the batch
@@ -875,6 +899,7 @@ std::string Engine::fit_error_message(int i) {
 // Cache.AssumePod / AddPod outside a batch.
 void Engine::pod_add(const Pod& p) {
   std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;
   if (pods.count(p.key())) throw std::runtime_error("pod " + p.key() + " is already in the cache");  // cache.go:127-129
   HostNode& hn = nodes[p.node_name];
   if (layout_dirty || !hn.has_node || hn.row < 0) {
@@ -929,6 +954,7 @@ void Engine::pod_add(const Pod& p) {
 // storage is never given back), so the row is recomputed from the host record and re-uploaded.
 void Engine::pod_remove(const std::string& ns, const std::string& name) {
   std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;
   auto it = pods.find(ns + "/" + name);
   if (it == pods.end()) throw std::runtime_error("pod " + ns + "/" + name + " is not in the cache");
   Pod p = it->second.pod;

@@ -1830,7 +1830,7 @@ __global__ void ksb_apply_kernel(KsbNodeTable T, const KsbPodHeader* header, con
 }
 
 extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
-  size_t o[12];
+  size_t o[13];
   return smem_layout(o, zone_stride);
 }
 

@@ -207,18 +207,27 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
     std::vector<ksb_result> again(np);
     h.check(ksb_replay_last_batch(h.get(), replay_iters, &replay_ms, again.data()), "replay");
     for (size_t i = 0; i < np; ++i)
-      if (again[i].status != results[i].status || again[i].node_index != results[i].node_index)
+      if (again[i].status != results[i].status || again[i].node_index != results[i].node_index ||
+          again[i].num_filtered != results[i].num_filtered || again[i].score != results[i].score ||
+          memcmp(again[i].device_mask, results[i].device_mask, sizeof again[i].device_mask) != 0)
         throw std::runtime_error("replay diverged from the first run at pod " + std::to_string(i));
   }
   ksb_stats st;
   ksb_get_stats(h.get(), &st);
 
-  uint64_t hash = 1469598103934665603ull;
+  uint64_t hash = 1469598103934665603ull, rhash = 1469598103934665603ull;
   size_t scheduled = 0, fit_errors = 0, errors = 0;
   for (size_t i = 0; i < np; ++i) {
     int32_t v[2] = {results[i].status, results[i].node_index};
     hash = fnv1a(hash, v, sizeof v);
     hash = fnv1a(hash, results[i].device_mask, sizeof results[i].device_mask);
+    // result_hash: everything Schedule returns per pod (the placement plus filtered count, total score and, below,
+    // the FitError text)
+    rhash = fnv1a(rhash, v, sizeof v);
+    rhash = fnv1a(rhash, results[i].device_mask, sizeof results[i].device_mask);
+    int64_t w[2] = {(int64_t)results[i].num_filtered, results[i].score};
+    rhash = fnv1a(rhash, w, sizeof w);
+    if (want_results && !messages[i].empty()) rhash = fnv1a(rhash, messages[i].data(), messages[i].size());
     if (results[i].status == KSB_SCHEDULED) scheduled++;
     else if (results[i].status == KSB_FIT_ERROR) fit_errors++;
     else errors++;
@@ -230,6 +239,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   out += ",\"fit_errors\":" + std::to_string(fit_errors);
   out += ",\"errors\":" + std::to_string(errors);
   out += ",\"placement_hash\":\"" + std::to_string(hash) + "\"";
+  out += ",\"result_hash\":\"" + std::to_string(rhash) + "\"";
   out += ",\"load_ms\":" + std::to_string(load_ms);
   out += ",\"e2e_ms\":" + std::to_string(std::chrono::duration<double, std::milli>(t1 - t0).count());
   out += ",\"kernel_ms\":" + std::to_string(kernel_ms);
