@@ -86,7 +86,7 @@ Engine::~Engine() {
   cudaSetDevice(cfg.device);
   for (void* m : ipc_mappings) cudaIpcCloseMemHandle(m);
   for (DevBuf* b : {&b_i64, &b_u32, &b_u64, &b_dev_class, &b_topo, &b_spread, &b_tables, &b_headers, &b_pool,
-                    &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush, &b_dep})
+                    &b_results, &b_scratch, &b_snapshot, &b_one_header, &b_one_pool, &b_flush, &b_dep, &b_fiterr})
     b->release();
   pin_chunk[0].release();
   pin_chunk[1].release();

@@ -235,7 +235,7 @@ class Engine {
   cudaStream_t stream = nullptr;
   KsbNodeTable dT{};
   DevBuf b_i64, b_u32, b_u64, b_dev_class, b_topo, b_spread, b_tables, b_headers, b_pool, b_results, b_scratch,
-      b_snapshot, b_one_header, b_one_pool, b_flush, b_dep;
+      b_snapshot, b_one_header, b_one_pool, b_flush, b_dep, b_fiterr;
   size_t spread_cap_cols = 0;
   int grid = 0, threads = 0, max_grid = 0, group = 1, nseg = 0, zone_stride = 64;
   size_t smem_bytes = 0;

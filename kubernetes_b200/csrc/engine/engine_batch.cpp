@@ -128,7 +128,14 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.barrier = (uint32_t*)(base + L.barrier);
   a.error_flag = (int32_t*)(base + L.error_flag);
   a.fiterr_count = (int32_t*)(base + L.fiterr_count);
-  a.fiterr_hist = (int32_t*)(base + L.fiterr_hist);
+  // reason histograms: one per pod of the launch, so that no FitError of a large single launch loses its text
+  a.fiterr_cap = std::max(n_pods, (int)KSB_MAX_FITERR);
+  if (a.fiterr_cap > (int)KSB_MAX_FITERR) {
+    b_fiterr.ensure((size_t)a.fiterr_cap * KSB_REASON_BITS * 4);
+    a.fiterr_hist = (int32_t*)b_fiterr.d;
+  } else {
+    a.fiterr_hist = (int32_t*)(base + L.fiterr_hist);
+  }
   a.last_node_index = (uint64_t*)(base + L.last_index);
   a.group_done = (int32_t*)(base + L.group_done);
   a.counters = (uint64_t*)(base + L.counters);
@@ -526,7 +533,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     }
     // reason histograms of the chunk's no-fit pods, appended to the batch's; slots are renumbered accordingly
     const int base = (int)(last_fiterr_hist.size() / KSB_REASON_BITS);
-    const int nfe = std::min(flags[1], (int32_t)KSB_MAX_FITERR);
+    const int nfe = std::min(flags[1], a.fiterr_cap);
     if (nfe > 0) {
       last_fiterr_hist.resize((size_t)(base + nfe) * KSB_REASON_BITS);
       CUDA_OK(cudaMemcpy(last_fiterr_hist.data() + (size_t)base * KSB_REASON_BITS, a.fiterr_hist, (size_t)nfe * KSB_REASON_BITS * 4,

@@ -66,6 +66,8 @@ constexpr int kMaxG = KSB_MAX_GROUP;  // pods per group
 constexpr int kMaxPoolWords = 1024;   // pool words one pod may use (checked on the host)
 constexpr int kGroupPoolWords = 4096; // pool words staged per group
 constexpr int kSegCache = KSB_SEG_CACHE;  // (pods in group) x (segments) entries of segment stats kept in shared memory
+constexpr int kCache = 32;            // row-cache entries (one lane each)
+constexpr int kDeciders = kWarps - 1; // phase 3: warps that decide; the last warp writes the table through
 
 template <bool CG, typename V>
 __device__ __forceinline__ V ldx(const V* p) {
@@ -617,7 +619,9 @@ constexpr uint32_t kDynMask = 0x1ffu | (1u << RB_PORTS) | (0xfu << RB_EXT0) | (1
 
 // select_devices on a row-cache entry: the per-device class test is taken from the entry when an earlier pod of the
 // group with the same interned class mask already ran it on this row. Same results as select_devices.
-__device__ __forceinline__ uint32_t select_devices_cached(const KsbNodeTable& T, RowCache* c, const PodView& pv, uint32_t* picks) {
+// `keep` false: the entry is read by several lanes at once (one pod per lane), so nothing is written back to it.
+__device__ __forceinline__ uint32_t select_devices_cached(const KsbNodeTable& T, RowCache* c, const PodView& pv, uint32_t* picks,
+                                                          bool keep = true) {
   const KsbPodHeader* h = pv.h;
   uint32_t avail[KSB_MAX_RES];
 #pragma unroll
@@ -635,8 +639,10 @@ __device__ __forceinline__ uint32_t select_devices_cached(const KsbNodeTable& T,
         match = c->mm[i];
       } else {
         match = device_match_mask(T, c->row, rs, pv.extcls + i * KSB_CLASS_WORDS);
-        c->mm[i] = match;
-        c->mid[i] = id;
+        if (keep) {
+          c->mm[i] = match;
+          c->mid[i] = id;
+        }
       }
       const uint32_t m = avail[rs] & match;
       if (__popc(m) < num) return 1u << (RB_EXT0 + i);
@@ -656,7 +662,7 @@ __device__ __forceinline__ uint32_t select_devices_cached(const KsbNodeTable& T,
 // Must stay in step with eval_node (the group-size tests compare the two paths bit for bit).
 __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, const PodView& pv,
                                             uint32_t static_reasons, uint32_t* reasons_out, int32_t* base_out,
-                                            uint32_t* picks, bool want_score) {
+                                            uint32_t* picks, bool want_score, bool keep = true) {
   const KsbPodHeader* h = pv.h;
   const uint32_t pf = h->flags;
   uint32_t reasons = static_reasons;
@@ -684,7 +690,7 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   }
   if (reasons == 0 && h->n_ext) {
     uint32_t local[KSB_MAX_EXT];
-    reasons |= select_devices_cached(T, &c, pv, picks ? picks : local);
+    reasons |= select_devices_cached(T, &c, pv, picks ? picks : local, keep);
   }
   *reasons_out = reasons;
   *base_out = 0;
@@ -724,46 +730,6 @@ __device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCach
   if (lane >= 24 && lane < 24 + KSB_MAX_EXT) c->mid[lane - 24] = 0;
 }
 
-// The class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
-// of the same group reads them, so they live in global memory only. Split in two so the loads can be in
-// flight together with the row-cache fill.
-struct CounterLoads {
-  uint32_t spread_v;
-  int32_t tab_v, tot_v;
-  uint32_t tab_d;
-};
-__device__ __forceinline__ bool counters_fast(const KsbPodHeader* h) { return h->n_spread_inc <= 32 && h->n_commit <= 32; }
-__device__ __forceinline__ CounterLoads counters_load(const KsbNodeTable& T, int r, const PodView& pv, int lane) {
-  const KsbPodHeader* h = pv.h;
-  const size_t np = T.n_pad;
-  CounterLoads L;
-  L.spread_v = 0;
-  L.tab_v = 0;
-  L.tot_v = 0;
-  L.tab_d = 0;
-  if (lane < h->n_spread_inc) L.spread_v = __ldcg(T.spread + (size_t)pv.spread_inc[lane] * np + r);
-  if (lane < h->n_commit) {
-    const uint64_t cm = pv.commits[2 * lane];
-    const uint32_t off = (uint32_t)cm;
-    L.tab_d = T.topo[((uint32_t)(cm >> 32) & 0xffu) * np + r];
-    if (L.tab_d) L.tab_v = __ldcg(T.tables + off + L.tab_d);
-    if ((cm >> 40) & 1ull) L.tot_v = __ldcg(T.tables + off);
-  }
-  return L;
-}
-__device__ __forceinline__ void counters_store(const KsbNodeTable& T, int r, const PodView& pv, const CounterLoads& L,
-                                               int lane) {
-  const KsbPodHeader* h = pv.h;
-  const size_t np = T.n_pad;
-  if (lane < h->n_spread_inc) T.spread[(size_t)pv.spread_inc[lane] * np + r] = L.spread_v + 1u;
-  if (lane < h->n_commit) {
-    const uint64_t cm = pv.commits[2 * lane];
-    const int32_t delta = (int32_t)(int64_t)pv.commits[2 * lane + 1];
-    const uint32_t off = (uint32_t)cm;
-    if (L.tab_d) T.tables[off + L.tab_d] = L.tab_v + delta;
-    if ((cm >> 40) & 1ull) T.tables[off] = L.tot_v + delta;  // slot 0: matching pods anywhere
-  }
-}
 // What the decider warp hands to the writer warp for one pod: the chosen row's mutable columns after the
 // assume step (a copy of the row-cache entry) and the result record.
 struct CommitRec {
@@ -846,27 +812,40 @@ __device__ __forceinline__ int nth_set_from_top(uint32_t w, int n) {
   return 31 - p;
 }
 
-// One warp: cnt[lo..hi) holds non-negative counts; walking the entries from hi-1 down to lo, find the entry in
-// which the rem-th item (0-based) lies. Returns its index and leaves in `rem` the item's rank inside that entry;
-// -1 if the counts hold fewer than rem+1 items.
-__device__ __forceinline__ int desc_select(const int32_t* cnt, int lo, int hi, int& rem, int lane) {
-  for (int top = hi; top > lo; top -= 32) {
-    const int i = top - 1 - lane;  // lane 0 = highest entry
-    const int c = i >= lo ? cnt[i] : 0;
-    int incl = c;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += t;
+// Rank-select helpers of phase 3, written for one THREAD so that a warp can run one pod per lane.
+//
+// Pod g's candidates for selectHost are the rows that held its maximum score when the group started (the
+// "snapshot holders": per 256-row segment a count and a 256-bit mask from phase 2, reduced here to suffix counts
+// `cum`), minus the changed rows that stopped being holders (D), plus the changed rows that became holders (A).
+// Changed rows live in the row cache; r0[i] is the number of snapshot holders strictly above the row of cache
+// entry i (rows are name-ordered, selectHost walks them in descending order, api/types.go:218-223).
+
+// The rem-th candidate (0-based) in descending row order. Returns the cache entry if it is an added row, else -1
+// with *q = its rank among the snapshot holders (deleted ones included in the count).
+__device__ __forceinline__ int select_merged(uint32_t A, uint32_t D, int rem, const int32_t* r0, const int32_t* erow, int* q) {
+  uint32_t m = A | D;
+  int adds = 0, dels = 0;
+  while (m) {
+    int best = -1, brow = -1;
+    for (uint32_t t = m; t; t &= t - 1) {  // the remaining patch with the largest row
+      const int b = __ffs(t) - 1;
+      const int r = erow[b];
+      if (r > brow) {
+        brow = r;
+        best = b;
+      }
     }
-    const uint32_t hit = __ballot_sync(0xffffffffu, rem >= incl - c && rem < incl);
-    if (hit) {
-      const int src = __ffs(hit) - 1;
-      rem -= __shfl_sync(0xffffffffu, incl - c, src);
-      return top - 1 - src;
+    m &= ~(1u << best);
+    const int before = r0[best] - dels + adds;  // candidates above this patch's position
+    if (rem < before) break;                    // the answer is a snapshot holder above it
+    if ((A >> best) & 1u) {
+      if (rem == before) return best;
+      adds += 1;
+    } else {
+      dels += 1;
     }
-    rem -= __shfl_sync(0xffffffffu, incl, 31);
   }
+  *q = rem - adds + dels;
   return -1;
 }
 
@@ -875,18 +854,20 @@ struct Smem {
   KsbPodHeader* hdr;   // [kMaxG]
   uint64_t* pool;      // [kGroupPoolWords]
   int32_t* pool_off;   // [kMaxG] offset of pod g's pool inside `pool`
-  int32_t* zone;       // [kMaxG][zone_stride] phase 1: block-local sums; phase 2/3: global sums
+  int32_t* zone;       // [kMaxG][zone_stride] phase 1: block-local sums; phase 2: global sums; phase 3: t_r0
   int32_t* part;       // [kMaxG][kWarps][8] per-warp partials of the Reduce inputs
   KsbNorms* norm;      // [kMaxG]
   int32_t* max_zone;   // [kMaxG]
   int32_t* wstat;      // [kMaxG][kWarps][3] per-warp (max, count, holder mask) of one segment
-  int32_t* seg_max;    // [kSegCache] block 0: [pod][segment]
-  int32_t* seg_cnt;    // [kSegCache]
-  RowCache* rows;      // [kMaxG] block 0: rows changed in this group
+  int32_t* cum;        // [kSegCache] block 0: [pod][segment] snapshot holders in segments >= this one
+  RowCache* rows;      // [kCache] block 0: rows changed since the snapshot the group was evaluated on
+  RowCache* post;      // [kMaxG] block 0: the window's chosen rows after their pod's assume step, not yet final
   int32_t* fe_hist;    // [KSB_REASON_BITS] block 0: FitError histogram correction for changed rows
-  int32_t* bsum;       // block 0: [pod][32-segment block] holders of the pod's maximum, per block of segments
-  CommitRec* recs;     // [kMaxG] block 0: decider -> writer hand-off
+  int32_t* r0;         // [kMaxG][kCache] block 0: snapshot holders of pod g above the row of cache entry i
+  int32_t* t_r0;       // [kMaxG][kMaxG] block 0: the same for the window's rows (aliases `zone`)
+  CommitRec* recs;     // [kMaxG] block 0: decider -> writer hand-off (aliases part + wstat)
 };
+constexpr int kSmemParts = 13;
 
 __device__ __host__ __forceinline__ size_t smem_layout(size_t* offs, int zone_stride) {
   size_t off = 0;
@@ -898,22 +879,22 @@ __device__ __host__ __forceinline__ size_t smem_layout(size_t* offs, int zone_st
   take(sizeof(KsbPodHeader) * kMaxG);
   take((size_t)kGroupPoolWords * 8);
   take(kMaxG * 4);
-  take((size_t)kMaxG * zone_stride * 4);
+  take((size_t)kMaxG * zone_stride * 4);  // zone; phase 3 reuses it as t_r0 (zone_stride >= 64 > kMaxG)
   take((size_t)kMaxG * kWarps * 8 * 4);   // part: phase 1/2 reduction scratch ...
   take((size_t)kMaxG * kWarps * 3 * 4);   // wstat: ... contiguous with part; phase 3 reuses both as S.recs
   take(sizeof(KsbNorms) * kMaxG);
   take(kMaxG * 4);
   take((size_t)kSegCache * 4);
-  take((size_t)kSegCache * 4);
+  take(sizeof(RowCache) * kCache);
   take(sizeof(RowCache) * kMaxG);
-  take((size_t)kMaxG * KSB_REASON_BITS * 4);
-  take((size_t)(kSegCache / 32 + kMaxG) * 4);  // bsum
+  take((size_t)KSB_REASON_BITS * 4);
+  take((size_t)kMaxG * kCache * 4);
   static_assert(sizeof(CommitRec) * kMaxG <= (size_t)kMaxG * kWarps * 11 * 4, "commit records alias part + wstat");
   return off;
 }
 
 __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
-  size_t o[13];
+  size_t o[kSmemParts];
   smem_layout(o, zone_stride);
   Smem s;
   s.hdr = (KsbPodHeader*)(base + o[0]);
@@ -924,11 +905,12 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
   s.wstat = (int32_t*)(base + o[5]);
   s.norm = (KsbNorms*)(base + o[6]);
   s.max_zone = (int32_t*)(base + o[7]);
-  s.seg_max = (int32_t*)(base + o[8]);
-  s.seg_cnt = (int32_t*)(base + o[9]);
-  s.rows = (RowCache*)(base + o[10]);
+  s.cum = (int32_t*)(base + o[8]);
+  s.rows = (RowCache*)(base + o[9]);
+  s.post = (RowCache*)(base + o[10]);
   s.fe_hist = (int32_t*)(base + o[11]);
-  s.bsum = (int32_t*)(base + o[12]);
+  s.r0 = (int32_t*)(base + o[12]);
+  s.t_r0 = (int32_t*)(base + o[3]);
   s.recs = (CommitRec*)(base + o[4]);
   return s;
 }
@@ -946,10 +928,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   __shared__ KsbPeer s_peers[KSB_MAX_RANKS];  // rank 0, block 0: the shard table, read once
   // one rank: the only shard is this GPU's own, described by the kernel parameters themselves
 #define PEER(x) (MULTI ? s_peers[(x)] : A.self)
-  __shared__ volatile int32_t s_ready[kMaxG]; // decider -> writer: record g is complete
-  __shared__ volatile int32_t s_stop;         // decider -> writer: pods decided in this group (-1: still deciding)
-  __shared__ int32_t s_gmax0[kMaxG], s_k0[kMaxG];  // block 0: per pod, maximum score at group start and its holders
-  __shared__ uint32_t s_words[kWarps];         // block 0: holder mask of the segment being searched
+  __shared__ volatile int32_t s_ready[kMaxG]; // deciders -> writer: record g is complete
+  __shared__ volatile int32_t s_stop;         // deciders -> writer: pods decided in this group (-1: still deciding)
+  // block 0, phase 3 (see there)
+  __shared__ int32_t s_gmax0[kMaxG], s_k0[kMaxG];  // per pod: maximum score at group start and the rows holding it
+  __shared__ int32_t s_lrel[kMaxG];                // per pod: earlier pods of the group that bump lastNodeIndex
+  __shared__ uint32_t s_snap[kMaxG], s_now[kMaxG]; // per pod: cache entries whose row held / holds its maximum
+  __shared__ int32_t s_erow[kCache];               // global row of cache entry i
+  __shared__ int32_t s_pick[kMaxG];                // window: the row each pod picked
+  __shared__ uint32_t t_dirty[kMaxG], t_now[kMaxG], t_snap[kMaxG], t_spec[kMaxG];  // window: column-pass outcomes per pick
+  __shared__ int32_t t_idx[kMaxG];                 // window: cache entry of the picked row, -1 none, -2 no pick
+  __shared__ volatile uint32_t s_special;          // pods the one-pod path must decide
+  __shared__ uint32_t s_prio, s_bad0;              // pods ranked by score; window pods whose pick failed
+  __shared__ volatile int32_t s_ncr, s_cut;        // rows in the cache; the group ends early
   __shared__ uint32_t s_b1_target;             // block 0, pipelined: barrier count at which the evaluation has read the table
 
   const KsbNodeTable& T = A.table;
@@ -976,7 +967,6 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   int ev_p0 = 0, ev_slot = 0;          // evaluation side: first pod and scratch half of the group
   bool cm_valid = false, cm_carry = false;  // commit side: a group is pending; it was evaluated next to another commit
   int cm_p0 = 0, cm_G = 0, cm_slot = 0, cm_floor = 0;
-  int ncr_keep = 0;  // block 0, warp 0: rows in the row cache, carried from group to group when pipelined
   // The block that shares an SM with block 0 would compete with the decider warp for issue slots: it sits the
   // evaluation out. group_done[4] = block 0's SM, group_done[5] = index of that block (0: none).
   int shun_b = 0;
@@ -1015,6 +1005,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   // in registers it would cost every thread of the kernel some thirty of them
   __shared__ long long s_tk[16];  // [0..7] cycles per stage, [8] time mark, [9] groups, [10] groups cut short
   if (tid < 16) s_tk[tid] = 0;
+  if (tid == 0) s_ncr = 0;
   __syncthreads();
   if (tid == 0) s_tk[8] = clock64();
 #define KSB_TICK(i)                                               \
@@ -1292,382 +1283,642 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
 
     // ---- phase 3: block 0 of rank 0 commits the group's pods in order. Rows of other shards are reached
     //      through the peer table (NVLink P2P loads/stores); with one rank every peer access is local.
+    //
+    // What selectHost + AssumePod need from pod to pod is small: the rows chosen earlier in the group (the row
+    // cache), and for every later pod whether such a row still is, or has become, a holder of that pod's maximum.
+    // That relation is kept as two bit masks per pod over the cache entries (s_snap: holder at group start,
+    // s_now: holder now) plus r0 (snapshot holders above the entry's row), filled by COLUMN PASSES: whenever an
+    // entry is created or changed, one warp evaluates every later pod on it, one pod per lane.
+    // Pods are then decided in WINDOWS: one warp picks a host for up to 32 consecutive pods at once, one pod per
+    // lane, each pick assuming that the window's earlier picks leave its pod's holder set alone; the deciding
+    // warps apply each pick's assume step to a scratch copy of its row and run the column pass on it, which
+    // tells which later pods of the window were wrong to assume so. Pods before the first such pod are final;
+    // the window restarts at that pod, which now knows every row it depends on. A pod whose situation is not the
+    // plain one (no fit, one fit, an error, a changed row that stopped fitting or that beats the snapshot's
+    // maximum) is decided alone by the exact one-pod path below ("serial"), as in a group of one.
     if (committer && Gc > 0) {
       const int nsegT = A.nseg_total;
       const int sps = A.segs_per_shard;
       const int R = MULTI ? A.n_ranks : 1;
-      // Segment statistics of every pod that will be ranked by score, one pod per warp: copy them to shared memory,
-      // then the pod's maximum over all segments, the number of rows holding it (k0), the count array with
-      // non-maximal segments zeroed, and its sums over blocks of 32 segments for the two-level rank-select
-      const int nb = (nsegT + 31) >> 5;
+      cm_gid += 1;
+      // rank-select over pod g's snapshot holders: the row of the holder with q holders above it
+      auto select_snapshot = [&](int g, int q) -> int {
+        const int32_t* cum = S.cum + g * nsegT;
+        int lo = 0, hi = nsegT - 1;
+        while (lo < hi) {  // the last segment whose suffix count exceeds q
+          const int mid = (lo + hi + 1) >> 1;
+          if (cum[mid] > q) lo = mid;
+          else hi = mid - 1;
+        }
+        int within = q - (lo + 1 < nsegT ? cum[lo + 1] : 0);
+        const int pr = min(R - 1, lo / sps);
+        const KsbPeer& P = PEER(pr);
+        const int ls = lo - P.seg_base;
+        const uint4* mp = reinterpret_cast<const uint4*>(P.seg_mask + ((half + g) * P.nseg + ls) * kWarps);
+        const uint4 m0 = __ldcv(mp), m1 = __ldcv(mp + 1);
+        const uint32_t w[kWarps] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        int row = -1;
+#pragma unroll
+        for (int wi = kWarps - 1; wi >= 0; --wi) {
+          const int c = __popc(w[wi]);
+          if (row < 0) {
+            if (within < c) row = P.table.row_base + ls * kSeg + wi * 32 + nth_set_from_top(w[wi], within);
+            else within -= c;
+          }
+        }
+        return row;
+      };
+      // Column pass (one warp): every pod g >= g_from of the group, one per lane, on the row held in `c` (its
+      // current columns). Per pod: is the row a holder of the pod's maximum now / was it at group start, does the
+      // pod need the serial path because of it, and how many snapshot holders lie above the row.
+      auto column_pass = [&](RowCache& c, int g_from, uint32_t* now_m, uint32_t* snap_m, uint32_t* spec_m, int32_t* r0_out) {
+        const int g = lane;
+        const bool act = g >= g_from && g < Gc && ((s_prio >> g) & 1u);
+        bool bit_now = false, bit_snap = false, spec = false;
+        if (act) {
+          const KsbPodHeader* h = S.hdr + g;
+          const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+          const KsbPeer& P = PEER(c.pad & 0xff);
+          const int crow = c.row;
+          const size_t at = (half + g) * P.table.n_pad + crow;
+          const int32_t base0 = __ldcv(&P.raw[at].x);
+          const uint32_t reasons0 = __ldcv(P.reasons + at);
+          const int32_t score0 = __ldcv(P.score + at);
+          const int ls = crow / kSeg, rel = crow % kSeg;
+          const int gseg = P.seg_base + ls;
+          const int32_t* cum = S.cum + g * nsegT;
+          const int32_t above = gseg + 1 < nsegT ? cum[gseg + 1] : 0;
+          int32_t r0v = above;
+          if (cum[gseg] > above) {  // the segment holds snapshot holders: count those above the row
+            const uint4* mp = reinterpret_cast<const uint4*>(P.seg_mask + ((half + g) * P.nseg + ls) * kWarps);
+            const uint4 m0 = __ldcv(mp), m1 = __ldcv(mp + 1);
+            const uint32_t w[kWarps] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+            const int wi0 = rel >> 5;
+#pragma unroll
+            for (int wi = 0; wi < kWarps; ++wi) {
+              if (wi > wi0) r0v += __popc(w[wi]);
+              else if (wi == wi0) r0v += __popc(w[wi] & ~((2u << (rel & 31)) - 1u));
+            }
+          }
+          r0_out[g] = r0v;
+          uint32_t new_reasons;
+          int32_t base;
+          eval_cached(P.table, c, pv, reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
+          const bool was_fit = base0 != INT32_MIN;
+          const int32_t gm = s_gmax0[g];
+          const int32_t cold = was_fit ? score0 : INT32_MIN;
+          const int32_t cnew = (was_fit && new_reasons == 0) ? (int32_t)((uint32_t)cold - (uint32_t)base0 + (uint32_t)base) : INT32_MIN;
+          bit_snap = cold == gm;
+          bit_now = cnew == gm;
+          spec = (was_fit && new_reasons != 0) || cnew > gm;
+        }
+        *now_m = __ballot_sync(0xffffffffu, bit_now);
+        *snap_m = __ballot_sync(0xffffffffu, bit_snap);
+        *spec_m = __ballot_sync(0xffffffffu, spec);
+      };
+      // make a column pass's outcome part of the later pods' state, as cache entry `t`
+      auto apply_column = [&](int t, int g_from, bool is_new, uint32_t now_m, uint32_t snap_m, uint32_t spec_m, const int32_t* r0_src) {
+        const int g = lane;
+        if (g >= g_from && g < Gc && ((s_prio >> g) & 1u)) {
+          const uint32_t bit = 1u << t;
+          if ((now_m >> g) & 1u) atomicOr(&s_now[g], bit);
+          else atomicAnd(&s_now[g], ~bit);
+          if (is_new) {
+            if ((snap_m >> g) & 1u) atomicOr(&s_snap[g], bit);
+            else atomicAnd(&s_snap[g], ~bit);
+            S.r0[g * kCache + t] = r0_src[g];
+          }
+        }
+        if (lane == 0 && spec_m) atomicOr(const_cast<uint32_t*>(&s_special), spec_m);
+      };
+
+      // Per pod ranked by score, one pod per warp: the maximum over all segments, and per segment the number of
+      // rows holding it in this and all higher segments (suffix counts; entry 0 is the pod's tie count k0).
       for (int g = warp; g < Gc; g += kWarps) {
         const KsbPodHeader* h = S.hdr + g;
         const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[g].fit_count >= 2;
-        if (!prio) continue;
-        int32_t* smax = S.seg_max + g * nsegT;
-        int32_t* scnt = S.seg_cnt + g * nsegT;
+        if (!prio) {
+          if (lane == 0) {
+            s_gmax0[g] = INT32_MIN;
+            s_k0[g] = 0;
+          }
+          continue;
+        }
+        int32_t* cum = S.cum + g * nsegT;
         int32_t m = INT32_MIN;
         for (int i = lane; i < nsegT; i += 32) {
-          const int q = i / sps;
+          const int q = min(R - 1, i / sps);
           const KsbPeer& P = PEER(q);
-          const int ls = i - q * sps;
-          const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + ls);
-          smax[i] = v;
-          scnt[i] = __ldcv(P.seg_cnt + (half + g) * P.nseg + ls);
+          const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + (i - P.seg_base));
+          cum[i] = v;
           m = max(m, v);
         }
         const int32_t gmax0 = warp_max(m);
-        int32_t k0 = 0;
-        for (int j = 0; j < nb; ++j) {
-          const int i = j * 32 + lane;
-          int32_t c = 0;
-          if (i < nsegT) {
-            c = (smax[i] == gmax0) ? scnt[i] : 0;
-            scnt[i] = c;
+        __syncwarp();
+        int32_t carry = 0;
+        for (int top = nsegT; top > 0; top -= 32) {
+          const int i = top - 1 - lane;  // lane 0 = highest segment
+          int32_t cnt = 0;
+          if (i >= 0 && cum[i] == gmax0) {
+            const int q = min(R - 1, i / sps);
+            const KsbPeer& P = PEER(q);
+            cnt = __ldcv(P.seg_cnt + (half + g) * P.nseg + (i - P.seg_base));
           }
-          c = warp_sum(c);
-          if (lane == 0) S.bsum[g * nb + j] = c;
-          k0 += c;
+          int32_t incl = cnt;
+#pragma unroll
+          for (int d = 1; d < 32; d <<= 1) {
+            const int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+          }
+          __syncwarp();
+          if (i >= 0) cum[i] = carry + incl;
+          carry += __shfl_sync(0xffffffffu, incl, 31);
         }
         if (lane == 0) {
           s_gmax0[g] = gmax0;
-          s_k0[g] = k0;
+          s_k0[g] = carry;
         }
       }
-      if (tid < kMaxG) s_ready[tid] = 0;
-      if (tid == 0) s_stop = -1;
-      __syncthreads();
-#if KSB_FINE_TIMING
-      long long t3[6] = {0, 0, 0, 0, 0, 0};
-      long long m3 = clock64();
-#define KSB_T3(i)                      \
-  do {                                 \
-    long long now_ = clock64();        \
-    t3[i] += now_ - m3;                \
-    m3 = now_;                         \
-  } while (0)
-#else
-#define KSB_T3(i) ((void)0)
-#endif
-      KSB_T3(0);
+      if (tid < kMaxG) {
+        s_ready[tid] = 0;
+        s_snap[tid] = 0;
+        s_now[tid] = 0;
+      }
       if (warp == 0) {
-        // Rows in the cache (uniform across the warp). Pipelined: this group was evaluated before the previous
-        // group's rows reached the table, so those rows (tagged with that group's number) stay in the cache and count
-        // as changed from the first pod on; older entries are dropped.
+        // which pods take the plain path, and how far lastNodeIndex has moved when each pod's turn comes: only pods
+        // that reach selectHost bump it (generic_scheduler.go:144-146, 186-189)
+        bool plain = false;
+        if (lane < Gc) {
+          const KsbPodHeader* h = S.hdr + lane;
+          plain = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && S.norm[lane].fit_count >= 2;
+        }
+        const uint32_t pm = __ballot_sync(0xffffffffu, plain);
+        s_lrel[lane] = __popc(pm & ((1u << lane) - 1u));
+        if (lane == 0) {
+          s_prio = pm;
+          s_special = A.commit ? ~pm : 0xffffffffu;
+          s_stop = -1;
+          s_cut = 0;
+        }
+        // Rows in the cache. Pipelined: this group was evaluated before the previous group's rows reached the
+        // table, so those rows (tagged with that group's number) stay in the cache and count as changed from the
+        // first pod on; older entries are dropped.
         int ncr = 0;
-        cm_gid += 1;
         if (pipe && cm_carry) {
           const int prev = cm_gid - 1;
-          int keep = 0;
-          for (int i = 0; i < ncr_keep; ++i) {
+          const int have = s_ncr;
+          for (int i = 0; i < have; ++i) {
             if ((S.rows[i].pad >> 8) == prev) {
-              if (keep != i) {
+              if (ncr != i) {
                 const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + i);
-                uint32_t* dst = reinterpret_cast<uint32_t*>(S.rows + keep);
+                uint32_t* dst = reinterpret_cast<uint32_t*>(S.rows + ncr);
                 for (int w = lane; w < (int)(sizeof(RowCache) / 4); w += 32) dst[w] = src[w];
               }
-              keep += 1;
+              ncr += 1;
             }
             __syncwarp();
           }
-          ncr = keep;
         }
-        int consumed = 0;
-        // group-start results of the NEXT pod on the cached rows, requested one pod ahead so that their L2
-        // round trip overlaps the current pod's commit
-        int32_t nx_base = INT32_MIN;  // raw.x: the base score at group start, INT32_MIN = the row did not fit
-        uint32_t nx_reasons = 0;
-        int32_t nx_score = INT32_MIN;
-        if (lane < ncr) {  // carried rows: the first pod's values
-          const KsbPeer& P = PEER(S.rows[lane].pad & 0xff);
-          const size_t at = half * P.table.n_pad + S.rows[lane].row;
-          nx_base = __ldcv(&P.raw[at].x);
-          nx_reasons = __ldcv(P.reasons + at);
-          nx_score = __ldcv(P.score + at);
-        }
-        for (int g = 0; g < Gc; ++g) {
-          const KsbPodHeader* h = S.hdr + g;
-          const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
-          const KsbNorms nm = S.norm[g];
-          const bool sched_err = (h->flags & PF_SCHED_ERROR) != 0;
-          const bool prio = !sched_err && !(h->flags & PF_PRIO_ERROR) && nm.fit_count >= 2;
-          KsbResult res;
-          res.status = 0;
-          res.row = -1;
-          res.num_filtered = nm.fit_count;  // lowered below when rows left the filtered list inside the group
-          res.fiterr_slot = -1;
-          res.score = 0;
-#pragma unroll
-          for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = 0;
-          int chosen = -1, chosen_rank = 0;  // local row on shard chosen_rank
-          if (sched_err) {
-            res.status = 3;
-          } else {
-            // (1) this pod on the rows changed earlier in the group, from the row cache
-            uint32_t old_reasons = 0, new_reasons = 0;
-            int32_t cnew = INT32_MIN, cold = INT32_MIN;
-            int crow = -1, crank = 0, cseg = -1;  // local row, shard, global segment
-            bool flip = false;
-            if (lane < ncr) {
-              RowCache& c = S.rows[lane];
-              crow = c.row;
-              crank = c.pad & 0xff;
-              const KsbPeer& P = PEER(crank);
-              cseg = P.seg_base + crow / kSeg;
-              const int32_t base0 = nx_base;
-              old_reasons = nx_reasons;
-              if (prio) cold = nx_score;
-              int32_t base;
-              eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
-              const bool was_fit = base0 != INT32_MIN;
-              flip = was_fit && new_reasons != 0;  // a fit row turned unfit: the Reduce inputs may have moved
-              if (prio && was_fit && new_reasons == 0)
-                // final_score = base + terms that depend only on group-start values: the new total is the old one
-                // with the base score exchanged
-                cnew = (int32_t)((uint32_t)cold - (uint32_t)base0 + (uint32_t)base);
-              if (!prio || !was_fit) cold = INT32_MIN;
-            }
-            int fit_now = nm.fit_count;
-            {
-              // A row that fit at group start and no longer does leaves the filtered list. The Reduce inputs of the
-              // snapshot stay valid if the row cannot have been a holder of any of them: then it simply stops being
-              // a candidate. Otherwise speculation is dropped and this pod opens the next group.
-              const uint32_t fb = __ballot_sync(0xffffffffu, flip);
-              if (fb) {
-                bool safe = true;
-                if (flip) {
-                  const KsbPeer& P = PEER(crank);
-                  const int4 raw = __ldcv(P.raw + (half + g) * P.table.n_pad + crow);
-                  const int32_t na = raw.y, tt = (int32_t)((uint32_t)raw.z >> 24), ipa = raw.w;
-                  const uint32_t sc = (uint32_t)raw.z & 0xffffffu;
-                  safe = (nm.max_na == 0 || na < nm.max_na) && (nm.max_tt == 0 || tt < nm.max_tt) && sc == 0 &&
-                         (nm.ipa_max == nm.ipa_min || (ipa > nm.ipa_min && ipa < nm.ipa_max));
-                }
-                fit_now -= __popc(fb);
-                if (!__all_sync(0xffffffffu, safe) || fit_now < 2) break;
-              }
-            }
-            res.num_filtered = fit_now;
-            KSB_T3(1);  // changed rows
-
-            if (nm.fit_count >= 2 && (h->flags & PF_PRIO_ERROR)) {
-              res.status = 3;
-            } else if (nm.fit_count == 0) {
-              // FitError (generic_scheduler.go:133-139): the histogram over all rows was built in phase 2; here
-              // only the correction for rows whose reasons changed since the group started
-              res.status = 2;
-              int slotv = 0;
-              if (lane == 0) slotv = atomicAdd(A.fiterr_count, 1);
-              slotv = __shfl_sync(0xffffffffu, slotv, 0);
-              if (slotv < KSB_MAX_FITERR) {
-                S.fe_hist[lane] = 0;
-                __syncwarp();
-                if (lane < ncr) {
-                  uint32_t m = old_reasons;
-                  while (m) {
-                    int bit = __ffs(m) - 1;
-                    m &= m - 1;
-                    atomicAdd(&S.fe_hist[bit], -1);
-                  }
-                  m = new_reasons;
-                  while (m) {
-                    int bit = __ffs(m) - 1;
-                    m &= m - 1;
-                    atomicAdd(&S.fe_hist[bit], 1);
-                  }
-                }
-                __syncwarp();
-                A.fiterr_hist[(size_t)slotv * KSB_REASON_BITS + lane] =
-                    __ldcg(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
-                res.fiterr_slot = slotv;
-              }
-              __syncwarp();
-            } else if (nm.fit_count == 1) {
-              // generic_scheduler.go:144-146: no selectHost, counter untouched
-              chosen_rank = min(R - 1, (nm.one_row / kSeg) / sps);
-              chosen = nm.one_row - PEER(chosen_rank).table.row_base;
-            } else {
-              // (2) selectHost (generic_scheduler.go:177-192): lastNodeIndex % k over the rows tied at the maximum, in
-              //     descending row order, from the group-start statistics patched with the changed rows
-              int32_t* smax = S.seg_max + g * nsegT;
-              int32_t* scnt = S.seg_cnt + g * nsegT;
-              int32_t* bsum = S.bsum + g * nb;
-              const int32_t gmax0 = s_gmax0[g];
-              const int32_t gmax = max(gmax0, warp_max(cnew));
-              int pick = -1, pick_rank = 0;
-              if (gmax > gmax0) {
-                // a changed row now beats every row of the snapshot: the ties are changed rows only
-                const bool cand = lane < ncr && cnew == gmax;
-                const uint32_t cb = __ballot_sync(0xffffffffu, cand);
-                const int k = __popc(cb);
-                const int rem = (int)(last_index % (uint64_t)k);
-                const int grow = cand ? PEER(crank).table.row_base + crow : -1;
-                int above = 0;
-                for (uint32_t mm = cb; mm; mm &= mm - 1) {
-                  const int gr = __shfl_sync(0xffffffffu, grow, __ffs(mm) - 1);
-                  above += (gr > grow) ? 1 : 0;
-                }
-                const uint32_t hit = __ballot_sync(0xffffffffu, cand && above == rem);
-                const int src = __ffs(hit) - 1;
-                pick = __shfl_sync(0xffffffffu, crow, src);
-                pick_rank = __shfl_sync(0xffffffffu, crank, src);
-              } else {
-                const int delta = (lane < ncr) ? ((cnew == gmax ? 1 : 0) - (cold == gmax ? 1 : 0)) : 0;
-                if (delta != 0) {
-                  atomicAdd(&scnt[cseg], delta);
-                  atomicAdd(&bsum[cseg >> 5], delta);
-                }
-                const int32_t k = s_k0[g] + warp_sum(delta);
-                if (k <= 0) break;  // every holder of the group-start maximum changed and fell below it
-                __syncwarp();
-                int rem = (last_index >> 32) == 0 ? (int)((uint32_t)last_index % (uint32_t)k) : (int)(last_index % (uint64_t)k);
-                // level 1: the block of 32 segments, from the top; level 2: the segment inside it
-                int blk = 0;
-                if (nb > 1) blk = desc_select(bsum, 0, nb, rem, lane);
-                const int found = blk < 0 ? -1 : desc_select(scnt, blk * 32, min(nsegT, blk * 32 + 32), rem, lane);
-                if (found >= 0) {
-                  // level 3: the row inside the segment, from its holder mask (phase 2) patched with the changed rows
-                  pick_rank = min(R - 1, found / sps);
-                  const KsbPeer& P = PEER(pick_rank);
-                  const int base_row = (found - P.seg_base) * kSeg;
-                  uint32_t word = 0;
-                  if (lane < kWarps && smax[found] == gmax)
-                    word = __ldcv(P.seg_mask + ((half + g) * P.nseg + (found - P.seg_base)) * kWarps + lane);
-                  const uint32_t inseg = __ballot_sync(0xffffffffu, lane < ncr && cseg == found && crank == pick_rank);
-                  if (inseg) {
-                    if (lane < kWarps) s_words[lane] = word;
-                    __syncwarp();
-                    if ((inseg >> lane) & 1u) {
-                      const int rel = crow - base_row;
-                      if (cnew == gmax) atomicOr(&s_words[rel >> 5], 1u << (rel & 31));
-                      else atomicAnd(&s_words[rel >> 5], ~(1u << (rel & 31)));
-                    }
-                    __syncwarp();
-                    if (lane < kWarps) word = s_words[lane];
-                  }
-                  // words from the top: lane w holds rows 32w..32w+31; ties above lane w = holders in words > w
-                  const int cw = __popc(word);
-                  int above = 0;
-#pragma unroll
-                  for (int w = 1; w < kWarps; ++w) {
-                    const int t = __shfl_down_sync(0xffffffffu, cw, w);
-                    if (lane + w < kWarps) above += t;
-                  }
-                  const uint32_t hit = __ballot_sync(0xffffffffu, lane < kWarps && rem >= above && rem < above + cw);
-                  if (hit) {
-                    const int src = __ffs(hit) - 1;
-                    const uint32_t wsel = __shfl_sync(0xffffffffu, word, src);
-                    const int skip = rem - __shfl_sync(0xffffffffu, above, src);
-                    const int bit = nth_set_from_top(wsel, skip);
-                    pick = base_row + src * 32 + bit;
-                  }
-                }
-              }
-              if (pick >= 0) {
-                chosen = pick;
-                chosen_rank = pick_rank;
-                res.score = gmax;
-              } else {
-                res.status = 3;  // only reachable after a barrier timeout
-              }
-              last_index += 1;
-            }
-          }
-          KSB_T3(2);  // select
-          // (3) the assume step on the chosen row: the decider updates the row cache and hands the write-through
-          //     (table columns, class counters, result records) to the writer warp
-          CommitRec& rec = S.recs[g];
-          int idx = -1;
-          if (chosen >= 0 && A.commit) {
-            const bool mine = lane < ncr && S.rows[lane].row == chosen && (S.rows[lane].pad & 0xff) == chosen_rank;
-            const uint32_t bal = __ballot_sync(0xffffffffu, mine);
-            if (bal) idx = __ffs(bal) - 1;
-          }
-          if (g + 1 < Gc) {
-            int prow = -1, prank = 0;
-            if (lane < ncr) {
-              prow = S.rows[lane].row;
-              prank = S.rows[lane].pad & 0xff;
-            } else if (lane == ncr && chosen >= 0 && A.commit && idx < 0) {
-              prow = chosen;  // the row this pod is about to add to the cache
-              prank = chosen_rank;
-            }
-            if (prow >= 0) {
-              const KsbPeer& P = PEER(prank);
-              const size_t at = (half + g + 1) * P.table.n_pad + prow;
-              nx_base = __ldcv(&P.raw[at].x);
-              nx_reasons = __ldcv(P.reasons + at);
-              nx_score = __ldcv(P.score + at);
-            }
-          }
-          if (chosen >= 0) {
-            const KsbPeer& P = PEER(chosen_rank);
-            uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
-            if (A.commit) {
-              if (idx < 0) {
-                idx = ncr;
-                cache_fill(P.table, chosen, S.rows + idx, lane);
-                ncr += 1;
-              }
-              if (lane == 31) S.rows[idx].pad = chosen_rank | (cm_gid << 8);  // shard, and the group that last changed it
-              __syncwarp();
-              if (h->n_ext) {
-                // the chosen row fits, so the device selection succeeds: only its picks are needed. Class tests the
-                // entry does not hold yet are run by the whole warp, one device per lane.
-                RowCache* ce = S.rows + idx;
-                for (int i = 0; i < h->n_ext; ++i) {
-                  const int rs = h->ext[i].rslot;
-                  const uint16_t id = h->ext[i].cls_id;
-                  if (rs < KSB_MAX_RES && h->ext[i].num > 0 && id != 0 && ce->mid[i] != id) {
-                    const uint32_t cls = P.table.dev_class[((size_t)rs * P.table.n_pad + chosen) * KSB_MAX_DEV + lane];
-                    const uint64_t* cm = pv.extcls + i * KSB_CLASS_WORDS;
-                    const uint32_t match = __ballot_sync(0xffffffffu, ((cm[cls >> 6] >> (cls & 63)) & 1ull) != 0);
-                    if (lane == 0) {
-                      ce->mm[i] = match;
-                      ce->mid[i] = id;
-                    }
-                  }
-                }
-                __syncwarp();
-                if (lane == 0) select_devices_cached(P.table, ce, pv, picks);
-#pragma unroll
-                for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
-              }
-              commit_and_record(S.rows + idx, &rec, pv, picks, chosen, chosen_rank, lane);
-            } else {
-              if (h->n_ext) {
-                if (lane == 0) {
-                  EvalOut o;
-                  RowCommon rc;
-                  load_row_common<true>(P.table, chosen, rc);
-                  eval_node<true>(P.table, chosen, rc, pv, o, picks);
-                }
-#pragma unroll
-                for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
-              }
-              if (lane == 31) rec.row = -1;
-            }
-            res.row = P.table.row_base + chosen;
-#pragma unroll
-            for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
-          } else if (lane == 31) {
-            rec.row = -1;
-          }
-          if (lane == 0) rec.res = res;
+        if (lane < ncr) s_erow[lane] = PEER(S.rows[lane].pad & 0xff).table.row_base + S.rows[lane].row;
+        if (lane == 0) s_ncr = ncr;
+      }
+      __syncthreads();
+      {  // carried rows: their column pass against this group's pods
+        const int ncr = s_ncr;
+        for (int i = warp; i < ncr; i += kWarps) {
+          uint32_t nm_, sm_, xm_;
+          column_pass(S.rows[i], 0, &nm_, &sm_, &xm_, S.t_r0 + i * kMaxG);
           __syncwarp();
-          __threadfence_block();
-          if (lane == 0) s_ready[g] = 1;
-          consumed = g + 1;
-          KSB_T3(3);  // cache update + hand-off
+          apply_column(i, 0, true, nm_, sm_, xm_, S.t_r0 + i * kMaxG);
         }
-        ncr_keep = ncr;
-        if (lane == 0) {
-          s_consumed = consumed;
-          __threadfence_block();
-          s_stop = consumed;
+      }
+      __syncthreads();
+#define KSB_BAR3() asm volatile("bar.sync 1, %0;" ::"n"(kDeciders * 32) : "memory")
+      if (warp < kDeciders) {
+        int f = 0;          // pods decided so far
+        int wcap = kDeciders;  // window size: grows while whole windows come out right
+        const uint64_t L0 = last_index;
+        while (f < Gc) {
+          const uint32_t special = s_special;
+          const int ncr = s_ncr;
+          KSB_BAR3();  // everyone holds this round's view before anyone changes it
+          if ((special >> f) & 1u) {
+            // ================= one pod, exact (warp 0) =================
+            if (warp == 0) {
+              const int g = f;
+              const KsbPodHeader* h = S.hdr + g;
+              const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+              const KsbNorms nm = S.norm[g];
+              const bool sched_err = (h->flags & PF_SCHED_ERROR) != 0;
+              const bool prio = !sched_err && !(h->flags & PF_PRIO_ERROR) && nm.fit_count >= 2;
+              const uint64_t last_g = L0 + (uint64_t)s_lrel[g];
+              KsbResult res;
+              res.status = 0;
+              res.row = -1;
+              res.num_filtered = nm.fit_count;  // lowered below when rows left the filtered list inside the group
+              res.fiterr_slot = -1;
+              res.score = 0;
+#pragma unroll
+              for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = 0;
+              int chosen = -1, chosen_rank = 0;  // local row on shard chosen_rank
+              bool cut = false;
+              if (sched_err) {
+                res.status = 3;
+              } else {
+                // (1) this pod on the rows changed since the snapshot, from the row cache
+                uint32_t old_reasons = 0, new_reasons = 0;
+                int32_t cnew = INT32_MIN, cold = INT32_MIN;
+                int crow = -1, crank = 0;
+                bool flip = false;
+                if (lane < ncr) {
+                  RowCache& c = S.rows[lane];
+                  crow = c.row;
+                  crank = c.pad & 0xff;
+                  const KsbPeer& P = PEER(crank);
+                  const size_t at = (half + g) * P.table.n_pad + crow;
+                  const int32_t base0 = __ldcv(&P.raw[at].x);  // INT32_MIN = the row did not fit at group start
+                  old_reasons = __ldcv(P.reasons + at);
+                  if (prio) cold = __ldcv(P.score + at);
+                  int32_t base;
+                  eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
+                  const bool was_fit = base0 != INT32_MIN;
+                  flip = was_fit && new_reasons != 0;  // a fit row turned unfit: the Reduce inputs may have moved
+                  if (prio && was_fit && new_reasons == 0)
+                    // final_score = base + terms that depend only on group-start values: the new total is the old one
+                    // with the base score exchanged
+                    cnew = (int32_t)((uint32_t)cold - (uint32_t)base0 + (uint32_t)base);
+                  if (!prio || !was_fit) cold = INT32_MIN;
+                }
+                int fit_now = nm.fit_count;
+                {
+                  // A row that fit at group start and no longer does leaves the filtered list. The Reduce inputs of the
+                  // snapshot stay valid if the row cannot have been a holder of any of them: then it simply stops being
+                  // a candidate. Otherwise speculation is dropped and this pod opens the next group.
+                  const uint32_t fb = __ballot_sync(0xffffffffu, flip);
+                  if (fb) {
+                    bool safe = true;
+                    if (flip) {
+                      const KsbPeer& P = PEER(crank);
+                      const int4 raw = __ldcv(P.raw + (half + g) * P.table.n_pad + crow);
+                      const int32_t na = raw.y, tt = (int32_t)((uint32_t)raw.z >> 24), ipa = raw.w;
+                      const uint32_t sc = (uint32_t)raw.z & 0xffffffu;
+                      safe = (nm.max_na == 0 || na < nm.max_na) && (nm.max_tt == 0 || tt < nm.max_tt) && sc == 0 &&
+                             (nm.ipa_max == nm.ipa_min || (ipa > nm.ipa_min && ipa < nm.ipa_max));
+                    }
+                    fit_now -= __popc(fb);
+                    if (!__all_sync(0xffffffffu, safe) || fit_now < 2) cut = true;
+                  }
+                }
+                res.num_filtered = fit_now;
+                if (cut) {
+                  // nothing
+                } else if (nm.fit_count >= 2 && (h->flags & PF_PRIO_ERROR)) {
+                  res.status = 3;
+                } else if (nm.fit_count == 0) {
+                  // FitError (generic_scheduler.go:133-139): the histogram over all rows was built in phase 2; here
+                  // only the correction for rows whose reasons changed since the group started
+                  res.status = 2;
+                  int slotv = 0;
+                  if (lane == 0) slotv = atomicAdd(A.fiterr_count, 1);
+                  slotv = __shfl_sync(0xffffffffu, slotv, 0);
+                  if (slotv < A.fiterr_cap) {
+                    S.fe_hist[lane] = 0;
+                    __syncwarp();
+                    if (lane < ncr) {
+                      uint32_t m = old_reasons;
+                      while (m) {
+                        int bit = __ffs(m) - 1;
+                        m &= m - 1;
+                        atomicAdd(&S.fe_hist[bit], -1);
+                      }
+                      m = new_reasons;
+                      while (m) {
+                        int bit = __ffs(m) - 1;
+                        m &= m - 1;
+                        atomicAdd(&S.fe_hist[bit], 1);
+                      }
+                    }
+                    __syncwarp();
+                    A.fiterr_hist[(size_t)slotv * KSB_REASON_BITS + lane] =
+                        __ldcg(A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane) + S.fe_hist[lane];
+                    res.fiterr_slot = slotv;
+                  }
+                  __syncwarp();
+                } else if (nm.fit_count == 1) {
+                  // generic_scheduler.go:144-146: no selectHost, counter untouched
+                  chosen_rank = min(R - 1, (nm.one_row / kSeg) / sps);
+                  chosen = nm.one_row - PEER(chosen_rank).table.row_base;
+                } else {
+                  // (2) selectHost (generic_scheduler.go:177-192): lastNodeIndex % k over the rows tied at the maximum,
+                  //     in descending row order: the snapshot's holders patched with the changed rows
+                  const int32_t gmax0 = s_gmax0[g];
+                  const int32_t gmax = max(gmax0, warp_max(cnew));
+                  int pick = -1, pick_rank = 0;
+                  if (gmax > gmax0) {
+                    // a changed row now beats every row of the snapshot: the ties are changed rows only
+                    const bool cand = lane < ncr && cnew == gmax;
+                    const uint32_t cb = __ballot_sync(0xffffffffu, cand);
+                    const int k = __popc(cb);
+                    const int rem = (int)(last_g % (uint64_t)k);
+                    const int grow = cand ? PEER(crank).table.row_base + crow : -1;
+                    int above = 0;
+                    for (uint32_t mm = cb; mm; mm &= mm - 1) {
+                      const int gr = __shfl_sync(0xffffffffu, grow, __ffs(mm) - 1);
+                      above += (gr > grow) ? 1 : 0;
+                    }
+                    const uint32_t hit = __ballot_sync(0xffffffffu, cand && above == rem);
+                    const int src = __ffs(hit) - 1;
+                    pick = __shfl_sync(0xffffffffu, crow, src);
+                    pick_rank = __shfl_sync(0xffffffffu, crank, src);
+                  } else {
+                    const uint32_t Am = __ballot_sync(0xffffffffu, lane < ncr && cnew == gmax && cold != gmax);
+                    const uint32_t Dm = __ballot_sync(0xffffffffu, lane < ncr && cold == gmax && cnew != gmax);
+                    const int32_t k = s_k0[g] + __popc(Am) - __popc(Dm);
+                    if (k <= 0) {
+                      cut = true;  // every holder of the group-start maximum changed and fell below it
+                    } else {
+                      const int rem = (last_g >> 32) == 0 ? (int)((uint32_t)last_g % (uint32_t)k) : (int)(last_g % (uint64_t)k);
+                      int q = 0;
+                      const int ent = select_merged(Am, Dm, rem, S.r0 + g * kCache, s_erow, &q);
+                      int grow = ent >= 0 ? s_erow[ent] : select_snapshot(g, q);
+                      if (grow >= 0) {
+                        pick_rank = min(R - 1, (grow / kSeg) / sps);
+                        pick = grow - PEER(pick_rank).table.row_base;
+                      }
+                    }
+                  }
+                  if (!cut) {
+                    if (pick >= 0) {
+                      chosen = pick;
+                      chosen_rank = pick_rank;
+                      res.score = gmax;
+                    } else {
+                      res.status = 3;  // only reachable after a barrier timeout
+                    }
+                  }
+                }
+              }
+              if (!cut) {
+                // (3) the assume step on the chosen row: the row cache is updated and the write-through (table columns,
+                //     class counters, result record) handed to the writer warp
+                CommitRec& rec = S.recs[g];
+                int idx = -1;
+                bool fresh = false;
+                if (chosen >= 0 && A.commit) {
+                  const bool mine = lane < ncr && S.rows[lane].row == chosen && (S.rows[lane].pad & 0xff) == chosen_rank;
+                  const uint32_t bal = __ballot_sync(0xffffffffu, mine);
+                  if (bal) idx = __ffs(bal) - 1;
+                }
+                if (chosen >= 0) {
+                  const KsbPeer& P = PEER(chosen_rank);
+                  uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
+                  if (A.commit) {
+                    if (idx < 0) {
+                      if (ncr >= kCache) {
+                        cut = true;  // the cache is full: this pod opens the next group (not reachable: groups are sized for it)
+                      } else {
+                        idx = ncr;
+                        fresh = true;
+                        cache_fill(P.table, chosen, S.rows + idx, lane);
+                      }
+                    }
+                    if (!cut) {
+                      if (lane == 31) S.rows[idx].pad = chosen_rank | (cm_gid << 8);  // shard, and the group that last changed it
+                      __syncwarp();
+                      if (h->n_ext) {
+                        // the chosen row fits, so the device selection succeeds: only its picks are needed. Class tests the
+                        // entry does not hold yet are run by the whole warp, one device per lane.
+                        RowCache* ce = S.rows + idx;
+                        for (int i = 0; i < h->n_ext; ++i) {
+                          const int rs = h->ext[i].rslot;
+                          const uint16_t id = h->ext[i].cls_id;
+                          if (rs < KSB_MAX_RES && h->ext[i].num > 0 && id != 0 && ce->mid[i] != id) {
+                            const uint32_t cls = P.table.dev_class[((size_t)rs * P.table.n_pad + chosen) * KSB_MAX_DEV + lane];
+                            const uint64_t* cm = pv.extcls + i * KSB_CLASS_WORDS;
+                            const uint32_t match = __ballot_sync(0xffffffffu, ((cm[cls >> 6] >> (cls & 63)) & 1ull) != 0);
+                            if (lane == 0) {
+                              ce->mm[i] = match;
+                              ce->mid[i] = id;
+                            }
+                          }
+                        }
+                        __syncwarp();
+                        if (lane == 0) select_devices_cached(P.table, ce, pv, picks);
+#pragma unroll
+                        for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+                      }
+                      commit_and_record(S.rows + idx, &rec, pv, picks, chosen, chosen_rank, lane);
+                    }
+                  } else {
+                    if (h->n_ext) {
+                      if (lane == 0) {
+                        EvalOut o;
+                        RowCommon rc;
+                        load_row_common<true>(P.table, chosen, rc);
+                        eval_node<true>(P.table, chosen, rc, pv, o, picks);
+                      }
+#pragma unroll
+                      for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+                    }
+                    if (lane == 31) rec.row = -1;
+                  }
+                  res.row = P.table.row_base + chosen;
+#pragma unroll
+                  for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
+                } else if (lane == 31) {
+                  rec.row = -1;
+                }
+                if (!cut) {
+                  if (lane == 0) rec.res = res;
+                  __syncwarp();
+                  __threadfence_block();
+                  if (lane == 0) s_ready[g] = 1;
+                  if (idx >= 0) {
+                    // the changed row against every later pod of the group
+                    if (lane == 0) {
+                      s_erow[idx] = res.row;
+                      if (fresh) s_ncr = ncr + 1;
+                    }
+                    uint32_t nm_, sm_, xm_;
+                    column_pass(S.rows[idx], g + 1, &nm_, &sm_, &xm_, S.t_r0);
+                    __syncwarp();
+                    apply_column(idx, g + 1, fresh, nm_, sm_, xm_, S.t_r0);
+                  }
+                }
+              }
+              if (cut && lane == 0) s_cut = 1;
+            }
+            KSB_BAR3();
+            if (s_cut) break;
+            f += 1;
+            continue;
+          }
+          // ================= a window of plain pods =================
+          int W = __ffs((int)(special >> f)) - 1;  // plain pods in a row from f on
+          if (W < 0) W = 32;
+          W = min(min(W, wcap), min(Gc - f, kCache - ncr));
+          if (W <= 0) {  // no room left in the row cache: the rest of the group opens the next one
+            if (tid == 0) s_cut = 1;
+            KSB_BAR3();
+            break;
+          }
+          // (1) picks, one pod per lane
+          if (warp == 0) {
+            int pick = -1;
+            bool bad = false;
+            if (lane < W) {
+              const int g = f + lane;
+              const uint32_t sn = s_snap[g], nw = s_now[g];
+              const uint32_t Am = nw & ~sn, Dm = sn & ~nw;
+              const int32_t k = s_k0[g] + __popc(Am) - __popc(Dm);
+              if (k <= 0) {
+                bad = true;
+              } else {
+                const uint64_t last_g = L0 + (uint64_t)s_lrel[g];
+                const int rem = (last_g >> 32) == 0 ? (int)((uint32_t)last_g % (uint32_t)k) : (int)(last_g % (uint64_t)k);
+                int q = 0;
+                const int ent = select_merged(Am, Dm, rem, S.r0 + g * kCache, s_erow, &q);
+                pick = ent >= 0 ? s_erow[ent] : select_snapshot(g, q);
+                if (pick < 0) bad = true;
+              }
+              s_pick[lane] = pick;
+            }
+            const uint32_t bm = __ballot_sync(0xffffffffu, bad);
+            if (lane == 0) s_bad0 = bm;  // these pods go to the serial path (which ends the group if it must)
+          }
+          KSB_BAR3();
+          // (2) per pick: its row after the assume step, and that row against the later pods
+          for (int w = warp; w < W; w += kDeciders) {
+            const int g = f + w;
+            const int e = s_pick[w];
+            if (e < 0) {
+              if (lane == 0) {
+                t_dirty[w] = 0;
+                t_idx[w] = -2;
+              }
+              continue;
+            }
+            const KsbPodHeader* h = S.hdr + g;
+            const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+            const int erank = min(R - 1, (e / kSeg) / sps);
+            const KsbPeer& P = PEER(erank);
+            const int lrow = e - P.table.row_base;
+            const uint32_t hit = __ballot_sync(0xffffffffu, lane < ncr && s_erow[lane] == e);
+            const int idx = hit ? __ffs(hit) - 1 : -1;
+            RowCache* pc = S.post + w;
+            if (idx >= 0) {
+              const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + idx);
+              uint32_t* dst = reinterpret_cast<uint32_t*>(pc);
+              for (int x = lane; x < (int)(sizeof(RowCache) / 4); x += 32) dst[x] = src[x];
+            } else {
+              cache_fill(P.table, lrow, pc, lane);
+            }
+            __syncwarp();
+            if (lane == 31) pc->pad = erank | (cm_gid << 8);
+            __syncwarp();
+            uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
+            if (h->n_ext) {
+              for (int i = 0; i < h->n_ext; ++i) {
+                const int rs = h->ext[i].rslot;
+                const uint16_t id = h->ext[i].cls_id;
+                if (rs < KSB_MAX_RES && h->ext[i].num > 0 && id != 0 && pc->mid[i] != id) {
+                  const uint32_t cls = P.table.dev_class[((size_t)rs * P.table.n_pad + lrow) * KSB_MAX_DEV + lane];
+                  const uint64_t* cm = pv.extcls + i * KSB_CLASS_WORDS;
+                  const uint32_t match = __ballot_sync(0xffffffffu, ((cm[cls >> 6] >> (cls & 63)) & 1ull) != 0);
+                  if (lane == 0) {
+                    pc->mm[i] = match;
+                    pc->mid[i] = id;
+                  }
+                }
+              }
+              __syncwarp();
+              if (lane == 0) select_devices_cached(P.table, pc, pv, picks);
+#pragma unroll
+              for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+            }
+            CommitRec& rec = S.recs[g];
+            commit_and_record(pc, &rec, pv, picks, lrow, erank, lane);
+            if (lane == 0) {
+              KsbResult res;
+              res.status = 0;
+              res.row = e;
+              res.num_filtered = S.norm[g].fit_count;
+              res.fiterr_slot = -1;
+              res.score = s_gmax0[g];
+#pragma unroll
+              for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
+              rec.res = res;
+            }
+            __syncwarp();
+            uint32_t nm_, sm_, xm_;
+            column_pass(*pc, g + 1, &nm_, &sm_, &xm_, S.t_r0 + w * kMaxG);
+            // later pods of the window whose pick assumed this row's standing unchanged, and were wrong (or chose the
+            // same row, whose copy here lacks this pod)
+            bool dirty = false;
+            {
+              const int g2 = lane;
+              if (g2 > g && g2 < f + W) {
+                const bool used = idx >= 0 ? ((s_now[g2] >> idx) & 1u) != 0 : ((sm_ >> g2) & 1u) != 0;
+                const bool now = ((nm_ >> g2) & 1u) != 0;
+                dirty = ((xm_ >> g2) & 1u) != 0 || now != used || s_pick[g2 - f] == e;
+              }
+            }
+            const uint32_t dm = __ballot_sync(0xffffffffu, dirty);
+            if (lane == 0) {
+              t_dirty[w] = dm;
+              t_now[w] = nm_;
+              t_snap[w] = sm_;
+              t_spec[w] = xm_;
+              t_idx[w] = idx;
+            }
+          }
+          KSB_BAR3();
+          // (3) how many of the window's pods are final
+          int n_ok;
+          uint32_t newmask;
+          {
+            const uint32_t d = lane < W ? t_dirty[lane] : 0u;
+            uint32_t dall = __reduce_or_sync(0xffffffffu, d) | (s_bad0 << f);
+            dall >>= f;
+            n_ok = dall ? min(W, __ffs((int)dall) - 1) : W;
+            newmask = __ballot_sync(0xffffffffu, lane < n_ok && t_idx[lane] == -1);
+          }
+          // (4) their rows enter the cache, their records go to the writer, the later pods learn about them
+          for (int w = warp; w < n_ok; w += kDeciders) {
+            const int g = f + w;
+            const int idx = t_idx[w];
+            const bool fresh = idx < 0;
+            const int t = fresh ? ncr + __popc(newmask & ((1u << w) - 1u)) : idx;
+            {
+              const uint32_t* src = reinterpret_cast<const uint32_t*>(S.post + w);
+              uint32_t* dst = reinterpret_cast<uint32_t*>(S.rows + t);
+              for (int x = lane; x < (int)(sizeof(RowCache) / 4); x += 32) dst[x] = src[x];
+            }
+            if (lane == 0) s_erow[t] = s_pick[w];
+            apply_column(t, g + 1, fresh, t_now[w], t_snap[w], t_spec[w], S.t_r0 + w * kMaxG);
+            __syncwarp();
+            __threadfence_block();
+            if (lane == 0) s_ready[g] = 1;
+          }
+          if (tid == 0) {
+            s_ncr = ncr + __popc(newmask);
+            if (s_bad0) atomicOr(const_cast<uint32_t*>(&s_special), s_bad0 << f);
+          }
+          wcap = n_ok == W ? min(32, wcap * 2) : max(kDeciders, min(32, n_ok + 2));
+          f += n_ok;
+          KSB_BAR3();
         }
-        if (lane < R) *PEER(lane).last_node_index = last_index;  // every rank's host reads its own copy
-      } else if (warp == 1) {
+        if (tid == 0) {
+          s_consumed = f;
+          last_index = L0 + (uint64_t)(f < Gc ? s_lrel[f] : s_lrel[Gc - 1] + ((s_prio >> (Gc - 1)) & 1u));
+          __threadfence_block();
+          s_stop = f;
+        }
+        if (warp == 0) {
+          last_index = __shfl_sync(0xffffffffu, last_index, 0);
+          if (lane < R) *PEER(lane).last_node_index = last_index;  // every rank's host reads its own copy
+        }
+      } else {
         // writer warp: table write-through, class counters and result records of every decided pod, in order
         bool table_open = false;
         for (int g = 0; g < Gc; ++g) {
@@ -1692,34 +1943,28 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             const KsbPeer& P = PEER(rec.rank);
             const int chosen = rec.row;
             write_through(P.table, rec, h, lane);
-            if (R == 1 && counters_fast(h)) {
-              const CounterLoads cl = counters_load(P.table, chosen, pv, lane);
-              counters_store(P.table, chosen, pv, cl, lane);
-            } else {
-              // SelectorSpread columns are sharded with the rows; affinity tables are replicated on every rank
-              const size_t pn = P.table.n_pad;
-              for (int i = lane; i < h->n_spread_inc; i += 32) {
-                uint32_t* pp = P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen;
-                *pp = __ldcv(pp) + 1u;
-              }
-              for (int i = lane; i < h->n_commit; i += 32) {
-                const uint64_t cm = pv.commits[2 * i];
-                const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
-                const uint32_t off = (uint32_t)cm;
-                const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
-                for (int q = 0; q < R; ++q) {
-                  int32_t* tb = PEER(q).table.tables;
-                  if (d) tb[off + d] = __ldcv(tb + off + d) + delta;
-                  if ((cm >> 40) & 1ull) tb[off] = __ldcv(tb + off) + delta;
-                }
+            // the class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
+            // of this group reads them. SelectorSpread columns are sharded with the rows; affinity tables are
+            // replicated on every rank.
+            const size_t pn = P.table.n_pad;
+            for (int i = lane; i < h->n_spread_inc; i += 32) atomicAdd(P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen, 1u);
+            for (int i = lane; i < h->n_commit; i += 32) {
+              const uint64_t cm = pv.commits[2 * i];
+              const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
+              const uint32_t off = (uint32_t)cm;
+              const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
+              for (int q = 0; q < R; ++q) {
+                int32_t* tb = PEER(q).table.tables;
+                if (d) atomicAdd(tb + off + d, delta);
+                if ((cm >> 40) & 1ull) atomicAdd(tb + off, delta);  // slot 0: total matching pods anywhere
               }
             }
           }
           __syncwarp();
         }
       }
+#undef KSB_BAR3
       __syncthreads();
-      KSB_T3(4);
       // publish how far the group got
       if (tid == 0) {
         A.group_done[gi & 1] = s_consumed;
@@ -1734,12 +1979,6 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         int32_t* gh = A.ghist + (size_t)(slot ^ 1) * kMaxG * KSB_REASON_BITS;
         for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
       }
-      KSB_T3(5);
-#if KSB_FINE_TIMING
-      if (tid == 0)
-        for (int i = 0; i < 6; ++i) A.counters[9 + i] += (uint64_t)t3[i];
-#endif
-#undef KSB_T3
     }
     KSB_TICK(5);
     if (pipe && committer && Gc > 0) {
@@ -1830,7 +2069,7 @@ __global__ void ksb_apply_kernel(KsbNodeTable T, const KsbPodHeader* header, con
 }
 
 extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
-  size_t o[13];
+  size_t o[kSmemParts];
   return smem_layout(o, zone_stride);
 }
 
@@ -1971,5 +2210,6 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->xstate = (uint32_t*)(b + kNaXstate);
   a->peers = (const KsbPeer*)(b + kNaPeer);
   a->fiterr_hist = (int32_t*)(b + kNaFitHist);
+  a->fiterr_cap = KSB_MAX_FITERR;
   return 0;
 }

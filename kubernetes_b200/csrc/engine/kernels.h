@@ -47,7 +47,8 @@ struct KsbBatchArgs {
   uint32_t* barrier;            // grid barrier counter, zero at launch
   int32_t* error_flag;
   int32_t* fiterr_count;
-  int32_t* fiterr_hist;         // [KSB_MAX_FITERR][KSB_REASON_BITS]
+  int32_t* fiterr_hist;         // [fiterr_cap][KSB_REASON_BITS] reason histograms of the launch's no-fit pods
+  int32_t fiterr_cap;           // histograms the buffer holds (>= KSB_MAX_FITERR; the engine sizes it to the launch)
   uint64_t* last_node_index;    // genericScheduler.lastNodeIndex
   int32_t* group_done;          // [8] pods consumed by the group, ping-pong; pipelined: [2..3] size of the group evaluated, [4] block 0's SM, [5] the block sharing it
   uint64_t* counters;           // [16] groups run, groups cut short by a dropped speculation, stage cycles
