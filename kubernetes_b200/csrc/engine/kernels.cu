@@ -150,6 +150,68 @@ __device__ __forceinline__ int64_t unused_score(int64_t requested, int64_t capac
   return q;
 }
 
+// 1/a for a in [1, 2^50): hardware estimate + two Newton steps (relative error of a few 2^-53). Only used where an
+// exact integer or guard-band check follows.
+__device__ __forceinline__ double fast_rcp(double a) {
+  double x;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+  x = __dmul_rn(x, __dsub_rn(2.0, __dmul_rn(a, x)));
+  x = __dmul_rn(x, __dsub_rn(2.0, __dmul_rn(a, x)));
+  return x;
+}
+
+// LeastRequested (least_requested.go:33-91) and BalancedResourceAllocation (balanced_resource_allocation.go:51-100)
+// for one (pod, node), with the results of the reference's arithmetic and without its divisions:
+//  * ((cap - req) * 10) / cap is estimated as floor(10 - 10 * req * (1/cap)) and corrected with the exact integer
+//    remainder, so it is exact whatever the estimate's rounding;
+//  * int((1 - |req_c/cap_c - req_m/cap_m|) * 10) is computed with reciprocal multiplies (error below 2e-14 on a value
+//    in (0, 10]); only when that lands within 1e-9 of an integer are the reference's two float64 divisions done.
+// rcp_c / rcp_m: fast_rcp of the capacities (per row). Outside 0 < capacity < 2^50, 0 <= request the reference's
+// own formulas run.
+__device__ __forceinline__ void lr_bra(int64_t cpu, int64_t mem, int64_t acpu, int64_t amem, double rcp_c, double rcp_m,
+                                       int32_t* lr_out, int32_t* bra_out) {
+  const int64_t lim = 1ll << 50;
+  if (acpu > 0 && amem > 0 && acpu < lim && amem < lim && cpu >= 0 && mem >= 0 && cpu < lim && mem < lim) {
+    const double cfa = __dmul_rn((double)cpu, rcp_c);
+    const double mfa = __dmul_rn((double)mem, rcp_m);
+    int64_t qc = 0, qm = 0;
+    if (cpu <= acpu) {
+      qc = (int64_t)__double2int_rd(__dsub_rn(10.0, __dmul_rn(10.0, cfa)));
+      const int64_t r = (acpu - cpu) * 10 - qc * acpu;
+      qc += (r >= acpu) ? 1 : ((r < 0) ? -1 : 0);
+    }
+    if (mem <= amem) {
+      qm = (int64_t)__double2int_rd(__dsub_rn(10.0, __dmul_rn(10.0, mfa)));
+      const int64_t r = (amem - mem) * 10 - qm * amem;
+      qm += (r >= amem) ? 1 : ((r < 0) ? -1 : 0);
+    }
+    *lr_out = (int32_t)((qc + qm) / 2);
+    int32_t bra = 0;
+    if (cpu < acpu && mem < amem) {  // below 2^50 the float64 fractions reach 1.0 exactly when request >= capacity
+      const double v = __dmul_rn(__dsub_rn(1.0, fabs(__dsub_rn(cfa, mfa))), 10.0);
+      const double near = rint(v);
+      if (fabs(__dsub_rn(v, near)) > 1e-9) {
+        bra = (int32_t)v;
+      } else {
+        const double cf = __ddiv_rn((double)cpu, (double)acpu);
+        const double mf = __ddiv_rn((double)mem, (double)amem);
+        bra = (int32_t)(__dmul_rn(__dsub_rn(1.0, fabs(__dsub_rn(cf, mf))), 10.0));
+      }
+    }
+    *bra_out = bra;
+    return;
+  }
+  *lr_out = (int32_t)((unused_score(cpu, acpu) + unused_score(mem, amem)) / 2);
+  const double cf = acpu == 0 ? 1.0 : __ddiv_rn((double)cpu, (double)acpu);
+  const double mf = amem == 0 ? 1.0 : __ddiv_rn((double)mem, (double)amem);
+  int32_t bra = 0;
+  if (!(cf >= 1.0 || mf >= 1.0)) {
+    double diff = fabs(__dsub_rn(cf, mf));
+    bra = (int32_t)(__dmul_rn(__dsub_rn(1.0, diff), 10.0));
+  }
+  *bra_out = bra;
+}
+
 // The fork's per-node device selection (core/extended_resources.go:83-150), devices visited in
 // ascending id order (= bit order). Returns the failing reason bit or 0; fills picks[] on success.
 // `avail_in` holds the node's available-device masks per resource slot.
@@ -254,6 +316,7 @@ struct RowCommon {
   uint64_t lab[kLabFast];
   int32_t num_pods, alloc_pods;
   uint32_t nflags, zone;
+  double rcp_cpu, rcp_mem;  // fast_rcp of the allocatable cpu / memory (lr_bra)
 };
 
 template <bool CG>
@@ -274,6 +337,8 @@ __device__ __forceinline__ void load_row_common(const KsbNodeTable& T, int r, Ro
   rc.avoid = T.avoid[r];
 #pragma unroll
   for (int w = 0; w < kLabFast; ++w) rc.lab[w] = w < T.W ? T.labels[w * np + r] : 0ull;
+  rc.rcp_cpu = fast_rcp((double)rc.acpu);
+  rc.rcp_mem = fast_rcp((double)rc.amem);
 }
 
 // eval_expr for label_words == kLabFast: the row's label words come from registers
@@ -432,15 +497,8 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   // --- priorities (Map halves)
   const int64_t cpu = h->nz_cpu + ncpu;
   const int64_t mem = h->nz_mem + nmem;
-  const int32_t lr = (int32_t)((unused_score(cpu, acpu) + unused_score(mem, amem)) / 2);  // least_requested.go:63-91
-  // balanced_resource_allocation.go:51-100
-  const double cf = acpu == 0 ? 1.0 : __ddiv_rn((double)cpu, (double)acpu);
-  const double mf = amem == 0 ? 1.0 : __ddiv_rn((double)mem, (double)amem);
-  int32_t bra = 0;
-  if (!(cf >= 1.0 || mf >= 1.0)) {
-    double diff = fabs(__dsub_rn(cf, mf));
-    bra = (int32_t)(__dmul_rn(__dsub_rn(1.0, diff), 10.0));
-  }
+  int32_t lr, bra;  // least_requested.go:63-91, balanced_resource_allocation.go:51-100
+  lr_bra(cpu, mem, acpu, amem, rc.rcp_cpu, rc.rcp_mem, &lr, &bra);
   const int32_t av = (rc.avoid & h->avoid_mask) ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
   o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
   o.na = na;
@@ -612,6 +670,7 @@ struct RowCache {
   // per extended-resource entry slot: which devices of the row match the class mask interned as `mid` (0: none kept)
   uint32_t mm[KSB_MAX_EXT];
   uint16_t mid[KSB_MAX_EXT];
+  double rcp[2];  // fast_rcp of q[0], q[1] (allocatable cpu / memory), set when the entry is filled
 };
 
 // reason bits that depend on columns a bind changes; every other bit of a row is constant inside a group
@@ -698,14 +757,8 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   const int64_t acpu = c.q[0], amem = c.q[1];
   const int64_t cpu = h->nz_cpu + c.q[8];
   const int64_t mem = h->nz_mem + c.q[9];
-  const int32_t lr = (int32_t)((unused_score(cpu, acpu) + unused_score(mem, amem)) / 2);
-  const double cf = acpu == 0 ? 1.0 : __ddiv_rn((double)cpu, (double)acpu);
-  const double mf = amem == 0 ? 1.0 : __ddiv_rn((double)mem, (double)amem);
-  int32_t bra = 0;
-  if (!(cf >= 1.0 || mf >= 1.0)) {
-    double diff = fabs(__dsub_rn(cf, mf));
-    bra = (int32_t)(__dmul_rn(__dsub_rn(1.0, diff), 10.0));
-  }
+  int32_t lr, bra;
+  lr_bra(cpu, mem, acpu, amem, c.rcp[0], c.rcp[1], &lr, &bra);
   const int32_t av = ((uint64_t)c.q[30] & h->avoid_mask) ? 0 : 10;
   *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
 }
@@ -728,6 +781,7 @@ __device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCach
   if (lane < 4 + KSB_MAX_RES) reinterpret_cast<uint32_t*>(&c->apods)[lane] = v2;
   if (lane == 31) c->row = r;
   if (lane >= 24 && lane < 24 + KSB_MAX_EXT) c->mid[lane - 24] = 0;
+  if (lane < 2) c->rcp[lane] = fast_rcp((double)v);
 }
 
 // What the decider warp hands to the writer warp for one pod: the chosen row's mutable columns after the
@@ -981,6 +1035,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     if (nblk < 4) shun_b = 0;
   }
   int cm_gid = 0;    // block 0: sequence number of the group being committed (row-cache tags)
+  int wcap = 2 * kDeciders;  // block 0, phase 3: window size; grows while whole windows come out right, shrinks when they do not
 
   if (MULTI && blockIdx.x == 0 && A.rank == 0) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(A.peers);
@@ -1003,8 +1058,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   }
   // measurement state lives in shared memory (thread 0 of each block updates it; block 0's copy is reported): kept
   // in registers it would cost every thread of the kernel some thirty of them
-  __shared__ long long s_tk[16];  // [0..7] cycles per stage, [8] time mark, [9] groups, [10] groups cut short
-  if (tid < 16) s_tk[tid] = 0;
+  __shared__ long long s_tk[24];  // [0..7] cycles per stage, [8] time mark, [9] groups, [10] groups cut short
+  if (tid < 24) s_tk[tid] = 0;
   if (tid == 0) s_ncr = 0;
   __syncthreads();
   if (tid == 0) s_tk[8] = clock64();
@@ -1311,48 +1366,79 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           else hi = mid - 1;
         }
         int within = q - (lo + 1 < nsegT ? cum[lo + 1] : 0);
-        const int pr = min(R - 1, lo / sps);
+        const int pr = MULTI ? min(R - 1, lo / sps) : 0;
         const KsbPeer& P = PEER(pr);
         const int ls = lo - P.seg_base;
         const uint4* mp = reinterpret_cast<const uint4*>(P.seg_mask + ((half + g) * P.nseg + ls) * kWarps);
         const uint4 m0 = __ldcv(mp), m1 = __ldcv(mp + 1);
         const uint32_t w[kWarps] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-        int row = -1;
+        // the word holding the answer: the highest word whose holders, counted from the top, exceed `within`
+        int wsel = -1, skip = 0, acc = 0;
+        uint32_t word = 0;
 #pragma unroll
         for (int wi = kWarps - 1; wi >= 0; --wi) {
           const int c = __popc(w[wi]);
-          if (row < 0) {
-            if (within < c) row = P.table.row_base + ls * kSeg + wi * 32 + nth_set_from_top(w[wi], within);
-            else within -= c;
+          if (wsel < 0 && within < acc + c) {
+            wsel = wi;
+            skip = within - acc;
+            word = w[wi];
           }
+          acc += c;
         }
+        const int row = wsel < 0 ? -1 : P.table.row_base + ls * kSeg + wsel * 32 + nth_set_from_top(word, skip);
         return row;
       };
-      // Column pass (one warp): every pod g >= g_from of the group, one per lane, on the row held in `c` (its
-      // current columns). Per pod: is the row a holder of the pod's maximum now / was it at group start, does the
-      // pod need the serial path because of it, and how many snapshot holders lie above the row.
-      auto column_pass = [&](RowCache& c, int g_from, uint32_t* now_m, uint32_t* snap_m, uint32_t* spec_m, int32_t* r0_out) {
+      // Column pass (one warp): every pod g >= g_from of the group, one per lane, on one changed row. Per pod: is the
+      // row a holder of the pod's maximum now / was it at group start, does the pod need the serial path because of
+      // it, and how many snapshot holders lie above the row. Split in two so that the loads of the pod's group-start
+      // results on the row (col_issue) are in flight while the row itself is fetched and committed.
+      struct ColIn {
+        int32_t base0, score0, above;
+        uint32_t reasons0;
+        uint4 m0, m1;
+        bool act, seg_holds;
+      };
+      auto col_issue = [&](int prank, int crow, int g_from) -> ColIn {
+        ColIn in;
         const int g = lane;
-        const bool act = g >= g_from && g < Gc && ((s_prio >> g) & 1u);
+        in.act = g >= g_from && g < Gc && ((s_prio >> g) & 1u);
+        in.base0 = INT32_MIN;
+        in.score0 = 0;
+        in.reasons0 = 0;
+        in.above = 0;
+        in.seg_holds = false;
+        in.m0 = make_uint4(0, 0, 0, 0);
+        in.m1 = in.m0;
+        if (in.act) {
+          const KsbPeer& P = PEER(prank);
+          const size_t at = (half + g) * P.table.n_pad + crow;
+          in.base0 = __ldcv(&P.raw[at].x);
+          in.reasons0 = __ldcv(P.reasons + at);
+          in.score0 = __ldcv(P.score + at);
+          const int ls = crow / kSeg;
+          const int gseg = P.seg_base + ls;
+          const int32_t* cum = S.cum + g * nsegT;
+          in.above = gseg + 1 < nsegT ? cum[gseg + 1] : 0;
+          in.seg_holds = cum[gseg] > in.above;
+          if (in.seg_holds) {  // the segment holds snapshot holders: its mask tells how many lie above the row
+            const uint4* mp = reinterpret_cast<const uint4*>(P.seg_mask + ((half + g) * P.nseg + ls) * kWarps);
+            in.m0 = __ldcv(mp);
+            in.m1 = __ldcv(mp + 1);
+          }
+        }
+        return in;
+      };
+      auto col_eval = [&](RowCache& c, const ColIn& in, uint32_t* now_m, uint32_t* snap_m, uint32_t* spec_m, int32_t* r0_out) {
+        const int g = lane;
         bool bit_now = false, bit_snap = false, spec = false;
-        if (act) {
+        if (in.act) {
           const KsbPodHeader* h = S.hdr + g;
           const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
           const KsbPeer& P = PEER(c.pad & 0xff);
-          const int crow = c.row;
-          const size_t at = (half + g) * P.table.n_pad + crow;
-          const int32_t base0 = __ldcv(&P.raw[at].x);
-          const uint32_t reasons0 = __ldcv(P.reasons + at);
-          const int32_t score0 = __ldcv(P.score + at);
-          const int ls = crow / kSeg, rel = crow % kSeg;
-          const int gseg = P.seg_base + ls;
-          const int32_t* cum = S.cum + g * nsegT;
-          const int32_t above = gseg + 1 < nsegT ? cum[gseg + 1] : 0;
-          int32_t r0v = above;
-          if (cum[gseg] > above) {  // the segment holds snapshot holders: count those above the row
-            const uint4* mp = reinterpret_cast<const uint4*>(P.seg_mask + ((half + g) * P.nseg + ls) * kWarps);
-            const uint4 m0 = __ldcv(mp), m1 = __ldcv(mp + 1);
-            const uint32_t w[kWarps] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+          int32_t r0v = in.above;
+          if (in.seg_holds) {
+            const uint32_t w[kWarps] = {in.m0.x, in.m0.y, in.m0.z, in.m0.w, in.m1.x, in.m1.y, in.m1.z, in.m1.w};
+            const int rel = c.row % kSeg;
             const int wi0 = rel >> 5;
 #pragma unroll
             for (int wi = 0; wi < kWarps; ++wi) {
@@ -1363,11 +1449,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           r0_out[g] = r0v;
           uint32_t new_reasons;
           int32_t base;
-          eval_cached(P.table, c, pv, reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
-          const bool was_fit = base0 != INT32_MIN;
+          eval_cached(P.table, c, pv, in.reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
+          const bool was_fit = in.base0 != INT32_MIN;
           const int32_t gm = s_gmax0[g];
-          const int32_t cold = was_fit ? score0 : INT32_MIN;
-          const int32_t cnew = (was_fit && new_reasons == 0) ? (int32_t)((uint32_t)cold - (uint32_t)base0 + (uint32_t)base) : INT32_MIN;
+          const int32_t cold = was_fit ? in.score0 : INT32_MIN;
+          const int32_t cnew =
+              (was_fit && new_reasons == 0) ? (int32_t)((uint32_t)cold - (uint32_t)in.base0 + (uint32_t)base) : INT32_MIN;
           bit_snap = cold == gm;
           bit_now = cnew == gm;
           spec = (was_fit && new_reasons != 0) || cnew > gm;
@@ -1375,6 +1462,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         *now_m = __ballot_sync(0xffffffffu, bit_now);
         *snap_m = __ballot_sync(0xffffffffu, bit_snap);
         *spec_m = __ballot_sync(0xffffffffu, spec);
+      };
+      auto column_pass = [&](RowCache& c, int g_from, uint32_t* now_m, uint32_t* snap_m, uint32_t* spec_m, int32_t* r0_out) {
+        const ColIn in = col_issue(c.pad & 0xff, c.row, g_from);
+        col_eval(c, in, now_m, snap_m, spec_m, r0_out);
       };
       // make a column pass's outcome part of the later pods' state, as cache entry `t`
       auto apply_column = [&](int t, int g_from, bool is_new, uint32_t now_m, uint32_t snap_m, uint32_t spec_m, const int32_t* r0_src) {
@@ -1405,34 +1496,79 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           continue;
         }
         int32_t* cum = S.cum + g * nsegT;
-        int32_t m = INT32_MIN;
-        for (int i = lane; i < nsegT; i += 32) {
-          const int q = min(R - 1, i / sps);
-          const KsbPeer& P = PEER(q);
-          const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + (i - P.seg_base));
-          cum[i] = v;
-          m = max(m, v);
-        }
-        const int32_t gmax0 = warp_max(m);
-        __syncwarp();
-        int32_t carry = 0;
-        for (int top = nsegT; top > 0; top -= 32) {
-          const int i = top - 1 - lane;  // lane 0 = highest segment
-          int32_t cnt = 0;
-          if (i >= 0 && cum[i] == gmax0) {
-            const int q = min(R - 1, i / sps);
-            const KsbPeer& P = PEER(q);
-            cnt = __ldcv(P.seg_cnt + (half + g) * P.nseg + (i - P.seg_base));
+        int32_t gmax0, carry = 0;
+        if (!MULTI && nsegT <= 8 * 32 && (A.self.nseg & 3) == 0) {
+          // one rank, up to 256 segments (65,536 rows): lane l takes segments 8l..8l+7 with four 16-byte loads, sums
+          // its own eight counts serially and one warp scan joins the lanes (the row stride of the per-pod statistics
+          // is a multiple of four segments, so the vectors are aligned)
+          const int32_t* pmax = A.self.seg_max + (half + g) * A.self.nseg;
+          const int32_t* pcnt = A.self.seg_cnt + (half + g) * A.self.nseg;
+          int32_t vmax[8], vcnt[8];
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const int i0 = lane * 8 + hh * 4;
+            int4 a4 = make_int4(INT32_MIN, INT32_MIN, INT32_MIN, INT32_MIN), c4 = make_int4(0, 0, 0, 0);
+            if (i0 < nsegT) {  // nsegT may end inside the vector: the statistics arrays are padded to the stride
+              a4 = __ldcv(reinterpret_cast<const int4*>(pmax + i0));
+              c4 = __ldcv(reinterpret_cast<const int4*>(pcnt + i0));
+            }
+            vmax[hh * 4 + 0] = a4.x; vmax[hh * 4 + 1] = a4.y; vmax[hh * 4 + 2] = a4.z; vmax[hh * 4 + 3] = a4.w;
+            vcnt[hh * 4 + 0] = c4.x; vcnt[hh * 4 + 1] = c4.y; vcnt[hh * 4 + 2] = c4.z; vcnt[hh * 4 + 3] = c4.w;
           }
-          int32_t incl = cnt;
+          int32_t m = INT32_MIN;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (lane * 8 + j >= nsegT) vmax[j] = INT32_MIN;
+            m = max(m, vmax[j]);
+          }
+          gmax0 = warp_max(m);
+          int32_t suf[8];  // holders in this lane's segments j..7
+          int32_t run = 0;
+#pragma unroll
+          for (int j = 7; j >= 0; --j) {
+            run += vmax[j] == gmax0 ? vcnt[j] : 0;
+            suf[j] = run;
+          }
+          int32_t incl = run;  // + the lanes above
 #pragma unroll
           for (int d = 1; d < 32; d <<= 1) {
-            const int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
+            const int32_t t = __shfl_down_sync(0xffffffffu, incl, d);
+            if (lane + d < 32) incl += t;
           }
+          const int32_t above = incl - run;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (lane * 8 + j < nsegT) cum[lane * 8 + j] = above + suf[j];
+          carry = __shfl_sync(0xffffffffu, incl, 0);
+        } else {
+          int32_t m = INT32_MIN;
+          for (int i = lane; i < nsegT; i += 32) {
+            const int q = MULTI ? min(R - 1, i / sps) : 0;
+            const KsbPeer& P = PEER(q);
+            const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + (i - P.seg_base));
+            cum[i] = v;
+            m = max(m, v);
+          }
+          gmax0 = warp_max(m);
           __syncwarp();
-          if (i >= 0) cum[i] = carry + incl;
-          carry += __shfl_sync(0xffffffffu, incl, 31);
+          for (int top = nsegT; top > 0; top -= 32) {
+            const int i = top - 1 - lane;  // lane 0 = highest segment
+            int32_t cnt = 0;
+            if (i >= 0 && cum[i] == gmax0) {
+              const int q = MULTI ? min(R - 1, i / sps) : 0;
+              const KsbPeer& P = PEER(q);
+              cnt = __ldcv(P.seg_cnt + (half + g) * P.nseg + (i - P.seg_base));
+            }
+            int32_t incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+              const int32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+              if (lane >= d) incl += t;
+            }
+            __syncwarp();
+            if (i >= 0) cum[i] = carry + incl;
+            carry += __shfl_sync(0xffffffffu, incl, 31);
+          }
         }
         if (lane == 0) {
           s_gmax0[g] = gmax0;
@@ -1493,15 +1629,34 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         }
       }
       __syncthreads();
+      long long t3_mark = 0;
+      if (tid == 0) {  // phase-3 breakdown (ksb_stats.stage_cycles[7..11]): rounds, window pods, one-pod-path pods, set-up and deciding cycles
+        t3_mark = clock64();
+        s_tk[14] += t3_mark - s_tk[8];
+      }
+#if KSB_FINE_TIMING
+      long long f3_mark = clock64();
+#define KSB_F3(i)                         \
+  do {                                    \
+    if (tid == 0) {                       \
+      const long long now_ = clock64();   \
+      s_tk[16 + (i)] += now_ - f3_mark;   \
+      f3_mark = now_;                     \
+    }                                     \
+  } while (0)
+#else
+#define KSB_F3(i) ((void)0)
+#endif
 #define KSB_BAR3() asm volatile("bar.sync 1, %0;" ::"n"(kDeciders * 32) : "memory")
       if (warp < kDeciders) {
         int f = 0;          // pods decided so far
-        int wcap = kDeciders;  // window size: grows while whole windows come out right
         const uint64_t L0 = last_index;
         while (f < Gc) {
           const uint32_t special = s_special;
           const int ncr = s_ncr;
+          KSB_F3(0);
           KSB_BAR3();  // everyone holds this round's view before anyone changes it
+          KSB_F3(1);
           if ((special >> f) & 1u) {
             // ================= one pod, exact (warp 0) =================
             if (warp == 0) {
@@ -1606,7 +1761,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   __syncwarp();
                 } else if (nm.fit_count == 1) {
                   // generic_scheduler.go:144-146: no selectHost, counter untouched
-                  chosen_rank = min(R - 1, (nm.one_row / kSeg) / sps);
+                  chosen_rank = MULTI ? min(R - 1, (nm.one_row / kSeg) / sps) : 0;
                   chosen = nm.one_row - PEER(chosen_rank).table.row_base;
                 } else {
                   // (2) selectHost (generic_scheduler.go:177-192): lastNodeIndex % k over the rows tied at the maximum,
@@ -1642,7 +1797,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                       const int ent = select_merged(Am, Dm, rem, S.r0 + g * kCache, s_erow, &q);
                       int grow = ent >= 0 ? s_erow[ent] : select_snapshot(g, q);
                       if (grow >= 0) {
-                        pick_rank = min(R - 1, (grow / kSeg) / sps);
+                        pick_rank = MULTI ? min(R - 1, (grow / kSeg) / sps) : 0;
                         pick = grow - PEER(pick_rank).table.row_base;
                       }
                     }
@@ -1748,8 +1903,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
               if (cut && lane == 0) s_cut = 1;
             }
+            KSB_F3(7);
             KSB_BAR3();
             if (s_cut) break;
+            if (tid == 0) s_tk[13] += 1;
             f += 1;
             continue;
           }
@@ -1786,7 +1943,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             const uint32_t bm = __ballot_sync(0xffffffffu, bad);
             if (lane == 0) s_bad0 = bm;  // these pods go to the serial path (which ends the group if it must)
           }
+          KSB_F3(2);
           KSB_BAR3();
+          KSB_F3(1);
           // (2) per pick: its row after the assume step, and that row against the later pods
           for (int w = warp; w < W; w += kDeciders) {
             const int g = f + w;
@@ -1800,11 +1959,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             }
             const KsbPodHeader* h = S.hdr + g;
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
-            const int erank = min(R - 1, (e / kSeg) / sps);
+            const int erank = MULTI ? min(R - 1, (e / kSeg) / sps) : 0;
             const KsbPeer& P = PEER(erank);
             const int lrow = e - P.table.row_base;
             const uint32_t hit = __ballot_sync(0xffffffffu, lane < ncr && s_erow[lane] == e);
             const int idx = hit ? __ffs(hit) - 1 : -1;
+            const ColIn cin = col_issue(erank, lrow, g + 1);
             RowCache* pc = S.post + w;
             if (idx >= 0) {
               const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + idx);
@@ -1851,7 +2011,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             }
             __syncwarp();
             uint32_t nm_, sm_, xm_;
-            column_pass(*pc, g + 1, &nm_, &sm_, &xm_, S.t_r0 + w * kMaxG);
+            col_eval(*pc, cin, &nm_, &sm_, &xm_, S.t_r0 + w * kMaxG);
             // later pods of the window whose pick assumed this row's standing unchanged, and were wrong (or chose the
             // same row, whose copy here lacks this pod)
             bool dirty = false;
@@ -1872,7 +2032,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               t_idx[w] = idx;
             }
           }
+          KSB_F3(3);
           KSB_BAR3();
+          KSB_F3(4);
           // (3) how many of the window's pods are final
           int n_ok;
           uint32_t newmask;
@@ -1904,11 +2066,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             s_ncr = ncr + __popc(newmask);
             if (s_bad0) atomicOr(const_cast<uint32_t*>(&s_special), s_bad0 << f);
           }
-          wcap = n_ok == W ? min(32, wcap * 2) : max(kDeciders, min(32, n_ok + 2));
+          // whole windows came out right: widen; else as many deciding warps' worth as the run of right pods suggests
+          wcap = n_ok == W ? min(32, wcap + kDeciders) : (n_ok < kDeciders ? kDeciders : 2 * kDeciders);
+          if (tid == 0) {
+            s_tk[11] += 1;
+            s_tk[12] += n_ok;
+          }
           f += n_ok;
+          KSB_F3(5);
           KSB_BAR3();
+          KSB_F3(1);
         }
         if (tid == 0) {
+          s_tk[15] += clock64() - t3_mark;
           s_consumed = f;
           last_index = L0 + (uint64_t)(f < Gc ? s_lrel[f] : s_lrel[Gc - 1] + ((s_prio >> (Gc - 1)) & 1u));
           __threadfence_block();
@@ -2038,6 +2208,15 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   if (b == 0 && tid == 0) {
     if (multi) *A.xstate = xepoch;
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[i];  // block 0's cycles per stage
+    for (int i = 0; i < 5; ++i) A.counters[9 + i] = (uint64_t)s_tk[11 + i];  // phase-3 breakdown
+#if KSB_FINE_TIMING
+    // instead: cycles of thread 0 in phase 3 by step: picks, own columns, wait for the other columns, finalize, one-pod path
+    A.counters[9] = (uint64_t)s_tk[18];
+    A.counters[10] = (uint64_t)s_tk[19];
+    A.counters[11] = (uint64_t)(s_tk[20] + s_tk[17]);
+    A.counters[12] = (uint64_t)s_tk[21];
+    A.counters[13] = (uint64_t)s_tk[23];
+#endif
     if (A.rank == 0) {
       A.counters[0] = (uint64_t)s_tk[9];
       A.counters[1] = (uint64_t)s_tk[10];
