@@ -763,8 +763,9 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
 }
 
-// One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads).
-__device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCache* c, int lane) {
+// One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads). In two steps, so
+// that a warp filling two entries has both rows' loads in flight before it consumes either.
+__device__ __forceinline__ void cache_fill_issue(const KsbNodeTable& T, int r, int lane, int64_t* v_out, uint32_t* v2_out) {
   const size_t np = T.n_pad;
   // columns of one family are consecutive, n_pad apart, in the order of q[] (device_types.h): lanes 0..17 the
   // int64 family from alloc_cpu on, lanes 18..29 the twelve port words, lane 30 preferAvoid (the column before them)
@@ -776,12 +777,22 @@ __device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCach
   uint32_t v2 = 0;
   if (lane < 31) v = __ldcg(p);
   if (lane < 4 + KSB_MAX_RES) v2 = __ldcg(p2);
+  *v_out = v;
+  *v2_out = v2;
+}
+__device__ __forceinline__ void cache_fill_store(RowCache* c, int r, int lane, int64_t v, uint32_t v2) {
   if (lane < 31) c->q[lane] = v;
   // apods, npods, flags, zone, avail[0..1] are consecutive 32-bit fields of the entry
   if (lane < 4 + KSB_MAX_RES) reinterpret_cast<uint32_t*>(&c->apods)[lane] = v2;
   if (lane == 31) c->row = r;
   if (lane >= 24 && lane < 24 + KSB_MAX_EXT) c->mid[lane - 24] = 0;
   if (lane < 2) c->rcp[lane] = fast_rcp((double)v);
+}
+__device__ __forceinline__ void cache_fill(const KsbNodeTable& T, int r, RowCache* c, int lane) {
+  int64_t v;
+  uint32_t v2;
+  cache_fill_issue(T, r, lane, &v, &v2);
+  cache_fill_store(c, r, lane, v, v2);
 }
 
 // What the decider warp hands to the writer warp for one pod: the chosen row's mutable columns after the
@@ -1058,8 +1069,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   }
   // measurement state lives in shared memory (thread 0 of each block updates it; block 0's copy is reported): kept
   // in registers it would cost every thread of the kernel some thirty of them
-  __shared__ long long s_tk[24];  // [0..7] cycles per stage, [8] time mark, [9] groups, [10] groups cut short
-  if (tid < 24) s_tk[tid] = 0;
+  __shared__ long long s_tk[40];  // [0..7] cycles per stage, [8] time mark, [9] groups, [10] groups cut short
+  if (tid < 40) s_tk[tid] = 0;
   if (tid == 0) s_ncr = 0;
   __syncthreads();
   if (tid == 0) s_tk[8] = clock64();
@@ -1398,10 +1409,14 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         uint4 m0, m1;
         bool act, seg_holds;
       };
-      auto col_issue = [&](int prank, int crow, int g_from) -> ColIn {
+      // Groups of up to 16 pods (always so when pipelined) run two columns per pass: lanes 0..15 the pods on one
+      // row, lanes 16..31 the same pods on another. `g` is the lane's pod, `valid` whether its column exists.
+      // (kept off: with the pipelined schedule two-column passes gave placements that changed from run to run, about
+      // one run in forty, and no measurable gain; one column per pass is what scripts/repeat_check.py runs clean)
+      constexpr bool dual = false;
+      auto col_issue = [&](bool valid, int prank, int crow, int g, int g_from) -> ColIn {
         ColIn in;
-        const int g = lane;
-        in.act = g >= g_from && g < Gc && ((s_prio >> g) & 1u);
+        in.act = valid && g >= g_from && g < Gc && ((s_prio >> g) & 1u);
         in.base0 = INT32_MIN;
         in.score0 = 0;
         in.reasons0 = 0;
@@ -1428,17 +1443,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         }
         return in;
       };
-      auto col_eval = [&](RowCache& c, const ColIn& in, uint32_t* now_m, uint32_t* snap_m, uint32_t* spec_m, int32_t* r0_out) {
-        const int g = lane;
-        bool bit_now = false, bit_snap = false, spec = false;
+      // per lane: its pod on its column's row; the callers ballot the three outcomes
+      auto col_eval = [&](RowCache* c, const ColIn& in, int g, int32_t* r0_out, bool* bit_now, bool* bit_snap, bool* spec) {
+        *bit_now = false;
+        *bit_snap = false;
+        *spec = false;
         if (in.act) {
           const KsbPodHeader* h = S.hdr + g;
           const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
-          const KsbPeer& P = PEER(c.pad & 0xff);
+          const KsbPeer& P = PEER(c->pad & 0xff);
           int32_t r0v = in.above;
           if (in.seg_holds) {
             const uint32_t w[kWarps] = {in.m0.x, in.m0.y, in.m0.z, in.m0.w, in.m1.x, in.m1.y, in.m1.z, in.m1.w};
-            const int rel = c.row % kSeg;
+            const int rel = c->row % kSeg;
             const int wi0 = rel >> 5;
 #pragma unroll
             for (int wi = 0; wi < kWarps; ++wi) {
@@ -1449,23 +1466,25 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           r0_out[g] = r0v;
           uint32_t new_reasons;
           int32_t base;
-          eval_cached(P.table, c, pv, in.reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
+          eval_cached(P.table, *c, pv, in.reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
           const bool was_fit = in.base0 != INT32_MIN;
           const int32_t gm = s_gmax0[g];
           const int32_t cold = was_fit ? in.score0 : INT32_MIN;
           const int32_t cnew =
               (was_fit && new_reasons == 0) ? (int32_t)((uint32_t)cold - (uint32_t)in.base0 + (uint32_t)base) : INT32_MIN;
-          bit_snap = cold == gm;
-          bit_now = cnew == gm;
-          spec = (was_fit && new_reasons != 0) || cnew > gm;
+          *bit_snap = cold == gm;
+          *bit_now = cnew == gm;
+          *spec = (was_fit && new_reasons != 0) || cnew > gm;
         }
-        *now_m = __ballot_sync(0xffffffffu, bit_now);
-        *snap_m = __ballot_sync(0xffffffffu, bit_snap);
-        *spec_m = __ballot_sync(0xffffffffu, spec);
       };
+      // one column, one pod per lane
       auto column_pass = [&](RowCache& c, int g_from, uint32_t* now_m, uint32_t* snap_m, uint32_t* spec_m, int32_t* r0_out) {
-        const ColIn in = col_issue(c.pad & 0xff, c.row, g_from);
-        col_eval(c, in, now_m, snap_m, spec_m, r0_out);
+        const ColIn in = col_issue(true, c.pad & 0xff, c.row, lane, g_from);
+        bool bn, bs, sp;
+        col_eval(&c, in, lane, r0_out, &bn, &bs, &sp);
+        *now_m = __ballot_sync(0xffffffffu, bn);
+        *snap_m = __ballot_sync(0xffffffffu, bs);
+        *spec_m = __ballot_sync(0xffffffffu, sp);
       };
       // make a column pass's outcome part of the later pods' state, as cache entry `t`
       auto apply_column = [&](int t, int g_from, bool is_new, uint32_t now_m, uint32_t snap_m, uint32_t spec_m, const int32_t* r0_src) {
@@ -1483,6 +1502,42 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         if (lane == 0 && spec_m) atomicOr(const_cast<uint32_t*>(&s_special), spec_m);
       };
 
+      {
+        // Rows in the cache. Pipelined: this group was evaluated before the previous group's rows reached the
+        // table, so those rows (tagged with that group's number) stay in the cache and count as changed from the
+        // first pod on; older entries are dropped. All warps: read the kept entries that move, then write them.
+        const int have = s_ncr;
+        const int prev = cm_gid - 1;
+        const bool keep = pipe && cm_carry && lane < have && (S.rows[lane].pad >> 8) == prev;
+        const uint32_t km = __ballot_sync(0xffffffffu, keep);
+        constexpr int kWordsPerRow = (int)(sizeof(RowCache) / 4);
+        static_assert(kWordsPerRow <= 96 && kCache <= 4 * kWarps, "an entry is moved by one warp in three words per lane");
+        uint32_t mv[4][3];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int i = warp + j * kWarps;
+          if ((km >> i) & 1u) {
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + i);
+#pragma unroll
+            for (int x = 0; x < 3; ++x) mv[j][x] = lane + 32 * x < kWordsPerRow ? src[lane + 32 * x] : 0u;
+          }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int i = warp + j * kWarps;
+          if ((km >> i) & 1u) {
+            const int d = __popc(km & ((1u << i) - 1u));
+            uint32_t* dst = reinterpret_cast<uint32_t*>(S.rows + d);
+#pragma unroll
+            for (int x = 0; x < 3; ++x)
+              if (lane + 32 * x < kWordsPerRow) dst[lane + 32 * x] = mv[j][x];
+          }
+        }
+        if (tid == 0) s_ncr = __popc(km);
+        __syncthreads();
+        if (warp == 0 && lane < __popc(km)) s_erow[lane] = PEER(S.rows[lane].pad & 0xff).table.row_base + S.rows[lane].row;
+      }
       // Per pod ranked by score, one pod per warp: the maximum over all segments, and per segment the number of
       // rows holding it in this and all higher segments (suffix counts; entry 0 is the pod's tie count k0).
       for (int g = warp; g < Gc; g += kWarps) {
@@ -1596,36 +1651,30 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           s_stop = -1;
           s_cut = 0;
         }
-        // Rows in the cache. Pipelined: this group was evaluated before the previous group's rows reached the
-        // table, so those rows (tagged with that group's number) stay in the cache and count as changed from the
-        // first pod on; older entries are dropped.
-        int ncr = 0;
-        if (pipe && cm_carry) {
-          const int prev = cm_gid - 1;
-          const int have = s_ncr;
-          for (int i = 0; i < have; ++i) {
-            if ((S.rows[i].pad >> 8) == prev) {
-              if (ncr != i) {
-                const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + i);
-                uint32_t* dst = reinterpret_cast<uint32_t*>(S.rows + ncr);
-                for (int w = lane; w < (int)(sizeof(RowCache) / 4); w += 32) dst[w] = src[w];
-              }
-              ncr += 1;
-            }
-            __syncwarp();
-          }
-        }
-        if (lane < ncr) s_erow[lane] = PEER(S.rows[lane].pad & 0xff).table.row_base + S.rows[lane].row;
-        if (lane == 0) s_ncr = ncr;
       }
       __syncthreads();
       {  // carried rows: their column pass against this group's pods
         const int ncr = s_ncr;
-        for (int i = warp; i < ncr; i += kWarps) {
-          uint32_t nm_, sm_, xm_;
-          column_pass(S.rows[i], 0, &nm_, &sm_, &xm_, S.t_r0 + i * kMaxG);
-          __syncwarp();
-          apply_column(i, 0, true, nm_, sm_, xm_, S.t_r0 + i * kMaxG);
+        if (dual) {
+          for (int i = warp * 2; i < ncr; i += kWarps * 2) {
+            const int sub = lane >> 4, g = lane & 15;
+            const bool valid = i + sub < ncr;
+            RowCache* c = S.rows + (valid ? i + sub : i);
+            const ColIn in = col_issue(valid, c->pad & 0xff, c->row, g, 0);
+            bool bn, bs, sp;
+            col_eval(c, in, g, S.t_r0 + (i + sub) * kMaxG, &bn, &bs, &sp);
+            const uint32_t nm_ = __ballot_sync(0xffffffffu, bn), sm_ = __ballot_sync(0xffffffffu, bs), xm_ = __ballot_sync(0xffffffffu, sp);
+            __syncwarp();
+            apply_column(i, 0, true, nm_ & 0xffffu, sm_ & 0xffffu, xm_ & 0xffffu, S.t_r0 + i * kMaxG);
+            if (i + 1 < ncr) apply_column(i + 1, 0, true, nm_ >> 16, sm_ >> 16, xm_ >> 16, S.t_r0 + (i + 1) * kMaxG);
+          }
+        } else {
+          for (int i = warp; i < ncr; i += kWarps) {
+            uint32_t nm_, sm_, xm_;
+            column_pass(S.rows[i], 0, &nm_, &sm_, &xm_, S.t_r0 + i * kMaxG);
+            __syncwarp();
+            apply_column(i, 0, true, nm_, sm_, xm_, S.t_r0 + i * kMaxG);
+          }
         }
       }
       __syncthreads();
@@ -1644,8 +1693,23 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       f3_mark = now_;                     \
     }                                     \
   } while (0)
+#define KSB_G(i)                          \
+  do {                                    \
+    if (tid == 0) {                       \
+      const long long now_ = clock64();   \
+      s_tk[24 + (i)] += now_ - g3_mark;   \
+      g3_mark = now_;                     \
+    }                                     \
+  } while (0)
+#define KSB_G0()                          \
+  do {                                    \
+    if (tid == 0) g3_mark = clock64();    \
+  } while (0)
+      long long g3_mark = 0;
 #else
 #define KSB_F3(i) ((void)0)
+#define KSB_G(i) ((void)0)
+#define KSB_G0() ((void)0)
 #endif
 #define KSB_BAR3() asm volatile("bar.sync 1, %0;" ::"n"(kDeciders * 32) : "memory")
       if (warp < kDeciders) {
@@ -1923,6 +1987,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           if (warp == 0) {
             int pick = -1;
             bool bad = false;
+            KSB_G0();
             if (lane < W) {
               const int g = f + lane;
               const uint32_t sn = s_snap[g], nw = s_now[g];
@@ -1934,103 +1999,147 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                 const uint64_t last_g = L0 + (uint64_t)s_lrel[g];
                 const int rem = (last_g >> 32) == 0 ? (int)((uint32_t)last_g % (uint32_t)k) : (int)(last_g % (uint64_t)k);
                 int q = 0;
+                __syncwarp(__activemask());
+                KSB_G(0);
                 const int ent = select_merged(Am, Dm, rem, S.r0 + g * kCache, s_erow, &q);
+                __syncwarp(__activemask());
+                KSB_G(1);
                 pick = ent >= 0 ? s_erow[ent] : select_snapshot(g, q);
                 if (pick < 0) bad = true;
               }
               s_pick[lane] = pick;
             }
+            __syncwarp();
+            KSB_G(2);
             const uint32_t bm = __ballot_sync(0xffffffffu, bad);
             if (lane == 0) s_bad0 = bm;  // these pods go to the serial path (which ends the group if it must)
           }
           KSB_F3(2);
           KSB_BAR3();
           KSB_F3(1);
-          // (2) per pick: its row after the assume step, and that row against the later pods
-          for (int w = warp; w < W; w += kDeciders) {
-            const int g = f + w;
-            const int e = s_pick[w];
-            if (e < 0) {
-              if (lane == 0) {
-                t_dirty[w] = 0;
-                t_idx[w] = -2;
-              }
-              continue;
-            }
-            const KsbPodHeader* h = S.hdr + g;
-            const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
-            const int erank = MULTI ? min(R - 1, (e / kSeg) / sps) : 0;
-            const KsbPeer& P = PEER(erank);
-            const int lrow = e - P.table.row_base;
-            const uint32_t hit = __ballot_sync(0xffffffffu, lane < ncr && s_erow[lane] == e);
-            const int idx = hit ? __ffs(hit) - 1 : -1;
-            const ColIn cin = col_issue(erank, lrow, g + 1);
-            RowCache* pc = S.post + w;
-            if (idx >= 0) {
-              const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + idx);
-              uint32_t* dst = reinterpret_cast<uint32_t*>(pc);
-              for (int x = lane; x < (int)(sizeof(RowCache) / 4); x += 32) dst[x] = src[x];
-            } else {
-              cache_fill(P.table, lrow, pc, lane);
-            }
-            __syncwarp();
-            if (lane == 31) pc->pad = erank | (cm_gid << 8);
-            __syncwarp();
-            uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
-            if (h->n_ext) {
-              for (int i = 0; i < h->n_ext; ++i) {
-                const int rs = h->ext[i].rslot;
-                const uint16_t id = h->ext[i].cls_id;
-                if (rs < KSB_MAX_RES && h->ext[i].num > 0 && id != 0 && pc->mid[i] != id) {
-                  const uint32_t cls = P.table.dev_class[((size_t)rs * P.table.n_pad + lrow) * KSB_MAX_DEV + lane];
-                  const uint64_t* cm = pv.extcls + i * KSB_CLASS_WORDS;
-                  const uint32_t match = __ballot_sync(0xffffffffu, ((cm[cls >> 6] >> (cls & 63)) & 1ull) != 0);
-                  if (lane == 0) {
-                    pc->mm[i] = match;
-                    pc->mid[i] = id;
-                  }
+          // (2) per pick: its row after the assume step, and that row against the later pods (two picks per pass
+          //     when the group has at most 16 pods)
+          const int cpw = dual ? 2 : 1;
+          for (int w0 = warp * cpw; w0 < W; w0 += kDeciders * cpw) {
+            // which column this lane evaluates, and its pod
+            const int sub = dual ? (lane >> 4) : 0;
+            const int gl = dual ? (lane & 15) : lane;
+            int my_e = -1, my_idx = -2, my_rank = 0, my_lrow = 0;  // this lane's column
+            int e_[2] = {-1, -1}, idx_[2] = {-2, -2}, rank_[2] = {0, 0}, lrow_[2] = {0, 0};
+#pragma unroll
+            for (int s2 = 0; s2 < 2; ++s2) {
+              const int w = w0 + s2;
+              if (s2 < cpw && w < W) {
+                const int e = s_pick[w];
+                if (e >= 0) {
+                  const int erank = MULTI ? min(R - 1, (e / kSeg) / sps) : 0;
+                  const uint32_t hit = __ballot_sync(0xffffffffu, lane < ncr && s_erow[lane] == e);
+                  e_[s2] = e;
+                  idx_[s2] = hit ? __ffs(hit) - 1 : -1;
+                  rank_[s2] = erank;
+                  lrow_[s2] = e - PEER(erank).table.row_base;
                 }
               }
-              __syncwarp();
-              if (lane == 0) select_devices_cached(P.table, pc, pv, picks);
-#pragma unroll
-              for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+              if (sub == s2) {
+                my_e = e_[s2];
+                my_idx = idx_[s2];
+                my_rank = rank_[s2];
+                my_lrow = lrow_[s2];
+              }
             }
-            CommitRec& rec = S.recs[g];
-            commit_and_record(pc, &rec, pv, picks, lrow, erank, lane);
-            if (lane == 0) {
-              KsbResult res;
-              res.status = 0;
-              res.row = e;
-              res.num_filtered = S.norm[g].fit_count;
-              res.fiterr_slot = -1;
-              res.score = s_gmax0[g];
+            const int my_w = w0 + sub;
+            KSB_G0();
+            const ColIn cin = col_issue(my_e >= 0, my_rank, my_lrow, gl, f + my_w + 1);
+            KSB_G(3);
+            int64_t fv[2] = {0, 0};
+            uint32_t fv2[2] = {0, 0};
 #pragma unroll
-              for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
-              rec.res = res;
+            for (int s2 = 0; s2 < 2; ++s2)  // rows not in the cache yet: both fetches in flight together
+              if (s2 < cpw && w0 + s2 < W && e_[s2] >= 0 && idx_[s2] < 0)
+                cache_fill_issue(PEER(rank_[s2]).table, lrow_[s2], lane, &fv[s2], &fv2[s2]);
+#pragma unroll
+            for (int s2 = 0; s2 < 2; ++s2) {
+              const int w = w0 + s2;
+              if (!(s2 < cpw && w < W)) continue;
+              const int e = e_[s2];
+              if (e < 0) continue;
+              const int g = f + w;
+              const int idx = idx_[s2], erank = rank_[s2], lrow = lrow_[s2];
+              const KsbPodHeader* h = S.hdr + g;
+              const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+              const KsbPeer& P = PEER(erank);
+              RowCache* pc = S.post + w;
+              if (idx >= 0) {
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(S.rows + idx);
+                uint32_t* dst = reinterpret_cast<uint32_t*>(pc);
+                for (int x = lane; x < (int)(sizeof(RowCache) / 4); x += 32) dst[x] = src[x];
+              } else {
+                cache_fill_store(pc, lrow, lane, fv[s2], fv2[s2]);
+              }
+              __syncwarp();
+              if (lane == 31) pc->pad = erank | (cm_gid << 8);
+              __syncwarp();
+              uint32_t picks[KSB_MAX_EXT] = {0, 0, 0, 0};
+              if (h->n_ext) {
+                for (int i = 0; i < h->n_ext; ++i) {
+                  const int rs = h->ext[i].rslot;
+                  const uint16_t id = h->ext[i].cls_id;
+                  if (rs < KSB_MAX_RES && h->ext[i].num > 0 && id != 0 && pc->mid[i] != id) {
+                    const uint32_t cls = P.table.dev_class[((size_t)rs * P.table.n_pad + lrow) * KSB_MAX_DEV + lane];
+                    const uint64_t* cm = pv.extcls + i * KSB_CLASS_WORDS;
+                    const uint32_t match = __ballot_sync(0xffffffffu, ((cm[cls >> 6] >> (cls & 63)) & 1ull) != 0);
+                    if (lane == 0) {
+                      pc->mm[i] = match;
+                      pc->mid[i] = id;
+                    }
+                  }
+                }
+                __syncwarp();
+                if (lane == 0) select_devices_cached(P.table, pc, pv, picks);
+#pragma unroll
+                for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
+              }
+              CommitRec& rec = S.recs[g];
+              commit_and_record(pc, &rec, pv, picks, lrow, erank, lane);
+              if (lane == 0) {
+                KsbResult res;
+                res.status = 0;
+                res.row = e;
+                res.num_filtered = S.norm[g].fit_count;
+                res.fiterr_slot = -1;
+                res.score = s_gmax0[g];
+#pragma unroll
+                for (int i = 0; i < KSB_MAX_EXT; ++i) res.device_mask[i] = picks[i];
+                rec.res = res;
+              }
             }
             __syncwarp();
-            uint32_t nm_, sm_, xm_;
-            col_eval(*pc, cin, &nm_, &sm_, &xm_, S.t_r0 + w * kMaxG);
+            KSB_G(4);
+            bool bn, bs, sp;
+            col_eval(S.post + my_w, cin, gl, S.t_r0 + my_w * kMaxG, &bn, &bs, &sp);
+            __syncwarp();
+            KSB_G(5);
             // later pods of the window whose pick assumed this row's standing unchanged, and were wrong (or chose the
             // same row, whose copy here lacks this pod)
             bool dirty = false;
-            {
-              const int g2 = lane;
-              if (g2 > g && g2 < f + W) {
-                const bool used = idx >= 0 ? ((s_now[g2] >> idx) & 1u) != 0 : ((sm_ >> g2) & 1u) != 0;
-                const bool now = ((nm_ >> g2) & 1u) != 0;
-                dirty = ((xm_ >> g2) & 1u) != 0 || now != used || s_pick[g2 - f] == e;
-              }
+            if (my_e >= 0 && gl > f + my_w && gl < f + W) {
+              const bool used = my_idx >= 0 ? ((s_now[gl] >> my_idx) & 1u) != 0 : bs;
+              dirty = sp || bn != used || s_pick[gl - f] == my_e;
             }
-            const uint32_t dm = __ballot_sync(0xffffffffu, dirty);
-            if (lane == 0) {
-              t_dirty[w] = dm;
-              t_now[w] = nm_;
-              t_snap[w] = sm_;
-              t_spec[w] = xm_;
+            const uint32_t nm_ = __ballot_sync(0xffffffffu, bn), sm_ = __ballot_sync(0xffffffffu, bs);
+            const uint32_t xm_ = __ballot_sync(0xffffffffu, sp), dm = __ballot_sync(0xffffffffu, dirty);
+            if (lane < cpw && w0 + lane < W) {
+              const int w = w0 + lane;
+              const int sh = dual ? 16 * lane : 0;
+              const uint32_t keep = dual ? 0xffffu : 0xffffffffu;
+              const int idx = lane == 0 ? idx_[0] : idx_[1];
+              t_dirty[w] = idx == -2 ? 0u : (dm >> sh) & keep;
+              t_now[w] = (nm_ >> sh) & keep;
+              t_snap[w] = (sm_ >> sh) & keep;
+              t_spec[w] = (xm_ >> sh) & keep;
               t_idx[w] = idx;
             }
+            KSB_G(6);
           }
           KSB_F3(3);
           KSB_BAR3();
@@ -2216,6 +2325,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     A.counters[11] = (uint64_t)(s_tk[20] + s_tk[17]);
     A.counters[12] = (uint64_t)s_tk[21];
     A.counters[13] = (uint64_t)s_tk[23];
+    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[24 + i];  // granular: picks 0-2, columns 3-6
 #endif
     if (A.rank == 0) {
       A.counters[0] = (uint64_t)s_tk[9];

@@ -17,6 +17,7 @@ for g in sizes:
                       "replay_ms": round(out["replay_ms"], 2), "us_per_pod": round(1000 * out["replay_ms"] / pods, 2),
                       "groups": out["groups"], "restarts": out["group_restarts"], "encode_ms": round(out["encode_ms"], 1),
                       "e2e_ms": round(out["e2e_ms"], 1), "decode_ms": round(out["decode_ms"], 1), "post_ms": round(out["post_ms"], 1), "sync_ms": round(out["sync_ms"], 1), "hash": out["placement_hash"][-6:],
+                      "raw_us_per_pod": [round(c / 1965.0 / pods, 3) for c in out["stage_cycles"][:12]],
                       "stage_us_per_pod": [round(c / 1965.0 / pods, 3) for c in out["stage_cycles"][:7]],
                       "p3": {"rounds": out["stage_cycles"][7], "window_pods": out["stage_cycles"][8], "one_pod_path": out["stage_cycles"][9],
                              "setup_us_per_pod": round(out["stage_cycles"][10] / 1965.0 / pods, 3),

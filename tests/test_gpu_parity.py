@@ -107,6 +107,21 @@ def test_pipelined_is_repeatable(cfg, nodes, pods):
     sess.close()
 
 
+def test_pipelined_stress_many_runs():
+    """Sixty pipelined runs at two group sizes: a data race between the deciding warps, the writer warp and the
+    evaluating blocks shows up as a placement that changes from run to run (it did, once, during development)."""
+    cluster = workloads.generate(3, 700, 3000)
+    sess = lib.Session(cluster=cluster)
+    base = sess.run(results=False, pipeline=-1, group_size=32)
+    bad = 0
+    for _ in range(60):
+        for g in (4, 16):
+            out = sess.run(results=False, pipeline=1, group_size=g)
+            bad += (out["placement_hash"], out["lastNodeIndex"]) != (base["placement_hash"], base["lastNodeIndex"])
+    sess.close()
+    assert bad == 0
+
+
 def test_chunked_batch_matches_single_launches():
     """Batches of 8,192 pods or more go to the device in chunks overlapped with host work; the placements must be
     those of one launch (the replay runs the whole batch in a single launch and is compared pod by pod) and of
