@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstring>
+#include <future>
 #include <stdexcept>
 #include <unordered_set>
 
@@ -577,7 +578,8 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
       apply_node_part_host(r.row, last_encoded[i], r.device_mask);
       apply_class_part_host(r.row, last_encoded[i].commits, last_encoded[i].spread_inc, +1);
       host_add_pod(p, hn);
-      pods[p.key()] = HostPod{p};
+      std::string key = p.key();
+      pods[std::move(key)] = HostPod{std::move(p)};  // the batch is the caller's scratch copy: its pods move into the cache
     }
     post_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
   };
@@ -590,6 +592,15 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   bounds(0, &c0, &c1);
   encode_chunk(c0, c1, 0);
   launch_chunk(c0, c1, 0);
+  // Chunked batches mirror the placements of chunk c on a second host thread while this one encodes chunk c+2 (and
+  // the device runs chunk c+1). The two touch disjoint state: the mirror thread writes the request / port columns
+  // of the host table, the class counters' values, the per-node records and the pod cache; the encoder reads the
+  // dictionaries, the class registry's static fields and node rows, and writes label columns only. Mirror tasks
+  // run strictly one after another.
+  std::future<void> mirror;
+  auto join_mirror = [&] {
+    if (mirror.valid()) mirror.get();  // rethrows what the task threw
+  };
   try {
     for (int c = 0; c < n_chunks; ++c) {
       bounds(c, &c0, &c1);
@@ -600,9 +611,19 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
       }
       wait_chunk(c0, c1);
       if (more) launch_chunk(n0, n1, (c + 1) & 1);
-      post_chunk(c0, c1);  // next to the kernel of chunk c+1
+      join_mirror();
+      if (more) {
+        const int m0 = c0, m1 = c1;
+        mirror = std::async(std::launch::async, [&post_chunk, m0, m1] { post_chunk(m0, m1); });  // next to the kernel of chunk c+1
+      } else {
+        post_chunk(c0, c1);
+      }
     }
   } catch (...) {
+    try {
+      join_mirror();
+    } catch (...) {
+    }
     // A limit met while encoding a later chunk (label universe, expression or pool caps) or a device error: a kernel
     // may be in flight and the device table may hold commits the host records do not. Drain the stream and have the
     // table rebuilt from the host records, which hold exactly the chunks posted so far (reported in `out`).

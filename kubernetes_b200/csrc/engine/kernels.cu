@@ -67,6 +67,7 @@ constexpr int kMaxPoolWords = 1024;   // pool words one pod may use (checked on 
 constexpr int kGroupPoolWords = 4096; // pool words staged per group
 constexpr int kSegCache = KSB_SEG_CACHE;  // (pods in group) x (segments) entries of segment stats kept in shared memory
 constexpr int kCache = 32;            // row-cache entries (one lane each)
+constexpr bool kHoldTableWrites = false;  // pipelined schedule: see the writer warp
 constexpr int kDeciders = kWarps - 1; // phase 3: warps that decide; the last warp writes the table through
 
 template <bool CG, typename V>
@@ -2212,8 +2213,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           const KsbPodHeader* h = S.hdr + g;
           if (lane < R) PEER(lane).results[p0 + g] = rec.res;  // every rank keeps a copy of the results
           if (rec.row >= 0) {
-            if (pipe && !table_open) {
-              // pipelined: the evaluation side is still reading the table until every block has passed barrier 1
+            // Pipelined: the other blocks may be reading the table for the next group while these rows are written.
+            // That is harmless: every row written here stays in the row cache for that group (the carried rows), so
+            // phase 3 re-evaluates it from the cache and only uses the group-start results on it to take its
+            // contribution to the Reduce inputs and tie counts back out, which works for whatever mix of old and new
+            // columns the evaluation happened to read: requests only grow, so a mix fits whenever the new row does.
+            // (kHoldTableWrites keeps the conservative schedule: no write before every block has read the table.)
+            if (kHoldTableWrites && pipe && !table_open) {
               if (lane == 0) spin_until<false>(A, A.barrier, s_b1_target, 7);
               __syncwarp();
               table_open = true;
