@@ -9,6 +9,8 @@
 
 namespace ksb {
 
+thread_local bool Engine::tl_readonly = false;
+
 #define CUDA_OK(call)                                                                          \
   do {                                                                                         \
     cudaError_t e_ = (call);                                                                   \
@@ -120,6 +122,7 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
   k += join3(key, value, kind == 'G' || kind == 'L' ? std::to_string(num) : std::string());
   auto it = label_bits.find(k);
   if (it != label_bits.end()) return it->second;
+  will_mutate();
   int bit = (int)label_defs.size();
   if (bit >= W * 64)
     throw std::runtime_error("label universe exceeds label_words*64 bits; create the engine with a larger label_words");
@@ -145,11 +148,8 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
       if (it2 != rows_by_key.end())
         for (auto& rv : it2->second) {
           bool on = true;
-          if (kind != 'K') {  // 'G' / 'L' (selector.go:214-233)
-            int64_t v;
-            on = sel::to_int64(*rv.second, &v) && (kind == 'G' ? v > num : v < num);
-          }
-          if (on) u64(bit >> 6, rv.first) |= m;
+          if (kind != 'K') on = rv.is_num && (kind == 'G' ? rv.num > num : rv.num < num);  // 'G' / 'L' (selector.go:214-233)
+          if (on) u64(bit >> 6, rv.row) |= m;
         }
     }
     dirty_label_words.insert(bit >> 6);
@@ -166,7 +166,11 @@ void Engine::build_label_index() {
       pk.push_back('\0');
       pk += kv.second;
       rows_by_pair[pk].push_back(r);
-      rows_by_key[kv.first].emplace_back(r, &kv.second);
+      KeyRow kr;
+      kr.row = r;
+      kr.num = 0;
+      kr.is_num = sel::to_int64(kv.second, &kr.num);
+      rows_by_key[kv.first].push_back(kr);
     }
   label_index_valid = true;
 }
@@ -174,6 +178,7 @@ void Engine::build_label_index() {
 int Engine::topo_key(const std::string& key) {
   auto it = topo_idx.find(key);
   if (it != topo_idx.end()) return it->second;
+  will_mutate();
   int k = (int)topo_keys.size();
   if (k >= KSB_MAX_TOPO) throw std::runtime_error("more than KSB_MAX_TOPO distinct topology keys");
   topo_keys.push_back(key);
@@ -205,6 +210,7 @@ int Engine::topo_domain(int k, const Node& nd) {  // priorities/util/topologies.
 int Engine::scalar_slot(const std::string& name) {
   auto it = scalar_idx.find(name);
   if (it != scalar_idx.end()) return it->second;
+  will_mutate();
   int s = (int)scalar_names.size();
   if (s >= KSB_MAX_SCALARS) throw std::runtime_error("more than KSB_MAX_SCALARS distinct scalar resource names");
   scalar_names.push_back(name);
@@ -215,6 +221,7 @@ int Engine::scalar_slot(const std::string& name) {
 int Engine::port_bit(const std::string& proto_port) {
   auto it = port_slot.find(proto_port);
   if (it != port_slot.end()) return it->second;
+  will_mutate();
   int b = (int)port_slot.size();
   if (b >= KSB_PORT_WORDS * 64) throw std::runtime_error("more than 256 distinct protocol/hostPort pairs");
   port_slot[proto_port] = b;
@@ -223,6 +230,7 @@ int Engine::port_bit(const std::string& proto_port) {
 int Engine::port_exact_bit(const std::string& triple) {
   auto it = port_exact_slot.find(triple);
   if (it != port_exact_slot.end()) return it->second;
+  will_mutate();
   int b = (int)port_exact_slot.size();
   if (b >= KSB_PORT_WORDS * 64) throw std::runtime_error("more than 256 distinct protocol/hostIP/hostPort triples");
   port_exact_slot[triple] = b;
@@ -241,6 +249,7 @@ SigInfo* Engine::sig_of(const Pod& p) {
   }
   auto it = sigs.find(k);
   if (it != sigs.end()) return it->second.get();
+  will_mutate();
   auto s = std::make_unique<SigInfo>();
   s->ns = p.ns;
   s->labels = p.labels;
@@ -250,8 +259,12 @@ SigInfo* Engine::sig_of(const Pod& p) {
 }
 
 bool Engine::sig_matches_sel(SigInfo* s, int c) {
-  if ((int)s->sel_match.size() <= c) s->sel_match.resize(selclasses.size(), -1);
+  if ((int)s->sel_match.size() <= c) {
+    will_mutate();
+    s->sel_match.resize(selclasses.size(), -1);
+  }
   if (s->sel_match[c] < 0) {
+    will_mutate();
     const SelClass& sc = selclasses[c];
     s->sel_match[c] = sc.nss.count(s->ns) && sel::matches(sc.selector, s->labels);  // topologies.go:41-50
   }
@@ -259,8 +272,12 @@ bool Engine::sig_matches_sel(SigInfo* s, int c) {
 }
 
 bool Engine::sig_matches_spread(SigInfo* s, int c) {
-  if ((int)s->spread_match.size() <= c) s->spread_match.resize(spread_classes.size(), -1);
+  if ((int)s->spread_match.size() <= c) {
+    will_mutate();
+    s->spread_match.resize(spread_classes.size(), -1);
+  }
   if (s->spread_match[c] < 0) {
+    will_mutate();
     const SpreadClass& sc = spread_classes[c];
     bool m = false;
     if (sc.ns == s->ns)
@@ -290,6 +307,7 @@ int Engine::selclass_of(const Pod& owner, const PodAffinityTerm& t, bool* ok) {
   key += sel::canonical(sx);
   auto it = selclass_idx.find(key);
   if (it != selclass_idx.end()) return it->second;
+  will_mutate();
   int id = (int)selclasses.size();
   SelClass c;
   c.nss = std::move(nss);
@@ -303,6 +321,7 @@ int Engine::table_of(int kind, int selclass, int topo) {
   std::string key = std::to_string(kind) + "|" + std::to_string(selclass) + "|" + std::to_string(topo);
   auto it = table_idx.find(key);
   if (it != table_idx.end()) return it->second;
+  will_mutate();
   int id = (int)tables.size();
   Table t;
   t.kind = kind;
@@ -342,6 +361,7 @@ void Engine::layout_arena() {
 // priorities/metadata.go:69-96 over the in-memory listers (testing/fake_lister.go:80-178)
 int Engine::spread_class_of(const Pod& p, SigInfo* s) {
   if (s->spread_class != -2) return s->spread_class;
+  will_mutate();
   std::vector<sel::Selector> sels;
   for (int kind = 0; kind < 2; ++kind)
     for (auto& o : owners[kind])

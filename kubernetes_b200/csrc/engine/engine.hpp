@@ -77,12 +77,18 @@ struct SpreadClass {
   std::vector<sel::Selector> selectors;
 };
 
+// Thrown by the dictionaries when a lookup would have to intern something new while the calling thread runs in
+// read-only mode (the parallel part of the batch encoder): the pod is then encoded again on the main thread.
+struct NeedsIntern {};
+
 struct SigInfo {  // memo per distinct (namespace, labels) signature
   std::string ns;
   StrMap labels;
   std::vector<int8_t> spread_match;  // per spread class
   std::vector<int8_t> sel_match;     // per SelClass
   int spread_class = -2;             // -2 unknown, -1 none
+  std::vector<int> spread_inc;       // spread classes the signature matches, valid for `spread_inc_classes` classes
+  size_t spread_inc_classes = (size_t)-1;
 };
 
 struct CommitEntry {  // one per-domain counter the assume step bumps
@@ -149,7 +155,12 @@ class Engine {
   std::map<std::array<uint64_t, KSB_CLASS_WORDS + 1>, uint16_t> ext_mask_ids;  // (device-class mask, slot) -> id
   // label -> rows index (built with the layout): rows holding a key=value pair; rows holding a key, with the value
   std::unordered_map<std::string, std::vector<int>> rows_by_pair;
-  std::unordered_map<std::string, std::vector<std::pair<int, const std::string*>>> rows_by_key;
+  struct KeyRow {  // a row holding the key, with its value parsed once for the Gt / Lt bits (selector.go:214-233)
+    int row;
+    bool is_num;
+    int64_t num;
+  };
+  std::unordered_map<std::string, std::vector<KeyRow>> rows_by_key;
   bool label_index_valid = false;
   void build_label_index();
   std::vector<Taint> hard_taints, soft_taints;
@@ -167,6 +178,10 @@ class Engine {
   std::vector<std::string> topo_keys;
   std::vector<std::unordered_map<std::string, int>> topo_values;  // value -> domain id (1-based)
 
+  static thread_local bool tl_readonly;  // this thread may only look the dictionaries up
+  static void will_mutate() {
+    if (tl_readonly) throw NeedsIntern();
+  }
   int label_bit(char kind, const std::string& key, const std::string& value, int64_t num);
   bool node_has_label_bit(const Node& n, const LabelBitDef& d) const;
   int topo_key(const std::string& key);

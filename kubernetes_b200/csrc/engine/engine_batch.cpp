@@ -2,9 +2,12 @@
 // FitError text, and the pod mutators that keep device and host mirror in step.
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <future>
 #include <stdexcept>
+#include <thread>
 #include <unordered_set>
 
 #include "engine.hpp"
@@ -318,9 +321,14 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   CUDA_OK(cudaSetDevice(cfg.device));
   const int np = (int)batch.size();
   auto t0 = std::chrono::steady_clock::now();
+  static const bool trace = getenv("KSB_TRACE") != nullptr;  // host timing breakdown of large batches on stderr
+  std::vector<std::pair<const char*, double>> marks;
+  auto mark = [&](const char* what) {
+    if (trace) marks.push_back({what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count()});
+  };
   if (layout_dirty) rebuild_layout();
   last_n_nodes = n;
-  last_encoded.assign(np, EncodedPod());
+  last_encoded.resize(np);  // encode_pod resets every field of an entry
   last_results.assign(np, KsbResult());
   last_fiterr_hist.clear();
   have_snapshot = false;
@@ -343,15 +351,31 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   if (assume) {
     // ksb_schedule_batch == n x {ksb_schedule; ksb_pod_add}: a key that is already cached, or repeated inside the
     // batch, is the error ksb_pod_add reports (cache.go:127-129); refuse before anything is placed
-    std::unordered_set<std::string> seen;
-    for (auto& p : batch) {
-      const std::string k = p.key();
-      if (pods.count(k) || !seen.insert(k).second) throw std::runtime_error("pod " + k + " is already in the cache");
-    }
+    // repeated keys inside the batch: 64-bit hashes sorted, exact comparison only where two hashes meet
+    auto key_hash = [](const Pod& p) {
+      uint64_t h = 1469598103934665603ull;
+      for (unsigned char ch : p.ns) h = (h ^ ch) * 1099511628211ull;
+      h = (h ^ (unsigned char)'/') * 1099511628211ull;
+      for (unsigned char ch : p.name) h = (h ^ ch) * 1099511628211ull;
+      return h;
+    };
+    std::vector<std::pair<uint64_t, int>> hs((size_t)np);
+    for (int i = 0; i < np; ++i) hs[i] = {key_hash(batch[i]), i};
+    std::sort(hs.begin(), hs.end());
+    for (int i = 1; i < np; ++i)
+      if (hs[i].first == hs[i - 1].first && batch[hs[i].second].key() == batch[hs[i - 1].second].key())
+        throw std::runtime_error("pod " + batch[hs[i].second].key() + " is already in the cache");
+    if (!pods.empty())
+      for (auto& p : batch) {
+        const std::string k = p.key();
+        if (pods.count(k)) throw std::runtime_error("pod " + k + " is already in the cache");
+      }
   }
+  mark("checks");
   // pass 1: classes (every pod of the batch, so that commit lists name every class a later pod introduces)
   for (auto& p : batch) register_pod_classes(p);
   layout_arena();
+  mark("classes");
 
   // Large batches on one GPU go to the device in chunks: while the kernel of chunk c runs, the host encodes chunk
   // c+1 and mirrors the placements of chunk c-1 into its records. Device work stays strictly ordered on one stream
@@ -383,12 +407,40 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     auto te0 = std::chrono::steady_clock::now();
     const int len = c1 - c0;
     const size_t first_word = pool_words;
+    // Large chunks are encoded on several threads in read-only mode: a pod that needs something new interned (a
+    // label bit, a signature, a class-mask id ...) is left for the main thread, which encodes those afterwards in
+    // stream order. Interned ids are arbitrary, so the order in which they are handed out does not matter.
+    std::vector<char> done((size_t)len, 0);
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const int workers = len >= 1024 ? (int)std::min(6u, hw > 3 ? hw - 2 : 1u) : 1;
+    if (workers > 1) {
+      std::vector<std::string> errors((size_t)workers);
+      auto work = [&](int t) {
+        tl_readonly = true;
+        const int lo = c0 + (int)((int64_t)len * t / workers), hi = c0 + (int)((int64_t)len * (t + 1) / workers);
+        for (int i = lo; i < hi; ++i) {
+          try {
+            encode_pod(batch[i], &last_encoded[i]);
+            done[i - c0] = 1;
+          } catch (const NeedsIntern&) {
+          } catch (const std::exception&) {
+            // limits and malformed pods: the main thread meets the same error in stream order and reports it
+          }
+        }
+        tl_readonly = false;
+      };
+      std::vector<std::thread> pool;
+      for (int t = 0; t < workers; ++t) pool.emplace_back(work, t);
+      for (auto& th : pool) th.join();
+    }
+    if (c0 == 0) mark("first encode: parallel part");
     for (int i = c0; i < c1; ++i) {
-      encode_pod(batch[i], &last_encoded[i]);
+      if (!done[i - c0]) encode_pod(batch[i], &last_encoded[i]);
       last_encoded[i].h.pool_off = (uint32_t)pool_words;
       pool_words += last_encoded[i].pool.size();
     }
     if (arena_dirty && c0 > 0) throw std::runtime_error("internal: the counter arena changed in the middle of a batch");
+    if (c0 == 0) mark("first encode: serial part");
     Staged& st = staged[which];
     st.hdr_bytes = (size_t)len * sizeof(KsbPodHeader);
     st.dep_off = (st.hdr_bytes + 255) & ~(size_t)255;
@@ -396,6 +448,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     st.pool_first = first_word;
     st.pool_words = pool_words - first_word;
     pin_chunk[which].ensure(st.pool_off + std::max<size_t>(1, st.pool_words) * 8);
+    if (c0 == 0) mark("first encode: staging buffer");
     KsbPodHeader* headers = (KsbPodHeader*)pin_chunk[which].p;
     int32_t* dep = (int32_t*)((char*)pin_chunk[which].p + st.dep_off);
     uint64_t* pool = (uint64_t*)((char*)pin_chunk[which].p + st.pool_off);
@@ -591,7 +644,9 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   int c0 = 0, c1 = 0, n0 = 0, n1 = 0;
   bounds(0, &c0, &c1);
   encode_chunk(c0, c1, 0);
+  mark("first encode");
   launch_chunk(c0, c1, 0);
+  mark("first launch");
   // Chunked batches mirror the placements of chunk c on a second host thread while this one encodes chunk c+2 (and
   // the device runs chunk c+1). The two touch disjoint state: the mirror thread writes the request / port columns
   // of the host table, the class counters' values, the per-node records and the pod cache; the encoder reads the
@@ -632,6 +687,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     have_snapshot = false;
     throw;
   }
+  mark("chunks done");
   if (n_chunks > 1) {
     // the replay entry points run the whole batch in one launch: dependency indices relative to the batch
     CUDA_OK(cudaMemcpyAsync(b_dep.d, last_dep.data(), (size_t)np * 4, cudaMemcpyHostToDevice, stream));
@@ -646,6 +702,12 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   stats.last_batch_sync_ms = sync_ms;
   stats.last_batch_kernel_ms = kernel_ms;
   stats.last_batch_post_ms = post_ms;
+  mark("end");
+  if (trace && np >= 4096) {
+    fprintf(stderr, "ksb_schedule_batch %d pods:", np);
+    for (auto& m : marks) fprintf(stderr, " %s %.1f ms;", m.first, m.second);
+    fprintf(stderr, " kernels %.1f, encode %.1f, mirror %.1f, table sync %.1f\n", kernel_ms, encode_ms, post_ms, sync_ms);
+  }
 }
 
 // Grow a device buffer and keep what it holds (the stream must be idle: the old block is freed).

@@ -84,9 +84,17 @@ void Engine::register_pod_classes(const Pod& p) {
 
 // What the assume step of this pod bumps besides its node's own columns.
 void Engine::commit_lists(const Pod& p, SigInfo* s, std::vector<CommitEntry>* commits, std::vector<int>* spread_inc) {
-  if (!p.deleting)
-    for (int c = 0; c < (int)spread_classes.size(); ++c)
-      if (sig_matches_spread(s, c)) spread_inc->push_back(c);
+  if (!p.deleting) {
+    // the spread classes this signature matches, kept with the signature while the set of classes stands
+    if (s->spread_inc_classes != spread_classes.size()) {
+      will_mutate();
+      s->spread_inc.clear();
+      for (int c = 0; c < (int)spread_classes.size(); ++c)
+        if (sig_matches_spread(s, c)) s->spread_inc.push_back(c);
+      s->spread_inc_classes = spread_classes.size();
+    }
+    *spread_inc = s->spread_inc;
+  }
   // the pod becomes an "existing pod": every MATCH table whose class it belongs to
   for (int c = 0; c < (int)selclasses.size(); ++c) {
     if (selclasses[c].match_tables.empty()) continue;
@@ -371,8 +379,10 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
     for (int w = 0; w < KSB_CLASS_WORDS; ++w) key[w] = cm[w];
     key[KSB_CLASS_WORDS] = h.ext[i].rslot;
     auto kid = ext_mask_ids.find(key);
-    if (kid == ext_mask_ids.end() && ext_mask_ids.size() < 65535)
+    if (kid == ext_mask_ids.end() && ext_mask_ids.size() < 65535) {
+      will_mutate();
       kid = ext_mask_ids.emplace(key, (uint16_t)(ext_mask_ids.size() + 1)).first;
+    }
     h.ext[i].cls_id = kid == ext_mask_ids.end() ? 0 : kid->second;
     h.ext[i].pad = 0;
   }
