@@ -118,6 +118,7 @@ struct __attribute__((aligned(16))) KsbPodHeader {
   uint8_t n_exprs, n_req_terms, n_pref, n_ext, n_checks, n_score, n_commit, n_spread_inc;
   uint8_t ext_err_entry;
   uint8_t pad[6];
+  uint8_t expr_wm[KSB_MAX_EXPRS];  // per expression: which of the first four label words its mask touches (bit w = word w)
 };
 
 // pool words, in order:

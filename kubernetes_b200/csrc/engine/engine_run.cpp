@@ -237,6 +237,8 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
     if (n_exprs >= KSB_MAX_EXPRS) throw std::runtime_error("pod " + p.key() + " has more than KSB_MAX_EXPRS label expressions");
     exprs.insert(exprs.end(), m.begin(), m.end());
     h.expr_kind[n_exprs >> 4] |= kind << ((n_exprs & 15) * 2);
+    for (int w = 0; w < 4 && w < (int)m.size(); ++w)
+      if (m[w]) h.expr_wm[n_exprs] |= (uint8_t)(1u << w);
     ++n_exprs;
   };
   if (!p.node_selector.empty()) {  // predicates.go:708-713 with labels.SelectorFromSet's degrade-to-everything

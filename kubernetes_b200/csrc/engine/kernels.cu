@@ -318,6 +318,7 @@ struct RowCommon {
   int32_t num_pods, alloc_pods;
   uint32_t nflags, zone;
   double rcp_cpu, rcp_mem;  // fast_rcp of the allocatable cpu / memory (lr_bra)
+  uint32_t over;            // bit 0: allocatable alpha-gpu < requested on the row, bit 1: the same for ephemeral storage
 };
 
 template <bool CG>
@@ -340,17 +341,22 @@ __device__ __forceinline__ void load_row_common(const KsbNodeTable& T, int r, Ro
   for (int w = 0; w < kLabFast; ++w) rc.lab[w] = w < T.W ? T.labels[w * np + r] : 0ull;
   rc.rcp_cpu = fast_rcp((double)rc.acpu);
   rc.rcp_mem = fast_rcp((double)rc.amem);
+  // pods that ask for neither (nearly all) then need no load of these four columns
+  rc.over = (T.alloc_agpu[r] < ldx<CG>(T.req_agpu + r) ? 1u : 0u) | (T.alloc_eph[r] < ldx<CG>(T.req_eph + r) ? 2u : 0u);
 }
 
-// eval_expr for label_words == kLabFast: the row's label words come from registers
-__device__ __forceinline__ bool eval_expr4(const uint64_t (&lab)[kLabFast], const uint64_t* mask, uint32_t kind) {
+// eval_expr for label_words == kLabFast: the row's label words come from registers. `wm` names the words the mask
+// touches (host-computed): an untouched word changes neither "any" nor "all", so it is not even loaded.
+__device__ __forceinline__ bool eval_expr4(const uint64_t (&lab)[kLabFast], const uint64_t* mask, uint32_t kind, uint32_t wm) {
   bool any = false, all = true;
 #pragma unroll
   for (int w = 0; w < kLabFast; ++w) {
-    const uint64_t m = mask[w];
-    const uint64_t x = lab[w] & m;
-    any |= (x != 0);
-    all &= (x == m);
+    if ((wm >> w) & 1u) {  // uniform across the warp: one pod per iteration
+      const uint64_t m = mask[w];
+      const uint64_t x = lab[w] & m;
+      any |= (x != 0);
+      all &= (x == m);
+    }
   }
   return kind == EK_ANY ? any : (kind == EK_NONE ? !any : all);
 }
@@ -405,14 +411,24 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   if (pf & PF_HAS_REQUEST) {
     if (acpu < h->req_cpu + rc.rcpu) reasons |= 1u << RB_CPU;
     if (amem < h->req_mem + rc.rmem) reasons |= 1u << RB_MEM;
-    if (T.alloc_agpu[r] < h->req_agpu + ldx<CG>(T.req_agpu + r)) reasons |= 1u << RB_AGPU;
-    if (T.alloc_eph[r] < h->req_eph + ldx<CG>(T.req_eph + r)) reasons |= 1u << RB_EPH;
-    uint32_t sm = h->scalar_mask;
+    if (h->req_agpu == 0) {
+      if (rc.over & 1u) reasons |= 1u << RB_AGPU;
+    } else if (T.alloc_agpu[r] < h->req_agpu + ldx<CG>(T.req_agpu + r)) {
+      reasons |= 1u << RB_AGPU;
+    }
+    if (h->req_eph == 0) {
+      if (rc.over & 2u) reasons |= 1u << RB_EPH;
+    } else if (T.alloc_eph[r] < h->req_eph + ldx<CG>(T.req_eph + r)) {
+      reasons |= 1u << RB_EPH;
+    }
+    const uint32_t sm = h->scalar_mask;
+    if (sm) {
 #pragma unroll
-    for (int s = 0; s < KSB_MAX_SCALARS; ++s)
-      if ((sm >> s) & 1u)
-        if (T.alloc_scalar[s * np + r] < h->scalar_req[s] + ldx<CG>(T.req_scalar + s * np + r))
-          reasons |= 1u << (RB_SCALAR0 + s);
+      for (int s = 0; s < KSB_MAX_SCALARS; ++s)
+        if ((sm >> s) & 1u)
+          if (T.alloc_scalar[s * np + r] < h->scalar_req[s] + ldx<CG>(T.req_scalar + s * np + r))
+            reasons |= 1u << (RB_SCALAR0 + s);
+    }
   }
   // --- PodFitsHost (predicates.go:764-776)
   if (h->pinned_row != -1 && h->pinned_row != T.row_base + r) reasons |= 1u << RB_HOSTNAME;
@@ -433,7 +449,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
     const int W = T.W;
 #define KSB_KIND(e) ((h->expr_kind[(e) >> 4] >> (((e) & 15) * 2)) & 3u)
     if (W == kLabFast) {
-#define KSB_EXPR_FAST(e) eval_expr4(rc.lab, pv.exprs + (e) * kLabFast, KSB_KIND(e))
+#define KSB_EXPR_FAST(e) eval_expr4(rc.lab, pv.exprs + (e) * kLabFast, KSB_KIND(e), h->expr_wm[(e)])
       KSB_LABEL_RULES(KSB_EXPR_FAST);
 #undef KSB_EXPR_FAST
     } else {
@@ -516,23 +532,52 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   o.reasons = reasons;
 }
 
-// PrioritizeNodes' Reduce functions and weighted sum (generic_scheduler.go:575-606).
-__device__ __forceinline__ int32_t final_score(const KsbNodeTable& T, const KsbNorms& nm, const int32_t* zone_sum,
+// PrioritizeNodes' Reduce functions and weighted sum (generic_scheduler.go:575-606). The float64 pieces are
+// functions of a handful of values per pod (the node's matching-pod count, its zone), so phase 2 tabulates them per
+// pod with exactly these operations (ScoreLut) and a (pod, node) evaluation looks them up; values beyond the tables
+// are computed in place by the same functions.
+// selector_spreading.go:141-147: 10 * (maxCount - count) / maxCount
+__device__ __forceinline__ double spread_node_f(int32_t max_sc, int32_t sc) {
+  return max_sc > 0 ? __dmul_rn(10.0, __ddiv_rn((double)(max_sc - sc), (double)max_sc)) : 10.0;
+}
+// selector_spreading.go:151-164: zoneWeighting * zoneScore
+__device__ __forceinline__ double spread_zone_term(int32_t max_zone, int32_t zone_sum) {
+  const double zw = 2.0 / 3.0;
+  const double zs = max_zone > 0 ? __dmul_rn(10.0, __ddiv_rn((double)(max_zone - zone_sum), (double)max_zone)) : 10.0;
+  return __dmul_rn(zw, zs);
+}
+__device__ __forceinline__ double spread_node_part(double f) {  // fScore * (1.0 - zoneWeighting)
+  const double zw = 2.0 / 3.0;
+  return __dmul_rn(f, __dsub_rn(1.0, zw));
+}
+// reduce.go:29-63, reverse = true
+__device__ __forceinline__ int32_t taint_score(int32_t max_tt, int32_t tt) { return max_tt > 0 ? 10 - (10 * tt) / max_tt : 10; }
+
+constexpr int kLutSc = 8, kLutZone = 16, kLutTt = 8;
+struct ScoreLut {
+  double fs[kLutSc];     // spread_node_f(max_sc, count)
+  double fsz[kLutSc];    // spread_node_part(fs[count])
+  double fz[kLutZone];   // spread_zone_term(max_zone, zone_sum[zone])
+  int32_t tts[kLutTt];   // taint_score(max_tt, count)
+};
+
+__device__ __forceinline__ int32_t final_score(const KsbNodeTable& T, const KsbNorms& nm, const ScoreLut& L, const int32_t* zone_sum,
                                                int32_t max_zone, int32_t base, int32_t na, int32_t tt, uint32_t sc,
                                                int32_t ipa, uint32_t zone) {
   // selector_spreading.go:119-174
-  double f = 10.0;
-  if (nm.max_sc > 0) f = __dmul_rn(10.0, __ddiv_rn((double)(nm.max_sc - (int32_t)sc), (double)nm.max_sc));
+  const bool small = sc < (uint32_t)kLutSc;
+  double f;
   if (nm.have_zones && zone != 0) {
-    double zs = 10.0;
-    if (max_zone > 0) zs = __dmul_rn(10.0, __ddiv_rn((double)(max_zone - zone_sum[zone]), (double)max_zone));
-    const double zw = 2.0 / 3.0;
-    f = __dadd_rn(__dmul_rn(f, __dsub_rn(1.0, zw)), __dmul_rn(zw, zs));
+    const double part = small ? L.fsz[sc] : spread_node_part(spread_node_f(nm.max_sc, (int32_t)sc));
+    const double zt = zone < (uint32_t)kLutZone ? L.fz[zone] : spread_zone_term(max_zone, zone_sum[zone]);
+    f = __dadd_rn(part, zt);
+  } else {
+    f = small ? L.fs[sc] : spread_node_f(nm.max_sc, (int32_t)sc);
   }
-  int32_t ss = (int32_t)f;
+  const int32_t ss = (int32_t)f;
   // reduce.go:29-63
-  int32_t nas = nm.max_na > 0 ? (10 * na) / nm.max_na : na;
-  int32_t tts = nm.max_tt > 0 ? 10 - (10 * tt) / nm.max_tt : 10;
+  const int32_t nas = na == 0 ? 0 : (nm.max_na > 0 ? (10 * na) / nm.max_na : na);
+  const int32_t tts = tt < kLutTt ? L.tts[tt] : taint_score(nm.max_tt, tt);
   // interpod_affinity.go:218-237
   int32_t ipas = 0;
   if (nm.ipa_max - nm.ipa_min > 0)
@@ -655,7 +700,6 @@ __device__ __forceinline__ void commit_pod(const KsbNodeTable& T, int r, const P
 
 __device__ __forceinline__ int32_t warp_max(int32_t v) { return __reduce_max_sync(0xffffffffu, v); }
 __device__ __forceinline__ int32_t warp_min(int32_t v) { return __reduce_min_sync(0xffffffffu, v); }
-__device__ __forceinline__ int32_t warp_sum(int32_t v) { return __reduce_add_sync(0xffffffffu, v); }
 
 // Mutable (and a few static) columns of one node row, kept in shared memory by phase 3 for every row
 // chosen earlier in the current group.
@@ -1155,8 +1199,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     // pipelined: block 0 does not evaluate, nor does the block on its SM
     const int eb = pipe ? b - 1 - ((shun_b != 0 && b > shun_b) ? 1 : 0) : b;
     const int enb = pipe ? nblk - 1 - (shun_b != 0 ? 1 : 0) : nblk;
-    const int it0 = do_eval ? (int)((long long)items * eb / enb) : 0;
-    const int it1 = do_eval ? (int)((long long)items * (eb + 1) / enb) : 0;
+    // (items <= 2048 segments x 32 pods and a few hundred blocks: the products fit 32 bits)
+    const int it0 = do_eval ? (int)((uint32_t)items * (uint32_t)eb / (uint32_t)enb) : 0;
+    const int it1 = do_eval ? (int)((uint32_t)items * (uint32_t)(eb + 1) / (uint32_t)enb) : 0;
     const bool active = it1 > it0;
     const int seg_lo = active ? it0 / Gc : 0, seg_hi = active ? (it1 - 1) / Gc : -1;
 
@@ -1169,9 +1214,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
         RowCommon rc;
         if (live) load_row_common<false>(T, r, rc);
-        for (int g = g_lo; g <= g_hi; ++g) {
+        size_t at = (half + (size_t)g_lo) * np + (size_t)r;  // this thread's slot in the (pod, row) stashes
+        for (int g = g_lo; g <= g_hi; ++g, at += np) {
           const KsbPodHeader* h = S.hdr + g;
-          int32_t fit = 0, mna = 0, mtt = 0, msc = 0, imax = 0, imin = 0, hz = 0, one = -1;
+          int32_t fit = 0, mna = 0, mtt = 0, msc = 0, ipa = 0, hz = 0;
           if (live && !(h->flags & PF_SCHED_ERROR)) {
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
             EvalOut o;
@@ -1182,9 +1228,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               mna = o.na;
               mtt = o.tt;
               msc = (int32_t)o.sc;
-              imax = max(0, o.ipa);
-              imin = min(0, o.ipa);
-              one = T.row_base + r;
+              ipa = o.ipa;
               if (o.zone) {
                 hz = 1;
                 if (o.sc) atomicAdd(&S.zone[g * zs + o.zone], (int32_t)o.sc);
@@ -1193,27 +1237,33 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             } else {
               raw = make_int4(INT32_MIN, 0, 0, 0);
             }
-            raw_s[(size_t)g * np + r] = raw;
-            reasons_s[(size_t)g * np + r] = o.reasons;
+            A.raw[at] = raw;
+            A.reasons[at] = o.reasons;
           }
-          fit = warp_sum(fit);
-          mna = warp_max(mna);
-          mtt = warp_max(mtt);
-          msc = warp_max(msc);
-          imax = warp_max(imax);
-          imin = warp_min(imin);
-          hz = warp_max(hz);
-          one = warp_max(one);
-          if (lane == 0) {  // this warp's own slot: no atomics needed
+          // Reduce inputs of this warp's 32 rows: ballots for the counts and flags, a redux only for the values the pod
+          // can have at all (uniform per pod); this warp's own slot, so no atomics
+          const uint32_t fb = __ballot_sync(0xffffffffu, fit != 0);
+          if (fb) {
             int32_t* pp = S.part + (g * kWarps + warp) * 8;
-            pp[0] += fit;
-            pp[1] = max(pp[1], mna);
-            pp[2] = max(pp[2], mtt);
-            pp[3] = max(pp[3], msc);
-            pp[4] = max(pp[4], imax);
-            pp[5] = min(pp[5], imin);
-            pp[6] = max(pp[6], hz);
-            pp[7] = max(pp[7], one);
+            const bool any_z = __any_sync(0xffffffffu, hz != 0);
+            int32_t vna = 0, vtt = 0, vsc = 0, vmax = 0, vmin = 0;
+            if (h->n_pref) vna = warp_max(mna);
+            if (h->soft_untol) vtt = warp_max(mtt);
+            if (h->spread_col >= 0) vsc = warp_max(msc);
+            if (h->n_score) {
+              vmax = warp_max(max(0, ipa));
+              vmin = warp_min(min(0, ipa));
+            }
+            if (lane == 0) {
+              pp[0] += __popc(fb);
+              pp[1] = max(pp[1], vna);
+              pp[2] = max(pp[2], vtt);
+              pp[3] = max(pp[3], vsc);
+              pp[4] = max(pp[4], vmax);
+              pp[5] = min(pp[5], vmin);
+              pp[6] = max(pp[6], any_z ? 1 : 0);
+              pp[7] = max(pp[7], T.row_base + seg * kSeg + warp * 32 + (31 - __clz(fb)));  // highest fitting row
+            }
           }
         }
       }
@@ -1258,12 +1308,37 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     // ---- phase 2: Reduce + weighted sum; per-segment (max, tie count) of every pod
     for (int i = tid; i < Gc * 8; i += kThreads)
       reinterpret_cast<int32_t*>(S.norm)[i] = __ldcv(reinterpret_cast<const int32_t*>(norms) + i);
-    for (int i = tid; i < Gc * zs; i += kThreads) S.zone[i] = (i % zs) < nz ? __ldcv(zsum + i) : 0;
+    for (int g = warp; g < Gc; g += kWarps)
+      for (int z = lane; z < zs; z += 32) S.zone[g * zs + z] = z < nz ? __ldcv(zsum + g * zs + z) : 0;
     __syncthreads();
     if (tid < Gc) {
       int32_t mz = 0;
       for (int z = 0; z < nz; ++z) mz = max(mz, S.zone[tid * zs + z]);
       S.max_zone[tid] = mz;
+    }
+    __syncthreads();
+    ScoreLut* lut = reinterpret_cast<ScoreLut*>(S.post);  // phase 3's window scratch is idle here
+    static_assert(sizeof(ScoreLut) * kMaxG <= sizeof(RowCache) * kMaxG, "score tables alias the window scratch");
+    if (active) {
+      // the pods this block scores: one run inside a segment, or all of them
+      const int lg_lo = seg_lo == seg_hi ? it0 - seg_lo * Gc : 0;
+      const int lg_hi = seg_lo == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
+      for (int i = tid; i < (lg_hi - lg_lo + 1) * 32; i += kThreads) {
+        const int g = lg_lo + (i >> 5), e = i & 31;
+        const KsbNorms nm = S.norm[g];
+        ScoreLut& L = lut[g];
+        if (e < kLutSc) {
+          const double f = spread_node_f(nm.max_sc, e);
+          L.fs[e] = f;
+          L.fsz[e] = spread_node_part(f);
+        } else if (e < kLutSc + kLutZone) {
+          const int z = e - kLutSc;
+          L.fz[z] = spread_zone_term(S.max_zone[g], z < zs ? S.zone[g * zs + z] : 0);
+        } else {
+          L.tts[e - kLutSc - kLutZone] = taint_score(nm.max_tt, e - kLutSc - kLutZone);
+        }
+      }
+      static_assert(kLutSc + kLutZone + kLutTt == 32, "one table entry per lane");
     }
     __syncthreads();
     if (active) {
@@ -1273,14 +1348,15 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         const uint32_t zone = live ? T.zone[r] : 0u;
         const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
         const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
-        for (int g = g_lo; g <= g_hi; ++g) {
+        size_t at = (half + (size_t)g_lo) * np + (size_t)r;
+        for (int g = g_lo; g <= g_hi; ++g, at += np) {
           const KsbPodHeader* h = S.hdr + g;
           const KsbNorms nm = S.norm[g];
           const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && nm.fit_count >= 2;
           if (nm.fit_count == 0 && !(h->flags & PF_SCHED_ERROR)) {
             // no node fits: histogram of failure reasons for FitError.Error() (generic_scheduler.go:70-88),
             // one ballot per reason bit present in the warp; lane b owns bit b
-            const uint32_t m = live ? reasons_s[(size_t)g * np + r] : 0u;
+            const uint32_t m = live ? A.reasons[at] : 0u;
             uint32_t un = __reduce_or_sync(0xffffffffu, m);
             int32_t acc = 0;
             while (un) {
@@ -1298,11 +1374,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           if (!prio) continue;  // uniform per (block, g)
           int32_t s = INT32_MIN;
           if (live) {
-            int4 raw = raw_s[(size_t)g * np + r];
+            const int4 raw = A.raw[at];
             if (raw.x != INT32_MIN)
-              s = final_score(T, nm, S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
+              s = final_score(T, nm, lut[g], S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
                               (uint32_t)raw.z & 0xffffffu, raw.w, zone);
-            score_s[(size_t)g * np + r] = s;
+            A.score[at] = s;
           }
           int32_t wm = warp_max(s);
           const uint32_t wmask = __ballot_sync(0xffffffffu, s == wm && s != INT32_MIN);
