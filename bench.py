@@ -99,7 +99,9 @@ def oracle_baseline(cluster, sample_pods, workers):
 
 def ncu_traffic(cfg, n_nodes, n_pods):
     """DRAM bytes per launch of the batch kernel from the committed `ncu --set full` summary of this workload, else None."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_summary.json")
+    path = os.path.join(ROOT, "profiles", "r02_ncu_summary.json")
+    if not os.path.exists(path):
+        return None
     try:
         with open(path) as f:
             for rec in json.load(f)["captures"]:
@@ -108,6 +110,57 @@ def ncu_traffic(cfg, n_nodes, n_pods):
     except (OSError, KeyError, ValueError):
         pass
     return None
+
+
+def one_pod_latency(sess, device, n_pods):
+    """p50 / p99 of the one-pod-per-call path (Schedule + AssumePod per pod, the reference's own call pattern): over
+    EVERY call after ksb_flush, first uses of labels and selector classes included, and over the warm tail alone."""
+    n_cold = min(n_pods // 2, 500)
+    n_lat = min(n_pods - n_cold, 2000)
+    every = sess.run(device=device, results=False, batch=0, limit=n_cold + n_lat, lat_skip=0)
+    warm = sess.run(device=device, results=False, batch=0, limit=n_cold + n_lat, lat_skip=n_cold)
+    return {"p50_us": every["p50_us"], "p99_us": every["p99_us"], "max_us": every["max_us"],
+            "warm_p50_us": warm["p50_us"], "warm_p99_us": warm["p99_us"], "warm_max_us": warm["max_us"],
+            "unit": "us per ksb_schedule call (host to host)",
+            "sample": "pods 0..%d of the stream, one C-ABI call per pod, every call counted; warm_* leaves the first %d "
+                      "calls out" % (n_cold + n_lat, n_cold)}
+
+
+def batch_latency(sess, device, n_pods, bsz=64):
+    """The queue drained `bsz` pods per call: a call's duration is the latency of each of its pods."""
+    n_b = min(n_pods, bsz * 160)
+    bl = sess.run(device=device, results=False, batch=bsz, limit=n_b)
+    if "batch_call_p50_us" not in bl:
+        return None
+    return {"call_p50_us": bl["batch_call_p50_us"], "call_p99_us": bl["batch_call_p99_us"], "calls": bl["batch_calls"],
+            "pods_per_s": n_b / (bl["e2e_ms"] / 1000.0)}
+
+
+def side_record(cfg, device, steps):
+    """The other half of BASELINE.json's metric ("at 5k and 50k nodes"): the 5,000-node config measured in the same
+    run, same method (end-to-end pass on a fresh engine, then a resident replay with L2 flushed)."""
+    from kubernetes_b200 import lib, workloads
+    n_nodes, n_pods = workloads.CONFIG_SIZES[cfg]
+    cluster = workloads.generate(cfg, n_nodes, n_pods)
+    sess = lib.Session(cluster=cluster)
+    sess.run(device=device, results=False)
+    e2e, rep, hashes = [], [], set()
+    for _ in range(max(2, steps)):
+        out = sess.run(device=device, results=False, replay_iters=1)
+        e2e.append(out["e2e_ms"])
+        rep.append(out["replay_ms"])
+        hashes.add(out["placement_hash"])
+    assert len(hashes) == 1, "placements changed between steps"
+    step_ms, e2e_ms = sum(rep) / len(rep), sum(e2e) / len(e2e)
+    peak, _ = measured_peak()
+    achieved = workloads.ALGO_BYTES[cfg] * n_nodes * n_pods / (step_ms / 1000.0) / 1e9
+    rec = {"workload": "cfg%d: %d nodes x %d pods (BASELINE.json configs[%d])" % (cfg, n_nodes, n_pods, cfg - 1),
+           "value": n_pods / (step_ms / 1000.0), "unit": UNIT, "ms_per_step": step_ms,
+           "e2e": {"value": n_pods / (e2e_ms / 1000.0), "unit": UNIT, "ms_per_step": e2e_ms},
+           "roofline": {"achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak},
+           "placement_hash": sorted(hashes)[0], "latency": one_pod_latency(sess, device, n_pods)}
+    sess.close()
+    return rec
 
 
 def pick_sample(n_nodes):
@@ -126,6 +179,7 @@ def main():
     ap.add_argument("--pods", type=int, default=None)
     ap.add_argument("--cpu-sample", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-side-config", action="store_true", help="skip the 5,000-node sub-record of the default run")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: anything a library prints there (NCCL's version banner) goes to stderr
     json_out = os.fdopen(os.dup(1), "w")
@@ -216,6 +270,7 @@ def main():
         h2d, d2h = out["h2d_bytes"], out["d2h_bytes"]
         launches += int(out.get("kernel_launches", 1))  # the engine's own count: chunk launches of the e2e pass + the replay
         hashes.add(out["placement_hash"])
+        result_hash = out.get("result_hash")
         scheduled, fit_errors = out["scheduled"], out["fit_errors"]
         groups, restarts = out["groups"], out["group_restarts"]
     barrier()
@@ -228,6 +283,14 @@ def main():
         t = torch.tensor([step_ms, e2e_step_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         step_ms, e2e_step_ms = float(t[0]), float(t[1])
+    matches_unsharded = None
+    if dist is not None:
+        # the unsharded pass once on rank 0 (the sharded engines are closed, the other ranks wait): same placements,
+        # filtered counts and scores (result_hash covers status, host, device ids, filtered count and score per pod)
+        if rank == 0:
+            solo = sess.run(device=local_rank, results=False)
+            matches_unsharded = (solo["placement_hash"] == sorted(hashes)[0] and solo.get("result_hash") == result_hash)
+        dist.barrier()
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -248,7 +311,7 @@ def main():
                    if world > 1 else "1 GPU",
                    "groups": groups, "group_restarts": restarts,
                    "l2": "L2 flushed (256 MiB memset) before every timed replay; the node table itself is L2-resident by design",
-                   "placement_hash": sorted(hashes)[0]},
+                   "placement_hash": sorted(hashes)[0], "result_hash": result_hash},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_step_ms},
         # ksb_schedule_batch_kernel launches inside the timed steps, as counted by the engine: one per 4,096-pod chunk
@@ -260,25 +323,16 @@ def main():
                      "kernel_ms_in_e2e": sum(kernel_ms) / len(kernel_ms)},
         "clocks": clocks,
     }
+    if world > 1:
+        line["matches_unsharded"] = matches_unsharded
     if world == 1:
-        # p99 per-pod latency (BASELINE.json's metric): the one-pod-per-call path, Schedule + AssumePod per pod
-        n_cold = min(n_pods // 2, 500)
-        n_lat = min(n_pods - n_cold, 2000)
-        lat = sess.run(device=local_rank, results=False, batch=0, limit=n_cold + n_lat, lat_skip=n_cold)
-        line["latency"] = {"p50_us": lat["p50_us"], "p99_us": lat["p99_us"], "max_us": lat["max_us"],
-                           "cold_max_us": max(x[1] for x in lat["slowest"]),
-                           "unit": "us per ksb_schedule call (host to host)",
-                           "sample": "pods %d..%d of the stream, one C-ABI call per pod; the first %d calls (cold label / "
-                                     "selector-class dictionaries) are reported as cold_max_us only" % (n_cold, n_cold + n_lat, n_cold)}
-    if world == 1:
-        # batch mode: the queue drained 64 pods at a time; a call's duration is the latency of each of its pods
-        bsz = 64
-        n_b = min(n_pods, 64 * 160)
-        bl = sess.run(device=local_rank, results=False, batch=bsz, limit=n_b)
-        if "batch_call_p50_us" in bl:
-            line["latency"]["batch%d" % bsz] = {"call_p50_us": bl["batch_call_p50_us"], "call_p99_us": bl["batch_call_p99_us"],
-                                                 "calls": bl["batch_calls"],
-                                                 "pods_per_s": n_b / (bl["e2e_ms"] / 1000.0)}
+        # p99 per-pod latency (BASELINE.json's metric)
+        line["latency"] = one_pod_latency(sess, local_rank, n_pods)
+        b64 = batch_latency(sess, local_rank, n_pods)
+        if b64:
+            line["latency"]["batch64"] = b64
+        if args.config == 4 and not args.no_side_config:
+            line["cfg3"] = side_record(3, local_rank, args.steps)
     if not args.no_cpu_baseline:
         sample = args.cpu_sample or pick_sample(n_nodes)
         pps, secs, _ = oracle_baseline(cluster, sample, workers)
