@@ -265,6 +265,7 @@ class Engine {
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
   // shard geometry: device rows [lbase, lbase + ln), device column stride ln_pad
   int lbase = 0, ln = 0, ln_pad = 0, rows_per_shard = 0;
+  int eval_base = 0, eval_n = 0;  // rows this GPU evaluates: global rows [eval_base, eval_base + eval_n)
   size_t min_spread_cols = 0, min_table_bytes = 0;
   bool shard_connected = false;
   struct PeerMap {
@@ -273,7 +274,7 @@ class Engine {
   };
   std::vector<PeerMap> peer_maps;    // rank 0: every other shard's buffers as mapped into this process
   size_t shard_results_cap = 0;
-  int segs_per_shard = 1, nseg_total = 0;
+  int segs_per_shard = 1, nseg_total = 0, eval_nseg = 0;
   void prepare_geometry();
   void* peer0_scratch = nullptr;     // other ranks: rank 0's scratch buffer, mapped
   std::vector<void*> ipc_mappings;

@@ -27,7 +27,7 @@ constexpr size_t kPodSlotDep = (sizeof(KsbPodHeader) + 15) & ~(size_t)15;  // of
 constexpr size_t kPodSlotPool = kPodSlotDep + 16;
 struct ScratchLayout {
   size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, seg_mask, barrier, error_flag, fiterr_count, last_index,
-      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, total;
+      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, base0, total;
 };
 ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int halves = 1) {
   ScratchLayout L;
@@ -62,6 +62,7 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   L.seg_max = take(halves * (size_t)G * nseg * 4);
   L.seg_cnt = take(halves * (size_t)G * nseg * 4);
   L.seg_mask = take(halves * (size_t)G * nseg * 32);
+  L.base0 = take(halves * (size_t)G * n_pad * 4);  // sharded engines: raw.x per (pod, global row) on rank 0
   L.total = off;
   return L;
 }
@@ -71,7 +72,8 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
 void Engine::prepare_geometry() {
   const int R = std::max(1, cfg.shard_count);
   zone_stride = (dT.n_zones + 63) & ~63;
-  nseg = (ln + 255) / 256;
+  nseg = (ln + 255) / 256;           // segments of this GPU's table (rank 0 of a sharded engine: all of them)
+  eval_nseg = (eval_n + 255) / 256;  // segments this GPU evaluates
   segs_per_shard = R == 1 ? std::max(1, nseg) : rows_per_shard / 256;
   nseg_total = R == 1 ? nseg : (n + 255) / 256;
   // group size: as configured, bounded by what the zone sums and the segment statistics may take of shared memory
@@ -80,7 +82,7 @@ void Engine::prepare_geometry() {
   if (nseg_total > KSB_MAX_SEGMENTS) throw std::runtime_error("more than 524,288 node rows");
   group = std::max(1, std::min(group, KSB_SEG_CACHE / std::max(1, nseg_total)));
   // pipelined launches: the row cache holds the previous group's rows next to the current one's
-  pipe = R == 1 && cfg.pipeline >= 0 && (cfg.pipeline > 0 || ln >= 16384);
+  pipe = cfg.pipeline >= 0 && (cfg.pipeline > 0 || n >= 16384);  // the same on every rank: decided by the whole table
   if (pipe) group = std::min(group, KSB_MAX_GROUP / 2);
   if (group < 2) pipe = false;
   if (zone_stride * 4 * KSB_MAX_GROUP > 160 * 1024) throw std::runtime_error("more than 1,280 distinct zones");
@@ -95,7 +97,8 @@ void Engine::prepare_geometry() {
   }
   if (max_grid < 1) throw std::runtime_error("batch kernel does not fit on this device");
   // enough blocks to cover every segment; when segments are few, extra blocks split the group's pods
-  grid = nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, std::max(1, nseg) * group));
+  grid = eval_nseg >= max_grid ? max_grid : std::max(1, std::min(max_grid, std::max(1, eval_nseg) * group));
+  if (R > 1) grid = max_grid;  // every rank runs the same schedule (block roles depend on the block index)
   if (pipe && grid < 2) pipe = false;
   ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
   if (shard_connected && L.total > b_scratch.cap)
@@ -119,7 +122,9 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.commit = commit ? 1 : 0;
   a.group_size = group;
   a.pipeline = (pipe && n_pods > group && (batch_pipe_ok || cfg.pipeline > 0)) ? 1 : 0;  // a batch of one group gains nothing from the extra iteration
-  a.nseg = nseg;
+  a.nseg = eval_nseg;  // segments this GPU evaluates
+  a.eval_n = eval_n;
+  a.seg_gbase = eval_base / 256;
   a.results = (KsbResult*)b_results.d;
   a.norms = (KsbNorms*)(base + L.norms);
   a.zone_sum = (int32_t*)(base + L.zone_sum);
@@ -163,6 +168,28 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
       a.xbar = (uint32_t*)(b0 + L.xbar);
     }
   }
+  // where the evaluation's results for phase 3 go: own arrays, or rank 0's (indexed by global row / segment)
+  a.gs_score = a.score;
+  a.gs_reasons = a.reasons;
+  a.gs_base0 = (int32_t*)(base + L.base0);
+  a.gs_seg_max = a.seg_max;
+  a.gs_seg_cnt = a.seg_cnt;
+  a.gs_seg_mask = a.seg_mask;
+  a.gs_np = ln_pad;
+  a.gs_nseg = std::max(1, nseg);
+  if (R > 1 && a.rank != 0) {
+    // rank 0's scratch layout follows from the whole table's geometry, which every rank knows
+    ScratchLayout L0 = scratch_layout(n_pad, zone_stride, std::max(1, nseg_total), group, pipe ? 2 : 1);
+    char* b0 = (char*)peer0_scratch;
+    a.gs_score = (int32_t*)(b0 + L0.score);
+    a.gs_reasons = (uint32_t*)(b0 + L0.reasons);
+    a.gs_base0 = (int32_t*)(b0 + L0.base0);
+    a.gs_seg_max = (int32_t*)(b0 + L0.seg_max);
+    a.gs_seg_cnt = (int32_t*)(b0 + L0.seg_cnt);
+    a.gs_seg_mask = (uint32_t*)(b0 + L0.seg_mask);
+    a.gs_np = n_pad;
+    a.gs_nseg = std::max(1, nseg_total);
+  }
   return a;
 }
 
@@ -179,8 +206,10 @@ void Engine::launch(const KsbBatchArgs& a_in) {
   a.self.seg_mask = a.seg_mask;
   a.self.results = a.results;
   a.self.last_node_index = a.last_node_index;
-  a.self.nseg = a.nseg;
+  a.self.nseg = a.gs_nseg;  // phase 3 (rank 0 only) reads the arrays the results were gathered into
   a.self.seg_base = 0;
+  a.self.raw_np = a.table.n_pad;
+  a.self.raw_row0 = 0;
   if (a.n_ranks == 1 && b_scratch.d && (char*)a.norms == (char*)b_scratch.d) {
     // the engine's own scratch on one GPU: every control field lies in one contiguous block at the start of the
     // buffer, so its initial image goes up in a single copy from page-locked memory
@@ -204,8 +233,10 @@ void Engine::launch(const KsbBatchArgs& a_in) {
     self->seg_mask = a.seg_mask;
     self->results = a.results;
     self->last_node_index = a.last_node_index;
-    self->nseg = a.nseg;
+    self->nseg = a.gs_nseg;
     self->seg_base = 0;
+    self->raw_np = a.table.n_pad;
+    self->raw_row0 = 0;
     CUDA_OK(cudaMemcpyAsync(b_scratch.d, img, bytes, cudaMemcpyHostToDevice, stream));
     int rc = ksb_launch_batch(&a, grid, smem_bytes, stream);
     if (rc != 0) throw std::runtime_error(std::string("kernel launch failed: ") + cudaGetErrorString((cudaError_t)rc));
@@ -244,8 +275,10 @@ void Engine::launch(const KsbBatchArgs& a_in) {
     self.seg_mask = a.seg_mask;
     self.results = a.results;
     self.last_node_index = a.last_node_index;
-    self.nseg = a.nseg;
+    self.nseg = a.gs_nseg;
     self.seg_base = 0;
+    self.raw_np = a.table.n_pad;
+    self.raw_row0 = 0;
     CUDA_OK(cudaMemcpyAsync((void*)a.peers, &self, sizeof self, cudaMemcpyHostToDevice, stream));
   } else if (a.rank == 0) {
     // the peer table: this rank from its own buffers, the others from their mapped buffers and geometry
@@ -259,8 +292,10 @@ void Engine::launch(const KsbBatchArgs& a_in) {
     pt[0].seg_mask = a.seg_mask;
     pt[0].results = a.results;
     pt[0].last_node_index = a.last_node_index;
-    pt[0].nseg = a.nseg;
+    pt[0].nseg = a.gs_nseg;
     pt[0].seg_base = 0;
+    pt[0].raw_np = a.table.n_pad;
+    pt[0].raw_row0 = 0;
     for (int q = 1; q < a.n_ranks; ++q) {
       const PeerMap& m = peer_maps[q];
       KsbPeer& P = pt[q];
@@ -270,7 +305,7 @@ void Engine::launch(const KsbBatchArgs& a_in) {
       P.table.row_base = m.lbase;
       fill_table_pointers(&P.table, m.p[0], m.p[1], m.p[2], m.p[3], m.p[4], m.p[5], m.p[6], (size_t)m.ln_pad);
       const int nseg_q = (m.ln + 255) / 256;
-      ScratchLayout Lq = scratch_layout(m.ln_pad, a.zone_stride, std::max(1, nseg_q), a.group_size);
+      ScratchLayout Lq = scratch_layout(m.ln_pad, a.zone_stride, std::max(1, nseg_q), a.group_size, pipe ? 2 : 1);
       char* sb = (char*)m.p[7];
       P.raw = (int4*)(sb + Lq.raw);
       P.score = (int32_t*)(sb + Lq.score);
@@ -282,6 +317,8 @@ void Engine::launch(const KsbBatchArgs& a_in) {
       P.results = (KsbResult*)m.p[8];
       P.nseg = nseg_q;
       P.seg_base = q * a.segs_per_shard;
+      P.raw_np = m.ln_pad;
+      P.raw_row0 = m.lbase;
     }
     CUDA_OK(cudaMemcpy((void*)a.peers, pt.data(), sizeof(KsbPeer) * pt.size(), cudaMemcpyHostToDevice));
   }

@@ -520,12 +520,24 @@ void Engine::plan_shard() {
     ln = n;
     ln_pad = n_pad;
     rows_per_shard = n_pad;
+    eval_base = 0;
+    eval_n = n;
     return;
   }
   rows_per_shard = std::max(256, (((n + R - 1) / R) + 255) & ~255);  // whole segments per shard
-  lbase = std::min(n, cfg.shard_rank * rows_per_shard);
-  ln = std::max(0, std::min(n - lbase, rows_per_shard));
-  ln_pad = rows_per_shard;
+  eval_base = std::min(n, cfg.shard_rank * rows_per_shard);
+  eval_n = std::max(0, std::min(n - eval_base, rows_per_shard));
+  if (cfg.shard_rank == 0) {
+    // rank 0 commits: it holds EVERY row (and receives every rank's evaluation results), so that the sequential part
+    // never reads another GPU's memory; it still evaluates only its own range of rows
+    lbase = 0;
+    ln = n;
+    ln_pad = n_pad;
+  } else {
+    lbase = eval_base;
+    ln = eval_n;
+    ln_pad = rows_per_shard;
+  }
 }
 
 void Engine::setup_table_pointers() {

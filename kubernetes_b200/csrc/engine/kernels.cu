@@ -622,7 +622,7 @@ __device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, u
 // grid has arrived, bumps a counter in rank 0's memory over NVLink and waits for all ranks, then releases
 // its grid. With one rank it is a plain grid barrier.
 // `wait` false (one rank only): arrive without waiting; the block contributes nothing to the phase that ends here.
-__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true) {
+__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true, int xb = 0) {
   __syncthreads();
   if (threadIdx.x == 0) {
     epoch += gridDim.x;
@@ -633,7 +633,7 @@ __device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, u
     } else {
       __threadfence_system();
       atomicAdd(A.barrier, 1u);
-      if (blockIdx.x == 0) {
+      if ((int)blockIdx.x == xb) {
         spin_until<false>(A, A.barrier, epoch, 2);
         xepoch += (uint32_t)A.n_ranks;
         __threadfence_system();
@@ -641,7 +641,7 @@ __device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, u
         spin_until<true>(A, A.xbar, xepoch, 3);
         __threadfence_system();
         atomicExch(A.release, epoch);
-      } else {
+      } else if (wait) {
         spin_until<false>(A, A.release, epoch, 4);
       }
       __threadfence_system();
@@ -891,9 +891,8 @@ __device__ __forceinline__ void commit_and_record(RowCache* c, CommitRec* rec, c
 
 // Writer side: the row's mutable columns from the record to the table (NodeInfo.AddPod, node_info.go:329-356,
 // and the bind echo of device ids, pkg/registry/core/pod/storage/storage.go:180-187).
-__device__ __forceinline__ void write_through(const KsbNodeTable& T, const CommitRec& rec, const KsbPodHeader* h, int lane) {
+__device__ __forceinline__ void write_through(const KsbNodeTable& T, const CommitRec& rec, int r, const KsbPodHeader* h, int lane) {
   const size_t np = T.n_pad;
-  const int r = rec.row;
   // requested / nonzero columns (lanes 4..9) and touched scalar columns (14..17): q[] order = column order
   const bool own = (lane >= 4 && lane < 10) || (lane >= 14 && lane < 18 && h->scalar_add[lane - 14] != 0);
   if (own) T.alloc_cpu[(size_t)lane * np + r] = rec.q[lane];
@@ -1072,6 +1071,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   // ("commit side") while the other blocks evaluate the next one ("evaluation side") against the table as it stood
   // before that commit; the commit's table writes are held back until the evaluation has read the table.
   constexpr bool pipe = PIPE;
+  constexpr int xb = PIPE ? 1 : 0;  // the block that runs the cross-GPU leg of the barriers (block 0 of rank 0 commits)
   const bool committer = b == 0 && A.rank == 0;
   const bool lag = pipe && committer;  // this block works on the commit-side group
   int ev_p0 = 0, ev_slot = 0;          // evaluation side: first pod and scratch half of the group
@@ -1080,14 +1080,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   // The block that shares an SM with block 0 would compete with the decider warp for issue slots: it sits the
   // evaluation out. group_done[4] = block 0's SM, group_done[5] = index of that block (0: none).
   int shun_b = 0;
+  if (MULTI) xepoch = *A.xstate;  // the cross-GPU counter is never reset: its epoch is carried from launch to launch
   if (pipe) {
+    // (sharded: only rank 0 has a committing block, so only its blocks take part; every rank runs the barriers)
     uint32_t smid;
     asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-    if (b == 0 && tid == 0) A.group_done[4] = (int32_t)smid;
-    grid_barrier(A, epoch, xepoch);
-    if (b != 0 && tid == 0 && (int32_t)smid == __ldcv(A.group_done + 4)) A.group_done[5] = b;
-    grid_barrier(A, epoch, xepoch);
-    shun_b = __ldcv(A.group_done + 5);
+    if (A.rank == 0 && b == 0 && tid == 0) {
+      A.group_done[4] = (int32_t)smid;
+      A.group_done[5] = 0;
+    }
+    grid_barrier(A, epoch, xepoch, true, xb);
+    if (A.rank == 0 && b != 0 && tid == 0 && (int32_t)smid == __ldcv(A.group_done + 4)) A.group_done[5] = b;
+    grid_barrier(A, epoch, xepoch, true, xb);
+    shun_b = A.rank == 0 ? __ldcv(A.group_done + 5) : 0;
     if (nblk < 4) shun_b = 0;
   }
   int cm_gid = 0;    // block 0: sequence number of the group being committed (row-cache tags)
@@ -1100,9 +1105,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     __syncthreads();
   }
   if (multi) {
-    // sharded: the cross-GPU counter is never reset, its epoch is carried from launch to launch; rank 0 clears
-    // the shared reduction targets itself and an opening barrier publishes that before any rank adds to them
-    xepoch = *A.xstate;
+    // sharded: rank 0 clears the shared reduction targets itself and an opening barrier publishes that before any
+    // rank adds to them
     if (A.rank == 0 && blockIdx.x == 0) {
       for (int i = threadIdx.x; i < 2 * kMaxG * 8; i += kThreads)
         reinterpret_cast<int32_t*>(A.norms)[i] = ((i & 7) == 7) ? -1 : 0;
@@ -1110,7 +1114,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       for (int i = threadIdx.x; i < 2 * kMaxG * KSB_REASON_BITS; i += kThreads) A.ghist[i] = 0;
       if (threadIdx.x < 2) A.group_done[threadIdx.x] = 0;
     }
-    grid_barrier(A, epoch, xepoch);
+    grid_barrier(A, epoch, xepoch, true, xb);
   }
   // measurement state lives in shared memory (thread 0 of each block updates it; block 0's copy is reported): kept
   // in registers it would cost every thread of the kernel some thirty of them
@@ -1142,9 +1146,6 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
 #define raw_s (A.raw + half * np)
 #define score_s (A.score + half * np)
 #define reasons_s (A.reasons + half * np)
-#define seg_max_s (A.seg_max + half * nseg)
-#define seg_cnt_s (A.seg_cnt + half * nseg)
-#define seg_mask_s (A.seg_mask + half * nseg * kWarps)
     // ---- stage the group's requirement blocks; every block derives the same group extent
     if (!have_group) {
       if (tid == 0) s_gc = 0;
@@ -1188,7 +1189,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     // iteration, not of the group: a block that runs ahead into the next iteration then never overwrites a value that a
     // slower block has yet to read (scratch halves do not alternate in an iteration that evaluates nothing).
     if (pipe && b == 1 && tid == 0) A.group_done[2 + (gi & 1)] = Gc;
-    const bool do_eval = !lag && Gc > 0 && !(shun_b != 0 && b == shun_b);
+    const bool do_eval = !lag && Gc > 0 && !(shun_b != 0 && b == shun_b) && !(pipe && b == 0);
     KSB_TICK(0);
     KsbNorms* norms = A.norms + (size_t)slot * kMaxG;
     int32_t* zsum = A.zone_sum + (size_t)slot * kMaxG * zs;
@@ -1209,13 +1210,15 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     if (active) {
       for (int seg = seg_lo; seg <= seg_hi; ++seg) {
         const int r = seg * kSeg + tid;
-        const bool live = r < T.n;
+        const bool live = r < A.eval_n;
         const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
         const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
         RowCommon rc;
         if (live) load_row_common<false>(T, r, rc);
         size_t at = (half + (size_t)g_lo) * np + (size_t)r;  // this thread's slot in the (pod, row) stashes
-        for (int g = g_lo; g <= g_hi; ++g, at += np) {
+        // sharded: what phase 3 reads goes to rank 0's arrays, indexed by global row
+        size_t gat = MULTI ? (half + (size_t)g_lo) * (size_t)A.gs_np + (size_t)(T.row_base + r) : at;
+        for (int g = g_lo; g <= g_hi; ++g, at += np, gat += MULTI ? (size_t)A.gs_np : np) {
           const KsbPodHeader* h = S.hdr + g;
           int32_t fit = 0, mna = 0, mtt = 0, msc = 0, ipa = 0, hz = 0;
           if (live && !(h->flags & PF_SCHED_ERROR)) {
@@ -1238,7 +1241,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               raw = make_int4(INT32_MIN, 0, 0, 0);
             }
             A.raw[at] = raw;
-            A.reasons[at] = o.reasons;
+            A.gs_reasons[gat] = o.reasons;
+            if (MULTI) A.gs_base0[gat] = raw.x;
           }
           // Reduce inputs of this warp's 32 rows: ballots for the counts and flags, a redux only for the values the pod
           // can have at all (uniform per pod); this warp's own slot, so no atomics
@@ -1301,7 +1305,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
     }
     KSB_TICK(1);
-    grid_barrier(A, epoch, xepoch, !lag);
+    grid_barrier(A, epoch, xepoch, !lag, xb);
     if (lag && tid == 0) s_b1_target = epoch;  // the writer warp holds its table writes until this barrier is complete
     KSB_TICK(2);
 
@@ -1344,19 +1348,20 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     if (active) {
       for (int seg = seg_lo; seg <= seg_hi; ++seg) {
         const int r = seg * kSeg + tid;
-        const bool live = r < T.n;
+        const bool live = r < A.eval_n;
         const uint32_t zone = live ? T.zone[r] : 0u;
         const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
         const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
         size_t at = (half + (size_t)g_lo) * np + (size_t)r;
-        for (int g = g_lo; g <= g_hi; ++g, at += np) {
+        size_t gat = MULTI ? (half + (size_t)g_lo) * (size_t)A.gs_np + (size_t)(T.row_base + r) : at;
+        for (int g = g_lo; g <= g_hi; ++g, at += np, gat += MULTI ? (size_t)A.gs_np : np) {
           const KsbPodHeader* h = S.hdr + g;
           const KsbNorms nm = S.norm[g];
           const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && nm.fit_count >= 2;
           if (nm.fit_count == 0 && !(h->flags & PF_SCHED_ERROR)) {
             // no node fits: histogram of failure reasons for FitError.Error() (generic_scheduler.go:70-88),
             // one ballot per reason bit present in the warp; lane b owns bit b
-            const uint32_t m = live ? A.reasons[at] : 0u;
+            const uint32_t m = live ? A.gs_reasons[gat] : 0u;
             uint32_t un = __reduce_or_sync(0xffffffffu, m);
             int32_t acc = 0;
             while (un) {
@@ -1378,7 +1383,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (raw.x != INT32_MIN)
               s = final_score(T, nm, lut[g], S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
                               (uint32_t)raw.z & 0xffffffu, raw.w, zone);
-            A.score[at] = s;
+            A.gs_score[gat] = s;
           }
           int32_t wm = warp_max(s);
           const uint32_t wmask = __ballot_sync(0xffffffffu, s == wm && s != INT32_MIN);
@@ -1405,14 +1410,15 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
             }
             if (m == INT32_MIN) c = 0;
-            seg_max_s[(size_t)g * nseg + seg] = m;
-            seg_cnt_s[(size_t)g * nseg + seg] = c;
+            const size_t sat = (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + seg);
+            A.gs_seg_max[sat] = m;
+            A.gs_seg_cnt[sat] = c;
             // which rows hold the segment's maximum: word w = rows 32w..32w+31 of the segment
             uint32_t mw[kWarps];
 #pragma unroll
             for (int w = 0; w < kWarps; ++w)
               mw[w] = (S.wstat[(g * kWarps + w) * 3] == m && m != INT32_MIN) ? (uint32_t)S.wstat[(g * kWarps + w) * 3 + 2] : 0u;
-            uint4* mp = reinterpret_cast<uint4*>(seg_mask_s + ((size_t)g * nseg + seg) * kWarps);
+            uint4* mp = reinterpret_cast<uint4*>(A.gs_seg_mask + sat * kWarps);
             mp[0] = make_uint4(mw[0], mw[1], mw[2], mw[3]);
             mp[1] = make_uint4(mw[4], mw[5], mw[6], mw[7]);
           }
@@ -1421,7 +1427,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
     }
     KSB_TICK(3);
-    if (!pipe) grid_barrier(A, epoch, xepoch);  // pipelined: block 0 decides while the others are in phases 1-2
+    if (!pipe) grid_barrier(A, epoch, xepoch, true, xb);  // pipelined: block 0 decides while the others are in phases 1-2
     KSB_TICK(4);
 
     // ---- phase 3: block 0 of rank 0 commits the group's pods in order. Rows of other shards are reached
@@ -1454,7 +1460,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           else hi = mid - 1;
         }
         int within = q - (lo + 1 < nsegT ? cum[lo + 1] : 0);
-        const int pr = MULTI ? min(R - 1, lo / sps) : 0;
+        const int pr = 0;
         const KsbPeer& P = PEER(pr);
         const int ls = lo - P.seg_base;
         const uint4* mp = reinterpret_cast<const uint4*>(P.seg_mask + ((half + g) * P.nseg + ls) * kWarps);
@@ -1504,7 +1510,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         if (in.act) {
           const KsbPeer& P = PEER(prank);
           const size_t at = (half + g) * P.table.n_pad + crow;
-          in.base0 = __ldcv(&P.raw[at].x);
+          in.base0 = MULTI ? __ldcv(A.gs_base0 + at) : __ldcv(&P.raw[at].x);
           in.reasons0 = __ldcv(P.reasons + at);
           in.score0 = __ldcv(P.score + at);
           const int ls = crow / kSeg;
@@ -1629,8 +1635,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         }
         int32_t* cum = S.cum + g * nsegT;
         int32_t gmax0, carry = 0;
-        if (!MULTI && nsegT <= 8 * 32 && (A.self.nseg & 3) == 0) {
-          // one rank, up to 256 segments (65,536 rows): lane l takes segments 8l..8l+7 with four 16-byte loads, sums
+        if (nsegT <= 8 * 32 && A.self.nseg == nsegT && (A.self.nseg & 3) == 0) {
+          // up to 256 segments (65,536 rows; sharded: rank 0's arrays hold every rank's segments): lane l takes segments 8l..8l+7 with four 16-byte loads, sums
           // its own eight counts serially and one warp scan joins the lanes (the row stride of the per-pod statistics
           // is a multiple of four segments, so the vectors are aligned)
           const int32_t* pmax = A.self.seg_max + (half + g) * A.self.nseg;
@@ -1675,7 +1681,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         } else {
           int32_t m = INT32_MIN;
           for (int i = lane; i < nsegT; i += 32) {
-            const int q = MULTI ? min(R - 1, i / sps) : 0;
+            const int q = 0;
             const KsbPeer& P = PEER(q);
             const int32_t v = __ldcv(P.seg_max + (half + g) * P.nseg + (i - P.seg_base));
             cum[i] = v;
@@ -1687,7 +1693,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             const int i = top - 1 - lane;  // lane 0 = highest segment
             int32_t cnt = 0;
             if (i >= 0 && cum[i] == gmax0) {
-              const int q = MULTI ? min(R - 1, i / sps) : 0;
+              const int q = 0;
               const KsbPeer& P = PEER(q);
               cnt = __ldcv(P.seg_cnt + (half + g) * P.nseg + (i - P.seg_base));
             }
@@ -1832,7 +1838,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   crank = c.pad & 0xff;
                   const KsbPeer& P = PEER(crank);
                   const size_t at = (half + g) * P.table.n_pad + crow;
-                  const int32_t base0 = __ldcv(&P.raw[at].x);  // INT32_MIN = the row did not fit at group start
+                  const int32_t base0 = MULTI ? __ldcv(A.gs_base0 + at) : __ldcv(&P.raw[at].x);  // INT32_MIN = the row did not fit at group start
                   old_reasons = __ldcv(P.reasons + at);
                   if (prio) cold = __ldcv(P.score + at);
                   int32_t base;
@@ -1855,7 +1861,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                     bool safe = true;
                     if (flip) {
                       const KsbPeer& P = PEER(crank);
-                      const int4 raw = __ldcv(P.raw + (half + g) * P.table.n_pad + crow);
+                      // the Map values of the row (sharded: kept by the rank that evaluated it, a remote read on this rare path)
+                      const int own = MULTI ? min(R - 1, (crow / kSeg) / sps) : 0;
+                      const KsbPeer& O = PEER(own);
+                      const int4 raw = __ldcv(O.raw + (half + g) * (MULTI ? (size_t)O.raw_np : (size_t)P.table.n_pad) +
+                                              (crow - (MULTI ? O.raw_row0 : 0)));
                       const int32_t na = raw.y, tt = (int32_t)((uint32_t)raw.z >> 24), ipa = raw.w;
                       const uint32_t sc = (uint32_t)raw.z & 0xffffffu;
                       safe = (nm.max_na == 0 || na < nm.max_na) && (nm.max_tt == 0 || tt < nm.max_tt) && sc == 0 &&
@@ -1902,7 +1912,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   __syncwarp();
                 } else if (nm.fit_count == 1) {
                   // generic_scheduler.go:144-146: no selectHost, counter untouched
-                  chosen_rank = MULTI ? min(R - 1, (nm.one_row / kSeg) / sps) : 0;
+                  chosen_rank = 0;
                   chosen = nm.one_row - PEER(chosen_rank).table.row_base;
                 } else {
                   // (2) selectHost (generic_scheduler.go:177-192): lastNodeIndex % k over the rows tied at the maximum,
@@ -1938,7 +1948,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                       const int ent = select_merged(Am, Dm, rem, S.r0 + g * kCache, s_erow, &q);
                       int grow = ent >= 0 ? s_erow[ent] : select_snapshot(g, q);
                       if (grow >= 0) {
-                        pick_rank = MULTI ? min(R - 1, (grow / kSeg) / sps) : 0;
+                        pick_rank = 0;
                         pick = grow - PEER(pick_rank).table.row_base;
                       }
                     }
@@ -2109,7 +2119,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               if (s2 < cpw && w < W) {
                 const int e = s_pick[w];
                 if (e >= 0) {
-                  const int erank = MULTI ? min(R - 1, (e / kSeg) / sps) : 0;
+                  const int erank = 0;
                   const uint32_t hit = __ballot_sync(0xffffffffu, lane < ncr && s_erow[lane] == e);
                   e_[s2] = e;
                   idx_[s2] = hit ? __ffs(hit) - 1 : -1;
@@ -2303,12 +2313,22 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
             const KsbPeer& P = PEER(rec.rank);
             const int chosen = rec.row;
-            write_through(P.table, rec, h, lane);
+            write_through(P.table, rec, chosen, h, lane);
+            // sharded: rank 0 holds every row (phase 3 works on that copy); the rank that evaluates the row gets the
+            // same columns over NVLink so that its next evaluation sees them
+            const int own = MULTI ? min(R - 1, (chosen / kSeg) / sps) : 0;
+            if (MULTI && own != 0) write_through(PEER(own).table, rec, chosen - own * sps * kSeg, h, lane);
             // the class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
             // of this group reads them. SelectorSpread columns are sharded with the rows; affinity tables are
             // replicated on every rank.
             const size_t pn = P.table.n_pad;
-            for (int i = lane; i < h->n_spread_inc; i += 32) atomicAdd(P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen, 1u);
+            for (int i = lane; i < h->n_spread_inc; i += 32) {
+              atomicAdd(P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen, 1u);
+              if (MULTI && own != 0) {
+                const KsbPeer& O = PEER(own);
+                atomicAdd_system(O.table.spread + (size_t)pv.spread_inc[i] * O.table.n_pad + (chosen - own * sps * kSeg), 1u);
+              }
+            }
             for (int i = lane; i < h->n_commit; i += 32) {
               const uint64_t cm = pv.commits[2 * i];
               const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
@@ -2316,8 +2336,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
               for (int q = 0; q < R; ++q) {
                 int32_t* tb = PEER(q).table.tables;
-                if (d) atomicAdd(tb + off + d, delta);
-                if ((cm >> 40) & 1ull) atomicAdd(tb + off, delta);  // slot 0: total matching pods anywhere
+                if (q == 0) {
+                  if (d) atomicAdd(tb + off + d, delta);
+                  if ((cm >> 40) & 1ull) atomicAdd(tb + off, delta);  // slot 0: total matching pods anywhere
+                } else {
+                  if (d) atomicAdd_system(tb + off + d, delta);
+                  if ((cm >> 40) & 1ull) atomicAdd_system(tb + off, delta);
+                }
               }
             }
           }
@@ -2352,7 +2377,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
     }
     // pipelined: the evaluation side has read the table and finished phase 2; the commit side has decided and written
-    grid_barrier(A, epoch, xepoch);
+    grid_barrier(A, epoch, xepoch, true, xb);
     KSB_TICK(6);
     if (__ldcg(A.error_flag) != 0) break;  // only after a barrier timeout: stop instead of spinning
     if (!pipe) {
@@ -2378,7 +2403,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           int32_t* gh = A.ghist + (size_t)(cm_slot ^ 1) * kMaxG * KSB_REASON_BITS;
           for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
         }
-        grid_barrier(A, epoch, xepoch);
+        grid_barrier(A, epoch, xepoch, true, xb);
         ev_p0 = cm_p0 + adv;
         cm_valid = false;
       } else if (ge > 0) {
@@ -2397,7 +2422,6 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     gi += 1;
   }
   if (b == 0 && tid == 0) {
-    if (multi) *A.xstate = xepoch;
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[i];  // block 0's cycles per stage
     for (int i = 0; i < 5; ++i) A.counters[9 + i] = (uint64_t)s_tk[11 + i];  // phase-3 breakdown
 #if KSB_FINE_TIMING
@@ -2414,14 +2438,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       A.counters[1] = (uint64_t)s_tk[10];
     }
   }
+  if (multi && b == xb && tid == 0) *A.xstate = xepoch;
 #undef KSB_TICK
 #undef PEER
 #undef raw_s
 #undef score_s
 #undef reasons_s
-#undef seg_max_s
-#undef seg_cnt_s
-#undef seg_mask_s
 }
 
 // Applies the assume step for a pod placed outside a batch (ksb_pod_add after ksb_schedule).
@@ -2446,8 +2468,9 @@ extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
 
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
   void* params[] = {(void*)args};
-  const void* fn = args->n_ranks > 1 ? (const void*)ksb_schedule_batch_kernel<false, true>
-                   : (args->pipeline ? (const void*)ksb_schedule_batch_kernel<true, false> : (const void*)ksb_schedule_batch_kernel<false, false>);
+  const void* fn = args->n_ranks > 1
+                       ? (args->pipeline ? (const void*)ksb_schedule_batch_kernel<true, true> : (const void*)ksb_schedule_batch_kernel<false, true>)
+                       : (args->pipeline ? (const void*)ksb_schedule_batch_kernel<true, false> : (const void*)ksb_schedule_batch_kernel<false, false>);
   cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,
                                               smem_bytes, stream);
   return (int)e;
@@ -2456,8 +2479,8 @@ extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_
 extern "C" int ksb_batch_kernel_limits(int device, size_t smem_bytes, int* max_grid, int* threads) {
   int per_sm = 0, sms = 0;
   // the three instantiations (plain, pipelined, sharded) share one grid size: the smallest occupancy of the three
-  const void* fns[3] = {(const void*)ksb_schedule_batch_kernel<false, false>, (const void*)ksb_schedule_batch_kernel<true, false>,
-                        (const void*)ksb_schedule_batch_kernel<false, true>};
+  const void* fns[4] = {(const void*)ksb_schedule_batch_kernel<false, false>, (const void*)ksb_schedule_batch_kernel<true, false>,
+                        (const void*)ksb_schedule_batch_kernel<false, true>, (const void*)ksb_schedule_batch_kernel<true, true>};
   cudaError_t e = cudaSuccess;
   per_sm = 1 << 30;
   for (const void* fn : fns) {
@@ -2582,5 +2605,15 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->peers = (const KsbPeer*)(b + kNaPeer);
   a->fiterr_hist = (int32_t*)(b + kNaFitHist);
   a->fiterr_cap = KSB_MAX_FITERR;
+  a->gs_score = a->score;
+  a->gs_reasons = a->reasons;
+  a->gs_base0 = nullptr;
+  a->gs_seg_max = a->seg_max;
+  a->gs_seg_cnt = a->seg_cnt;
+  a->gs_seg_mask = a->seg_mask;
+  a->gs_np = n_pad;
+  a->gs_nseg = a->nseg;
+  a->seg_gbase = 0;
+  a->eval_n = a->table.n;
   return 0;
 }
