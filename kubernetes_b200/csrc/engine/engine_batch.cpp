@@ -27,7 +27,7 @@ constexpr size_t kPodSlotDep = (sizeof(KsbPodHeader) + 15) & ~(size_t)15;  // of
 constexpr size_t kPodSlotPool = kPodSlotDep + 16;
 struct ScratchLayout {
   size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, seg_mask, barrier, error_flag, fiterr_count, last_index,
-      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, base0, total;
+      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, tot_norms, tot_zone, total;
 };
 ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int halves = 1) {
   ScratchLayout L;
@@ -53,6 +53,8 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   L.xbar = take(4);
   L.xstate = take(4);
   L.peers = take(sizeof(KsbPeer) * KSB_MAX_RANKS);
+  L.tot_norms = take(2 * (size_t)KSB_MAX_GROUP * sizeof(KsbNorms));  // sharded, ranks > 0: totals fetched from rank 0
+  L.tot_zone = take(2 * (size_t)KSB_MAX_GROUP * zone_stride * 4);
   // one-pod calls: header, dependency index and pool words travel inside the control block's single upload
   L.pod_slot = take(kPodSlotPool + (size_t)ksb_max_pool_words() * 8);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
@@ -62,7 +64,6 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   L.seg_max = take(halves * (size_t)G * nseg * 4);
   L.seg_cnt = take(halves * (size_t)G * nseg * 4);
   L.seg_mask = take(halves * (size_t)G * nseg * 32);
-  L.base0 = take(halves * (size_t)G * n_pad * 4);  // sharded engines: raw.x per (pod, global row) on rank 0
   L.total = off;
   return L;
 }
@@ -157,9 +158,18 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.rank = R == 1 ? 0 : cfg.shard_rank;
   a.segs_per_shard = segs_per_shard;
   a.nseg_total = nseg_total;
+  // accumulators and totals of the Reduce inputs: the targets themselves, except on ranks > 0 of a sharded engine
+  a.acc_norms = a.norms;
+  a.tot_norms = a.norms;
+  a.acc_zone_sum = a.zone_sum;
+  a.tot_zone_sum = a.zone_sum;
+  a.acc_ghist = a.ghist;
+  a.l_group_done = a.group_done;
   if (R > 1) {
     if (!shard_connected) throw std::runtime_error("sharded engine: call ksb_shard_export / ksb_shard_connect first");
     if (a.rank != 0) {  // the reduction targets and the cross-GPU barrier live in rank 0's memory
+      a.tot_norms = (KsbNorms*)(base + L.tot_norms);
+      a.tot_zone_sum = (int32_t*)(base + L.tot_zone);
       char* b0 = (char*)peer0_scratch;
       a.norms = (KsbNorms*)(b0 + L.norms);
       a.zone_sum = (int32_t*)(b0 + L.zone_sum);
@@ -169,9 +179,6 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
     }
   }
   // where the evaluation's results for phase 3 go: own arrays, or rank 0's (indexed by global row / segment)
-  a.gs_score = a.score;
-  a.gs_reasons = a.reasons;
-  a.gs_base0 = (int32_t*)(base + L.base0);
   a.gs_seg_max = a.seg_max;
   a.gs_seg_cnt = a.seg_cnt;
   a.gs_seg_mask = a.seg_mask;
@@ -181,9 +188,6 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
     // rank 0's scratch layout follows from the whole table's geometry, which every rank knows
     ScratchLayout L0 = scratch_layout(n_pad, zone_stride, std::max(1, nseg_total), group, pipe ? 2 : 1);
     char* b0 = (char*)peer0_scratch;
-    a.gs_score = (int32_t*)(b0 + L0.score);
-    a.gs_reasons = (uint32_t*)(b0 + L0.reasons);
-    a.gs_base0 = (int32_t*)(b0 + L0.base0);
     a.gs_seg_max = (int32_t*)(b0 + L0.seg_max);
     a.gs_seg_cnt = (int32_t*)(b0 + L0.seg_cnt);
     a.gs_seg_mask = (uint32_t*)(b0 + L0.seg_mask);

@@ -618,36 +618,93 @@ __device__ __forceinline__ void spin_until(KsbBatchArgs& A, const uint32_t* p, u
 }
 
 // Barrier over every block of every GPU holding a shard. Locally: a monotonically increasing arrival
-// counter (cooperative launch guarantees co-residency). Across GPUs: block 0 of each rank, once its own
+// counter (cooperative launch guarantees co-residency). Across GPUs: one block of each rank (`xb`), once its own
 // grid has arrived, bumps a counter in rank 0's memory over NVLink and waits for all ranks, then releases
 // its grid. With one rank it is a plain grid barrier.
-// `wait` false (one rank only): arrive without waiting; the block contributes nothing to the phase that ends here.
-__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true, int xb = 0) {
+// `wait` false: arrive without waiting; the block contributes nothing to the phase that ends here.
+// `push` runs on the crossing block after its grid has arrived and before the cross-GPU leg (the rank's partial
+// reductions go to rank 0 in one go instead of one NVLink atomic per block and value); `fetch` after it, before the
+// grid is released (totals and progress words come back once per rank instead of once per block).
+#if KSB_FINE_TIMING == 3
+__device__ long long g_xdbg[8];  // crossing block: cycles in local wait, push, cross-GPU leg, fetch
+#define KSB_XT(i)                                   \
+  do {                                              \
+    if (threadIdx.x == 0) {                         \
+      const long long n_ = clock64();               \
+      g_xdbg[i] += n_ - xt_;                        \
+      xt_ = n_;                                     \
+    }                                               \
+  } while (0)
+#else
+#define KSB_XT(i) ((void)0)
+#endif
+struct NoXfer {
+  __device__ __forceinline__ void operator()() const {}
+};
+template <class Push, class Fetch>
+__device__ __forceinline__ void grid_barrier_x(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait, int xb, Push push,
+                                               Fetch fetch) {
   __syncthreads();
-  if (threadIdx.x == 0) {
-    epoch += gridDim.x;
-    if (A.n_ranks == 1) {
+  if (A.n_ranks == 1) {
+    if (threadIdx.x == 0) {
+      epoch += gridDim.x;
       __threadfence();
       atomicAdd(A.barrier, 1u);
       if (wait) spin_until<false>(A, A.barrier, epoch, 1);
-    } else {
+    }
+    __syncthreads();
+    return;
+  }
+  const bool crossing = (int)blockIdx.x == xb;
+  // Which blocks write another GPU's memory between barriers: the crossing block (its pushes) and block 0 of rank 0
+  // (the writer warp's copies of committed rows, results and counters). Every other block only touches this GPU's
+  // memory and pays for a GPU-scope fence; the crossing block's system-scope fence after it has seen every local
+  // arrival carries their writes along.
+  const bool far_writer = crossing || (blockIdx.x == 0 && A.rank == 0);
+#if KSB_FINE_TIMING == 3
+  long long xt_ = clock64();
+#endif
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    if (far_writer) __threadfence_system();
+    else __threadfence();
+    if (crossing) KSB_XT(0);
+    atomicAdd(A.barrier, 1u);
+    if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
+    else if (wait) spin_until<false>(A, A.release, epoch, 4);
+  }
+  if (crossing) {
+    __syncthreads();
+    KSB_XT(1);
+    push();
+    __syncthreads();
+    KSB_XT(2);
+    if (threadIdx.x == 0) {
+      xepoch += (uint32_t)A.n_ranks;
       __threadfence_system();
-      atomicAdd(A.barrier, 1u);
-      if ((int)blockIdx.x == xb) {
-        spin_until<false>(A, A.barrier, epoch, 2);
-        xepoch += (uint32_t)A.n_ranks;
-        __threadfence_system();
-        atomicAdd_system(A.xbar, 1u);
-        spin_until<true>(A, A.xbar, xepoch, 3);
-        __threadfence_system();
-        atomicExch(A.release, epoch);
-      } else if (wait) {
-        spin_until<false>(A, A.release, epoch, 4);
-      }
+      KSB_XT(3);
+      atomicAdd_system(A.xbar, 1u);
+      spin_until<true>(A, A.xbar, xepoch, 3);
       __threadfence_system();
+      KSB_XT(4);
+    }
+    __syncthreads();
+    fetch();
+    __syncthreads();
+    KSB_XT(5);
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      atomicExch(A.release, epoch);
     }
   }
+  if (threadIdx.x == 0) {
+    if (far_writer) __threadfence_system();
+    else __threadfence();
+  }
   __syncthreads();
+}
+__device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true, int xb = 0) {
+  grid_barrier_x(A, epoch, xepoch, wait, xb, NoXfer(), NoXfer());
 }
 
 // The assume step on the chosen node: NodeInfo.AddPod (schedulercache/node_info.go:329-356) plus
@@ -1114,6 +1171,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       for (int i = threadIdx.x; i < 2 * kMaxG * KSB_REASON_BITS; i += kThreads) A.ghist[i] = 0;
       if (threadIdx.x < 2) A.group_done[threadIdx.x] = 0;
     }
+    if (A.rank != 0 && (int)blockIdx.x == xb) {  // this GPU's accumulators
+      for (int i = threadIdx.x; i < 2 * kMaxG * 8; i += kThreads)
+        reinterpret_cast<int32_t*>(A.acc_norms)[i] = ((i & 7) == 7) ? -1 : 0;
+      for (int i = threadIdx.x; i < 2 * kMaxG * A.zone_stride; i += kThreads) A.acc_zone_sum[i] = 0;
+      for (int i = threadIdx.x; i < 2 * kMaxG * KSB_REASON_BITS; i += kThreads) A.acc_ghist[i] = 0;
+      if (threadIdx.x < 8) A.l_group_done[threadIdx.x] = 0;
+    }
     grid_barrier(A, epoch, xepoch, true, xb);
   }
   // measurement state lives in shared memory (thread 0 of each block updates it; block 0's copy is reported): kept
@@ -1188,11 +1252,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     // Block 0 learns the evaluated group's size from here. Both published numbers are indexed by the parity of the
     // iteration, not of the group: a block that runs ahead into the next iteration then never overwrites a value that a
     // slower block has yet to read (scratch halves do not alternate in an iteration that evaluates nothing).
-    if (pipe && b == 1 && tid == 0) A.group_done[2 + (gi & 1)] = Gc;
+    if (pipe && b == 1 && tid == 0) A.l_group_done[2 + (gi & 1)] = Gc;  // (every rank derives the same number)
     const bool do_eval = !lag && Gc > 0 && !(shun_b != 0 && b == shun_b) && !(pipe && b == 0);
     KSB_TICK(0);
-    KsbNorms* norms = A.norms + (size_t)slot * kMaxG;
-    int32_t* zsum = A.zone_sum + (size_t)slot * kMaxG * zs;
+    // Reduce inputs of the group: accumulated per GPU (acc_*: the targets themselves on rank 0), pushed to rank 0's
+    // targets at the barrier after phase 1, read back as totals (tot_*: again the targets themselves on rank 0)
+    // (recomputed where used: held in registers across the loop body they would be spilled)
+#define cur_norms (A.norms + (size_t)slot * kMaxG)
+#define cur_zsum (A.zone_sum + (size_t)slot * kMaxG * zs)
+#define cur_acc_norms (A.acc_norms + (size_t)slot * kMaxG)
+#define cur_acc_zsum (A.acc_zone_sum + (size_t)slot * kMaxG * zs)
+#define cur_tot_norms (A.tot_norms + (size_t)slot * kMaxG)
+#define cur_tot_zsum (A.tot_zone_sum + (size_t)slot * kMaxG * zs)
+#define cur_acc_ghist (A.acc_ghist + (size_t)slot * kMaxG * KSB_REASON_BITS)
 
     // work split for phases 1 and 2: the (segment, pod) pairs, pod index fastest, are dealt to the blocks in
     // contiguous runs of equal length, so every block is busy whatever the ratio of segments to blocks
@@ -1216,9 +1288,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         RowCommon rc;
         if (live) load_row_common<false>(T, r, rc);
         size_t at = (half + (size_t)g_lo) * np + (size_t)r;  // this thread's slot in the (pod, row) stashes
-        // sharded: what phase 3 reads goes to rank 0's arrays, indexed by global row
-        size_t gat = MULTI ? (half + (size_t)g_lo) * (size_t)A.gs_np + (size_t)(T.row_base + r) : at;
-        for (int g = g_lo; g <= g_hi; ++g, at += np, gat += MULTI ? (size_t)A.gs_np : np) {
+        for (int g = g_lo; g <= g_hi; ++g, at += np) {
           const KsbPodHeader* h = S.hdr + g;
           int32_t fit = 0, mna = 0, mtt = 0, msc = 0, ipa = 0, hz = 0;
           if (live && !(h->flags & PF_SCHED_ERROR)) {
@@ -1241,8 +1311,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               raw = make_int4(INT32_MIN, 0, 0, 0);
             }
             A.raw[at] = raw;
-            A.gs_reasons[gat] = o.reasons;
-            if (MULTI) A.gs_base0[gat] = raw.x;
+            A.reasons[at] = o.reasons;
           }
           // Reduce inputs of this warp's 32 rows: ballots for the counts and flags, a redux only for the values the pod
           // can have at all (uniform per pod); this warp's own slot, so no atomics
@@ -1283,37 +1352,79 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           else if (f == 5) v = min(v, x);
           else v = max(v, x);
         }
-        int32_t* dst = reinterpret_cast<int32_t*>(norms + g) + f;
-        if (multi) {  // the reduction targets live in rank 0's memory: NVLink atomics
+        int32_t* dst = reinterpret_cast<int32_t*>(cur_acc_norms + g) + f;
+        if (f == 0) { if (v) atomicAdd(dst, v); }
+        else if (f == 5) { if (v) atomicMin(dst, v); }
+        else if (f == 7) { if (v >= 0) atomicMax(dst, v); }
+        else { if (v) atomicMax(dst, v); }
+      }
+      for (int g = warp; g < Gc; g += kWarps)
+        for (int z = lane; z < nz; z += 32)
+          if (S.zone[g * zs + z]) atomicAdd(&cur_acc_zsum[g * zs + z], S.zone[g * zs + z]);
+    }
+    KSB_TICK(1);
+    {
+      // sharded, ranks other than 0: this GPU's partial Reduce inputs go to rank 0's targets in one go, the totals
+      // come back into this GPU's copy once every rank has pushed
+      const bool far = MULTI && A.rank != 0;
+      auto push1 = [&] {
+        if constexpr (MULTI) {
+        if (!far) return;
+        // (group of at most 32 pods x 8 values: one value per thread; zones: only the interned ones, in one wave of
+        // independent reductions per thread, none of which returns a value)
+        if (tid < Gc * 8) {
+          const int f = tid & 7;
+          int32_t* src = reinterpret_cast<int32_t*>(cur_acc_norms) + tid;
+          int32_t* dst = reinterpret_cast<int32_t*>(cur_norms) + tid;
+          const int32_t v = __ldcg(src);
           if (f == 0) { if (v) atomicAdd_system(dst, v); }
           else if (f == 5) { if (v) atomicMin_system(dst, v); }
           else if (f == 7) { if (v >= 0) atomicMax_system(dst, v); }
           else { if (v) atomicMax_system(dst, v); }
-        } else {
-          if (f == 0) { if (v) atomicAdd(dst, v); }
-          else if (f == 5) { if (v) atomicMin(dst, v); }
-          else if (f == 7) { if (v >= 0) atomicMax(dst, v); }
-          else { if (v) atomicMax(dst, v); }
+          *src = f == 7 ? -1 : 0;
         }
-      }
-      for (int i = tid; i < Gc * zs; i += kThreads) {
-        int z = i % zs;
-        if (z < nz && S.zone[i]) {
-          if (multi) atomicAdd_system(&zsum[i], S.zone[i]);
-          else atomicAdd(&zsum[i], S.zone[i]);
+        for (int i = tid; i < Gc * nz; i += kThreads) {
+          const int at = (i / nz) * zs + (i % nz);
+          const int32_t v = __ldcg(cur_acc_zsum + at);
+          if (v) {
+            atomicAdd_system(&cur_zsum[at], v);
+            cur_acc_zsum[at] = 0;
+          }
         }
-      }
+        }
+      };
+      auto fetch1 = [&] {
+        if constexpr (MULTI) {
+        if (!far) return;
+        // every load over NVLink is issued before the first is stored: one round trip, not one per value
+        int32_t vn = 0, vz[4] = {0, 0, 0, 0};
+        if (tid < Gc * 8) vn = __ldcv(reinterpret_cast<const int32_t*>(cur_norms) + tid);
+        const int nzv = Gc * nz;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int i = tid + j * kThreads;
+          if (i < nzv) vz[j] = __ldcv(cur_zsum + (i / nz) * zs + (i % nz));
+        }
+        if (tid < Gc * 8) reinterpret_cast<int32_t*>(cur_tot_norms)[tid] = vn;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int i = tid + j * kThreads;
+          if (i < nzv) cur_tot_zsum[(i / nz) * zs + (i % nz)] = vz[j];
+        }
+        for (int i = tid + 4 * kThreads; i < nzv; i += kThreads)  // more than 1,024 (pod, zone) pairs: the slow way
+          cur_tot_zsum[(i / nz) * zs + (i % nz)] = __ldcv(cur_zsum + (i / nz) * zs + (i % nz));
+        }
+      };
+      grid_barrier_x(A, epoch, xepoch, !lag, xb, push1, fetch1);
     }
-    KSB_TICK(1);
-    grid_barrier(A, epoch, xepoch, !lag, xb);
     if (lag && tid == 0) s_b1_target = epoch;  // the writer warp holds its table writes until this barrier is complete
     KSB_TICK(2);
 
     // ---- phase 2: Reduce + weighted sum; per-segment (max, tie count) of every pod
     for (int i = tid; i < Gc * 8; i += kThreads)
-      reinterpret_cast<int32_t*>(S.norm)[i] = __ldcv(reinterpret_cast<const int32_t*>(norms) + i);
+      reinterpret_cast<int32_t*>(S.norm)[i] = __ldcv(reinterpret_cast<const int32_t*>(cur_tot_norms) + i);
     for (int g = warp; g < Gc; g += kWarps)
-      for (int z = lane; z < zs; z += 32) S.zone[g * zs + z] = z < nz ? __ldcv(zsum + g * zs + z) : 0;
+      for (int z = lane; z < zs; z += 32) S.zone[g * zs + z] = z < nz ? __ldcv(cur_tot_zsum + g * zs + z) : 0;
     __syncthreads();
     if (tid < Gc) {
       int32_t mz = 0;
@@ -1353,15 +1464,14 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         const int g_lo = seg == seg_lo ? it0 - seg_lo * Gc : 0;
         const int g_hi = seg == seg_hi ? it1 - 1 - seg_hi * Gc : Gc - 1;
         size_t at = (half + (size_t)g_lo) * np + (size_t)r;
-        size_t gat = MULTI ? (half + (size_t)g_lo) * (size_t)A.gs_np + (size_t)(T.row_base + r) : at;
-        for (int g = g_lo; g <= g_hi; ++g, at += np, gat += MULTI ? (size_t)A.gs_np : np) {
+        for (int g = g_lo; g <= g_hi; ++g, at += np) {
           const KsbPodHeader* h = S.hdr + g;
           const KsbNorms nm = S.norm[g];
           const bool prio = !(h->flags & (PF_SCHED_ERROR | PF_PRIO_ERROR)) && nm.fit_count >= 2;
           if (nm.fit_count == 0 && !(h->flags & PF_SCHED_ERROR)) {
             // no node fits: histogram of failure reasons for FitError.Error() (generic_scheduler.go:70-88),
             // one ballot per reason bit present in the warp; lane b owns bit b
-            const uint32_t m = live ? A.gs_reasons[gat] : 0u;
+            const uint32_t m = live ? A.reasons[at] : 0u;
             uint32_t un = __reduce_or_sync(0xffffffffu, m);
             int32_t acc = 0;
             while (un) {
@@ -1371,9 +1481,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               if (lane == bit) acc = c;
             }
             if (acc) {
-              int32_t* gp = A.ghist + ((size_t)slot * kMaxG + g) * KSB_REASON_BITS + lane;
-              if (multi) atomicAdd_system(gp, acc);
-              else atomicAdd(gp, acc);
+              atomicAdd(cur_acc_ghist + g * KSB_REASON_BITS + lane, acc);
             }
           }
           if (!prio) continue;  // uniform per (block, g)
@@ -1383,7 +1491,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (raw.x != INT32_MIN)
               s = final_score(T, nm, lut[g], S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
                               (uint32_t)raw.z & 0xffffffu, raw.w, zone);
-            A.gs_score[gat] = s;
+            A.score[at] = s;
           }
           int32_t wm = warp_max(s);
           const uint32_t wmask = __ballot_sync(0xffffffffu, s == wm && s != INT32_MIN);
@@ -1410,15 +1518,19 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
             }
             if (m == INT32_MIN) c = 0;
-            const size_t sat = (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + seg);
-            A.gs_seg_max[sat] = m;
-            A.gs_seg_cnt[sat] = c;
+            // this GPU's own arrays: on rank 0 (and with one rank) they are the arrays phase 3 reads, numbered by global
+            // segment; on the other ranks a staging area numbered by the rank's own segments
+            const bool direct = !MULTI || A.rank == 0;
+            const size_t sat = direct ? (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + seg)
+                                      : (half + (size_t)g) * (size_t)nseg + (size_t)seg;
+            A.seg_max[sat] = m;
+            A.seg_cnt[sat] = c;
             // which rows hold the segment's maximum: word w = rows 32w..32w+31 of the segment
             uint32_t mw[kWarps];
 #pragma unroll
             for (int w = 0; w < kWarps; ++w)
               mw[w] = (S.wstat[(g * kWarps + w) * 3] == m && m != INT32_MIN) ? (uint32_t)S.wstat[(g * kWarps + w) * 3 + 2] : 0u;
-            uint4* mp = reinterpret_cast<uint4*>(A.gs_seg_mask + sat * kWarps);
+            uint4* mp = reinterpret_cast<uint4*>(A.seg_mask + sat * kWarps);
             mp[0] = make_uint4(mw[0], mw[1], mw[2], mw[3]);
             mp[1] = make_uint4(mw[4], mw[5], mw[6], mw[7]);
           }
@@ -1427,7 +1539,41 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
     }
     KSB_TICK(3);
-    if (!pipe) grid_barrier(A, epoch, xepoch, true, xb);  // pipelined: block 0 decides while the others are in phases 1-2
+    // FitError histograms of the group: this GPU's partial counts go to rank 0 before phase 3 reads them (plain
+    // schedule: at the barrier before phase 3; pipelined: at the barrier that ends the iteration)
+    auto push_hist = [&] {
+      if constexpr (MULTI) {
+      if (A.rank == 0) return;
+      // this GPU's per-segment statistics of the group, into rank 0's arrays at the global segment numbers
+      for (int i = tid; i < Gc * nseg; i += kThreads) {
+        const int g = i / nseg, sg = i - g * nseg;
+        const size_t src = (half + (size_t)g) * (size_t)nseg + (size_t)sg;
+        const size_t dst = (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + sg);
+        const uint4* ms = reinterpret_cast<const uint4*>(A.seg_mask + src * kWarps);
+        const int32_t vmx = __ldcg(A.seg_max + src), vct = __ldcg(A.seg_cnt + src);
+        const uint4 m0 = __ldcg(ms), m1 = __ldcg(ms + 1);
+        uint4* md = reinterpret_cast<uint4*>(A.gs_seg_mask + dst * kWarps);
+        A.gs_seg_max[dst] = vmx;
+        A.gs_seg_cnt[dst] = vct;
+        md[0] = m0;
+        md[1] = m1;
+      }
+      for (int i = tid; i < Gc * KSB_REASON_BITS; i += kThreads) {
+        const int32_t v = __ldcg(cur_acc_ghist + i);
+        if (v) {
+          atomicAdd_system(A.ghist + (size_t)slot * kMaxG * KSB_REASON_BITS + i, v);
+          cur_acc_ghist[i] = 0;
+        }
+      }
+      }
+    };
+    // how far the commit got (rank 0 writes it before it arrives): one NVLink read per rank, not per block
+    auto fetch_done = [&] {
+      if constexpr (MULTI) {
+        if (A.rank != 0 && tid < 2) A.l_group_done[tid] = __ldcv(A.group_done + tid);
+      }
+    };
+    if (!pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, NoXfer());  // pipelined: block 0 decides while the others are in phases 1-2
     KSB_TICK(4);
 
     // ---- phase 3: block 0 of rank 0 commits the group's pods in order. Rows of other shards are reached
@@ -1509,10 +1655,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         in.m1 = in.m0;
         if (in.act) {
           const KsbPeer& P = PEER(prank);
-          const size_t at = (half + g) * P.table.n_pad + crow;
-          in.base0 = MULTI ? __ldcv(A.gs_base0 + at) : __ldcv(&P.raw[at].x);
-          in.reasons0 = __ldcv(P.reasons + at);
-          in.score0 = __ldcv(P.score + at);
+          // sharded: the group-start results stay on the GPU that evaluated the row (three loads over NVLink per changed
+          // row and pod; pushing every rank's results to rank 0 instead made NVLink writes the bottleneck)
+          const KsbPeer& O = PEER(MULTI ? min(R - 1, (crow / kSeg) / sps) : 0);
+          const size_t at = (half + g) * (size_t)O.raw_np + (size_t)(crow - O.raw_row0);
+          in.base0 = __ldcv(&O.raw[at].x);
+          in.reasons0 = __ldcv(O.reasons + at);
+          in.score0 = __ldcv(O.score + at);
           const int ls = crow / kSeg;
           const int gseg = P.seg_base + ls;
           const int32_t* cum = S.cum + g * nsegT;
@@ -1766,7 +1915,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         t3_mark = clock64();
         s_tk[14] += t3_mark - s_tk[8];
       }
-#if KSB_FINE_TIMING
+#if KSB_FINE_TIMING == 1
       long long f3_mark = clock64();
 #define KSB_F3(i)                         \
   do {                                    \
@@ -1837,10 +1986,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   crow = c.row;
                   crank = c.pad & 0xff;
                   const KsbPeer& P = PEER(crank);
-                  const size_t at = (half + g) * P.table.n_pad + crow;
-                  const int32_t base0 = MULTI ? __ldcv(A.gs_base0 + at) : __ldcv(&P.raw[at].x);  // INT32_MIN = the row did not fit at group start
-                  old_reasons = __ldcv(P.reasons + at);
-                  if (prio) cold = __ldcv(P.score + at);
+                  const KsbPeer& O = PEER(MULTI ? min(R - 1, (crow / kSeg) / sps) : 0);  // the GPU that evaluated the row
+                  const size_t at = (half + g) * (size_t)O.raw_np + (size_t)(crow - O.raw_row0);
+                  const int32_t base0 = __ldcv(&O.raw[at].x);  // INT32_MIN = the row did not fit at group start
+                  old_reasons = __ldcv(O.reasons + at);
+                  if (prio) cold = __ldcv(O.score + at);
                   int32_t base;
                   eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
                   const bool was_fit = base0 != INT32_MIN;
@@ -2377,11 +2527,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
     }
     // pipelined: the evaluation side has read the table and finished phase 2; the commit side has decided and written
-    grid_barrier(A, epoch, xepoch, true, xb);
+    if (pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, fetch_done);
+    else grid_barrier_x(A, epoch, xepoch, true, xb, NoXfer(), fetch_done);
     KSB_TICK(6);
     if (__ldcg(A.error_flag) != 0) break;  // only after a barrier timeout: stop instead of spinning
     if (!pipe) {
-      const int adv = __ldcv(A.group_done + (gi & 1));
+      const int adv = __ldcv(A.l_group_done + (gi & 1));
       if (adv <= 0) {
         if (tid == 0) atomicCAS(A.error_flag, 0, 5);
         break;
@@ -2390,8 +2541,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       ev_slot ^= 1;
     } else {
       // every block draws the same conclusions from the two published numbers
-      const int ge = ev_valid ? __ldcv(A.group_done + 2 + (gi & 1)) : 0;  // pods evaluated in this iteration
-      const int adv = cm_valid ? __ldcv(A.group_done + (gi & 1)) : 0;    // pods committed in this iteration
+      const int ge = ev_valid ? __ldcv(A.l_group_done + 2 + (gi & 1)) : 0;  // pods evaluated in this iteration
+      const int adv = cm_valid ? __ldcv(A.l_group_done + (gi & 1)) : 0;    // pods committed in this iteration
       if (cm_valid && adv < cm_G) {
         // speculation was dropped inside the committed group: everything evaluated after it is void. The next
         // evaluation starts at the first uncommitted pod, against a table that holds every commit so far.
@@ -2422,9 +2573,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     gi += 1;
   }
   if (b == 0 && tid == 0) {
+#if KSB_FINE_TIMING < 2
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[i];  // block 0's cycles per stage
+#endif
+#if KSB_FINE_TIMING != 3
     for (int i = 0; i < 5; ++i) A.counters[9 + i] = (uint64_t)s_tk[11 + i];  // phase-3 breakdown
-#if KSB_FINE_TIMING
+#endif
+#if KSB_FINE_TIMING == 1
     // instead: cycles of thread 0 in phase 3 by step: picks, own columns, wait for the other columns, finalize, one-pod path
     A.counters[9] = (uint64_t)s_tk[18];
     A.counters[10] = (uint64_t)s_tk[19];
@@ -2439,8 +2594,33 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     }
   }
   if (multi && b == xb && tid == 0) *A.xstate = xepoch;
+#if KSB_FINE_TIMING == 2
+  if (b == (pipe ? 1 : 0) && tid == 0)  // FINE_TIMING=2: an evaluating block's stage cycles instead of block 0's
+    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[i];
+#endif
+#if KSB_FINE_TIMING == 3
+  if (multi && b == xb && tid == 0)
+    for (int i = 0; i < 7; ++i) {
+      A.counters[2 + i] = (uint64_t)g_xdbg[i];
+      g_xdbg[i] = 0;
+    }
+  if (multi && b == xb && tid == 0) {  // the same block's stage cycles next to them
+    A.counters[9] = (uint64_t)s_tk[0];
+    A.counters[10] = (uint64_t)s_tk[1];
+    A.counters[11] = (uint64_t)s_tk[2];
+    A.counters[12] = (uint64_t)s_tk[3];
+    A.counters[13] = (uint64_t)s_tk[6];
+  }
+#endif
 #undef KSB_TICK
 #undef PEER
+#undef cur_norms
+#undef cur_zsum
+#undef cur_acc_norms
+#undef cur_acc_zsum
+#undef cur_tot_norms
+#undef cur_tot_zsum
+#undef cur_acc_ghist
 #undef raw_s
 #undef score_s
 #undef reasons_s
@@ -2605,9 +2785,12 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->peers = (const KsbPeer*)(b + kNaPeer);
   a->fiterr_hist = (int32_t*)(b + kNaFitHist);
   a->fiterr_cap = KSB_MAX_FITERR;
-  a->gs_score = a->score;
-  a->gs_reasons = a->reasons;
-  a->gs_base0 = nullptr;
+  a->acc_norms = a->norms;
+  a->tot_norms = a->norms;
+  a->acc_zone_sum = a->zone_sum;
+  a->tot_zone_sum = a->zone_sum;
+  a->acc_ghist = a->ghist;
+  a->l_group_done = a->group_done;
   a->gs_seg_max = a->seg_max;
   a->gs_seg_cnt = a->seg_cnt;
   a->gs_seg_mask = a->seg_mask;

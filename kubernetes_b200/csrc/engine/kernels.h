@@ -55,18 +55,24 @@ struct KsbBatchArgs {
   int32_t* group_done;          // [8] pods consumed by the group, ping-pong; pipelined: [2..3] size of the group evaluated, [4] block 0's SM, [5] the block sharing it
   uint64_t* counters;           // [16] groups run, groups cut short by a dropped speculation, stage cycles
   int32_t* ghist;               // [2][KSB_MAX_GROUP][KSB_REASON_BITS] reason histograms of no-fit pods, ping-pong
-  // Where the evaluation's results for phase 3 go: this GPU's own arrays with one rank; with several ranks rank 0's
-  // arrays (every rank writes its rows' results there over NVLink, indexed by GLOBAL row / segment), because phase 3
-  // runs on rank 0 against its own full copy of the node table and never reads another GPU's memory on its chain.
-  int32_t* gs_score;            // [halves * group_size][gs_np]
-  uint32_t* gs_reasons;
-  int32_t* gs_base0;            // sharded only: raw.x per (pod, global row); one rank reads raw itself
+  // Where the per-segment statistics of phase 2 go: this GPU's own arrays with one rank; with several ranks rank 0's
+  // arrays (every rank writes its segments' statistics there over NVLink, indexed by GLOBAL segment), because phase 3
+  // runs on rank 0 against its own full copy of the node table. The per-(pod, row) results stay where they were
+  // computed; phase 3 reads the few it needs (changed rows) from there.
   int32_t* gs_seg_max;          // [halves * group_size][gs_nseg]
   int32_t* gs_seg_cnt;
   uint32_t* gs_seg_mask;
   int32_t gs_np, gs_nseg;
   int32_t seg_gbase;            // global index of this rank's first evaluated segment
   int32_t eval_n;               // rows this rank evaluates: rows [0, eval_n) of its table (rank 0's table holds all rows)
+  // Reduce inputs: accumulated per GPU, pushed to rank 0's targets (norms / zone_sum / ghist above) at a barrier,
+  // read back as totals. On rank 0 and with one rank all of these are the targets themselves.
+  KsbNorms* acc_norms;
+  KsbNorms* tot_norms;
+  int32_t* acc_zone_sum;
+  int32_t* tot_zone_sum;
+  int32_t* acc_ghist;
+  int32_t* l_group_done;        // this GPU's copy of group_done
   // sharding (n_ranks == 1: everything local). With n_ranks > 1 the reduction targets above (norms, zone_sum,
   // ghist, group_done) and xbar point into rank 0's memory on every rank.
   const KsbPeer* peers;         // [n_ranks], dereferenced by rank 0 only

@@ -12,6 +12,7 @@ from kubernetes_b200 import lib, workloads
 
 cfg, nodes, pods = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
 gsize = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+pipeline = int(sys.argv[5]) if len(sys.argv) > 5 else 0
 rank = int(os.environ.get("RANK", "0"))
 world = int(os.environ.get("WORLD_SIZE", "1"))
 local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -20,7 +21,7 @@ dist.init_process_group("gloo")
 cluster = workloads.generate(cfg, nodes, pods)
 sess = lib.Session(cluster=cluster)
 ref = sess.run(device=local, results=False) if rank == 0 else None
-eng = lib.OpenEngine(sess, device=local, shard_rank=rank, shard_count=world, group_size=gsize)
+eng = lib.OpenEngine(sess, device=local, shard_rank=rank, shard_count=world, group_size=gsize, pipeline=pipeline)
 blob = eng.shard_export(pods)
 blobs = [None] * world
 dist.all_gather_object(blobs, blob)
