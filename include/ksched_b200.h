@@ -136,6 +136,12 @@ int32_t ksb_flush(ksb_engine* e);
  * FitError carries and nodesWherePreemptionMightHelp :957-991 reads): masks[i] has bit b set when node row i failed
  * for reason b; 0 = the node fitted. `n` must be at least the number of node rows (ksb_result.num_nodes). */
 int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n);
+/* HostPriorityList of the most recent single-pod ksb_schedule (what PrioritizeNodes returns,
+ * core/generic_scheduler.go:509-640, api/types.go:204-227): scores[i] = weighted total of node row i, INT64_MIN for a
+ * row that was filtered out. The reference only prioritizes when at least two nodes fit (:144-149); with fewer the
+ * call fails. `n` must be at least the number of node rows. Lets a test compare the whole list, as the reference's
+ * priority tests do (priorities/test_util.go:45-61), not only the winner. */
+int32_t ksb_scores(ksb_engine* e, int64_t* scores, int32_t n);
 /* Text of failure reason `bit` as predicates/error.go:33-54, :84-86 spells it ("Insufficient cpu",
  * "MatchNodeSelector", ...); for the extended-resource bits, the text for the pod of the last call. Empty if unused. */
 int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len);

@@ -196,6 +196,13 @@ int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n) {
   });
 }
 
+int32_t ksb_scores(ksb_engine* e, int64_t* scores, int32_t n) {
+  return guarded(e, [&] {
+    if (!scores) throw std::runtime_error("scores must not be null");
+    e->impl->scores(scores, n);
+  });
+}
+
 int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len) {
   return guarded(e, [&] {
     std::string t = e->impl->reason_name(bit);

@@ -790,9 +790,14 @@ void Engine::rebuild_layout() {
   for (int r = 0; r < n; ++r) fill_row(r);
   build_label_index();  // here, not inside the first Schedule that mentions a new label
   // per-class counters follow the pods: recount them all
-  for (auto& t : tables) std::fill(t.vals.begin(), t.vals.end(), 0);
+  // (a table first registered here is created with the existing pods already counted: zero AFTER registering, or
+  // those pods are counted twice by the recount below)
   for (auto& kv : pods) register_pod_classes(kv.second.pod);
-  for (auto& t : tables) t.vals.resize(topo_values[t.topo].size() + 1, 0);
+  for (auto& t : tables) {
+    t.vals.resize(topo_values[t.topo].size() + 1, 0);
+    std::fill(t.vals.begin(), t.vals.end(), 0);
+  }
+  for (auto& c : h_spread) c.assign((size_t)n_pad, 0u);  // the same for SelectorSpread columns created just now
   for (auto& kv : pods) {
     const Pod& p = kv.second.pod;
     auto nit = nodes.find(p.node_name);

@@ -123,6 +123,7 @@ class Engine {
   std::string node_info_json(const std::string& name);
   void grow_keep(DevBuf& b, size_t bytes);
   void failed_predicates(uint32_t* out, int32_t n_out);
+  void scores(int64_t* out, int32_t n_out);
   std::string reason_name(int bit);
   void replay_last_batch(int iters, double* avg_ms, ksb_result* out);
   void replay_last_batch_noalloc(ksb_result* out);

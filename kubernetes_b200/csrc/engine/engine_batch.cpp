@@ -969,6 +969,30 @@ void Engine::failed_predicates(uint32_t* out, int32_t n_out) {
   stats.d2h_bytes += (size_t)n * 4;
 }
 
+// HostPriorityList of the most recent ksb_schedule (core/generic_scheduler.go:509-640): the per-row totals phase 2 left
+// in the scratch buffer; rows outside the filtered list are INT64_MIN.
+void Engine::scores(int64_t* out, int32_t n_out) {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  if (cfg.shard_count > 1) throw std::runtime_error("ksb_scores: not available on a sharded engine");
+  if (last_results.size() != 1) throw std::runtime_error("ksb_scores: the last call was not a single-pod ksb_schedule");
+  if (n_out < n) throw std::runtime_error("ksb_scores: buffer holds fewer entries than there are node rows");
+  if (last_results[0].num_filtered < 2)
+    throw std::runtime_error("ksb_scores: fewer than two nodes fitted, so nothing was prioritized (generic_scheduler.go:144-149)");
+  if (n == 0) return;
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
+  std::vector<int32_t> raw((size_t)n);
+  CUDA_OK(cudaMemcpyAsync(raw.data(), (char*)b_scratch.d + L.score, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));
+  stats.d2h_bytes += (size_t)n * 4;
+  for (int i = 0; i < n; ++i) out[i] = raw[i] == INT32_MIN ? INT64_MIN : (int64_t)raw[i];
+  if (getenv("KSB_SCORES_RAW")) {  // debugging aid: the raw InterPodAffinity sums (Map half) instead of the totals
+    std::vector<int32_t> r4((size_t)n * 4);
+    CUDA_OK(cudaMemcpy(r4.data(), (char*)b_scratch.d + L.raw, (size_t)n * 16, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < n; ++i) out[i] = r4[(size_t)i * 4] == INT32_MIN ? INT64_MIN : (int64_t)r4[(size_t)i * 4 + 3];
+  }
+}
+
 std::string Engine::reason_name(int bit) {
   std::lock_guard<std::mutex> g(mu);
   static const char* fixed[KSB_REASON_BITS] = {

@@ -99,6 +99,8 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   std::vector<ExtendedResourceBinding> bindings(np);
   std::vector<std::string> failed_json(np);  // "failed_predicates": per pod, {node: [reasons]} of the nodes that did not fit
   const bool want_failed = opt.get_bool("failed_predicates", false);
+  const bool want_scores = opt.get_bool("scores", false);  // "scores": per pod, {node: total} over the filtered list (batch 0 only)
+  std::vector<std::string> scores_json(np);
   GpuScheduler sched(h);
   CacheDecorator cache(h);
   double kernel_ms = 0, encode_ms = 0, replay_ms = 0, decode_ms = 0, post_ms = 0, sync_ms = 0;
@@ -150,6 +152,21 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
           fj += "]";
         }
         failed_json[i] = fj + "}";
+      }
+      if (want_scores && r.status == KSB_SCHEDULED && r.num_filtered >= 2) {
+        std::vector<int64_t> sc((size_t)r.num_nodes);
+        h.check(ksb_scores(h.get(), sc.data(), r.num_nodes), "scores");
+        std::string sj = "{";
+        bool first_node = true;
+        for (int32_t row = 0; row < r.num_nodes; ++row) {
+          if (sc[row] == INT64_MIN) continue;
+          const char* nm = nullptr;
+          size_t nl = 0;
+          h.check(ksb_node_name(h.get(), row, &nm, &nl), "node_name");
+          sj += std::string(first_node ? "" : ",") + esc(std::string(nm, nl)) + ":" + std::to_string(sc[row]);
+          first_node = false;
+        }
+        scores_json[i] = sj + "}";
       }
       try {
         ScheduleOutcome o = sched.outcome(pod, r, 0);
@@ -291,6 +308,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
       out += "{\"host\":" + esc(hosts[i]) + ",\"status\":" + std::to_string(results[i].status) +
              ",\"filtered\":" + std::to_string(results[i].num_filtered) + ",\"score\":" + std::to_string(results[i].score) +
              ",\"message\":" + esc(messages[i]) + (failed_json[i].empty() ? std::string() : ",\"failed\":" + failed_json[i]) +
+             (scores_json[i].empty() ? std::string() : ",\"scores\":" + scores_json[i]) +
              ",\"devices\":{";
       bool first = true;
       for (auto& kv : bindings[i]) {

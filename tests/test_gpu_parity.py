@@ -220,12 +220,15 @@ def test_golden_predicates_on_gpu():
 
 
 def test_golden_priorities_on_gpu():
-    """Every transcribed priority vector: schedule the pod with only that priority weighted and check
-    the winning score and winner set against the golden list."""
+    """Every transcribed priority vector: schedule the pod with only that priority weighted and compare the WHOLE
+    HostPriorityList (ksb_scores) with the golden list, as the reference's tests do with reflect.DeepEqual
+    (priorities/test_util.go:45-61). Cases in which a predicate removes a node are counted, not silently skipped:
+    the golden lists are computed without predicates, so only the nodes that stayed are compared there."""
     names = {"LeastRequestedPriority", "BalancedResourceAllocation", "SelectorSpreadPriority", "NodeAffinityPriority",
              "TaintTolerationPriority", "InterPodAffinityPriority", "NodePreferAvoidPodsPriority"}
     with open(os.path.join(HERE, "golden", "reference_vectors.json")) as f:
         cases = [c for c in json.load(f)["cases"] if c["op"] == "priority"]
+    whole = partial = skipped = 0
     for c in cases:
         cl = _as_stream(c)
         for n in cl["nodes"]:  # priorities are tested without predicates in the reference: make every node fit
@@ -235,11 +238,23 @@ def test_golden_priorities_on_gpu():
         best = max(scores.values())
         winners = {h for h, s in scores.items() if s == best}
         sess = lib.Session(cluster=cl)
-        out = sess.run(weights=weights, hardPodAffinityWeight=c.get("hardPodAffinityWeight", 1))
+        out = sess.run(batch=0, scores=True, weights=weights, hardPodAffinityWeight=c.get("hardPodAffinityWeight", 1))
         sess.close()
         r = out["results"][0]
-        if r["status"] != 0 or r["filtered"] != len(scores):
-            continue  # a predicate removed a node: the golden list (computed without predicates) does not apply
-        assert r["host"] in winners, (c["source"], c["test"], r, scores)
-        if len(scores) > 1:
-            assert r["score"] == best, (c["source"], c["test"], r, scores)
+        if r["status"] != 0 or r["filtered"] < 2:
+            skipped += 1  # fewer than two nodes fit: the reference does not prioritize at all
+            continue
+        got = r["scores"]
+        if r["filtered"] == len(scores):
+            assert got == scores, (c["source"], c["test"], got, scores)
+            assert r["host"] in winners and r["score"] == best, (c["source"], c["test"], r, scores)
+            whole += 1
+        else:
+            # a predicate removed nodes; priorities whose Reduce normalises over the filtered list may legitimately
+            # differ from the golden list then, the Map-only ones may not
+            if c["name"] in ("LeastRequestedPriority", "BalancedResourceAllocation", "NodePreferAvoidPodsPriority"):
+                assert all(got[h] == scores[h] for h in got), (c["source"], c["test"], got, scores)
+            partial += 1
+    assert whole + partial + skipped == len(cases)
+    print("priority vectors: %d whole lists, %d partial, %d not prioritized" % (whole, partial, skipped))
+    assert whole >= 70, (whole, partial, skipped)
