@@ -50,7 +50,7 @@ typedef struct ksb_config {
   int32_t shard_count;              /* number of shards (1 when unsharded) */
   int32_t group_size;               /* pods evaluated per speculative group (0 = default) */
   int32_t pipeline;                 /* overlap a group's commit with the next group's evaluation: 0 = automatic
-                                       (on from 16,384 node rows, one GPU), 1 = on, -1 = off */
+                                       (on from 16,384 node rows, any shard count), 1 = on, -1 = off */
 } ksb_config;
 
 /* Fill *cfg with the DefaultProvider values (algorithmprovider/defaults/defaults.go:217-257). */
@@ -132,6 +132,17 @@ int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_le
  * Schedule; calling it after the informers' initial sync keeps that cost out of the first pod's latency. */
 int32_t ksb_flush(ksb_engine* e);
 
+/* Recovery (the reference rebuilds its cache from LIST+WATCH after a restart,
+ * plugin/cmd/kube-scheduler/app/server.go:593-598, factory/factory.go:948 WaitForCacheSync; this is the same for the
+ * device mirror after a CUDA error or whenever the caller's cache and the engine may have drifted apart).
+ * ksb_resync_begin forgets every node, pod and selector owner and clears the device's sticky error state; the caller
+ * then replays its cache (ksb_node_upsert / ksb_selector_owner_upsert / ksb_pod_add for every object it holds) and
+ * calls ksb_resync_end, which rebuilds the device table from those records (same work as ksb_flush). The dictionaries
+ * (label bits, classes) and lastNodeIndex survive: they do not depend on cluster state. Not to be called while a
+ * ksb_schedule* call is running. */
+int32_t ksb_resync_begin(ksb_engine* e);
+int32_t ksb_resync_end(ksb_engine* e);
+
 /* FailedPredicateMap of the most recent single-pod ksb_schedule (core/generic_scheduler.go:283-362, the map that
  * FitError carries and nodesWherePreemptionMightHelp :957-991 reads): masks[i] has bit b set when node row i failed
  * for reason b; 0 = the node fitted. `n` must be at least the number of node rows (ksb_result.num_nodes). */
@@ -201,17 +212,21 @@ int32_t ksb_shard_connect(ksb_engine* e, const uint8_t* blobs, const uint64_t* o
 /* No counterpart in the reference. One run of what ksb_replay_last_batch runs (the resident batch,
  * against the restored node table), for callers that must not allocate GPU memory while they work:
  * a process confined to a fixed memory budget (a MIG slice or an MPS client with a hard limit, where
- * a late cudaMalloc can fail), or code called back on another component's stream, where the
- * device-wide synchronisation hidden in cudaMalloc/cudaFree would stall work that is not ours. This
- * entry point calls no cudaMalloc, cudaFree or other allocating routine: the kernel's working memory
- * is a fixed array inside the loaded library (about 2.4 MiB, held by every GPU that loads the library
- * until the process exits), state is restored into buffers that already exist, and results are
- * written directly into `out` (one ksb_result per pod of the batch, caller-owned).
+ * a late cudaMalloc can fail). This entry point calls no cudaMalloc, cudaFree or other allocating
+ * routine: the kernel's working memory is a fixed array inside the loaded library (about 2.4 MiB, held
+ * by every GPU that loads the library until the process exits) and state is restored into buffers that
+ * already exist.
+ *  - It runs on the engine's own stream and is synchronous: the kernel writes the engine's result
+ *    buffer, a device-to-host copy into `out` (one ksb_result per pod of the batch, caller-owned, pageable
+ *    or pinned) follows, and the call returns after cudaStreamSynchronize. It cannot be captured into a
+ *    CUDA graph and does not run on a caller's stream.
+ *  - Valid only directly after the ksb_schedule_batch it repeats: any mutator, ksb_flush or layout
+ *    rebuild in between makes it (and ksb_replay_last_batch) fail with "no batch to replay".
  *  - Limits: at most 65,536 padded node rows (node count rounded up to 256), 1,024 zone slots and
- *    1,024 thread blocks; a batch beyond them is rejected with an error naming the limit.
+ *    1,024 thread blocks; a batch beyond them is rejected with an error naming the limit. Engines
+ *    created with shard_count > 1 are refused.
  *  - The first call on a GPU looks up that GPU's address of the array (cudaGetSymbolAddress, with
- *    the engine's device current) and caches it: make that first call before starting any stream
- *    capture.
+ *    the engine's device current) and caches it.
  *  - Every call, from every engine in the process, shares the one array, and the array keeps what
  *    the last call left in it; the counters that must start at zero are cleared on each call. Two
  *    calls whose kernels overlap on one GPU would race on it: serialise them. */

@@ -1,0 +1,220 @@
+package gpusched
+
+// scheduler.go: algorithm.ScheduleAlgorithm (plugin/pkg/scheduler/algorithm/scheduler_interface.go:48-61) over the
+// C-ABI. Constructed at plugin/pkg/scheduler/factory/factory.go:936 in place of core.NewGenericScheduler; the
+// generic scheduler is still built and kept for Preempt / Predicates / Prioritizers, never for Schedule.
+// Source only: see the package comment in encode.go.
+
+/*
+#cgo LDFLAGS: -lksched_b200
+#include <stdlib.h>
+#include "ksched_b200.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"sync"
+	"unsafe"
+
+	"k8s.io/api/core/v1"
+	"k8s.io/kubernetes/plugin/pkg/scheduler/algorithm"
+	"k8s.io/kubernetes/plugin/pkg/scheduler/algorithm/predicates"
+	"k8s.io/kubernetes/plugin/pkg/scheduler/core"
+	"k8s.io/kubernetes/plugin/pkg/scheduler/schedulercache"
+)
+
+// the predicate / priority keys the engine implements (algorithmprovider/defaults/defaults.go:119-184, 217-257)
+var supportedPredicates = map[string]bool{
+	"GeneralPredicates": true, "PodToleratesNodeTaints": true, "CheckNodeCondition": true,
+	"CheckNodeMemoryPressure": true, "CheckNodeDiskPressure": true, "MatchInterPodAffinity": true,
+	// volume predicates are registered by the DefaultProvider and are trivially true for pods without volumes; the
+	// engine refuses pods that have volumes (no CPU fallback), so accepting the keys is safe
+	"NoVolumeZoneConflict": true, "MaxEBSVolumeCount": true, "MaxGCEPDVolumeCount": true,
+	"MaxAzureDiskVolumeCount": true, "NoDiskConflict": true, "CheckVolumeBinding": true,
+}
+
+var weightField = map[string]func(*C.ksb_config, C.int32_t){
+	"LeastRequestedPriority":      func(c *C.ksb_config, w C.int32_t) { c.w_least_requested = w },
+	"BalancedResourceAllocation":  func(c *C.ksb_config, w C.int32_t) { c.w_balanced = w },
+	"SelectorSpreadPriority":      func(c *C.ksb_config, w C.int32_t) { c.w_selector_spread = w },
+	"NodeAffinityPriority":        func(c *C.ksb_config, w C.int32_t) { c.w_node_affinity = w },
+	"TaintTolerationPriority":     func(c *C.ksb_config, w C.int32_t) { c.w_taint_toleration = w },
+	"InterPodAffinityPriority":    func(c *C.ksb_config, w C.int32_t) { c.w_inter_pod_affinity = w },
+	"NodePreferAvoidPodsPriority": func(c *C.ksb_config, w C.int32_t) { c.w_prefer_avoid = w },
+}
+
+// GPUScheduler implements algorithm.ScheduleAlgorithm.
+type GPUScheduler struct {
+	mu      sync.Mutex // Schedule is called from one goroutine (scheduler.go:179); the lock documents it
+	e       *C.ksb_engine
+	generic algorithm.ScheduleAlgorithm
+}
+
+// New refuses any predicate or priority key outside the DefaultProvider set: there is no CPU fallback for Schedule.
+func New(predicateKeys []string, priorityWeights map[string]int, hardPodAffinityWeight int32,
+	generic algorithm.ScheduleAlgorithm) (*GPUScheduler, error) {
+	for _, k := range predicateKeys {
+		if !supportedPredicates[k] {
+			return nil, fmt.Errorf("gpusched: predicate %q is not implemented by the GPU engine", k)
+		}
+	}
+	var cfg C.ksb_config
+	C.ksb_config_default(&cfg)
+	for name, set := range weightField {
+		set(&cfg, 0) // a priority that is not configured does not count
+		_ = name
+	}
+	for name, w := range priorityWeights {
+		set, ok := weightField[name]
+		if !ok {
+			return nil, fmt.Errorf("gpusched: priority %q is not implemented by the GPU engine", name)
+		}
+		set(&cfg, C.int32_t(w))
+	}
+	cfg.hard_pod_affinity_weight = C.int32_t(hardPodAffinityWeight)
+	var errbuf [512]C.char
+	e := C.ksb_create(&cfg, &errbuf[0], 512)
+	if e == nil {
+		return nil, fmt.Errorf("ksb_create: %s", C.GoString(&errbuf[0]))
+	}
+	return &GPUScheduler{e: e, generic: generic}, nil
+}
+
+func (g *GPUScheduler) lastError() error { return fmt.Errorf("%s", C.GoString(C.ksb_last_error(g.e))) }
+
+func bytesPtr(b []byte) (*C.uint8_t, C.size_t) {
+	if len(b) == 0 {
+		return nil, 0
+	}
+	return (*C.uint8_t)(unsafe.Pointer(&b[0])), C.size_t(len(b))
+}
+
+// Schedule: genericScheduler.Schedule (core/generic_scheduler.go:109-161) on the device.
+func (g *GPUScheduler) Schedule(pod *v1.Pod, nodeLister algorithm.NodeLister) (string, v1.ExtendedResourceBinding, error) {
+	g.mu.Lock()
+	defer g.mu.Unlock()
+	buf := encodePod(pod)
+	p, n := bytesPtr(buf)
+	var r C.ksb_result
+	if C.ksb_schedule(g.e, p, n, &r) != 0 {
+		return "", nil, g.lastError()
+	}
+	switch r.status {
+	case C.KSB_NO_NODES:
+		return "", nil, core.ErrNoNodesAvailable
+	case C.KSB_FIT_ERROR:
+		return "", nil, g.fitError(pod, int(r.num_nodes))
+	case C.KSB_SCHEDULE_ERROR:
+		return "", nil, g.lastError()
+	}
+	var name *C.char
+	var nameLen C.size_t
+	if C.ksb_node_name(g.e, r.node_index, &name, &nameLen) != 0 {
+		return "", nil, fmt.Errorf("gpusched: node row %d has no name", int(r.node_index))
+	}
+	host := C.GoStringN(name, C.int(nameLen))
+	return host, g.binding(pod, &r), nil
+}
+
+// binding: device bit masks -> v1.ExtendedResourceBinding (resource entry name -> device ids), what
+// core.GetExtendedResources returns (core/extended_resources.go:42-81).
+func (g *GPUScheduler) binding(pod *v1.Pod, r *C.ksb_result) v1.ExtendedResourceBinding {
+	if len(pod.Spec.ExtendedResources) == 0 {
+		return nil
+	}
+	out := v1.ExtendedResourceBinding{}
+	for i, e := range pod.Spec.ExtendedResources {
+		if i >= C.KSB_MAX_EXT_ENTRIES || len(e.Resources.Limits) != 1 {
+			continue
+		}
+		var rname string
+		for k := range e.Resources.Limits {
+			rname = string(k)
+		}
+		crname := C.CString(rname)
+		var ids []string
+		mask := uint32(r.device_mask[i])
+		for bit := 0; bit < C.KSB_MAX_DEVICES; bit++ {
+			if mask&(1<<uint(bit)) == 0 {
+				continue
+			}
+			var id *C.char
+			var idLen C.size_t
+			if C.ksb_device_id(g.e, r.node_index, crname, C.size_t(len(rname)), C.int32_t(bit), &id, &idLen) == 0 {
+				ids = append(ids, C.GoStringN(id, C.int(idLen)))
+			}
+		}
+		C.free(unsafe.Pointer(crname))
+		out[e.Name] = v1.ExtendedResourceList{Resources: ids}
+	}
+	return out
+}
+
+// fitError rebuilds *core.FitError (core/generic_scheduler.go:47-51) from the per-node reason masks: the text of
+// Error() (:70-88) and nodesWherePreemptionMightHelp (:957-991) both read FailedPredicates.
+func (g *GPUScheduler) fitError(pod *v1.Pod, numNodes int) error {
+	masks := make([]C.uint32_t, numNodes)
+	failed := core.FailedPredicateMap{}
+	if numNodes > 0 && C.ksb_failed_predicates(g.e, &masks[0], C.int32_t(numNodes)) == 0 {
+		for row := 0; row < numNodes; row++ {
+			if masks[row] == 0 {
+				continue
+			}
+			var name *C.char
+			var nameLen C.size_t
+			if C.ksb_node_name(g.e, C.int32_t(row), &name, &nameLen) != 0 {
+				continue
+			}
+			var reasons []algorithm.PredicateFailureReason
+			for bit := 0; bit < 32; bit++ {
+				if uint32(masks[row])&(1<<uint(bit)) == 0 {
+					continue
+				}
+				var text [160]C.char
+				if C.ksb_reason_name(g.e, C.int32_t(bit), &text[0], 160) == 0 {
+					reasons = append(reasons, predicates.NewFailureReason(C.GoString(&text[0])))
+				}
+			}
+			failed[C.GoStringN(name, C.int(nameLen))] = reasons
+		}
+	}
+	return &core.FitError{Pod: pod, NumAllNodes: numNodes, FailedPredicates: failed}
+}
+
+// Preempt, Predicates and Prioritizers stay with the generic scheduler (the engine's scope is Schedule).
+func (g *GPUScheduler) Preempt(pod *v1.Pod, nodeLister algorithm.NodeLister, scheduleErr error) (*v1.Node, []*v1.Pod, []*v1.Pod, error) {
+	return g.generic.Preempt(pod, nodeLister, scheduleErr)
+}
+func (g *GPUScheduler) Predicates() map[string]algorithm.FitPredicate { return g.generic.Predicates() }
+func (g *GPUScheduler) Prioritizers() []algorithm.PriorityConfig     { return g.generic.Prioritizers() }
+
+// Resync replays a schedulercache snapshot into the engine after a device error (ksb_resync_begin/end).
+func (g *GPUScheduler) Resync(nodes []*v1.Node, infos map[string]*schedulercache.NodeInfo) error {
+	g.mu.Lock()
+	defer g.mu.Unlock()
+	if C.ksb_resync_begin(g.e) != 0 {
+		return g.lastError()
+	}
+	for _, n := range nodes {
+		p, l := bytesPtr(encodeNode(n))
+		if C.ksb_node_upsert(g.e, p, l) != 0 {
+			return g.lastError()
+		}
+	}
+	for _, info := range infos {
+		for _, pod := range info.Pods() {
+			p, l := bytesPtr(encodePod(pod))
+			if C.ksb_pod_add(g.e, p, l) != 0 {
+				return g.lastError()
+			}
+		}
+	}
+	if C.ksb_resync_end(g.e) != 0 {
+		return g.lastError()
+	}
+	return nil
+}
+
+// Close releases the engine.
+func (g *GPUScheduler) Close() { C.ksb_destroy(g.e) }

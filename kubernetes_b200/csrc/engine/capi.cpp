@@ -196,6 +196,14 @@ int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n) {
   });
 }
 
+int32_t ksb_resync_begin(ksb_engine* e) {
+  return guarded(e, [&] { e->impl->resync_begin(); });
+}
+
+int32_t ksb_resync_end(ksb_engine* e) {
+  return guarded(e, [&] { e->impl->flush(); });
+}
+
 int32_t ksb_scores(ksb_engine* e, int64_t* scores, int32_t n) {
   return guarded(e, [&] {
     if (!scores) throw std::runtime_error("scores must not be null");

@@ -120,6 +120,7 @@ class Engine {
   // hot path
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void flush();
+  void resync_begin();
   std::string node_info_json(const std::string& name);
   void grow_keep(DevBuf& b, size_t bytes);
   void failed_predicates(uint32_t* out, int32_t n_out);

@@ -764,6 +764,26 @@ void Engine::grow_keep(DevBuf& b, size_t bytes) {
   b = nb;
 }
 
+// ksb_resync_begin: drop every cluster record (the caller replays its cache), keep the dictionaries.
+void Engine::resync_begin() {
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  cudaStreamSynchronize(stream);  // whatever it returns: a failed launch is what brought the caller here
+  cudaGetLastError();             // clear the sticky error of a failed launch, if any
+  nodes.clear();
+  rows.clear();
+  pods.clear();
+  for (auto& o : owners) o.clear();
+  for (auto& kv : sigs) kv.second->spread_class = -2;  // selector owners are gone: signatures forget their class
+  n = 0;
+  layout_dirty = true;
+  have_snapshot = false;
+  label_index_valid = false;
+  last_encoded.clear();
+  last_results.clear();
+  last_fiterr_hist.clear();
+}
+
 void Engine::flush() {
   std::lock_guard<std::mutex> g(mu);
   CUDA_OK(cudaSetDevice(cfg.device));
