@@ -279,6 +279,7 @@ class Engine {
   int segs_per_shard = 1, nseg_total = 0, eval_nseg = 0;
   void prepare_geometry();
   void* peer0_scratch = nullptr;     // other ranks: rank 0's scratch buffer, mapped
+  std::vector<void*> peer_scratch;   // every other rank's scratch buffer, mapped (barrier flags, Reduce inboxes)
   std::vector<void*> ipc_mappings;
   void plan_shard();
   void fill_table_pointers(KsbNodeTable* T, void* i64b, void* u32b, void* u64b, void* devb, void* topob, void* spreadb,

@@ -27,7 +27,8 @@ constexpr size_t kPodSlotDep = (sizeof(KsbPodHeader) + 15) & ~(size_t)15;  // of
 constexpr size_t kPodSlotPool = kPodSlotDep + 16;
 struct ScratchLayout {
   size_t norms, zone_sum, raw, score, reasons, seg_max, seg_cnt, seg_mask, barrier, error_flag, fiterr_count, last_index,
-      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, tot_norms, tot_zone, total;
+      group_done, counters, res_slot, ghist, release, xbar, xstate, peers, pod_slot, fiterr_hist, tot_norms, tot_zone, xflag, xin_norms,
+      xin_zone, base0, total;
 };
 ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int halves = 1) {
   ScratchLayout L;
@@ -58,12 +59,17 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   // one-pod calls: header, dependency index and pool words travel inside the control block's single upload
   L.pod_slot = take(kPodSlotPool + (size_t)ksb_max_pool_words() * 8);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
+  // sharded: the inbox peers write into (behind the one-pod upload block, still independent of the row count)
+  L.xflag = take(4 * KSB_MAX_RANKS);
+  L.xin_norms = take((size_t)KSB_MAX_RANKS * KSB_MAX_GROUP * sizeof(KsbNorms));
+  L.xin_zone = take((size_t)KSB_MAX_RANKS * KSB_MAX_GROUP * zone_stride * 4);
   L.raw = take(halves * (size_t)G * n_pad * 16);
   L.score = take(halves * (size_t)G * n_pad * 4);
   L.reasons = take(halves * (size_t)G * n_pad * 4);
   L.seg_max = take(halves * (size_t)G * nseg * 4);
   L.seg_cnt = take(halves * (size_t)G * nseg * 4);
   L.seg_mask = take(halves * (size_t)G * nseg * 32);
+  L.base0 = take(halves * (size_t)G * n_pad * 4);  // sharded engines only use it (rank 0's copy is the one read)
   L.total = off;
   return L;
 }
@@ -167,9 +173,16 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.l_group_done = a.group_done;
   if (R > 1) {
     if (!shard_connected) throw std::runtime_error("sharded engine: call ksb_shard_export / ksb_shard_connect first");
-    if (a.rank != 0) {  // the reduction targets and the cross-GPU barrier live in rank 0's memory
-      a.tot_norms = (KsbNorms*)(base + L.tot_norms);
-      a.tot_zone_sum = (int32_t*)(base + L.tot_zone);
+    // Reduce inputs: every rank accumulates its own partials (acc_*), stores them into its slot of every rank's
+    // inbox at the barrier after phase 1 and combines the totals (tot_*) from its own inbox
+    a.tot_norms = (KsbNorms*)(base + L.tot_norms);
+    a.tot_zone_sum = (int32_t*)(base + L.tot_zone);
+    for (int q = 0; q < R; ++q) a.xpeer[q] = q == a.rank ? base : (char*)peer_scratch[q];
+    a.xo_flag = (uint32_t)L.xflag;
+    a.xo_norms = (uint32_t)L.xin_norms;
+    a.xo_zone = (uint32_t)L.xin_zone;
+    a.xo_gdone = (uint32_t)L.group_done;
+    if (a.rank != 0) {  // FitError histograms and the commit's progress words live in rank 0's memory
       char* b0 = (char*)peer0_scratch;
       a.norms = (KsbNorms*)(b0 + L.norms);
       a.zone_sum = (int32_t*)(b0 + L.zone_sum);
@@ -184,6 +197,10 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   a.gs_seg_mask = a.seg_mask;
   a.gs_np = ln_pad;
   a.gs_nseg = std::max(1, nseg);
+  a.gs_score = a.score;
+  a.gs_reasons = a.reasons;
+  a.gs_base0 = (int32_t*)(base + L.base0);
+  a.gs_row0 = eval_base;
   if (R > 1 && a.rank != 0) {
     // rank 0's scratch layout follows from the whole table's geometry, which every rank knows
     ScratchLayout L0 = scratch_layout(n_pad, zone_stride, std::max(1, nseg_total), group, pipe ? 2 : 1);
@@ -193,6 +210,9 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
     a.gs_seg_mask = (uint32_t*)(b0 + L0.seg_mask);
     a.gs_np = n_pad;
     a.gs_nseg = std::max(1, nseg_total);
+    a.gs_score = (int32_t*)(b0 + L0.score);
+    a.gs_reasons = (uint32_t*)(b0 + L0.reasons);
+    a.gs_base0 = (int32_t*)(b0 + L0.base0);
   }
   return a;
 }
@@ -966,10 +986,19 @@ void Engine::shard_connect(const std::vector<std::string>& blobs) {
         ipc_mappings.push_back(m.p[i]);
       }
     }
-  } else {
-    CUDA_OK(cudaIpcOpenMemHandle(&peer0_scratch, bs[0].h[7], cudaIpcMemLazyEnablePeerAccess));
-    ipc_mappings.push_back(peer0_scratch);
   }
+  // every rank maps every other rank's scratch buffer: the barrier flags and the Reduce inboxes are written all-to-all
+  peer_scratch.assign(R, nullptr);
+  for (int q = 0; q < R; ++q) {
+    if (q == cfg.shard_rank) continue;
+    if (cfg.shard_rank == 0) {
+      peer_scratch[q] = peer_maps[q].p[7];
+    } else {
+      CUDA_OK(cudaIpcOpenMemHandle(&peer_scratch[q], bs[q].h[7], cudaIpcMemLazyEnablePeerAccess));
+      ipc_mappings.push_back(peer_scratch[q]);
+    }
+  }
+  if (cfg.shard_rank != 0) peer0_scratch = peer_scratch[0];
   shard_connected = true;
 }
 

@@ -641,14 +641,18 @@ __device__ long long g_xdbg[8];  // crossing block: cycles in local wait, push, 
 struct NoXfer {
   __device__ __forceinline__ void operator()() const {}
 };
+// `far`: this block stored into another GPU's memory since the last barrier (results for phase 3 on a rank other
+// than 0, the writer warp's copies on rank 0): its arrival is preceded by a system-scope fence instead of a GPU-scope
+// one. `early` (rank 0 at the barrier that ends an iteration): the grid is released as soon as every rank has
+// arrived; what this rank sends (progress words, its own flag) leaves afterwards, off the committing block's path.
 template <class Push, class Fetch>
 __device__ __forceinline__ void grid_barrier_x(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait, int xb, Push push,
-                                               Fetch fetch) {
+                                               Fetch fetch, bool far = false, bool early = false) {
   __syncthreads();
   if (A.n_ranks == 1) {
     if (threadIdx.x == 0) {
       epoch += gridDim.x;
-      __threadfence();
+      if (wait) __threadfence();  // a block that does not wait contributed nothing to the phase that ends here
       atomicAdd(A.barrier, 1u);
       if (wait) spin_until<false>(A, A.barrier, epoch, 1);
     }
@@ -656,18 +660,13 @@ __device__ __forceinline__ void grid_barrier_x(KsbBatchArgs& A, uint32_t& epoch,
     return;
   }
   const bool crossing = (int)blockIdx.x == xb;
-  // Which blocks write another GPU's memory between barriers: the crossing block (its pushes) and block 0 of rank 0
-  // (the writer warp's copies of committed rows, results and counters). Every other block only touches this GPU's
-  // memory and pays for a GPU-scope fence; the crossing block's system-scope fence after it has seen every local
-  // arrival carries their writes along.
-  const bool far_writer = crossing || (blockIdx.x == 0 && A.rank == 0);
 #if KSB_FINE_TIMING == 3
   long long xt_ = clock64();
 #endif
   if (threadIdx.x == 0) {
     epoch += gridDim.x;
-    if (far_writer) __threadfence_system();
-    else __threadfence();
+    if (far) __threadfence_system();
+    else if (wait) __threadfence();
     if (crossing) KSB_XT(0);
     atomicAdd(A.barrier, 1u);
     if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
@@ -676,31 +675,45 @@ __device__ __forceinline__ void grid_barrier_x(KsbBatchArgs& A, uint32_t& epoch,
   if (crossing) {
     __syncthreads();
     KSB_XT(1);
+    // arrival number of this barrier (every thread of the block keeps count; the other blocks never read theirs)
+    xepoch += (uint32_t)A.n_ranks;
+    const uint32_t* my_flags = reinterpret_cast<const uint32_t*>(A.xpeer[A.rank] + A.xo_flag);
+    if (early) {
+      // every other rank's flag (its results for the next commit came before it), then the grid goes on
+      if ((int)threadIdx.x < A.n_ranks && (int)threadIdx.x != A.rank) spin_until<true>(A, my_flags + threadIdx.x, xepoch, 3);
+      __syncthreads();
+      KSB_XT(4);
+      fetch();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence();
+        atomicExch(A.release, epoch);
+      }
+    }
     push();
     __syncthreads();
     KSB_XT(2);
     if (threadIdx.x == 0) {
-      xepoch += (uint32_t)A.n_ranks;
-      __threadfence_system();
+      __threadfence_system();  // this block's pushes, and through the local arrivals every block's writes, before the flags
       KSB_XT(3);
-      atomicAdd_system(A.xbar, 1u);
-      spin_until<true>(A, A.xbar, xepoch, 3);
-      __threadfence_system();
+      for (int q = 0; q < A.n_ranks; ++q)
+        *reinterpret_cast<volatile uint32_t*>(A.xpeer[q] + A.xo_flag + 4 * A.rank) = xepoch;
+    }
+    if (!early) {
+      // one lane per rank polls this GPU's own flag array: no NVLink read on the path
+      if ((int)threadIdx.x < A.n_ranks) spin_until<true>(A, my_flags + threadIdx.x, xepoch, 3);
+      __syncthreads();
       KSB_XT(4);
-    }
-    __syncthreads();
-    fetch();
-    __syncthreads();
-    KSB_XT(5);
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      atomicExch(A.release, epoch);
+      fetch();
+      __syncthreads();
+      KSB_XT(5);
+      if (threadIdx.x == 0) {
+        __threadfence();
+        atomicExch(A.release, epoch);
+      }
     }
   }
-  if (threadIdx.x == 0) {
-    if (far_writer) __threadfence_system();
-    else __threadfence();
-  }
+  if (threadIdx.x == 0 && wait) __threadfence();
   __syncthreads();
 }
 __device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true, int xb = 0) {
@@ -1104,6 +1117,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   __shared__ int32_t s_pick[kMaxG];                // window: the row each pod picked
   __shared__ uint32_t t_dirty[kMaxG], t_now[kMaxG], t_snap[kMaxG], t_spec[kMaxG];  // window: column-pass outcomes per pick
   __shared__ int32_t t_idx[kMaxG];                 // window: cache entry of the picked row, -1 none, -2 no pick
+#if KSB_FINE_TIMING == 1
+  __shared__ uint32_t t_cause[4][kMaxG];
+  for (int i = threadIdx.x; i < 4 * kMaxG; i += kThreads) (&t_cause[0][0])[i] = 0;
+#endif
   __shared__ volatile uint32_t s_special;          // pods the one-pod path must decide
   __shared__ uint32_t s_prio, s_bad0;              // pods ranked by score; window pods whose pick failed
   __shared__ volatile int32_t s_ncr, s_cut;        // rows in the cache; the group ends early
@@ -1153,7 +1170,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     if (nblk < 4) shun_b = 0;
   }
   int cm_gid = 0;    // block 0: sequence number of the group being committed (row-cache tags)
-  int wcap = 2 * kDeciders;  // block 0, phase 3: window size; grows while whole windows come out right, shrinks when they do not
+#ifndef KSB_WCAP_MAX
+#define KSB_WCAP_MAX kDeciders
+#endif
+  // One column per deciding warp and round: wider windows (two columns in a row per warp) decided more pods per round but
+  // fewer per microsecond (cfg4 at 50,000 nodes: 2.87 -> 2.70 us/pod; about one (pick, later pod) pair in thirty is dirty)
+  const int wcap = KSB_WCAP_MAX;
+  // block 0, phase 3: window size; grows while whole windows come out right, shrinks when they do not
 
   if (MULTI && blockIdx.x == 0 && A.rank == 0) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(A.peers);
@@ -1312,6 +1335,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             }
             A.raw[at] = raw;
             A.reasons[at] = o.reasons;
+            if constexpr (MULTI) {  // what phase 3 reads of a changed row lives on rank 0, at the global row
+              const size_t gat = (half + (size_t)g) * (size_t)A.gs_np + (size_t)(A.gs_row0 + r);
+              A.gs_base0[gat] = raw.x;
+              if (A.rank != 0) A.gs_reasons[gat] = o.reasons;
+            }
           }
           // Reduce inputs of this warp's 32 rows: ballots for the counts and flags, a redux only for the values the pod
           // can have at all (uniform per pod); this warp's own slot, so no atomics
@@ -1366,53 +1394,66 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     {
       // sharded, ranks other than 0: this GPU's partial Reduce inputs go to rank 0's targets in one go, the totals
       // come back into this GPU's copy once every rank has pushed
-      const bool far = MULTI && A.rank != 0;
       auto push1 = [&] {
         if constexpr (MULTI) {
-        if (!far) return;
-        // (group of at most 32 pods x 8 values: one value per thread; zones: only the interned ones, in one wave of
-        // independent reductions per thread, none of which returns a value)
-        if (tid < Gc * 8) {
-          const int f = tid & 7;
-          int32_t* src = reinterpret_cast<int32_t*>(cur_acc_norms) + tid;
-          int32_t* dst = reinterpret_cast<int32_t*>(cur_norms) + tid;
-          const int32_t v = __ldcg(src);
-          if (f == 0) { if (v) atomicAdd_system(dst, v); }
-          else if (f == 5) { if (v) atomicMin_system(dst, v); }
-          else if (f == 7) { if (v >= 0) atomicMax_system(dst, v); }
-          else { if (v) atomicMax_system(dst, v); }
-          *src = f == 7 ? -1 : 0;
-        }
-        for (int i = tid; i < Gc * nz; i += kThreads) {
-          const int at = (i / nz) * zs + (i % nz);
-          const int32_t v = __ldcg(cur_acc_zsum + at);
-          if (v) {
-            atomicAdd_system(&cur_zsum[at], v);
-            cur_acc_zsum[at] = 0;
+          // this GPU's partial Reduce inputs of the group (at most 32 pods x 8 values, and the interned zones' sums)
+          // into this rank's slot of every rank's inbox: plain stores, one wave, nothing read over NVLink
+          const int R = A.n_ranks;
+          int32_t vn = 0;
+          if (tid < Gc * 8) {
+            int32_t* src = reinterpret_cast<int32_t*>(cur_acc_norms) + tid;
+            vn = __ldcg(src);
+            *src = (tid & 7) == 7 ? -1 : 0;
           }
-        }
+          const int nzv = Gc * nz;
+          for (int i0 = 0; i0 < nzv; i0 += 4 * kThreads) {
+            int32_t vz[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int i = i0 + tid + j * kThreads;
+              if (i < nzv) {
+                const int at = (i / nz) * zs + (i % nz);
+                vz[j] = __ldcg(cur_acc_zsum + at);
+                if (vz[j]) cur_acc_zsum[at] = 0;
+              }
+            }
+            for (int q = 0; q < R; ++q) {
+              int32_t* dz = reinterpret_cast<int32_t*>(A.xpeer[q] + A.xo_zone) + (size_t)A.rank * kMaxG * zs;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int i = i0 + tid + j * kThreads;
+                if (i < nzv) dz[(i / nz) * zs + (i % nz)] = vz[j];
+              }
+            }
+          }
+          if (tid < Gc * 8)
+            for (int q = 0; q < R; ++q)
+              reinterpret_cast<int32_t*>(A.xpeer[q] + A.xo_norms)[A.rank * kMaxG * 8 + tid] = vn;
         }
       };
       auto fetch1 = [&] {
         if constexpr (MULTI) {
-        if (!far) return;
-        // every load over NVLink is issued before the first is stored: one round trip, not one per value
-        int32_t vn = 0, vz[4] = {0, 0, 0, 0};
-        if (tid < Gc * 8) vn = __ldcv(reinterpret_cast<const int32_t*>(cur_norms) + tid);
-        const int nzv = Gc * nz;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int i = tid + j * kThreads;
-          if (i < nzv) vz[j] = __ldcv(cur_zsum + (i / nz) * zs + (i % nz));
-        }
-        if (tid < Gc * 8) reinterpret_cast<int32_t*>(cur_tot_norms)[tid] = vn;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int i = tid + j * kThreads;
-          if (i < nzv) cur_tot_zsum[(i / nz) * zs + (i % nz)] = vz[j];
-        }
-        for (int i = tid + 4 * kThreads; i < nzv; i += kThreads)  // more than 1,024 (pod, zone) pairs: the slow way
-          cur_tot_zsum[(i / nz) * zs + (i % nz)] = __ldcv(cur_zsum + (i / nz) * zs + (i % nz));
+          // every rank's slot has arrived in this GPU's inbox: combine the totals locally
+          const int R = A.n_ranks;
+          const char* inbox = A.xpeer[A.rank];
+          if (tid < Gc * 8) {
+            const int f = tid & 7;
+            int32_t v = __ldcv(reinterpret_cast<const int32_t*>(inbox + A.xo_norms) + tid);
+            for (int q = 1; q < R; ++q) {
+              const int32_t x = __ldcv(reinterpret_cast<const int32_t*>(inbox + A.xo_norms) + q * kMaxG * 8 + tid);
+              if (f == 0) v += x;
+              else if (f == 5) v = min(v, x);
+              else v = max(v, x);
+            }
+            reinterpret_cast<int32_t*>(cur_tot_norms)[tid] = v;
+          }
+          const int nzv = Gc * nz;
+          for (int i = tid; i < nzv; i += kThreads) {
+            const int at = (i / nz) * zs + (i % nz);
+            int32_t v = 0;
+            for (int q = 0; q < R; ++q) v += __ldcv(reinterpret_cast<const int32_t*>(inbox + A.xo_zone) + (size_t)q * kMaxG * zs + at);
+            cur_tot_zsum[at] = v;
+          }
         }
       };
       grid_barrier_x(A, epoch, xepoch, !lag, xb, push1, fetch1);
@@ -1491,7 +1532,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (raw.x != INT32_MIN)
               s = final_score(T, nm, lut[g], S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
                               (uint32_t)raw.z & 0xffffffu, raw.w, zone);
-            A.score[at] = s;
+            if constexpr (MULTI) A.gs_score[(half + (size_t)g) * (size_t)A.gs_np + (size_t)(A.gs_row0 + r)] = s;
+            else A.score[at] = s;
           }
           int32_t wm = warp_max(s);
           const uint32_t wmask = __ballot_sync(0xffffffffu, s == wm && s != INT32_MIN);
@@ -1518,19 +1560,18 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
             }
             if (m == INT32_MIN) c = 0;
-            // this GPU's own arrays: on rank 0 (and with one rank) they are the arrays phase 3 reads, numbered by global
-            // segment; on the other ranks a staging area numbered by the rank's own segments
-            const bool direct = !MULTI || A.rank == 0;
-            const size_t sat = direct ? (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + seg)
-                                      : (half + (size_t)g) * (size_t)nseg + (size_t)seg;
-            A.seg_max[sat] = m;
-            A.seg_cnt[sat] = c;
+            // straight into the arrays phase 3 reads, numbered by global segment: this GPU's own with one rank and on
+            // rank 0, rank 0's over NVLink on the other ranks (their blocks fence system-wide before the barrier that
+            // ends the iteration anyway, for the per-row results)
+            const size_t sat = (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + seg);
+            A.gs_seg_max[sat] = m;
+            A.gs_seg_cnt[sat] = c;
             // which rows hold the segment's maximum: word w = rows 32w..32w+31 of the segment
             uint32_t mw[kWarps];
 #pragma unroll
             for (int w = 0; w < kWarps; ++w)
               mw[w] = (S.wstat[(g * kWarps + w) * 3] == m && m != INT32_MIN) ? (uint32_t)S.wstat[(g * kWarps + w) * 3 + 2] : 0u;
-            uint4* mp = reinterpret_cast<uint4*>(A.seg_mask + sat * kWarps);
+            uint4* mp = reinterpret_cast<uint4*>(A.gs_seg_mask + sat * kWarps);
             mp[0] = make_uint4(mw[0], mw[1], mw[2], mw[3]);
             mp[1] = make_uint4(mw[4], mw[5], mw[6], mw[7]);
           }
@@ -1541,23 +1582,21 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     KSB_TICK(3);
     // FitError histograms of the group: this GPU's partial counts go to rank 0 before phase 3 reads them (plain
     // schedule: at the barrier before phase 3; pipelined: at the barrier that ends the iteration)
+    // how far the commit got (block 0 of rank 0 writes it before it arrives): rank 0 stores the two words into every
+    // rank's copy on its way through the barrier, so nobody reads them over NVLink
+    auto push_done = [&] {
+      if constexpr (MULTI) {
+        if (A.rank == 0 && tid < 2) {
+          const int32_t v = __ldcv(A.group_done + tid);
+          for (int q = 1; q < A.n_ranks; ++q) reinterpret_cast<volatile int32_t*>(A.xpeer[q] + A.xo_gdone)[tid] = v;
+        }
+      }
+    };
     auto push_hist = [&] {
       if constexpr (MULTI) {
+      if (pipe) push_done();
       if (A.rank == 0) return;
-      // this GPU's per-segment statistics of the group, into rank 0's arrays at the global segment numbers
-      for (int i = tid; i < Gc * nseg; i += kThreads) {
-        const int g = i / nseg, sg = i - g * nseg;
-        const size_t src = (half + (size_t)g) * (size_t)nseg + (size_t)sg;
-        const size_t dst = (half + (size_t)g) * (size_t)A.gs_nseg + (size_t)(A.seg_gbase + sg);
-        const uint4* ms = reinterpret_cast<const uint4*>(A.seg_mask + src * kWarps);
-        const int32_t vmx = __ldcg(A.seg_max + src), vct = __ldcg(A.seg_cnt + src);
-        const uint4 m0 = __ldcg(ms), m1 = __ldcg(ms + 1);
-        uint4* md = reinterpret_cast<uint4*>(A.gs_seg_mask + dst * kWarps);
-        A.gs_seg_max[dst] = vmx;
-        A.gs_seg_cnt[dst] = vct;
-        md[0] = m0;
-        md[1] = m1;
-      }
+      // FitError histograms of the group: this GPU's partial counts go to rank 0 before phase 3 reads them
       for (int i = tid; i < Gc * KSB_REASON_BITS; i += kThreads) {
         const int32_t v = __ldcg(cur_acc_ghist + i);
         if (v) {
@@ -1567,13 +1606,8 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       }
       }
     };
-    // how far the commit got (rank 0 writes it before it arrives): one NVLink read per rank, not per block
-    auto fetch_done = [&] {
-      if constexpr (MULTI) {
-        if (A.rank != 0 && tid < 2) A.l_group_done[tid] = __ldcv(A.group_done + tid);
-      }
-    };
-    if (!pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, NoXfer());  // pipelined: block 0 decides while the others are in phases 1-2
+    // (pipelined: block 0 decides while the others are in phases 1-2; sharded: ranks other than 0 stored results into rank 0's memory)
+    if (!pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, NoXfer(), MULTI && A.rank != 0);
     KSB_TICK(4);
 
     // ---- phase 3: block 0 of rank 0 commits the group's pods in order. Rows of other shards are reached
@@ -1657,11 +1691,17 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           const KsbPeer& P = PEER(prank);
           // sharded: the group-start results stay on the GPU that evaluated the row (three loads over NVLink per changed
           // row and pod; pushing every rank's results to rank 0 instead made NVLink writes the bottleneck)
-          const KsbPeer& O = PEER(MULTI ? min(R - 1, (crow / kSeg) / sps) : 0);
-          const size_t at = (half + g) * (size_t)O.raw_np + (size_t)(crow - O.raw_row0);
-          in.base0 = __ldcv(&O.raw[at].x);
-          in.reasons0 = __ldcv(O.reasons + at);
-          in.score0 = __ldcv(O.score + at);
+          if constexpr (MULTI) {  // every rank stored these into rank 0's arrays at the global row
+            const size_t at = (half + g) * (size_t)A.gs_np + (size_t)crow;
+            in.base0 = __ldcv(A.gs_base0 + at);
+            in.reasons0 = __ldcv(A.gs_reasons + at);
+            in.score0 = __ldcv(A.gs_score + at);
+          } else {
+            const size_t at = (half + g) * (size_t)P.raw_np + (size_t)crow;
+            in.base0 = __ldcv(&P.raw[at].x);
+            in.reasons0 = __ldcv(P.reasons + at);
+            in.score0 = __ldcv(P.score + at);
+          }
           const int ls = crow / kSeg;
           const int gseg = P.seg_base + ls;
           const int32_t* cum = S.cum + g * nsegT;
@@ -1986,11 +2026,18 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                   crow = c.row;
                   crank = c.pad & 0xff;
                   const KsbPeer& P = PEER(crank);
-                  const KsbPeer& O = PEER(MULTI ? min(R - 1, (crow / kSeg) / sps) : 0);  // the GPU that evaluated the row
-                  const size_t at = (half + g) * (size_t)O.raw_np + (size_t)(crow - O.raw_row0);
-                  const int32_t base0 = __ldcv(&O.raw[at].x);  // INT32_MIN = the row did not fit at group start
-                  old_reasons = __ldcv(O.reasons + at);
-                  if (prio) cold = __ldcv(O.score + at);
+                  int32_t base0;  // INT32_MIN = the row did not fit at group start
+                  if constexpr (MULTI) {  // stored into rank 0's arrays, at the global row, by the rank that evaluated it
+                    const size_t at = (half + g) * (size_t)A.gs_np + (size_t)crow;
+                    base0 = __ldcv(A.gs_base0 + at);
+                    old_reasons = __ldcv(A.gs_reasons + at);
+                    if (prio) cold = __ldcv(A.gs_score + at);
+                  } else {
+                    const size_t at = (half + g) * (size_t)P.raw_np + (size_t)crow;
+                    base0 = __ldcv(&P.raw[at].x);
+                    old_reasons = __ldcv(P.reasons + at);
+                    if (prio) cold = __ldcv(P.score + at);
+                  }
                   int32_t base;
                   eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
                   const bool was_fit = base0 != INT32_MIN;
@@ -2362,9 +2409,25 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             if (my_e >= 0 && gl > f + my_w && gl < f + W) {
               const bool used = my_idx >= 0 ? ((s_now[gl] >> my_idx) & 1u) != 0 : bs;
               dirty = sp || bn != used || s_pick[gl - f] == my_e;
+#if KSB_FINE_TIMING == 1
+              // why windows end early: per (pick, later pod) cause masks, read for the first dirty pod in step (3)
+              if (sp) atomicOr(&t_cause[0][my_w], 1u << gl);
+              if (bn != used) atomicOr(&t_cause[bn ? 1 : 2][my_w], 1u << gl);
+              if (s_pick[gl - f] == my_e) atomicOr(&t_cause[3][my_w], 1u << gl);
+#endif
             }
             const uint32_t nm_ = __ballot_sync(0xffffffffu, bn), sm_ = __ballot_sync(0xffffffffu, bs);
             const uint32_t xm_ = __ballot_sync(0xffffffffu, sp), dm = __ballot_sync(0xffffffffu, dirty);
+#if KSB_FINE_TIMING == 1 && defined(KSB_CAUSES)
+            {  // (pick, later pod of the window) pairs: all, the row held the pod's maximum at group start, and it no longer does
+              const uint32_t inwin = __ballot_sync(0xffffffffu, my_e >= 0 && gl > f + my_w && gl < f + W);
+              if (lane == 0) {
+                atomicAdd(reinterpret_cast<unsigned long long*>(&s_tk[38]), (unsigned long long)__popc(inwin));
+                atomicAdd(reinterpret_cast<unsigned long long*>(&s_tk[39]), (unsigned long long)__popc(inwin & sm_));
+                atomicAdd(reinterpret_cast<unsigned long long*>(&s_tk[36]), (unsigned long long)__popc(inwin & sm_ & ~nm_));
+              }
+            }
+#endif
             if (lane < cpw && w0 + lane < W) {
               const int w = w0 + lane;
               const int sh = dual ? 16 * lane : 0;
@@ -2390,6 +2453,25 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             dall >>= f;
             n_ok = dall ? min(W, __ffs((int)dall) - 1) : W;
             newmask = __ballot_sync(0xffffffffu, lane < n_ok && t_idx[lane] == -1);
+#if KSB_FINE_TIMING == 1
+            if (warp == 0) {
+              const int dpod = f + n_ok;  // the pod that ended the window (if any)
+              uint32_t c[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t m = lane < W ? t_cause[k][lane] : 0u;
+                c[k] = __reduce_or_sync(0xffffffffu, m);
+                if (lane < W) t_cause[k][lane] = 0;
+              }
+              if (lane == 0) {
+                if (n_ok < W) {
+                  for (int k = 0; k < 4; ++k)
+                    if ((c[k] >> dpod) & 1u) s_tk[32 + k] += 1;
+                }
+                s_tk[37] += W;
+              }
+            }
+#endif
           }
           // (4) their rows enter the cache, their records go to the writer, the later pods learn about them
           for (int w = warp; w < n_ok; w += kDeciders) {
@@ -2412,8 +2494,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             s_ncr = ncr + __popc(newmask);
             if (s_bad0) atomicOr(const_cast<uint32_t*>(&s_special), s_bad0 << f);
           }
-          // whole windows came out right: widen; else as many deciding warps' worth as the run of right pods suggests
-          wcap = n_ok == W ? min(32, wcap + kDeciders) : (n_ok < kDeciders ? kDeciders : 2 * kDeciders);
+
           if (tid == 0) {
             s_tk[11] += 1;
             s_tk[12] += n_ok;
@@ -2527,8 +2608,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       for (int i = tid; i < kMaxG * KSB_REASON_BITS; i += kThreads) gh[i] = 0;
     }
     // pipelined: the evaluation side has read the table and finished phase 2; the commit side has decided and written
-    if (pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, fetch_done);
-    else grid_barrier_x(A, epoch, xepoch, true, xb, NoXfer(), fetch_done);
+    // stores into other GPUs' memory since the last barrier: the writer warp's copies (block 0 of rank 0) and, pipelined,
+    // the evaluation results of ranks other than 0
+    if (pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, NoXfer(), MULTI && (A.rank != 0 || b == 0), MULTI && A.rank == 0);
+    else grid_barrier_x(A, epoch, xepoch, true, xb, push_done, NoXfer(), MULTI && committer, MULTI && A.rank == 0);
     KSB_TICK(6);
     if (__ldcg(A.error_flag) != 0) break;  // only after a barrier timeout: stop instead of spinning
     if (!pipe) {
@@ -2587,6 +2670,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     A.counters[12] = (uint64_t)s_tk[21];
     A.counters[13] = (uint64_t)s_tk[23];
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[24 + i];  // granular: picks 0-2, columns 3-6
+#ifdef KSB_CAUSES  // instead: why windows ended early (special, became holder, stopped being holder, same pick, bad pick) and pods tried
+    for (int i = 0; i < 4; ++i) A.counters[2 + i] = (uint64_t)s_tk[32 + i] * 1965ull;
+    A.counters[6] = (uint64_t)s_tk[38] * 1965ull;  // pairs
+    A.counters[7] = (uint64_t)s_tk[39] * 1965ull;  // pairs whose row was a holder for the later pod
+    A.counters[8] = (uint64_t)s_tk[36] * 1965ull;  // ... and stopped being one
+#endif
 #endif
     if (A.rank == 0) {
       A.counters[0] = (uint64_t)s_tk[9];
@@ -2795,6 +2884,10 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->gs_seg_cnt = a->seg_cnt;
   a->gs_seg_mask = a->seg_mask;
   a->gs_np = n_pad;
+  a->gs_score = a->score;  // (read by sharded kernels only: one rank reads score / raw / reasons)
+  a->gs_reasons = a->reasons;
+  a->gs_base0 = nullptr;
+  a->gs_row0 = 0;
   a->gs_nseg = a->nseg;
   a->seg_gbase = 0;
   a->eval_n = a->table.n;

@@ -63,6 +63,13 @@ struct KsbBatchArgs {
   int32_t* gs_seg_cnt;
   uint32_t* gs_seg_mask;
   int32_t gs_np, gs_nseg;
+  // Sharded: the per-(pod, row) results phase 3 reads of a changed row (group-start total, its bind-dependent part and
+  // the reason mask) are stored by every rank straight into rank 0's arrays at the GLOBAL row, so that the commit
+  // never reads over NVLink. One rank: score / reasons themselves (base0 unused: raw[].x is read instead).
+  int32_t* gs_score;            // [halves * group_size][gs_np]
+  int32_t* gs_base0;            // [halves * group_size][gs_np] raw[].x: INT32_MIN = the row did not fit
+  uint32_t* gs_reasons;         // [halves * group_size][gs_np]
+  int32_t gs_row0;              // global row of this rank's evaluation row 0
   int32_t seg_gbase;            // global index of this rank's first evaluated segment
   int32_t eval_n;               // rows this rank evaluates: rows [0, eval_n) of its table (rank 0's table holds all rows)
   // Reduce inputs: accumulated per GPU, pushed to rank 0's targets (norms / zone_sum / ghist above) at a barrier,
@@ -76,7 +83,17 @@ struct KsbBatchArgs {
   // sharding (n_ranks == 1: everything local). With n_ranks > 1 the reduction targets above (norms, zone_sum,
   // ghist, group_done) and xbar point into rank 0's memory on every rank.
   const KsbPeer* peers;         // [n_ranks], dereferenced by rank 0 only
-  uint32_t* xbar;               // cross-GPU barrier counter in rank 0's memory
+  uint32_t* xbar;               // (unused since the flag barrier; kept so that the control block keeps its layout)
+  // Cross-GPU barrier and Reduce exchange, all-to-all: every rank owns an inbox in its scratch buffer with one slot
+  // per source rank; a rank stores its partial Reduce inputs into its slot of EVERY inbox, then its arrival number
+  // into its word of every rank's flag array, and waits on its OWN flag array (local polling, no NVLink read on
+  // the path); the totals are then combined from the local inbox. xpeer[q] = rank q's scratch buffer as mapped
+  // here (own buffer for q == rank), xo_* the byte offsets of the inbox parts inside every scratch buffer.
+  char* xpeer[KSB_MAX_RANKS];
+  uint32_t xo_flag;             // uint32_t [KSB_MAX_RANKS]: arrival number last written by each rank
+  uint32_t xo_norms;            // KsbNorms [KSB_MAX_RANKS][KSB_MAX_GROUP]
+  uint32_t xo_zone;             // int32_t [KSB_MAX_RANKS][KSB_MAX_GROUP][zone_stride]
+  uint32_t xo_gdone;            // int32_t [8]: the rank's copy of group_done (rank 0 pushes words 0..1)
   uint32_t* release;            // local: epoch up to which this GPU's blocks may proceed
   uint32_t* xstate;             // local: cross-GPU barrier epoch carried from launch to launch (xbar is never reset)
   int32_t n_ranks, rank;

@@ -9,7 +9,7 @@ import subprocess
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
-LIB_DIR = os.path.join(PKG, "lib")
+LIB_DIR = os.environ.get("KSB_LIB_DIR") or os.path.join(PKG, "lib")  # KSB_LIB_DIR: an instrumented build (make OUT=... FINE_TIMING=n)
 ENGINE_SO = os.path.join(LIB_DIR, "libksched_b200.so")
 HOST_SO = os.path.join(LIB_DIR, "libksched_host.so")
 

@@ -86,3 +86,7 @@ print("top lines:")
 for ln, s in per_line.most_common(topn):
     st = ", ".join("%s %d" % (k.replace("stall_", ""), v) for k, v in per_line_stall[ln].most_common(3))
     print("%6d %7d %5.1f%%  inst %10d | %s | %s" % (ln, s, 100.0 * s / total, per_line_inst[ln], st, src[ln - 1].strip()[:110]))
+print("top lines by warp instructions executed:")
+tot_inst = max(1, sum(per_line_inst.values()))
+for ln, ix in per_line_inst.most_common(topn):
+    print("%6d %12d %5.1f%%  samples %7d | %s" % (ln, ix, 100.0 * ix / tot_inst, per_line[ln], src[ln - 1].strip()[:110]))
