@@ -60,9 +60,10 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   L.pod_slot = take(kPodSlotPool + (size_t)ksb_max_pool_words() * 8);
   L.fiterr_hist = take((size_t)KSB_MAX_FITERR * KSB_REASON_BITS * 4);
   // sharded: the inbox peers write into (behind the one-pod upload block, still independent of the row count)
-  L.xflag = take(4 * KSB_MAX_RANKS);
-  L.xin_norms = take((size_t)KSB_MAX_RANKS * KSB_MAX_GROUP * sizeof(KsbNorms));
-  L.xin_zone = take((size_t)KSB_MAX_RANKS * KSB_MAX_GROUP * zone_stride * 4);
+  L.xflag = take(256);  // +0: barrier flags [KSB_MAX_RANKS], +64: evaluation-done flags [KSB_MAX_RANKS], +128: commit-done words [2] x 8 bytes
+  // two halves x one slot per source rank x one 8-byte word {value, exchange number} per value
+  L.xin_norms = take(2 * (size_t)KSB_MAX_RANKS * KSB_MAX_GROUP * 8 * 8);
+  L.xin_zone = take(2 * (size_t)KSB_MAX_RANKS * KSB_MAX_GROUP * zone_stride * 8);
   L.raw = take(halves * (size_t)G * n_pad * 16);
   L.score = take(halves * (size_t)G * n_pad * 4);
   L.reasons = take(halves * (size_t)G * n_pad * 4);

@@ -716,6 +716,105 @@ __device__ __forceinline__ void grid_barrier_x(KsbBatchArgs& A, uint32_t& epoch,
   if (threadIdx.x == 0 && wait) __threadfence();
   __syncthreads();
 }
+// The barrier between phases 1 and 2 on a sharded table: each GPU's own grid barrier, with the exchange of the Reduce
+// inputs (`exch`, which needs no other cross-GPU synchronisation: see there) run by the crossing block between the
+// arrival of its grid and its release. `x1` numbers the exchanges (carried from launch to launch).
+template <class Exch>
+__device__ __forceinline__ void reduce_barrier_x(KsbBatchArgs& A, uint32_t& epoch, uint32_t& x1, bool wait, int xb, Exch exch) {
+  __syncthreads();
+  x1 += 1u;
+  const bool crossing = (int)blockIdx.x == xb;
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    if (wait) __threadfence();
+    atomicAdd(A.barrier, 1u);
+    if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
+    else if (wait) spin_until<false>(A, A.release, epoch, 4);
+  }
+  if (crossing) {
+    __syncthreads();
+    exch(x1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicExch(A.release, epoch);
+    }
+  }
+  if (threadIdx.x == 0 && wait) __threadfence();
+  __syncthreads();
+}
+
+// The barrier that ends a pipelined iteration on a sharded table. Nobody needs the full cross-GPU rendezvous here:
+//  * a rank other than 0 may start the next evaluation once the commit it ran next to is complete ("commit done":
+//    one 8-byte word {pods consumed, number} that block 0 of rank 0 stores into every rank the moment it finishes,
+//    after a system-scope fence for the writer warp's copies of the committed rows), and
+//  * the committing block may start the next commit once every rank's evaluation results have reached rank 0
+//    ("evaluation done": one word per rank, stored by its crossing block after the rank's own grid has arrived).
+// Everything else is each GPU's own grid barrier. `x2` numbers these barriers (carried from launch to launch).
+template <class Push>
+__device__ __forceinline__ void end_barrier_x(KsbBatchArgs& A, uint32_t& epoch, uint32_t& x2, int xb, Push push, bool committer,
+                                              int done_idx) {
+  __syncthreads();
+  x2 += 1u;
+  const bool crossing = (int)blockIdx.x == xb;
+  char* mine = A.xpeer[A.rank] + A.xo_flag;
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    if (committer) {
+      __threadfence_system();
+      const unsigned long long word = ((unsigned long long)(uint32_t)__ldcv(A.group_done + done_idx) << 32) | (unsigned long long)x2;
+      for (int q = 1; q < A.n_ranks; ++q)
+        *reinterpret_cast<volatile unsigned long long*>(A.xpeer[q] + A.xo_flag + 128 + 8 * (x2 & 1u)) = word;
+    } else if (A.rank != 0) {
+      __threadfence_system();  // this block's results went into rank 0's memory
+    } else {
+      __threadfence();
+    }
+    atomicAdd(A.barrier, 1u);
+    if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
+    else spin_until<false>(A, A.release, epoch, 4);
+  }
+  if (crossing) {
+    __syncthreads();
+    if (A.rank != 0) {
+      push();
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(A.xpeer[0] + A.xo_flag + 64 + 4 * A.rank) = x2;
+        const unsigned long long* w = reinterpret_cast<const unsigned long long*>(mine + 128 + 8 * (x2 & 1u));
+        unsigned long long v;
+        uint32_t spins = 0;
+        long long t0 = 0;
+        for (;;) {
+          asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
+          if ((uint32_t)v == x2) break;
+          if ((++spins & 1023u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            if (now - t0 > 6000000000ll || ld_acquire((const uint32_t*)A.error_flag) != 0) {
+              atomicCAS(A.error_flag, 0, 7);
+              break;
+            }
+          }
+        }
+        A.l_group_done[done_idx] = (int32_t)(v >> 32);
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicExch(A.release, epoch);
+    }
+  }
+  if (threadIdx.x == 0) __threadfence();
+  __syncthreads();
+  if (committer) {  // the other ranks' results for the next commit
+    if (threadIdx.x >= 1 && (int)threadIdx.x < A.n_ranks)
+      spin_until<true>(A, reinterpret_cast<const uint32_t*>(mine + 64) + threadIdx.x, x2, 3);
+    __syncthreads();
+  }
+}
 __device__ __forceinline__ void grid_barrier(KsbBatchArgs& A, uint32_t& epoch, uint32_t& xepoch, bool wait = true, int xb = 0) {
   grid_barrier_x(A, epoch, xepoch, wait, xb, NoXfer(), NoXfer());
 }
@@ -1154,7 +1253,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   // The block that shares an SM with block 0 would compete with the decider warp for issue slots: it sits the
   // evaluation out. group_done[4] = block 0's SM, group_done[5] = index of that block (0: none).
   int shun_b = 0;
-  if (MULTI) xepoch = *A.xstate;  // the cross-GPU counter is never reset: its epoch is carried from launch to launch
+  uint32_t x2 = 0, x1 = 0;  // numbers of the iteration-ending barriers (sharded, pipelined) and of the Reduce exchanges
+  if (MULTI) {  // the cross-GPU flags are never reset: their numbers are carried from launch to launch
+    xepoch = A.xstate[0];
+    x2 = A.xstate[1];
+    x1 = A.xstate[2];
+  }
   if (pipe) {
     // (sharded: only rank 0 has a committing block, so only its blocks take part; every rank runs the barriers)
     uint32_t smid;
@@ -1392,20 +1496,24 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     }
     KSB_TICK(1);
     {
-      // sharded, ranks other than 0: this GPU's partial Reduce inputs go to rank 0's targets in one go, the totals
-      // come back into this GPU's copy once every rank has pushed
-      auto push1 = [&] {
+      // Sharded: once this GPU's grid has arrived, its crossing block sends the GPU's partial Reduce inputs of the group
+      // (at most 32 pods x 8 values, and the interned zones' sums) to every rank and combines the totals from what
+      // every rank sent here. Each value travels as one 8-byte word {value, number of this exchange}: a word is
+      // complete when its number matches, so there is no fence, no flag and no NVLink read on the path; the inbox
+      // alternates between two halves, so a word is overwritten only after its reader has sent the exchange after.
+      auto exch1 = [&](uint32_t tag) {
         if constexpr (MULTI) {
-          // this GPU's partial Reduce inputs of the group (at most 32 pods x 8 values, and the interned zones' sums)
-          // into this rank's slot of every rank's inbox: plain stores, one wave, nothing read over NVLink
           const int R = A.n_ranks;
-          int32_t vn = 0;
+          const size_t hslot = (size_t)(tag & 1u) * KSB_MAX_RANKS;  // inbox half of this exchange
+          auto word = [&](int32_t v) { return ((unsigned long long)(uint32_t)v << 32) | (unsigned long long)tag; };
+          const int nzv = Gc * nz;
           if (tid < Gc * 8) {
             int32_t* src = reinterpret_cast<int32_t*>(cur_acc_norms) + tid;
-            vn = __ldcg(src);
+            const int32_t vn = __ldcg(src);
             *src = (tid & 7) == 7 ? -1 : 0;
+            for (int q = 0; q < R; ++q)
+              reinterpret_cast<volatile unsigned long long*>(A.xpeer[q] + A.xo_norms)[(hslot + A.rank) * kMaxG * 8 + tid] = word(vn);
           }
-          const int nzv = Gc * nz;
           for (int i0 = 0; i0 < nzv; i0 += 4 * kThreads) {
             int32_t vz[4] = {0, 0, 0, 0};
 #pragma unroll
@@ -1418,45 +1526,59 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               }
             }
             for (int q = 0; q < R; ++q) {
-              int32_t* dz = reinterpret_cast<int32_t*>(A.xpeer[q] + A.xo_zone) + (size_t)A.rank * kMaxG * zs;
+              volatile unsigned long long* dz =
+                  reinterpret_cast<volatile unsigned long long*>(A.xpeer[q] + A.xo_zone) + (hslot + A.rank) * (size_t)kMaxG * zs;
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int i = i0 + tid + j * kThreads;
-                if (i < nzv) dz[(i / nz) * zs + (i % nz)] = vz[j];
+                if (i < nzv) dz[(i / nz) * zs + (i % nz)] = word(vz[j]);
               }
             }
           }
-          if (tid < Gc * 8)
-            for (int q = 0; q < R; ++q)
-              reinterpret_cast<int32_t*>(A.xpeer[q] + A.xo_norms)[A.rank * kMaxG * 8 + tid] = vn;
-        }
-      };
-      auto fetch1 = [&] {
-        if constexpr (MULTI) {
-          // every rank's slot has arrived in this GPU's inbox: combine the totals locally
-          const int R = A.n_ranks;
+          // ... and what every rank sent here
           const char* inbox = A.xpeer[A.rank];
+          long long t0 = 0;
+          uint32_t spins = 0;
+          bool dead = false;
+          auto take = [&](const unsigned long long* w) -> int32_t {
+            unsigned long long v;
+            for (;;) {
+              asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
+              if ((uint32_t)v == tag || dead) break;
+              if ((++spins & 1023u) == 0) {
+                const long long now = clock64();
+                if (t0 == 0) t0 = now;
+                if (now - t0 > 6000000000ll || ld_acquire((const uint32_t*)A.error_flag) != 0) {
+                  atomicCAS(A.error_flag, 0, 3);
+                  dead = true;
+                }
+              }
+            }
+            return (int32_t)(v >> 32);
+          };
           if (tid < Gc * 8) {
             const int f = tid & 7;
-            int32_t v = __ldcv(reinterpret_cast<const int32_t*>(inbox + A.xo_norms) + tid);
+            const unsigned long long* base = reinterpret_cast<const unsigned long long*>(inbox + A.xo_norms) + hslot * kMaxG * 8 + tid;
+            int32_t v = take(base);
             for (int q = 1; q < R; ++q) {
-              const int32_t x = __ldcv(reinterpret_cast<const int32_t*>(inbox + A.xo_norms) + q * kMaxG * 8 + tid);
+              const int32_t x = take(base + (size_t)q * kMaxG * 8);
               if (f == 0) v += x;
               else if (f == 5) v = min(v, x);
               else v = max(v, x);
             }
             reinterpret_cast<int32_t*>(cur_tot_norms)[tid] = v;
           }
-          const int nzv = Gc * nz;
           for (int i = tid; i < nzv; i += kThreads) {
             const int at = (i / nz) * zs + (i % nz);
+            const unsigned long long* base = reinterpret_cast<const unsigned long long*>(inbox + A.xo_zone) + hslot * (size_t)kMaxG * zs + at;
             int32_t v = 0;
-            for (int q = 0; q < R; ++q) v += __ldcv(reinterpret_cast<const int32_t*>(inbox + A.xo_zone) + (size_t)q * kMaxG * zs + at);
+            for (int q = 0; q < R; ++q) v += take(base + (size_t)q * kMaxG * zs);
             cur_tot_zsum[at] = v;
           }
         }
       };
-      grid_barrier_x(A, epoch, xepoch, !lag, xb, push1, fetch1);
+      if constexpr (MULTI) reduce_barrier_x(A, epoch, x1, !lag, xb, exch1);
+      else grid_barrier(A, epoch, xepoch, !lag, xb);
     }
     if (lag && tid == 0) s_b1_target = epoch;  // the writer warp holds its table writes until this barrier is complete
     KSB_TICK(2);
@@ -1594,7 +1716,6 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     };
     auto push_hist = [&] {
       if constexpr (MULTI) {
-      if (pipe) push_done();
       if (A.rank == 0) return;
       // FitError histograms of the group: this GPU's partial counts go to rank 0 before phase 3 reads them
       for (int i = tid; i < Gc * KSB_REASON_BITS; i += kThreads) {
@@ -2439,7 +2560,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
               t_spec[w] = (xm_ >> sh) & keep;
               t_idx[w] = idx;
             }
-            KSB_G(6);
+            // (slot 6 of the granular marks holds the wait for the writer warp)
           }
           KSB_F3(3);
           KSB_BAR3();
@@ -2581,7 +2702,13 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         }
       }
 #undef KSB_BAR3
+#if KSB_FINE_TIMING == 1
+      const long long drain0 = clock64();
+#endif
       __syncthreads();
+#if KSB_FINE_TIMING == 1
+      if (tid == 0) s_tk[30] += clock64() - drain0;  // deciders done, writer warp still writing
+#endif
       // publish how far the group got
       if (tid == 0) {
         A.group_done[gi & 1] = s_consumed;
@@ -2610,7 +2737,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     // pipelined: the evaluation side has read the table and finished phase 2; the commit side has decided and written
     // stores into other GPUs' memory since the last barrier: the writer warp's copies (block 0 of rank 0) and, pipelined,
     // the evaluation results of ranks other than 0
-    if (pipe) grid_barrier_x(A, epoch, xepoch, true, xb, push_hist, NoXfer(), MULTI && (A.rank != 0 || b == 0), MULTI && A.rank == 0);
+    if (pipe) {
+      if constexpr (MULTI) end_barrier_x(A, epoch, x2, xb, push_hist, committer, gi & 1);
+      else grid_barrier(A, epoch, xepoch, true, xb);
+    }
     else grid_barrier_x(A, epoch, xepoch, true, xb, push_done, NoXfer(), MULTI && committer, MULTI && A.rank == 0);
     KSB_TICK(6);
     if (__ldcg(A.error_flag) != 0) break;  // only after a barrier timeout: stop instead of spinning
@@ -2669,7 +2799,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
     A.counters[11] = (uint64_t)(s_tk[20] + s_tk[17]);
     A.counters[12] = (uint64_t)s_tk[21];
     A.counters[13] = (uint64_t)s_tk[23];
-    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[24 + i];  // granular: picks 0-2, columns 3-6
+    for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[24 + i];  // granular: picks 0-2, columns 3-5, [6] wait for the writer warp
 #ifdef KSB_CAUSES  // instead: why windows ended early (special, became holder, stopped being holder, same pick, bad pick) and pods tried
     for (int i = 0; i < 4; ++i) A.counters[2 + i] = (uint64_t)s_tk[32 + i] * 1965ull;
     A.counters[6] = (uint64_t)s_tk[38] * 1965ull;  // pairs
@@ -2682,7 +2812,11 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       A.counters[1] = (uint64_t)s_tk[10];
     }
   }
-  if (multi && b == xb && tid == 0) *A.xstate = xepoch;
+  if (multi && b == xb && tid == 0) {
+    A.xstate[0] = xepoch;
+    A.xstate[1] = x2;
+    A.xstate[2] = x1;
+  }
 #if KSB_FINE_TIMING == 2
   if (b == (pipe ? 1 : 0) && tid == 0)  // FINE_TIMING=2: an evaluating block's stage cycles instead of block 0's
     for (int i = 0; i < 7; ++i) A.counters[2 + i] = (uint64_t)s_tk[i];

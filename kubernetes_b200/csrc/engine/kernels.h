@@ -91,11 +91,13 @@ struct KsbBatchArgs {
   // here (own buffer for q == rank), xo_* the byte offsets of the inbox parts inside every scratch buffer.
   char* xpeer[KSB_MAX_RANKS];
   uint32_t xo_flag;             // uint32_t [KSB_MAX_RANKS]: arrival number last written by each rank
-  uint32_t xo_norms;            // KsbNorms [KSB_MAX_RANKS][KSB_MAX_GROUP]
-  uint32_t xo_zone;             // int32_t [KSB_MAX_RANKS][KSB_MAX_GROUP][zone_stride]
+                                // (+64: [KSB_MAX_RANKS] "evaluation done" numbers, read by rank 0's committing block;
+                                //  +128: two 8-byte words {pods consumed, number} "commit done", written by rank 0)
+  uint32_t xo_norms;            // uint64_t [2][KSB_MAX_RANKS][KSB_MAX_GROUP * 8]: {value, exchange number} words
+  uint32_t xo_zone;             // uint64_t [2][KSB_MAX_RANKS][KSB_MAX_GROUP][zone_stride]
   uint32_t xo_gdone;            // int32_t [8]: the rank's copy of group_done (rank 0 pushes words 0..1)
   uint32_t* release;            // local: epoch up to which this GPU's blocks may proceed
-  uint32_t* xstate;             // local: cross-GPU barrier epoch carried from launch to launch (xbar is never reset)
+  uint32_t* xstate;             // local [3]: the cross-GPU arrival numbers carried from launch to launch (the flags are never reset)
   int32_t n_ranks, rank;
   int32_t segs_per_shard;       // segments per shard (the last shard may hold fewer)
   int32_t nseg_total;           // segments over all shards
