@@ -94,6 +94,9 @@ Engine::~Engine() {
   pin_chunk[1].release();
   pin_ctl.release();
   pin_out.release();
+  pin_col.release();
+  b_fill_rows.release();
+  for (auto& kv : numcols) kv.second.buf.release();
   if (ev_start) cudaEventDestroy(ev_start);
   if (ev_stop) cudaEventDestroy(ev_stop);
   if (stream) cudaStreamDestroy(stream);
@@ -135,26 +138,124 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
   label_bits[k] = bit;
   if (!layout_dirty) {  // fill the new bit column from the retained node labels
     if (!label_index_valid) build_label_index();
-    const uint64_t m = 1ull << (bit & 63);
-    if (kind == 'P') {
-      std::string pk = key;
-      pk.push_back('\0');
-      pk += value;
-      auto it2 = rows_by_pair.find(pk);
-      if (it2 != rows_by_pair.end())
-        for (int r : it2->second) u64(bit >> 6, r) |= m;
+    // on one GPU with the table already uploaded the device sets the bit itself (run_pending_fills)
+    const bool dev_fill = cfg.shard_count <= 1 && !full_upload && b_u64.d != nullptr && dirty_rows.size() <= 64;
+    if (dev_fill && (kind == 'G' || kind == 'L') && ensure_numcol(key)) {
+      pending_fills.push_back(PendingFill{bit, {}});
+      stale_host_bits.push_back(bit);
     } else {
-      auto it2 = rows_by_key.find(key);
-      if (it2 != rows_by_key.end())
-        for (auto& rv : it2->second) {
-          bool on = true;
-          if (kind != 'K') on = rv.is_num && (kind == 'G' ? rv.num > num : rv.num < num);  // 'G' / 'L' (selector.go:214-233)
-          if (on) u64(bit >> 6, rv.row) |= m;
+      host_fill_bit(bit);
+      if (dev_fill) {
+        // the rows holding the pair / the key, as a list for the device (however long: a column re-sent from the host
+        // mirror would first need every kernel-set bit of the mirror brought up to date)
+        PendingFill f{bit, {}};
+        if (kind == 'P') {
+          std::string pk = key;
+          pk.push_back('\0');
+          pk += value;
+          auto it2 = rows_by_pair.find(pk);
+          if (it2 != rows_by_pair.end()) f.rows.assign(it2->second.begin(), it2->second.end());
+        } else {
+          auto it2 = rows_by_key.find(key);
+          if (it2 != rows_by_key.end())
+            for (auto& rv : it2->second)
+              if (kind == 'K' || (rv.is_num && (kind == 'G' ? rv.num > num : rv.num < num))) f.rows.push_back(rv.row);
         }
+        if (!f.rows.empty()) pending_fills.push_back(std::move(f));
+      } else {
+        dirty_label_words.insert(bit >> 6);
+      }
     }
-    dirty_label_words.insert(bit >> 6);
   }
   return bit;
+}
+
+// the host mirror's copy of one label bit, from the label index
+void Engine::host_fill_bit(int bit) {
+  const LabelBitDef& d = label_defs[bit];
+  const uint64_t m = 1ull << (bit & 63);
+  if (d.kind == 'P') {
+    std::string pk = d.key;
+    pk.push_back('\0');
+    pk += d.value;
+    auto it2 = rows_by_pair.find(pk);
+    if (it2 != rows_by_pair.end())
+      for (int r : it2->second) u64(bit >> 6, r) |= m;
+  } else {
+    auto it2 = rows_by_key.find(d.key);
+    if (it2 != rows_by_key.end())
+      for (auto& rv : it2->second) {
+        bool on = true;
+        if (d.kind != 'K') on = rv.is_num && (d.kind == 'G' ? rv.num > d.num : rv.num < d.num);  // 'G' / 'L' (selector.go:214-233)
+        if (on) u64(bit >> 6, rv.row) |= m;
+      }
+  }
+}
+
+void Engine::settle_host_bits() {
+  if (stale_host_bits.empty()) return;
+  if (!label_index_valid) build_label_index();
+  for (int b : stale_host_bits) host_fill_bit(b);
+  stale_host_bits.clear();
+}
+
+void Engine::invalidate_numcols() {
+  for (auto& kv : numcols) kv.second.valid = false;
+}
+
+// device column of the key's parsed numeric values; false when no row has a numeric value under the key
+bool Engine::ensure_numcol(const std::string& key) {
+  auto it = numcols.find(key);
+  if (it != numcols.end() && it->second.valid) return true;
+  if (!label_index_valid) build_label_index();
+  auto rk = rows_by_key.find(key);
+  if (rk == rows_by_key.end()) return false;
+  std::vector<int64_t> num((size_t)n_pad, 0);
+  std::vector<uint8_t> ok((size_t)n_pad, 0);
+  bool any = false;
+  for (auto& rv : rk->second)
+    if (rv.is_num) {
+      num[rv.row] = rv.num;
+      ok[rv.row] = 1;
+      any = true;
+    }
+  if (!any) return false;
+  NumCol& c = numcols[key];
+  c.buf.ensure((size_t)n_pad * 9);
+  CUDA_OK(cudaMemcpyAsync(c.buf.d, num.data(), (size_t)n_pad * 8, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemcpyAsync((char*)c.buf.d + (size_t)n_pad * 8, ok.data(), (size_t)n_pad, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));  // the sources are locals
+  stats.h2d_bytes += (size_t)n_pad * 9;
+  c.valid = true;
+  return true;
+}
+
+// the device's copy of the bits interned since the last upload (words re-sent as a whole already carry them)
+void Engine::run_pending_fills(const std::set<int>& uploaded_words) {
+  for (auto& f : pending_fills) {
+    const int w = f.bit >> 6;
+    if (uploaded_words.count(w)) continue;
+    uint64_t* col = (uint64_t*)b_u64.d + (size_t)w * ln_pad;
+    const uint64_t m = 1ull << (f.bit & 63);
+    int rc;
+    if (f.rows.empty()) {  // (a list is never empty: this is a threshold fill)
+      const LabelBitDef& d = label_defs[f.bit];
+      NumCol& c = numcols[d.key];
+      rc = ksb_launch_label_threshold(col, (const int64_t*)c.buf.d, (const uint8_t*)c.buf.d + (size_t)n_pad * 8, n, m, d.kind == 'G' ? 1 : 0,
+                                      d.num, stream);
+    } else {
+      b_fill_rows.ensure(std::max(f.rows.size(), (size_t)n_pad) * 4);
+      pin_col.ensure(std::max(f.rows.size() * 4, (size_t)ln_pad * 8));
+      memcpy(pin_col.p, f.rows.data(), f.rows.size() * 4);
+      CUDA_OK(cudaMemcpyAsync(b_fill_rows.d, pin_col.p, f.rows.size() * 4, cudaMemcpyHostToDevice, stream));
+      rc = ksb_launch_label_scatter(col, (const int32_t*)b_fill_rows.d, (int)f.rows.size(), m, stream);
+      CUDA_OK(cudaStreamSynchronize(stream));  // one staging buffer, pageable source
+      stats.h2d_bytes += f.rows.size() * 4;
+    }
+    if (rc != 0) throw std::runtime_error(std::string("label fill kernel failed: ") + cudaGetErrorString((cudaError_t)rc));
+    stats.kernel_launches += 1;
+  }
+  pending_fills.clear();
 }
 
 void Engine::build_label_index() {
@@ -330,14 +431,16 @@ int Engine::table_of(int kind, int selclass, int topo) {
   t.vals.assign(topo_values[topo].size() + 1, 0);
   if (kind == TK_MATCH && !layout_dirty) {
     // count the existing pods that match this class, per topology domain of their node
-    for (auto& kv : pods) {
-      const Pod& ep = kv.second.pod;
-      auto nit = nodes.find(ep.node_name);
-      if (nit == nodes.end() || nit->second.row < 0) continue;
-      if (!sig_matches_sel(sig_of(ep), selclass)) continue;
-      uint32_t d = h_topo[(size_t)topo * n_pad + nit->second.row];
-      if (d) t.vals[d] += 1;
-      t.vals[0] += 1;
+    for (auto& kv : sigs) {  // through the signatures, as for a new SelectorSpread class
+      SigInfo* es = kv.second.get();
+      if (es->placed.empty() || !sig_matches_sel(es, selclass)) continue;
+      for (auto& pl : es->placed) {
+        auto nit = nodes.find(pl.first);
+        if (nit == nodes.end() || nit->second.row < 0) continue;
+        uint32_t d = h_topo[(size_t)topo * n_pad + nit->second.row];
+        if (d) t.vals[d] += pl.second.first;
+        t.vals[0] += pl.second.first;
+      }
     }
   }
   tables.push_back(std::move(t));
@@ -345,7 +448,11 @@ int Engine::table_of(int kind, int selclass, int topo) {
   if (kind == TK_MATCH) selclasses[selclass].match_tables.push_back(id);
   else if (kind == TK_HELD_ANTI) held_anti_tables.push_back(id);
   else held_w_tables.push_back(id);
-  arena_dirty = true;
+  // A new table goes to the end of the arena (layout_arena numbers the tables in creation order), so only its own
+  // counters need to reach the device: re-sending the whole arena for every first use of an affinity term cost a
+  // Schedule call about a millisecond with hostname-keyed tables.
+  if (!arena_dirty && !layout_dirty && cfg.shard_count <= 1) appended_tables.push_back(id);
+  else arena_dirty = true;
   return id;
 }
 
@@ -408,12 +515,15 @@ int Engine::spread_class_of(const Pod& p, SigInfo* s) {
   h_spread.emplace_back((size_t)n_pad, 0u);
   if (!layout_dirty) {  // selector_spreading.go:85-108 over every pod already on a node
     auto& col = h_spread.back();
-    for (auto& kv : pods) {
-      const Pod& ep = kv.second.pod;
-      if (ep.deleting) continue;
-      auto nit = nodes.find(ep.node_name);
-      if (nit == nodes.end() || nit->second.row < 0) continue;
-      if (sig_matches_spread(sig_of(ep), id)) col[nit->second.row] += 1;
+    for (auto& kv : sigs) {  // every cached pod, through its signature
+      SigInfo* es = kv.second.get();
+      if (es->placed.empty() || !sig_matches_spread(es, id)) continue;
+      for (auto& pl : es->placed) {
+        if (pl.second.second <= 0) continue;
+        auto nit = nodes.find(pl.first);
+        if (nit == nodes.end() || nit->second.row < 0) continue;
+        col[nit->second.row] += (uint32_t)pl.second.second;
+      }
     }
     dirty_spread_cols.insert(id);
   }
@@ -485,9 +595,11 @@ void Engine::node_upsert(const Node& nd) {
     layout_dirty = true;
   } else {
     // topology domains may be new; tables are resized inside topo_domain
+    settle_host_bits();  // (with the index as it stood: this row is recomputed from its labels just below)
     fill_row(hn.row);
     dirty_rows.insert(hn.row);
     label_index_valid = false;
+    invalidate_numcols();
   }
 }
 
@@ -544,6 +656,11 @@ void Engine::host_add_pod(const Pod& p, HostNode& hn) {
       if (port.host_port != 0) hn.used_ports.insert(port_string(port));
   }
   hn.pod_keys.insert(p.key());
+  {
+    auto& pl = sig_of(p)->placed[p.node_name];
+    pl.first += 1;
+    if (!p.deleting) pl.second += 1;
+  }
   for (auto& e : p.extended) {  // extended_resources.go:86-110
     if (e.limits.size() != 1) continue;
     auto ds = hn.ext.find(e.limits.begin()->first);
@@ -575,6 +692,15 @@ void Engine::host_remove_pod(const Pod& p, HostNode& hn) {
   hn.req_agpu -= agpu;
   for (auto& kv : sc) hn.req_scalar[kv.first] -= kv.second;
   hn.pod_keys.erase(p.key());
+  {
+    SigInfo* s = sig_of(p);
+    auto pit = s->placed.find(p.node_name);
+    if (pit != s->placed.end()) {
+      pit->second.first -= 1;
+      if (!p.deleting) pit->second.second -= 1;
+      if (pit->second.first <= 0) s->placed.erase(pit);
+    }
+  }
   for (auto& e : p.extended) {  // extended_resources.go:114-152
     if (e.limits.size() != 1) continue;
     auto ds = hn.ext.find(e.limits.begin()->first);
@@ -789,6 +915,9 @@ void Engine::rebuild_layout() {
   layout_dirty = false;
   for (int r = 0; r < n; ++r) fill_row(r);
   build_label_index();  // here, not inside the first Schedule that mentions a new label
+  stale_host_bits.clear();  // every row was just recomputed from its labels
+  pending_fills.clear();
+  invalidate_numcols();
   // per-class counters follow the pods: recount them all
   // (a table first registered here is created with the existing pods already counted: zero AFTER registering, or
   // those pods are counted twice by the recount below)

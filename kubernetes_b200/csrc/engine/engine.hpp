@@ -89,6 +89,9 @@ struct SigInfo {  // memo per distinct (namespace, labels) signature
   int spread_class = -2;             // -2 unknown, -1 none
   std::vector<int> spread_inc;       // spread classes the signature matches, valid for `spread_inc_classes` classes
   size_t spread_inc_classes = (size_t)-1;
+  // where the cached pods with this signature are: node name -> {all, not being deleted}. Lets a new SelectorSpread
+  // class or affinity table be counted from the signatures (hundreds) instead of from every cached pod.
+  std::unordered_map<std::string, std::pair<int32_t, int32_t>> placed;
 };
 
 struct CommitEntry {  // one per-domain counter the assume step bumps
@@ -121,6 +124,7 @@ class Engine {
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void flush();
   void resync_begin();
+  void warm_dictionaries();
   std::string node_info_json(const std::string& name);
   void grow_keep(DevBuf& b, size_t bytes);
   void failed_predicates(uint32_t* out, int32_t n_out);
@@ -165,6 +169,27 @@ class Engine {
   std::unordered_map<std::string, std::vector<KeyRow>> rows_by_key;
   bool label_index_valid = false;
   void build_label_index();
+  // Label bits interned after the table went up are set by a small kernel instead of a column upload: Gt / Lt bits from
+  // a device column of the key's parsed values (created at ksb_flush for every key with a numeric value, or on first
+  // use), bits matching few rows from a row list. For kernel-set Gt / Lt bits the host mirror is brought up to date
+  // only when it is next needed as a whole (a column or full upload): `stale_host_bits`.
+  struct NumCol {
+    DevBuf buf;  // int64_t[n_pad] values, then uint8_t[n_pad] "parsed as an integer"
+    bool valid = false;
+  };
+  std::map<std::string, NumCol> numcols;
+  struct PendingFill {
+    int bit;
+    std::vector<int32_t> rows;  // scatter list; empty: threshold fill from numcols[label_defs[bit].key]
+  };
+  std::vector<PendingFill> pending_fills;
+  std::vector<int> stale_host_bits;
+  DevBuf b_fill_rows;
+  void host_fill_bit(int bit);
+  void settle_host_bits();
+  bool ensure_numcol(const std::string& key);
+  void run_pending_fills(const std::set<int>& uploaded_words);
+  void invalidate_numcols();
   std::vector<Taint> hard_taints, soft_taints;
   std::unordered_map<std::string, int> hard_taint_idx, soft_taint_idx;
   std::unordered_map<std::string, int> avoid_idx;
@@ -206,6 +231,7 @@ class Engine {
   std::unordered_map<std::string, int> table_idx;
   std::vector<int> held_anti_tables, held_w_tables;
   bool arena_dirty = true;
+  std::vector<int> appended_tables;  // tables created since the arena last went to the device, while it was otherwise up to date
   uint32_t arena_words = 0;
   std::vector<SpreadClass> spread_classes;
   std::unordered_map<std::string, int> spread_idx;
@@ -262,13 +288,14 @@ class Engine {
   size_t one_pod_bytes = 0;           // ... and size (0: the pod block was uploaded to its own buffers)
   bool batch_pipe_ok = true;  // the last encoded batch has few pods that depend on a very recent pod
   size_t limits_for_smem = (size_t)-1;  // shared-memory size the cached max_grid / threads were queried for
+  PinnedBuf pin_col;  // one column on its way up (first uses inside a Schedule call): a pageable source cost the first such copy 2 ms
   PinnedBuf pin_chunk[2], pin_ctl, pin_out;  // pod blocks in (two chunks in flight); control block in; control block + results out
   std::vector<int32_t> last_dep;              // dependency indices of the last batch, relative to the batch
   cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
   // shard geometry: device rows [lbase, lbase + ln), device column stride ln_pad
   int lbase = 0, ln = 0, ln_pad = 0, rows_per_shard = 0;
   int eval_base = 0, eval_n = 0;  // rows this GPU evaluates: global rows [eval_base, eval_base + eval_n)
-  size_t min_spread_cols = 0, min_table_bytes = 0;
+  size_t min_spread_cols = 0, min_table_bytes = (size_t)64 << 20;  // affinity tables: room up front, growing costs a Schedule call a millisecond
   bool shard_connected = false;
   struct PeerMap {
     void* p[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

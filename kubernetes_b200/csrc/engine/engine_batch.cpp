@@ -795,7 +795,10 @@ void Engine::resync_begin() {
   rows.clear();
   pods.clear();
   for (auto& o : owners) o.clear();
-  for (auto& kv : sigs) kv.second->spread_class = -2;  // selector owners are gone: signatures forget their class
+  for (auto& kv : sigs) {
+    kv.second->spread_class = -2;  // selector owners are gone: signatures forget their class
+    kv.second->placed.clear();     // ... and the pods
+  }
   n = 0;
   layout_dirty = true;
   have_snapshot = false;
@@ -810,8 +813,68 @@ void Engine::flush() {
   CUDA_OK(cudaSetDevice(cfg.device));
   if (layout_dirty) rebuild_layout();
   if (n == 0) return;
+  warm_dictionaries();
   sync_device();
+  prepare_geometry();  // the scratch buffer for the first call
+  if (cfg.shard_count <= 1) {
+    b_fill_rows.ensure((size_t)n_pad * 4);  // row lists of label bits interned later
+    pin_col.ensure((size_t)ln_pad * 8);
+    // an empty launch of each kernel variant this table can use: module loading and the cooperative-launch set-up
+    // otherwise land in the first Schedule call (1.5 - 3 ms)
+    for (int p = 0; p < 2; ++p) {
+      KsbBatchArgs a = make_args(0, false);
+      if (p == 1 && !(pipe && grid >= 2)) break;
+      a.pipeline = p;
+      one_pod_bytes = 0;
+      launch(a);
+      CUDA_OK(cudaStreamSynchronize(stream));
+    }
+  }
   CUDA_OK(cudaStreamSynchronize(stream));
+}
+
+// What the first pods of a stream would otherwise pay for inside their Schedule call: the label bits any selector
+// over a low-cardinality node label can mention, and the SelectorSpread class of every selector owner on its own
+// (a pod matched by several owners still creates its class on first use). Bounded: at most half of the label
+// universe and 1,024 classes.
+void Engine::warm_dictionaries() {
+  if (cfg.shard_count > 1) return;  // shared buffers keep the capacity they were exported with
+  if (!label_index_valid) build_label_index();
+  std::map<std::string, std::set<std::string>> values;
+  for (auto& kv : rows_by_pair) {
+    const size_t z = kv.first.find('\0');
+    values[kv.first.substr(0, z)].insert(kv.first.substr(z + 1));
+  }
+  const int budget = W * 64 / 2;  // the rest stays free for what pods actually mention
+  for (auto& kv : values) {
+    if (kv.second.size() > 16) continue;  // hostname-like keys: one bit per value would not fit
+    if ((int)label_defs.size() + (int)kv.second.size() + 1 > budget) break;
+    label_bit('K', kv.first, std::string(), 0);
+    for (auto& v : kv.second) label_bit('P', kv.first, v, 0);
+  }
+  for (auto& kv : values)
+    if (kv.second.size() > 16 && (int)label_defs.size() < budget) label_bit('K', kv.first, std::string(), 0);
+  for (auto& kv : rows_by_key) {  // keys with integer values: the device column Gt / Lt bits are later set from
+    bool any = false;
+    for (auto& rv : kv.second) any = any || rv.is_num;
+    if (any) ensure_numcol(kv.first);
+  }
+  for (int kind = 0; kind < 4; ++kind)
+    for (auto& o : owners[kind]) {
+      if (spread_classes.size() >= 1024) return;
+      Pod probe;  // a pod this owner (and, as far as known here, no other) selects
+      probe.ns = o.ns;
+      sel::Selector sx;
+      if (kind < 2) {
+        if (o.map_selector.empty()) continue;
+        probe.labels = o.map_selector;
+      } else {
+        if (!sel::from_label_selector(o.selector, &sx)) continue;
+        if (!o.selector.match_expressions.empty() || o.selector.match_labels.empty()) continue;
+        probe.labels = o.selector.match_labels;
+      }
+      spread_class_of(probe, sig_of(probe));
+    }
 }
 
 void Engine::replay_last_batch(int iters, double* avg_ms, ksb_result* out) {

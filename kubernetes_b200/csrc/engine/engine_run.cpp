@@ -609,6 +609,8 @@ void Engine::upload_family(DevBuf& dst, const void* src, size_t elem, int cols) 
 }
 
 void Engine::upload_all() {
+  settle_host_bits();
+  pending_fills.clear();
   plan_shard();
   upload_family(b_i64, h_i64.data(), 8, I64_COLS);
   upload_family(b_u32, h_u32.data(), 4, U32_COLS);
@@ -624,9 +626,20 @@ void Engine::upload_all() {
 
 void Engine::upload_column(void* dev_base, const void* host_col, size_t elem, int dev_col) {
   if (ln <= 0) return;
-  CUDA_OK(cudaMemcpyAsync((char*)dev_base + (size_t)dev_col * ln_pad * elem, (const char*)host_col + (size_t)lbase * elem,
-                          (size_t)ln * elem, cudaMemcpyHostToDevice, stream));
-  stats.h2d_bytes += (size_t)ln * elem;
+  const size_t bytes = (size_t)ln * elem;
+  static const bool trace = getenv("KSB_TRACE") != nullptr;
+  const auto tc0 = std::chrono::steady_clock::now();
+  pin_col.ensure(std::max(bytes, (size_t)ln_pad * 8));  // (sized for the widest column at the first use, i.e. ksb_flush)
+  memcpy(pin_col.p, (const char*)host_col + (size_t)lbase * elem, bytes);
+  CUDA_OK(cudaMemcpyAsync((char*)dev_base + (size_t)dev_col * ln_pad * elem, pin_col.p, bytes, cudaMemcpyHostToDevice, stream));
+  const auto tc1 = std::chrono::steady_clock::now();
+  CUDA_OK(cudaStreamSynchronize(stream));  // one staging buffer
+  stats.h2d_bytes += bytes;
+  if (trace) {
+    const auto tc2 = std::chrono::steady_clock::now();
+    const double a = std::chrono::duration<double, std::milli>(tc1 - tc0).count(), b = std::chrono::duration<double, std::milli>(tc2 - tc1).count();
+    if (a + b > 0.15) fprintf(stderr, "[ksb] column upload %zu bytes: stage+issue %.3f ms, wait %.3f ms\n", bytes, a, b);
+  }
 }
 
 void Engine::upload_dirty() {
@@ -634,7 +647,9 @@ void Engine::upload_dirty() {
     upload_all();
     return;
   }
+  if (!dirty_label_words.empty()) settle_host_bits();
   for (int w : dirty_label_words) upload_column(b_u64.d, &h_u64[(size_t)w * n_pad], 8, w);
+  run_pending_fills(dirty_label_words);
   dirty_label_words.clear();
   for (int k : dirty_topo_cols) upload_column(b_topo.d, &h_topo[(size_t)k * n_pad], 4, k);
   dirty_topo_cols.clear();
@@ -663,6 +678,23 @@ void Engine::upload_dirty() {
 }
 
 void Engine::sync_device() {
+  static const bool trace = getenv("KSB_TRACE") != nullptr;  // what a slow table sync was made of, on stderr
+  const auto t_sync0 = std::chrono::steady_clock::now();
+  struct Report {
+    const std::chrono::steady_clock::time_point t0;
+    Engine* e;
+    bool on;
+    size_t lw, tc, dr, sp, pf, at;
+    bool ld, fu, ad;
+    ~Report() {
+      if (!on) return;
+      const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+      if (ms > 0.3)
+        fprintf(stderr, "[ksb] table sync %.3f ms: layout %d full %d arena %d label words %zu topo cols %zu rows %zu spread cols %zu fills %zu appended %zu\n",
+                ms, (int)ld, (int)fu, (int)ad, lw, tc, dr, sp, pf, at);
+    }
+  } report{t_sync0, this, trace, dirty_label_words.size(), dirty_topo_cols.size(), dirty_rows.size(), dirty_spread_cols.size(),
+           pending_fills.size(), appended_tables.size(), layout_dirty, full_upload, arena_dirty};
   if (layout_dirty) rebuild_layout();
   if (full_upload) upload_all();
   else upload_dirty();
@@ -681,6 +713,17 @@ void Engine::sync_device() {
   }
   for (int c : dirty_spread_cols) upload_column(b_spread.d, h_spread[c].data(), 4, c);
   dirty_spread_cols.clear();
+  if (!arena_dirty && !appended_tables.empty()) {
+    layout_arena();
+    grow_keep(b_tables, std::max<size_t>((size_t)arena_words * 4, min_table_bytes));
+    for (int id : appended_tables) {
+      const Table& t = tables[id];
+      CUDA_OK(cudaMemcpyAsync((int32_t*)b_tables.d + t.off, t.vals.data(), t.vals.size() * 4, cudaMemcpyHostToDevice, stream));
+      stats.h2d_bytes += t.vals.size() * 4;
+    }
+    CUDA_OK(cudaStreamSynchronize(stream));  // pageable sources that may change right after
+  }
+  appended_tables.clear();
   if (arena_dirty) {
     layout_arena();
     std::vector<int32_t> arena(std::max<uint32_t>(arena_words, 1), 0);

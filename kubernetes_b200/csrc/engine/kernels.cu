@@ -2909,6 +2909,30 @@ extern "C" int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* heade
 
 extern "C" int ksb_max_pool_words() { return kMaxPoolWords; }
 
+// A label bit interned after the table went up (first pod whose selector mentions it) is set on the device instead of
+// re-sending the 64-bit column it lives in: from the per-key column of parsed numeric values for Gt / Lt bits
+// (selector.go:214-233), from a list of rows for everything that matches few rows.
+__global__ void ksb_label_threshold_kernel(uint64_t* col, const int64_t* num, const uint8_t* valid, int n, uint64_t mask, int greater,
+                                           int64_t x) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < n && valid[r] && (greater ? num[r] > x : num[r] < x)) col[r] |= mask;
+}
+__global__ void ksb_label_scatter_kernel(uint64_t* col, const int32_t* rows, int k, uint64_t mask) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < k) col[rows[i]] |= mask;  // a row appears once in the list
+}
+extern "C" int ksb_launch_label_threshold(uint64_t* col, const int64_t* num, const uint8_t* valid, int n, uint64_t mask, int greater,
+                                          int64_t x, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  ksb_label_threshold_kernel<<<(n + 255) / 256, 256, 0, stream>>>(col, num, valid, n, mask, greater, x);
+  return (int)cudaGetLastError();
+}
+extern "C" int ksb_launch_label_scatter(uint64_t* col, const int32_t* rows, int k, uint64_t mask, cudaStream_t stream) {
+  if (k <= 0) return 0;
+  ksb_label_scatter_kernel<<<(k + 255) / 256, 256, 0, stream>>>(col, rows, k, mask);
+  return (int)cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------------
 // Scratch for ksb_replay_last_batch_noalloc (include/ksched_b200.h).
 //

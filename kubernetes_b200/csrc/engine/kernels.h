@@ -113,6 +113,11 @@ int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* header, const ui
                      const uint32_t* masks, cudaStream_t stream);
 size_t ksb_batch_smem_bytes(int zone_stride);
 int ksb_max_pool_words();
+// Set one label bit on the device (a bit interned after the table was uploaded): rows whose parsed numeric label value
+// is greater / less than x, or the listed rows.
+int ksb_launch_label_threshold(uint64_t* col, const int64_t* num, const uint8_t* valid, int n, uint64_t mask, int greater, int64_t x,
+                               cudaStream_t stream);
+int ksb_launch_label_scatter(uint64_t* col, const int32_t* rows, int k, uint64_t mask, cudaStream_t stream);
 // Point the scratch fields of *a at the module's static device array (no allocation) and set the group
 // size that array supports; -1 + text on error, including batches beyond the array's stated limits.
 int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid, KsbBatchArgs* a, char* err, size_t err_len);
