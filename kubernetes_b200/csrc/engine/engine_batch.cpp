@@ -12,6 +12,8 @@
 
 #include "engine.hpp"
 
+#include <nvtx3/nvToolsExt.h>
+
 namespace ksb {
 
 #define CUDA_OK(call)                                                                          \
@@ -23,6 +25,16 @@ namespace ksb {
   } while (0)
 
 namespace {
+// NVTX ranges for a profiler's timeline, named after the reference's own trace of a Schedule call
+// (utiltrace steps "Computing predicates", "Prioritizing", "Selecting host", core/generic_scheduler.go:110-154):
+// on the device those three are phases 1-3 of one kernel, so one range covers the launch; the host work around it
+// gets ranges of its own. Without a tool attached the calls are no-ops.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 constexpr size_t kPodSlotDep = (sizeof(KsbPodHeader) + 15) & ~(size_t)15;  // offsets inside the one-pod slot
 constexpr size_t kPodSlotPool = kPodSlotDep + 16;
 struct ScratchLayout {
@@ -382,6 +394,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   std::lock_guard<std::mutex> g(mu);
   CUDA_OK(cudaSetDevice(cfg.device));
   const int np = (int)batch.size();
+  NvtxRange r_call(np == 1 ? "Scheduling (ksb_schedule)" : "Scheduling (ksb_schedule_batch)");
   auto t0 = std::chrono::steady_clock::now();
   static const bool trace = getenv("KSB_TRACE") != nullptr;  // host timing breakdown of large batches on stderr
   std::vector<std::pair<const char*, double>> marks;
@@ -466,6 +479,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
 
   // encode pods [c0, c1) into page-locked staging buffer `which`
   auto encode_chunk = [&](int c0, int c1, int which) {
+    NvtxRange r_enc("predicateMetadata / priorityMetadata (encode pods)");
     auto te0 = std::chrono::steady_clock::now();
     const int len = c1 - c0;
     const size_t first_word = pool_words;
@@ -552,7 +566,11 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
     // counter written by either. Streams where many pods depend on a very recent pod (dense inter-pod affinity)
     // would stall it at every group: those run the plain schedule.
     batch_pipe_ok = recent_deps * 10 <= c1;
-    sync_device();
+    {
+      NvtxRange r_sync("UpdateNodeNameToInfoMap (table sync)");
+      sync_device();
+    }
+    NvtxRange r_launch("Computing predicates + Prioritizing + Selecting host (upload, launch)");
     sync_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ts0).count();
     char* src = (char*)pin_chunk[which].p;
     if (one_call) {
@@ -626,7 +644,10 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
   // wait for the chunk launched last and take its results
   auto wait_chunk = [&](int c0, int c1) {
     const int len = c1 - c0;
-    CUDA_OK(cudaStreamSynchronize(stream));
+    {
+      NvtxRange r_wait("Computing predicates + Prioritizing + Selecting host (device)");
+      CUDA_OK(cudaStreamSynchronize(stream));
+    }
     float ms = 0;
     if (!one_call) CUDA_OK(cudaEventElapsedTime(&ms, ev_start, ev_stop));  // one-pod calls are not timed on the device
     kernel_ms += ms;
@@ -667,6 +688,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
 
   // results to the caller; the device's assume step mirrored on the host records (scheduler.go:478, storage.go:180-187)
   auto post_chunk = [&](int c0, int c1) {
+    NvtxRange r_post("AssumePod (host mirror)");
     auto tp0 = std::chrono::steady_clock::now();
     for (int i = c0; i < c1; ++i) {
       const KsbResult& r = last_results[i];
