@@ -20,6 +20,7 @@
 #define KSB_REASON_BITS 32
 #define KSB_MAX_GROUP 32      // pods evaluated against one snapshot of the table
 #define KSB_MAX_SEGMENTS 2048 // 256-row segments per shard (524,288 node rows)
+#define KSB_MAX_TAINT_WORDS 3  // 192 distinct NoSchedule/NoExecute taints, PreferNoSchedule taints and preferAvoidPods references
 #define KSB_MAX_RANKS 8        // shards of one node table (one NVSwitch domain)
 #define KSB_SEG_CACHE 4096    // (group size) x (segments) bound: segment statistics held in shared memory
 
@@ -67,6 +68,8 @@ struct KsbNodeTable {
   int32_t row_base;  // global row of local row 0
   int32_t n_total;   // rows over all shards
   int32_t W;         // label words
+  int32_t tw;        // 64-bit words of each taint / preferAvoid set (columns taint_hard, taint_soft, avoid hold tw words each,
+                     // word w at + w * n_pad; a pod's masks for the words above 0 trail its pool block)
   int32_t n_zones;   // interned zone keys (+1: id 0 = no zone)
   // weights (defaults.go:217-257)
   int32_t w_lr, w_bra, w_ss, w_na, w_tt, w_ipa, w_avoid;

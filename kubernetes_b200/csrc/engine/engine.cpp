@@ -783,6 +783,22 @@ void Engine::fill_devices(int row) {
 
 // Everything about one row that derives from its Node object and its aggregates (not the
 // per-class counters, which follow the pods).
+// Bit index of a new entry of a taint / preferAvoid set that already holds `have`. When the set outgrows its words, the
+// word count grows (up to KSB_MAX_TAINT_WORDS) and the table is re-laid on the next sync: the row being filled keeps
+// going (its bits beyond the current words are dropped here and set by the rebuild, which recomputes every row).
+int Engine::set_bit_slot(int have, const char* what) {
+  if (have >= 64 * KSB_MAX_TAINT_WORDS)
+    throw std::runtime_error("more than " + std::to_string(64 * KSB_MAX_TAINT_WORDS) + " distinct " + what);
+  if (have >= 64 * TW) {
+    if (cfg.shard_count > 1 && shard_connected)
+      throw std::runtime_error(std::string("sharded engine: more than ") + std::to_string(64 * TW) + " distinct " + what +
+                               " after ksb_shard_connect (shared buffers keep their layout)");
+    pending_TW = std::max(pending_TW, have / 64 + 1);
+    layout_dirty = true;
+  }
+  return have;
+}
+
 void Engine::fill_row(int row) {
   HostNode& hn = *rows[row];
   const Node& nd = hn.node;
@@ -839,38 +855,33 @@ void Engine::fill_row(int row) {
   for (int w = 0; w < W; ++w) u64(w, row) = 0;
   for (size_t b = 0; b < label_defs.size(); ++b)
     if (node_has_label_bit(nd, label_defs[b])) u64((int)(b >> 6), row) |= 1ull << (b & 63);
-  uint64_t hard = 0, soft = 0;
+  for (int w = 0; w < 3 * TW; ++w) u64(U64_HARD() + w, row) = 0;
   for (auto& t : nd.taints) {
     std::string k = join3(t.key, t.value, t.effect);
     if (t.effect == "NoSchedule" || t.effect == "NoExecute") {
       auto it = hard_taint_idx.find(k);
       int b;
       if (it == hard_taint_idx.end()) {
-        b = (int)hard_taints.size();
-        if (b >= 64) throw std::runtime_error("more than 64 distinct NoSchedule/NoExecute taints");
+        b = set_bit_slot((int)hard_taints.size(), "NoSchedule/NoExecute taints");
         hard_taints.push_back(t);
         hard_taint_idx[k] = b;
       } else {
         b = it->second;
       }
-      hard |= 1ull << b;
+      if (b < 64 * TW) u64(U64_HARD(b >> 6), row) |= 1ull << (b & 63);
     } else if (t.effect == "PreferNoSchedule") {
       auto it = soft_taint_idx.find(k);
       int b;
       if (it == soft_taint_idx.end()) {
-        b = (int)soft_taints.size();
-        if (b >= 64) throw std::runtime_error("more than 64 distinct PreferNoSchedule taints");
+        b = set_bit_slot((int)soft_taints.size(), "PreferNoSchedule taints");
         soft_taints.push_back(t);
         soft_taint_idx[k] = b;
       } else {
         b = it->second;
       }
-      soft |= 1ull << b;
+      if (b < 64 * TW) u64(U64_SOFT(b >> 6), row) |= 1ull << (b & 63);
     }
   }
-  u64(U64_HARD(), row) = hard;
-  u64(U64_SOFT(), row) = soft;
-  uint64_t avoid = 0;
   if (!nd.avoid_annotation_invalid)
     for (auto& a : nd.avoid) {
       std::string k = a.kind;
@@ -879,15 +890,13 @@ void Engine::fill_row(int row) {
       auto it = avoid_idx.find(k);
       int b;
       if (it == avoid_idx.end()) {
-        b = (int)avoid_idx.size();
-        if (b >= 64) throw std::runtime_error("more than 64 distinct preferAvoidPods controller references");
+        b = set_bit_slot((int)avoid_idx.size(), "preferAvoidPods controller references");
         avoid_idx[k] = b;
       } else {
         b = it->second;
       }
-      avoid |= 1ull << b;
+      if (b < 64 * TW) u64(U64_AVOID(b >> 6), row) |= 1ull << (b & 63);
     }
-  u64(U64_AVOID(), row) = avoid;
   fill_ports(row);
   fill_devices(row);
   for (int k = 0; k < (int)topo_keys.size(); ++k) h_topo[(size_t)k * n_pad + row] = (uint32_t)topo_domain(k, nd);
@@ -906,14 +915,19 @@ void Engine::rebuild_layout() {
   }
   n = (int)rows.size();
   n_pad = std::max(256, (n + 255) & ~255);
-  h_i64.assign((size_t)I64_COLS * n_pad, 0);
-  h_u32.assign((size_t)U32_COLS * n_pad, 0);
-  h_u64.assign((size_t)u64_cols() * n_pad, 0);
-  h_dev_class.assign((size_t)KSB_MAX_RES * n_pad * KSB_MAX_DEV, 0);
-  h_topo.assign((size_t)KSB_MAX_TOPO * n_pad, 0);
-  for (auto& c : h_spread) c.assign((size_t)n_pad, 0u);
+  for (;;) {
+    TW = std::max(TW, pending_TW);  // a taint / preferAvoid set outgrew its words: wider columns from here on
+    h_i64.assign((size_t)I64_COLS * n_pad, 0);
+    h_u32.assign((size_t)U32_COLS * n_pad, 0);
+    h_u64.assign((size_t)u64_cols() * n_pad, 0);
+    h_dev_class.assign((size_t)KSB_MAX_RES * n_pad * KSB_MAX_DEV, 0);
+    h_topo.assign((size_t)KSB_MAX_TOPO * n_pad, 0);
+    for (auto& c : h_spread) c.assign((size_t)n_pad, 0u);
+    layout_dirty = false;
+    for (int r = 0; r < n; ++r) fill_row(r);
+    if (pending_TW <= TW) break;  // else a row met the 65th (129th) entry of a set: lay the table out again
+  }
   layout_dirty = false;
-  for (int r = 0; r < n; ++r) fill_row(r);
   build_label_index();  // here, not inside the first Schedule that mentions a new label
   stale_host_bits.clear();  // every row was just recomputed from its labels
   pending_fills.clear();

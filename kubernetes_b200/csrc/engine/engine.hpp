@@ -250,13 +250,16 @@ class Engine {
          I64_REQ_EPH, I64_NZ_CPU, I64_NZ_MEM, I64_ALLOC_SCALAR, I64_REQ_SCALAR = I64_ALLOC_SCALAR + KSB_MAX_SCALARS,
          I64_COLS = I64_REQ_SCALAR + KSB_MAX_SCALARS };
   enum { U32_ALLOC_PODS = 0, U32_NUM_PODS, U32_FLAGS, U32_ZONE, U32_DEV_AVAIL, U32_COLS = U32_DEV_AVAIL + KSB_MAX_RES };
-  int u64_cols() const { return W + 3 + 3 * KSB_PORT_WORDS; }
-  int U64_HARD() const { return W; }
-  int U64_SOFT() const { return W + 1; }
-  int U64_AVOID() const { return W + 2; }
-  int U64_PORT_ANY() const { return W + 3; }
-  int U64_PORT_WILD() const { return W + 3 + KSB_PORT_WORDS; }
-  int U64_PORT_EXACT() const { return W + 3 + 2 * KSB_PORT_WORDS; }
+  // taint / preferAvoid sets: TW 64-bit words each (1 until a 65th distinct entry is interned; growing re-lays the table)
+  int TW = 1, pending_TW = 1;
+  int u64_cols() const { return W + 3 * TW + 3 * KSB_PORT_WORDS; }
+  int U64_HARD(int w = 0) const { return W + w; }
+  int U64_SOFT(int w = 0) const { return W + TW + w; }
+  int U64_AVOID(int w = 0) const { return W + 2 * TW + w; }
+  int U64_PORT_ANY() const { return W + 3 * TW; }
+  int U64_PORT_WILD() const { return W + 3 * TW + KSB_PORT_WORDS; }
+  int U64_PORT_EXACT() const { return W + 3 * TW + 2 * KSB_PORT_WORDS; }
+  int set_bit_slot(int have, const char* what);  // bit index for a new entry of such a set; grows TW when needed
   std::vector<int64_t> h_i64;
   std::vector<uint32_t> h_u32;
   std::vector<uint64_t> h_u64;

@@ -307,17 +307,27 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
   h.n_exprs = (uint8_t)n_exprs;
 
   // --- taints (predicates.go:1349-1373, taint_toleration.go:29-53)
+  // word 0 of each set travels in the header, the words above it (engines with more than 64 distinct entries) behind
+  // the pool block: [TW-1] hard, [TW-1] soft, [TW-1] preferAvoid
+  std::vector<uint64_t> tw_ext((size_t)3 * (TW - 1), 0);
+  auto set_mask = [&](int set, size_t i) {
+    if (i < 64) {
+      (set == 0 ? h.hard_untol : set == 1 ? h.soft_untol : h.avoid_mask) |= 1ull << i;
+    } else if ((int)(i >> 6) < TW) {
+      tw_ext[(size_t)set * (TW - 1) + (i >> 6) - 1] |= 1ull << (i & 63);
+    }
+  };
   for (size_t i = 0; i < hard_taints.size(); ++i) {
     bool tol = false;
     for (auto& t : p.tolerations)
       if (tolerates(t, hard_taints[i])) tol = true;
-    if (!tol) h.hard_untol |= 1ull << i;
+    if (!tol) set_mask(0, i);
   }
   for (size_t i = 0; i < soft_taints.size(); ++i) {
     bool tol = false;
     for (auto& t : p.tolerations)
       if ((t.effect.empty() || t.effect == "PreferNoSchedule") && tolerates(t, soft_taints[i])) tol = true;
-    if (!tol) h.soft_untol |= 1ull << i;
+    if (!tol) set_mask(1, i);
   }
   // --- NodePreferAvoidPods (node_prefer_avoid_pods.go:35-57)
   if (p.controller.present && (p.controller.kind == "ReplicationController" || p.controller.kind == "ReplicaSet")) {
@@ -325,7 +335,7 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
     k.push_back('\0');
     k += p.controller.uid;
     auto it = avoid_idx.find(k);
-    if (it != avoid_idx.end()) h.avoid_mask = 1ull << it->second;
+    if (it != avoid_idx.end()) set_mask(2, (size_t)it->second);
   }
   // --- host ports (util/utils.go:33-62)
   std::vector<uint64_t> ports(6 * KSB_PORT_WORDS, 0);
@@ -470,6 +480,7 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
     pool.push_back((uint64_t)(int64_t)c.delta);
   }
   for (int c : out->spread_inc) pool.push_back((uint64_t)c);
+  pool.insert(pool.end(), tw_ext.begin(), tw_ext.end());
   if ((int)pool.size() > ksb_max_pool_words()) throw std::runtime_error("pod " + p.key() + " requirement block too large");
 }
 
@@ -584,6 +595,7 @@ void Engine::fill_table_pointers(KsbNodeTable* T, void* i64b, void* u32b, void* 
   T->dev_avail = b + (size_t)U32_DEV_AVAIL * np;
   uint64_t* c = (uint64_t*)u64b;
   T->labels = c;
+  T->tw = TW;
   T->taint_hard = c + (size_t)U64_HARD() * np;
   T->taint_soft = c + (size_t)U64_SOFT() * np;
   T->avoid = c + (size_t)U64_AVOID() * np;

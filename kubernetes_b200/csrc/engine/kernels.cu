@@ -85,6 +85,7 @@ struct PodView {
   const uint64_t* score;
   const uint64_t* commits;
   const uint64_t* spread_inc;
+  const uint64_t* tw_ext;  // tw > 1: [tw-1] untolerated NoSchedule/NoExecute words, [tw-1] PreferNoSchedule, [tw-1] preferAvoid
 };
 
 __device__ __forceinline__ PodView make_view(const KsbPodHeader* h, const uint64_t* pool, int W) {
@@ -104,12 +105,14 @@ __device__ __forceinline__ PodView make_view(const KsbPodHeader* h, const uint64
   v.commits = p;
   p += 2 * (int)h->n_commit;
   v.spread_inc = p;
+  v.tw_ext = p + h->n_spread_inc;
+
   return v;
 }
 
-__device__ __forceinline__ int pool_words(const KsbPodHeader* h, int W) {
+__device__ __forceinline__ int pool_words(const KsbPodHeader* h, int W, int tw) {
   return (int)h->n_exprs * W + ((h->flags & PF_HAS_PORTS) ? 6 * KSB_PORT_WORDS : 0) + (int)h->n_ext * KSB_CLASS_WORDS +
-         h->n_checks + 2 * (int)h->n_score + 2 * (int)h->n_commit + h->n_spread_inc;
+         h->n_checks + 2 * (int)h->n_score + 2 * (int)h->n_commit + h->n_spread_inc + 3 * (tw - 1);
 }
 
 struct EvalOut {
@@ -465,7 +468,18 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   }
   // --- PodToleratesNodeTaints (predicates.go:1349-1373) and TaintTolerationPriority Map (taint_toleration.go:55-73)
   if (rc.hard & h->hard_untol) reasons |= 1u << RB_TAINTS;
-  const int32_t tt = __popcll(rc.soft & h->soft_untol);
+  int32_t tt = __popcll(rc.soft & h->soft_untol);
+  uint64_t avoid_hit = rc.avoid & h->avoid_mask;
+  if (T.tw > 1) {  // more than 64 distinct taints / references: the words above 0 (static columns)
+    const int x = T.tw - 1;
+    uint64_t hard_hit = 0;
+    for (int w = 0; w < x; ++w) {
+      hard_hit |= T.taint_hard[(size_t)(w + 1) * np + r] & pv.tw_ext[w];
+      tt += __popcll(T.taint_soft[(size_t)(w + 1) * np + r] & pv.tw_ext[x + w]);
+      avoid_hit |= T.avoid[(size_t)(w + 1) * np + r] & pv.tw_ext[2 * x + w];
+    }
+    if (hard_hit) reasons |= 1u << RB_TAINTS;
+  }
   // --- pressure / conditions (predicates.go:1382-1441)
   if ((pf & PF_BEST_EFFORT) && (nflags & NF_MEM_PRESSURE)) reasons |= 1u << RB_MEM_PRESSURE;
   if (nflags & NF_DISK_PRESSURE) reasons |= 1u << RB_DISK_PRESSURE;
@@ -516,7 +530,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   const int64_t mem = h->nz_mem + nmem;
   int32_t lr, bra;  // least_requested.go:63-91, balanced_resource_allocation.go:51-100
   lr_bra(cpu, mem, acpu, amem, rc.rcp_cpu, rc.rcp_mem, &lr, &bra);
-  const int32_t av = (rc.avoid & h->avoid_mask) ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
+  const int32_t av = avoid_hit ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
   o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
   o.na = na;
   o.tt = tt;
@@ -973,7 +987,10 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   const int64_t mem = h->nz_mem + c.q[9];
   int32_t lr, bra;
   lr_bra(cpu, mem, acpu, amem, c.rcp[0], c.rcp[1], &lr, &bra);
-  const int32_t av = ((uint64_t)c.q[30] & h->avoid_mask) ? 0 : 10;
+  uint64_t avoid_hit = (uint64_t)c.q[30] & h->avoid_mask;
+  if (T.tw > 1)  // the words above 0 of the preferAvoid set: static columns, read in place
+    for (int w = 0; w < T.tw - 1; ++w) avoid_hit |= T.avoid[(size_t)(w + 1) * T.n_pad + c.row] & pv.tw_ext[2 * (T.tw - 1) + w];
+  const int32_t av = avoid_hit ? 0 : 10;
   *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
 }
 
@@ -982,9 +999,10 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
 __device__ __forceinline__ void cache_fill_issue(const KsbNodeTable& T, int r, int lane, int64_t* v_out, uint32_t* v2_out) {
   const size_t np = T.n_pad;
   // columns of one family are consecutive, n_pad apart, in the order of q[] (device_types.h): lanes 0..17 the
-  // int64 family from alloc_cpu on, lanes 18..29 the twelve port words, lane 30 preferAvoid (the column before them)
-  const int64_t* p = lane < 18 ? T.alloc_cpu + (size_t)lane * np + r
-                               : reinterpret_cast<const int64_t*>(T.port_any) + (ptrdiff_t)(lane == 30 ? -1 : lane - 18) * (ptrdiff_t)np + r;
+  // int64 family from alloc_cpu on, lanes 18..29 the twelve port words, lane 30 preferAvoid
+  const int64_t* p = lane < 18   ? T.alloc_cpu + (size_t)lane * np + r
+                     : lane == 30 ? reinterpret_cast<const int64_t*>(T.avoid) + r  // word 0 of the preferAvoid set
+                                  : reinterpret_cast<const int64_t*>(T.port_any) + (size_t)(lane - 18) * np + r;
   // lanes 0..5: the u32 family from alloc_pods on (alloc_pods, num_pods, flags, zone, dev_avail[2])
   const uint32_t* p2 = reinterpret_cast<const uint32_t*>(T.alloc_pods) + (size_t)(lane < 4 + KSB_MAX_RES ? lane : 0) * np + r;
   int64_t v = 0;
@@ -1352,7 +1370,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
         bool ok = false;
         if (lane < avail) {
           const KsbPodHeader* h = S.hdr + lane;
-          int rel_end = (int)(h->pool_off - S.hdr[0].pool_off) + pool_words(h, T.W);
+          int rel_end = (int)(h->pool_off - S.hdr[0].pool_off) + pool_words(h, T.W, T.tw);
           ok = rel_end <= kGroupPoolWords && __ldg(A.dep + p0 + lane) < dep_floor;
           S.pool_off[lane] = (int32_t)(h->pool_off - S.hdr[0].pool_off);
         }
@@ -1365,7 +1383,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
       __syncthreads();
       const int gc = s_gc;
       const KsbPodHeader* hl = S.hdr + max(0, gc - 1);
-      const int words = gc > 0 ? S.pool_off[gc - 1] + pool_words(hl, T.W) : 0;
+      const int words = gc > 0 ? S.pool_off[gc - 1] + pool_words(hl, T.W, T.tw) : 0;
       const uint64_t* psrc = A.pool + S.hdr[0].pool_off;
       for (int i = tid; i < words; i += kThreads) S.pool[i] = psrc[i];
       for (int i = tid; i < gc * zs; i += kThreads) S.zone[i] = 0;
@@ -1453,7 +1471,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             const bool any_z = __any_sync(0xffffffffu, hz != 0);
             int32_t vna = 0, vtt = 0, vsc = 0, vmax = 0, vmin = 0;
             if (h->n_pref) vna = warp_max(mna);
-            if (h->soft_untol) vtt = warp_max(mtt);
+            if (h->soft_untol || T.tw > 1) vtt = warp_max(mtt);
             if (h->spread_col >= 0) vsc = warp_max(msc);
             if (h->n_score) {
               vmax = warp_max(max(0, ipa));

@@ -258,3 +258,34 @@ def test_golden_priorities_on_gpu():
     assert whole + partial + skipped == len(cases)
     print("priority vectors: %d whole lists, %d partial, %d not prioritized" % (whole, partial, skipped))
     assert whole >= 70, (whole, partial, skipped)
+
+
+def _many_sets_cluster(n_nodes=300, n_pods=1200, n_hard=150, n_soft=140, n_avoid=130):
+    """cfg3 with more than 64 distinct NoSchedule taints, PreferNoSchedule taints and preferAvoidPods references."""
+    cluster = workloads.generate(3, n_nodes, n_pods)
+    for i, node in enumerate(cluster["nodes"]):
+        taints = list(node.get("taints") or [])
+        if i % 3 == 0:
+            taints.append({"key": "hard-%d" % ((i // 3) % n_hard), "value": "x", "effect": "NoSchedule"})  # 100 distinct at 300 nodes
+        if i % 2 == 0:
+            taints.append({"key": "soft-%d" % (i % n_soft), "value": "y", "effect": "PreferNoSchedule"})
+            taints.append({"key": "soft-%d" % ((7 * i + 3) % n_soft), "value": "y", "effect": "PreferNoSchedule"})
+        node["taints"] = taints
+        node["avoid"] = [{"kind": "ReplicationController", "uid": "rc-%d" % ((i + j) % n_avoid)} for j in range(3)]
+    for i, pod in enumerate(cluster["pods"]):
+        tols = list(pod.get("tolerations") or [])
+        for j in range(40):  # tolerate a spread of the hard taints, so that many nodes stay feasible
+            tols.append({"key": "hard-%d" % ((i + 4 * j) % n_hard), "operator": "Exists", "value": "", "effect": "NoSchedule"})
+        for j in range(5):
+            tols.append({"key": "soft-%d" % ((3 * i + j) % n_soft), "operator": "Equal", "value": "y", "effect": "PreferNoSchedule"})
+        pod["tolerations"] = tols
+        pod["controller"] = {"kind": "ReplicationController" if i % 2 else "ReplicaSet", "uid": "rc-%d" % (i % n_avoid)}
+    return cluster
+
+
+def test_more_than_64_taints_and_avoid_references():
+    """The taint / preferAvoid sets grow to several 64-bit words (first 64 entries in the header word, the rest behind
+    the pod's pool block): batch and one-pod paths against the oracle."""
+    cluster = _many_sets_cluster()
+    compare(cluster, "many taints")
+    compare(_many_sets_cluster(120, 300), "many taints single", gpu_opts={"batch": 0})
