@@ -15,9 +15,15 @@
  *    engine copies what it needs before returning and never retains caller memory.
  *  - Every call returns 0 on success, <0 on error (text via ksb_last_error).
  *  - ksb_schedule* are called from one thread at a time (the reference calls Schedule from a
- *    single goroutine, scheduler.go:179). Mutators may be called from other threads; they
- *    are serialised by an internal mutex and become visible at the next ksb_schedule* call,
- *    which is the reference's snapshot point (core/generic_scheduler.go:122).
+ *    single goroutine, scheduler.go:179). Mutators may be called from other threads and never
+ *    wait for a scheduling call: one that arrives while ksb_schedule* / ksb_flush works on the
+ *    table is queued (the lock it takes is held for the time of an append, like the cache's own
+ *    mutex, schedulercache/cache.go:83-97) and returns 0; queued mutators are applied in arrival
+ *    order when that call ends and before the next one starts, which is the reference's snapshot
+ *    point (core/generic_scheduler.go:122). A mutator that finds the engine free and nothing
+ *    queued is applied on the spot and reports its own failure; the failure of a queued one is
+ *    logged and kept for ksb_deferred_errors (the reference's informer handlers only log such
+ *    errors, factory/factory.go:554-778).
  *  - There is no CPU fallback: if no CUDA device is usable ksb_create fails.
  */
 #ifndef KSCHED_B200_H_
@@ -131,6 +137,9 @@ int32_t ksb_fit_error_message(ksb_engine* e, int32_t i, char* buf, size_t buf_le
  * (schedulercache/cache.go:79-96, called at core/generic_scheduler.go:124) does at the start of each
  * Schedule; calling it after the informers' initial sync keeps that cost out of the first pod's latency. */
 int32_t ksb_flush(ksb_engine* e);
+/* Failures of mutators that were queued behind a scheduling call (see "Conventions"): returns their number and
+ * writes their texts, one per line, into buf; the list is cleared. */
+int32_t ksb_deferred_errors(ksb_engine* e, char* buf, size_t buf_len);
 
 /* Recovery (the reference rebuilds its cache from LIST+WATCH after a restart,
  * plugin/cmd/kube-scheduler/app/server.go:593-598, factory/factory.go:948 WaitForCacheSync; this is the same for the

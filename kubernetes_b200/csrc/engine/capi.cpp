@@ -1,5 +1,8 @@
 // extern "C" surface of include/ksched_b200.h over ksb::Engine.
 #include <chrono>
+#include <cstdio>
+#include <functional>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <cstring>
@@ -11,10 +14,19 @@
 #include "../../../include/ksched_b200.h"
 #include "engine.hpp"
 
+// Delta queue (the reference's only lock scope is the cache's own short mutex, schedulercache/cache.go:
+// 83-97): a mutator that arrives while a scheduling call works on the table does not wait for it. It is queued under a
+// lock held for a push_back and applied, in arrival order, when that call ends or before the next one starts, which is
+// the reference's snapshot point (UpdateNodeNameToInfoMap, core/generic_scheduler.go:122). With no such call running,
+// and nothing queued before it, a mutator is applied on the spot and reports its own failure.
 struct ksb_engine {
   ksb::Engine* impl;
   std::mutex err_mu;  // mutators may fail on several threads at once (include/ksched_b200.h "Threading")
   std::string err;
+  std::mutex q_mu;
+  bool busy = false;  // a scheduling call (or its drain of the queue) owns the engine
+  std::vector<std::function<void()>> queue;
+  std::vector<std::string> deferred_errors;  // failures of queued mutators, kept for ksb_deferred_errors
 };
 
 namespace {
@@ -29,6 +41,81 @@ int32_t guarded(ksb_engine* e, F&& f) {
     e->err = ex.what();
     return -1;
   }
+}
+
+// apply queued mutators in arrival order; a failure is kept (and logged), the rest still apply
+void apply_deltas(ksb_engine* e, std::vector<std::function<void()>>& take) {
+  for (auto& f : take) {
+    try {
+      f();
+    } catch (const std::exception& ex) {
+      fprintf(stderr, "[ksb] queued cache update failed: %s\n", ex.what());
+      std::lock_guard<std::mutex> g(e->q_mu);
+      if (e->deferred_errors.size() < 256) e->deferred_errors.push_back(ex.what());
+    }
+  }
+  take.clear();
+}
+
+// a mutator: on the spot if the engine is free and nothing is queued ahead of it, else queued
+template <class F>
+int32_t mutate(ksb_engine* e, F&& make_delta) {
+  if (!e || !e->impl) return -1;
+  std::function<void()> delta;
+  try {
+    delta = make_delta();  // decodes the wire record on the caller's thread; the closure owns what it needs
+  } catch (const std::exception& ex) {
+    std::lock_guard<std::mutex> g(e->err_mu);
+    e->err = ex.what();
+    return -1;
+  }
+  std::unique_lock<std::mutex> q(e->q_mu);
+  if (e->busy || !e->queue.empty()) {
+    e->queue.push_back(std::move(delta));
+    return 0;
+  }
+  // free: apply under the queue lock, so that a scheduling call that starts now waits for this one update only
+  try {
+    delta();
+    return 0;
+  } catch (const std::exception& ex) {
+    q.unlock();
+    std::lock_guard<std::mutex> g(e->err_mu);
+    e->err = ex.what();
+    return -1;
+  }
+}
+
+// a call that reads or schedules against the table: takes the engine, applies what was queued, runs, and applies what
+// arrived meanwhile before giving the engine back
+template <class F>
+int32_t scheduling(ksb_engine* e, F&& f) {
+  if (!e || !e->impl) return -1;
+  std::vector<std::function<void()>> take;
+  {
+    std::unique_lock<std::mutex> q(e->q_mu);
+    while (e->busy) {  // another scheduling call: the header asks for one at a time; wait rather than interleave
+      q.unlock();
+      std::this_thread::yield();
+      q.lock();
+    }
+    e->busy = true;
+    take.swap(e->queue);
+  }
+  apply_deltas(e, take);
+  const int32_t rc = guarded(e, f);
+  for (;;) {
+    {
+      std::lock_guard<std::mutex> q(e->q_mu);
+      if (e->queue.empty()) {
+        e->busy = false;
+        break;
+      }
+      take.swap(e->queue);
+    }
+    apply_deltas(e, take);
+  }
+  return rc;
 }
 }  // namespace
 
@@ -83,41 +170,53 @@ const char* ksb_last_error(const ksb_engine* e) {
 }
 
 int32_t ksb_node_upsert(ksb_engine* e, const uint8_t* buf, size_t len) {
-  return guarded(e, [&] {
+  return mutate(e, [&]() -> std::function<void()> {
     ksb::wire::Reader r(buf, len);
-    e->impl->node_upsert(ksb::wire::get_node(r));
+    auto nd = std::make_shared<ksb::Node>(ksb::wire::get_node(r));
+    return [e, nd] { e->impl->node_upsert(*nd); };
   });
 }
 
 int32_t ksb_node_remove(ksb_engine* e, const char* name, size_t name_len) {
-  return guarded(e, [&] { e->impl->node_remove(std::string(name, name_len)); });
+  return mutate(e, [&]() -> std::function<void()> {
+    std::string nm(name, name_len);
+    return [e, nm] { e->impl->node_remove(nm); };
+  });
 }
 
 int32_t ksb_pod_add(ksb_engine* e, const uint8_t* buf, size_t len) {
-  return guarded(e, [&] {
+  return mutate(e, [&]() -> std::function<void()> {
     ksb::wire::Reader r(buf, len);
-    e->impl->pod_add(ksb::wire::get_pod(r));
+    auto p = std::make_shared<ksb::Pod>(ksb::wire::get_pod(r));
+    return [e, p] { e->impl->pod_add(*p); };
   });
 }
 
 int32_t ksb_pod_remove(ksb_engine* e, const char* ns, size_t ns_len, const char* name, size_t name_len) {
-  return guarded(e, [&] { e->impl->pod_remove(std::string(ns, ns_len), std::string(name, name_len)); });
+  return mutate(e, [&]() -> std::function<void()> {
+    std::string a(ns, ns_len), b(name, name_len);
+    return [e, a, b] { e->impl->pod_remove(a, b); };
+  });
 }
 
 int32_t ksb_selector_owner_upsert(ksb_engine* e, int32_t kind, const uint8_t* buf, size_t len) {
-  return guarded(e, [&] {
+  return mutate(e, [&]() -> std::function<void()> {
     ksb::wire::Reader r(buf, len);
-    e->impl->owner_upsert(kind, ksb::wire::get_owner(r));
+    auto o = std::make_shared<ksb::SelectorOwner>(ksb::wire::get_owner(r));
+    return [e, kind, o] { e->impl->owner_upsert(kind, *o); };
   });
 }
 
 int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, size_t ns_len, const char* name,
                                   size_t name_len) {
-  return guarded(e, [&] { e->impl->owner_remove(kind, std::string(ns, ns_len), std::string(name, name_len)); });
+  return mutate(e, [&]() -> std::function<void()> {
+    std::string a(ns, ns_len), b(name, name_len);
+    return [e, kind, a, b] { e->impl->owner_remove(kind, a, b); };
+  });
 }
 
 int32_t ksb_schedule(ksb_engine* e, const uint8_t* pod, size_t len, ksb_result* out) {
-  return guarded(e, [&] {
+  return scheduling(e, [&] {
     ksb::wire::Reader r(pod, len);
     std::vector<ksb::Pod> batch;
     batch.push_back(ksb::wire::get_pod(r));
@@ -126,7 +225,7 @@ int32_t ksb_schedule(ksb_engine* e, const uint8_t* pod, size_t len, ksb_result* 
 }
 
 int32_t ksb_schedule_batch(ksb_engine* e, const uint8_t* pods, const uint64_t* offsets, int32_t n, ksb_result* out) {
-  return guarded(e, [&] {
+  return scheduling(e, [&] {
     auto t0 = std::chrono::steady_clock::now();
     // wire records are independent: decode them on a few host threads when the batch is large
     std::vector<ksb::Pod> batch((size_t)std::max(0, n));
@@ -197,11 +296,11 @@ int32_t ksb_failed_predicates(ksb_engine* e, uint32_t* masks, int32_t n) {
 }
 
 int32_t ksb_resync_begin(ksb_engine* e) {
-  return guarded(e, [&] { e->impl->resync_begin(); });
+  return scheduling(e, [&] { e->impl->resync_begin(); });
 }
 
 int32_t ksb_resync_end(ksb_engine* e) {
-  return guarded(e, [&] { e->impl->flush(); });
+  return scheduling(e, [&] { e->impl->flush(); });
 }
 
 int32_t ksb_scores(ksb_engine* e, int64_t* scores, int32_t n) {
@@ -223,7 +322,7 @@ int32_t ksb_reason_name(ksb_engine* e, int32_t bit, char* buf, size_t buf_len) {
 
 int32_t ksb_node_info(ksb_engine* e, const char* name, size_t name_len, char* buf, size_t buf_len, size_t* len) {
   bool small = false;
-  int32_t rc = guarded(e, [&] {
+  int32_t rc = scheduling(e, [&] {
     std::string t = e->impl->node_info_json(std::string(name ? name : "", name_len));
     if (len) *len = t.size();
     if (!buf || buf_len < t.size() + 1) {
@@ -235,8 +334,25 @@ int32_t ksb_node_info(ksb_engine* e, const char* name, size_t name_len, char* bu
   return rc != 0 ? rc : (small ? 1 : 0);
 }
 
+int32_t ksb_deferred_errors(ksb_engine* e, char* buf, size_t buf_len) {
+  if (!e || !e->impl) return -1;
+  std::lock_guard<std::mutex> q(e->q_mu);
+  const int32_t count = (int32_t)e->deferred_errors.size();
+  if (buf && buf_len) {
+    std::string all;
+    for (auto& t : e->deferred_errors) {
+      all += t;
+      all.push_back('\n');
+    }
+    strncpy(buf, all.c_str(), buf_len - 1);
+    buf[buf_len - 1] = 0;
+  }
+  e->deferred_errors.clear();
+  return count;
+}
+
 int32_t ksb_flush(ksb_engine* e) {
-  return guarded(e, [&] { e->impl->flush(); });
+  return scheduling(e, [&] { e->impl->flush(); });
 }
 
 uint64_t ksb_get_last_node_index(const ksb_engine* e) { return e && e->impl ? e->impl->last_node_index : 0; }
@@ -251,11 +367,11 @@ int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out) {
 }
 
 int32_t ksb_replay_last_batch(ksb_engine* e, int32_t iters, double* avg_ms, ksb_result* out) {
-  return guarded(e, [&] { e->impl->replay_last_batch(iters, avg_ms, out); });
+  return scheduling(e, [&] { e->impl->replay_last_batch(iters, avg_ms, out); });
 }
 
 int32_t ksb_shard_export(ksb_engine* e, int32_t max_batch_pods, uint8_t* out, size_t cap, size_t* len) {
-  return guarded(e, [&] {
+  return scheduling(e, [&] {
     std::string b = e->impl->shard_export(max_batch_pods);
     if (b.size() > cap) throw std::runtime_error("ksb_shard_export: output buffer too small");
     memcpy(out, b.data(), b.size());
@@ -273,7 +389,7 @@ int32_t ksb_shard_connect(ksb_engine* e, const uint8_t* blobs, const uint64_t* o
 }
 
 int32_t ksb_replay_last_batch_noalloc(ksb_engine* e, ksb_result* out) {
-  return guarded(e, [&] { e->impl->replay_last_batch_noalloc(out); });
+  return scheduling(e, [&] { e->impl->replay_last_batch_noalloc(out); });
 }
 
 }  // extern "C"
