@@ -81,6 +81,29 @@ int32_t ksb_pod_add(ksb_engine* e, const uint8_t* buf, size_t len);
  * (node_info.go:359-419). The pod is identified by namespace/name. */
 int32_t ksb_pod_remove(ksb_engine* e, const char* ns, size_t ns_len, const char* name, size_t name_len);
 
+/* ---- schedulercache.Cache as entry points of its own (schedulercache/interface.go:61-121) ----
+ * The pod state machine of schedulercache/cache.go (Initial -> Assumed -> Added -> Deleted, Assumed -> Expired; :44-66,
+ * :118-462) inside the library, for a caller that wants the informer handlers (factory/factory.go:554-778:
+ * addPodToCache, updatePodInCache, deletePodFromCache) to be one call each instead of keeping the states itself above
+ * ksb_pod_add / ksb_pod_remove. Each call decides from the states at the time of the call and returns the reference's
+ * own error text on a bad transition ("pod ns/name state wasn't initial but get assumed", ...; a text starting with
+ * "fatal:" is where the reference calls glog.Fatalf); what the transition does to the table goes through the mutator
+ * queue. buf = Pod record with NodeName set. Time is the caller's clock in seconds (the reference injects it the same
+ * way, cache.go:426-431). From the first ksb_cache_* call on, pods placed by ksb_schedule_batch enter as assumed.
+ * Nodes use ksb_node_upsert / ksb_node_remove (AddNode / UpdateNode / RemoveNode have no state machine). */
+void ksb_cache_set_ttl(ksb_engine* e, double seconds);                                          /* schedulercache.New(ttl, ..): 30 s */
+int32_t ksb_cache_assume_pod(ksb_engine* e, const uint8_t* buf, size_t len);                    /* cache.go:118-137 */
+int32_t ksb_cache_finish_binding(ksb_engine* e, const uint8_t* buf, size_t len, double now_seconds);  /* :139-160 */
+int32_t ksb_cache_forget_pod(ksb_engine* e, const uint8_t* buf, size_t len);                    /* :162-190 */
+int32_t ksb_cache_add_pod(ksb_engine* e, const uint8_t* buf, size_t len);                       /* :223-257 */
+int32_t ksb_cache_update_pod(ksb_engine* e, const uint8_t* old_buf, size_t old_len, const uint8_t* new_buf, size_t new_len); /* :259-285 */
+int32_t ksb_cache_remove_pod(ksb_engine* e, const uint8_t* buf, size_t len);                    /* :287-312 */
+int32_t ksb_cache_is_assumed_pod(ksb_engine* e, const uint8_t* buf, size_t len, int32_t* assumed);  /* :314-328 */
+int32_t ksb_cache_cleanup_assumed(ksb_engine* e, double now_seconds);                           /* cleanupAssumedPods, :431-462 */
+/* configFactory.skipPodUpdate (factory/factory.go:306-353): 1 when the pod is assumed and the update differs from the
+ * assumed pod in nothing but NodeName (ResourceVersion and Annotations do not cross this boundary at all). */
+int32_t ksb_cache_skip_pod_update(ksb_engine* e, const uint8_t* buf, size_t len, int32_t* skip);
+
 /* The listers SelectorSpread reads (algorithm/priorities/metadata.go:69-96; algorithm/types.go
  * ServiceLister/ControllerLister/ReplicaSetLister/StatefulSetLister). kind: 0 service, 1 RC,
  * 2 ReplicaSet, 3 StatefulSet. buf = SelectorOwner record. */

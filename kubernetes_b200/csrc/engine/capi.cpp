@@ -2,6 +2,7 @@
 #include <chrono>
 #include <cstdio>
 #include <functional>
+#include <map>
 #include <memory>
 #include <mutex>
 #include <thread>
@@ -27,6 +28,19 @@ struct ksb_engine {
   bool busy = false;  // a scheduling call (or its drain of the queue) owns the engine
   std::vector<std::function<void()>> queue;
   std::vector<std::string> deferred_errors;  // failures of queued mutators, kept for ksb_deferred_errors
+  // schedulercache.Cache's pod state machine (schedulercache/cache.go:44-66, :118-462) behind the ksb_cache_* entry
+  // points: which pods are assumed / added, on which node, and when an assumed pod expires. It decides at call time
+  // (its errors are the call's errors); what it does to the table goes through the delta queue like any mutator.
+  struct PodState {
+    std::string ns, name, node;
+    bool assumed = false, binding_finished = false;
+    double deadline = 0;
+    std::string record;  // the pod's wire record as it came in: what skipPodUpdate compares, NodeName aside (factory.go:312-353)
+  };
+  std::mutex cache_mu;
+  std::map<std::string, PodState> pod_states;
+  double cache_ttl = 30.0;     // factory.go:171: schedulercache.New(30*time.Second, ...)
+  bool cache_tracking = false;  // set by the first ksb_cache_* call: from then on ksb_schedule_batch's placements enter as assumed
 };
 
 namespace {
@@ -116,6 +130,56 @@ int32_t scheduling(ksb_engine* e, F&& f) {
     apply_deltas(e, take);
   }
   return rc;
+}
+}  // namespace
+
+// ---- schedulercache.Cache (schedulercache/interface.go:61-121): the state machine of cache.go, exported ----
+namespace {
+struct CacheFail : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+std::string blank_node_record(ksb::Pod p) {
+  p.node_name.clear();
+  ksb::wire::Writer w;
+  ksb::wire::put(w, p);
+  return std::string(w.buf.begin(), w.buf.end());
+}
+ksb::Pod decode_pod(const uint8_t* buf, size_t len) {
+  ksb::wire::Reader r(buf, len);
+  return ksb::wire::get_pod(r);
+}
+// engine side of a transition: through the delta queue; a failure on the spot is the call's failure
+void engine_add(ksb_engine* e, const ksb::Pod& p) {
+  auto sp = std::make_shared<ksb::Pod>(p);
+  if (mutate(e, [&]() -> std::function<void()> { return [e, sp] { e->impl->pod_add(*sp); }; }) != 0)
+    throw CacheFail(ksb_last_error(e));
+}
+void engine_remove(ksb_engine* e, const std::string& ns, const std::string& name) {
+  if (mutate(e, [&]() -> std::function<void()> { return [e, ns, name] { e->impl->pod_remove(ns, name); }; }) != 0)
+    throw CacheFail(ksb_last_error(e));
+}
+template <class F>
+int32_t cache_call(ksb_engine* e, F&& f) {
+  if (!e || !e->impl) return -1;
+  std::lock_guard<std::mutex> g(e->cache_mu);
+  e->cache_tracking = true;
+  try {
+    f();
+    return 0;
+  } catch (const std::exception& ex) {
+    std::lock_guard<std::mutex> g2(e->err_mu);
+    e->err = ex.what();
+    return -1;
+  }
+}
+ksb_engine::PodState make_state(const ksb::Pod& p, bool assumed, const uint8_t* buf, size_t len) {
+  ksb_engine::PodState st;
+  st.ns = p.ns;
+  st.name = p.name;
+  st.node = p.node_name;
+  st.assumed = assumed;
+  st.record.assign((const char*)buf, len);
+  return st;
 }
 }  // namespace
 
@@ -254,8 +318,30 @@ int32_t ksb_schedule_batch(ksb_engine* e, const uint8_t* pods, const uint64_t* o
     for (auto& msg : errors)
       if (!msg.empty()) throw std::runtime_error(msg);
     const double decode_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    // callers that drive the cache through ksb_cache_*: the pods this call places and assumes enter its state machine
+    // as assumed (scheduler.go:478 calls AssumePod right after Schedule; here both happen inside the batch)
+    bool tracking;
+    {
+      std::lock_guard<std::mutex> g(e->cache_mu);
+      tracking = e->cache_tracking;
+    }
+    std::vector<ksb_engine::PodState> noted;
+    if (tracking) {
+      noted.resize(batch.size());
+      for (size_t i = 0; i < batch.size(); ++i) noted[i] = make_state(batch[i], true, pods + offsets[i], (size_t)(offsets[i + 1] - offsets[i]));
+    }
     e->impl->schedule_batch(batch, out, true);
     e->impl->stats.last_batch_decode_ms = decode_ms;
+    if (tracking) {
+      std::lock_guard<std::mutex> g(e->cache_mu);
+      for (size_t i = 0; i < noted.size(); ++i) {
+        if (out[i].status != KSB_SCHEDULED) continue;
+        const std::string* host = e->impl->node_name_at(out[i].node_index);
+        if (!host) continue;
+        noted[i].node = *host;
+        e->pod_states[noted[i].ns + "/" + noted[i].name] = std::move(noted[i]);
+      }
+    }
   });
 }
 
@@ -332,6 +418,139 @@ int32_t ksb_node_info(ksb_engine* e, const char* name, size_t name_len, char* bu
     memcpy(buf, t.c_str(), t.size() + 1);
   });
   return rc != 0 ? rc : (small ? 1 : 0);
+}
+
+// ---- the exported state machine ----
+void ksb_cache_set_ttl(ksb_engine* e, double seconds) {
+  if (!e) return;
+  std::lock_guard<std::mutex> g(e->cache_mu);
+  e->cache_ttl = seconds;
+  e->cache_tracking = true;
+}
+
+int32_t ksb_cache_assume_pod(ksb_engine* e, const uint8_t* buf, size_t len) {  // cache.go:118-137
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    const std::string key = p.key();
+    if (e->pod_states.count(key)) throw CacheFail("pod " + key + " state wasn't initial but get assumed");
+    engine_add(e, p);
+    e->pod_states[key] = make_state(p, true, buf, len);
+  });
+}
+
+int32_t ksb_cache_finish_binding(ksb_engine* e, const uint8_t* buf, size_t len, double now_seconds) {  // cache.go:139-160
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    auto it = e->pod_states.find(p.key());
+    if (it != e->pod_states.end() && it->second.assumed) {
+      it->second.binding_finished = true;
+      it->second.deadline = now_seconds + e->cache_ttl;
+    }
+  });
+}
+
+int32_t ksb_cache_forget_pod(ksb_engine* e, const uint8_t* buf, size_t len) {  // cache.go:162-190
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    const std::string key = p.key();
+    auto it = e->pod_states.find(key);
+    if (it != e->pod_states.end() && it->second.node != p.node_name)
+      throw CacheFail("pod " + key + " state was assumed on a different node");
+    if (it != e->pod_states.end() && it->second.assumed) {
+      engine_remove(e, p.ns, p.name);
+      e->pod_states.erase(it);
+      return;
+    }
+    throw CacheFail("pod " + key + " state wasn't assumed but get forgotten");
+  });
+}
+
+int32_t ksb_cache_add_pod(ksb_engine* e, const uint8_t* buf, size_t len) {  // cache.go:223-257
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    const std::string key = p.key();
+    auto it = e->pod_states.find(key);
+    if (it != e->pod_states.end() && it->second.assumed) {
+      if (it->second.node != p.node_name) {  // added to a different node than it was assumed to
+        engine_remove(e, it->second.ns, it->second.name);
+        engine_add(e, p);
+      }
+      it->second = make_state(p, false, buf, len);
+      return;
+    }
+    if (it == e->pod_states.end()) {  // expired, or never seen: add it (back)
+      engine_add(e, p);
+      e->pod_states[key] = make_state(p, false, buf, len);
+      return;
+    }
+    throw CacheFail("pod was already in added state. Pod key: " + key);
+  });
+}
+
+int32_t ksb_cache_update_pod(ksb_engine* e, const uint8_t* old_buf, size_t old_len, const uint8_t* new_buf, size_t new_len) {
+  return cache_call(e, [&] {  // cache.go:259-285
+    ksb::Pod oldp = decode_pod(old_buf, old_len), newp = decode_pod(new_buf, new_len);
+    const std::string key = oldp.key();
+    auto it = e->pod_states.find(key);
+    if (it != e->pod_states.end() && !it->second.assumed) {
+      if (it->second.node != newp.node_name)
+        throw CacheFail("fatal: pod " + key + " updated on a different node than previously added to");
+      engine_remove(e, oldp.ns, oldp.name);
+      engine_add(e, newp);
+      // (the reference leaves the cached object stale here, cache.go:269-281; only NodeName is read from it later)
+      return;
+    }
+    throw CacheFail("pod " + key + " state wasn't added but get updated");
+  });
+}
+
+int32_t ksb_cache_remove_pod(ksb_engine* e, const uint8_t* buf, size_t len) {  // cache.go:287-312
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    const std::string key = p.key();
+    auto it = e->pod_states.find(key);
+    if (it != e->pod_states.end() && !it->second.assumed) {
+      if (it->second.node != p.node_name)
+        throw CacheFail("fatal: pod " + key + " removed from a different node than previously added to");
+      engine_remove(e, it->second.ns, it->second.name);
+      e->pod_states.erase(it);
+      return;
+    }
+    throw CacheFail("pod state wasn't added but get removed. Pod key: " + key);
+  });
+}
+
+int32_t ksb_cache_is_assumed_pod(ksb_engine* e, const uint8_t* buf, size_t len, int32_t* assumed) {  // cache.go:314-328
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    auto it = e->pod_states.find(p.key());
+    if (assumed) *assumed = it != e->pod_states.end() && it->second.assumed ? 1 : 0;
+  });
+}
+
+int32_t ksb_cache_cleanup_assumed(ksb_engine* e, double now_seconds) {  // cache.go:431-462
+  return cache_call(e, [&] {
+    for (auto it = e->pod_states.begin(); it != e->pod_states.end();) {
+      ksb_engine::PodState& st = it->second;
+      if (st.assumed && st.binding_finished && now_seconds > st.deadline) {  // binding still in progress: keep
+        engine_remove(e, st.ns, st.name);
+        it = e->pod_states.erase(it);
+      } else {
+        ++it;
+      }
+    }
+  });
+}
+
+int32_t ksb_cache_skip_pod_update(ksb_engine* e, const uint8_t* buf, size_t len, int32_t* skip) {  // factory.go:306-353
+  return cache_call(e, [&] {
+    ksb::Pod p = decode_pod(buf, len);
+    auto it = e->pod_states.find(p.key());
+    bool s = false;
+    if (it != e->pod_states.end() && it->second.assumed)
+      s = blank_node_record(p) == blank_node_record(decode_pod((const uint8_t*)it->second.record.data(), it->second.record.size()));
+    if (skip) *skip = s ? 1 : 0;
+  });
 }
 
 int32_t ksb_deferred_errors(ksb_engine* e, char* buf, size_t buf_len) {

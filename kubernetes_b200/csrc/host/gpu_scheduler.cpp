@@ -102,7 +102,10 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
   const bool want_scores = opt.get_bool("scores", false);  // "scores": per pod, {node: total} over the filtered list (batch 0 only)
   std::vector<std::string> scores_json(np);
   GpuScheduler sched(h);
-  CacheDecorator cache(h);
+  // one-pod mode drives the exported cache state machine (AssumePod after every Schedule); batch mode leaves it off, so
+  // that ksb_schedule_batch does not record every pod it places
+  std::unique_ptr<CacheDecorator> cache_holder;
+  if (batch == 0) cache_holder = std::make_unique<CacheDecorator>(h);
   double kernel_ms = 0, encode_ms = 0, replay_ms = 0, decode_ms = 0, post_ms = 0, sync_ms = 0;
   std::vector<double> lat_us;
   std::vector<double> call_us;  // batch mode: duration of each ksb_schedule_batch call
@@ -178,7 +181,7 @@ std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double l
           auto it = o.binding.find(e.name);
           if (it != o.binding.end()) e.assigned = it->second;
         }
-        const std::string cache_err = cache.AssumePod(assumed);
+        const std::string cache_err = cache_holder->AssumePod(assumed);
         if (!cache_err.empty()) throw std::runtime_error(cache_err);
       } catch (const FitError& fe) {
         messages[i] = fe.what();

@@ -63,126 +63,56 @@ class EngineHandle {
 // and injected, as the reference's tests do with finishBinding / cleanupAssumedPods.
 class CacheDecorator {
  public:
-  explicit CacheDecorator(EngineHandle& h, double ttl_seconds = 30.0) : h_(h), ttl_(ttl_seconds) {}
+  // A thin wrapper: the state machine itself is the library's (ksb_cache_*, include/ksched_b200.h), so that the
+  // vectors of schedulercache/cache_test.go run against the exported entry points.
+  explicit CacheDecorator(EngineHandle& h, double ttl_seconds = 30.0) : h_(h) { ksb_cache_set_ttl(h_.get(), ttl_seconds); }
   void AddNode(const Node& n) { upsert(n); }
   void UpdateNode(const Node& /*old*/, const Node& n) { upsert(n); }
   void RemoveNode(const Node& n) { h_.check(ksb_node_remove(h_.get(), n.name.data(), n.name.size()), "RemoveNode"); }
 
-  std::string AssumePod(const Pod& p) {  // :118-137
-    const std::string key = p.key();
-    if (states_.count(key)) return "pod " + key + " state wasn't initial but get assumed";
-    add(p, "AssumePod");
-    states_[key].pod = p;
-    assumed_.insert(key);
-    return "";
+  std::string AssumePod(const Pod& p) { return call(p, [&](const uint8_t* b, size_t n) { return ksb_cache_assume_pod(h_.get(), b, n); }); }
+  std::string FinishBinding(const Pod& p, double now) {
+    return call(p, [&](const uint8_t* b, size_t n) { return ksb_cache_finish_binding(h_.get(), b, n, now); });
   }
-  std::string FinishBinding(const Pod& p, double now) {  // :139-160
-    auto it = states_.find(p.key());
-    if (it != states_.end() && assumed_.count(p.key())) {
-      it->second.binding_finished = true;
-      it->second.has_deadline = true;
-      it->second.deadline = now + ttl_;
-    }
-    return "";
+  std::string ForgetPod(const Pod& p) { return call(p, [&](const uint8_t* b, size_t n) { return ksb_cache_forget_pod(h_.get(), b, n); }); }
+  std::string AddPod(const Pod& p) { return call(p, [&](const uint8_t* b, size_t n) { return ksb_cache_add_pod(h_.get(), b, n); }); }
+  std::string UpdatePod(const Pod& oldp, const Pod& newp) {
+    wire::Writer wo;
+    wire::put(wo, oldp);
+    return call(newp, [&](const uint8_t* b, size_t n) {
+      return ksb_cache_update_pod(h_.get(), (const uint8_t*)wo.buf.data(), wo.buf.size(), b, n);
+    });
   }
-  std::string ForgetPod(const Pod& p) {  // :162-190
-    const std::string key = p.key();
-    auto it = states_.find(key);
-    if (it != states_.end() && it->second.pod.node_name != p.node_name) return "pod " + key + " state was assumed on a different node";
-    if (it != states_.end() && assumed_.count(key)) {
-      remove(p, "ForgetPod");
-      assumed_.erase(key);
-      states_.erase(key);
-      return "";
-    }
-    return "pod " + key + " state wasn't assumed but get forgotten";
+  std::string RemovePod(const Pod& p) { return call(p, [&](const uint8_t* b, size_t n) { return ksb_cache_remove_pod(h_.get(), b, n); }); }
+  bool IsAssumedPod(const Pod& p) const {
+    int32_t a = 0;
+    wire::Writer w;
+    wire::put(w, p);
+    ksb_cache_is_assumed_pod(h_.get(), (const uint8_t*)w.buf.data(), w.buf.size(), &a);
+    return a != 0;
   }
-  std::string AddPod(const Pod& p) {  // :223-257
-    const std::string key = p.key();
-    auto it = states_.find(key);
-    if (it != states_.end() && assumed_.count(key)) {
-      if (it->second.pod.node_name != p.node_name) {  // added to a different node than it was assumed to
-        remove(it->second.pod, "AddPod");
-        add(p, "AddPod");
-      }
-      assumed_.erase(key);
-      it->second.has_deadline = false;
-      it->second.pod = p;
-      return "";
-    }
-    if (it == states_.end()) {  // expired, or never seen: add it (back)
-      add(p, "AddPod");
-      states_[key].pod = p;
-      return "";
-    }
-    return "pod was already in added state. Pod key: " + key;
-  }
-  std::string UpdatePod(const Pod& oldp, const Pod& newp) {  // :259-285
-    const std::string key = oldp.key();
-    auto it = states_.find(key);
-    if (it != states_.end() && !assumed_.count(key)) {
-      if (it->second.pod.node_name != newp.node_name)
-        return "fatal: pod " + key + " updated on a different node than previously added to";
-      remove(oldp, "UpdatePod");
-      add(newp, "UpdatePod");
-      return "";
-    }
-    return "pod " + key + " state wasn't added but get updated";
-  }
-  std::string RemovePod(const Pod& p) {  // :287-312
-    const std::string key = p.key();
-    auto it = states_.find(key);
-    if (it != states_.end() && !assumed_.count(key)) {
-      if (it->second.pod.node_name != p.node_name)
-        return "fatal: pod " + key + " removed from a different node than previously added to";
-      remove(it->second.pod, "RemovePod");
-      states_.erase(key);
-      return "";
-    }
-    return "pod state wasn't added but get removed. Pod key: " + key;
-  }
-  bool IsAssumedPod(const Pod& p) const { return assumed_.count(p.key()) != 0; }  // :314-328
-  void CleanupAssumedPods(double now) {  // :431-462
-    std::vector<std::string> keys(assumed_.begin(), assumed_.end());
-    for (auto& key : keys) {
-      State& st = states_.at(key);
-      if (!st.binding_finished) continue;  // binding still in progress
-      if (now > st.deadline) {
-        remove(st.pod, "expirePod");
-        assumed_.erase(key);
-        states_.erase(key);
-      }
-    }
-  }
-  // Pods the engine placed and assumed itself (ksb_schedule_batch) enter the state machine as assumed.
-  void NoteAssumed(const Pod& p) {
-    states_[p.key()].pod = p;
-    assumed_.insert(p.key());
+  void CleanupAssumedPods(double now) { h_.check(ksb_cache_cleanup_assumed(h_.get(), now), "cleanupAssumedPods"); }
+  bool SkipPodUpdate(const Pod& p) const {  // factory.go:306-353
+    int32_t s = 0;
+    wire::Writer w;
+    wire::put(w, p);
+    ksb_cache_skip_pod_update(h_.get(), (const uint8_t*)w.buf.data(), w.buf.size(), &s);
+    return s != 0;
   }
 
  private:
-  struct State {
-    Pod pod;
-    bool binding_finished = false;
-    bool has_deadline = false;
-    double deadline = 0;
-  };
   EngineHandle& h_;
-  double ttl_;
-  std::map<std::string, State> states_;
-  std::set<std::string> assumed_;
+  template <class F>
+  std::string call(const Pod& p, F&& f) {
+    wire::Writer w;
+    wire::put(w, p);
+    if (f((const uint8_t*)w.buf.data(), w.buf.size()) == 0) return "";
+    return ksb_last_error(h_.get());
+  }
   void upsert(const Node& n) {
     wire::Writer w;
     wire::put(w, n);
     h_.check(ksb_node_upsert(h_.get(), (const uint8_t*)w.buf.data(), w.buf.size()), "AddNode");
-  }
-  void add(const Pod& p, const char* what) {
-    wire::Writer w;
-    wire::put(w, p);
-    h_.check(ksb_pod_add(h_.get(), (const uint8_t*)w.buf.data(), w.buf.size()), what);
-  }
-  void remove(const Pod& p, const char* what) {
-    h_.check(ksb_pod_remove(h_.get(), p.ns.data(), p.ns.size(), p.name.data(), p.name.size()), what);
   }
 };
 
