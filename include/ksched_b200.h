@@ -111,6 +111,27 @@ int32_t ksb_selector_owner_upsert(ksb_engine* e, int32_t kind, const uint8_t* bu
 int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, size_t ns_len, const char* name,
                                   size_t name_len);
 
+/* ---- plugins a Policy enables next to the DefaultProvider set (api/types.go:36-125; registered by name in
+ * algorithmprovider/defaults/defaults.go:93-116) ----
+ * Call before the first ksb_schedule* (any later call re-lays the table). kind:
+ *   KSB_POLICY_NODE_LABEL_PRIORITY  adds one NodeLabelPriority instance (priorities/node_label.go:29-60): label = key,
+ *                                   `presence`, `weight`
+ *   KSB_POLICY_LABEL_PRESENCE       adds `key` to the labels of the CheckNodeLabelPresence predicate
+ *                                   (predicates/predicates.go:778-826); `presence` is the predicate's one flag
+ *   KSB_POLICY_MOST_REQUESTED       MostRequestedPriority (priorities/most_requested.go:32-88) with `weight`
+ *   KSB_POLICY_RESOURCE_LIMITS      ResourceLimitsPriority (priorities/resource_limits.go:34-126) with `weight`
+ *   KSB_POLICY_CLEAR                back to the DefaultProvider set
+ * The other Policy-only plugins (ImageLocalityPriority, ServiceSpreadingPriority / ServiceAntiAffinity, the ServiceAffinity
+ * predicate) are not implemented: a factory that is asked for them must refuse, as gpusched.New does for unknown keys. */
+enum {
+  KSB_POLICY_NODE_LABEL_PRIORITY = 0,
+  KSB_POLICY_LABEL_PRESENCE = 1,
+  KSB_POLICY_MOST_REQUESTED = 2,
+  KSB_POLICY_RESOURCE_LIMITS = 3,
+  KSB_POLICY_CLEAR = 4
+};
+int32_t ksb_policy_set(ksb_engine* e, int32_t kind, const char* key, size_t key_len, int32_t presence, int32_t weight);
+
 /* ---- the hot path ---- */
 
 enum {

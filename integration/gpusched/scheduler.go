@@ -30,6 +30,7 @@ var supportedPredicates = map[string]bool{
 	"CheckNodeMemoryPressure": true, "CheckNodeDiskPressure": true, "MatchInterPodAffinity": true,
 	// volume predicates are registered by the DefaultProvider and are trivially true for pods without volumes; the
 	// engine refuses pods that have volumes (no CPU fallback), so accepting the keys is safe
+	"CheckNodeLabelPresence": true, // with its labels passed through AddLabelPresence
 	"NoVolumeZoneConflict": true, "MaxEBSVolumeCount": true, "MaxGCEPDVolumeCount": true,
 	"MaxAzureDiskVolumeCount": true, "NoDiskConflict": true, "CheckVolumeBinding": true,
 }
@@ -42,6 +43,12 @@ var weightField = map[string]func(*C.ksb_config, C.int32_t){
 	"TaintTolerationPriority":     func(c *C.ksb_config, w C.int32_t) { c.w_taint_toleration = w },
 	"InterPodAffinityPriority":    func(c *C.ksb_config, w C.int32_t) { c.w_inter_pod_affinity = w },
 	"NodePreferAvoidPodsPriority": func(c *C.ksb_config, w C.int32_t) { c.w_prefer_avoid = w },
+}
+
+// priorities a Policy can enable by name that take no arguments (ksb_policy_set)
+var policyWeightKind = map[string]C.int32_t{
+	"MostRequestedPriority":  C.KSB_POLICY_MOST_REQUESTED,
+	"ResourceLimitsPriority": C.KSB_POLICY_RESOURCE_LIMITS,
 }
 
 // GPUScheduler implements algorithm.ScheduleAlgorithm.
@@ -65,7 +72,12 @@ func New(predicateKeys []string, priorityWeights map[string]int, hardPodAffinity
 		set(&cfg, 0) // a priority that is not configured does not count
 		_ = name
 	}
+	policyWeights := map[string]int{}
 	for name, w := range priorityWeights {
+		if _, ok := policyWeightKind[name]; ok {
+			policyWeights[name] = w
+			continue
+		}
 		set, ok := weightField[name]
 		if !ok {
 			return nil, fmt.Errorf("gpusched: priority %q is not implemented by the GPU engine", name)
@@ -78,7 +90,38 @@ func New(predicateKeys []string, priorityWeights map[string]int, hardPodAffinity
 	if e == nil {
 		return nil, fmt.Errorf("ksb_create: %s", C.GoString(&errbuf[0]))
 	}
+	for name, w := range policyWeights {
+		if C.ksb_policy_set(e, policyWeightKind[name], nil, 0, 0, C.int32_t(w)) != 0 {
+			return nil, fmt.Errorf("ksb_policy_set: %s", C.GoString(C.ksb_last_error(e)))
+		}
+	}
 	return &GPUScheduler{e: e, generic: generic}, nil
+}
+
+// AddNodeLabelPriority / AddLabelPresence: the Policy plugins that carry arguments (api/types.go:64-125:
+// LabelPreference, LabelsPresence). Called by the factory for each such entry of the Policy, before the first Schedule.
+func (g *GPUScheduler) AddNodeLabelPriority(label string, presence bool, weight int) error {
+	p := C.int32_t(0)
+	if presence {
+		p = 1
+	}
+	if C.ksb_policy_set(g.e, C.KSB_POLICY_NODE_LABEL_PRIORITY, (*C.char)(unsafe.Pointer(unsafe.StringData(label))), C.size_t(len(label)), p, C.int32_t(weight)) != 0 {
+		return g.lastError()
+	}
+	return nil
+}
+
+func (g *GPUScheduler) AddLabelPresence(labels []string, presence bool) error {
+	p := C.int32_t(0)
+	if presence {
+		p = 1
+	}
+	for _, l := range labels {
+		if C.ksb_policy_set(g.e, C.KSB_POLICY_LABEL_PRESENCE, (*C.char)(unsafe.Pointer(unsafe.StringData(l))), C.size_t(len(l)), p, 0) != 0 {
+			return g.lastError()
+		}
+	}
+	return nil
 }
 
 func (g *GPUScheduler) lastError() error { return fmt.Errorf("%s", C.GoString(C.ksb_last_error(g.e))) }

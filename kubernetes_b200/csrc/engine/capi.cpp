@@ -553,6 +553,10 @@ int32_t ksb_cache_skip_pod_update(ksb_engine* e, const uint8_t* buf, size_t len,
   });
 }
 
+int32_t ksb_policy_set(ksb_engine* e, int32_t kind, const char* key, size_t key_len, int32_t presence, int32_t weight) {
+  return scheduling(e, [&] { e->impl->policy_set(kind, std::string(key ? key : "", key ? key_len : 0), presence != 0, weight); });
+}
+
 int32_t ksb_deferred_errors(ksb_engine* e, char* buf, size_t buf_len) {
   if (!e || !e->impl) return -1;
   std::lock_guard<std::mutex> q(e->q_mu);

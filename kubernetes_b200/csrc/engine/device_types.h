@@ -31,13 +31,14 @@
 #define NF_UNSCHEDULABLE 8u
 #define NF_MEM_PRESSURE 16u
 #define NF_DISK_PRESSURE 32u
+#define NF_LABEL_PRESENCE 64u  // CheckNodeLabelPresence (Policy-enabled predicate) fails on this node
 
 // failure-reason bits (error.go:33-54, :84-86)
 enum {
   RB_PODS = 0, RB_CPU, RB_MEM, RB_AGPU, RB_EPH, RB_SCALAR0, RB_SCALAR1, RB_SCALAR2, RB_SCALAR3,
   RB_HOSTNAME, RB_PORTS, RB_SELECTOR, RB_TAINTS, RB_MEM_PRESSURE, RB_DISK_PRESSURE, RB_NOT_READY,
   RB_OUT_OF_DISK, RB_NET_UNAVAILABLE, RB_UNSCHEDULABLE, RB_IPA, RB_IPA_EXISTING_ANTI, RB_IPA_AFFINITY,
-  RB_IPA_ANTI, RB_EXT0, RB_EXT1, RB_EXT2, RB_EXT3, RB_EXT_LIMITS
+  RB_IPA_ANTI, RB_EXT0, RB_EXT1, RB_EXT2, RB_EXT3, RB_EXT_LIMITS, RB_LABEL_PRESENCE
 };
 
 // pod flags
@@ -67,6 +68,7 @@ struct KsbNodeTable {
   int32_t n_pad;     // column stride
   int32_t row_base;  // global row of local row 0
   int32_t n_total;   // rows over all shards
+  int32_t w_mr, w_rl; // MostRequestedPriority / ResourceLimitsPriority weights (0: not enabled by the Policy)
   int32_t W;         // label words
   int32_t tw;        // 64-bit words of each taint / preferAvoid set (columns taint_hard, taint_soft, avoid hold tw words each,
                      // word w at + w * n_pad; a pod's masks for the words above 0 trail its pool block)
@@ -88,6 +90,7 @@ struct KsbNodeTable {
   uint64_t *avoid;        // preferAvoidPods controller refs
   uint64_t *port_any, *port_wild, *port_exact;  // [KSB_PORT_WORDS][n_pad]
   uint32_t *dev_avail;    // [KSB_MAX_RES][n_pad]
+  int32_t *static_score;  // [n_pad] weighted sum of the node's NodeLabelPriority scores (the u32 column after dev_avail)
   uint16_t *dev_class;    // [KSB_MAX_RES][n_pad][KSB_MAX_DEV]
   uint32_t *topo;         // [KSB_MAX_TOPO][n_pad] domain ids, 0 = label absent
   uint32_t *spread;       // [spread classes][n_pad] matching-pod counts (selector_spreading.go:85-108)
@@ -108,6 +111,7 @@ struct __attribute__((aligned(16))) KsbPodHeader {
   int64_t scalar_req[KSB_MAX_SCALARS];
   int64_t scalar_add[KSB_MAX_SCALARS];
   uint64_t hard_untol, soft_untol, avoid_mask;
+  int64_t lim_cpu, lim_mem;  // the pod's cpu / memory limits (resource_limits.go:96-126), for ResourceLimitsPriority
   uint32_t flags;
   int32_t pinned_row;  // PodFitsHost: -1 no pin, -2 pinned to an unknown node, else global row
   int32_t spread_col;  // -1: pod has no selectors

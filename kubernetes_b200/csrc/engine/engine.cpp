@@ -783,6 +783,37 @@ void Engine::fill_devices(int row) {
 
 // Everything about one row that derives from its Node object and its aggregates (not the
 // per-class counters, which follow the pods).
+void Engine::policy_set(int kind, const std::string& key, bool presence, int32_t weight) {
+  std::lock_guard<std::mutex> g(mu);
+  have_snapshot = false;
+  switch (kind) {
+    case 0:
+      if (key.empty()) throw std::runtime_error("NodeLabelPriority needs a label");
+      pol_node_label.push_back(NodeLabelPrio{key, presence, weight});
+      break;
+    case 1:
+      if (key.empty()) throw std::runtime_error("CheckNodeLabelPresence needs a label");
+      pol_presence_labels.push_back(key);
+      pol_presence = presence;
+      break;
+    case 2:
+      w_most_requested = weight;
+      break;
+    case 3:
+      w_resource_limits = weight;
+      break;
+    case 4:
+      pol_node_label.clear();
+      pol_presence_labels.clear();
+      pol_presence = true;
+      w_most_requested = w_resource_limits = 0;
+      break;
+    default:
+      throw std::runtime_error("unknown policy plugin kind");
+  }
+  layout_dirty = true;  // per-node facts are recomputed with the table
+}
+
 // Bit index of a new entry of a taint / preferAvoid set that already holds `have`. When the set outgrows its words, the
 // word count grows (up to KSB_MAX_TAINT_WORDS) and the table is re-laid on the next sync: the row being filled keeps
 // going (its bits beyond the current words are dropped here and set by the rebuild, which recomputes every row).
@@ -852,6 +883,21 @@ void Engine::fill_row(int row) {
     }
   }
   u32(U32_ZONE, row) = zone;
+  {  // Policy plugins that depend on the node alone (node_label.go:46-60, predicates.go:800-826)
+    int32_t sscore = 0;
+    for (auto& a : pol_node_label) {
+      const bool exists = nd.has_labels && nd.labels.count(a.label) != 0;
+      if ((exists && a.presence) || (!exists && !a.presence)) sscore += 10 * a.weight;
+    }
+    u32(U32_STATIC, row) = (uint32_t)sscore;
+    for (auto& l : pol_presence_labels) {
+      const bool exists = nd.has_labels && nd.labels.count(l) != 0;
+      if ((exists && !pol_presence) || (!exists && pol_presence)) {
+        u32(U32_FLAGS, row) |= NF_LABEL_PRESENCE;
+        break;
+      }
+    }
+  }
   for (int w = 0; w < W; ++w) u64(w, row) = 0;
   for (size_t b = 0; b < label_defs.size(); ++b)
     if (node_has_label_bit(nd, label_defs[b])) u64((int)(b >> 6), row) |= 1ull << (b & 63);

@@ -124,6 +124,19 @@ class Engine {
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void flush();
   void resync_begin();
+  // Plugins a Policy enables next to the DefaultProvider set (api/types.go:36-125): NodeLabelPriority instances and the
+  // CheckNodeLabelPresence labels are per-node facts computed on the host (a score column, a node flag); the
+  // MostRequestedPriority and ResourceLimitsPriority weights go to the kernel.
+  struct NodeLabelPrio {
+    std::string label;
+    bool presence;
+    int32_t weight;
+  };
+  std::vector<NodeLabelPrio> pol_node_label;
+  std::vector<std::string> pol_presence_labels;
+  bool pol_presence = true;
+  int32_t w_most_requested = 0, w_resource_limits = 0;
+  void policy_set(int kind, const std::string& key, bool presence, int32_t weight);
   void warm_dictionaries();
   std::string node_info_json(const std::string& name);
   void grow_keep(DevBuf& b, size_t bytes);
@@ -249,7 +262,8 @@ class Engine {
   enum { I64_ALLOC_CPU = 0, I64_ALLOC_MEM, I64_ALLOC_AGPU, I64_ALLOC_EPH, I64_REQ_CPU, I64_REQ_MEM, I64_REQ_AGPU,
          I64_REQ_EPH, I64_NZ_CPU, I64_NZ_MEM, I64_ALLOC_SCALAR, I64_REQ_SCALAR = I64_ALLOC_SCALAR + KSB_MAX_SCALARS,
          I64_COLS = I64_REQ_SCALAR + KSB_MAX_SCALARS };
-  enum { U32_ALLOC_PODS = 0, U32_NUM_PODS, U32_FLAGS, U32_ZONE, U32_DEV_AVAIL, U32_COLS = U32_DEV_AVAIL + KSB_MAX_RES };
+  enum { U32_ALLOC_PODS = 0, U32_NUM_PODS, U32_FLAGS, U32_ZONE, U32_DEV_AVAIL, U32_STATIC = U32_DEV_AVAIL + KSB_MAX_RES,
+         U32_COLS = U32_STATIC + 1 };
   // taint / preferAvoid sets: TW 64-bit words each (1 until a 65th distinct entry is interned; growing re-lays the table)
   int TW = 1, pending_TW = 1;
   int u64_cols() const { return W + 3 * TW + 3 * KSB_PORT_WORDS; }

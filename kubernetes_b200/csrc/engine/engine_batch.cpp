@@ -1136,7 +1136,7 @@ std::string Engine::reason_name(int bit) {
       "MatchNodeSelector", "PodToleratesNodeTaints", "NodeUnderMemoryPressure", "NodeUnderDiskPressure", "NodeNotReady",
       "NodeOutOfDisk", "NodeNetworkUnavailable", "NodeUnschedulable", "MatchInterPodAffinity",
       "ExistingPodsAntiAffinityRulesNotMatch", "PodAffinityRulesNotMatch", "PodAntiAffinityRulesNotMatch", nullptr, nullptr,
-      nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      nullptr, nullptr, nullptr, "CheckNodeLabelPresence", nullptr, nullptr, nullptr};
   if (bit < 0 || bit >= KSB_REASON_BITS) throw std::runtime_error("reason bit out of range");
   if (fixed[bit]) return fixed[bit];
   if (bit >= RB_SCALAR0 && bit <= RB_SCALAR3)
@@ -1162,7 +1162,7 @@ std::string Engine::fit_error_message(int i) {
       "MatchNodeSelector", "PodToleratesNodeTaints", "NodeUnderMemoryPressure", "NodeUnderDiskPressure", "NodeNotReady",
       "NodeOutOfDisk", "NodeNetworkUnavailable", "NodeUnschedulable", "MatchInterPodAffinity",
       "ExistingPodsAntiAffinityRulesNotMatch", "PodAffinityRulesNotMatch", "PodAntiAffinityRulesNotMatch", nullptr, nullptr,
-      nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      nullptr, nullptr, nullptr, "CheckNodeLabelPresence", nullptr, nullptr, nullptr};
   std::map<std::string, int> reasons;
   for (int b = 0; b < KSB_REASON_BITS; ++b) {
     if (hist[b] == 0) continue;

@@ -306,6 +306,22 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
   }
   h.n_exprs = (uint8_t)n_exprs;
 
+  // --- pod limits (resource_limits.go:96-126): sum over the containers, raised to any init container's
+  {
+    int64_t lc = 0, lm = 0;
+    for (auto& c : p.containers)
+      for (auto& kv : c.limits) {
+        if (kv.first == kResCPU) lc += kv.second;
+        else if (kv.first == kResMemory) lm += kv.second;
+      }
+    for (auto& c : p.init_containers)
+      for (auto& kv : c.limits) {
+        if (kv.first == kResCPU) lc = std::max(lc, kv.second);
+        else if (kv.first == kResMemory) lm = std::max(lm, kv.second);
+      }
+    h.lim_cpu = lc;
+    h.lim_mem = lm;
+  }
   // --- taints (predicates.go:1349-1373, taint_toleration.go:29-53)
   // word 0 of each set travels in the header, the words above it (engines with more than 64 distinct entries) behind
   // the pool block: [TW-1] hard, [TW-1] soft, [TW-1] preferAvoid
@@ -561,6 +577,8 @@ void Engine::setup_table_pointers() {
   T.W = W;
   T.n_zones = (int)zone_idx.size() + 1;
   T.w_lr = cfg.w_least_requested;
+  T.w_mr = w_most_requested;
+  T.w_rl = w_resource_limits;
   T.w_bra = cfg.w_balanced;
   T.w_ss = cfg.w_selector_spread;
   T.w_na = cfg.w_node_affinity;
@@ -593,6 +611,7 @@ void Engine::fill_table_pointers(KsbNodeTable* T, void* i64b, void* u32b, void* 
   T->flags = b + (size_t)U32_FLAGS * np;
   T->zone = b + (size_t)U32_ZONE * np;
   T->dev_avail = b + (size_t)U32_DEV_AVAIL * np;
+  T->static_score = reinterpret_cast<int32_t*>(b + (size_t)U32_STATIC * np);
   uint64_t* c = (uint64_t*)u64b;
   T->labels = c;
   T->tw = TW;

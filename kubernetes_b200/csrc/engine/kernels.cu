@@ -322,6 +322,7 @@ struct RowCommon {
   uint32_t nflags, zone;
   double rcp_cpu, rcp_mem;  // fast_rcp of the allocatable cpu / memory (lr_bra)
   uint32_t over;            // bit 0: allocatable alpha-gpu < requested on the row, bit 1: the same for ephemeral storage
+  int32_t sscore;           // the node's NodeLabelPriority sum (0 unless a Policy configured some)
 };
 
 template <bool CG>
@@ -337,6 +338,7 @@ __device__ __forceinline__ void load_row_common(const KsbNodeTable& T, int r, Ro
   rc.nmem = ldx<CG>(T.nz_mem + r);
   rc.nflags = T.flags[r];
   rc.zone = T.zone[r];
+  rc.sscore = T.static_score[r];
   rc.hard = T.taint_hard[r];
   rc.soft = T.taint_soft[r];
   rc.avoid = T.avoid[r];
@@ -392,6 +394,25 @@ __device__ __forceinline__ bool eval_expr4(const uint64_t (&lab)[kLabFast], cons
       if (all) na += h->pref_weight[t];                                          \
     }                                                                            \
   } while (0)
+
+// The priorities a Policy can enable next to the DefaultProvider set (Map only, no Reduce), as one addend to the
+// bind-dependent part of the score: MostRequestedPriority (most_requested.go:32-88) over the same non-zero totals as
+// LeastRequested, ResourceLimitsPriority (resource_limits.go:34-94) and the node's NodeLabelPriority sum (node_label.go).
+__device__ __forceinline__ int32_t policy_score(const KsbNodeTable& T, const KsbPodHeader* h, int64_t cpu, int64_t mem, int64_t acpu,
+                                                int64_t amem, int32_t static_score) {
+  int32_t s = static_score;
+  if (T.w_mr) {
+    const int64_t cs = (acpu == 0 || cpu > acpu) ? 0 : (cpu * 10) / acpu;
+    const int64_t ms = (amem == 0 || mem > amem) ? 0 : (mem * 10) / amem;
+    s += T.w_mr * (int32_t)((cs + ms) / 2);
+  }
+  if (T.w_rl) {
+    const bool c1 = h->lim_cpu != 0 && acpu != 0 && h->lim_cpu <= acpu;
+    const bool m1 = h->lim_mem != 0 && amem != 0 && h->lim_mem <= amem;
+    s += T.w_rl * ((c1 || m1) ? 1 : 0);
+  }
+  return s;
+}
 
 // Everything the reference computes for one (pod, node): podFitsOnNode's predicates
 // (core/generic_scheduler.go:402-501) and the Map functions of PrioritizeNodes (:557-574).
@@ -487,6 +508,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   if (nflags & NF_OUT_OF_DISK) reasons |= 1u << RB_OUT_OF_DISK;
   if (nflags & NF_NET_UNAVAILABLE) reasons |= 1u << RB_NET_UNAVAILABLE;
   if (nflags & NF_UNSCHEDULABLE) reasons |= 1u << RB_UNSCHEDULABLE;
+  if (nflags & NF_LABEL_PRESENCE) reasons |= 1u << RB_LABEL_PRESENCE;  // CheckNodeLabelPresence (predicates.go:800-826), per node on the host
   // --- MatchInterPodAffinity (predicates.go:1047-1346) over per-(term class, topology domain) counts.
   //     Inside a group no pod reads a table an earlier pod of the group writes, so plain loads do.
   for (int i = 0; i < h->n_checks; ++i) {
@@ -531,7 +553,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   int32_t lr, bra;  // least_requested.go:63-91, balanced_resource_allocation.go:51-100
   lr_bra(cpu, mem, acpu, amem, rc.rcp_cpu, rc.rcp_mem, &lr, &bra);
   const int32_t av = avoid_hit ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
-  o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
+  o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av + policy_score(T, h, cpu, mem, acpu, amem, rc.sscore);
   o.na = na;
   o.tt = tt;
   o.sc = h->spread_col >= 0 ? ldx<CG>(T.spread + (size_t)h->spread_col * np + r) : 0u;  // selector_spreading.go:64-113
@@ -894,6 +916,7 @@ struct RowCache {
   int32_t apods, npods;
   uint32_t flags, zone;
   uint32_t avail[KSB_MAX_RES];
+  int32_t sscore;  // the node's NodeLabelPriority sum (static; the u32 column after dev_avail)
   int32_t row, pad;
   // per extended-resource entry slot: which devices of the row match the class mask interned as `mid` (0: none kept)
   uint32_t mm[KSB_MAX_EXT];
@@ -991,7 +1014,7 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   if (T.tw > 1)  // the words above 0 of the preferAvoid set: static columns, read in place
     for (int w = 0; w < T.tw - 1; ++w) avoid_hit |= T.avoid[(size_t)(w + 1) * T.n_pad + c.row] & pv.tw_ext[2 * (T.tw - 1) + w];
   const int32_t av = avoid_hit ? 0 : 10;
-  *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
+  *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av + policy_score(T, h, cpu, mem, acpu, amem, c.sscore);
 }
 
 // One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads). In two steps, so
@@ -1003,19 +1026,19 @@ __device__ __forceinline__ void cache_fill_issue(const KsbNodeTable& T, int r, i
   const int64_t* p = lane < 18   ? T.alloc_cpu + (size_t)lane * np + r
                      : lane == 30 ? reinterpret_cast<const int64_t*>(T.avoid) + r  // word 0 of the preferAvoid set
                                   : reinterpret_cast<const int64_t*>(T.port_any) + (size_t)(lane - 18) * np + r;
-  // lanes 0..5: the u32 family from alloc_pods on (alloc_pods, num_pods, flags, zone, dev_avail[2])
-  const uint32_t* p2 = reinterpret_cast<const uint32_t*>(T.alloc_pods) + (size_t)(lane < 4 + KSB_MAX_RES ? lane : 0) * np + r;
+  // lanes 0..6: the u32 family from alloc_pods on (alloc_pods, num_pods, flags, zone, dev_avail[2], static_score)
+  const uint32_t* p2 = reinterpret_cast<const uint32_t*>(T.alloc_pods) + (size_t)(lane < 5 + KSB_MAX_RES ? lane : 0) * np + r;
   int64_t v = 0;
   uint32_t v2 = 0;
   if (lane < 31) v = __ldcg(p);
-  if (lane < 4 + KSB_MAX_RES) v2 = __ldcg(p2);
+  if (lane < 5 + KSB_MAX_RES) v2 = __ldcg(p2);
   *v_out = v;
   *v2_out = v2;
 }
 __device__ __forceinline__ void cache_fill_store(RowCache* c, int r, int lane, int64_t v, uint32_t v2) {
   if (lane < 31) c->q[lane] = v;
-  // apods, npods, flags, zone, avail[0..1] are consecutive 32-bit fields of the entry
-  if (lane < 4 + KSB_MAX_RES) reinterpret_cast<uint32_t*>(&c->apods)[lane] = v2;
+  // apods, npods, flags, zone, avail[0..1], sscore are consecutive 32-bit fields of the entry
+  if (lane < 5 + KSB_MAX_RES) reinterpret_cast<uint32_t*>(&c->apods)[lane] = v2;
   if (lane == 31) c->row = r;
   if (lane >= 24 && lane < 24 + KSB_MAX_EXT) c->mid[lane - 24] = 0;
   if (lane < 2) c->rcp[lane] = fast_rcp((double)v);

@@ -76,9 +76,32 @@ ksb_config config_from(const json::Value& opt) {
 
 std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double load_ms);
 
+// Policy-enabled plugins from the options: {"weights": {"MostRequestedPriority": w, "ResourceLimitsPriority": w},
+// "policy": {"nodeLabelPriorities": [{"label", "presence", "weight"}], "labelsPresence": {"labels": [...], "presence": b}}}
+void apply_policy(EngineHandle& h, const json::Value& opt) {
+  if (const json::Value* w = opt.find("weights"); w && !w->is_null()) {
+    if (w->get_int("MostRequestedPriority", 0) != 0)
+      h.check(ksb_policy_set(h.get(), KSB_POLICY_MOST_REQUESTED, nullptr, 0, 0, (int32_t)w->get_int("MostRequestedPriority", 0)), "policy");
+    if (w->get_int("ResourceLimitsPriority", 0) != 0)
+      h.check(ksb_policy_set(h.get(), KSB_POLICY_RESOURCE_LIMITS, nullptr, 0, 0, (int32_t)w->get_int("ResourceLimitsPriority", 0)), "policy");
+  }
+  if (const json::Value* pv = opt.find("policy"); pv && !pv->is_null()) {
+    if (pv->has("nodeLabelPriorities"))
+      for (auto& a : pv->get_arr("nodeLabelPriorities")) {
+        const std::string label = a.get_str("label");
+        h.check(ksb_policy_set(h.get(), KSB_POLICY_NODE_LABEL_PRIORITY, label.data(), label.size(), a.get_bool("presence", true) ? 1 : 0,
+                               (int32_t)a.get_int("weight", 1)), "policy");
+      }
+    if (const json::Value* lp = pv->find("labelsPresence"); lp && !lp->is_null())
+      for (auto& l : lp->get_arr("labels"))
+        h.check(ksb_policy_set(h.get(), KSB_POLICY_LABEL_PRESENCE, l.s.data(), l.s.size(), lp->get_bool("presence", true) ? 1 : 0, 0), "policy");
+  }
+}
+
 std::string run(Session& s, const json::Value& opt) {
   ksb_config cfg = config_from(opt);
   EngineHandle h(cfg);
+  apply_policy(h, opt);
   ksb_set_last_node_index(h.get(), (uint64_t)opt.get_int("lastNodeIndex", 0));
   auto tl0 = std::chrono::steady_clock::now();
   load_cluster(h, s);
@@ -465,6 +488,7 @@ void* ksbh_engine_open(void* session, const char* options_json, char** err) {
     oe->s = (Session*)session;
     ksb_config cfg = config_from(opt);
     oe->h = std::make_unique<EngineHandle>(cfg);
+    apply_policy(*oe->h, opt);
     auto t0 = std::chrono::steady_clock::now();
     load_cluster(*oe->h, *oe->s);
     oe->load_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();

@@ -56,6 +56,23 @@ static void apply_options(Oracle& o, const json::Value& v) {
     o.weights.taint_toleration = w->get_int("TaintTolerationPriority", 1);
     o.weights.inter_pod_affinity = w->get_int("InterPodAffinityPriority", 1);
     o.weights.prefer_avoid = w->get_int("NodePreferAvoidPodsPriority", 10000);
+    o.weights.most_requested = w->get_int("MostRequestedPriority", 0);
+    o.weights.resource_limits = w->get_int("ResourceLimitsPriority", 0);
+  }
+  // {"policy": {"nodeLabelPriorities": [{"label", "presence", "weight"}], "labelsPresence": {"labels": [...], "presence": bool}}}
+  if (const json::Value* pv = v.find("policy"); pv && !pv->is_null()) {
+    if (const json::Value* nl = pv->find("nodeLabelPriorities"); nl && !nl->is_null())
+      for (auto& a : pv->get_arr("nodeLabelPriorities")) {
+        NodeLabelPriorityArg x;
+        x.label = a.get_str("label");
+        x.presence = a.get_bool("presence", true);
+        x.weight = a.get_int("weight", 1);
+        o.policy.node_label.push_back(x);
+      }
+    if (const json::Value* lp = pv->find("labelsPresence"); lp && !lp->is_null()) {
+      for (auto& l : lp->get_arr("labels")) o.policy.presence_labels.push_back(l.s);
+      o.policy.presence = lp->get_bool("presence", true);
+    }
   }
 }
 
@@ -117,6 +134,14 @@ static std::string run_priority(const json::Value& req) {
         if (!Oracle::node_affinity_map(pod, ni, &s, &err)) return "{\"error\":\"" + err + "\"}";
       } else if (name == "TaintTolerationPriority") s = Oracle::taint_toleration_map(pm, ni);
       else if (name == "NodePreferAvoidPodsPriority") s = Oracle::prefer_avoid_map(pod, ni);
+      else if (name == "MostRequestedPriority") s = Oracle::most_requested_map(pm, ni);
+      else if (name == "ResourceLimitsPriority") s = Oracle::resource_limits_map(pod, ni);
+      else if (name == "NodeLabelPriority") {
+        NodeLabelPriorityArg a;
+        a.label = req.find("args")->get_str("label");
+        a.presence = req.find("args")->get_bool("presence", true);
+        s = Oracle::node_label_map(a, ni);
+      }
       else return "{\"error\":\"unknown priority\"}";
       list.push_back({n->name, s});
     }
@@ -172,6 +197,8 @@ static std::string run_predicate(const json::Value& req) {
     if (ni.diskPressure == "True") fails.push_back("NodeUnderDiskPressure");
   } else if (name == "CheckNodeCondition") {
     Oracle::check_node_condition(ni, &fails);
+  } else if (name == "CheckNodeLabelPresence") {
+    Oracle::check_node_label_presence(o.policy, ni, &fails);
   } else if (name == "MatchInterPodAffinity" || name == "all") {
     std::vector<PodPtr> allPods = o.all_pods();
     std::vector<Oracle::TermProbe> aff, anti;

@@ -301,6 +301,21 @@ struct ScheduleResult {
 struct PriorityWeights {
   int64_t least_requested = 1, balanced = 1, selector_spread = 1, node_affinity = 1, taint_toleration = 1,
           inter_pod_affinity = 1, prefer_avoid = 10000;
+  // not in the DefaultProvider set (registered by name, enabled through a Policy: defaults.go:93-116, api/types.go:36-125)
+  int64_t most_requested = 0, resource_limits = 0;
+};
+
+// Policy-configured plugins that take arguments (api/types.go:64-125): NodeLabelPriority instances
+// (priorities/node_label.go:29-60) and the CheckNodeLabelPresence predicate (predicates.go:778-826).
+struct NodeLabelPriorityArg {
+  std::string label;
+  bool presence = true;
+  int64_t weight = 1;
+};
+struct Policy {
+  std::vector<NodeLabelPriorityArg> node_label;
+  std::vector<std::string> presence_labels;
+  bool presence = true;
 };
 
 struct Oracle {
@@ -311,6 +326,7 @@ struct Oracle {
   int workers = 1;  // 16 mirrors Parallelize(16, ...)
   int hardPodAffinityWeight = 1;
   PriorityWeights weights;
+  Policy policy;
 
   // ---------------- predicates
 
@@ -696,6 +712,54 @@ struct Oracle {
     int64_t ms = unused_score(mem, ni.allocatable.Memory);
     return (cs + ms) / 2;
   }
+  // most_requested.go:32-88: calculateUsedScore per resource, integer average
+  static int64_t used_score(int64_t requested, int64_t capacity) {
+    if (capacity == 0) return 0;
+    if (requested > capacity) return 0;
+    return (requested * kMaxPriority) / capacity;
+  }
+  static int64_t most_requested_map(const PriorityMeta& pm, const NodeInfo& ni) {
+    int64_t cpu = pm.nonZeroCPU + ni.nonzero.MilliCPU;
+    int64_t mem = pm.nonZeroMem + ni.nonzero.Memory;
+    return (used_score(cpu, ni.allocatable.MilliCPU) + used_score(mem, ni.allocatable.Memory)) / 2;
+  }
+  // node_label.go:46-60
+  static int64_t node_label_map(const NodeLabelPriorityArg& a, const NodeInfo& ni) {
+    const bool exists = ni.node->has_labels && ni.node->labels.count(a.label) != 0;
+    return (exists && a.presence) || (!exists && !a.presence) ? kMaxPriority : 0;
+  }
+  // resource_limits.go:34-126: 1 when the pod's cpu or memory limit is set and fits the node's allocatable
+  static void pod_limits(const Pod& pod, int64_t* cpu, int64_t* mem) {
+    *cpu = 0;
+    *mem = 0;
+    for (auto& c : pod.containers)
+      for (auto& kv : c.limits) {
+        if (kv.first == ksb::kResCPU) *cpu += kv.second;
+        else if (kv.first == ksb::kResMemory) *mem += kv.second;
+      }
+    for (auto& c : pod.init_containers)
+      for (auto& kv : c.limits) {
+        if (kv.first == ksb::kResCPU) *cpu = std::max(*cpu, kv.second);
+        else if (kv.first == ksb::kResMemory) *mem = std::max(*mem, kv.second);
+      }
+  }
+  static int64_t resource_limits_map(const Pod& pod, const NodeInfo& ni) {
+    int64_t lc, lm;
+    pod_limits(pod, &lc, &lm);
+    auto one = [](int64_t limit, int64_t alloc) { return limit != 0 && alloc != 0 && limit <= alloc; };
+    return one(lc, ni.allocatable.MilliCPU) || one(lm, ni.allocatable.Memory) ? 1 : 0;
+  }
+  // predicates.go:800-826
+  static void check_node_label_presence(const Policy& pol, const NodeInfo& ni, std::vector<std::string>* fails) {
+    for (auto& l : pol.presence_labels) {
+      const bool exists = ni.node->has_labels && ni.node->labels.count(l) != 0;
+      if ((exists && !pol.presence) || (!exists && pol.presence)) {
+        fails->push_back("CheckNodeLabelPresence");
+        return;
+      }
+    }
+  }
+
   static int64_t balanced_map(const PriorityMeta& pm, const NodeInfo& ni) {  // :51-93
     int64_t cpu = pm.nonZeroCPU + ni.nonzero.MilliCPU;
     int64_t mem = pm.nonZeroMem + ni.nonzero.Memory;
@@ -924,6 +988,7 @@ struct Oracle {
     if (meta.bestEffort && ni.memoryPressure == "True") fails->push_back("NodeUnderMemoryPressure");
     if (ni.diskPressure == "True") fails->push_back("NodeUnderDiskPressure");
     check_node_condition(ni, fails);
+    if (!policy.presence_labels.empty()) check_node_label_presence(policy, ni, fails);
     if (ix && ix->usable) inter_pod_affinity_matches_indexed(pod, ni, *ix, affTerms, antiTerms, fails);
     else if (!inter_pod_affinity_matches(pod, meta, ni, allPods, affTerms, antiTerms, fails, err)) return false;
     return true;
@@ -1097,6 +1162,11 @@ struct Oracle {
                           lr[i].score * weights.least_requested + bra[i].score * weights.balanced +
                           av[i].score * weights.prefer_avoid + na[i].score * weights.node_affinity +
                           tt[i].score * weights.taint_toleration;
+      // Policy-enabled priorities (Map only, no Reduce)
+      const NodeInfo& ni = cachedNodeInfoMap.at(filtered[i]->name);
+      if (weights.most_requested) (*total)[i].score += most_requested_map(pm, ni) * weights.most_requested;
+      if (weights.resource_limits) (*total)[i].score += resource_limits_map(pod, ni) * weights.resource_limits;
+      for (auto& a : policy.node_label) (*total)[i].score += node_label_map(a, ni) * a.weight;
     }
     return true;
   }

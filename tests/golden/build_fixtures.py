@@ -328,6 +328,11 @@ def main():
         BUILDERS.extend(golden_extra.builders(globals()))
     except ImportError:
         pass
+    try:
+        import golden_policy  # noqa: F401  (fourth batch: Policy-enabled priorities and predicate)
+        BUILDERS.extend(golden_policy.builders(globals()))
+    except ImportError:
+        pass
     for b in BUILDERS:
         b()
     out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "reference_vectors.json")

@@ -1,0 +1,101 @@
+"""Fourth batch of transcriptions of the reference's own tests (see build_fixtures.py): the priorities and the
+predicate that are registered by name but only enabled through a Policy (algorithmprovider/defaults/defaults.go:93-116,
+api/types.go:36-125). Each builder cites its source."""
+
+
+def builders(g):
+    node, pod, ctr = g["node"], g["pod"], g["ctr"]
+    CASES = g["CASES"]
+
+    def lift(*keys):  # arguments of the plugin itself belong to the case, not to the cluster
+        for k in keys:
+            if k in CASES[-1]["cluster"]:
+                CASES[-1][k] = CASES[-1]["cluster"].pop(k)
+
+    def priority(*a, **kw):
+        g["priority"](*a, **kw)
+        lift("args", "policy")
+
+    def predicate(*a, **kw):
+        g["predicate"](*a, **kw)
+        lift("args", "policy")
+
+    # ----------------------------------------------------------------- MostRequestedPriority
+    # algorithm/priorities/most_requested_test.go:30-222
+    def build_most_requested():
+        src = "algorithm/priorities/most_requested_test.go:107-210"
+        l1, l2 = {"foo": "bar", "baz": "blah"}, {"bar": "foo", "baz": "blah"}
+        cpu_only = [ctr(1000, 0), ctr(2000, 0)]
+        cpu_mem = [ctr(1000, 2000), ctr(2000, 3000)]
+        big = [ctr(2000, 4000), ctr(3000, 5000)]
+        P = "MostRequestedPriority"
+        priority(P, src, "nothing scheduled, nothing requested", pod(containers=[]),
+                 [node("machine1", 4000, 10000), node("machine2", 4000, 10000)], [], [("machine1", 0), ("machine2", 0)])
+        priority(P, src, "nothing scheduled, resources requested, differently sized machines", pod(containers=cpu_mem),
+                 [node("machine1", 4000, 10000), node("machine2", 6000, 10000)], [], [("machine1", 6), ("machine2", 5)])
+        priority(P, src, "no resources requested, pods scheduled with resources", pod(containers=[]),
+                 [node("machine1", 10000, 20000), node("machine2", 10000, 20000)],
+                 [pod("machine1", labels=l2, containers=cpu_only), pod("machine1", labels=l1, containers=cpu_only),
+                  pod("machine2", labels=l1, containers=cpu_only), pod("machine2", labels=l1, containers=cpu_mem)],
+                 [("machine1", 3), ("machine2", 4)])
+        priority(P, src, "resources requested, pods scheduled with resources", pod(containers=cpu_mem),
+                 [node("machine1", 10000, 20000), node("machine2", 10000, 20000)],
+                 [pod("machine1", containers=cpu_only), pod("machine2", containers=cpu_mem)],
+                 [("machine1", 4), ("machine2", 5)])
+        priority(P, src, "resources requested with more than the node, pods scheduled with resources", pod(containers=big),
+                 [node("machine1", 4000, 10000), node("machine2", 10000, 8000)], [], [("machine1", 4), ("machine2", 2)])
+
+    # ----------------------------------------------------------------- NodeLabelPriority
+    # algorithm/priorities/node_label_test.go:30-125 (the pod is nil there: an empty pod here)
+    def build_node_label():
+        src = "algorithm/priorities/node_label_test.go:42-108"
+        nodes = lambda: [node("machine1", labels={"foo": "bar"}), node("machine2", labels={"bar": "foo"}),
+                         node("machine3", labels={"bar": "baz"})]
+        for label, presence, scores, test in [
+                ("baz", True, (0, 0, 0), "no match found, presence true"),
+                ("baz", False, (10, 10, 10), "no match found, presence false"),
+                ("foo", True, (10, 0, 0), "one match found, presence true"),
+                ("foo", False, (0, 10, 10), "one match found, presence false"),
+                ("bar", True, (0, 10, 10), "two matches found, presence true"),
+                ("bar", False, (10, 0, 0), "two matches found, presence false")]:
+            priority("NodeLabelPriority", src, test, pod(containers=[]), nodes(), [],
+                     list(zip(("machine1", "machine2", "machine3"), scores)), args={"label": label, "presence": presence})
+
+    # ----------------------------------------------------------------- ResourceLimitsPriority
+    # algorithm/priorities/resource_limits_test.go:30-151
+    def build_resource_limits():
+        src = "algorithm/priorities/resource_limits_test.go:104-137"
+        lim = lambda c, m: ctr(limits={"cpu": c, "memory": m})
+        cpu_only = [lim(1000, 0), lim(2000, 0)]
+        mem_only = [lim(0, 2000), lim(0, 3000)]
+        cpu_mem = [lim(1000, 2000), lim(2000, 3000)]
+        P = "ResourceLimitsPriority"
+        priority(P, src, "pod does not specify its resource limits", pod(containers=[]),
+                 [node("machine1", 4000, 10000), node("machine2", 4000, 0), node("machine3", 0, 10000), node("machine4", 0, 0)],
+                 [], [("machine1", 0), ("machine2", 0), ("machine3", 0), ("machine4", 0)])
+        priority(P, src, "pod only specifies  cpu limits", pod(containers=cpu_only),
+                 [node("machine1", 3000, 10000), node("machine2", 2000, 10000)], [], [("machine1", 1), ("machine2", 0)])
+        priority(P, src, "pod only specifies  mem limits", pod(containers=mem_only),
+                 [node("machine1", 4000, 4000), node("machine2", 5000, 10000)], [], [("machine1", 0), ("machine2", 1)])
+        priority(P, src, "pod specifies both cpu and  mem limits", pod(containers=cpu_mem),
+                 [node("machine1", 4000, 4000), node("machine2", 5000, 10000)], [], [("machine1", 1), ("machine2", 1)])
+        priority(P, src, "node does not advertise its allocatables", pod(containers=cpu_mem), [node("machine1", 0, 0)], [],
+                 [("machine1", 0)])
+
+    # ----------------------------------------------------------------- CheckNodeLabelPresence
+    # algorithm/predicates/predicates_test.go:1387-1452
+    def build_label_presence():
+        src = "algorithm/predicates/predicates_test.go:1396-1431"
+        for labels, presence, fits, test in [
+                (["baz"], True, False, "label does not match, presence true"),
+                (["baz"], False, True, "label does not match, presence false"),
+                (["foo", "baz"], True, False, "one label matches, presence true"),
+                (["foo", "baz"], False, False, "one label matches, presence false"),
+                (["foo", "bar"], True, True, "all labels match, presence true"),
+                (["foo", "bar"], False, False, "all labels match, presence false")]:
+            predicate("CheckNodeLabelPresence", src, test, pod(containers=[]),
+                      node("machine1", labels={"foo": "bar", "bar": "foo"}), fits=fits,
+                      reasons=None if fits else ["CheckNodeLabelPresence"],
+                      policy={"labelsPresence": {"labels": labels, "presence": presence}})
+
+    return [build_most_requested, build_node_label, build_resource_limits, build_label_presence]

@@ -207,9 +207,10 @@ def test_golden_predicates_on_gpu():
         if c["expect"].get("error"):
             continue
         cl = _as_stream(c)
-        want = oracle_lib.call({"op": "stream", "cluster": cl})
+        policy = c.get("policy")  # CheckNodeLabelPresence takes its labels from a Policy
+        want = oracle_lib.call({"op": "stream", "cluster": cl, "policy": policy})
         sess = lib.Session(cluster=cl)
-        got = sess.run()
+        got = sess.run(policy=policy) if policy else sess.run()
         sess.close()
         g, w = got["results"][0], want["results"][0]
         assert (g["status"], g["host"], g["devices"]) == (w["status"], w["host"], w["devices"]), (c["source"], c["test"], g, w)
@@ -225,7 +226,8 @@ def test_golden_priorities_on_gpu():
     (priorities/test_util.go:45-61). Cases in which a predicate removes a node are counted, not silently skipped:
     the golden lists are computed without predicates, so only the nodes that stayed are compared there."""
     names = {"LeastRequestedPriority", "BalancedResourceAllocation", "SelectorSpreadPriority", "NodeAffinityPriority",
-             "TaintTolerationPriority", "InterPodAffinityPriority", "NodePreferAvoidPodsPriority"}
+             "TaintTolerationPriority", "InterPodAffinityPriority", "NodePreferAvoidPodsPriority", "MostRequestedPriority",
+             "ResourceLimitsPriority"}
     with open(os.path.join(HERE, "golden", "reference_vectors.json")) as f:
         cases = [c for c in json.load(f)["cases"] if c["op"] == "priority"]
     whole = partial = skipped = 0
@@ -237,8 +239,12 @@ def test_golden_priorities_on_gpu():
         scores = dict((h, s) for h, s in c["expect"]["scores"])
         best = max(scores.values())
         winners = {h for h, s in scores.items() if s == best}
+        policy = None
+        if c["name"] == "NodeLabelPriority":  # an instance with arguments (node_label.go:29-44), not a weight by name
+            policy = {"nodeLabelPriorities": [dict(c["args"], weight=1)]}
         sess = lib.Session(cluster=cl)
-        out = sess.run(batch=0, scores=True, weights=weights, hardPodAffinityWeight=c.get("hardPodAffinityWeight", 1))
+        out = sess.run(batch=0, scores=True, weights=weights, hardPodAffinityWeight=c.get("hardPodAffinityWeight", 1),
+                       **({"policy": policy} if policy else {}))
         sess.close()
         r = out["results"][0]
         if r["status"] != 0 or r["filtered"] < 2:
@@ -252,12 +258,13 @@ def test_golden_priorities_on_gpu():
         else:
             # a predicate removed nodes; priorities whose Reduce normalises over the filtered list may legitimately
             # differ from the golden list then, the Map-only ones may not
-            if c["name"] in ("LeastRequestedPriority", "BalancedResourceAllocation", "NodePreferAvoidPodsPriority"):
+            if c["name"] in ("LeastRequestedPriority", "BalancedResourceAllocation", "NodePreferAvoidPodsPriority",
+                             "MostRequestedPriority", "ResourceLimitsPriority", "NodeLabelPriority"):
                 assert all(got[h] == scores[h] for h in got), (c["source"], c["test"], got, scores)
             partial += 1
     assert whole + partial + skipped == len(cases)
     print("priority vectors: %d whole lists, %d partial, %d not prioritized" % (whole, partial, skipped))
-    assert whole >= 70, (whole, partial, skipped)
+    assert whole >= 85, (whole, partial, skipped)
 
 
 def _many_sets_cluster(n_nodes=300, n_pods=1200, n_hard=150, n_soft=140, n_avoid=130):
@@ -289,3 +296,22 @@ def test_more_than_64_taints_and_avoid_references():
     cluster = _many_sets_cluster()
     compare(cluster, "many taints")
     compare(_many_sets_cluster(120, 300), "many taints single", gpu_opts={"batch": 0})
+
+
+def test_policy_plugins_match_oracle():
+    """A Policy that enables MostRequestedPriority, ResourceLimitsPriority, two NodeLabelPriority instances and the
+    CheckNodeLabelPresence predicate next to the DefaultProvider set: whole streams (batch and one pod per call)
+    against the oracle."""
+    cluster = workloads.generate(3, 300, 1500)
+    for i, p in enumerate(cluster["pods"]):  # limits on some pods, so that ResourceLimitsPriority has something to score
+        if i % 3 == 0:
+            p["containers"][0]["limits"] = {"cpu": 500 * (1 + i % 80), "memory": (1 + i % 5) << 30}
+    opts = {"weights": {"LeastRequestedPriority": 1, "BalancedResourceAllocation": 1, "SelectorSpreadPriority": 1,
+                        "NodeAffinityPriority": 1, "TaintTolerationPriority": 1, "InterPodAffinityPriority": 1,
+                        "NodePreferAvoidPodsPriority": 10000, "MostRequestedPriority": 2, "ResourceLimitsPriority": 3},
+            "policy": {"nodeLabelPriorities": [{"label": "lk03", "presence": True, "weight": 2},
+                                               {"label": "lk07", "presence": False, "weight": 1}],
+                       "labelsPresence": {"labels": ["lk11"], "presence": False}}}
+    compare(cluster, "policy", gpu_opts=opts, oracle_opts=opts)
+    small = workloads.generate(3, 120, 300)
+    compare(small, "policy single", gpu_opts=dict(opts, batch=0), oracle_opts=opts)
