@@ -69,6 +69,8 @@ struct KsbNodeTable {
   int32_t row_base;  // global row of local row 0
   int32_t n_total;   // rows over all shards
   int32_t w_mr, w_rl; // MostRequestedPriority / ResourceLimitsPriority weights (0: not enabled by the Policy)
+  int32_t has_static; // a Policy configured NodeLabelPriority instances: static_score holds their per-node sum
+  int32_t has_presence; // ... CheckNodeLabelPresence labels: NF_LABEL_PRESENCE marks the nodes that fail it
   int32_t W;         // label words
   int32_t tw;        // 64-bit words of each taint / preferAvoid set (columns taint_hard, taint_soft, avoid hold tw words each,
                      // word w at + w * n_pad; a pod's masks for the words above 0 trail its pool block)

@@ -579,6 +579,8 @@ void Engine::setup_table_pointers() {
   T.w_lr = cfg.w_least_requested;
   T.w_mr = w_most_requested;
   T.w_rl = w_resource_limits;
+  T.has_static = pol_node_label.empty() ? 0 : 1;
+  T.has_presence = pol_presence_labels.empty() ? 0 : 1;
   T.w_bra = cfg.w_balanced;
   T.w_ss = cfg.w_selector_spread;
   T.w_na = cfg.w_node_affinity;

@@ -322,7 +322,6 @@ struct RowCommon {
   uint32_t nflags, zone;
   double rcp_cpu, rcp_mem;  // fast_rcp of the allocatable cpu / memory (lr_bra)
   uint32_t over;            // bit 0: allocatable alpha-gpu < requested on the row, bit 1: the same for ephemeral storage
-  int32_t sscore;           // the node's NodeLabelPriority sum (0 unless a Policy configured some)
 };
 
 template <bool CG>
@@ -338,7 +337,6 @@ __device__ __forceinline__ void load_row_common(const KsbNodeTable& T, int r, Ro
   rc.nmem = ldx<CG>(T.nz_mem + r);
   rc.nflags = T.flags[r];
   rc.zone = T.zone[r];
-  rc.sscore = T.static_score[r];
   rc.hard = T.taint_hard[r];
   rc.soft = T.taint_soft[r];
   rc.avoid = T.avoid[r];
@@ -398,26 +396,33 @@ __device__ __forceinline__ bool eval_expr4(const uint64_t (&lab)[kLabFast], cons
 // The priorities a Policy can enable next to the DefaultProvider set (Map only, no Reduce), as one addend to the
 // bind-dependent part of the score: MostRequestedPriority (most_requested.go:32-88) over the same non-zero totals as
 // LeastRequested, ResourceLimitsPriority (resource_limits.go:34-94) and the node's NodeLabelPriority sum (node_label.go).
-__device__ __forceinline__ int32_t policy_score(const KsbNodeTable& T, const KsbPodHeader* h, int64_t cpu, int64_t mem, int64_t acpu,
-                                                int64_t amem, int32_t static_score) {
-  int32_t s = static_score;
-  if (T.w_mr) {
+// (a real call, taken only when a Policy enabled one of the two: inlined, its 64-bit divisions cost every evaluation
+// registers and spills, 3 % of the headline launch and 15 % of a one-pod call)
+__device__ __noinline__ int32_t policy_score_enabled(int32_t w_mr, int32_t w_rl, int64_t lim_cpu, int64_t lim_mem, int64_t cpu,
+                                                     int64_t mem, int64_t acpu, int64_t amem) {
+  int32_t s = 0;
+  if (w_mr) {
     const int64_t cs = (acpu == 0 || cpu > acpu) ? 0 : (cpu * 10) / acpu;
     const int64_t ms = (amem == 0 || mem > amem) ? 0 : (mem * 10) / amem;
-    s += T.w_mr * (int32_t)((cs + ms) / 2);
+    s += w_mr * (int32_t)((cs + ms) / 2);
   }
-  if (T.w_rl) {
-    const bool c1 = h->lim_cpu != 0 && acpu != 0 && h->lim_cpu <= acpu;
-    const bool m1 = h->lim_mem != 0 && amem != 0 && h->lim_mem <= amem;
-    s += T.w_rl * ((c1 || m1) ? 1 : 0);
+  if (w_rl) {
+    const bool c1 = lim_cpu != 0 && acpu != 0 && lim_cpu <= acpu;
+    const bool m1 = lim_mem != 0 && amem != 0 && lim_mem <= amem;
+    s += w_rl * ((c1 || m1) ? 1 : 0);
   }
   return s;
+}
+__device__ __forceinline__ int32_t policy_score(const KsbNodeTable& T, const KsbPodHeader* h, int64_t cpu, int64_t mem, int64_t acpu,
+                                                int64_t amem, int32_t static_score) {
+  if ((T.w_mr | T.w_rl) == 0) return static_score;
+  return static_score + policy_score_enabled(T.w_mr, T.w_rl, h->lim_cpu, h->lim_mem, cpu, mem, acpu, amem);
 }
 
 // Everything the reference computes for one (pod, node): podFitsOnNode's predicates
 // (core/generic_scheduler.go:402-501) and the Map functions of PrioritizeNodes (:557-574).
 // CG = true reads the columns the kernel mutates straight from L2 (phase 3, rows just rewritten).
-template <bool CG>
+template <bool CG, bool POL>
 __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const RowCommon& rc, const PodView& pv, EvalOut& o,
                                           uint32_t* picks) {
   const KsbPodHeader* h = pv.h;
@@ -508,7 +513,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   if (nflags & NF_OUT_OF_DISK) reasons |= 1u << RB_OUT_OF_DISK;
   if (nflags & NF_NET_UNAVAILABLE) reasons |= 1u << RB_NET_UNAVAILABLE;
   if (nflags & NF_UNSCHEDULABLE) reasons |= 1u << RB_UNSCHEDULABLE;
-  if (nflags & NF_LABEL_PRESENCE) reasons |= 1u << RB_LABEL_PRESENCE;  // CheckNodeLabelPresence (predicates.go:800-826), per node on the host
+  if (POL && (nflags & NF_LABEL_PRESENCE)) reasons |= 1u << RB_LABEL_PRESENCE;  // CheckNodeLabelPresence (predicates.go:800-826), per node on the host
   // --- MatchInterPodAffinity (predicates.go:1047-1346) over per-(term class, topology domain) counts.
   //     Inside a group no pod reads a table an earlier pod of the group writes, so plain loads do.
   for (int i = 0; i < h->n_checks; ++i) {
@@ -553,7 +558,10 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   int32_t lr, bra;  // least_requested.go:63-91, balanced_resource_allocation.go:51-100
   lr_bra(cpu, mem, acpu, amem, rc.rcp_cpu, rc.rcp_mem, &lr, &bra);
   const int32_t av = avoid_hit ? 0 : 10;  // node_prefer_avoid_pods.go:29-59
-  o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av + policy_score(T, h, cpu, mem, acpu, amem, rc.sscore);
+  // (the node's NodeLabelPriority sum is read here, and only when a Policy configured an instance: carried with the
+  //  row's common columns it cost every evaluation a register)
+  o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
+  if constexpr (POL) o.base += policy_score(T, h, cpu, mem, acpu, amem, T.has_static ? T.static_score[r] : 0);
   o.na = na;
   o.tt = tt;
   o.sc = h->spread_col >= 0 ? ldx<CG>(T.spread + (size_t)h->spread_col * np + r) : 0u;  // selector_spreading.go:64-113
@@ -970,6 +978,7 @@ __device__ __forceinline__ uint32_t select_devices_cached(const KsbNodeTable& T,
 
 // The part of eval_node that can change while a group is committed, computed from the row cache.
 // Must stay in step with eval_node (the group-size tests compare the two paths bit for bit).
+template <bool POL>
 __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, const PodView& pv,
                                             uint32_t static_reasons, uint32_t* reasons_out, int32_t* base_out,
                                             uint32_t* picks, bool want_score, bool keep = true) {
@@ -1014,7 +1023,8 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   if (T.tw > 1)  // the words above 0 of the preferAvoid set: static columns, read in place
     for (int w = 0; w < T.tw - 1; ++w) avoid_hit |= T.avoid[(size_t)(w + 1) * T.n_pad + c.row] & pv.tw_ext[2 * (T.tw - 1) + w];
   const int32_t av = avoid_hit ? 0 : 10;
-  *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av + policy_score(T, h, cpu, mem, acpu, amem, c.sscore);
+  *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
+  if constexpr (POL) *base_out += policy_score(T, h, cpu, mem, acpu, amem, c.sscore);
 }
 
 // One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads). In two steps, so
@@ -1238,7 +1248,9 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
 
 // PIPE: the pipelined schedule (see `pipe` below) as a separate instantiation, so that the plain one carries none
 // of its state in registers.
-template <bool PIPE, bool MULTI>
+// POL: a Policy enabled plugins outside the DefaultProvider set (ksb_policy_set); the default instantiations carry none
+// of their code.
+template <bool PIPE, bool MULTI, bool POL>
 __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const Smem S = carve(smem_raw, A.zone_stride);
@@ -1462,7 +1474,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           if (live && !(h->flags & PF_SCHED_ERROR)) {
             const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
             EvalOut o;
-            eval_node<false>(T, r, rc, pv, o, nullptr);
+            eval_node<false, POL>(T, r, rc, pv, o, nullptr);
             int4 raw;
             if (o.reasons == 0) {
               fit = 1;
@@ -1900,7 +1912,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           r0_out[g] = r0v;
           uint32_t new_reasons;
           int32_t base;
-          eval_cached(P.table, *c, pv, in.reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
+          eval_cached<POL>(P.table, *c, pv, in.reasons0 & ~kDynMask, &new_reasons, &base, nullptr, true, false);
           const bool was_fit = in.base0 != INT32_MIN;
           const int32_t gm = s_gmax0[g];
           const int32_t cold = was_fit ? in.score0 : INT32_MIN;
@@ -2201,7 +2213,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                     if (prio) cold = __ldcv(P.score + at);
                   }
                   int32_t base;
-                  eval_cached(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
+                  eval_cached<POL>(P.table, c, pv, old_reasons & ~kDynMask, &new_reasons, &base, nullptr, prio);
                   const bool was_fit = base0 != INT32_MIN;
                   flip = was_fit && new_reasons != 0;  // a fit row turned unfit: the Reduce inputs may have moved
                   if (prio && was_fit && new_reasons == 0)
@@ -2380,7 +2392,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
                         EvalOut o;
                         RowCommon rc;
                         load_row_common<true>(P.table, chosen, rc);
-                        eval_node<true>(P.table, chosen, rc, pv, o, picks);
+                        eval_node<true, POL>(P.table, chosen, rc, pv, o, picks);
                       }
 #pragma unroll
                       for (int i = 0; i < KSB_MAX_EXT; ++i) picks[i] = __shfl_sync(0xffffffffu, picks[i], 0);
@@ -2910,11 +2922,19 @@ extern "C" size_t ksb_batch_smem_bytes(int zone_stride) {
   return smem_layout(o, zone_stride);
 }
 
+static const void* batch_kernel(bool pipe, bool multi, bool pol) {
+  static const void* const fns[8] = {
+      (const void*)ksb_schedule_batch_kernel<false, false, false>, (const void*)ksb_schedule_batch_kernel<true, false, false>,
+      (const void*)ksb_schedule_batch_kernel<false, true, false>,  (const void*)ksb_schedule_batch_kernel<true, true, false>,
+      (const void*)ksb_schedule_batch_kernel<false, false, true>,  (const void*)ksb_schedule_batch_kernel<true, false, true>,
+      (const void*)ksb_schedule_batch_kernel<false, true, true>,   (const void*)ksb_schedule_batch_kernel<true, true, true>};
+  return fns[(pipe ? 1 : 0) + (multi ? 2 : 0) + (pol ? 4 : 0)];
+}
+
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
   void* params[] = {(void*)args};
-  const void* fn = args->n_ranks > 1
-                       ? (args->pipeline ? (const void*)ksb_schedule_batch_kernel<true, true> : (const void*)ksb_schedule_batch_kernel<false, true>)
-                       : (args->pipeline ? (const void*)ksb_schedule_batch_kernel<true, false> : (const void*)ksb_schedule_batch_kernel<false, false>);
+  const bool pol = args->table.w_mr != 0 || args->table.w_rl != 0 || args->table.has_static != 0 || args->table.has_presence != 0;
+  const void* fn = batch_kernel(args->pipeline != 0, args->n_ranks > 1, pol);
   cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,
                                               smem_bytes, stream);
   return (int)e;
@@ -2922,9 +2942,10 @@ extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_
 
 extern "C" int ksb_batch_kernel_limits(int device, size_t smem_bytes, int* max_grid, int* threads) {
   int per_sm = 0, sms = 0;
-  // the three instantiations (plain, pipelined, sharded) share one grid size: the smallest occupancy of the three
-  const void* fns[4] = {(const void*)ksb_schedule_batch_kernel<false, false>, (const void*)ksb_schedule_batch_kernel<true, false>,
-                        (const void*)ksb_schedule_batch_kernel<false, true>, (const void*)ksb_schedule_batch_kernel<true, true>};
+  // every instantiation (plain / pipelined, one GPU / sharded, with / without Policy plugins) shares one grid size: the
+  // smallest occupancy of them all
+  const void* fns[8];
+  for (int k = 0; k < 8; ++k) fns[k] = batch_kernel((k & 1) != 0, (k & 2) != 0, (k & 4) != 0);
   cudaError_t e = cudaSuccess;
   per_sm = 1 << 30;
   for (const void* fn : fns) {
