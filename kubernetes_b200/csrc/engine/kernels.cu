@@ -496,7 +496,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   if (rc.hard & h->hard_untol) reasons |= 1u << RB_TAINTS;
   int32_t tt = __popcll(rc.soft & h->soft_untol);
   uint64_t avoid_hit = rc.avoid & h->avoid_mask;
-  if (T.tw > 1) {  // more than 64 distinct taints / references: the words above 0 (static columns)
+  if (POL && T.tw > 1) {  // more than 64 distinct taints / references: the words above 0 (static columns)
     const int x = T.tw - 1;
     uint64_t hard_hit = 0;
     for (int w = 0; w < x; ++w) {
@@ -1020,7 +1020,7 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
   int32_t lr, bra;
   lr_bra(cpu, mem, acpu, amem, c.rcp[0], c.rcp[1], &lr, &bra);
   uint64_t avoid_hit = (uint64_t)c.q[30] & h->avoid_mask;
-  if (T.tw > 1)  // the words above 0 of the preferAvoid set: static columns, read in place
+  if (POL && T.tw > 1)  // the words above 0 of the preferAvoid set: static columns, read in place
     for (int w = 0; w < T.tw - 1; ++w) avoid_hit |= T.avoid[(size_t)(w + 1) * T.n_pad + c.row] & pv.tw_ext[2 * (T.tw - 1) + w];
   const int32_t av = avoid_hit ? 0 : 10;
   *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
@@ -1248,8 +1248,8 @@ __device__ __forceinline__ Smem carve(unsigned char* base, int zone_stride) {
 
 // PIPE: the pipelined schedule (see `pipe` below) as a separate instantiation, so that the plain one carries none
 // of its state in registers.
-// POL: a Policy enabled plugins outside the DefaultProvider set (ksb_policy_set); the default instantiations carry none
-// of their code.
+// POL: a Policy enabled plugins outside the DefaultProvider set (ksb_policy_set), or a taint / preferAvoid set has grown
+// beyond 64 entries; the default instantiations carry none of that code.
 template <bool PIPE, bool MULTI, bool POL>
 __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1506,7 +1506,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             const bool any_z = __any_sync(0xffffffffu, hz != 0);
             int32_t vna = 0, vtt = 0, vsc = 0, vmax = 0, vmin = 0;
             if (h->n_pref) vna = warp_max(mna);
-            if (h->soft_untol || T.tw > 1) vtt = warp_max(mtt);
+            if (h->soft_untol || (POL && T.tw > 1)) vtt = warp_max(mtt);
             if (h->spread_col >= 0) vsc = warp_max(msc);
             if (h->n_score) {
               vmax = warp_max(max(0, ipa));
@@ -2933,7 +2933,9 @@ static const void* batch_kernel(bool pipe, bool multi, bool pol) {
 
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
   void* params[] = {(void*)args};
-  const bool pol = args->table.w_mr != 0 || args->table.w_rl != 0 || args->table.has_static != 0 || args->table.has_presence != 0;
+  // (the instantiations with the Policy plugins also carry the words above 0 of the taint / preferAvoid sets)
+  const bool pol = args->table.w_mr != 0 || args->table.w_rl != 0 || args->table.has_static != 0 || args->table.has_presence != 0 ||
+                   args->table.tw > 1;
   const void* fn = batch_kernel(args->pipeline != 0, args->n_ranks > 1, pol);
   cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,
                                               smem_bytes, stream);
