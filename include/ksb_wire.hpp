@@ -23,6 +23,7 @@
 //   list<toleration: str key, str operator, str value, str effect>;
 //   list<extended: str name; reslist limits; list<req>; list<str assigned>>;
 //   i32 num_volumes
+//   i32 priority   (util.GetPodPriority: *Spec.Priority, 0 when unset; read by preemption only)
 //   req = str key; str op; list<str value>
 //
 // SelectorOwner record: str namespace; str name; map map_selector; u8 selector_present; map match_labels; list<req>
@@ -344,6 +345,7 @@ inline void put(Writer& w, const Pod& p) {
     w.strs(e.assigned);
   }
   w.i32(p.num_volumes);
+  w.i32(p.priority);
 }
 
 inline Pod get_pod(Reader& r) {
@@ -398,6 +400,7 @@ inline Pod get_pod(Reader& r) {
     p.extended.push_back(std::move(e));
   }
   p.num_volumes = r.i32();
+  p.priority = r.i32();
   return p;
 }
 

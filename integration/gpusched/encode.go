@@ -280,6 +280,11 @@ func encodePod(p *v1.Pod) []byte {
 		w.strs(e.Assigned)
 	}
 	w.i32(int32(len(p.Spec.Volumes)))
+	prio := int32(0) // util.GetPodPriority
+	if p.Spec.Priority != nil {
+		prio = *p.Spec.Priority
+	}
+	w.i32(prio)
 	return w.b
 }
 

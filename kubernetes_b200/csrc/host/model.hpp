@@ -131,6 +131,7 @@ struct Pod {
   std::vector<Toleration> tolerations;
   std::vector<PodExtendedResource> extended;
   int32_t num_volumes = 0;
+  int32_t priority = 0;  // util.GetPodPriority (plugin/pkg/scheduler/util/utils.go:76-87): *Spec.Priority, 0 when unset
   std::string key() const { return ns + "/" + name; }
 };
 
@@ -313,6 +314,7 @@ inline Pod pod_from_json(const json::Value& v) {
     p.extended.push_back(std::move(r));
   }
   p.num_volumes = (int32_t)v.get_int("volumes");
+  p.priority = (int32_t)v.get_int("priority");
   return p;
 }
 

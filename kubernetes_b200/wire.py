@@ -175,6 +175,7 @@ def pod_record(p):
         w.reqs(e.get("required"))
         w.strs(e.get("assigned"))
     w.i32(p.get("volumes", 0))
+    w.i32(p.get("priority", 0))
     return bytes(w.b)
 
 

@@ -9,6 +9,7 @@
 #include "json.hpp"
 #include "model.hpp"
 #include "scheduler.hpp"
+#include "preempt.hpp"
 
 using namespace oracle;
 namespace json = ksb::json;
@@ -371,7 +372,70 @@ static std::string run_cache_ops(const json::Value& req) {
 
 extern "C" {
 
-// Generic entry: {"op": "stream" | "priority" | "predicate" | "device_match" | "node_info", ...}.
+// genericScheduler.Preempt for one pod on a loaded cluster (core/generic_scheduler.go:199-256), see preempt.hpp.
+// {"cluster", "pod", "resources_only": bool, "failed": {node: [reasons]} (optional: the FailedPredicateMap to use instead
+// of the one the predicates give)} -> {"potential", "candidates": [[node, [victims]]], "node", "victims", "clear_nomination"}
+static std::string run_preempt(const json::Value& req) {
+  ksb::Cluster cl = ksb::cluster_from_json(*req.find("cluster"));
+  ksb::Pod pod = ksb::pod_from_json(*req.find("pod"));
+  Oracle o;
+  apply_options(o, req);
+  o.load(cl);
+  o.cachedNodeInfoMap = o.cache.nodes;
+  const bool resources_only = req.get_bool("resources_only", false);
+  std::vector<NodePtr> nodes = o.node_list();
+  std::map<std::string, std::vector<std::string>> failed;
+  if (const json::Value* f = req.find("failed"); f && f->is_obj()) {
+    for (auto& kv : *f->o) {
+      std::vector<std::string> rs;
+      for (auto& r : *kv.second.a) rs.push_back(r.s);
+      failed[kv.first] = rs;
+    }
+  } else {
+    PredicateMeta meta = o.make_predicate_meta(pod);
+    std::vector<PodPtr> allPods = o.all_pods();
+    std::vector<Oracle::TermProbe> none;
+    for (auto& n : nodes) {
+      const NodeInfo& ni = o.cachedNodeInfoMap.at(n->name);
+      std::vector<std::string> fails;
+      std::string err;
+      if (resources_only) Oracle::pod_fits_resources(meta, ni, &fails);
+      else if (!o.pod_fits_on_node(pod, meta, ni, allPods, none, none, &fails, &err)) return "{\"error\":\"" + err + "\"}";
+      if (!fails.empty()) failed[n->name] = fails;
+    }
+  }
+  PreemptResult r = preempt(o, pod, nodes, failed, resources_only);
+  std::string out = "{";
+  put_kv(out, "error", r.error);
+  out += "\"potential\":[";
+  for (size_t i = 0; i < r.potential.size(); ++i) {
+    if (i) out += ",";
+    json::escape_to(out, r.potential[i]);
+  }
+  out += "],\"candidates\":[";
+  for (size_t i = 0; i < r.candidates.size(); ++i) {
+    if (i) out += ",";
+    out += "[";
+    json::escape_to(out, r.candidates[i].first);
+    out += ",[";
+    for (size_t k = 0; k < r.candidates[i].second.pods.size(); ++k) {
+      if (k) out += ",";
+      json::escape_to(out, r.candidates[i].second.pods[k]->key());
+    }
+    out += "]]";
+  }
+  out += "],";
+  put_kv(out, "node", r.node);
+  out += "\"victims\":[";
+  for (size_t i = 0; i < r.victims.size(); ++i) {
+    if (i) out += ",";
+    json::escape_to(out, r.victims[i]);
+  }
+  out += std::string("],\"clear_nomination\":") + (r.clear_nomination ? "true" : "false") + "}";
+  return out;
+}
+
+// Generic entry: {"op": "stream" | "priority" | "predicate" | "device_match" | "node_info" | "preempt", ...}.
 // Returns a malloc'd NUL-terminated JSON string; free with oracle_free.
 char* oracle_call(const char* json_in) {
   std::string out;
@@ -384,6 +448,7 @@ char* oracle_call(const char* json_in) {
     else if (op == "device_match") out = run_device_match(req);
     else if (op == "node_info") out = run_node_info(req);
     else if (op == "cache_ops") out = run_cache_ops(req);
+    else if (op == "preempt") out = run_preempt(req);
     else out = "{\"error\":\"unknown op\"}";
   } catch (const std::exception& e) {
     out = "{\"error\":";

@@ -333,6 +333,11 @@ def main():
         BUILDERS.extend(golden_policy.builders(globals()))
     except ImportError:
         pass
+    try:
+        import golden_preempt  # noqa: F401  (fifth batch: preemption)
+        BUILDERS.extend(golden_preempt.builders(globals()))
+    except ImportError:
+        pass
     for b in BUILDERS:
         b()
     out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "reference_vectors.json")

@@ -47,6 +47,15 @@ def check_case(c, call):
     elif c["op"] == "node_info":
         for k, v in exp.items():
             assert out[k] == v, (k, out, c["source"], c["test"])
+    elif c["op"] == "preempt":
+        assert not out.get("error"), out
+        if "candidates" in exp:  # selectNodesForPreemption: node -> set of victims (generic_scheduler_test.go:575-601)
+            got = {n: sorted(v.split("/", 1)[1] for v in vs) for n, vs in out["candidates"]}
+            assert got == {n: sorted(vs) for n, vs in exp["candidates"].items()}, (out, c["source"], c["test"])
+        if "node_in" in exp:  # pickOneNodeForPreemption: any of the listed nodes
+            assert out["node"] in exp["node_in"], (out, c["source"], c["test"])
+        if "potential" in exp:  # nodesWherePreemptionMightHelp
+            assert sorted(out["potential"]) == sorted(exp["potential"]), (out, c["source"], c["test"])
     elif c["op"] == "cache_ops":
         assert out["errors"] == exp["errors"], (out["errors"], c["source"], c["test"])
         assert out["nodes"] == exp["nodes"], (out["nodes"], c["source"], c["test"])
