@@ -132,6 +132,30 @@ enum {
 };
 int32_t ksb_policy_set(ksb_engine* e, int32_t kind, const char* key, size_t key_len, int32_t presence, int32_t weight);
 
+/* ---- preemption: ScheduleAlgorithm.Preempt (algorithm/scheduler_interface.go:48-61; genericScheduler.Preempt,
+ * core/generic_scheduler.go:199-256) ----
+ * For a pod whose ksb_schedule ended in KSB_FIT_ERROR. The call evaluates the pod once more (nothing is assumed) to have
+ * its FailedPredicateMap, keeps the nodes where preemption might help (nodesWherePreemptionMightHelp, :957-991), finds on
+ * every one of them the victims whose removal lets the pod fit (selectVictimsOnNode, :883-953: all lower-priority pods
+ * off, then reprieved from the highest priority down, equal priorities in the order go1.9's sort.Sort leaves them) and
+ * picks the node as pickOneNodeForPreemption does (:654-758: a node without victims, else the lowest highest victim
+ * priority, the lowest priority sum, the fewest victims, the first). Where the reference walks a Go map the rows are
+ * walked in node-name order. Nothing is removed: the caller deletes the victims and reports them with ksb_pod_remove.
+ * Not implemented (the call fails with a text that says which): a preemptor with pod (anti-)affinity terms or host
+ * ports, cached pods with required anti-affinity terms, PodDisruptionBudgets, nominated pods, extenders, sharded engines.
+ * status: 0 node picked (node_index, num_victims; victims by ksb_preempt_victim in decreasing priority),
+ *         1 no node qualifies, 2 preemption cannot help on any node: clear the pod's nominated node name (:227-231). */
+typedef struct {
+  int32_t status;
+  int32_t node_index;
+  int32_t num_victims;
+  int32_t num_potential;   /* nodes where preemption might help */
+  int32_t num_candidates;  /* of those, nodes on which the pod fits once victims are gone */
+} ksb_preempt_result;
+int32_t ksb_preempt(ksb_engine* e, const uint8_t* pod, size_t len, ksb_preempt_result* out);
+/* "namespace/name" of victim i of the most recent ksb_preempt; valid until the next call on this engine. */
+int32_t ksb_preempt_victim(ksb_engine* e, int32_t i, const char** key, size_t* len);
+
 /* ---- the hot path ---- */
 
 enum {

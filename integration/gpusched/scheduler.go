@@ -225,7 +225,43 @@ func (g *GPUScheduler) fitError(pod *v1.Pod, numNodes int) error {
 	return &core.FitError{Pod: pod, NumAllNodes: numNodes, FailedPredicates: failed}
 }
 
-// Preempt, Predicates and Prioritizers stay with the generic scheduler (the engine's scope is Schedule).
+// PreemptOnGPU: genericScheduler.Preempt's decision (core/generic_scheduler.go:199-256) from the engine: the node to
+// preempt on, the victims as namespace/name keys in decreasing priority, and whether the pod's own nomination is to be
+// cleared. An error means the case is outside the engine's scope (inter-pod affinity in play, host ports on the
+// preemptor, PDBs, nominated pods): Preempt below then asks the generic scheduler, as before.
+func (g *GPUScheduler) PreemptOnGPU(pod *v1.Pod) (string, []string, bool, error) {
+	g.mu.Lock()
+	defer g.mu.Unlock()
+	p, n := bytesPtr(encodePod(pod))
+	var r C.ksb_preempt_result
+	if C.ksb_preempt(g.e, p, n, &r) != 0 {
+		return "", nil, false, g.lastError()
+	}
+	if r.status == 2 {
+		return "", nil, true, nil
+	}
+	if r.status != 0 {
+		return "", nil, false, nil
+	}
+	var name *C.char
+	var nameLen C.size_t
+	if C.ksb_node_name(g.e, r.node_index, &name, &nameLen) != 0 {
+		return "", nil, false, fmt.Errorf("gpusched: node row %d has no name", int(r.node_index))
+	}
+	victims := make([]string, 0, int(r.num_victims))
+	for i := 0; i < int(r.num_victims); i++ {
+		var key *C.char
+		var keyLen C.size_t
+		if C.ksb_preempt_victim(g.e, C.int32_t(i), &key, &keyLen) == 0 {
+			victims = append(victims, C.GoStringN(key, C.int(keyLen)))
+		}
+	}
+	return C.GoStringN(name, C.int(nameLen)), victims, false, nil
+}
+
+// Preempt asks the generic scheduler (which resolves victims to *v1.Pod objects from its own cache, honours PDBs and
+// nominated pods); a factory that wants the engine's decision calls PreemptOnGPU first and maps the keys through its
+// pod lister. Predicates and Prioritizers stay with the generic scheduler as well.
 func (g *GPUScheduler) Preempt(pod *v1.Pod, nodeLister algorithm.NodeLister, scheduleErr error) (*v1.Node, []*v1.Pod, []*v1.Pod, error) {
 	return g.generic.Preempt(pod, nodeLister, scheduleErr)
 }

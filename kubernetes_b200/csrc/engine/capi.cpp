@@ -553,6 +553,27 @@ int32_t ksb_cache_skip_pod_update(ksb_engine* e, const uint8_t* buf, size_t len,
   });
 }
 
+int32_t ksb_preempt(ksb_engine* e, const uint8_t* pod, size_t len, ksb_preempt_result* out) {
+  return scheduling(e, [&] {
+    if (!out) throw std::runtime_error("out must not be null");
+    ksb::PreemptOutcome r = e->impl->preempt(decode_pod(pod, len));
+    out->status = r.status;
+    out->node_index = r.row;
+    out->num_victims = (int32_t)r.victims.size();
+    out->num_potential = r.num_potential;
+    out->num_candidates = r.num_candidates;
+  });
+}
+
+int32_t ksb_preempt_victim(ksb_engine* e, int32_t i, const char** key, size_t* len) {
+  if (!e || !e->impl || !key || !len) return -1;
+  const auto& v = e->impl->last_preempt.victims;
+  if (i < 0 || (size_t)i >= v.size()) return -1;
+  *key = v[(size_t)i].data();
+  *len = v[(size_t)i].size();
+  return 0;
+}
+
 int32_t ksb_policy_set(ksb_engine* e, int32_t kind, const char* key, size_t key_len, int32_t presence, int32_t weight) {
   return scheduling(e, [&] { e->impl->policy_set(kind, std::string(key ? key : "", key ? key_len : 0), presence != 0, weight); });
 }

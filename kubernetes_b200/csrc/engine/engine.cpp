@@ -96,6 +96,9 @@ Engine::~Engine() {
   pin_out.release();
   pin_col.release();
   b_fill_rows.release();
+  b_pre_pods.release();
+  b_pre_rows.release();
+  b_pre_out.release();
   for (auto& kv : numcols) kv.second.buf.release();
   if (ev_start) cudaEventDestroy(ev_start);
   if (ev_stop) cudaEventDestroy(ev_stop);
@@ -656,6 +659,7 @@ void Engine::host_add_pod(const Pod& p, HostNode& hn) {
       if (port.host_port != 0) hn.used_ports.insert(port_string(port));
   }
   hn.pod_keys.insert(p.key());
+  hn.pod_order.push_back(p.key());
   {
     auto& pl = sig_of(p)->placed[p.node_name];
     pl.first += 1;
@@ -692,6 +696,12 @@ void Engine::host_remove_pod(const Pod& p, HostNode& hn) {
   hn.req_agpu -= agpu;
   for (auto& kv : sc) hn.req_scalar[kv.first] -= kv.second;
   hn.pod_keys.erase(p.key());
+  for (size_t i = 0; i < hn.pod_order.size(); ++i)
+    if (hn.pod_order[i] == p.key()) {
+      hn.pod_order[i] = hn.pod_order.back();
+      hn.pod_order.pop_back();
+      break;
+    }
   {
     SigInfo* s = sig_of(p);
     auto pit = s->placed.find(p.node_name);
@@ -711,6 +721,11 @@ void Engine::host_remove_pod(const Pod& p, HostNode& hn) {
       if (ds->second.allocatable.count(id)) ds->second.available.insert(id);
     }
   }
+}
+
+void reslist_to_aggregates_public(const ResourceList& rl, int64_t* cpu, int64_t* mem, int64_t* agpu, int64_t* eph, int64_t* pods,
+                                  std::map<std::string, int64_t>* scalars) {
+  reslist_to_aggregates(rl, cpu, mem, agpu, eph, pods, scalars);
 }
 
 // ------------------------------------------------------------------ layout

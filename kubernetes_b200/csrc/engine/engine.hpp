@@ -47,6 +47,7 @@ struct HostNode {
   bool has_node = false;
   int row = -1;
   std::set<std::string> pod_keys;
+  std::vector<std::string> pod_order;  // NodeInfo.pods: appended by AddPod, RemovePod moves the last into the hole (node_info.go:329-419)
   std::set<std::string> used_ports;  // "proto/ip/port" (node_info.go:435-466)
   std::map<std::string, DeviceState> ext;
   int64_t req_cpu = 0, req_mem = 0, req_agpu = 0, req_eph = 0, nz_cpu = 0, nz_mem = 0;
@@ -56,6 +57,16 @@ struct HostNode {
 
 struct HostPod {
   Pod pod;  // node_name and extended[i].assigned filled in
+};
+
+void reslist_to_aggregates_public(const ResourceList& rl, int64_t* cpu, int64_t* mem, int64_t* agpu, int64_t* eph, int64_t* pods,
+                                  std::map<std::string, int64_t>* scalars);  // node_info.go:90-111
+
+struct PreemptOutcome {  // genericScheduler.Preempt's return values (core/generic_scheduler.go:199-256)
+  int status = 0;  // 0 a node was picked, 1 no node qualifies, 2 preemption cannot help anywhere: clear the pod's nomination
+  int row = -1;
+  int num_potential = 0, num_candidates = 0;
+  std::vector<std::string> victims;  // namespace/name, decreasing priority
 };
 
 struct SelClass {  // (namespaces, label selector) of a pod-affinity term
@@ -137,6 +148,9 @@ class Engine {
   bool pol_presence = true;
   int32_t w_most_requested = 0, w_resource_limits = 0;
   void policy_set(int kind, const std::string& key, bool presence, int32_t weight);
+  PreemptOutcome preempt(const Pod& p);
+  PreemptOutcome last_preempt;
+  DevBuf b_pre_pods, b_pre_rows, b_pre_out;
   void warm_dictionaries();
   std::string node_info_json(const std::string& name);
   void grow_keep(DevBuf& b, size_t bytes);

@@ -12,6 +12,8 @@
 
 #include "engine.hpp"
 
+#include <climits>
+
 #include <nvtx3/nvToolsExt.h>
 
 namespace ksb {
@@ -1184,6 +1186,162 @@ std::string Engine::fit_error_message(int i) {
   }
   msg += ".";
   return msg;
+}
+
+// genericScheduler.Preempt (core/generic_scheduler.go:199-256) for a pod whose Schedule ended in a FitError. The call
+// evaluates the pod once more (no assume) to have its FailedPredicateMap on the device, then runs one thread per node:
+// nodesWherePreemptionMightHelp, selectVictimsOnNode (ksb_preempt_kernel), and picks the node on the host
+// (pickOneNodeForPreemption over the per-row statistics, rows visited in name order where the reference walks a Go map).
+// Scope, enforced here: no inter-pod affinity in play (the preemptor has no pod (anti-)affinity terms, no cached pod has
+// required anti-affinity terms), no host ports on the preemptor, no PodDisruptionBudgets, no nominated pods.
+PreemptOutcome Engine::preempt(const Pod& p) {
+  if (cfg.shard_count > 1) throw std::runtime_error("ksb_preempt: not available on a sharded engine");
+  if (p.affinity.present && (p.affinity.pod.present || p.affinity.anti.present))
+    throw std::runtime_error("preemption for a pod with inter-pod (anti-)affinity terms is not implemented");
+  for (auto& c : p.containers)
+    for (auto& port : c.ports)
+      if (port.host_port != 0) throw std::runtime_error("preemption for a pod with host ports is not implemented");
+  {
+    std::lock_guard<std::mutex> g(mu);
+    for (auto& kv : pods) {
+      const Pod& ep = kv.second.pod;
+      if (ep.affinity.present && ep.affinity.anti.present && !ep.affinity.anti.required.empty())
+        throw std::runtime_error("preemption next to pods with required anti-affinity terms is not implemented");
+    }
+  }
+  // the FailedPredicateMap: one evaluation of the pod, nothing assumed (ksb_schedule)
+  std::vector<Pod> one{p};
+  ksb_result sr;
+  schedule_batch(one, &sr, false);
+  std::lock_guard<std::mutex> g(mu);
+  CUDA_OK(cudaSetDevice(cfg.device));
+  PreemptOutcome out;
+  if (sr.status == KSB_NO_NODES) throw std::runtime_error("no nodes available to schedule pods");
+  if (sr.status == KSB_SCHEDULE_ERROR) throw std::runtime_error("ksb_preempt: the pod cannot be evaluated");
+  ScratchLayout L = scratch_layout(ln_pad, zone_stride, std::max(1, nseg), group, pipe ? 2 : 1);
+  // cached pods per node, in NodeInfo.pods order
+  std::vector<int32_t> row_start((size_t)n + 1, 0);
+  std::vector<KsbVictimPod> vp;
+  std::vector<const std::string*> vkey;
+  for (int r = 0; r < n; ++r) {
+    row_start[r] = (int32_t)vp.size();
+    for (auto& key : rows[r]->pod_order) {
+      auto it = pods.find(key);
+      if (it == pods.end()) continue;
+      const Pod& ep = it->second.pod;
+      KsbVictimPod v;
+      memset(&v, 0, sizeof v);
+      int64_t dummy_pods = 0;
+      std::map<std::string, int64_t> sc;
+      for (auto& c : ep.containers) {  // calculateResource (node_info.go:421-433): containers only
+        reslist_to_aggregates_public(c.requests, &v.cpu, &v.mem, &v.agpu, &v.eph, &dummy_pods, &sc);
+        auto cpu = c.requests.find(kResCPU);
+        auto mem = c.requests.find(kResMemory);
+        v.nz_cpu += cpu == c.requests.end() ? 100 : cpu->second;
+        v.nz_mem += mem == c.requests.end() ? 200LL * 1024 * 1024 : mem->second;
+      }
+      for (auto& kv : sc) {
+        const int slot = scalar_slot(kv.first);
+        v.scalar[slot] += kv.second;
+      }
+      v.priority = ep.priority;
+      vp.push_back(v);
+      vkey.push_back(&it->first);
+    }
+  }
+  row_start[n] = (int32_t)vp.size();
+  b_pre_pods.ensure(std::max<size_t>(1, vp.size()) * sizeof(KsbVictimPod));
+  b_pre_rows.ensure(((size_t)n + 1) * 4);
+  // outputs: state, victims, highest [n] int32 each; sum [n] int64; victim list; error flag
+  const size_t o_state = 0, o_vict = (size_t)n_pad * 4, o_high = (size_t)n_pad * 8, o_sum = (size_t)n_pad * 12,
+               o_list = o_sum + (size_t)n_pad * 8, o_err = o_list + (size_t)KSB_MAX_VICTIMS * 4, o_total = o_err + 16;
+  b_pre_out.ensure(o_total);
+  if (!vp.empty()) CUDA_OK(cudaMemcpyAsync(b_pre_pods.d, vp.data(), vp.size() * sizeof(KsbVictimPod), cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemcpyAsync(b_pre_rows.d, row_start.data(), row_start.size() * 4, cudaMemcpyHostToDevice, stream));
+  CUDA_OK(cudaMemsetAsync((char*)b_pre_out.d + o_err, 0, 16, stream));
+  stats.h2d_bytes += vp.size() * sizeof(KsbVictimPod) + row_start.size() * 4;
+  const KsbPodHeader& h = last_encoded[0].h;
+  KsbPreemptArgs a;
+  memset(&a, 0, sizeof a);
+  a.table = dT;
+  a.reasons = (const uint32_t*)((char*)b_scratch.d + L.reasons);
+  a.pods = (const KsbVictimPod*)b_pre_pods.d;
+  a.row_start = (const int32_t*)b_pre_rows.d;
+  a.req_cpu = h.req_cpu;
+  a.req_mem = h.req_mem;
+  a.req_agpu = h.req_agpu;
+  a.req_eph = h.req_eph;
+  for (int s = 0; s < KSB_MAX_SCALARS; ++s) a.scalar_req[s] = h.scalar_req[s];
+  a.scalar_mask = h.scalar_mask;
+  a.has_request = (h.flags & PF_HAS_REQUEST) ? 1 : 0;
+  a.priority = p.priority;
+  a.only_row = -1;
+  char* ob = (char*)b_pre_out.d;
+  a.row_state = (int32_t*)(ob + o_state);
+  a.row_victims = (int32_t*)(ob + o_vict);
+  a.row_highest = (int32_t*)(ob + o_high);
+  a.row_sum = (int64_t*)(ob + o_sum);
+  a.victim_list = (int32_t*)(ob + o_list);
+  a.error_flag = (int32_t*)(ob + o_err);
+  int rc = ksb_launch_preempt(&a, stream);
+  if (rc != 0) throw std::runtime_error(std::string("preemption kernel failed: ") + cudaGetErrorString((cudaError_t)rc));
+  stats.kernel_launches += 1;
+  std::vector<int32_t> st((size_t)n), nv((size_t)n), hi((size_t)n);
+  std::vector<int64_t> sum((size_t)n);
+  int32_t err = 0;
+  CUDA_OK(cudaMemcpyAsync(st.data(), ob + o_state, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(nv.data(), ob + o_vict, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(hi.data(), ob + o_high, (size_t)n * 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(sum.data(), ob + o_sum, (size_t)n * 8, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaMemcpyAsync(&err, ob + o_err, 4, cudaMemcpyDeviceToHost, stream));
+  CUDA_OK(cudaStreamSynchronize(stream));
+  stats.d2h_bytes += (size_t)n * 20 + 4;
+  if (err != 0) throw std::runtime_error("a node holds more than " + std::to_string(KSB_MAX_VICTIMS) + " lower-priority pods");
+  for (int r = 0; r < n; ++r) {
+    if (st[r] >= 1) out.num_potential += 1;
+    if (st[r] == 2) out.num_candidates += 1;
+  }
+  if (out.num_potential == 0) {  // generic_scheduler.go:227-231: clean up the pod's nominated node name
+    out.status = 2;
+    last_preempt = out;
+    return out;
+  }
+  // pickOneNodeForPreemption (:654-758); no PDBs, so every node has zero violations
+  int pick = -1;
+  for (int r = 0; r < n && pick < 0; ++r)
+    if (st[r] == 2 && nv[r] == 0) pick = r;  // a node that needs no preemption
+  if (pick < 0) {
+    int32_t min_high = INT32_MAX;
+    for (int r = 0; r < n; ++r)
+      if (st[r] == 2) min_high = std::min(min_high, hi[r]);
+    int64_t min_sum = INT64_MAX;
+    for (int r = 0; r < n; ++r)
+      if (st[r] == 2 && hi[r] == min_high) min_sum = std::min(min_sum, sum[r]);
+    int32_t min_n = INT32_MAX;
+    for (int r = 0; r < n; ++r)
+      if (st[r] == 2 && hi[r] == min_high && sum[r] == min_sum) min_n = std::min(min_n, nv[r]);
+    for (int r = 0; r < n && pick < 0; ++r)
+      if (st[r] == 2 && hi[r] == min_high && sum[r] == min_sum && nv[r] == min_n) pick = r;
+  }
+  if (pick < 0) {
+    out.status = 1;
+    last_preempt = out;
+    return out;
+  }
+  out.status = 0;
+  out.row = pick;
+  if (nv[pick] > 0) {  // the picked row once more, this time writing its victims
+    a.only_row = pick;
+    rc = ksb_launch_preempt(&a, stream);
+    if (rc != 0) throw std::runtime_error(std::string("preemption kernel failed: ") + cudaGetErrorString((cudaError_t)rc));
+    stats.kernel_launches += 1;
+    std::vector<int32_t> list((size_t)nv[pick]);
+    CUDA_OK(cudaMemcpyAsync(list.data(), ob + o_list, list.size() * 4, cudaMemcpyDeviceToHost, stream));
+    CUDA_OK(cudaStreamSynchronize(stream));
+    for (int32_t i : list) out.victims.push_back(*vkey[(size_t)i]);
+  }
+  last_preempt = out;
+  return out;
 }
 
 // Cache.AssumePod / AddPod outside a batch.

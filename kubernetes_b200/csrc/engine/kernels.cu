@@ -3115,3 +3115,260 @@ extern "C" int ksb_noalloc_bind(int device, int n_pad, int zone_stride, int grid
   a->eval_n = a->table.n;
   return 0;
 }
+
+// ------------------------------------------------------------------ preemption
+// selectVictimsOnNode (core/generic_scheduler.go:883-953) for every node where preemption might help (:957-991), one
+// thread per row: take every lower-priority pod off the node's aggregates, check that the preemptor fits, order the
+// potential victims by decreasing priority exactly as the reference's sort.Sort does (go1.9 src/sort/sort.go,
+// restated below: the order among equal priorities decides who is reprieved), then put them back one by one as long
+// as the preemptor still fits. pickOneNodeForPreemption (:654-758) runs on the host over the per-row statistics.
+// Scope (enforced by Engine::preempt): no inter-pod affinity in play, no host ports on the preemptor, no PDBs.
+namespace {
+constexpr uint32_t kUnresolvable = (1u << RB_SELECTOR) | (1u << RB_HOSTNAME) | (1u << RB_TAINTS) | (1u << RB_LABEL_PRESENCE) |
+                                   (1u << RB_NOT_READY) | (1u << RB_NET_UNAVAILABLE) | (1u << RB_UNSCHEDULABLE);
+// bits that removing pods can clear, and bits podFitsOnNode never sets (the fork's device selection runs after it)
+constexpr uint32_t kByRemoval = 0x1ffu;  // RB_PODS .. RB_SCALAR3
+constexpr uint32_t kNotPodFits = (0xfu << RB_EXT0) | (1u << RB_EXT_LIMITS);
+
+struct NodeAgg {
+  int64_t cpu, mem, agpu, eph, scalar[KSB_MAX_SCALARS];
+  int32_t pods;
+};
+
+struct GoSortDev {  // sort.Sort over idx[0..n): Less(i, j) = priority(idx[i]) > priority(idx[j])
+  int32_t* idx;
+  const KsbVictimPod* pods;
+  __device__ bool less(int i, int j) const { return pods[idx[i]].priority > pods[idx[j]].priority; }
+  __device__ void swap(int i, int j) {
+    const int32_t t = idx[i];
+    idx[i] = idx[j];
+    idx[j] = t;
+  }
+  __device__ void insertionSort(int a, int b) {
+    for (int i = a + 1; i < b; i++)
+      for (int j = i; j > a && less(j, j - 1); j--) swap(j, j - 1);
+  }
+  __device__ void siftDown(int lo, int hi, int first) {
+    int root = lo;
+    for (;;) {
+      int child = 2 * root + 1;
+      if (child >= hi) return;
+      if (child + 1 < hi && less(first + child, first + child + 1)) child++;
+      if (!less(first + root, first + child)) return;
+      swap(first + root, first + child);
+      root = child;
+    }
+  }
+  __device__ void heapSort(int a, int b) {
+    const int first = a, lo = 0, hi = b - a;
+    for (int i = (hi - 1) / 2; i >= 0; i--) siftDown(i, hi, first);
+    for (int i = hi - 1; i >= 0; i--) {
+      swap(first, first + i);
+      siftDown(lo, i, first);
+    }
+  }
+  __device__ void medianOfThree(int m1, int m0, int m2) {
+    if (less(m1, m0)) swap(m1, m0);
+    if (less(m2, m1)) {
+      swap(m2, m1);
+      if (less(m1, m0)) swap(m1, m0);
+    }
+  }
+  __device__ void doPivot(int lo, int hi, int* midlo, int* midhi) {
+    const int m = (int)((unsigned)(lo + hi) >> 1);
+    if (hi - lo > 40) {
+      const int s = (hi - lo) / 8;
+      medianOfThree(lo, lo + s, lo + 2 * s);
+      medianOfThree(m, m - s, m + s);
+      medianOfThree(hi - 1, hi - 1 - s, hi - 1 - 2 * s);
+    }
+    medianOfThree(lo, m, hi - 1);
+    const int pivot = lo;
+    int a = lo + 1, c = hi - 1;
+    for (; a < c && less(a, pivot); a++) {
+    }
+    int b = a;
+    for (;;) {
+      for (; b < c && !less(pivot, b); b++) {
+      }
+      for (; b < c && less(pivot, c - 1); c--) {
+      }
+      if (b >= c) break;
+      swap(b, c - 1);
+      b++;
+      c--;
+    }
+    bool protect = hi - c < 5;
+    if (!protect && hi - c < (hi - lo) / 4) {
+      int dups = 0;
+      if (!less(pivot, hi - 1)) {
+        swap(c, hi - 1);
+        c++;
+        dups++;
+      }
+      if (!less(b - 1, pivot)) {
+        b--;
+        dups++;
+      }
+      if (!less(m, pivot)) {
+        swap(m, b - 1);
+        b--;
+        dups++;
+      }
+      protect = dups > 1;
+    }
+    if (protect) {
+      for (;;) {
+        for (; a < b && !less(b - 1, pivot); b--) {
+        }
+        for (; a < b && less(a, pivot); a++) {
+        }
+        if (a >= b) break;
+        swap(a, b - 1);
+        a++;
+        b--;
+      }
+    }
+    swap(pivot, b - 1);
+    *midlo = b - 1;
+    *midhi = c;
+  }
+  // quickSort(data, 0, n, maxDepth(n)) with the recursion on the smaller side kept on an explicit stack (the ranges
+  // are disjoint, so the order in which they are finished does not change the result)
+  __device__ void sort(int n) {
+    int depth = 0;
+    for (int i = n; i > 0; i >>= 1) depth++;
+    int stack[3 * 24];
+    int sp = 0;
+    stack[sp++] = 0;
+    stack[sp++] = n;
+    stack[sp++] = depth * 2;
+    while (sp > 0) {
+      int maxDepth = stack[--sp], b = stack[--sp], a = stack[--sp];
+      bool done = false;
+      while (b - a > 12) {
+        if (maxDepth == 0) {
+          heapSort(a, b);
+          done = true;
+          break;
+        }
+        maxDepth--;
+        int mlo, mhi;
+        doPivot(a, b, &mlo, &mhi);
+        if (mlo - a < b - mhi) {
+          stack[sp++] = a;  // the smaller side: at most lg(n) ranges wait at a time
+          stack[sp++] = mlo;
+          stack[sp++] = maxDepth;
+          a = mhi;
+        } else {
+          stack[sp++] = mhi;
+          stack[sp++] = b;
+          stack[sp++] = maxDepth;
+          b = mlo;
+        }
+      }
+      if (done) continue;
+      if (b - a > 1) {
+        for (int i = a + 6; i < b; i++)
+          if (less(i, i - 6)) swap(i, i - 6);
+        insertionSort(a, b);
+      }
+    }
+  }
+};
+}  // namespace
+
+__global__ void ksb_preempt_kernel(KsbPreemptArgs A) {
+  const KsbNodeTable& T = A.table;
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (A.only_row >= 0) {
+    if (r != 0) return;
+    r = A.only_row;
+  }
+  if (r >= T.n) return;
+  const size_t np = T.n_pad;
+  const uint32_t mask = A.reasons[r];
+  int32_t state = 0, nv = 0, highest = 0;
+  int64_t sum = 0;
+  if (!(mask & kUnresolvable)) {  // nodesWherePreemptionMightHelp
+    state = 1;
+    if (!(mask & ~(kByRemoval | kNotPodFits))) {  // nothing fails that removing pods cannot change
+      NodeAgg g;
+      g.cpu = T.req_cpu[r];
+      g.mem = T.req_mem[r];
+      g.agpu = T.req_agpu[r];
+      g.eph = T.req_eph[r];
+      for (int s = 0; s < KSB_MAX_SCALARS; ++s) g.scalar[s] = T.req_scalar[s * np + r];
+      g.pods = T.num_pods[r];
+      const int64_t acpu = T.alloc_cpu[r], amem = T.alloc_mem[r], aagpu = T.alloc_agpu[r], aeph = T.alloc_eph[r];
+      const int32_t apods = T.alloc_pods[r];
+      auto fits = [&]() {  // PodFitsResources (predicates.go:630-687)
+        if (g.pods + 1 > apods) return false;
+        if (!A.has_request) return true;
+        if (acpu < A.req_cpu + g.cpu || amem < A.req_mem + g.mem || aagpu < A.req_agpu + g.agpu || aeph < A.req_eph + g.eph) return false;
+        for (int s = 0; s < KSB_MAX_SCALARS; ++s)
+          if (((A.scalar_mask >> s) & 1u) && T.alloc_scalar[s * np + r] < A.scalar_req[s] + g.scalar[s]) return false;
+        return true;
+      };
+      auto remove = [&](const KsbVictimPod& p) {  // NodeInfo.RemovePod: ephemeral storage is never given back (node_info.go:396-398)
+        g.cpu -= p.cpu;
+        g.mem -= p.mem;
+        g.agpu -= p.agpu;
+        for (int s = 0; s < KSB_MAX_SCALARS; ++s) g.scalar[s] -= p.scalar[s];
+        g.pods -= 1;
+      };
+      auto add = [&](const KsbVictimPod& p) {  // NodeInfo.AddPod
+        g.cpu += p.cpu;
+        g.mem += p.mem;
+        g.agpu += p.agpu;
+        g.eph += p.eph;
+        for (int s = 0; s < KSB_MAX_SCALARS; ++s) g.scalar[s] += p.scalar[s];
+        g.pods += 1;
+      };
+      int32_t idx[KSB_MAX_VICTIMS];
+      int n = 0;
+      bool overflow = false;
+      for (int i = A.row_start[r]; i < A.row_start[r + 1]; ++i)
+        if (A.pods[i].priority < A.priority) {  // NodeInfo.pods order (see oracle/preempt.hpp on the range-while-removing loop)
+          if (n == KSB_MAX_VICTIMS) {
+            overflow = true;
+            break;
+          }
+          idx[n++] = i;
+          remove(A.pods[i]);
+        }
+      if (overflow) {
+        atomicExch(A.error_flag, 1);
+      } else {
+        GoSortDev gs{idx, A.pods};
+        gs.sort(n);
+        if (fits()) {
+          state = 2;
+          for (int k = 0; k < n; ++k) {  // reprieve from the highest priority down
+            const KsbVictimPod& p = A.pods[idx[k]];
+            add(p);
+            if (!fits()) {
+              remove(p);
+              if (nv == 0) highest = p.priority;
+              sum += (int64_t)p.priority + 2147483648ll;
+              if (A.only_row >= 0) A.victim_list[nv] = idx[k];
+              nv += 1;
+            }
+          }
+        }
+      }
+    }
+  }
+  A.row_state[r] = state;
+  A.row_victims[r] = nv;
+  A.row_highest[r] = highest;
+  A.row_sum[r] = sum;
+}
+
+extern "C" int ksb_launch_preempt(const KsbPreemptArgs* args, cudaStream_t stream) {
+  const int n = args->only_row >= 0 ? 1 : args->table.n;
+  if (n <= 0) return 0;
+  ksb_preempt_kernel<<<(n + 127) / 128, 128, 0, stream>>>(*args);
+  return (int)cudaGetLastError();
+}
+

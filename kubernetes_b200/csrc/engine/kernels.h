@@ -113,6 +113,39 @@ int ksb_launch_apply(const KsbNodeTable* T, const KsbPodHeader* header, const ui
                      const uint32_t* masks, cudaStream_t stream);
 size_t ksb_batch_smem_bytes(int zone_stride);
 int ksb_max_pool_words();
+// ---- preemption (core/generic_scheduler.go:199-256, :654-991), one thread per node row
+// A cached pod as selectVictimsOnNode needs it: what NodeInfo.RemovePod / AddPod move (node_info.go:329-419) and its
+// priority. Pods of one node are consecutive, in NodeInfo.pods order.
+struct KsbVictimPod {
+  int64_t cpu, mem, agpu, eph, nz_cpu, nz_mem;
+  int64_t scalar[KSB_MAX_SCALARS];
+  int32_t priority;
+  int32_t pad;
+};
+struct KsbPreemptArgs {
+  KsbNodeTable table;
+  const uint32_t* reasons;       // [n] FailedPredicateMap of the Schedule call that failed: one reason mask per row
+  const KsbVictimPod* pods;      // CSR values
+  const int32_t* row_start;      // [n + 1] CSR offsets
+  // the preemptor (GetResourceRequest, predicates.go:630-687)
+  int64_t req_cpu, req_mem, req_agpu, req_eph;
+  int64_t scalar_req[KSB_MAX_SCALARS];
+  uint32_t scalar_mask;
+  int32_t has_request;
+  int32_t priority;
+  int32_t only_row;              // -1: every row, statistics only; else: this row, with its victim list
+  // per row: state (0 preemption cannot help, 1 potential node, 2 candidate: the pod fits once victims are gone),
+  // number of victims, highest victim priority; sum of (priority + 2^31) over the victims
+  int32_t* row_state;
+  int32_t* row_victims;
+  int32_t* row_highest;
+  int64_t* row_sum;
+  int32_t* victim_list;          // only_row >= 0: the row's victims as indices into pods[], decreasing priority
+  int32_t* error_flag;           // 1: a node holds more lower-priority pods than KSB_MAX_VICTIMS
+};
+#define KSB_MAX_VICTIMS 512
+int ksb_launch_preempt(const KsbPreemptArgs* args, cudaStream_t stream);
+
 // Set one label bit on the device (a bit interned after the table was uploaded): rows whose parsed numeric label value
 // is greater / less than x, or the listed rows.
 int ksb_launch_label_threshold(uint64_t* col, const int64_t* num, const uint8_t* valid, int n, uint64_t mask, int greater, int64_t x,

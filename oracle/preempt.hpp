@@ -12,8 +12,9 @@
 //   the insertion-sort path).
 //
 // Scope of this restatement (the engine's ksb_preempt has the same): podFitsOnNode is evaluated without the
-// inter-pod-affinity metadata updates of meta.RemovePod / meta.AddPod, so a preemptor with pod (anti-)affinity terms,
-// or a cluster in which an existing pod carries required anti-affinity terms, is refused with an error. No
+// inter-pod-affinity metadata updates of meta.RemovePod / meta.AddPod, so a preemptor with pod (anti-)affinity terms
+// (or host ports: the engine keeps port bitmaps per node, not per pod), or a cluster in which an existing pod carries
+// required anti-affinity terms, is refused with an error. No
 // PodDisruptionBudgets (numPDBViolations is 0), no nominated pods (the scheduling queue is nil), no extenders.
 //
 // Where the reference iterates a Go map (pickOneNodeForPreemption over nodesToVictims) its result is one of several
@@ -295,6 +296,12 @@ inline PreemptResult preempt(Oracle& o, const Pod& pod, const std::vector<NodePt
       res.error = "preemption for a pod with inter-pod (anti-)affinity terms is not implemented";
       return res;
     }
+    for (auto& c : pod.containers)
+      for (auto& port : c.ports)
+        if (port.host_port != 0) {
+          res.error = "preemption for a pod with host ports is not implemented";
+          return res;
+        }
     for (auto& kv : o.cachedNodeInfoMap)
       for (auto& ep : kv.second.podsWithAffinity)
         if (ep->affinity.present && !required_terms(ep->affinity.anti).empty()) {
