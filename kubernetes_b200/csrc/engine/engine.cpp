@@ -130,8 +130,12 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
   if (it != label_bits.end()) return it->second;
   will_mutate();
   int bit = (int)label_defs.size();
-  if (bit >= W * 64)
-    throw std::runtime_error("label universe exceeds label_words*64 bits; create the engine with a larger label_words");
+  if (bit >= W * 64) {
+    if (W >= 16 || (cfg.shard_count > 1 && shard_connected))
+      throw std::runtime_error("label universe exceeds label_words*64 bits (1,024 at most; a sharded engine keeps the width it was connected with)");
+    pending_W = std::min(16, W * 2);
+    throw GrowLabels();
+  }
   LabelBitDef d;
   d.kind = kind;
   d.key = key;
@@ -976,6 +980,7 @@ void Engine::rebuild_layout() {
   }
   n = (int)rows.size();
   n_pad = std::max(256, (n + 255) & ~255);
+  if (pending_W > W) W = pending_W;  // wider label columns (GrowLabels)
   for (;;) {
     TW = std::max(TW, pending_TW);  // a taint / preferAvoid set outgrew its words: wider columns from here on
     h_i64.assign((size_t)I64_COLS * n_pad, 0);

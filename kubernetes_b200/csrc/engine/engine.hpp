@@ -90,6 +90,12 @@ struct SpreadClass {
 
 // Thrown by the dictionaries when a lookup would have to intern something new while the calling thread runs in
 // read-only mode (the parallel part of the batch encoder): the pod is then encoded again on the main thread.
+// A label bit beyond the current words was asked for: the table has to be re-laid with wider label columns before the
+// pod can be encoded (caught by ksb_schedule* / ksb_pod_add, which grow the columns and start over).
+struct GrowLabels : std::exception {
+  const char* what() const noexcept override { return "label universe outgrew its words"; }
+};
+
 struct NeedsIntern {};
 
 struct SigInfo {  // memo per distinct (namespace, labels) signature
@@ -135,6 +141,7 @@ class Engine {
   void schedule_batch(std::vector<Pod>& pods, ksb_result* out, bool assume);
   void flush();
   void resync_begin();
+  void schedule_batch_once(std::vector<Pod>& batch, ksb_result* out, bool assume);
   // Plugins a Policy enables next to the DefaultProvider set (api/types.go:36-125): NodeLabelPriority instances and the
   // CheckNodeLabelPresence labels are per-node facts computed on the host (a score column, a node flag); the
   // MostRequestedPriority and ResourceLimitsPriority weights go to the kernel.
@@ -175,7 +182,9 @@ class Engine {
 
  private:
   // ---- dictionaries
-  int W;  // label words
+  int W;  // label words (64 bits each); grows by doubling, up to 16, when a selector mentions more distinct pairs
+  int pending_W = 0;
+  size_t batch_posted = 0;  // pods of the running batch already committed and mirrored (chunked batches)
   std::unordered_map<std::string, int> label_bits;  // "P\0k\0v" | "K\0k" | "G\0k\0n" | "L\0k\0n" -> bit
   struct LabelBitDef {
     char kind;

@@ -392,8 +392,27 @@ void Engine::restore_dynamic() {
   CUDA_OK(cudaMemcpyAsync(b_tables.d, d + s0 + s1 + s2 + s3, s4, cudaMemcpyDeviceToDevice, stream));
 }
 
+// ksb_schedule / ksb_schedule_batch. A selector may mention more distinct label pairs than the label columns have bits
+// for: the columns are then doubled (up to 16 words) and the call starts over, unless chunks of it are already committed.
 void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assume) {
+  for (int attempt = 0;; ++attempt) {
+    try {
+      schedule_batch_once(batch, out, assume);
+      return;
+    } catch (const GrowLabels&) {
+      std::lock_guard<std::mutex> g(mu);
+      if (batch_posted > 0)
+        throw std::runtime_error("label universe outgrew its words inside a chunked batch: the first " + std::to_string(batch_posted) +
+                                 " pods are committed (see the results), resubmit the rest");
+      if (attempt >= 3) throw std::runtime_error("label universe keeps outgrowing its words");
+      layout_dirty = true;  // rebuild_layout takes pending_W
+    }
+  }
+}
+
+void Engine::schedule_batch_once(std::vector<Pod>& batch, ksb_result* out, bool assume) {
   std::lock_guard<std::mutex> g(mu);
+  batch_posted = 0;
   CUDA_OK(cudaSetDevice(cfg.device));
   const int np = (int)batch.size();
   NvtxRange r_call(np == 1 ? "Scheduling (ksb_schedule)" : "Scheduling (ksb_schedule_batch)");
@@ -721,6 +740,7 @@ void Engine::schedule_batch(std::vector<Pod>& batch, ksb_result* out, bool assum
       pods[std::move(key)] = HostPod{std::move(p)};  // the batch is the caller's scratch copy: its pods move into the cache
     }
     post_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
+    if (assume) batch_posted = (size_t)c1;
   };
 
   auto bounds = [&](int c, int* c0, int* c1) {
@@ -1367,7 +1387,16 @@ void Engine::pod_add(const Pod& p) {
   register_pod_classes(p);
   layout_arena();
   EncodedPod e;
-  encode_pod(p, &e);
+  try {
+    encode_pod(p, &e);
+  } catch (const GrowLabels&) {
+    // (a pod's own selectors play no part in AddPod, but the encoder compiles them): wider label columns, then as for
+    // any table that is about to be rebuilt
+    layout_dirty = true;
+    host_add_pod(p, hn);
+    pods[p.key()] = HostPod{p};
+    return;
+  }
   e.h.pool_off = 0;
   uint32_t masks[KSB_MAX_EXT] = {0, 0, 0, 0};
   for (size_t j = 0; j < p.extended.size() && j < KSB_MAX_EXT; ++j) {

@@ -315,3 +315,19 @@ def test_policy_plugins_match_oracle():
     compare(cluster, "policy", gpu_opts=opts, oracle_opts=opts)
     small = workloads.generate(3, 120, 300)
     compare(small, "policy single", gpu_opts=dict(opts, batch=0), oracle_opts=opts)
+
+
+def test_label_universe_grows_past_256_pairs():
+    """More distinct (key, value) pairs in selectors than four 64-bit label words hold: the engine doubles the label
+    columns (GrowLabels) and goes on; the general label-word path of the kernel against the oracle."""
+    cluster = workloads.generate(3, 240, 900)
+    for i, n in enumerate(cluster["nodes"]):
+        for k in range(6):
+            n["labels"]["grp%02d" % ((i + 7 * k) % 45)] = "val%d" % ((i // 3 + k) % 9)  # 405 possible pairs
+    for i, p in enumerate(cluster["pods"]):
+        p["nodeSelector"] = {}
+        p["affinity"] = {"node": {"required": [{"matchExpressions": [
+            {"key": "grp%02d" % ((3 * i + j) % 45), "op": "In", "values": ["val%d" % ((i + j + v) % 9) for v in range(5)]}
+            for j in range(2)]}, {"matchExpressions": [{"key": "grp%02d" % ((5 * i) % 45), "op": "Exists", "values": []}]}]}}
+    compare(cluster, "wide labels")
+    compare(cluster, "wide labels single", gpu_opts={"batch": 0, "limit": 300}, oracle_opts={"limit": 300})
