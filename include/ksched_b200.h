@@ -270,6 +270,20 @@ typedef struct ksb_stats {
 } ksb_stats;
 int32_t ksb_get_stats(const ksb_engine* e, ksb_stats* out);
 
+/* ---- scheduler extenders (algorithm.SchedulerExtender; core/extender.go, wire form api/types.go:127-202) ----
+ * The extenders are HTTP services the Go side calls (HTTPExtender.Filter / Prioritize with ExtenderArgs ->
+ * ExtenderFilterResult / HostPriorityList); the engine takes their verdict for one pod. Sequence in the shim, as in
+ * findNodesThatFit / PrioritizeNodes (core/generic_scheduler.go:333-351, :608-632): ksb_schedule for the nodes that pass
+ * the predicates (ksb_failed_predicates: rows whose mask has no bit outside the device-selection reasons), the
+ * extenders' Filter calls on that list and Prioritize calls on the outcome, then ksb_schedule_extended with
+ *   keep_rows  one bit per node row (bit r of word r/32): the rows the Filter calls kept; NULL = no Filter verdict.
+ *              A row that is not kept fails with the reason "extender" (the shim puts the extender's own message into
+ *              FailedPredicateMap) before the fork's device selection runs, as in the reference;
+ *   row_scores sum over the extenders of weight * score per node row (combinedScores); NULL = none.
+ * Same result record as ksb_schedule; nothing is assumed. */
+int32_t ksb_schedule_extended(ksb_engine* e, const uint8_t* pod, size_t len, const uint32_t* keep_rows, const int32_t* row_scores,
+                              ksb_result* out);
+
 /* Re-run the device part of the most recent ksb_schedule_batch `iters` times against a
  * restored copy of the node table it started from, with inputs already resident in HBM, and
  * return the average CUDA-event milliseconds per run (measurement only; state is restored). */

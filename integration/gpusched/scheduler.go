@@ -160,6 +160,72 @@ func (g *GPUScheduler) Schedule(pod *v1.Pod, nodeLister algorithm.NodeLister) (s
 	return host, g.binding(pod, &r), nil
 }
 
+// ScheduleWithExtenders: Schedule when algorithm.SchedulerExtender instances are configured
+// (core/generic_scheduler.go:333-351, :608-632). The extenders are called from Go exactly as the generic scheduler
+// calls them (HTTPExtender.Filter / Prioritize, core/extender.go; wire form api/types.go:127-202); the engine gets their
+// verdict: `keep` = the node names their Filter calls left (nil: no Filter extender), `scores` = combinedScores, the sum
+// over extenders of weight * score by node name (nil: no Prioritize extender). The caller obtains the list to show the
+// extenders from a first Schedule: the nodes without a failed predicate (FitError.FailedPredicates otherwise).
+func (g *GPUScheduler) ScheduleWithExtenders(pod *v1.Pod, keep map[string]bool, scores map[string]int) (string, v1.ExtendedResourceBinding, error) {
+	g.mu.Lock()
+	defer g.mu.Unlock()
+	p, n := bytesPtr(encodePod(pod))
+	numNodes := 0
+	for ; ; numNodes++ { // rows are the nodes in name order; ksb_node_name fails past the last one
+		var name *C.char
+		var nameLen C.size_t
+		if C.ksb_node_name(g.e, C.int32_t(numNodes), &name, &nameLen) != 0 {
+			break
+		}
+	}
+	var keepRows []C.uint32_t
+	var rowScores []C.int32_t
+	if keep != nil {
+		keepRows = make([]C.uint32_t, (numNodes+31)/32)
+	}
+	if scores != nil {
+		rowScores = make([]C.int32_t, numNodes)
+	}
+	for row := 0; row < numNodes; row++ {
+		var name *C.char
+		var nameLen C.size_t
+		C.ksb_node_name(g.e, C.int32_t(row), &name, &nameLen)
+		host := C.GoStringN(name, C.int(nameLen))
+		if keep != nil && keep[host] {
+			keepRows[row/32] |= 1 << uint(row%32)
+		}
+		if scores != nil {
+			rowScores[row] = C.int32_t(scores[host])
+		}
+	}
+	var kp *C.uint32_t
+	var sp *C.int32_t
+	if len(keepRows) > 0 {
+		kp = &keepRows[0]
+	}
+	if len(rowScores) > 0 {
+		sp = &rowScores[0]
+	}
+	var r C.ksb_result
+	if C.ksb_schedule_extended(g.e, p, n, kp, sp, &r) != 0 {
+		return "", nil, g.lastError()
+	}
+	switch r.status {
+	case C.KSB_NO_NODES:
+		return "", nil, core.ErrNoNodesAvailable
+	case C.KSB_FIT_ERROR:
+		return "", nil, g.fitError(pod, int(r.num_nodes)) // "extender" stands for the extenders' own messages
+	case C.KSB_SCHEDULE_ERROR:
+		return "", nil, g.lastError()
+	}
+	var name *C.char
+	var nameLen C.size_t
+	if C.ksb_node_name(g.e, r.node_index, &name, &nameLen) != 0 {
+		return "", nil, fmt.Errorf("gpusched: node row %d has no name", int(r.node_index))
+	}
+	return C.GoStringN(name, C.int(nameLen)), g.binding(pod, &r), nil
+}
+
 // binding: device bit masks -> v1.ExtendedResourceBinding (resource entry name -> device ids), what
 // core.GetExtendedResources returns (core/extended_resources.go:42-81).
 func (g *GPUScheduler) binding(pod *v1.Pod, r *C.ksb_result) v1.ExtendedResourceBinding {

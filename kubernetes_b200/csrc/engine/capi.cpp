@@ -553,6 +553,14 @@ int32_t ksb_cache_skip_pod_update(ksb_engine* e, const uint8_t* buf, size_t len,
   });
 }
 
+int32_t ksb_schedule_extended(ksb_engine* e, const uint8_t* pod, size_t len, const uint32_t* keep_rows, const int32_t* row_scores,
+                              ksb_result* out) {
+  return scheduling(e, [&] {
+    if (!out) throw std::runtime_error("out must not be null");
+    e->impl->schedule_extended(decode_pod(pod, len), keep_rows, row_scores, out);
+  });
+}
+
 int32_t ksb_preempt(ksb_engine* e, const uint8_t* pod, size_t len, ksb_preempt_result* out) {
   return scheduling(e, [&] {
     if (!out) throw std::runtime_error("out must not be null");

@@ -38,7 +38,7 @@ enum {
   RB_PODS = 0, RB_CPU, RB_MEM, RB_AGPU, RB_EPH, RB_SCALAR0, RB_SCALAR1, RB_SCALAR2, RB_SCALAR3,
   RB_HOSTNAME, RB_PORTS, RB_SELECTOR, RB_TAINTS, RB_MEM_PRESSURE, RB_DISK_PRESSURE, RB_NOT_READY,
   RB_OUT_OF_DISK, RB_NET_UNAVAILABLE, RB_UNSCHEDULABLE, RB_IPA, RB_IPA_EXISTING_ANTI, RB_IPA_AFFINITY,
-  RB_IPA_ANTI, RB_EXT0, RB_EXT1, RB_EXT2, RB_EXT3, RB_EXT_LIMITS, RB_LABEL_PRESENCE
+  RB_IPA_ANTI, RB_EXT0, RB_EXT1, RB_EXT2, RB_EXT3, RB_EXT_LIMITS, RB_LABEL_PRESENCE, RB_EXTENDER
 };
 
 // pod flags
@@ -71,6 +71,10 @@ struct KsbNodeTable {
   int32_t w_mr, w_rl; // MostRequestedPriority / ResourceLimitsPriority weights (0: not enabled by the Policy)
   int32_t has_static; // a Policy configured NodeLabelPriority instances: static_score holds their per-node sum
   int32_t has_presence; // ... CheckNodeLabelPresence labels: NF_LABEL_PRESENCE marks the nodes that fail it
+  // One-pod calls with scheduler-extender verdicts (core/generic_scheduler.go:333-351, :608-632), else null: the nodes
+  // the extenders' Filter calls kept (one bit per row) and the sum over extenders of weight * Prioritize score per row
+  const uint32_t* ext_keep;
+  const int32_t* ext_score;
   int32_t W;         // label words
   int32_t tw;        // 64-bit words of each taint / preferAvoid set (columns taint_hard, taint_soft, avoid hold tw words each,
                      // word w at + w * n_pad; a pod's masks for the words above 0 trail its pool block)

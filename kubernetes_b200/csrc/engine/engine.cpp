@@ -99,6 +99,8 @@ Engine::~Engine() {
   b_pre_pods.release();
   b_pre_rows.release();
   b_pre_out.release();
+  b_ext_keep.release();
+  b_ext_score.release();
   for (auto& kv : numcols) kv.second.buf.release();
   if (ev_start) cudaEventDestroy(ev_start);
   if (ev_stop) cudaEventDestroy(ev_stop);

@@ -156,6 +156,12 @@ class Engine {
   int32_t w_most_requested = 0, w_resource_limits = 0;
   void policy_set(int kind, const std::string& key, bool presence, int32_t weight);
   PreemptOutcome preempt(const Pod& p);
+  // ksb_schedule with scheduler-extender verdicts: `keep` one bit per node row (null: no Filter verdict), `scores` the
+  // extenders' weighted Prioritize sums per row (null: none)
+  void schedule_extended(const Pod& p, const uint32_t* keep, const int32_t* scores, ksb_result* out);
+  DevBuf b_ext_keep, b_ext_score;
+  const uint32_t* call_ext_keep = nullptr;  // device pointers for the call in progress
+  const int32_t* call_ext_score = nullptr;
   PreemptOutcome last_preempt;
   DevBuf b_pre_pods, b_pre_rows, b_pre_out;
   void warm_dictionaries();

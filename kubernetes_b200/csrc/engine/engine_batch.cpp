@@ -136,6 +136,8 @@ KsbBatchArgs Engine::make_args(int n_pods, bool commit) {
   KsbBatchArgs a;
   memset(&a, 0, sizeof a);
   a.table = dT;
+  a.table.ext_keep = n_pods == 1 ? call_ext_keep : nullptr;  // extender verdicts belong to one pod
+  a.table.ext_score = n_pods == 1 ? call_ext_score : nullptr;
   a.headers = (const KsbPodHeader*)b_headers.d;
   a.pool = (const uint64_t*)b_pool.d;
   a.dep = (const int32_t*)b_dep.d;
@@ -1158,7 +1160,7 @@ std::string Engine::reason_name(int bit) {
       "MatchNodeSelector", "PodToleratesNodeTaints", "NodeUnderMemoryPressure", "NodeUnderDiskPressure", "NodeNotReady",
       "NodeOutOfDisk", "NodeNetworkUnavailable", "NodeUnschedulable", "MatchInterPodAffinity",
       "ExistingPodsAntiAffinityRulesNotMatch", "PodAffinityRulesNotMatch", "PodAntiAffinityRulesNotMatch", nullptr, nullptr,
-      nullptr, nullptr, nullptr, "CheckNodeLabelPresence", nullptr, nullptr, nullptr};
+      nullptr, nullptr, nullptr, "CheckNodeLabelPresence", "extender", nullptr, nullptr};
   if (bit < 0 || bit >= KSB_REASON_BITS) throw std::runtime_error("reason bit out of range");
   if (fixed[bit]) return fixed[bit];
   if (bit >= RB_SCALAR0 && bit <= RB_SCALAR3)
@@ -1184,7 +1186,7 @@ std::string Engine::fit_error_message(int i) {
       "MatchNodeSelector", "PodToleratesNodeTaints", "NodeUnderMemoryPressure", "NodeUnderDiskPressure", "NodeNotReady",
       "NodeOutOfDisk", "NodeNetworkUnavailable", "NodeUnschedulable", "MatchInterPodAffinity",
       "ExistingPodsAntiAffinityRulesNotMatch", "PodAffinityRulesNotMatch", "PodAntiAffinityRulesNotMatch", nullptr, nullptr,
-      nullptr, nullptr, nullptr, "CheckNodeLabelPresence", nullptr, nullptr, nullptr};
+      nullptr, nullptr, nullptr, "CheckNodeLabelPresence", "extender", nullptr, nullptr};
   std::map<std::string, int> reasons;
   for (int b = 0; b < KSB_REASON_BITS; ++b) {
     if (hist[b] == 0) continue;
@@ -1206,6 +1208,45 @@ std::string Engine::fit_error_message(int i) {
   }
   msg += ".";
   return msg;
+}
+
+// Schedule with scheduler extenders (core/generic_scheduler.go:333-351, :608-632). The extenders themselves are HTTP
+// services the Go shim talks to (core/extender.go); what reaches the engine is their verdict for this pod: the rows their
+// Filter calls kept, applied after the predicates and before the fork's device selection, and the sum over extenders of
+// weight * Prioritize score per row, added to the weighted sum of the built-in priorities.
+void Engine::schedule_extended(const Pod& p, const uint32_t* keep, const int32_t* scores, ksb_result* out) {
+  if (cfg.shard_count > 1) throw std::runtime_error("ksb_schedule_extended: not available on a sharded engine");
+  {
+    std::lock_guard<std::mutex> g(mu);
+    CUDA_OK(cudaSetDevice(cfg.device));
+    if (layout_dirty) rebuild_layout();
+    if (n == 0) throw std::runtime_error("ksb_schedule_extended: no nodes");
+    const size_t words = ((size_t)n_pad + 31) / 32;
+    call_ext_keep = nullptr;
+    call_ext_score = nullptr;
+    if (keep) {
+      b_ext_keep.ensure(words * 4);
+      CUDA_OK(cudaMemcpyAsync(b_ext_keep.d, keep, (((size_t)n + 31) / 32) * 4, cudaMemcpyHostToDevice, stream));
+      call_ext_keep = (const uint32_t*)b_ext_keep.d;
+    }
+    if (scores) {
+      b_ext_score.ensure((size_t)n_pad * 4);
+      CUDA_OK(cudaMemcpyAsync(b_ext_score.d, scores, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+      call_ext_score = (const int32_t*)b_ext_score.d;
+    }
+    CUDA_OK(cudaStreamSynchronize(stream));  // the caller's arrays
+    stats.h2d_bytes += (keep ? (((size_t)n + 31) / 32) * 4 : 0) + (scores ? (size_t)n * 4 : 0);
+  }
+  std::vector<Pod> one{p};
+  try {
+    schedule_batch(one, out, false);
+  } catch (...) {
+    call_ext_keep = nullptr;
+    call_ext_score = nullptr;
+    throw;
+  }
+  call_ext_keep = nullptr;
+  call_ext_score = nullptr;
 }
 
 // genericScheduler.Preempt (core/generic_scheduler.go:199-256) for a pod whose Schedule ended in a FitError. The call

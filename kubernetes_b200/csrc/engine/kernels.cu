@@ -542,6 +542,9 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
       break;  // the reference reports the first failing rule only
     }
   }
+  // --- scheduler extenders filter after the predicates and before the fork's device selection (generic_scheduler.go:333-351)
+  if constexpr (POL)
+    if (reasons == 0 && T.ext_keep && !((T.ext_keep[r >> 5] >> (r & 31)) & 1u)) reasons |= 1u << RB_EXTENDER;  // only nodes that passed are shown to the extenders
   // --- fork: device selection runs only on nodes that passed every predicate (generic_scheduler.go:357)
   if (reasons == 0 && h->n_ext) {
     uint32_t local[KSB_MAX_EXT];
@@ -1704,9 +1707,12 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           int32_t s = INT32_MIN;
           if (live) {
             const int4 raw = A.raw[at];
-            if (raw.x != INT32_MIN)
+            if (raw.x != INT32_MIN) {
               s = final_score(T, nm, lut[g], S.zone + g * zs, S.max_zone[g], raw.x, raw.y, (int32_t)((uint32_t)raw.z >> 24),
                               (uint32_t)raw.z & 0xffffffu, raw.w, zone);
+              if constexpr (POL)
+                if (T.ext_score) s += T.ext_score[r];  // combinedScores of the extenders (generic_scheduler.go:608-632)
+            }
             if constexpr (MULTI) A.gs_score[(half + (size_t)g) * (size_t)A.gs_np + (size_t)(A.gs_row0 + r)] = s;
             else A.score[at] = s;
           }
@@ -2935,7 +2941,7 @@ extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_
   void* params[] = {(void*)args};
   // (the instantiations with the Policy plugins also carry the words above 0 of the taint / preferAvoid sets)
   const bool pol = args->table.w_mr != 0 || args->table.w_rl != 0 || args->table.has_static != 0 || args->table.has_presence != 0 ||
-                   args->table.tw > 1;
+                   args->table.tw > 1 || args->table.ext_keep != nullptr || args->table.ext_score != nullptr;
   const void* fn = batch_kernel(args->pipeline != 0, args->n_ranks > 1, pol);
   cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,
                                               smem_bytes, stream);

@@ -18,7 +18,7 @@ CABI_SYMBOLS = [
     "ksb_config_default", "ksb_create", "ksb_destroy", "ksb_last_error", "ksb_node_upsert", "ksb_node_remove",
     "ksb_pod_add", "ksb_pod_remove", "ksb_selector_owner_upsert", "ksb_selector_owner_remove", "ksb_schedule",
     "ksb_schedule_batch", "ksb_node_name", "ksb_device_id", "ksb_fit_error_message", "ksb_get_last_node_index",
-    "ksb_set_last_node_index", "ksb_failed_predicates", "ksb_scores", "ksb_resync_begin", "ksb_resync_end", "ksb_reason_name", "ksb_node_info", "ksb_flush", "ksb_deferred_errors", "ksb_policy_set", "ksb_preempt", "ksb_preempt_victim", "ksb_cache_set_ttl", "ksb_cache_assume_pod", "ksb_cache_finish_binding", "ksb_cache_forget_pod",
+    "ksb_set_last_node_index", "ksb_failed_predicates", "ksb_scores", "ksb_resync_begin", "ksb_resync_end", "ksb_reason_name", "ksb_node_info", "ksb_flush", "ksb_deferred_errors", "ksb_policy_set", "ksb_preempt", "ksb_preempt_victim", "ksb_schedule_extended", "ksb_cache_set_ttl", "ksb_cache_assume_pod", "ksb_cache_finish_binding", "ksb_cache_forget_pod",
     "ksb_cache_add_pod", "ksb_cache_update_pod", "ksb_cache_remove_pod", "ksb_cache_is_assumed_pod", "ksb_cache_cleanup_assumed",
     "ksb_cache_skip_pod_update", "ksb_get_stats", "ksb_replay_last_batch", "ksb_replay_last_batch_noalloc",
     "ksb_shard_export", "ksb_shard_connect",

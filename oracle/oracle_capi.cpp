@@ -60,6 +60,15 @@ static void apply_options(Oracle& o, const json::Value& v) {
     o.weights.most_requested = w->get_int("MostRequestedPriority", 0);
     o.weights.resource_limits = w->get_int("ResourceLimitsPriority", 0);
   }
+  // {"extender": {"keep": [node names] (optional), "scores": {node: weighted score}}}
+  if (const json::Value* ev = v.find("extender"); ev && !ev->is_null()) {
+    if (const json::Value* k = ev->find("keep"); k && !k->is_null()) {
+      o.extender.has_filter = true;
+      for (auto& x : *k->a) o.extender.keep.insert(x.s);
+    }
+    if (const json::Value* sc = ev->find("scores"); sc && sc->is_obj())
+      for (auto& kv : *sc->o) o.extender.scores[kv.first] = kv.second.i;
+  }
   // {"policy": {"nodeLabelPriorities": [{"label", "presence", "weight"}], "labelsPresence": {"labels": [...], "presence": bool}}}
   if (const json::Value* pv = v.find("policy"); pv && !pv->is_null()) {
     if (const json::Value* nl = pv->find("nodeLabelPriorities"); nl && !nl->is_null())

@@ -312,6 +312,14 @@ struct NodeLabelPriorityArg {
   bool presence = true;
   int64_t weight = 1;
 };
+// The verdict of the scheduler extenders for the pods of a run (core/extender.go; the HTTP services themselves are outside
+// this path): nodes their Filter calls kept (empty + has_filter=false: no Filter verdict) and their weighted scores.
+struct ExtenderVerdict {
+  bool has_filter = false;
+  std::set<std::string> keep;
+  std::map<std::string, int64_t> scores;  // combinedScores: sum of weight * score
+};
+
 struct Policy {
   std::vector<NodeLabelPriorityArg> node_label;
   std::vector<std::string> presence_labels;
@@ -327,6 +335,7 @@ struct Oracle {
   int hardPodAffinityWeight = 1;
   PriorityWeights weights;
   Policy policy;
+  ExtenderVerdict extender;
 
   // ---------------- predicates
 
@@ -1064,6 +1073,15 @@ struct Oracle {
       if (fits[i]) filtered.push_back(nodes[i]);
       else failedPredicateMap[nodes[i]->name] = fails[i];
     }
+    // extenders' Filter :333-351, before the fork's device selection
+    if (!filtered.empty() && extender.has_filter) {
+      std::vector<NodePtr> kept;
+      for (auto& nd : filtered) {
+        if (extender.keep.count(nd->name)) kept.push_back(nd);
+        else failedPredicateMap[nd->name].push_back("extender");
+      }
+      filtered.swap(kept);
+    }
     // GetExtendedResources (fork) :357 -> extended_resources.go:42-81
     std::map<std::string, std::map<std::string, std::vector<std::string>>> extRes;
     if (!filtered.empty() && !pod.extended.empty()) {
@@ -1167,6 +1185,9 @@ struct Oracle {
       if (weights.most_requested) (*total)[i].score += most_requested_map(pm, ni) * weights.most_requested;
       if (weights.resource_limits) (*total)[i].score += resource_limits_map(pod, ni) * weights.resource_limits;
       for (auto& a : policy.node_label) (*total)[i].score += node_label_map(a, ni) * a.weight;
+      // extenders' Prioritize :608-632
+      auto es = extender.scores.find(filtered[i]->name);
+      if (es != extender.scores.end()) (*total)[i].score += es->second;
     }
     return true;
   }
