@@ -56,7 +56,7 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   // other ranks address them inside rank 0's buffer with a layout computed from their own geometry
   L.norms = take(2 * (size_t)KSB_MAX_GROUP * sizeof(KsbNorms));
   L.zone_sum = take(2 * (size_t)KSB_MAX_GROUP * zone_stride * 4);
-  L.barrier = take(4);
+  L.barrier = take(8);
   L.error_flag = take(4);
   L.fiterr_count = take(4);
   L.last_index = take(8);
@@ -64,7 +64,7 @@ ScratchLayout scratch_layout(int n_pad, int zone_stride, int nseg, int G, int ha
   L.counters = take(128);
   L.res_slot = take(sizeof(KsbResult));  // one-pod calls: the result record, read back with the control words
   L.ghist = take(2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4);
-  L.release = take(4);
+  L.release = take(8);
   L.xbar = take(4);
   L.xstate = take(4);
   L.peers = take(sizeof(KsbPeer) * KSB_MAX_RANKS);
@@ -297,12 +297,12 @@ void Engine::launch(const KsbBatchArgs& a_in) {
     CUDA_OK(cudaMemsetAsync(a.ghist, 0, 2 * (size_t)KSB_MAX_GROUP * KSB_REASON_BITS * 4, stream));
     CUDA_OK(cudaMemsetAsync(a.group_done, 0, 32, stream));
   }
-  CUDA_OK(cudaMemsetAsync(a.barrier, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.barrier, 0, 8, stream));  // two counters: slot 1 is the barrier between phases 1 and 2
   CUDA_OK(cudaMemsetAsync(a.error_flag, 0, 4, stream));
   CUDA_OK(cudaMemsetAsync(a.fiterr_count, 0, 4, stream));
   CUDA_OK(cudaMemsetAsync(a.counters, 0, 128, stream));
   CUDA_OK(cudaMemcpyAsync(a.last_node_index, &last_node_index, 8, cudaMemcpyHostToDevice, stream));
-  CUDA_OK(cudaMemsetAsync(a.release, 0, 4, stream));
+  CUDA_OK(cudaMemsetAsync(a.release, 0, 8, stream));
   KsbPeer& self = launch_self;  // what rank 0 sees of this (only) shard: its own buffers
   if (a.n_ranks == 1) {
     CUDA_OK(cudaMemsetAsync(a.xbar, 0, 4, stream));

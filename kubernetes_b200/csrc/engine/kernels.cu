@@ -774,9 +774,9 @@ __device__ __forceinline__ void reduce_barrier_x(KsbBatchArgs& A, uint32_t& epoc
   if (threadIdx.x == 0) {
     epoch += gridDim.x;
     if (wait) __threadfence();
-    atomicAdd(A.barrier, 1u);
-    if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
-    else if (wait) spin_until<false>(A, A.release, epoch, 4);
+    atomicAdd(A.barrier + 1, 1u);
+    if (crossing) spin_until<false>(A, A.barrier + 1, epoch, 2);
+    else if (wait) spin_until<false>(A, A.release + 1, epoch, 4);
   }
   if (crossing) {
     __syncthreads();
@@ -784,10 +784,22 @@ __device__ __forceinline__ void reduce_barrier_x(KsbBatchArgs& A, uint32_t& epoc
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence();
-      atomicExch(A.release, epoch);
+      atomicExch(A.release + 1, epoch);
     }
   }
   if (threadIdx.x == 0 && wait) __threadfence();
+  __syncthreads();
+}
+
+// The same barrier on one GPU (no exchange).
+__device__ __forceinline__ void grid_barrier_b1(KsbBatchArgs& A, uint32_t& epoch, bool wait) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    if (wait) __threadfence();
+    atomicAdd(A.barrier + 1, 1u);
+    if (wait) spin_until<false>(A, A.barrier + 1, epoch, 1);
+  }
   __syncthreads();
 }
 
@@ -817,13 +829,35 @@ __device__ __forceinline__ void end_barrier_x(KsbBatchArgs& A, uint32_t& epoch, 
     } else {
       __threadfence();
     }
-    atomicAdd(A.barrier, 1u);
-    if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
-    else spin_until<false>(A, A.release, epoch, 4);
+#ifdef KSB_NO_LAST_ARRIVER
+    if (false) {
+#else
+    if (A.rank == 0) {
+#endif
+      // nothing crosses from here: a plain grid barrier in which the LAST block to arrive (as a rule the committing one)
+      // releases the others itself instead of waiting for the crossing block to notice and do it
+      const uint32_t before = atomicAdd(A.barrier, 1u);
+      if (before + 1u == epoch) {
+        __threadfence();
+        atomicExch(A.release, epoch);
+      } else {
+        spin_until<false>(A, A.release, epoch, 4);
+      }
+    } else {
+      atomicAdd(A.barrier, 1u);
+      if (crossing) spin_until<false>(A, A.barrier, epoch, 2);
+      else spin_until<false>(A, A.release, epoch, 4);
+    }
   }
+#ifdef KSB_NO_LAST_ARRIVER
   if (crossing) {
     __syncthreads();
     if (A.rank != 0) {
+#else
+  if (crossing && A.rank != 0) {
+    __syncthreads();
+    {
+#endif
       push();
       __syncthreads();
       if (threadIdx.x == 0) {
@@ -1293,6 +1327,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
   const int G = A.group_size;
   const size_t np = T.n_pad;
   uint32_t epoch = 0, xepoch = 0;
+  uint32_t epoch1 = 0;  // arrivals at the barrier between phases 1 and 2 (its own counter, see reduce_barrier_x)
   constexpr bool multi = MULTI;
   uint64_t last_index = *A.last_node_index;  // used by warp 0 of block 0 only
   int gi = 0;
@@ -1633,10 +1668,10 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           }
         }
       };
-      if constexpr (MULTI) reduce_barrier_x(A, epoch, x1, !lag, xb, exch1);
-      else grid_barrier(A, epoch, xepoch, !lag, xb);
+      if constexpr (MULTI) reduce_barrier_x(A, epoch1, x1, !lag, xb, exch1);
+      else grid_barrier_b1(A, epoch1, !lag);
     }
-    if (lag && tid == 0) s_b1_target = epoch;  // the writer warp holds its table writes until this barrier is complete
+    if (lag && tid == 0) s_b1_target = epoch1;  // the writer warp holds its table writes until this barrier is complete
     KSB_TICK(2);
 
     // ---- phase 2: Reduce + weighted sum; per-segment (max, tie count) of every pod
@@ -2708,7 +2743,9 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
           __threadfence_block();
           const CommitRec& rec = S.recs[g];
           const KsbPodHeader* h = S.hdr + g;
-          if (lane < R) PEER(lane).results[p0 + g] = rec.res;  // every rank keeps a copy of the results
+          // (sharded: this warp writes rank 0's copies only; the other ranks' are written by all warps once the group is
+          //  decided, below, off this warp's serial path)
+          if (lane == 0) PEER(0).results[p0 + g] = rec.res;
           if (rec.row >= 0) {
             // Pipelined: the other blocks may be reading the table for the next group while these rows are written.
             // That is harmless: every row written here stays in the row cache for that group (the carried rows), so
@@ -2717,7 +2754,7 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             // columns the evaluation happened to read: requests only grow, so a mix fits whenever the new row does.
             // (kHoldTableWrites keeps the conservative schedule: no write before every block has read the table.)
             if (kHoldTableWrites && pipe && !table_open) {
-              if (lane == 0) spin_until<false>(A, A.barrier, s_b1_target, 7);
+              if (lane == 0) spin_until<false>(A, A.barrier + 1, s_b1_target, 7);
               __syncwarp();
               table_open = true;
             }
@@ -2728,39 +2765,71 @@ __global__ void __launch_bounds__(kThreads) ksb_schedule_batch_kernel(KsbBatchAr
             // sharded: rank 0 holds every row (phase 3 works on that copy); the rank that evaluates the row gets the
             // same columns over NVLink so that its next evaluation sees them
             const int own = MULTI ? min(R - 1, (chosen / kSeg) / sps) : 0;
-            if (MULTI && own != 0) write_through(PEER(own).table, rec, chosen - own * sps * kSeg, h, lane);
             // the class counters a bind bumps (SelectorSpread column entries, inter-pod-affinity table slots): no pod
             // of this group reads them. SelectorSpread columns are sharded with the rows; affinity tables are
             // replicated on every rank.
             const size_t pn = P.table.n_pad;
             for (int i = lane; i < h->n_spread_inc; i += 32) {
               atomicAdd(P.table.spread + (size_t)pv.spread_inc[i] * pn + chosen, 1u);
-              if (MULTI && own != 0) {
-                const KsbPeer& O = PEER(own);
-                atomicAdd_system(O.table.spread + (size_t)pv.spread_inc[i] * O.table.n_pad + (chosen - own * sps * kSeg), 1u);
-              }
             }
             for (int i = lane; i < h->n_commit; i += 32) {
               const uint64_t cm = pv.commits[2 * i];
               const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
               const uint32_t off = (uint32_t)cm;
               const uint32_t d = P.table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
-              for (int q = 0; q < R; ++q) {
-                int32_t* tb = PEER(q).table.tables;
-                if (q == 0) {
-                  if (d) atomicAdd(tb + off + d, delta);
-                  if ((cm >> 40) & 1ull) atomicAdd(tb + off, delta);  // slot 0: total matching pods anywhere
-                } else {
-                  if (d) atomicAdd_system(tb + off + d, delta);
-                  if ((cm >> 40) & 1ull) atomicAdd_system(tb + off, delta);
-                }
-              }
+              int32_t* tb = PEER(0).table.tables;
+              if (d) atomicAdd(tb + off + d, delta);
+              if ((cm >> 40) & 1ull) atomicAdd(tb + off, delta);  // slot 0: total matching pods anywhere
             }
           }
           __syncwarp();
         }
       }
 #undef KSB_BAR3
+      if constexpr (MULTI) {
+        // Sharded: what the other ranks keep of this group's commits, written by all warps at once, a pod per warp:
+        // the result record on every rank, the committed row's columns and SelectorSpread counters on the rank that
+        // evaluates the row, the affinity-table counters on every rank. Of several pods of the group on one row the warp
+        // of the last one writes the row (all of them, in order).
+        __syncthreads();
+        const int decided = s_consumed;
+        for (int g = warp; g < decided; g += kWarps) {
+          const CommitRec& rec = S.recs[g];
+          const KsbPodHeader* h = S.hdr + g;
+          if (lane >= 1 && lane < R) PEER(lane).results[p0 + g] = rec.res;
+          if (rec.row < 0) continue;
+          const PodView pv = make_view(h, S.pool + S.pool_off[g], T.W);
+          const int chosen = rec.row;
+          const int own = min(R - 1, (chosen / kSeg) / sps);
+          if (own != 0) {
+            bool later = false;
+            for (int g2 = g + 1; g2 < decided; ++g2) later = later || S.recs[g2].row == chosen;
+            const KsbPeer& O = PEER(own);
+            const int orow = chosen - own * sps * kSeg;
+            if (!later) {
+              // write_through stores only the columns its own pod touched (ports, scalars, devices), so the earlier
+              // pods of the group on this row are replayed first, in order, by this warp
+              for (int g1 = 0; g1 < g; ++g1)
+                if (S.recs[g1].row == chosen) write_through(O.table, S.recs[g1], orow, S.hdr + g1, lane);
+              write_through(O.table, rec, orow, h, lane);
+            }
+            for (int i = lane; i < h->n_spread_inc; i += 32)
+              atomicAdd_system(O.table.spread + (size_t)pv.spread_inc[i] * O.table.n_pad + orow, 1u);
+          }
+          const size_t pn = PEER(0).table.n_pad;
+          for (int i = lane; i < h->n_commit; i += 32) {
+            const uint64_t cm = pv.commits[2 * i];
+            const int32_t delta = (int32_t)(int64_t)pv.commits[2 * i + 1];
+            const uint32_t off = (uint32_t)cm;
+            const uint32_t d = PEER(0).table.topo[((uint32_t)(cm >> 32) & 0xffu) * pn + chosen];
+            for (int q = 1; q < R; ++q) {
+              int32_t* tb = PEER(q).table.tables;
+              if (d) atomicAdd_system(tb + off + d, delta);
+              if ((cm >> 40) & 1ull) atomicAdd_system(tb + off, delta);
+            }
+          }
+        }
+      }
 #if KSB_FINE_TIMING == 1
       const long long drain0 = clock64();
 #endif

@@ -46,7 +46,7 @@ struct KsbBatchArgs {
   int32_t* seg_max;             // [group_size][nseg]
   int32_t* seg_cnt;             // [group_size][nseg]
   uint32_t* seg_mask;           // [group_size][nseg][8] rows of the segment that hold its maximum, one bit per row
-  uint32_t* barrier;            // grid barrier counter, zero at launch
+  uint32_t* barrier;            // [2] grid barrier counters, zero at launch: [1] counts the barrier between phases 1 and 2, [0] all others
   int32_t* error_flag;
   int32_t* fiterr_count;
   int32_t* fiterr_hist;         // [fiterr_cap][KSB_REASON_BITS] reason histograms of the launch's no-fit pods
@@ -96,7 +96,7 @@ struct KsbBatchArgs {
   uint32_t xo_norms;            // uint64_t [2][KSB_MAX_RANKS][KSB_MAX_GROUP * 8]: {value, exchange number} words
   uint32_t xo_zone;             // uint64_t [2][KSB_MAX_RANKS][KSB_MAX_GROUP][zone_stride]
   uint32_t xo_gdone;            // int32_t [8]: the rank's copy of group_done (rank 0 pushes words 0..1)
-  uint32_t* release;            // local: epoch up to which this GPU's blocks may proceed
+  uint32_t* release;            // local [2]: per counter, the arrival count up to which this GPU's blocks may proceed
   uint32_t* xstate;             // local [3]: the cross-GPU arrival numbers carried from launch to launch (the flags are never reset)
   int32_t n_ranks, rank;
   int32_t segs_per_shard;       // segments per shard (the last shard may hold fewer)
