@@ -3108,7 +3108,7 @@ constexpr size_t kNaFitCount = kNaError + 256;
 constexpr size_t kNaLastIndex = kNaFitCount + 256;
 constexpr size_t kNaGroupDone = kNaLastIndex + 256;
 constexpr size_t kNaCounters = kNaGroupDone + 256;
-constexpr size_t kNaRelease = kNaCounters + 256;  // counters: 15 x 8 bytes
+constexpr size_t kNaRelease = kNaCounters + 256;  // counters: 16 x 8 bytes
 constexpr size_t kNaXbar = kNaRelease + 256;
 constexpr size_t kNaXstate = kNaXbar + 256;
 constexpr size_t kNaPeer = kNaXstate + 256;
