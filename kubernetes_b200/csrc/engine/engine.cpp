@@ -133,9 +133,14 @@ int Engine::label_bit(char kind, const std::string& key, const std::string& valu
   will_mutate();
   int bit = (int)label_defs.size();
   if (bit >= W * 64) {
-    if (W >= 16 || (cfg.shard_count > 1 && shard_connected))
-      throw std::runtime_error("label universe exceeds label_words*64 bits (1,024 at most; a sharded engine keeps the width it was connected with)");
-    pending_W = std::min(16, W * 2);
+    if (cfg.shard_count > 1 && shard_connected)
+      throw std::runtime_error("label universe exceeds label_words*64 bits (a sharded engine keeps the width it was connected with)");
+    // Nothing outside the pod being encoded refers to a label bit by number (encoded pods are not kept across a
+    // rebuild), so a full universe at the widest columns starts afresh instead of failing every later pod that
+    // mentions a new pair: a long-running scheduler sees many selector values come and go. Only a single call that
+    // itself needs more than 1,024 distinct pairs cannot be served (schedule_batch gives up after three rounds).
+    if (W >= 16) label_reset_pending = true;
+    else pending_W = std::min(16, W * 2);
     throw GrowLabels();
   }
   LabelBitDef d;
@@ -983,6 +988,22 @@ void Engine::rebuild_layout() {
   n = (int)rows.size();
   n_pad = std::max(256, (n + 255) & ~255);
   if (pending_W > W) W = pending_W;  // wider label columns (GrowLabels)
+  if (label_reset_pending) {
+    label_defs.clear();
+    label_bits.clear();
+    label_reset_pending = false;
+  }
+  // The taint and preferAvoid dictionaries follow the nodes that exist now: entries of nodes long gone do not pile up
+  // (every row is recomputed below, and encoded pods do not outlive a rebuild).
+  if (!(cfg.shard_count > 1 && shard_connected)) {  // (shared buffers keep the layout they were connected with)
+    hard_taints.clear();
+    soft_taints.clear();
+    hard_taint_idx.clear();
+    soft_taint_idx.clear();
+    avoid_idx.clear();
+    TW = 1;
+    pending_TW = 1;
+  }
   for (;;) {
     TW = std::max(TW, pending_TW);  // a taint / preferAvoid set outgrew its words: wider columns from here on
     h_i64.assign((size_t)I64_COLS * n_pad, 0);

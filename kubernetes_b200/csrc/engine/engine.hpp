@@ -190,6 +190,7 @@ class Engine {
   // ---- dictionaries
   int W;  // label words (64 bits each); grows by doubling, up to 16, when a selector mentions more distinct pairs
   int pending_W = 0;
+  bool label_reset_pending = false;  // the universe is full at 16 words: the next rebuild starts the label dictionary afresh
   size_t batch_posted = 0;  // pods of the running batch already committed and mirrored (chunked batches)
   std::unordered_map<std::string, int> label_bits;  // "P\0k\0v" | "K\0k" | "G\0k\0n" | "L\0k\0n" -> bit
   struct LabelBitDef {

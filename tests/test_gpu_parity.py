@@ -331,3 +331,28 @@ def test_label_universe_grows_past_256_pairs():
             for j in range(2)]}, {"matchExpressions": [{"key": "grp%02d" % ((5 * i) % 45), "op": "Exists", "values": []}]}]}}
     compare(cluster, "wide labels")
     compare(cluster, "wide labels single", gpu_opts={"batch": 0, "limit": 300}, oracle_opts={"limit": 300})
+
+
+def test_label_dictionary_starts_afresh_when_full():
+    """Selectors that mention more than 1,024 distinct pairs over time (never in one call): at 16 label words the
+    dictionary is rebuilt from what the current call needs instead of failing; results stay those of the oracle."""
+    cluster = workloads.generate(1, 120, 0)
+    for i, n in enumerate(cluster["nodes"]):
+        for k in range(40):
+            n["labels"]["k%03d" % ((i * 7 + k * 13) % 300)] = "v%d" % ((i + k) % 8)
+    pods = []
+    for b in range(5):  # five batches, each mentioning about 480 pairs of its own key range
+        for i in range(60):
+            p = {"name": "p-%d-%d" % (b, i), "namespace": "default", "containers": [{"requests": {"cpu": 100, "memory": 1 << 27}}]}
+            p["affinity"] = {"node": {"required": [{"matchExpressions": [
+                {"key": "k%03d" % (60 * b + (i + j) % 60), "op": "In", "values": ["v%d" % ((i + j + v) % 8) for v in range(4)]}
+                for j in range(2)]}]}}
+            pods.append(p)
+    cluster["pods"] = pods
+    want = oracle_lib.call({"op": "stream", "cluster": cluster})
+    sess = lib.Session(cluster=cluster)
+    got = sess.run(batch=60)
+    sess.close()
+    for i, (g, w) in enumerate(zip(got["results"], want["results"])):
+        assert (g["status"], g["host"], g["filtered"]) == (w["status"], w["host"], w["filtered"]), (i, g, w)
+    assert sum(1 for r in want["results"] if r["status"] == 0) > 100
