@@ -68,3 +68,39 @@ def test_generator_is_deterministic_and_shaped():
     assert all(len(n["extendedResources"]["nvidia.com/gpu"]) == 16 for n in c["nodes"])
     d = workloads.generate(1, 12, 5, padded=False)
     assert d["nodes"][10]["name"] == "node-10"
+
+
+def test_go_shim_binds_only_declared_symbols():
+    """integration/gpusched/*.go cannot be compiled here (no Go toolchain): at least every C symbol, constant and type the
+    shim names must exist in include/ksched_b200.h, and the Go encoders must write the records field for field as
+    kubernetes_b200/wire.py does (same sequence of writer calls per record kind)."""
+    header = open(os.path.join(ROOT, "include", "ksched_b200.h")).read()
+    declared = set(re.findall(r"\b(ksb_[a-z_0-9]+)\b", header)) | set(re.findall(r"\b(KSB_[A-Z_0-9]+)\b", header))
+    gdir = os.path.join(ROOT, "integration", "gpusched")
+    used = set()
+    for fn in sorted(os.listdir(gdir)):
+        if fn.endswith(".go"):
+            used |= set(re.findall(r"\bC\.((?:ksb|KSB)_[A-Za-z_0-9]+)\b", open(os.path.join(gdir, fn)).read()))
+    assert used, "the shim binds nothing?"
+    assert used <= declared, sorted(used - declared)
+    # the shim covers the path's entry points
+    for name in ("ksb_create", "ksb_schedule", "ksb_schedule_extended", "ksb_preempt", "ksb_node_upsert", "ksb_node_remove",
+                 "ksb_pod_add", "ksb_pod_remove", "ksb_selector_owner_upsert", "ksb_failed_predicates", "ksb_resync_begin",
+                 "ksb_policy_set"):
+        assert name in used, name
+
+
+def test_go_and_python_pod_encoders_agree_on_field_order():
+    """Both writers are sequences of u8 / u32 / i32 / i64 / str / map calls: the pod record's tail (extended resources,
+    volume count, priority) and the node record's head are compared by the order of the field names they mention."""
+    go = open(os.path.join(ROOT, "integration", "gpusched", "encode.go")).read()
+    py = open(os.path.join(ROOT, "kubernetes_b200", "wire.py")).read()
+    go_pod = go[go.index("func encodePod"):go.index("// selector owners for SelectorSpread")]
+    py_pod = py[py.index("def pod_record"):]
+    order_go = [go_pod.index(k) for k in ("p.Namespace", "p.Name", "p.Labels", "DeletionTimestamp", "NodeName", "Containers",
+                                          "InitContainers", "NodeSelector", "Tolerations", "ExtendedResources", "Volumes", "prio")]
+    assert order_go == sorted(order_go), order_go
+    order_py = [py_pod.index(k) for k in ('"namespace"', '"name"', '"labels"', '"deleting"', '"nodeName"', '"controller"',
+                                          '"containers"', '"nodeSelector"', '"tolerations"', '"extendedResources"', '"volumes"',
+                                          '"priority"')]
+    assert order_py == sorted(order_py), order_py
