@@ -8,7 +8,8 @@
 //   str name; u8 has_labels; map labels; reslist allocatable;
 //   list<taint: str key, str value, str effect>; list<condition: str type, str status>;
 //   u8 unschedulable; u8 avoid_annotation_invalid; list<avoid: str kind, str uid>;
-//   list<resource: str name; list<device: str id, str health, map attributes>>
+//   list<resource: str name; list<device: str id, str health, map attributes>>;
+//   list<image: list<str name>, i64 size_bytes>   (Status.Images; read by ImageLocalityPriority only)
 //
 // Pod record (v1.Pod fields the path reads):
 //   str namespace; str name; map labels; u8 deleting; str node_name;
@@ -24,6 +25,7 @@
 //   list<extended: str name; reslist limits; list<req>; list<str assigned>>;
 //   i32 num_volumes
 //   i32 priority   (util.GetPodPriority: *Spec.Priority, 0 when unset; read by preemption only)
+//   list<str image>   (Spec.Containers[i].Image in container order; read by ImageLocalityPriority only)
 //   req = str key; str op; list<str value>
 //
 // SelectorOwner record: str namespace; str name; map map_selector; u8 selector_present; map match_labels; list<req>
@@ -188,6 +190,11 @@ inline void put(Writer& w, const Node& n) {
       w.map(d.attributes);
     }
   }
+  w.u32((uint32_t)n.images.size());
+  for (auto& im : n.images) {
+    w.strs(im.names);
+    w.i64(im.size_bytes);
+  }
 }
 
 inline Node get_node(Reader& r) {
@@ -233,6 +240,13 @@ inline Node get_node(Reader& r) {
       devs.push_back(std::move(d));
     }
     n.extended[rname] = std::move(devs);
+  }
+  uint32_t ni = r.u32();
+  for (uint32_t i = 0; i < ni; ++i) {
+    NodeImage im;
+    im.names = r.strs();
+    im.size_bytes = r.i64();
+    n.images.push_back(std::move(im));
   }
   return n;
 }
@@ -346,6 +360,7 @@ inline void put(Writer& w, const Pod& p) {
   }
   w.i32(p.num_volumes);
   w.i32(p.priority);
+  w.strs(p.images);
 }
 
 inline Pod get_pod(Reader& r) {
@@ -401,6 +416,7 @@ inline Pod get_pod(Reader& r) {
   }
   p.num_volumes = r.i32();
   p.priority = r.i32();
+  p.images = r.strs();
   return p;
 }
 

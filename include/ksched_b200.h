@@ -121,14 +121,17 @@ int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, s
  *   KSB_POLICY_MOST_REQUESTED       MostRequestedPriority (priorities/most_requested.go:32-88) with `weight`
  *   KSB_POLICY_RESOURCE_LIMITS      ResourceLimitsPriority (priorities/resource_limits.go:34-126) with `weight`
  *   KSB_POLICY_CLEAR                back to the DefaultProvider set
- * The other Policy-only plugins (ImageLocalityPriority, ServiceSpreadingPriority / ServiceAntiAffinity, the ServiceAffinity
- * predicate) are not implemented: a factory that is asked for them must refuse, as gpusched.New does for unknown keys. */
+ *   KSB_POLICY_IMAGE_LOCALITY       ImageLocalityPriority (priorities/image_locality.go:32-82) with `weight`: reads the
+ *                                   image lists at the end of the node and pod records (ksb_wire.hpp)
+ * The other Policy-only plugins (ServiceSpreadingPriority / ServiceAntiAffinity, the ServiceAffinity predicate) are not
+ * implemented: a factory that is asked for them must refuse, as gpusched.New does for unknown keys. */
 enum {
   KSB_POLICY_NODE_LABEL_PRIORITY = 0,
   KSB_POLICY_LABEL_PRESENCE = 1,
   KSB_POLICY_MOST_REQUESTED = 2,
   KSB_POLICY_RESOURCE_LIMITS = 3,
-  KSB_POLICY_CLEAR = 4
+  KSB_POLICY_CLEAR = 4,
+  KSB_POLICY_IMAGE_LOCALITY = 5
 };
 int32_t ksb_policy_set(ksb_engine* e, int32_t kind, const char* key, size_t key_len, int32_t presence, int32_t weight);
 

@@ -160,6 +160,11 @@ func encodeNode(n *v1.Node) []byte {
 			w.strMap(d.Attributes)
 		}
 	}
+	w.u32(uint32(len(n.Status.Images))) // priorities/image_locality.go:66-73
+	for _, im := range n.Status.Images {
+		w.strs(im.Names)
+		w.i64(im.SizeBytes)
+	}
 	return w.b
 }
 
@@ -285,6 +290,10 @@ func encodePod(p *v1.Pod) []byte {
 		prio = *p.Spec.Priority
 	}
 	w.i32(prio)
+	w.u32(uint32(len(p.Spec.Containers))) // priorities/image_locality.go:75-80
+	for i := range p.Spec.Containers {
+		w.str(p.Spec.Containers[i].Image)
+	}
 	return w.b
 }
 

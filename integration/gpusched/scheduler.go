@@ -49,6 +49,7 @@ var weightField = map[string]func(*C.ksb_config, C.int32_t){
 var policyWeightKind = map[string]C.int32_t{
 	"MostRequestedPriority":  C.KSB_POLICY_MOST_REQUESTED,
 	"ResourceLimitsPriority": C.KSB_POLICY_RESOURCE_LIMITS,
+	"ImageLocalityPriority":  C.KSB_POLICY_IMAGE_LOCALITY,
 }
 
 // GPUScheduler implements algorithm.ScheduleAlgorithm.

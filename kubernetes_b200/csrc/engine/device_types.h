@@ -69,6 +69,7 @@ struct KsbNodeTable {
   int32_t row_base;  // global row of local row 0
   int32_t n_total;   // rows over all shards
   int32_t w_mr, w_rl; // MostRequestedPriority / ResourceLimitsPriority weights (0: not enabled by the Policy)
+  int32_t w_il;       // ImageLocalityPriority weight (0: not enabled); its per-node scores are columns of `spread`
   int32_t has_static; // a Policy configured NodeLabelPriority instances: static_score holds their per-node sum
   int32_t has_presence; // ... CheckNodeLabelPresence labels: NF_LABEL_PRESENCE marks the nodes that fail it
   // One-pod calls with scheduler-extender verdicts (core/generic_scheduler.go:333-351, :608-632), else null: the nodes
@@ -130,7 +131,8 @@ struct __attribute__((aligned(16))) KsbPodHeader {
   uint8_t scalar_mask;  // bit s: scalar slot s is in podRequest.ScalarResources
   uint8_t n_exprs, n_req_terms, n_pref, n_ext, n_checks, n_score, n_commit, n_spread_inc;
   uint8_t ext_err_entry;
-  uint8_t pad[6];
+  int16_t img_col;  // ImageLocalityPriority: column of `spread` holding this image set's score per node, -1 none
+  uint8_t pad[4];
   uint8_t expr_wm[KSB_MAX_EXPRS];  // per expression: which of the first four label words its mask touches (bit w = word w)
 };
 

@@ -395,7 +395,7 @@ bool Engine::sig_matches_spread(SigInfo* s, int c) {
     will_mutate();
     const SpreadClass& sc = spread_classes[c];
     bool m = false;
-    if (sc.ns == s->ns)
+    if (!sc.image_class && sc.ns == s->ns)
       for (auto& selx : sc.selectors)
         if (sel::matches(selx, s->labels)) {
           m = true;
@@ -542,6 +542,57 @@ int Engine::spread_class_of(const Pod& p, SigInfo* s) {
     dirty_spread_cols.insert(id);
   }
   s->spread_class = id;
+  return id;
+}
+
+// priorities/image_locality.go:32-82: total size of the listed images present on the node, bucketed into 0..10
+uint32_t Engine::image_score(const HostNode& hn, const std::vector<std::string>& images) const {
+  constexpr int64_t mb = 1024 * 1024, min_size = 23 * mb, max_size = 1000 * mb;  // balanced_resource_allocation.go:32-36
+  int64_t total = 0;
+  for (auto& want : images) {
+    int64_t size = 0;
+    bool have = false;
+    for (auto& im : hn.node.images)  // totalImageSize :66-82: a later entry carrying the same name replaces an earlier one
+      for (auto& name : im.names)
+        if (name == want) {
+          size = im.size_bytes;
+          have = true;
+        }
+    if (have) total += size;
+  }
+  if (total == 0 || total < min_size) return 0;
+  if (total >= max_size) return 10;
+  return (uint32_t)(10 * (total - min_size) / (max_size - min_size) + 1);
+}
+
+void Engine::fill_image_scores(int row) {
+  for (size_t c = 0; c < spread_classes.size(); ++c)
+    if (spread_classes[c].image_class) h_spread[c][row] = image_score(*rows[row], spread_classes[c].images);
+}
+
+// The score column of a pod's container image list (one per distinct list, created on first use)
+int Engine::image_class_of(const Pod& p) {
+  if (p.images.empty()) return -1;
+  std::string key = "\x07img";
+  for (auto& im : p.images) {
+    key.push_back('\x06');
+    key += im;
+  }
+  auto it = spread_idx.find(key);
+  if (it != spread_idx.end()) return it->second;
+  will_mutate();
+  int id = (int)spread_classes.size();
+  if (id >= 32767) throw std::runtime_error("more than 32,767 SelectorSpread / ImageLocality classes");
+  SpreadClass sc;
+  sc.image_class = true;
+  sc.images = p.images;
+  spread_classes.push_back(std::move(sc));
+  spread_idx[key] = id;
+  h_spread.emplace_back((size_t)n_pad, 0u);
+  if (!layout_dirty) {
+    for (int r = 0; r < n; ++r) h_spread[id][r] = image_score(*rows[r], spread_classes[id].images);
+    dirty_spread_cols.insert(id);
+  }
   return id;
 }
 
@@ -832,7 +883,10 @@ void Engine::policy_set(int kind, const std::string& key, bool presence, int32_t
       pol_node_label.clear();
       pol_presence_labels.clear();
       pol_presence = true;
-      w_most_requested = w_resource_limits = 0;
+      w_most_requested = w_resource_limits = w_image_locality = 0;
+      break;
+    case 5:
+      w_image_locality = weight;
       break;
     default:
       throw std::runtime_error("unknown policy plugin kind");
@@ -916,6 +970,7 @@ void Engine::fill_row(int row) {
       if ((exists && a.presence) || (!exists && !a.presence)) sscore += 10 * a.weight;
     }
     u32(U32_STATIC, row) = (uint32_t)sscore;
+    fill_image_scores(row);
     for (auto& l : pol_presence_labels) {
       const bool exists = nd.has_labels && nd.labels.count(l) != 0;
       if ((exists && !pol_presence) || (!exists && pol_presence)) {
@@ -1039,6 +1094,7 @@ void Engine::rebuild_layout() {
     commit_lists(p, sig_of(p), &commits, &inc);
     apply_class_part_host(nit->second.row, commits, inc, +1);
   }
+  for (int r = 0; r < n; ++r) fill_image_scores(r);  // (zeroed with the SelectorSpread counters above)
   dirty_rows.clear();
   dirty_label_words.clear();
   dirty_topo_cols.clear();

@@ -86,6 +86,10 @@ struct Table {
 struct SpreadClass {
   std::string ns;
   std::vector<sel::Selector> selectors;
+  // An ImageLocalityPriority class shares the column store: its column holds the 0..10 score of this list of container
+  // images on every node (priorities/image_locality.go:32-82), no pod ever matches it and no commit touches it.
+  bool image_class = false;
+  std::vector<std::string> images;
 };
 
 // Thrown by the dictionaries when a lookup would have to intern something new while the calling thread runs in
@@ -153,7 +157,10 @@ class Engine {
   std::vector<NodeLabelPrio> pol_node_label;
   std::vector<std::string> pol_presence_labels;
   bool pol_presence = true;
-  int32_t w_most_requested = 0, w_resource_limits = 0;
+  int32_t w_most_requested = 0, w_resource_limits = 0, w_image_locality = 0;
+  int image_class_of(const Pod& p);
+  uint32_t image_score(const HostNode& hn, const std::vector<std::string>& images) const;
+  void fill_image_scores(int row);
   void policy_set(int kind, const std::string& key, bool presence, int32_t weight);
   PreemptOutcome preempt(const Pod& p);
   // ksb_schedule with scheduler-extender verdicts: `keep` one bit per node row (null: no Filter verdict), `scores` the

@@ -416,6 +416,7 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
   }
   // --- SelectorSpread class (selector_spreading.go:64-113)
   h.spread_col = spread_class_of(p, sig);
+  h.img_col = w_image_locality ? (int16_t)image_class_of(p) : (int16_t)-1;
 
   // --- inter-pod affinity: checks (predicates.go:1238-1346) and score terms (interpod_affinity.go:121-216)
   std::vector<uint64_t> checks, score;
@@ -579,6 +580,7 @@ void Engine::setup_table_pointers() {
   T.w_lr = cfg.w_least_requested;
   T.w_mr = w_most_requested;
   T.w_rl = w_resource_limits;
+  T.w_il = w_image_locality;
   T.has_static = pol_node_label.empty() ? 0 : 1;
   T.has_presence = pol_presence_labels.empty() ? 0 : 1;
   T.w_bra = cfg.w_balanced;

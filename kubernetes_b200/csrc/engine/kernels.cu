@@ -414,7 +414,9 @@ __device__ __noinline__ int32_t policy_score_enabled(int32_t w_mr, int32_t w_rl,
   return s;
 }
 __device__ __forceinline__ int32_t policy_score(const KsbNodeTable& T, const KsbPodHeader* h, int64_t cpu, int64_t mem, int64_t acpu,
-                                                int64_t amem, int32_t static_score) {
+                                                int64_t amem, int32_t static_score, int r) {
+  // ImageLocalityPriority (image_locality.go:32-62): the host keeps the 0..10 score of the pod's image list per node
+  if (T.w_il && h->img_col >= 0) static_score += T.w_il * (int32_t)T.spread[(size_t)h->img_col * T.n_pad + r];
   if ((T.w_mr | T.w_rl) == 0) return static_score;
   return static_score + policy_score_enabled(T.w_mr, T.w_rl, h->lim_cpu, h->lim_mem, cpu, mem, acpu, amem);
 }
@@ -564,7 +566,7 @@ __device__ __forceinline__ void eval_node(const KsbNodeTable& T, int r, const Ro
   // (the node's NodeLabelPriority sum is read here, and only when a Policy configured an instance: carried with the
   //  row's common columns it cost every evaluation a register)
   o.base = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
-  if constexpr (POL) o.base += policy_score(T, h, cpu, mem, acpu, amem, T.has_static ? T.static_score[r] : 0);
+  if constexpr (POL) o.base += policy_score(T, h, cpu, mem, acpu, amem, T.has_static ? T.static_score[r] : 0, r);
   o.na = na;
   o.tt = tt;
   o.sc = h->spread_col >= 0 ? ldx<CG>(T.spread + (size_t)h->spread_col * np + r) : 0u;  // selector_spreading.go:64-113
@@ -1061,7 +1063,7 @@ __device__ __forceinline__ void eval_cached(const KsbNodeTable& T, RowCache& c, 
     for (int w = 0; w < T.tw - 1; ++w) avoid_hit |= T.avoid[(size_t)(w + 1) * T.n_pad + c.row] & pv.tw_ext[2 * (T.tw - 1) + w];
   const int32_t av = avoid_hit ? 0 : 10;
   *base_out = T.w_lr * lr + T.w_bra * bra + T.w_avoid * av;
-  if constexpr (POL) *base_out += policy_score(T, h, cpu, mem, acpu, amem, c.sscore);
+  if constexpr (POL) *base_out += policy_score(T, h, cpu, mem, acpu, amem, c.sscore, c.row);
 }
 
 // One warp: load row r's mutable columns into a cache entry (one round of independent L2 loads). In two steps, so
@@ -3009,7 +3011,7 @@ static const void* batch_kernel(bool pipe, bool multi, bool pol) {
 extern "C" int ksb_launch_batch(const KsbBatchArgs* args, int grid, size_t smem_bytes, cudaStream_t stream) {
   void* params[] = {(void*)args};
   // (the instantiations with the Policy plugins also carry the words above 0 of the taint / preferAvoid sets)
-  const bool pol = args->table.w_mr != 0 || args->table.w_rl != 0 || args->table.has_static != 0 || args->table.has_presence != 0 ||
+  const bool pol = args->table.w_mr != 0 || args->table.w_rl != 0 || args->table.w_il != 0 || args->table.has_static != 0 || args->table.has_presence != 0 ||
                    args->table.tw > 1 || args->table.ext_keep != nullptr || args->table.ext_score != nullptr;
   const void* fn = batch_kernel(args->pipeline != 0, args->n_ranks > 1, pol);
   cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kThreads), params,

@@ -76,7 +76,7 @@ ksb_config config_from(const json::Value& opt) {
 
 std::string run_on(EngineHandle& h, Session& s, const json::Value& opt, double load_ms);
 
-// Policy-enabled plugins from the options: {"weights": {"MostRequestedPriority": w, "ResourceLimitsPriority": w},
+// Policy-enabled plugins from the options: {"weights": {"MostRequestedPriority": w, "ResourceLimitsPriority": w, "ImageLocalityPriority": w},
 // "policy": {"nodeLabelPriorities": [{"label", "presence", "weight"}], "labelsPresence": {"labels": [...], "presence": b}}}
 void apply_policy(EngineHandle& h, const json::Value& opt) {
   if (const json::Value* w = opt.find("weights"); w && !w->is_null()) {
@@ -84,6 +84,8 @@ void apply_policy(EngineHandle& h, const json::Value& opt) {
       h.check(ksb_policy_set(h.get(), KSB_POLICY_MOST_REQUESTED, nullptr, 0, 0, (int32_t)w->get_int("MostRequestedPriority", 0)), "policy");
     if (w->get_int("ResourceLimitsPriority", 0) != 0)
       h.check(ksb_policy_set(h.get(), KSB_POLICY_RESOURCE_LIMITS, nullptr, 0, 0, (int32_t)w->get_int("ResourceLimitsPriority", 0)), "policy");
+    if (w->get_int("ImageLocalityPriority", 0) != 0)
+      h.check(ksb_policy_set(h.get(), KSB_POLICY_IMAGE_LOCALITY, nullptr, 0, 0, (int32_t)w->get_int("ImageLocalityPriority", 0)), "policy");
   }
   if (const json::Value* pv = opt.find("policy"); pv && !pv->is_null()) {
     if (pv->has("nodeLabelPriorities"))

@@ -132,6 +132,7 @@ struct Pod {
   std::vector<PodExtendedResource> extended;
   int32_t num_volumes = 0;
   int32_t priority = 0;  // util.GetPodPriority (plugin/pkg/scheduler/util/utils.go:76-87): *Spec.Priority, 0 when unset
+  std::vector<std::string> images;  // Spec.Containers[i].Image in order (priorities/image_locality.go:66-80)
   std::string key() const { return ns + "/" + name; }
 };
 
@@ -149,6 +150,11 @@ struct AvoidEntry {
   std::string kind, uid;
 };
 
+struct NodeImage {  // v1.ContainerImage
+  std::vector<std::string> names;
+  int64_t size_bytes = 0;
+};
+
 struct Node {
   std::string name;
   bool has_labels = true;  // false: Labels == nil (matters for topology helpers)
@@ -161,6 +167,7 @@ struct Node {
   bool avoid_annotation_invalid = false;
   // resource name -> devices
   std::map<std::string, std::vector<ExtendedDevice>> extended;
+  std::vector<NodeImage> images;  // Status.Images (read by ImageLocalityPriority only)
 };
 
 struct SelectorOwner {  // Service / ReplicationController (map selector) or RS / StatefulSet (LabelSelector)
@@ -272,7 +279,10 @@ inline Pod pod_from_json(const json::Value& v) {
     p.controller.kind = o->get_str("kind");
     p.controller.uid = o->get_str("uid");
   }
-  for (auto& c : v.get_arr("containers")) p.containers.push_back(container(c));
+  for (auto& c : v.get_arr("containers")) {
+    p.containers.push_back(container(c));
+    p.images.push_back(c.get_str("image"));
+  }
   for (auto& c : v.get_arr("initContainers")) p.init_containers.push_back(container(c));
   p.node_selector = strmap(v.find("nodeSelector"));
   if (const json::Value* a = v.find("affinity"); a && !a->is_null()) {
@@ -359,6 +369,12 @@ inline Node node_from_json(const json::Value& v) {
       }
       n.extended[kv.first] = std::move(devs);
     }
+  }
+  for (auto& im : v.get_arr("images")) {
+    NodeImage x;
+    x.names = strlist(im.find("names"));
+    x.size_bytes = im.get_int("sizeBytes");
+    n.images.push_back(std::move(x));
   }
   return n;
 }

@@ -87,6 +87,11 @@ def node_record(n):
             w.s(d["id"])
             w.s(d.get("health", ""))
             w.map(d.get("attributes"))
+    images = n.get("images") or []
+    w.u32(len(images))
+    for im in images:
+        w.strs(im.get("names"))
+        w.i64(im.get("sizeBytes", 0))
     return bytes(w.b)
 
 
@@ -176,6 +181,7 @@ def pod_record(p):
         w.strs(e.get("assigned"))
     w.i32(p.get("volumes", 0))
     w.i32(p.get("priority", 0))
+    w.strs([c.get("image", "") for c in (p.get("containers") or [])])
     return bytes(w.b)
 
 

@@ -59,6 +59,7 @@ static void apply_options(Oracle& o, const json::Value& v) {
     o.weights.prefer_avoid = w->get_int("NodePreferAvoidPodsPriority", 10000);
     o.weights.most_requested = w->get_int("MostRequestedPriority", 0);
     o.weights.resource_limits = w->get_int("ResourceLimitsPriority", 0);
+    o.weights.image_locality = w->get_int("ImageLocalityPriority", 0);
   }
   // {"extender": {"keep": [node names] (optional), "scores": {node: weighted score}}}
   if (const json::Value* ev = v.find("extender"); ev && !ev->is_null()) {
@@ -146,6 +147,7 @@ static std::string run_priority(const json::Value& req) {
       else if (name == "NodePreferAvoidPodsPriority") s = Oracle::prefer_avoid_map(pod, ni);
       else if (name == "MostRequestedPriority") s = Oracle::most_requested_map(pm, ni);
       else if (name == "ResourceLimitsPriority") s = Oracle::resource_limits_map(pod, ni);
+      else if (name == "ImageLocalityPriority") s = Oracle::image_locality_map(pod, ni);
       else if (name == "NodeLabelPriority") {
         NodeLabelPriorityArg a;
         a.label = req.find("args")->get_str("label");

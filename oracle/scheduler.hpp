@@ -302,7 +302,7 @@ struct PriorityWeights {
   int64_t least_requested = 1, balanced = 1, selector_spread = 1, node_affinity = 1, taint_toleration = 1,
           inter_pod_affinity = 1, prefer_avoid = 10000;
   // not in the DefaultProvider set (registered by name, enabled through a Policy: defaults.go:93-116, api/types.go:36-125)
-  int64_t most_requested = 0, resource_limits = 0;
+  int64_t most_requested = 0, resource_limits = 0, image_locality = 0;
 };
 
 // Policy-configured plugins that take arguments (api/types.go:64-125): NodeLabelPriority instances
@@ -752,6 +752,21 @@ struct Oracle {
         else if (kv.first == ksb::kResMemory) *mem = std::max(*mem, kv.second);
       }
   }
+  // image_locality.go:32-82: the sizes of the pod's container images already on the node, bucketed into 0..10
+  static int64_t image_locality_map(const Pod& pod, const NodeInfo& ni) {
+    constexpr int64_t mb = 1024 * 1024, minImgSize = 23 * mb, maxImgSize = 1000 * mb;  // balanced_resource_allocation.go:32-36
+    std::map<std::string, int64_t> imageSizes;  // totalImageSize :66-82 (a later entry of the same name wins)
+    for (auto& im : ni.node->images)
+      for (auto& name : im.names) imageSizes[name] = im.size_bytes;
+    int64_t total = 0;
+    for (auto& image : pod.images) {
+      auto it = imageSizes.find(image);
+      if (it != imageSizes.end()) total += it->second;
+    }
+    if (total == 0 || total < minImgSize) return 0;  // calculateScoreFromSize :49-62
+    if (total >= maxImgSize) return kMaxPriority;
+    return kMaxPriority * (total - minImgSize) / (maxImgSize - minImgSize) + 1;
+  }
   static int64_t resource_limits_map(const Pod& pod, const NodeInfo& ni) {
     int64_t lc, lm;
     pod_limits(pod, &lc, &lm);
@@ -1184,6 +1199,7 @@ struct Oracle {
       const NodeInfo& ni = cachedNodeInfoMap.at(filtered[i]->name);
       if (weights.most_requested) (*total)[i].score += most_requested_map(pm, ni) * weights.most_requested;
       if (weights.resource_limits) (*total)[i].score += resource_limits_map(pod, ni) * weights.resource_limits;
+      if (weights.image_locality) (*total)[i].score += image_locality_map(pod, ni) * weights.image_locality;
       for (auto& a : policy.node_label) (*total)[i].score += node_label_map(a, ni) * a.weight;
       // extenders' Prioritize :608-632
       auto es = extender.scores.find(filtered[i]->name);

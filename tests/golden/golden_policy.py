@@ -98,4 +98,24 @@ def builders(g):
                       reasons=None if fits else ["CheckNodeLabelPresence"],
                       policy={"labelsPresence": {"labels": labels, "presence": presence}})
 
-    return [build_most_requested, build_node_label, build_resource_limits, build_label_presence]
+    # ----------------------------------------------------------------- ImageLocalityPriority
+    # algorithm/priorities/image_locality_test.go:30-176
+    def build_image_locality():
+        src = "algorithm/priorities/image_locality_test.go:31-161"
+        mb = 1024 * 1024
+        img = lambda *names: [{"requests": {}, "image": n} for n in names]
+        node_40_140_2000 = [{"names": ["gcr.io/40", "gcr.io/40:v1", "gcr.io/40:v1"], "sizeBytes": 40 * mb},
+                            {"names": ["gcr.io/140", "gcr.io/140:v1"], "sizeBytes": 140 * mb},
+                            {"names": ["gcr.io/2000"], "sizeBytes": 2000 * mb}]
+        node_250_10 = [{"names": ["gcr.io/250"], "sizeBytes": 250 * mb},
+                       {"names": ["gcr.io/10", "gcr.io/10:v1"], "sizeBytes": 10 * mb}]
+        nodes = lambda: [node("machine1", images=node_40_140_2000), node("machine2", images=node_250_10)]
+        P = "ImageLocalityPriority"
+        priority(P, src, "two images spread on two nodes, prefer the larger image one",
+                 pod(containers=img("gcr.io/40", "gcr.io/250")), nodes(), [], [("machine1", 1), ("machine2", 3)])
+        priority(P, src, "two images on one node, prefer this node",
+                 pod(containers=img("gcr.io/40", "gcr.io/140")), nodes(), [], [("machine1", 2), ("machine2", 0)])
+        priority(P, src, "if exceed limit, use limit",
+                 pod(containers=img("gcr.io/10", "gcr.io/2000")), nodes(), [], [("machine1", 10), ("machine2", 0)])
+
+    return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality]

@@ -227,10 +227,10 @@ def test_golden_priorities_on_gpu():
     the golden lists are computed without predicates, so only the nodes that stayed are compared there."""
     names = {"LeastRequestedPriority", "BalancedResourceAllocation", "SelectorSpreadPriority", "NodeAffinityPriority",
              "TaintTolerationPriority", "InterPodAffinityPriority", "NodePreferAvoidPodsPriority", "MostRequestedPriority",
-             "ResourceLimitsPriority"}
+             "ResourceLimitsPriority", "ImageLocalityPriority"}
     with open(os.path.join(HERE, "golden", "reference_vectors.json")) as f:
         cases = [c for c in json.load(f)["cases"] if c["op"] == "priority"]
-    whole = partial = skipped = 0
+    whole = partial = skipped = image_whole = 0
     for c in cases:
         cl = _as_stream(c)
         for n in cl["nodes"]:  # priorities are tested without predicates in the reference: make every node fit
@@ -255,16 +255,17 @@ def test_golden_priorities_on_gpu():
             assert got == scores, (c["source"], c["test"], got, scores)
             assert r["host"] in winners and r["score"] == best, (c["source"], c["test"], r, scores)
             whole += 1
+            image_whole += c["name"] == "ImageLocalityPriority"
         else:
             # a predicate removed nodes; priorities whose Reduce normalises over the filtered list may legitimately
             # differ from the golden list then, the Map-only ones may not
             if c["name"] in ("LeastRequestedPriority", "BalancedResourceAllocation", "NodePreferAvoidPodsPriority",
-                             "MostRequestedPriority", "ResourceLimitsPriority", "NodeLabelPriority"):
+                             "MostRequestedPriority", "ResourceLimitsPriority", "NodeLabelPriority", "ImageLocalityPriority"):
                 assert all(got[h] == scores[h] for h in got), (c["source"], c["test"], got, scores)
             partial += 1
     assert whole + partial + skipped == len(cases)
     print("priority vectors: %d whole lists, %d partial, %d not prioritized" % (whole, partial, skipped))
-    assert whole >= 85, (whole, partial, skipped)
+    assert whole >= 85 and image_whole == 3, (whole, partial, skipped, image_whole)
 
 
 def _many_sets_cluster(n_nodes=300, n_pods=1200, n_hard=150, n_soft=140, n_avoid=130):

@@ -92,15 +92,16 @@ def test_go_shim_binds_only_declared_symbols():
 
 def test_go_and_python_pod_encoders_agree_on_field_order():
     """Both writers are sequences of u8 / u32 / i32 / i64 / str / map calls: the pod record's tail (extended resources,
-    volume count, priority) and the node record's head are compared by the order of the field names they mention."""
+    volume count, priority, container images) and the node record's head are compared by the order of the field names they mention."""
     go = open(os.path.join(ROOT, "integration", "gpusched", "encode.go")).read()
     py = open(os.path.join(ROOT, "kubernetes_b200", "wire.py")).read()
     go_pod = go[go.index("func encodePod"):go.index("// selector owners for SelectorSpread")]
     py_pod = py[py.index("def pod_record"):]
     order_go = [go_pod.index(k) for k in ("p.Namespace", "p.Name", "p.Labels", "DeletionTimestamp", "NodeName", "Containers",
-                                          "InitContainers", "NodeSelector", "Tolerations", "ExtendedResources", "Volumes", "prio")]
+                                          "InitContainers", "NodeSelector", "Tolerations", "ExtendedResources", "Volumes", "prio",
+                                          ".Image")]
     assert order_go == sorted(order_go), order_go
     order_py = [py_pod.index(k) for k in ('"namespace"', '"name"', '"labels"', '"deleting"', '"nodeName"', '"controller"',
                                           '"containers"', '"nodeSelector"', '"tolerations"', '"extendedResources"', '"volumes"',
-                                          '"priority"')]
+                                          '"priority"', '"image"')]
     assert order_py == sorted(order_py), order_py
