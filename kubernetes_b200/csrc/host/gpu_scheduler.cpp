@@ -410,6 +410,27 @@ void* ksbh_session_create(const char* cluster_json_or_path, int is_path, char** 
 
 void ksbh_session_destroy(void* s) { delete (Session*)s; }
 
+// The wire record the session built for one object (kind 0 node, 1 pod of the stream, 2 existing pod, 3 selector owner),
+// so that a test can hold the C++ encoder against the Python one (kubernetes_b200/wire.py) byte for byte. Returns 0, or 1
+// when there is no such record.
+int ksbh_session_record(void* session, int kind, int index, const uint8_t** data, size_t* len) {
+  Session* s = (Session*)session;
+  if (!s || index < 0) return 1;
+  const std::string* b = nullptr;
+  if (kind == 0 && (size_t)index < s->node_bufs.size()) b = &s->node_bufs[index];
+  else if (kind == 2 && (size_t)index < s->existing_bufs.size()) b = &s->existing_bufs[index];
+  else if (kind == 3 && (size_t)index < s->owner_bufs.size()) b = &s->owner_bufs[index].second;
+  else if (kind == 1 && (size_t)index + 1 < s->pod_offsets.size()) {
+    *data = (const uint8_t*)s->pod_stream.data() + s->pod_offsets[index];
+    *len = (size_t)(s->pod_offsets[index + 1] - s->pod_offsets[index]);
+    return 0;
+  }
+  if (!b) return 1;
+  *data = (const uint8_t*)b->data();
+  *len = b->size();
+  return 0;
+}
+
 // Run the pod stream on a fresh engine. Returns JSON (free with ksbh_free); on failure {"error": ...}.
 char* ksbh_session_run(void* session, const char* options_json) {
   try {

@@ -130,6 +130,17 @@ class Session:
             raise RuntimeError("engine: " + out["error"])
         return out
 
+    def record(self, kind, index):
+        """The wire record the C++ encoder built for one object (kind: 0 node, 1 pod of the stream, 2 existing pod,
+        3 selector owner), or None. Tests hold it against kubernetes_b200/wire.py."""
+        h = host()
+        h.ksbh_session_record.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_void_p),
+                                          ctypes.POINTER(ctypes.c_size_t)]
+        data, n = ctypes.c_void_p(), ctypes.c_size_t()
+        if h.ksbh_session_record(self._s, kind, index, ctypes.byref(data), ctypes.byref(n)) != 0:
+            return None
+        return ctypes.string_at(data, n.value)
+
     def close(self):
         if self._s:
             host().ksbh_session_destroy(self._s)

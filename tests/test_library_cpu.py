@@ -1,12 +1,13 @@
 """CPU-side checks: the C-ABI library loads and exports every symbol include/ksched_b200.h declares,
 refuses to run without a GPU, and the wire/JSON harness parses clusters. No compute calls here."""
 import ctypes
+import json
 import os
 import re
 
 import pytest
 
-from kubernetes_b200 import lib, workloads
+from kubernetes_b200 import lib, wire, workloads
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -105,3 +106,53 @@ def test_go_and_python_pod_encoders_agree_on_field_order():
                                           '"containers"', '"nodeSelector"', '"tolerations"', '"extendedResources"', '"volumes"',
                                           '"priority"', '"image"')]
     assert order_py == sorted(order_py), order_py
+
+
+def _records_agree(cluster, label):
+    """Every record of `cluster` as the C++ encoder (JSON loader of csrc/host/model.hpp + include/ksb_wire.hpp) and as the
+    Python encoder (kubernetes_b200/wire.py, written against the layout comment alone) produce it."""
+    s = lib.Session(cluster=cluster)
+    try:
+        n = 0
+        for i, node in enumerate(cluster.get("nodes") or []):
+            assert s.record(0, i) == wire.node_record(node), (label, "node", i)
+            n += 1
+        for i, pod in enumerate(cluster.get("pods") or []):
+            assert s.record(1, i) == wire.pod_record(pod), (label, "pod", i)
+            n += 1
+        for i, pod in enumerate(cluster.get("existingPods") or []):
+            assert s.record(2, i) == wire.pod_record(pod), (label, "existing pod", i)
+            n += 1
+        k = 0
+        for kind, key in enumerate(("services", "rcs", "rss", "sss")):
+            for i, o in enumerate(cluster.get(key) or []):
+                o = dict(o, name=o.get("name") or "owner-%d-%d" % (kind, i))
+                assert s.record(3, k) == wire.owner_record(o, kind >= 2), (label, key, i)
+                k += 1
+                n += 1
+        assert s.record(0, len(cluster.get("nodes") or [])) is None
+        return n
+    finally:
+        s.close()
+
+
+def test_cpp_and_python_encoders_write_the_same_bytes():
+    """The oracle reads its clusters through the same JSON loader as the product's host side (model.hpp): a field dropped
+    there would be invisible to the parity tests. The Python encoder shares no code with it, so byte-equal records for
+    the generated workloads and for every transcribed reference vector pin the loader and both encoders to the layout
+    in include/ksb_wire.hpp (a pod or node field that one side forgets shifts every byte after it)."""
+    _built()
+    total = 0
+    for cfg in (1, 2, 3, 4, 5):
+        total += _records_agree(workloads.generate(cfg, 50, 150), "cfg%d" % cfg)
+    with open(os.path.join(ROOT, "tests", "golden", "reference_vectors.json")) as f:
+        cases = json.load(f)["cases"]
+    for c in cases:
+        cl = c.get("cluster")
+        if not isinstance(cl, dict):
+            continue
+        cl = dict(cl)
+        if isinstance(c.get("pod"), dict):
+            cl["pods"] = list(cl.get("pods") or []) + [c["pod"]]
+        total += _records_agree(cl, "%s / %s" % (c.get("source"), c.get("test")))
+    assert total > 2000, total
