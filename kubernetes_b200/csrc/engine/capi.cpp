@@ -294,7 +294,7 @@ int32_t ksb_schedule_batch(ksb_engine* e, const uint8_t* pods, const uint64_t* o
     // wire records are independent: decode them on a few host threads when the batch is large
     std::vector<ksb::Pod> batch((size_t)std::max(0, n));
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const int nthreads = n >= 4096 ? (int)std::min(8u, hw) : 1;
+    const int nthreads = n >= 4096 ? (int)std::min(16u, hw) : 1;  // (nothing else of this engine runs yet)
     std::vector<std::string> errors((size_t)nthreads);
     auto decode_range = [&](int t) {
       try {

@@ -709,7 +709,7 @@ static std::string port_string(const ContainerPort& p) {  // node_info.go:444-45
 }
 
 // NodeInfo.AddPod (node_info.go:329-356) on the host-side record
-void Engine::host_add_pod(const Pod& p, HostNode& hn) {
+void Engine::host_add_pod(const Pod& p, HostNode& hn, const std::string* key, SigInfo* sig) {
   int64_t dummy_pods = 0;
   for (auto& c : p.containers) {
     reslist_to_aggregates(c.requests, &hn.req_cpu, &hn.req_mem, &hn.req_agpu, &hn.req_eph, &dummy_pods, &hn.req_scalar);
@@ -720,10 +720,17 @@ void Engine::host_add_pod(const Pod& p, HostNode& hn) {
     for (auto& port : c.ports)
       if (port.host_port != 0) hn.used_ports.insert(port_string(port));
   }
-  hn.pod_keys.insert(p.key());
-  hn.pod_order.push_back(p.key());
   {
-    auto& pl = sig_of(p)->placed[p.node_name];
+    std::string own;
+    if (!key) {
+      own = p.key();
+      key = &own;
+    }
+    hn.pod_keys.insert(*key);
+    hn.pod_order.push_back(*key);
+  }
+  {
+    auto& pl = (sig ? sig : sig_of(p))->placed[p.node_name];
     pl.first += 1;
     if (!p.deleting) pl.second += 1;
   }

@@ -126,6 +126,7 @@ struct EncodedPod {
   std::vector<CommitEntry> commits;  // host-side form of the pool's commit list
   std::vector<int> spread_inc;
   std::vector<std::string> ext_reasons;  // failure text for RB_EXT0.. / RB_EXT_LIMITS
+  SigInfo* sig = nullptr;  // the pod's (namespace, labels) signature record, so that the host mirror need not look it up again
 };
 
 class Engine {
@@ -385,7 +386,7 @@ class Engine {
   void apply_node_part_host(int row, const EncodedPod& e, const uint32_t* dev_masks);
   void apply_class_part_host(int row, const std::vector<CommitEntry>& commits, const std::vector<int>& spread_inc,
                              int sign);
-  void host_add_pod(const Pod& p, HostNode& hn);
+  void host_add_pod(const Pod& p, HostNode& hn, const std::string* key = nullptr, SigInfo* sig = nullptr);
   void host_remove_pod(const Pod& p, HostNode& hn);
 
   // ---- last batch (for ksb_replay_last_batch and fit-error messages)

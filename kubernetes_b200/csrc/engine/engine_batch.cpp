@@ -449,7 +449,7 @@ void Engine::schedule_batch_once(std::vector<Pod>& batch, ksb_result* out, bool 
   if (assume) {
     // ksb_schedule_batch == n x {ksb_schedule; ksb_pod_add}: a key that is already cached, or repeated inside the
     // batch, is the error ksb_pod_add reports (cache.go:127-129); refuse before anything is placed
-    // repeated keys inside the batch: 64-bit hashes sorted, exact comparison only where two hashes meet
+    // repeated keys inside the batch: 64-bit hashes, exact comparison only where two hashes meet
     auto key_hash = [](const Pod& p) {
       uint64_t h = 1469598103934665603ull;
       for (unsigned char ch : p.ns) h = (h ^ ch) * 1099511628211ull;
@@ -457,17 +457,29 @@ void Engine::schedule_batch_once(std::vector<Pod>& batch, ksb_result* out, bool 
       for (unsigned char ch : p.name) h = (h ^ ch) * 1099511628211ull;
       return h;
     };
-    std::vector<std::pair<uint64_t, int>> hs((size_t)np);
-    for (int i = 0; i < np; ++i) hs[i] = {key_hash(batch[i]), i};
-    std::sort(hs.begin(), hs.end());
-    for (int i = 1; i < np; ++i)
-      if (hs[i].first == hs[i - 1].first && batch[hs[i].second].key() == batch[hs[i - 1].second].key())
-        throw std::runtime_error("pod " + batch[hs[i].second].key() + " is already in the cache");
+    // (an open-addressing table of the batch's indices under their hashes: a tenth of the time of sorting them)
+    size_t cap = 1;
+    while (cap < 2 * (size_t)np) cap <<= 1;
+    std::vector<int32_t> slot(cap, -1);
+    std::vector<uint64_t> hv((size_t)np);
+    for (int i = 0; i < np; ++i) {
+      const uint64_t h = key_hash(batch[i]);
+      hv[i] = h;
+      size_t s = (size_t)(h ^ (h >> 29)) & (cap - 1);
+      while (slot[s] >= 0) {
+        const int j = slot[s];
+        if (hv[j] == h && batch[j].ns == batch[i].ns && batch[j].name == batch[i].name)
+          throw std::runtime_error("pod " + batch[i].key() + " is already in the cache");
+        s = (s + 1) & (cap - 1);
+      }
+      slot[s] = i;
+    }
     if (!pods.empty())
       for (auto& p : batch) {
         const std::string k = p.key();
         if (pods.count(k)) throw std::runtime_error("pod " + k + " is already in the cache");
       }
+    pods.reserve(pods.size() + (size_t)np);  // no rehash while the mirror thread inserts
   }
   mark("checks");
   // pass 1: classes (every pod of the batch, so that commit lists name every class a later pod introduces)
@@ -737,9 +749,9 @@ void Engine::schedule_batch_once(std::vector<Pod>& batch, ksb_result* out, bool 
       }
       apply_node_part_host(r.row, last_encoded[i], r.device_mask);
       apply_class_part_host(r.row, last_encoded[i].commits, last_encoded[i].spread_inc, +1);
-      host_add_pod(p, hn);
       std::string key = p.key();
-      pods[std::move(key)] = HostPod{std::move(p)};  // the batch is the caller's scratch copy: its pods move into the cache
+      host_add_pod(p, hn, &key, last_encoded[i].sig);
+      pods.insert_or_assign(std::move(key), HostPod{std::move(p)});  // the batch is the caller's scratch copy: its pods move into the cache
     }
     post_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp0).count();
     if (assume) batch_posted = (size_t)c1;

@@ -169,6 +169,7 @@ void Engine::encode_pod(const Pod& p, EncodedPod* out) {
   out->spread_inc.clear();
   out->ext_reasons.assign(KSB_MAX_EXT + 1, std::string());
   SigInfo* sig = sig_of(p);
+  out->sig = sig;
 
   // --- resources: GetResourceRequest (predicates.go:583-621), calculateResource (node_info.go:421-433),
   //     getNonZeroRequests (priorities/metadata.go / non_zero.go:29-50)
