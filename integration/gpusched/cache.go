@@ -12,8 +12,6 @@ package gpusched
 import "C"
 
 import (
-	"unsafe"
-
 	"k8s.io/api/core/v1"
 	"k8s.io/apimachinery/pkg/labels"
 	"k8s.io/kubernetes/plugin/pkg/scheduler/schedulercache"
@@ -37,9 +35,9 @@ func (c *Cache) podAdd(pod *v1.Pod) error {
 }
 
 func (c *Cache) podRemove(pod *v1.Pod) error {
-	ns, name := pod.Namespace, pod.Name
-	if C.ksb_pod_remove(c.g.e, (*C.char)(unsafe.Pointer(unsafe.StringData(ns))), C.size_t(len(ns)),
-		(*C.char)(unsafe.Pointer(unsafe.StringData(name))), C.size_t(len(name))) != 0 {
+	ns, nsLen := strArg(pod.Namespace)
+	name, nameLen := strArg(pod.Name)
+	if C.ksb_pod_remove(c.g.e, ns, nsLen, name, nameLen) != 0 {
 		return c.g.lastError()
 	}
 	return nil
@@ -123,8 +121,8 @@ func (c *Cache) RemoveNode(node *v1.Node) error {
 	if err := c.Cache.RemoveNode(node); err != nil {
 		return err
 	}
-	name := node.Name
-	if C.ksb_node_remove(c.g.e, (*C.char)(unsafe.Pointer(unsafe.StringData(name))), C.size_t(len(name))) != 0 {
+	name, nameLen := strArg(node.Name)
+	if C.ksb_node_remove(c.g.e, name, nameLen) != 0 {
 		return c.g.lastError()
 	}
 	return nil
@@ -145,8 +143,9 @@ func (g *GPUScheduler) UpsertMapSelectorOwner(kind int, ns, name string, selecto
 }
 
 func (g *GPUScheduler) RemoveSelectorOwner(kind int, ns, name string) error {
-	if C.ksb_selector_owner_remove(g.e, C.int32_t(kind), (*C.char)(unsafe.Pointer(unsafe.StringData(ns))), C.size_t(len(ns)),
-		(*C.char)(unsafe.Pointer(unsafe.StringData(name))), C.size_t(len(name))) != 0 {
+	nsp, nsLen := strArg(ns)
+	namep, nameLen := strArg(name)
+	if C.ksb_selector_owner_remove(g.e, C.int32_t(kind), nsp, nsLen, namep, nameLen) != 0 {
 		return g.lastError()
 	}
 	return nil

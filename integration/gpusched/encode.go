@@ -8,7 +8,6 @@
 package gpusched
 
 import (
-	"encoding/binary"
 	"encoding/json"
 	"sort"
 
@@ -25,9 +24,9 @@ func (w *writer) u8(v bool) {
 		w.b = append(w.b, 0)
 	}
 }
-func (w *writer) u32(v uint32) { w.b = binary.LittleEndian.AppendUint32(w.b, v) }
+func (w *writer) u32(v uint32) { w.b = append(w.b, byte(v), byte(v>>8), byte(v>>16), byte(v>>24)) } // little-endian
 func (w *writer) i32(v int32)  { w.u32(uint32(v)) }
-func (w *writer) i64(v int64)  { w.b = binary.LittleEndian.AppendUint64(w.b, uint64(v)) }
+func (w *writer) i64(v int64)  { w.u32(uint32(uint64(v))); w.u32(uint32(uint64(v) >> 32)) }
 func (w *writer) str(s string) { w.u32(uint32(len(s))); w.b = append(w.b, s...) }
 
 // maps are written with sorted keys, as wire.py does (the engine does not depend on the order)

@@ -106,7 +106,8 @@ func (g *GPUScheduler) AddNodeLabelPriority(label string, presence bool, weight 
 	if presence {
 		p = 1
 	}
-	if C.ksb_policy_set(g.e, C.KSB_POLICY_NODE_LABEL_PRIORITY, (*C.char)(unsafe.Pointer(unsafe.StringData(label))), C.size_t(len(label)), p, C.int32_t(weight)) != 0 {
+	lp, ll := strArg(label)
+	if C.ksb_policy_set(g.e, C.KSB_POLICY_NODE_LABEL_PRIORITY, lp, ll, p, C.int32_t(weight)) != 0 {
 		return g.lastError()
 	}
 	return nil
@@ -118,7 +119,8 @@ func (g *GPUScheduler) AddLabelPresence(labels []string, presence bool) error {
 		p = 1
 	}
 	for _, l := range labels {
-		if C.ksb_policy_set(g.e, C.KSB_POLICY_LABEL_PRESENCE, (*C.char)(unsafe.Pointer(unsafe.StringData(l))), C.size_t(len(l)), p, 0) != 0 {
+		lp, ll := strArg(l)
+		if C.ksb_policy_set(g.e, C.KSB_POLICY_LABEL_PRESENCE, lp, ll, p, 0) != 0 {
 			return g.lastError()
 		}
 	}
@@ -126,6 +128,19 @@ func (g *GPUScheduler) AddLabelPresence(labels []string, presence bool) error {
 }
 
 func (g *GPUScheduler) lastError() error { return fmt.Errorf("%s", C.GoString(C.ksb_last_error(g.e))) }
+
+// strArg: a string's bytes for the duration of one C call (the engine copies what it keeps). A copy, because the
+// tree this is written for builds with go1.9, which has no unsafe.StringData; never nil, so that the C side may
+// build a std::string from it even when the length is 0.
+var emptyArg [1]byte
+
+func strArg(s string) (*C.char, C.size_t) {
+	if len(s) == 0 {
+		return (*C.char)(unsafe.Pointer(&emptyArg[0])), 0
+	}
+	b := []byte(s)
+	return (*C.char)(unsafe.Pointer(&b[0])), C.size_t(len(b))
+}
 
 func bytesPtr(b []byte) (*C.uint8_t, C.size_t) {
 	if len(b) == 0 {

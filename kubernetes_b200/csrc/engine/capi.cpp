@@ -243,7 +243,7 @@ int32_t ksb_node_upsert(ksb_engine* e, const uint8_t* buf, size_t len) {
 
 int32_t ksb_node_remove(ksb_engine* e, const char* name, size_t name_len) {
   return mutate(e, [&]() -> std::function<void()> {
-    std::string nm(name, name_len);
+    std::string nm(name ? name : "", name ? name_len : 0);
     return [e, nm] { e->impl->node_remove(nm); };
   });
 }
@@ -258,7 +258,7 @@ int32_t ksb_pod_add(ksb_engine* e, const uint8_t* buf, size_t len) {
 
 int32_t ksb_pod_remove(ksb_engine* e, const char* ns, size_t ns_len, const char* name, size_t name_len) {
   return mutate(e, [&]() -> std::function<void()> {
-    std::string a(ns, ns_len), b(name, name_len);
+    std::string a(ns ? ns : "", ns ? ns_len : 0), b(name ? name : "", name ? name_len : 0);
     return [e, a, b] { e->impl->pod_remove(a, b); };
   });
 }
@@ -274,7 +274,7 @@ int32_t ksb_selector_owner_upsert(ksb_engine* e, int32_t kind, const uint8_t* bu
 int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, size_t ns_len, const char* name,
                                   size_t name_len) {
   return mutate(e, [&]() -> std::function<void()> {
-    std::string a(ns, ns_len), b(name, name_len);
+    std::string a(ns ? ns : "", ns ? ns_len : 0), b(name ? name : "", name ? name_len : 0);
     return [e, kind, a, b] { e->impl->owner_remove(kind, a, b); };
   });
 }
