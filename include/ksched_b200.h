@@ -123,7 +123,12 @@ int32_t ksb_selector_owner_remove(ksb_engine* e, int32_t kind, const char* ns, s
  *   KSB_POLICY_CLEAR                back to the DefaultProvider set
  *   KSB_POLICY_IMAGE_LOCALITY       ImageLocalityPriority (priorities/image_locality.go:32-82) with `weight`: reads the
  *                                   image lists at the end of the node and pod records (ksb_wire.hpp)
- * The other Policy-only plugins (ServiceSpreadingPriority / ServiceAntiAffinity, the ServiceAffinity predicate) are not
+ *   KSB_POLICY_SERVICE_SPREADING    ServiceSpreadingPriority (defaults.go:90-102) with `weight`. Its Map reads the selectors of
+ *                                   the priorityMetadata whenever one exists (priorities/selector_spreading.go:71-76), and
+ *                                   PrioritizeNodes always has one, so it scores exactly as SelectorSpreadPriority does
+ *   KSB_POLICY_EQUAL                EqualPriority (core/generic_scheduler.go:643-652) with `weight`: 1 on every node. A factory
+ *                                   whose Policy lists no priority at all passes weight 1 (generic_scheduler.go:517-529)
+ * The other Policy-only plugins (ServiceAntiAffinity, the ServiceAffinity predicate) are not
  * implemented: a factory that is asked for them must refuse, as gpusched.New does for unknown keys. */
 enum {
   KSB_POLICY_NODE_LABEL_PRIORITY = 0,
@@ -131,7 +136,9 @@ enum {
   KSB_POLICY_MOST_REQUESTED = 2,
   KSB_POLICY_RESOURCE_LIMITS = 3,
   KSB_POLICY_CLEAR = 4,
-  KSB_POLICY_IMAGE_LOCALITY = 5
+  KSB_POLICY_IMAGE_LOCALITY = 5,
+  KSB_POLICY_SERVICE_SPREADING = 6,
+  KSB_POLICY_EQUAL = 7
 };
 int32_t ksb_policy_set(ksb_engine* e, int32_t kind, const char* key, size_t key_len, int32_t presence, int32_t weight);
 

@@ -47,9 +47,11 @@ var weightField = map[string]func(*C.ksb_config, C.int32_t){
 
 // priorities a Policy can enable by name that take no arguments (ksb_policy_set)
 var policyWeightKind = map[string]C.int32_t{
-	"MostRequestedPriority":  C.KSB_POLICY_MOST_REQUESTED,
-	"ResourceLimitsPriority": C.KSB_POLICY_RESOURCE_LIMITS,
-	"ImageLocalityPriority":  C.KSB_POLICY_IMAGE_LOCALITY,
+	"MostRequestedPriority":    C.KSB_POLICY_MOST_REQUESTED,
+	"ResourceLimitsPriority":   C.KSB_POLICY_RESOURCE_LIMITS,
+	"ImageLocalityPriority":    C.KSB_POLICY_IMAGE_LOCALITY,
+	"ServiceSpreadingPriority": C.KSB_POLICY_SERVICE_SPREADING,
+	"EqualPriority":            C.KSB_POLICY_EQUAL,
 }
 
 // GPUScheduler implements algorithm.ScheduleAlgorithm.
@@ -84,6 +86,11 @@ func New(predicateKeys []string, priorityWeights map[string]int, hardPodAffinity
 			return nil, fmt.Errorf("gpusched: priority %q is not implemented by the GPU engine", name)
 		}
 		set(&cfg, C.int32_t(w))
+	}
+	if len(priorityWeights) == 0 {
+		// PrioritizeNodes without any priority config (and without extenders) applies EqualPriorityMap: every node
+		// scores 1 (core/generic_scheduler.go:517-529)
+		policyWeights["EqualPriority"] = 1
 	}
 	cfg.hard_pod_affinity_weight = C.int32_t(hardPodAffinityWeight)
 	var errbuf [512]C.char

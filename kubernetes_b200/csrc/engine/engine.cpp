@@ -890,10 +890,16 @@ void Engine::policy_set(int kind, const std::string& key, bool presence, int32_t
       pol_node_label.clear();
       pol_presence_labels.clear();
       pol_presence = true;
-      w_most_requested = w_resource_limits = w_image_locality = 0;
+      w_most_requested = w_resource_limits = w_image_locality = w_service_spreading = w_equal = 0;
       break;
     case 5:
       w_image_locality = weight;
+      break;
+    case 6:
+      w_service_spreading = weight;
+      break;
+    case 7:
+      w_equal = weight;
       break;
     default:
       throw std::runtime_error("unknown policy plugin kind");
@@ -971,7 +977,7 @@ void Engine::fill_row(int row) {
   }
   u32(U32_ZONE, row) = zone;
   {  // Policy plugins that depend on the node alone (node_label.go:46-60, predicates.go:800-826)
-    int32_t sscore = 0;
+    int32_t sscore = w_equal;  // EqualPriorityMap: 1 on every node
     for (auto& a : pol_node_label) {
       const bool exists = nd.has_labels && nd.labels.count(a.label) != 0;
       if ((exists && a.presence) || (!exists && !a.presence)) sscore += 10 * a.weight;

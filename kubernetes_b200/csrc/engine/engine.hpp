@@ -159,6 +159,11 @@ class Engine {
   std::vector<std::string> pol_presence_labels;
   bool pol_presence = true;
   int32_t w_most_requested = 0, w_resource_limits = 0, w_image_locality = 0;
+  // ServiceSpreadingPriority (defaults.go:94-102) is SelectorSpread built over the service lister alone, but its Map takes
+  // the selectors from the priorityMetadata whenever there is one (selector_spreading.go:71-76), and PrioritizeNodes always
+  // has one (defaults.go:47-50): its weight simply adds to SelectorSpread's. EqualPriority (generic_scheduler.go:643-652)
+  // is 1 on every node: its weight joins the per-node static score.
+  int32_t w_service_spreading = 0, w_equal = 0;
   int image_class_of(const Pod& p);
   uint32_t image_score(const HostNode& hn, const std::vector<std::string>& images) const;
   void fill_image_scores(int row);

@@ -582,10 +582,10 @@ void Engine::setup_table_pointers() {
   T.w_mr = w_most_requested;
   T.w_rl = w_resource_limits;
   T.w_il = w_image_locality;
-  T.has_static = pol_node_label.empty() ? 0 : 1;
+  T.has_static = (pol_node_label.empty() && w_equal == 0) ? 0 : 1;
   T.has_presence = pol_presence_labels.empty() ? 0 : 1;
   T.w_bra = cfg.w_balanced;
-  T.w_ss = cfg.w_selector_spread;
+  T.w_ss = cfg.w_selector_spread + w_service_spreading;
   T.w_na = cfg.w_node_affinity;
   T.w_tt = cfg.w_taint_toleration;
   T.w_ipa = cfg.w_inter_pod_affinity;

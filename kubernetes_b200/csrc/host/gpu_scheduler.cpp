@@ -86,6 +86,10 @@ void apply_policy(EngineHandle& h, const json::Value& opt) {
       h.check(ksb_policy_set(h.get(), KSB_POLICY_RESOURCE_LIMITS, nullptr, 0, 0, (int32_t)w->get_int("ResourceLimitsPriority", 0)), "policy");
     if (w->get_int("ImageLocalityPriority", 0) != 0)
       h.check(ksb_policy_set(h.get(), KSB_POLICY_IMAGE_LOCALITY, nullptr, 0, 0, (int32_t)w->get_int("ImageLocalityPriority", 0)), "policy");
+    if (w->get_int("ServiceSpreadingPriority", 0) != 0)
+      h.check(ksb_policy_set(h.get(), KSB_POLICY_SERVICE_SPREADING, nullptr, 0, 0, (int32_t)w->get_int("ServiceSpreadingPriority", 0)), "policy");
+    if (w->get_int("EqualPriority", 0) != 0)
+      h.check(ksb_policy_set(h.get(), KSB_POLICY_EQUAL, nullptr, 0, 0, (int32_t)w->get_int("EqualPriority", 0)), "policy");
   }
   if (const json::Value* pv = opt.find("policy"); pv && !pv->is_null()) {
     if (pv->has("nodeLabelPriorities"))

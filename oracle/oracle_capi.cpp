@@ -60,6 +60,8 @@ static void apply_options(Oracle& o, const json::Value& v) {
     o.weights.most_requested = w->get_int("MostRequestedPriority", 0);
     o.weights.resource_limits = w->get_int("ResourceLimitsPriority", 0);
     o.weights.image_locality = w->get_int("ImageLocalityPriority", 0);
+    o.weights.service_spreading = w->get_int("ServiceSpreadingPriority", 0);
+    o.weights.equal = w->get_int("EqualPriority", 0);
   }
   // {"extender": {"keep": [node names] (optional), "scores": {node: weighted score}}}
   if (const json::Value* ev = v.find("extender"); ev && !ev->is_null()) {

@@ -303,6 +303,8 @@ struct PriorityWeights {
           inter_pod_affinity = 1, prefer_avoid = 10000;
   // not in the DefaultProvider set (registered by name, enabled through a Policy: defaults.go:93-116, api/types.go:36-125)
   int64_t most_requested = 0, resource_limits = 0, image_locality = 0;
+  int64_t service_spreading = 0;  // defaults.go:90-102: SelectorSpread's Map / Reduce; with a priorityMetadata (always, in PrioritizeNodes) the same selectors too (selector_spreading.go:71-76)
+  int64_t equal = 0;              // generic_scheduler.go:643-652: 1 on every node
 };
 
 // Policy-configured plugins that take arguments (api/types.go:64-125): NodeLabelPriority instances
@@ -1200,6 +1202,7 @@ struct Oracle {
       if (weights.most_requested) (*total)[i].score += most_requested_map(pm, ni) * weights.most_requested;
       if (weights.resource_limits) (*total)[i].score += resource_limits_map(pod, ni) * weights.resource_limits;
       if (weights.image_locality) (*total)[i].score += image_locality_map(pod, ni) * weights.image_locality;
+      (*total)[i].score += ss[i].score * weights.service_spreading + 1 * weights.equal;
       for (auto& a : policy.node_label) (*total)[i].score += node_label_map(a, ni) * a.weight;
       // extenders' Prioritize :608-632
       auto es = extender.scores.find(filtered[i]->name);

@@ -316,6 +316,17 @@ def test_policy_plugins_match_oracle():
     compare(cluster, "policy", gpu_opts=opts, oracle_opts=opts)
     small = workloads.generate(3, 120, 300)
     compare(small, "policy single", gpu_opts=dict(opts, batch=0), oracle_opts=opts)
+    # the two legacy names: ServiceSpreadingPriority scores as SelectorSpread does once a priorityMetadata exists
+    # (selector_spreading.go:71-76), EqualPriority is 1 on every node (generic_scheduler.go:643-652)
+    legacy = {"weights": dict(opts["weights"], ServiceSpreadingPriority=2, EqualPriority=3, MostRequestedPriority=0,
+                              ResourceLimitsPriority=0)}
+    got, want = compare(workloads.generate(3, 200, 800), "legacy names", gpu_opts=legacy, oracle_opts=legacy)
+    plain = oracle_lib.call({"op": "stream", "cluster": workloads.generate(3, 200, 800)})
+    assert any(w["score"] != p["score"] for w, p in zip(want["results"], plain["results"]))
+    only_equal = {"weights": {k: 0 for k in opts["weights"]}}
+    only_equal["weights"]["EqualPriority"] = 1  # a Policy without priorities: every node scores 1, round-robin over all that fit
+    compare(workloads.generate(1, 50, 200), "equal only", gpu_opts=dict(only_equal, batch=0), oracle_opts=only_equal)
+    compare(workloads.generate(1, 50, 200), "equal only batch", gpu_opts=only_equal, oracle_opts=only_equal)
 
 
 def test_label_universe_grows_past_256_pairs():
