@@ -118,4 +118,30 @@ def builders(g):
         priority(P, src, "if exceed limit, use limit",
                  pod(containers=img("gcr.io/10", "gcr.io/2000")), nodes(), [], [("machine1", 10), ("machine2", 0)])
 
-    return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality]
+    # ----------------------------------------------------------------- selectHost
+    # core/generic_scheduler_test.go:117-181 (TestSelectHost). The HostPriorityList is handed to the whole Schedule path
+    # as the combined score of an extender (core/generic_scheduler.go:608-632) with every priority weighted 0, ten pods
+    # in a row as the test's ten calls. `host_in` is what the reference asserts; `hosts` is the order selectHost's code
+    # implies (:177-192: descending (score, host), lastNodeIndex round-robin over the top scorers, starting at 0).
+    # The fourth case of the test (an empty list is an error) cannot occur on this path: an empty filtered list is a
+    # FitError before selectHost is reached (:131-137).
+    def build_select_host():
+        src = "core/generic_scheduler_test.go:117-181"
+        zero = {k: 0 for k in ("LeastRequestedPriority", "BalancedResourceAllocation", "SelectorSpreadPriority",
+                               "NodeAffinityPriority", "TaintTolerationPriority", "InterPodAffinityPriority",
+                               "NodePreferAvoidPodsPriority")}
+        for test, lst, possible in [
+                ("unique, properly ordered scores", [("machine1.1", 1), ("machine2.1", 2)], ["machine2.1"]),
+                ("equal scores", [("machine1.1", 1), ("machine1.2", 2), ("machine1.3", 2), ("machine2.1", 2)],
+                 ["machine1.2", "machine1.3", "machine2.1"]),
+                ("out of order scores", [("machine1.1", 3), ("machine1.2", 3), ("machine2.1", 2), ("machine3.1", 1),
+                                         ("machine1.3", 3)], ["machine1.1", "machine1.2", "machine1.3"])]:
+            order = sorted(possible, reverse=True)
+            CASES.append({"op": "stream", "source": src, "test": "selectHost: " + test, "weights": zero,
+                          "extender": {"scores": dict(lst)},
+                          "cluster": {"nodes": [node(h, 4000, 1 << 33, pods=110) for h, _ in lst],
+                                      "pods": [pod(containers=[]) for _ in range(10)]},
+                          "expect": {"host_in": [possible] * 10, "hosts": [order[i % len(order)] for i in range(10)]}})
+
+    return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality,
+            build_select_host]

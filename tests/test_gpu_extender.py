@@ -2,6 +2,8 @@
 against the oracle: Filter verdicts cut the filtered list before the fork's device selection and before the Reduce
 halves normalise over it, Prioritize verdicts are added to the weighted sum."""
 import ctypes
+import json
+import os
 
 import pytest
 
@@ -87,3 +89,45 @@ def test_extender_verdicts_match_oracle(cfg, nodes, pods):
         assert checked == len(probes)
     finally:
         so.ksb_destroy(e)
+
+
+def test_select_host_vectors_on_gpu():
+    """TestSelectHost (core/generic_scheduler_test.go:117-181) through the C-ABI: the test's HostPriorityList arrives as
+    the extenders' combined score with every priority weighted 0, ten Schedule + AssumePod rounds per list; the chosen
+    host must be one of the reference's possibleHosts every time, and follow the round-robin order selectHost implies."""
+    so = lib.engine()
+    so.ksb_schedule_extended.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint32),
+                                         ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(lib.KsbResult)]
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.json")) as f:
+        cases = [c for c in json.load(f)["cases"] if c["op"] == "stream" and "extender" in c]
+    assert len(cases) == 3
+    for c in cases:
+        cfg = lib.KsbConfig()
+        so.ksb_config_default(ctypes.byref(cfg))
+        for f_ in ("w_least_requested", "w_balanced", "w_selector_spread", "w_node_affinity", "w_taint_toleration",
+                   "w_inter_pod_affinity", "w_prefer_avoid"):
+            setattr(cfg, f_, 0)
+        err = ctypes.create_string_buffer(512)
+        e = so.ksb_create(ctypes.byref(cfg), err, 512)
+        assert e, err.value
+        try:
+            names = sorted((n["name"] for n in c["cluster"]["nodes"]), key=lambda s: s.encode())
+            for n in c["cluster"]["nodes"]:
+                b = wire.node_record(n)
+                assert so.ksb_node_upsert(e, b, len(b)) == 0
+            sarr = (ctypes.c_int32 * len(names))(*[c["extender"]["scores"][nm] for nm in names])
+            got = []
+            for pod in c["cluster"]["pods"]:
+                b = wire.pod_record(pod)
+                res = lib.KsbResult()
+                assert so.ksb_schedule_extended(e, b, len(b), None, sarr, ctypes.byref(res)) == 0, so.ksb_last_error(e)
+                assert res.status == 0 and res.num_filtered == len(names), (c["test"], res.status, res.num_filtered)
+                got.append(names[res.node_index])
+                assert res.score == max(c["extender"]["scores"].values()), (c["test"], res.score)
+                placed = wire.pod_record(dict(pod, nodeName=names[res.node_index]))  # AssumePod (scheduler.go:478)
+                assert so.ksb_pod_add(e, placed, len(placed)) == 0, so.ksb_last_error(e)
+            for g, allowed in zip(got, c["expect"]["host_in"]):
+                assert g in allowed, (c["test"], got)
+            assert got == c["expect"]["hosts"], (c["test"], got)
+        finally:
+            so.ksb_destroy(e)
