@@ -191,6 +191,13 @@ static std::string run_predicate(const json::Value& req) {
   bool hard_error = false;
   if (name == "PodFitsResources") {
     Oracle::pod_fits_resources(meta, ni, &fails);
+  } else if (name == "GeneralPredicates") {
+    // predicates.go:965-1035: noncriticalPredicates (PodFitsResources), then EssentialPredicates (PodFitsHost,
+    // PodFitsHostPorts, PodMatchNodeSelector); every failing one adds its reasons
+    Oracle::pod_fits_resources(meta, ni, &fails);
+    if (!pod.node_name.empty() && pod.node_name != ni.node->name) fails.push_back("HostName");
+    if (!meta.podPorts.empty() && ports_conflict(ni.usedPorts, meta.podPorts)) fails.push_back("PodFitsHostPorts");
+    if (!Oracle::pod_matches_node_labels(pod, *ni.node)) fails.push_back("MatchNodeSelector");
   } else if (name == "PodFitsHost") {
     if (!pod.node_name.empty() && pod.node_name != ni.node->name) fails.push_back("HostName");
   } else if (name == "PodFitsHostPorts") {

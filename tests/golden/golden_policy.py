@@ -143,5 +143,24 @@ def builders(g):
                                       "pods": [pod(containers=[]) for _ in range(10)]},
                           "expect": {"host_in": [possible] * 10, "hosts": [order[i % len(order)] for i in range(10)]}})
 
+    # ----------------------------------------------------------------- GeneralPredicates
+    # algorithm/predicates/predicates_test.go:2051-2159 (TestRunGeneralPredicates)
+    def build_general_predicates():
+        src = "algorithm/predicates/predicates_test.go:2051-2159"
+        GPU = "alpha.kubernetes.io/nvidia-gpu"
+        rpod = lambda cpu, mem, gpu=None: pod(containers=[ctr(cpu, mem, requests={GPU: gpu} if gpu is not None else None)])
+        plain = lambda: node("machine1", alloc={"cpu": 10, "memory": 20, GPU: 0, "pods": 32})
+        gpu1 = lambda: node("machine1", alloc={"cpu": 10, "memory": 20, GPU: 1, "pods": 32})
+        port_pod = lambda: pod(containers=[{"requests": {}, "ports": [{"hostPort": 123}]}])
+        P = "GeneralPredicates"
+        predicate(P, src, "no resources/port/host requested always fits", pod(), plain(), [rpod(9, 19)], True, [])
+        predicate(P, src, "not enough cpu and memory resource", rpod(8, 10), plain(), [rpod(5, 19)], False,
+                  ["Insufficient cpu", "Insufficient memory"])
+        predicate(P, src, "no resources/port/host requested always fits on GPU machine", pod(), gpu1(), [rpod(9, 19)], True, [])
+        predicate(P, src, "not enough GPU resource", rpod(3, 1, 1), gpu1(), [rpod(5, 10, 1)], False, ["Insufficient " + GPU])
+        predicate(P, src, "enough GPU resource", rpod(3, 1, 1), gpu1(), [rpod(5, 10, 0)], True, [])
+        predicate(P, src, "host not match", pod(nodeName="machine2"), plain(), [], False, ["HostName"])
+        predicate(P, src, "hostport conflict", port_pod(), plain(), [port_pod()], False, ["PodFitsHostPorts"])
+
     return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality,
-            build_select_host]
+            build_select_host, build_general_predicates]
