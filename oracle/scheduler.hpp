@@ -510,6 +510,10 @@ struct Oracle {
     for (auto& tp : affTerms) {
       bool termMatches, exists;
       if (!any_pod_matches_term(tp, allPods, node, &termMatches, &exists)) {
+        // :1293-1297 returns ErrPodAffinityRulesNotMatch WITH the error; InterPodAffinityMatches (:1155-1160) puts
+        // ErrPodAffinityNotMatch in front and hands both on (podFitsOnNode then fails the whole Schedule call)
+        fails->push_back("MatchInterPodAffinity");
+        fails->push_back("PodAffinityRulesNotMatch");
         *err = "Cannot schedule pod onto node, because of PodAffinityTerm";
         return false;
       }

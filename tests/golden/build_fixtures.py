@@ -198,6 +198,10 @@ def build_selector_spread():
          pod(labels={"foo": "bar", "bar": "foo"}, controller=cref("ReplicaSet")),
          [pod(M1, l2), pod(M1, l1, controller=cref("ReplicaSet")), pod(M2, l1, controller=cref("ReplicaSet"))],
          {"services": [svc({"bar": "foo"})], "rss": [ls({"foo": "bar"})]}, (0, 5)),
+        ("disjoined service and stateful set should be treated equally",  # (named "... replica set ..." a second time in the reference, :249-261)
+         pod(labels={"foo": "bar", "bar": "foo"}, controller=cref("StatefulSet")),
+         [pod(M1, l2), pod(M1, l1, controller=cref("StatefulSet")), pod(M2, l1, controller=cref("StatefulSet"))],
+         {"services": [svc({"bar": "foo"})], "sss": [ls({"foo": "bar"})]}, (0, 5)),
         ("Replication controller with partial pod label matches", pod(labels=l1, controller=cref("ReplicationController")),
          [pod(M1, l2), pod(M1, l1, controller=cref("ReplicationController")),
           pod(M2, l1, controller=cref("ReplicationController"))], {"rcs": [svc({"foo": "bar"})]}, (0, 0)),

@@ -210,6 +210,8 @@ def builders(g):
             (pod(affinity=req([expr("GPU", "Exists")])), {"GPU": "NVIDIA-GRID-K1"}, True, "Exists operator that matches"),
             (pod(affinity=req([expr("foo", "In", "value1", "value2")])), foo, False, "affinity that doesn't match node's labels"),
             (pod(affinity={"node": {"required": []}}), foo, False, "nil []NodeSelectorTerm matches nothing"),
+            # (a nil and an empty slice are the same record on this wire: a term count of 0; the reference has one case each)
+            (pod(affinity={"node": {"required": []}}), foo, False, "empty []NodeSelectorTerm matches nothing"),
             (pod(affinity=req([])), foo, False, "empty MatchExpressions matches no objects"),
             (pod(), foo, True, "Pod with no Affinity will schedule onto a node"),
             (pod(affinity={"node": {"required": None}}), foo, True, "Affinity but nil NodeSelector will schedule onto a node"),
@@ -269,6 +271,16 @@ def builders(g):
         predicate(M, src, "PodAffinity NotIn operator matches the existing pod",
                   pod(labels=podLabel2, affinity={"podAffinity": aff(term(sel(expr("service", "NotIn", "securityscan3", "value3")), "region"))}),
                   n1(), ex(), True, [])
+        # (the next two terms carry no topologyKey in the reference's table, predicates_test.go:2246-2308: the predicate
+        #  returns its reasons AND an error, :1293-1297; the Go test drops the error, a Schedule call would fail on it)
+        predicate(M, src, "Does not satisfy the PodAffinity with labelSelector because of diff Namespace",
+                  pod(labels=podLabel2, affinity={"podAffinity": aff(term(svc_in("securityscan", "value2"), "", ["DiffNameSpace"]))}),
+                  n1(), ex(ns="ns"), False, [A, B])
+        CASES[-1]["expect"]["error"] = "Cannot schedule pod onto node, because of PodAffinityTerm"
+        predicate(M, src, "Doesn't satisfy the PodAffinity because of unmatching labelSelector with the existing pod",
+                  pod(labels=podLabel, affinity={"podAffinity": aff(term(svc_in("antivirusscan", "value2"), ""))}),
+                  n1(), ex(), False, [A, B])
+        CASES[-1]["expect"]["error"] = "Cannot schedule pod onto node, because of PodAffinityTerm"
         multi_ok = aff(term(sel(expr("service", "Exists"), expr("wrongkey", "DoesNotExist")), "region"),
                        term(sel(expr("service", "In", "securityscan"), expr("service", "NotIn", "WrongValue")), "region"))
         predicate(M, src, "different label Operators in multiple required terms",
@@ -409,6 +421,10 @@ def builders(g):
             CASES.append({"op": "stream", "source": src, "test": "test priority of " + test, "weights": w,
                           "cluster": {"nodes": nodes(), "existingPods": existing(), "pods": [pod(containers=c)]},
                           "expect": {"scores": [score], "host_in": [["machine1", "machine2"]]}})
+        # "we're not just getting the same score no matter what we schedule" (:505-514, :548-551)
+        CASES.append({"op": "stream", "source": src, "test": "test priority of larger pod", "weights": w,
+                      "cluster": {"nodes": nodes(), "existingPods": existing(), "pods": [pod(containers=large)]},
+                      "expect": {"scores_not": [25], "host_in": [["machine1", "machine2"]]}})
 
     return [build_zero_request, build_interpod_priority, build_fits_resources, build_host_ports, build_fits_selector, build_tolerates_taints,
             build_interpod_predicate, build_devices] + g.get("_EXTRA_BUILDERS", [])

@@ -162,5 +162,18 @@ def builders(g):
         predicate(P, src, "host not match", pod(nodeName="machine2"), plain(), [], False, ["HostName"])
         predicate(P, src, "hostport conflict", port_pod(), plain(), [port_pod()], False, ["PodFitsHostPorts"])
 
+    # ----------------------------------------------------------------- FitError text
+    # core/generic_scheduler_test.go:410-426 (TestHumanReadableFitError): one node under memory pressure, two under disk
+    # pressure; here the FailedPredicateMap comes out of a real Schedule call of a best-effort pod
+    def build_fit_error_text():
+        cond = lambda *pairs: [{"type": t, "status": s} for t, s in pairs]
+        CASES.append({"op": "stream", "source": "core/generic_scheduler_test.go:410-426", "test": "human readable FitError",
+                      "cluster": {"nodes": [node("1", 1000, 1 << 30, pods=110, conditions=cond(("MemoryPressure", "True"))),
+                                            node("2", 1000, 1 << 30, pods=110, conditions=cond(("DiskPressure", "True"))),
+                                            node("3", 1000, 1 << 30, pods=110, conditions=cond(("DiskPressure", "True")))],
+                                  "pods": [pod(name="2", containers=[{}])]},
+                      "expect": {"status": [2], "message_contains": [["0/3 nodes are available", "2 NodeUnderDiskPressure",
+                                                                       "1 NodeUnderMemoryPressure"]]}})
+
     return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality,
-            build_select_host, build_general_predicates]
+            build_select_host, build_general_predicates, build_fit_error_text]

@@ -183,6 +183,15 @@ def test_golden_stream_cases_on_gpu():
         if "host_in" in exp:
             for r, allowed in zip(out["results"], exp["host_in"]):
                 assert r["host"] in allowed
+        if "status" in exp:
+            assert [r["status"] for r in out["results"]] == exp["status"], c["test"]
+        if "scores_not" in exp:
+            for r, s in zip(out["results"], exp["scores_not"]):
+                assert r["status"] == 0 and r["score"] != s, (c["test"], r)
+        if "message_contains" in exp:
+            for r, parts in zip(out["results"], exp["message_contains"]):
+                for part in parts:
+                    assert part in r["message"], (c["test"], r)
 
 
 def _as_stream(case):

@@ -44,6 +44,13 @@ def check_case(c, call):
             assert [r["status"] for r in out["results"]] == exp["status"], (out, c["source"], c["test"])
         if "scores" in exp:
             assert [r["score"] for r in out["results"]] == exp["scores"], (out, c["source"], c["test"])
+        if "scores_not" in exp:
+            for r, s in zip(out["results"], exp["scores_not"]):
+                assert r["status"] == 0 and r["score"] != s, (out, c["source"], c["test"])
+        if "message_contains" in exp:
+            for r, parts in zip(out["results"], exp["message_contains"]):
+                for part in parts:
+                    assert part in r["message"], (r, c["source"], c["test"])
     elif c["op"] == "node_info":
         for k, v in exp.items():
             assert out[k] == v, (k, out, c["source"], c["test"])
