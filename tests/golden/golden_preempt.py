@@ -1,7 +1,7 @@
 """Fifth batch of transcriptions of the reference's own tests (see build_fixtures.py): preemption
 (core/generic_scheduler_test.go). Only the cases that plug in the real PodFitsResources predicate are transcribed; the
-ones built on the test's stub predicates (falsePredicate, truePredicate, matchesPredicate) and the anti-affinity case
-have no counterpart here."""
+ones built on the test's stub predicates (falsePredicate, truePredicate, matchesPredicate), the anti-affinity case and
+TestPreempt's two cases with fake extenders have no counterpart here."""
 
 CPU, MEM = 100, 200 * 1024 * 1024  # priorityutil.DefaultMilliCpuRequest, DefaultMemoryRequest (non_zero.go:29-34)
 NEG, LOW, MID, HIGH, VERY_HIGH = -100, 0, 100, 1000, 10000
@@ -95,4 +95,19 @@ def builders(g):
              failed={"machine1": ["MatchNodeSelector", "NodeOutOfDisk", "Insufficient memory"], "machine2": ["HostName", "NoDiskConflict"],
                      "machine3": ["Insufficient memory"], "machine4": []})
 
-    return [build_select_nodes, build_pick_one, build_might_help]
+    # ----------------------------------------------------------------- TestPreempt
+    # core/generic_scheduler_test.go:1083-1217, the two cases without extenders; `failed` is the test's own failedPredMap
+    # (:1084-1088: machine2 carries a reason preemption cannot resolve)
+    def build_preempt():
+        src = "core/generic_scheduler_test.go:1102-1133"
+        n3 = lambda: mk_nodes(["machine1", "machine2", "machine3"])
+        failed = {"machine1": ["Insufficient memory"], "machine2": ["NoDiskConflict"], "machine3": ["Insufficient memory"]}
+        case("basic preemption logic", src, n3(), P("pod1", very_large, HIGH),
+             [P("m1.1", small, LOW, "machine1"), P("m1.2", small, LOW, "machine1"), P("m2.1", large, HIGH, "machine2"),
+              P("m3.1", medium, MID, "machine3")],
+             {"node_in": ["machine1"], "victims": ["m1.1", "m1.2"]}, failed=failed)
+        case("One node doesn't need any preemption", src, n3(), P("pod1", very_large, HIGH),
+             [P("m1.1", small, LOW, "machine1"), P("m1.2", small, LOW, "machine1"), P("m2.1", large, HIGH, "machine2")],
+             {"node_in": ["machine3"], "victims": []}, failed=failed)
+
+    return [build_select_nodes, build_pick_one, build_might_help, build_preempt]

@@ -61,6 +61,8 @@ def check_case(c, call):
             assert got == {n: sorted(vs) for n, vs in exp["candidates"].items()}, (out, c["source"], c["test"])
         if "node_in" in exp:  # pickOneNodeForPreemption: any of the listed nodes
             assert out["node"] in exp["node_in"], (out, c["source"], c["test"])
+        if "victims" in exp:  # Preempt: the pods to evict on the chosen node (generic_scheduler_test.go:1202-1216)
+            assert sorted(v.split("/", 1)[1] for v in out["victims"]) == sorted(exp["victims"]), (out, c["source"], c["test"])
         if "potential" in exp:  # nodesWherePreemptionMightHelp
             assert sorted(out["potential"]) == sorted(exp["potential"]), (out, c["source"], c["test"])
     elif c["op"] == "cache_ops":
