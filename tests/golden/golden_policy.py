@@ -175,5 +175,33 @@ def builders(g):
                       "expect": {"status": [2], "message_contains": [["0/3 nodes are available", "2 NodeUnderDiskPressure",
                                                                        "1 NodeUnderMemoryPressure"]]}})
 
+    # ----------------------------------------------------------------- extender verdicts
+    # core/extender_test.go:188-337 (TestGenericSchedulerWithExtenders). The fake extenders' verdicts are worked out
+    # here as HTTPExtender's caller would hand them on: `keep` = intersection of their Filter results (:108-133),
+    # `scores` = sum over extenders of extender weight * sum over its prioritizers of (score * prioritizer weight)
+    # (:135-158, generic_scheduler.go:608-632). The built-in side is truePredicate + EqualPriority weight 1, as in the
+    # test. "test 1" (an extender returns an error) has no counterpart: the shim fails the call before the engine.
+    # In "test 7" the built-in fake machine2Prioritizer (weight 20) is folded into the scores.
+    def build_extenders():
+        src = "core/extender_test.go:215-306"
+        w = {k: 0 for k in ("LeastRequestedPriority", "BalancedResourceAllocation", "SelectorSpreadPriority",
+                            "NodeAffinityPriority", "TaintTolerationPriority", "InterPodAffinityPriority",
+                            "NodePreferAvoidPodsPriority")}
+        w["EqualPriority"] = 1
+        m = lambda *names: [node(n, 4000, 1 << 33, pods=110) for n in names]
+        for test, names, ext, expect in [
+                ("test 2", ("machine1", "machine2"), {"keep": []}, {"status": [2]}),
+                ("test 3", ("machine1", "machine2"), {"keep": ["machine1"]}, {"status": [0], "hosts": ["machine1"]}),
+                ("test 4", ("machine1", "machine2"), {"keep": []}, {"status": [2]}),
+                ("test 5", ("machine1",), {"keep": ["machine1"]}, {"status": [0], "hosts": ["machine1"]}),
+                ("test 6", ("machine1", "machine2"),
+                 {"keep": ["machine1", "machine2"], "scores": {"machine1": 1 * (10 * 10) + 5 * (1 * 10), "machine2": 1 * (1 * 10) + 5 * (10 * 10)}},
+                 {"status": [0], "hosts": ["machine2"], "scores": [511]}),
+                ("test 7", ("machine1", "machine2"),
+                 {"keep": ["machine1", "machine2"], "scores": {"machine1": 20 * 1 + 1 * (10 * 10), "machine2": 20 * 10 + 1 * (1 * 10)}},
+                 {"status": [0], "hosts": ["machine2"]})]:
+            CASES.append({"op": "stream", "source": src, "test": "extenders: " + test, "weights": w, "extender": ext,
+                          "cluster": {"nodes": m(*names), "pods": [pod(containers=[])]}, "expect": expect})
+
     return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality,
-            build_select_host, build_general_predicates, build_fit_error_text]
+            build_select_host, build_general_predicates, build_fit_error_text, build_extenders]

@@ -91,16 +91,19 @@ def test_extender_verdicts_match_oracle(cfg, nodes, pods):
         so.ksb_destroy(e)
 
 
-def test_select_host_vectors_on_gpu():
-    """TestSelectHost (core/generic_scheduler_test.go:117-181) through the C-ABI: the test's HostPriorityList arrives as
-    the extenders' combined score with every priority weighted 0, ten Schedule + AssumePod rounds per list; the chosen
-    host must be one of the reference's possibleHosts every time, and follow the round-robin order selectHost implies."""
+def test_extender_reference_vectors_on_gpu():
+    """The reference's own vectors that reach the engine as extender verdicts, through the C-ABI: TestSelectHost
+    (core/generic_scheduler_test.go:117-181: the HostPriorityList arrives as the extenders' combined score with every
+    priority weighted 0, ten Schedule + AssumePod rounds per list; the host must be one of possibleHosts every time and
+    follow the round-robin order selectHost implies) and TestGenericSchedulerWithExtenders (core/extender_test.go:188-337:
+    Filter verdicts as the rows kept, Prioritize verdicts as scores, EqualPriority weight 1 on the built-in side)."""
     so = lib.engine()
     so.ksb_schedule_extended.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_uint32),
                                          ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(lib.KsbResult)]
+    so.ksb_policy_set.argtypes = [ctypes.c_void_p, ctypes.c_int32, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int32, ctypes.c_int32]
     with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_vectors.json")) as f:
         cases = [c for c in json.load(f)["cases"] if c["op"] == "stream" and "extender" in c]
-    assert len(cases) == 3
+    assert len(cases) == 9
     for c in cases:
         cfg = lib.KsbConfig()
         so.ksb_config_default(ctypes.byref(cfg))
@@ -111,23 +114,42 @@ def test_select_host_vectors_on_gpu():
         e = so.ksb_create(ctypes.byref(cfg), err, 512)
         assert e, err.value
         try:
+            equal = c["weights"].get("EqualPriority", 0)
+            if equal:
+                assert so.ksb_policy_set(e, 7, None, 0, 0, equal) == 0, so.ksb_last_error(e)
             names = sorted((n["name"] for n in c["cluster"]["nodes"]), key=lambda s: s.encode())
             for n in c["cluster"]["nodes"]:
                 b = wire.node_record(n)
                 assert so.ksb_node_upsert(e, b, len(b)) == 0
-            sarr = (ctypes.c_int32 * len(names))(*[c["extender"]["scores"][nm] for nm in names])
-            got = []
+            ext = c["extender"]
+            sarr = karr = None
+            if "scores" in ext:
+                sarr = (ctypes.c_int32 * len(names))(*[ext["scores"][nm] for nm in names])
+            if "keep" in ext:
+                bits = [0] * ((len(names) + 31) // 32)
+                for r, nm in enumerate(names):
+                    if nm in ext["keep"]:
+                        bits[r >> 5] |= 1 << (r & 31)
+                karr = (ctypes.c_uint32 * len(bits))(*bits)
+            hosts, status, scores = [], [], []
             for pod in c["cluster"]["pods"]:
                 b = wire.pod_record(pod)
                 res = lib.KsbResult()
-                assert so.ksb_schedule_extended(e, b, len(b), None, sarr, ctypes.byref(res)) == 0, so.ksb_last_error(e)
-                assert res.status == 0 and res.num_filtered == len(names), (c["test"], res.status, res.num_filtered)
-                got.append(names[res.node_index])
-                assert res.score == max(c["extender"]["scores"].values()), (c["test"], res.score)
-                placed = wire.pod_record(dict(pod, nodeName=names[res.node_index]))  # AssumePod (scheduler.go:478)
-                assert so.ksb_pod_add(e, placed, len(placed)) == 0, so.ksb_last_error(e)
-            for g, allowed in zip(got, c["expect"]["host_in"]):
-                assert g in allowed, (c["test"], got)
-            assert got == c["expect"]["hosts"], (c["test"], got)
+                assert so.ksb_schedule_extended(e, b, len(b), karr, sarr, ctypes.byref(res)) == 0, so.ksb_last_error(e)
+                status.append(res.status)
+                scores.append(res.score)
+                hosts.append(names[res.node_index] if res.status == 0 else "")
+                if res.status == 0:
+                    placed = wire.pod_record(dict(pod, nodeName=names[res.node_index]))  # AssumePod (scheduler.go:478)
+                    assert so.ksb_pod_add(e, placed, len(placed)) == 0, so.ksb_last_error(e)
+            exp = c["expect"]
+            if "status" in exp:
+                assert status == exp["status"], (c["test"], status)
+            for g, allowed in zip(hosts, exp.get("host_in", [])):
+                assert g in allowed, (c["test"], hosts)
+            if "hosts" in exp:
+                assert hosts == exp["hosts"], (c["test"], hosts)
+            if "scores" in exp:
+                assert scores == exp["scores"], (c["test"], scores)
         finally:
             so.ksb_destroy(e)
