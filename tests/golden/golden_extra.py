@@ -240,6 +240,28 @@ def builders(g):
             CASES.append({"op": "cache_ops", "source": src, "test": "TestAddAndRemovePodExtendedResources: " + test, "ttl": 30,
                           "ops": ops, "report": ["n"], "expect": {"errors": [""] * len(ops), "nodes": {"n": expect}}})
 
+    # ----------------------------------------------------------------- fork: SetNode over a changing device set
+    # schedulercache/node_info_test.go:36-109 (TestSetNode), driven through the cache's AddNode / UpdateNode
+    def build_set_node():
+        src = "schedulercache/node_info_test.go:36-109"
+        r1, r2 = "nvidia.com/gpu", "nvidia.com/bar"
+        dev = lambda i: {"id": i, "health": "Healthy", "attributes": {}}
+        v1_ = node("n", extendedResources={r1: [dev("someId1"), dev("someId2")]})
+        v2_ = node("n", extendedResources={r1: [dev("someId2"), dev("someId3")], r2: [dev("someId1")]})
+        v3_ = node("n", extendedResources={r2: [dev("someId1")]})
+        ops = [{"do": "add_node", "node": v1_}, {"do": "update_node", "node": v2_}, {"do": "update_node", "node": v3_}]
+
+        def info(avail):
+            return {"requested": {"cpu": 0, "memory": 0, "gpu": 0, "ephemeral": 0, "scalars": {}},
+                    "nonzero": {"cpu": 0, "memory": 0}, "pods": 0, "usedPorts": [],
+                    "allocatable": {"cpu": 0, "memory": 0, "pods": 0, "scalars": {}}, "available": avail}
+
+        for k, (test, avail) in enumerate([("two devices of one resource", {r1: ["someId1", "someId2"]}),
+                                           ("a device replaced, a second resource appears", {r1: ["someId2", "someId3"], r2: ["someId1"]}),
+                                           ("a resource the node no longer reports keeps an empty domain", {r1: [], r2: ["someId1"]})]):
+            CASES.append({"op": "cache_ops", "source": src, "test": "TestSetNode: " + test, "ttl": 30, "ops": ops[:k + 1],
+                          "report": ["n"], "expect": {"errors": [""] * (k + 1), "nodes": {"n": info(avail)}}})
+
     # ----------------------------------------------------------------- node add / update / remove
     # schedulercache/cache_test.go:700-893 (TestNodeOperators). Quantities as the API reads them: memory "100m" and
     # "50m" are fractions of a byte and round up to 1 (Quantity.Value()).
@@ -269,4 +291,4 @@ def builders(g):
                               "expect": {"errors": [""] * len(ops), "nodes": {"test-node": info(len(pods_), ports, alloc)}}})
 
     return [build_prefer_avoid, build_hard_affinity_weight, build_fits_host, build_pressure_and_conditions, build_assume_pod,
-            build_cache_ops, build_device_cache, build_node_operators]
+            build_cache_ops, build_device_cache, build_set_node, build_node_operators]
