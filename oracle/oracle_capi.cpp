@@ -455,6 +455,39 @@ static std::string run_preempt(const json::Value& req) {
   return out;
 }
 
+// The small helpers under algorithm/priorities/util that the path leans on (topologies.go:28-75), one call each:
+// {"fn": "same_topology", "nodeA", "nodeB", "key"} | {"fn": "term_namespaces", "pod", "term"} |
+// {"fn": "ns_selector_match", "pod", "namespaces": [...], "selector": LabelSelector}
+static std::string run_helper(const json::Value& req) {
+  const std::string fn = req.get_str("fn");
+  if (fn == "same_topology") {
+    ksb::Node a = ksb::node_from_json(*req.find("nodeA")), b = ksb::node_from_json(*req.find("nodeB"));
+    return std::string("{\"result\":") + (nodes_have_same_topology_key(a, b, req.get_str("key")) ? "true" : "false") + "}";
+  }
+  if (fn == "term_namespaces") {
+    ksb::Pod pod = ksb::pod_from_json(*req.find("pod"));
+    ksb::PodAffinityTerm term = ksb::detail::pod_term(*req.find("term"));
+    std::string out = "{\"result\":[";
+    bool first = true;
+    for (auto& n : namespaces_from_term(pod, term)) {
+      if (!first) out += ",";
+      first = false;
+      json::escape_to(out, n);
+    }
+    return out + "]}";
+  }
+  if (fn == "ns_selector_match") {
+    ksb::Pod pod = ksb::pod_from_json(*req.find("pod"));
+    std::set<std::string> nss;
+    for (auto& n : req.get_arr("namespaces")) nss.insert(n.s);
+    Selector sel;
+    std::string err;
+    if (!label_selector_as_selector(ksb::detail::label_selector(req.find("selector")), &sel, &err)) return "{\"error\":\"selector\"}";
+    return std::string("{\"result\":") + (pod_matches_ns_and_selector(pod, nss, sel) ? "true" : "false") + "}";
+  }
+  return "{\"error\":\"unknown helper\"}";
+}
+
 // Generic entry: {"op": "stream" | "priority" | "predicate" | "device_match" | "node_info" | "preempt", ...}.
 // Returns a malloc'd NUL-terminated JSON string; free with oracle_free.
 char* oracle_call(const char* json_in) {
@@ -469,6 +502,7 @@ char* oracle_call(const char* json_in) {
     else if (op == "node_info") out = run_node_info(req);
     else if (op == "cache_ops") out = run_cache_ops(req);
     else if (op == "preempt") out = run_preempt(req);
+    else if (op == "helper") out = run_helper(req);
     else out = "{\"error\":\"unknown op\"}";
   } catch (const std::exception& e) {
     out = "{\"error\":";

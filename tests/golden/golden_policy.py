@@ -203,5 +203,35 @@ def builders(g):
             CASES.append({"op": "stream", "source": src, "test": "extenders: " + test, "weights": w, "extender": ext,
                           "cluster": {"nodes": m(*names), "pods": [pod(containers=[])]}, "expect": expect})
 
+    # ----------------------------------------------------------------- topology helpers
+    # algorithm/priorities/util/topologies_test.go:41-260
+    def build_topology_helpers():
+        src = "algorithm/priorities/util/topologies_test.go"
+        fake = lambda **kw: dict({"name": "topologies_pod", "namespace": "default"}, **kw)
+
+        def helper(test, lines, expect, **req):
+            CASES.append(dict({"op": "helper", "source": "%s:%s" % (src, lines), "test": test, "expect": {"result": expect}}, **req))
+
+        helper("podAffinityTerm_namespace_empty", "41-66", ["default"], fn="term_namespaces", pod=fake(), term={})
+        helper("podAffinityTerm_namespace_not_empty", "41-66", ["kube-public", "kube-system"], fn="term_namespaces", pod=fake(),
+               term={"namespaces": ["kube-public", "kube-system"]})
+        sel_ = {"matchExpressions": [{"key": "service", "op": "In", "values": ["topologies_service1", "topologies_service2"]}]}
+        for test, ns, labels, want in [("namespace_not_in", "default", {"service": "topologies_service1"}, False),
+                                       ("label_not_match", "kube-public", {"service": "topologies_service3"}, False),
+                                       ("normal_case", "kube-public", {"service": "topologies_service1"}, True)]:
+            helper(test, "68-109", want, fn="ns_selector_match", pod=fake(namespace=ns, labels=labels),
+                   namespaces=["kube-public", "kube-system"], selector=sel_)
+        n = lambda labels=None: ({"name": "n", "labels": labels} if labels is not None else {"name": "n"})
+        for test, a, b, key, want in [
+                ("nodeA{'a':'a'} vs. empty label in nodeB", n({"a": "a"}), n(), "a", False),
+                ("nodeA{'a':'a'} vs. nodeB{'a':'a'}", n({"a": "a"}), n({"a": "a"}), "a", True),
+                ("nodeA{'a':''} vs. empty label in nodeB", n({"a": ""}), n(), "a", False),
+                ("nodeA{'a':''} vs. nodeB{'a':''}", n({"a": ""}), n({"a": ""}), "a", True),
+                ("nodeA{'a':'a'} vs. nodeB{'a':'a'} by key{'b'}", n({"a": "a"}), n({"a": "a"}), "b", False),
+                ("topologyKey empty", n({"a": ""}), n({"a": ""}), "", False),
+                ("nodeA lable nil vs. nodeB{'a':''} by key('a')", n(), n({"a": ""}), "a", False),
+                ("nodeA{'a':''}  vs. nodeB label is nil by key('a')", n({"a": ""}), n(), "a", False)]:
+            helper(test, "111-260", want, fn="same_topology", nodeA=a, nodeB=b, key=key)
+
     return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality,
-            build_select_host, build_general_predicates, build_fit_error_text, build_extenders]
+            build_select_host, build_general_predicates, build_fit_error_text, build_extenders, build_topology_helpers]

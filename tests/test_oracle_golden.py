@@ -65,6 +65,9 @@ def check_case(c, call):
             assert sorted(v.split("/", 1)[1] for v in out["victims"]) == sorted(exp["victims"]), (out, c["source"], c["test"])
         if "potential" in exp:  # nodesWherePreemptionMightHelp
             assert sorted(out["potential"]) == sorted(exp["potential"]), (out, c["source"], c["test"])
+    elif c["op"] == "helper":
+        assert "error" not in out, out
+        assert out["result"] == exp["result"], (out, c["source"], c["test"])
     elif c["op"] == "cache_ops":
         assert out["errors"] == exp["errors"], (out["errors"], c["source"], c["test"])
         assert out["nodes"] == exp["nodes"], (out["nodes"], c["source"], c["test"])
