@@ -485,6 +485,28 @@ static std::string run_helper(const json::Value& req) {
     if (!label_selector_as_selector(ksb::detail::label_selector(req.find("selector")), &sel, &err)) return "{\"error\":\"selector\"}";
     return std::string("{\"result\":") + (pod_matches_ns_and_selector(pod, nss, sel) ? "true" : "false") + "}";
   }
+  if (fn == "nonzero_requests") {  // non_zero.go:36-50 on one container's requests
+    ksb::Pod pod = ksb::pod_from_json(*req.find("pod"));
+    int64_t cpu = 0, mem = 0;
+    get_nonzero_requests(pod.containers.at(0).requests, &cpu, &mem);
+    return "{\"result\":[" + std::to_string(cpu) + "," + std::to_string(mem) + "]}";
+  }
+  if (fn == "pod_priority") {  // util/utils.go:76-87
+    return "{\"result\":" + std::to_string(ksb::pod_from_json(*req.find("pod")).priority) + "}";
+  }
+  if (fn == "sort_by_priority") {  // util.SortableList{CompFunc: HigherPriorityPod}.Sort() = go1.9 sort.Sort (util/utils.go:89-135)
+    std::vector<int64_t> prio;
+    for (auto& x : req.get_arr("priorities")) prio.push_back(x.i);
+    std::vector<int> order(prio.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+    GoSort gs;
+    gs.less = [&](int i, int j) { return prio[order[i]] > prio[order[j]]; };
+    gs.swap = [&](int i, int j) { std::swap(order[i], order[j]); };
+    gs.sort((int)order.size());
+    std::string out = "{\"result\":[";
+    for (size_t i = 0; i < order.size(); ++i) out += (i ? "," : "") + std::to_string(order[i]);
+    return out + "]}";
+  }
   return "{\"error\":\"unknown helper\"}";
 }
 

@@ -233,5 +233,25 @@ def builders(g):
                 ("nodeA{'a':''}  vs. nodeB label is nil by key('a')", n({"a": ""}), n(), "a", False)]:
             helper(test, "111-260", want, fn="same_topology", nodeA=a, nodeB=b, key=key)
 
+    # ----------------------------------------------------------------- small utilities
+    # algorithm/priorities/util/non_zero_test.go:27-74, util/utils_test.go:25-104
+    def build_utilities():
+        def helper(src, test, expect, **req):
+            CASES.append(dict({"op": "helper", "source": src, "test": test, "expect": {"result": expect}}, **req))
+
+        DC, DM = 100, 200 * 1024 * 1024
+        src = "algorithm/priorities/util/non_zero_test.go:27-74"
+        for test, requests, want in [("cpu_and_memory_not_found", {}, [DC, DM]), ("only_cpu_exist", {"cpu": 200}, [200, DM]),
+                                     ("only_memory_exist", {"memory": 400 << 20}, [DC, 400 << 20]),
+                                     ("cpu_memory_exist", {"cpu": 200, "memory": 400 << 20}, [200, 400 << 20])]:
+            helper(src, test, want, fn="nonzero_requests", pod=pod(containers=[{"requests": requests}]))
+        src = "util/utils_test.go:25-59"
+        helper(src, "no priority pod resolves to static default priority", 0, fn="pod_priority", pod=pod(containers=[{}]))
+        helper(src, "pod with priority resolves correctly", 20, fn="pod_priority", pod=pod(containers=[{}], priority=20))
+        # TestSortableList: ten pods of priorities 0..9 in that order, sorted by HigherPriorityPod: 9 first
+        helper("util/utils_test.go:61-104", "SortableList sorts by decreasing priority", list(range(9, -1, -1)),
+               fn="sort_by_priority", priorities=list(range(10)))
+
     return [build_most_requested, build_node_label, build_resource_limits, build_label_presence, build_image_locality,
-            build_select_host, build_general_predicates, build_fit_error_text, build_extenders, build_topology_helpers]
+            build_select_host, build_general_predicates, build_fit_error_text, build_extenders, build_topology_helpers,
+            build_utilities]
