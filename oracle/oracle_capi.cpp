@@ -491,6 +491,24 @@ static std::string run_helper(const json::Value& req) {
     get_nonzero_requests(pod.containers.at(0).requests, &cpu, &mem);
     return "{\"result\":[" + std::to_string(cpu) + "," + std::to_string(mem) + "]}";
   }
+  if (fn == "priority_meta") {  // priorities/metadata.go:45-66: non-zero request totals and the PreferNoSchedule tolerations
+    Oracle o;
+    Oracle::PriorityMeta pm = o.make_priority_meta(ksb::pod_from_json(*req.find("pod")));
+    std::string out = "{\"result\":{\"nonzero\":[" + std::to_string(pm.nonZeroCPU) + "," + std::to_string(pm.nonZeroMem) + "],\"tolerations\":[";
+    for (size_t i = 0; i < pm.tolerationsPreferNoSchedule.size(); ++i) {
+      out += i ? ",[" : "[";
+      const ksb::Toleration& t = pm.tolerationsPreferNoSchedule[i];
+      json::escape_to(out, t.key);
+      out += ",";
+      json::escape_to(out, t.op);
+      out += ",";
+      json::escape_to(out, t.value);
+      out += ",";
+      json::escape_to(out, t.effect);
+      out += "]";
+    }
+    return out + "]}}";
+  }
   if (fn == "pod_priority") {  // util/utils.go:76-87
     return "{\"result\":" + std::to_string(ksb::pod_from_json(*req.find("pod")).priority) + "}";
   }

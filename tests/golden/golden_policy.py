@@ -248,6 +248,18 @@ def builders(g):
         src = "util/utils_test.go:25-59"
         helper(src, "no priority pod resolves to static default priority", 0, fn="pod_priority", pod=pod(containers=[{}]))
         helper(src, "pod with priority resolves correctly", 20, fn="pod_priority", pod=pod(containers=[{}], priority=20))
+        # algorithm/priorities/metadata_test.go:32-160 (the nil pod of its first case has no counterpart)
+        src = "algorithm/priorities/metadata_test.go:118-145"
+        tol = [{"key": "foo", "operator": "Equal", "value": "bar", "effect": "PreferNoSchedule"}]
+        tol_out = [["foo", "Equal", "bar", "PreferNoSchedule"]]
+        aff = {"podAffinity": {"preferred": [{"weight": 5, "term": {"selector": {"matchExpressions": [
+            {"key": "security", "op": "In", "values": ["S1"]}]}, "topologyKey": "region"}}]}}
+        helper(src, "Produce a priorityMetadata with default requests", {"nonzero": [DC, DM], "tolerations": tol_out},
+               fn="priority_meta", pod=pod(containers=[{}], affinity=aff, tolerations=tol))
+        helper(src, "Produce a priorityMetadata with specified requests (tolerations)", {"nonzero": [200, 2000], "tolerations": tol_out},
+               fn="priority_meta", pod=pod(containers=[ctr(200, 2000)], tolerations=tol))
+        helper(src, "Produce a priorityMetadata with specified requests (affinity)", {"nonzero": [200, 2000], "tolerations": []},
+               fn="priority_meta", pod=pod(containers=[ctr(200, 2000)], affinity=aff))
         # TestSortableList: ten pods of priorities 0..9 in that order, sorted by HigherPriorityPod: 9 first
         helper("util/utils_test.go:61-104", "SortableList sorts by decreasing priority", list(range(9, -1, -1)),
                fn="sort_by_priority", priorities=list(range(10)))
