@@ -402,9 +402,18 @@ __device__ __noinline__ int32_t policy_score_enabled(int32_t w_mr, int32_t w_rl,
                                                      int64_t mem, int64_t acpu, int64_t amem) {
   int32_t s = 0;
   if (w_mr) {
-    const int64_t cs = (acpu == 0 || cpu > acpu) ? 0 : (cpu * 10) / acpu;
-    const int64_t ms = (amem == 0 || mem > amem) ? 0 : (mem * 10) / amem;
-    s += w_mr * (int32_t)((cs + ms) / 2);
+    // most_requested.go:61-75: (requested * 10) / capacity is in [0, 10] here: the number of s in 1..10 with
+    // s * capacity <= requested * 10, ten independent compares instead of the 64-bit division routine
+    auto used = [](int64_t requested, int64_t capacity) -> int64_t {
+      if (capacity == 0 || requested > capacity) return 0;
+      const int64_t num = requested * 10;
+      if (capacity < 0 || num < 0 || capacity >= (1ll << 59)) return num / capacity;  // never for real nodes; Go's own arithmetic
+      int32_t cnt = 0;
+#pragma unroll
+      for (int k = 1; k <= 10; ++k) cnt += (num >= (int64_t)k * capacity) ? 1 : 0;
+      return cnt;
+    };
+    s += w_mr * (int32_t)((used(cpu, acpu) + used(mem, amem)) / 2);
   }
   if (w_rl) {
     const bool c1 = lim_cpu != 0 && acpu != 0 && lim_cpu <= acpu;
