@@ -509,6 +509,19 @@ static std::string run_helper(const json::Value& req) {
     }
     return out + "]}}";
   }
+  if (fn == "used_ports") {  // util/utils.go:33-62 over several pods
+    std::set<std::string> all;
+    for (auto& pj : req.get_arr("pods"))
+      for (auto& x : get_used_ports(ksb::pod_from_json(pj))) all.insert(x);
+    std::string out = "{\"result\":[";
+    bool first = true;
+    for (auto& x : all) {
+      if (!first) out += ",";
+      first = false;
+      json::escape_to(out, x);
+    }
+    return out + "]}";
+  }
   if (fn == "pod_priority") {  // util/utils.go:76-87
     return "{\"result\":" + std::to_string(ksb::pod_from_json(*req.find("pod")).priority) + "}";
   }

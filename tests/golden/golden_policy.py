@@ -260,6 +260,21 @@ def builders(g):
                fn="priority_meta", pod=pod(containers=[ctr(200, 2000)], tolerations=tol))
         helper(src, "Produce a priorityMetadata with specified requests (affinity)", {"nonzero": [200, 2000], "tolerations": []},
                fn="priority_meta", pod=pod(containers=[ctr(200, 2000)], affinity=aff))
+        # algorithm/predicates/predicates_test.go:656-689 (TestGetUsedPorts)
+        src = "algorithm/predicates/predicates_test.go:656-689"
+
+        def ports_pod(*infos):
+            ports = []
+            for i in infos:
+                proto, ip, port = i.split("/")
+                ports.append({"protocol": proto, "hostIP": ip, "hostPort": int(port)})
+            return pod(containers=[{"ports": ports}])
+
+        helper(src, "one pod, one port", ["UDP/127.0.0.1/9090"], fn="used_ports", pods=[ports_pod("UDP/127.0.0.1/9090")])
+        helper(src, "two pods on one machine", ["UDP/127.0.0.1/9090", "UDP/127.0.0.1/9091"], fn="used_ports",
+               pods=[ports_pod("UDP/127.0.0.1/9090"), ports_pod("UDP/127.0.0.1/9091")])
+        helper(src, "two pods, two protocols", ["TCP/0.0.0.0/9090", "UDP/127.0.0.1/9091"], fn="used_ports",
+               pods=[ports_pod("TCP/0.0.0.0/9090"), ports_pod("UDP/127.0.0.1/9091")])
         # TestSortableList: ten pods of priorities 0..9 in that order, sorted by HigherPriorityPod: 9 first
         helper("util/utils_test.go:61-104", "SortableList sorts by decreasing priority", list(range(9, -1, -1)),
                fn="sort_by_priority", priorities=list(range(10)))
