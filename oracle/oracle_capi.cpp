@@ -522,6 +522,26 @@ static std::string run_helper(const json::Value& req) {
     }
     return out + "]}";
   }
+  if (fn == "tolerates_taint") {  // api/core/v1/toleration.go:30-56
+    const json::Value& tj = *req.find("toleration");
+    const json::Value& xj = *req.find("taint");
+    ksb::Toleration tol;
+    tol.key = tj.get_str("key");
+    tol.op = tj.get_str("operator");
+    tol.value = tj.get_str("value");
+    tol.effect = tj.get_str("effect");
+    ksb::Taint taint;
+    taint.key = xj.get_str("key");
+    taint.value = xj.get_str("value");
+    taint.effect = xj.get_str("effect");
+    return std::string("{\"result\":") + (tolerates_taint(tol, taint) ? "true" : "false") + "}";
+  }
+  if (fn == "requirements_match") {  // labels.Requirement.Matches (apimachinery/pkg/labels/selector.go:186-230) over a label set
+    Selector sel;
+    std::string err;
+    if (!requirements_as_selector(ksb::detail::reqs(req.find("reqs")), &sel, &err)) return "{\"error\":\"requirements\"}";
+    return std::string("{\"result\":") + (sel_matches(sel, ksb::detail::strmap(req.find("labels"))) ? "true" : "false") + "}";
+  }
   if (fn == "pod_priority") {  // util/utils.go:76-87
     return "{\"result\":" + std::to_string(ksb::pod_from_json(*req.find("pod")).priority) + "}";
   }

@@ -275,6 +275,33 @@ def builders(g):
                pods=[ports_pod("UDP/127.0.0.1/9090"), ports_pod("UDP/127.0.0.1/9091")])
         helper(src, "two pods, two protocols", ["TCP/0.0.0.0/9090", "UDP/127.0.0.1/9091"], fn="used_ports",
                pods=[ports_pod("TCP/0.0.0.0/9090"), ports_pod("UDP/127.0.0.1/9091")])
+        # staging/src/k8s.io/api/core/v1/toleration_test.go:23-125 (TestTolerationToleratesTaint); paths outside the
+        # scheduler tree are given from the repository root
+        src = "/staging/src/k8s.io/api/core/v1/toleration_test.go:23-125"
+        NS, NE = "NoSchedule", "NoExecute"
+        for test, tol_, taint, want in [
+                ("same key and effect, Exists, taint has no value", ("foo", "Exists", "", NS), ("foo", "", NS), True),
+                ("same key and effect, Exists, taint has some value", ("foo", "Exists", "", NS), ("foo", "bar", NS), True),
+                ("empty key with Exists matches all taints", ("", "Exists", "", NS), ("foo", "bar", NS), True),
+                ("same key, effect and value, Equal", ("foo", "Equal", "bar", NS), ("foo", "bar", NS), True),
+                ("different values, Equal", ("foo", "Equal", "value1", NS), ("foo", "value2", NS), False),
+                ("different effects, Equal", ("foo", "Equal", "bar", NS), ("foo", "bar", NE), False)]:
+            helper(src, test, want, fn="tolerates_taint",
+                   toleration=dict(zip(("key", "operator", "value", "effect"), tol_)), taint=dict(zip(("key", "value", "effect"), taint)))
+        # staging/src/k8s.io/apimachinery/pkg/labels/selector_test.go:379-425 (TestRequirementSelectorMatching; its first
+        # case, a zero-value Requirement, cannot be built through the constructors the path uses)
+        src = "/staging/src/k8s.io/apimachinery/pkg/labels/selector_test.go:379-425"
+        rq = lambda key, op, *values: {"key": key, "op": op, "values": list(values)}
+        for k, (labels_, reqs_, want) in enumerate([
+                ({"x": "foo", "y": "baz"}, [rq("x", "In", "foo"), rq("y", "NotIn", "alpha")], True),
+                ({"x": "foo", "y": "baz"}, [rq("x", "In", "foo"), rq("y", "In", "alpha")], False),
+                ({"y": ""}, [rq("x", "NotIn", ""), rq("y", "Exists")], True),
+                ({"y": ""}, [rq("x", "DoesNotExist"), rq("y", "Exists")], True),
+                ({"y": ""}, [rq("x", "NotIn", ""), rq("y", "DoesNotExist")], False),
+                ({"y": "baz"}, [rq("x", "In", "")], False),
+                ({"z": "2"}, [rq("z", "Gt", "1")], True),
+                ({"z": "v2"}, [rq("z", "Gt", "1")], False)]):
+            helper(src, "requirement selector matching, case %d" % (k + 2), want, fn="requirements_match", labels=labels_, reqs=reqs_)
         # TestSortableList: ten pods of priorities 0..9 in that order, sorted by HigherPriorityPod: 9 first
         helper("util/utils_test.go:61-104", "SortableList sorts by decreasing priority", list(range(9, -1, -1)),
                fn="sort_by_priority", priorities=list(range(10)))
