@@ -1,6 +1,7 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY. C entry points (JSON in, JSON out) so the
 // Python tests and bench.py's cpu_baseline leg can drive the CPU restatement.
 // Nothing under kubernetes_b200/ may include or link this.
+#include <algorithm>
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
@@ -541,6 +542,33 @@ static std::string run_helper(const json::Value& req) {
     std::string err;
     if (!requirements_as_selector(ksb::detail::reqs(req.find("reqs")), &sel, &err)) return "{\"error\":\"requirements\"}";
     return std::string("{\"result\":") + (sel_matches(sel, ksb::detail::strmap(req.find("labels"))) ? "true" : "false") + "}";
+  }
+  if (fn == "requirements_selector" || fn == "label_selector") {
+    // NodeSelectorRequirementsAsSelector (pkg/apis/core/v1/helper/helpers.go:212-242) / LabelSelectorAsSelector
+    // (apimachinery/pkg/apis/meta/v1/helpers.go:31-67); the selector's requirements sorted by key, as labels.Parse leaves them
+    Selector sel;
+    std::string err;
+    const bool ok = fn == "label_selector" ? label_selector_as_selector(ksb::detail::label_selector(req.find("selector")), &sel, &err)
+                                           : requirements_as_selector(ksb::detail::reqs(req.find("reqs")), &sel, &err);
+    if (!ok) return "{\"result\":{\"error\":true}}";
+    std::sort(sel.reqs.begin(), sel.reqs.end(), [](const Requirement& a, const Requirement& b) { return a.key < b.key; });
+    static const char* names[] = {"In", "NotIn", "Equals", "Exists", "DoesNotExist", "Gt", "Lt"};
+    std::string out = std::string("{\"result\":{\"nothing\":") + (sel.nothing ? "true" : "false") + ",\"reqs\":[";
+    for (size_t i = 0; i < sel.reqs.size(); ++i) {
+      out += i ? ",[" : "[";
+      json::escape_to(out, sel.reqs[i].key);
+      out += ",";
+      json::escape_to(out, names[(int)sel.reqs[i].op]);
+      out += ",[";
+      std::vector<std::string> vals = sel.reqs[i].values;
+      std::sort(vals.begin(), vals.end());
+      for (size_t k = 0; k < vals.size(); ++k) {
+        if (k) out += ",";
+        json::escape_to(out, vals[k]);
+      }
+      out += "]]";
+    }
+    return out + "]}}";
   }
   if (fn == "pod_priority") {  // util/utils.go:76-87
     return "{\"result\":" + std::to_string(ksb::pod_from_json(*req.find("pod")).priority) + "}";

@@ -302,6 +302,27 @@ def builders(g):
                 ({"z": "2"}, [rq("z", "Gt", "1")], True),
                 ({"z": "v2"}, [rq("z", "Gt", "1")], False)]):
             helper(src, "requirement selector matching, case %d" % (k + 2), want, fn="requirements_match", labels=labels_, reqs=reqs_)
+        # pkg/apis/core/v1/helper/helpers_test.go:246-308 (TestNodeSelectorRequirementsAsSelector)
+        src = "/pkg/apis/core/v1/helper/helpers_test.go:246-308"
+        for test, reqs_, want in [
+                ("no requirements select nothing", [], {"nothing": True, "reqs": []}),
+                ("In with two values", [rq("foo", "In", "bar", "baz")], {"nothing": False, "reqs": [["foo", "In", ["bar", "baz"]]]}),
+                ("Exists with values is an error", [rq("foo", "Exists", "bar", "baz")], {"error": True}),
+                ("Gt", [rq("foo", "Gt", "1")], {"nothing": False, "reqs": [["foo", "Gt", ["1"]]]}),
+                ("Lt", [rq("bar", "Lt", "7")], {"nothing": False, "reqs": [["bar", "Lt", ["7"]]]})]:
+            helper(src, "NodeSelectorRequirementsAsSelector: " + test, want, fn="requirements_selector", reqs=reqs_)
+        # staging/src/k8s.io/apimachinery/pkg/apis/meta/v1/helpers_test.go:27-84 (TestLabelSelectorAsSelector)
+        src = "/staging/src/k8s.io/apimachinery/pkg/apis/meta/v1/helpers_test.go:27-84"
+        ml, me = {"foo": "bar"}, [rq("baz", "In", "qux", "norf")]
+        for test, sel_in, want in [
+                ("nil selects nothing", None, {"nothing": True, "reqs": []}),
+                ("empty selects everything", {}, {"nothing": False, "reqs": []}),
+                ("matchLabels", {"matchLabels": ml}, {"nothing": False, "reqs": [["foo", "Equals", ["bar"]]]}),
+                ("matchExpressions", {"matchExpressions": me}, {"nothing": False, "reqs": [["baz", "In", ["norf", "qux"]]]}),
+                ("both", {"matchLabels": ml, "matchExpressions": me},
+                 {"nothing": False, "reqs": [["baz", "In", ["norf", "qux"]], ["foo", "Equals", ["bar"]]]}),
+                ("Exists with values is an error", {"matchExpressions": [rq("baz", "Exists", "qux", "norf")]}, {"error": True})]:
+            helper(src, "LabelSelectorAsSelector: " + test, want, fn="label_selector", selector=sel_in)
         # TestSortableList: ten pods of priorities 0..9 in that order, sorted by HigherPriorityPod: 9 first
         helper("util/utils_test.go:61-104", "SortableList sorts by decreasing priority", list(range(9, -1, -1)),
                fn="sort_by_priority", priorities=list(range(10)))
